@@ -1,0 +1,117 @@
+// common.cuh — shared device helpers and host error plumbing for libb2llm.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include "../../include/b2llm.h"
+
+// ---------------------------------------------------------------- host error plumbing
+void b2_set_error(const char *fmt, ...);
+#define B2_CUDA(expr)                                                                         \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess) {                                                              \
+            b2_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return B2_ECUDA;                                                                  \
+        }                                                                                     \
+    } while (0)
+#define B2_CHECK(cond, code, ...)                                                             \
+    do {                                                                                      \
+        if (!(cond)) { b2_set_error(__VA_ARGS__); return (code); }                            \
+    } while (0)
+#define B2_TRY(expr)                                                                          \
+    do { int _r = (expr); if (_r != B2_OK) return _r; } while (0)
+
+// ---------------------------------------------------------------- block geometry
+#define QK        32      // weights per Q4_0 / Q8_0 block and per activation block
+#define QK_K      256     // weights per K-quant super-block
+#define ACT_BITS  20      // |X| <= 2^20 on the activation grid
+#define PAGE_TOKENS 16    // tokens per KV page
+
+// Activation vector on the block-fixed-point grid (numerics contract):
+// per 32 elements: 3 planes of int8 digits (balanced base 128), scale = 2^e (float), sum of X (int32).
+// Memory image for n elements (nb = n/32):  int8 dig[nb][3][32] | float scale[nb] | int32 bsum[nb]
+struct ActView {
+    const int8_t *dig;
+    const float *scale;
+    const int32_t *bsum;
+};
+__host__ __device__ inline uint64_t act_bytes(int64_t n) { return (uint64_t)(n / QK) * (96 + 8); }
+__host__ __device__ inline ActView act_view(const void *p, int64_t n) {
+    ActView v;
+    v.dig = (const int8_t *)p;
+    v.scale = (const float *)((const char *)p + (n / QK) * 96);
+    v.bsum = (const int32_t *)((const char *)p + (n / QK) * 100);
+    return v;
+}
+
+// Packed Q4_0 matrix: uint4 qs[rows][nb] (GGML nibble order kept) | half d[rows][nb]
+__host__ __device__ inline uint64_t q4_0_packed_bytes(int64_t rows, int64_t cols) { return (uint64_t)rows * (cols / QK) * 18; }
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- warp helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+// dot of 4 unsigned bytes (weights 0..15) with 4 signed bytes (activation digits)
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp4a_ss(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {  // weights: read once, keep out of L1
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+
+// Activation grid, one block of 32 per warp: lane holds x; returns X (integer on the grid) and the
+// block's scale 2^(e-19), e = max(floor(log2 max|x|), -100).  Matches oracle/model.py:fxp_round.
+__device__ __forceinline__ int act_grid_lane(float x, float &scale_out) {
+    float m = warp_max(fabsf(x));
+    int e = (int)((__float_as_uint(m) >> 23) & 0xFF) - 127;   // floor(log2 m) for normal m
+    e = max(e, -100);
+    // scale = 2^(e-19), inv = 2^(19-e): both exact powers of two, exponent fields in range
+    scale_out = __uint_as_float((uint32_t)(e - (ACT_BITS - 1) + 127) << 23);
+    float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - e + 127) << 23);
+    return __float2int_rn(x * inv);
+}
+// split X into balanced base-128 digits
+__device__ __forceinline__ void act_digits(int X, int &d0, int &d1, int &d2) {
+    d0 = ((X + 64) & 127) - 64;
+    int X1 = (X - d0) >> 7;
+    d1 = ((X1 + 64) & 127) - 64;
+    d2 = (X1 - d1) >> 7;
+}
+// store one block (warp-cooperative): lane = element index in block
+__device__ __forceinline__ void act_store_block(void *act, int64_t n, int64_t blk, int lane, int X, float scale) {
+    int d0, d1, d2;
+    act_digits(X, d0, d1, d2);
+    int8_t *dig = (int8_t *)act + blk * 96;
+    dig[lane] = (int8_t)d0;
+    dig[32 + lane] = (int8_t)d1;
+    dig[64 + lane] = (int8_t)d2;
+    int s = X;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+        ((float *)((char *)act + (n / QK) * 96))[blk] = scale;
+        ((int32_t *)((char *)act + (n / QK) * 100))[blk] = s;
+    }
+}
+#endif

@@ -1,0 +1,732 @@
+// engine.cu — model / session objects and the C ABI of libb2llm (include/b2llm.h).
+// Replaces what happens inside Ollama's POST /api/generate (reference call site
+// experiment/RunnerConfig.py:128-131): model load, prompt evaluation, the batch-1 decode loop.
+#include "kernels.cuh"
+#include "randinit.cuh"
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <vector>
+#include <string>
+#include <map>
+
+// ------------------------------------------------------------------------------------ errors
+static thread_local char g_err[1024] = "";
+void b2_set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+extern "C" const char *b2_last_error(void) { return g_err; }
+extern "C" const char *b2_version(void) { return "b2llm 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------------------------ objects
+struct b2_engine {
+    int device = 0, tp_rank = 0, tp_size = 1;
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+};
+struct Mat {
+    void *packed = nullptr;
+    int64_t rows = 0, cols = 0;
+    int type = B2_T_Q4_0;
+};
+struct LayerW {
+    float *attn_norm = nullptr, *ffn_norm = nullptr, *qkv_bias = nullptr;
+    Mat qkv, o, gateup, down;
+};
+struct b2_model {
+    b2_engine *e = nullptr;
+    b2_arch_cfg cfg{};
+    Mat embd, head;
+    float *out_norm = nullptr;
+    std::vector<LayerW> layers;
+    float *rope_cos = nullptr, *rope_sin = nullptr;
+    uint64_t weight_bytes = 0;
+    std::vector<void *> allocs;
+    int q_dim() const { return cfg.n_heads * cfg.head_dim; }
+    int kv_dim() const { return cfg.n_kv_heads * cfg.head_dim; }
+};
+enum { G_PREFILL_BODY = 0, G_PREFILL_LAST, G_DECODE, G_DECODE_LOG, G_FORCED, G_COUNT };
+struct b2_session {
+    b2_model *m = nullptr;
+    int max_ctx = 0, n_pages = 0;
+    __half *kcache = nullptr, *vcache = nullptr;   // [L][n_pages][nkv][PAGE_TOKENS][hd]
+    int32_t *page_table = nullptr;
+    DevState *state = nullptr;
+    int *d_prompt = nullptr;
+    int prompt_cap = 0;
+    int *d_out_tokens = nullptr;
+    int out_cap = 0;
+    int *d_sampled = nullptr;
+    float *x = nullptr, *qkv = nullptr, *attn_out = nullptr, *h = nullptr, *logits = nullptr;
+    void *act_a = nullptr, *act_b = nullptr, *attn_scratch = nullptr, *argmax_scratch = nullptr;
+    float *logits_log = nullptr;
+    uint64_t logits_log_cap = 0;   // in floats
+    cudaGraphExec_t graphs[G_COUNT] = {};
+    int graph_launches[G_COUNT] = {};
+    bool use_graphs = true;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    b2_stats stats{};
+    int host_pos = 0;
+    bool have_logits = false;
+    std::vector<void *> allocs;
+};
+
+static int dev_alloc(std::vector<void *> &owner, void **p, uint64_t n) {
+    cudaError_t e = cudaMalloc(p, n ? n : 16);
+    if (e != cudaSuccess) {
+        b2_set_error("cudaMalloc(%llu) failed: %s", (unsigned long long)n, cudaGetErrorString(e));
+        return e == cudaErrorMemoryAllocation ? B2_ENOMEM : B2_ECUDA;
+    }
+    owner.push_back(*p);
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------ engine
+extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, const void *nccl_uid, b2_engine **out) {
+    (void)nccl_uid;
+    B2_CHECK(out, B2_EINVAL, "b2_engine_create: out is NULL");
+    B2_CHECK(tp_size == 1 && tp_rank == 0, B2_EINVAL, "b2_engine_create: tensor parallel size %d not supported in this build", tp_size);
+    int n = 0;
+    B2_CUDA(cudaGetDeviceCount(&n));
+    B2_CHECK(device_ordinal >= 0 && device_ordinal < n, B2_EINVAL, "b2_engine_create: device %d of %d", device_ordinal, n);
+    B2_CUDA(cudaSetDevice(device_ordinal));
+    cudaDeviceProp prop;
+    B2_CUDA(cudaGetDeviceProperties(&prop, device_ordinal));
+    B2_CHECK(prop.major == 10, B2_EINVAL, "b2_engine_create: device %d is sm_%d%d; this library is built for sm_100a only", device_ordinal, prop.major, prop.minor);
+    b2_engine *e = new b2_engine();
+    e->device = device_ordinal;
+    e->sm_count = prop.multiProcessorCount;
+    B2_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    *out = e;
+    return B2_OK;
+}
+extern "C" int b2_engine_destroy(b2_engine *e) {
+    if (!e) return B2_OK;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+    return B2_OK;
+}
+extern "C" int b2_engine_device(const b2_engine *e, int *d) {
+    B2_CHECK(e && d, B2_EINVAL, "b2_engine_device: NULL");
+    *d = e->device;
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------ model
+static int check_cfg(const b2_arch_cfg *c) {
+    B2_CHECK(c, B2_EINVAL, "arch cfg is NULL");
+    B2_CHECK(c->hidden > 0 && c->hidden % QK == 0, B2_EINVAL, "hidden %d must be a positive multiple of 32", c->hidden);
+    B2_CHECK(c->ffn > 0 && c->ffn % QK == 0, B2_EINVAL, "ffn %d must be a positive multiple of 32", c->ffn);
+    B2_CHECK(c->head_dim >= 32 && c->head_dim <= 256 && c->head_dim % 32 == 0, B2_EINVAL, "head_dim %d must be a multiple of 32 in [32,256]", c->head_dim);
+    B2_CHECK(c->n_heads > 0 && c->n_kv_heads > 0 && c->n_heads % c->n_kv_heads == 0, B2_EINVAL, "heads %d / kv heads %d", c->n_heads, c->n_kv_heads);
+    B2_CHECK(c->n_layers > 0 && c->vocab > 0, B2_EINVAL, "layers %d vocab %d", c->n_layers, c->vocab);
+    B2_CHECK(c->max_ctx > 0, B2_EINVAL, "max_ctx %d", c->max_ctx);
+    B2_CHECK(c->hidden <= 16384, B2_EINVAL, "hidden %d too large", c->hidden);
+    return B2_OK;
+}
+
+static int build_rope(b2_model *m) {
+    const b2_arch_cfg &c = m->cfg;
+    int half = c.head_dim / 2;
+    std::vector<double> inv(half);
+    for (int j = 0; j < half; ++j) {
+        double f = 1.0 / pow((double)c.rope_theta, (2.0 * j) / c.head_dim);
+        if (c.rope_llama3) {   // Llama-3.1 frequency scaling (oracle/model.py:rope_inv_freq)
+            double factor = c.rope_factor, lo = c.rope_low_freq, hi = c.rope_high_freq, orig = c.rope_orig_ctx;
+            double wavelen = 2.0 * M_PI / f, lo_wl = orig / lo, hi_wl = orig / hi;
+            double scaled = wavelen > lo_wl ? f / factor : f;
+            double smooth = (orig / wavelen - lo) / (hi - lo);
+            double mid = (1.0 - smooth) * f / factor + smooth * f;
+            bool is_mid = !(wavelen < hi_wl) && !(wavelen > lo_wl);
+            f = is_mid ? mid : scaled;
+        }
+        inv[j] = f;
+    }
+    std::vector<float> cs((size_t)c.max_ctx * half), sn((size_t)c.max_ctx * half);
+    for (int p = 0; p < c.max_ctx; ++p)
+        for (int j = 0; j < half; ++j) {
+            double a = (double)p * inv[j];
+            cs[(size_t)p * half + j] = (float)cos(a);
+            sn[(size_t)p * half + j] = (float)sin(a);
+        }
+    B2_TRY(dev_alloc(m->allocs, (void **)&m->rope_cos, cs.size() * 4));
+    B2_TRY(dev_alloc(m->allocs, (void **)&m->rope_sin, sn.size() * 4));
+    B2_CUDA(cudaMemcpy(m->rope_cos, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
+    B2_CUDA(cudaMemcpy(m->rope_sin, sn.data(), sn.size() * 4, cudaMemcpyHostToDevice));
+    return B2_OK;
+}
+
+static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type) {
+    B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "tensor type %d not supported (Q4_0 only in this build)", type);
+    mat.rows = rows;
+    mat.cols = cols;
+    mat.type = type;
+    return dev_alloc(m->allocs, &mat.packed, q4_0_packed_bytes(rows, cols));
+}
+
+static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype, int head_qtype, b2_model **out) {
+    B2_CHECK(e && out, B2_EINVAL, "NULL engine/out");
+    B2_TRY(check_cfg(cfg));
+    B2_CUDA(cudaSetDevice(e->device));
+    b2_model *m = new b2_model();
+    m->e = e;
+    m->cfg = *cfg;
+    const b2_arch_cfg &c = m->cfg;
+    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
+    int rc = B2_OK;
+    do {
+        if ((rc = alloc_mat(m, m->embd, c.vocab, H, head_qtype))) break;
+        if (c.tied) m->head = m->embd;
+        else if ((rc = alloc_mat(m, m->head, c.vocab, H, head_qtype))) break;
+        if ((rc = dev_alloc(m->allocs, (void **)&m->out_norm, H * 4))) break;
+        m->layers.resize(c.n_layers);
+        for (auto &ly : m->layers) {
+            if ((rc = dev_alloc(m->allocs, (void **)&ly.attn_norm, H * 4))) break;
+            if ((rc = dev_alloc(m->allocs, (void **)&ly.ffn_norm, H * 4))) break;
+            if (c.qkv_bias && (rc = dev_alloc(m->allocs, (void **)&ly.qkv_bias, (qd + 2 * kvd) * 4))) break;
+            if ((rc = alloc_mat(m, ly.qkv, qd + 2 * kvd, H, qtype))) break;
+            if ((rc = alloc_mat(m, ly.o, H, qd, qtype))) break;
+            if ((rc = alloc_mat(m, ly.gateup, 2 * (int64_t)I, H, qtype))) break;
+            if ((rc = alloc_mat(m, ly.down, H, I, qtype))) break;
+        }
+        if (rc) break;
+        if ((rc = build_rope(m))) break;
+    } while (0);
+    if (rc) { b2_model_destroy(m); return rc; }
+    // algorithmic bytes per decoded token: every matmul weight once (4.5 bit/weight), LM head included
+    uint64_t w = 0;
+    for (auto &ly : m->layers) w += q4_0_packed_bytes(ly.qkv.rows, ly.qkv.cols) + q4_0_packed_bytes(ly.o.rows, ly.o.cols) +
+                                    q4_0_packed_bytes(ly.gateup.rows, ly.gateup.cols) + q4_0_packed_bytes(ly.down.rows, ly.down.cols);
+    w += q4_0_packed_bytes(m->head.rows, m->head.cols);
+    m->weight_bytes = w;
+    *out = m;
+    return B2_OK;
+}
+
+extern "C" int b2_model_destroy(b2_model *m) {
+    if (!m) return B2_OK;
+    if (m->e) cudaSetDevice(m->e->device);
+    for (void *p : m->allocs) cudaFree(p);
+    delete m;
+    return B2_OK;
+}
+extern "C" int b2_model_weight_bytes(const b2_model *m, uint64_t *out) {
+    B2_CHECK(m && out, B2_EINVAL, "NULL");
+    *out = m->weight_bytes;
+    return B2_OK;
+}
+
+// tensor ids of the random initialiser (oracle/archs.py:KIND)
+enum { K_EMBD = 0, K_OUT_NORM, K_OUTPUT, K_ATTN_NORM, K_Q, K_K, K_V, K_QB, K_KB, K_VB, K_O, K_FFN_NORM, K_GATE, K_UP, K_DOWN };
+#define GLOBAL_LAYER 0xFFFFu
+static inline uint32_t tid_of(int kind, uint32_t layer) { return layer * 16 + kind; }
+
+extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint64_t seed, int qtype, int head_qtype, b2_model **out) {
+    b2_model *m = nullptr;
+    B2_TRY(alloc_model_skeleton(e, cfg, qtype, head_qtype, &m));
+    const b2_arch_cfg &c = m->cfg;
+    cudaStream_t st = e->stream;
+    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
+    float nsig = 0.1f, noff = c.norm_plus_one ? 0.0f : 1.0f, wsig = 0.02f, bsig = 0.1f;
+    auto key = [&](int kind, uint32_t layer) { return ri_tensor_key(seed, tid_of(kind, layer)); };
+    launch_randinit_q4_0(key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, m->embd.packed, 0, 1, c.vocab, st);
+    if (!c.tied) launch_randinit_q4_0(key(K_OUTPUT, GLOBAL_LAYER), wsig, c.vocab, H, m->head.packed, 0, 1, c.vocab, st);
+    launch_randinit_f32(key(K_OUT_NORM, GLOBAL_LAYER), nsig, noff, H, m->out_norm, st);
+    for (int l = 0; l < c.n_layers; ++l) {
+        LayerW &ly = m->layers[l];
+        launch_randinit_f32(key(K_ATTN_NORM, l), nsig, noff, H, ly.attn_norm, st);
+        launch_randinit_f32(key(K_FFN_NORM, l), nsig, noff, H, ly.ffn_norm, st);
+        int64_t tr = qd + 2 * kvd;
+        launch_randinit_q4_0(key(K_Q, l), wsig, qd, H, ly.qkv.packed, 0, 1, tr, st);
+        launch_randinit_q4_0(key(K_K, l), wsig, kvd, H, ly.qkv.packed, qd, 1, tr, st);
+        launch_randinit_q4_0(key(K_V, l), wsig, kvd, H, ly.qkv.packed, qd + kvd, 1, tr, st);
+        if (c.qkv_bias) {
+            launch_randinit_f32(key(K_QB, l), bsig, 0.f, qd, ly.qkv_bias, st);
+            launch_randinit_f32(key(K_KB, l), bsig, 0.f, kvd, ly.qkv_bias + qd, st);
+            launch_randinit_f32(key(K_VB, l), bsig, 0.f, kvd, ly.qkv_bias + qd + kvd, st);
+        }
+        launch_randinit_q4_0(key(K_O, l), wsig, H, qd, ly.o.packed, 0, 1, H, st);
+        launch_randinit_q4_0(key(K_GATE, l), wsig, I, H, ly.gateup.packed, 0, 2, 2 * (int64_t)I, st);
+        launch_randinit_q4_0(key(K_UP, l), wsig, I, H, ly.gateup.packed, 1, 2, 2 * (int64_t)I, st);
+        launch_randinit_q4_0(key(K_DOWN, l), wsig, H, I, ly.down.packed, 0, 1, H, st);
+    }
+    cudaError_t err = cudaStreamSynchronize(st);
+    if (err == cudaSuccess) err = cudaGetLastError();
+    if (err != cudaSuccess) {
+        b2_set_error("b2_model_create_random: %s", cudaGetErrorString(err));
+        b2_model_destroy(m);
+        return B2_ECUDA;
+    }
+    *out = m;
+    return B2_OK;
+}
+
+struct Staging {
+    void *buf = nullptr;
+    uint64_t cap = 0;
+    ~Staging() { if (buf) cudaFree(buf); }
+    int ensure(uint64_t n) {
+        if (n <= cap) return B2_OK;
+        if (buf) cudaFree(buf);
+        buf = nullptr;
+        cap = 0;
+        B2_CUDA(cudaMalloc(&buf, n));
+        cap = n;
+        return B2_OK;
+    }
+};
+
+static int upload_mat(b2_model *m, Staging &sg, const b2_tensor_desc &t, Mat &dst, int64_t dst_row0, int64_t stride, int64_t src_row0, int64_t nrows) {
+    B2_CHECK(t.type == B2_T_Q4_0, B2_EINVAL, "tensor %s: type %d not supported (Q4_0 only in this build)", t.name, t.type);
+    B2_CHECK(t.cols == dst.cols, B2_EINVAL, "tensor %s: cols %lld, expected %lld", t.name, (long long)t.cols, (long long)dst.cols);
+    uint64_t row_bytes = (uint64_t)(t.cols / QK) * 18;
+    B2_CHECK(t.nbytes == (uint64_t)t.rows * row_bytes, B2_EINVAL, "tensor %s: %llu bytes, expected %llu", t.name, (unsigned long long)t.nbytes, (unsigned long long)(t.rows * row_bytes));
+    B2_CHECK(src_row0 + nrows <= t.rows, B2_EINVAL, "tensor %s: has %lld rows, need %lld", t.name, (long long)t.rows, (long long)(src_row0 + nrows));
+    B2_TRY(sg.ensure(nrows * row_bytes));
+    B2_CUDA(cudaMemcpyAsync(sg.buf, (const char *)t.data + src_row0 * row_bytes, nrows * row_bytes, cudaMemcpyHostToDevice, m->e->stream));
+    launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, dst.rows, m->e->stream);
+    B2_CUDA(cudaStreamSynchronize(m->e->stream));
+    return B2_OK;
+}
+static int upload_vec(b2_model *m, const b2_tensor_desc &t, float *dst, int64_t n) {
+    B2_CHECK(t.type == B2_T_F32 && t.rows == n && t.nbytes == (uint64_t)n * 4, B2_EINVAL, "tensor %s: expected f32[%lld]", t.name, (long long)n);
+    B2_CUDA(cudaMemcpy(dst, t.data, n * 4, cudaMemcpyHostToDevice));
+    (void)m;
+    return B2_OK;
+}
+
+extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_tensor_desc *tensors, int n_tensors, b2_model **out) {
+    B2_CHECK(tensors && n_tensors > 0, B2_EINVAL, "b2_model_create: no tensors");
+    std::map<std::string, const b2_tensor_desc *> by_name;
+    for (int i = 0; i < n_tensors; ++i) {
+        B2_CHECK(tensors[i].name && tensors[i].data, B2_EINVAL, "tensor %d has NULL name/data", i);
+        by_name[tensors[i].name] = &tensors[i];
+    }
+    auto find = [&](const std::string &n) -> const b2_tensor_desc * {
+        auto it = by_name.find(n);
+        return it == by_name.end() ? nullptr : it->second;
+    };
+    const b2_tensor_desc *te = find("token_embd.weight");
+    B2_CHECK(te, B2_EINVAL, "missing tensor token_embd.weight");
+    const b2_tensor_desc *l0 = find("blk.0.attn_q.weight");
+    if (!l0) l0 = find("blk.0.attn_qkv.weight");
+    B2_CHECK(l0, B2_EINVAL, "missing tensor blk.0.attn_q.weight / blk.0.attn_qkv.weight");
+    b2_model *m = nullptr;
+    B2_TRY(alloc_model_skeleton(e, cfg, l0->type, te->type, &m));
+    const b2_arch_cfg &c = m->cfg;
+    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
+    Staging sg;
+    int rc = B2_OK;
+#define NEED(var, name)                                                        \
+    const b2_tensor_desc *var = find(name);                                    \
+    if (!var) { b2_set_error("missing tensor %s", std::string(name).c_str()); rc = B2_EINVAL; break; }
+    do {
+        if ((rc = upload_mat(m, sg, *te, m->embd, 0, 1, 0, c.vocab))) break;
+        NEED(on, "output_norm.weight");
+        if ((rc = upload_vec(m, *on, m->out_norm, H))) break;
+        if (!c.tied) {
+            NEED(ow, "output.weight");
+            if ((rc = upload_mat(m, sg, *ow, m->head, 0, 1, 0, c.vocab))) break;
+        }
+        for (int l = 0; l < c.n_layers && !rc; ++l) {
+            LayerW &ly = m->layers[l];
+            std::string p = "blk." + std::to_string(l) + ".";
+            do {
+                NEED(an, p + "attn_norm.weight");
+                if ((rc = upload_vec(m, *an, ly.attn_norm, H))) break;
+                NEED(fn, p + "ffn_norm.weight");
+                if ((rc = upload_vec(m, *fn, ly.ffn_norm, H))) break;
+                if (const b2_tensor_desc *f = find(p + "attn_qkv.weight")) {
+                    if ((rc = upload_mat(m, sg, *f, ly.qkv, 0, 1, 0, qd + 2 * kvd))) break;
+                } else {
+                    NEED(tq, p + "attn_q.weight");
+                    NEED(tk, p + "attn_k.weight");
+                    NEED(tv, p + "attn_v.weight");
+                    if ((rc = upload_mat(m, sg, *tq, ly.qkv, 0, 1, 0, qd))) break;
+                    if ((rc = upload_mat(m, sg, *tk, ly.qkv, qd, 1, 0, kvd))) break;
+                    if ((rc = upload_mat(m, sg, *tv, ly.qkv, qd + kvd, 1, 0, kvd))) break;
+                }
+                if (c.qkv_bias) {
+                    NEED(bq, p + "attn_q.bias");
+                    NEED(bk, p + "attn_k.bias");
+                    NEED(bv, p + "attn_v.bias");
+                    if ((rc = upload_vec(m, *bq, ly.qkv_bias, qd))) break;
+                    if ((rc = upload_vec(m, *bk, ly.qkv_bias + qd, kvd))) break;
+                    if ((rc = upload_vec(m, *bv, ly.qkv_bias + qd + kvd, kvd))) break;
+                }
+                NEED(to, p + "attn_output.weight");
+                if ((rc = upload_mat(m, sg, *to, ly.o, 0, 1, 0, H))) break;
+                const b2_tensor_desc *tg = find(p + "ffn_gate.weight");
+                NEED(tu, p + "ffn_up.weight");
+                if (tg) {
+                    if ((rc = upload_mat(m, sg, *tg, ly.gateup, 0, 2, 0, I))) break;
+                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 1, 2, 0, I))) break;
+                } else {   // phi3-style fused [gate; up]
+                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 0, 2, 0, I))) break;
+                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 1, 2, I, I))) break;
+                }
+                NEED(td, p + "ffn_down.weight");
+                if ((rc = upload_mat(m, sg, *td, ly.down, 0, 1, 0, H))) break;
+            } while (0);
+        }
+    } while (0);
+#undef NEED
+    if (rc) { b2_model_destroy(m); return rc; }
+    *out = m;
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------ session
+__global__ void k_load_prompt(DevState *st, const int *prompt) {
+    st->cur_token = prompt[st->prompt_idx];
+    st->prompt_idx += 1;
+}
+__global__ void k_commit_sample(DevState *st, const int *sampled, int *out_tokens) {
+    int t = *sampled;
+    st->cur_token = t;
+    out_tokens[st->step] = t;
+}
+__global__ void k_advance(DevState *st, int inc_step) {
+    st->pos += 1;
+    st->step += inc_step;
+}
+__global__ void k_copy_logits(const float *logits, int n, float *log, const DevState *st) {
+    float *dst = log + (int64_t)st->step * n;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = logits[i];
+}
+
+// enqueue one forward pass for the token in state->cur_token at position state->pos; returns #launches
+static int enqueue_forward(b2_session *s, bool with_head) {
+    b2_model *m = s->m;
+    const b2_arch_cfg &c = m->cfg;
+    cudaStream_t st = m->e->stream;
+    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
+    int n = 0;
+    float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
+    launch_embed_q4_0(m->embd.packed, m->embd.rows, m->embd.cols, &s->state->cur_token, escale, s->x, st); n++;
+    uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    for (int l = 0; l < c.n_layers; ++l) {
+        LayerW &ly = m->layers[l];
+        launch_rmsnorm_quant(s->x, ly.attn_norm, H, c.rms_eps, c.norm_plus_one, s->act_a, nullptr, st); n++;
+        launch_gemv_q4_0(ly.qkv.packed, ly.qkv.rows, H, s->act_a, ly.qkv_bias, 0, 0, s->qkv, st); n++;
+        launch_rope_kv(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
+                       s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, st); n++;
+        launch_attn_decode(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, s->kcache + l * layer_kv, s->vcache + l * layer_kv,
+                           s->page_table, s->attn_out, s->attn_scratch, s->max_ctx, st); n++;
+        launch_quant_act(s->attn_out, qd, s->act_b, st); n++;
+        launch_gemv_q4_0(ly.o.packed, H, qd, s->act_b, s->x, 1, 0, s->x, st); n++;
+        launch_rmsnorm_quant(s->x, ly.ffn_norm, H, c.rms_eps, c.norm_plus_one, s->act_a, nullptr, st); n++;
+        launch_gemv_q4_0(ly.gateup.packed, 2 * (int64_t)I, H, s->act_a, nullptr, 2, c.act, s->h, st); n++;
+        launch_quant_act(s->h, I, s->act_b, st); n++;
+        launch_gemv_q4_0(ly.down.packed, H, I, s->act_b, s->x, 1, 0, s->x, st); n++;
+    }
+    if (with_head) {
+        launch_rmsnorm_quant(s->x, m->out_norm, H, c.rms_eps, c.norm_plus_one, s->act_a, nullptr, st); n++;
+        launch_gemv_q4_0(m->head.packed, c.vocab, H, s->act_a, nullptr, 0, 0, s->logits, st); n++;
+    }
+    (void)kvd;
+    return n;
+}
+
+static int enqueue_graph_body(b2_session *s, int which) {
+    cudaStream_t st = s->m->e->stream;
+    int n = 0;
+    switch (which) {
+    case G_PREFILL_BODY:
+    case G_PREFILL_LAST:
+    case G_FORCED:
+        k_load_prompt<<<1, 1, 0, st>>>(s->state, s->d_prompt); n++;
+        n += enqueue_forward(s, which != G_PREFILL_BODY);
+        if (which == G_FORCED) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
+        k_advance<<<1, 1, 0, st>>>(s->state, which == G_FORCED ? 1 : 0); n++;
+        break;
+    case G_DECODE:
+    case G_DECODE_LOG:
+        if (which == G_DECODE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
+        launch_argmax(s->logits, s->m->cfg.vocab, s->d_sampled, s->argmax_scratch, st); n++;
+        k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
+        n += enqueue_forward(s, true);
+        k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
+        break;
+    }
+    return n;
+}
+
+static void drop_graphs(b2_session *s) {
+    for (int g = 0; g < G_COUNT; ++g)
+        if (s->graphs[g]) { cudaGraphExecDestroy(s->graphs[g]); s->graphs[g] = nullptr; }
+}
+
+// run graph `which` `times` times (captured lazily; plain launches when B2_NO_GRAPH=1)
+static int run_graph(b2_session *s, int which, int times) {
+    cudaStream_t st = s->m->e->stream;
+    if (!s->use_graphs) {
+        for (int i = 0; i < times; ++i) s->graph_launches[which] = enqueue_graph_body(s, which);
+        B2_CUDA(cudaGetLastError());
+        s->stats.kernel_launches += (uint64_t)times * s->graph_launches[which];
+        return B2_OK;
+    }
+    if (!s->graphs[which]) {
+        cudaGraph_t g = nullptr;
+        B2_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        s->graph_launches[which] = enqueue_graph_body(s, which);
+        cudaError_t e1 = cudaStreamEndCapture(st, &g);
+        if (e1 != cudaSuccess) { b2_set_error("graph capture failed: %s", cudaGetErrorString(e1)); return B2_ECUDA; }
+        cudaError_t e2 = cudaGraphInstantiate(&s->graphs[which], g, 0);
+        cudaGraphDestroy(g);
+        if (e2 != cudaSuccess) { b2_set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return B2_ECUDA; }
+    }
+    for (int i = 0; i < times; ++i) B2_CUDA(cudaGraphLaunch(s->graphs[which], st));
+    s->stats.kernel_launches += (uint64_t)times * s->graph_launches[which];
+    return B2_OK;
+}
+
+extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
+    B2_CHECK(m && out, B2_EINVAL, "b2_session_create: NULL");
+    B2_CHECK(max_ctx > 0 && max_ctx <= m->cfg.max_ctx, B2_EINVAL, "max_ctx %d out of range (model max %d)", max_ctx, m->cfg.max_ctx);
+    B2_CUDA(cudaSetDevice(m->e->device));
+    const b2_arch_cfg &c = m->cfg;
+    b2_session *s = new b2_session();
+    s->m = m;
+    s->max_ctx = max_ctx;
+    s->n_pages = (max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const char *ng = getenv("B2_NO_GRAPH");
+    s->use_graphs = !(ng && ng[0] == '1');
+    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
+    uint64_t kv_elems = (uint64_t)c.n_layers * s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    int rc = B2_OK;
+    do {
+        if ((rc = dev_alloc(s->allocs, (void **)&s->kcache, kv_elems * 2))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->vcache, kv_elems * 2))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->page_table, s->n_pages * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->state, sizeof(DevState)))) break;
+        s->prompt_cap = max_ctx;
+        s->out_cap = max_ctx;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->d_prompt, s->prompt_cap * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->d_out_tokens, s->out_cap * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->d_sampled, 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->x, H * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->qkv, (qd + 2 * kvd) * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->attn_out, qd * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->h, I * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->logits, (uint64_t)c.vocab * 4))) break;
+        if ((rc = dev_alloc(s->allocs, &s->act_a, act_bytes(H)))) break;
+        if ((rc = dev_alloc(s->allocs, &s->act_b, act_bytes(qd > I ? qd : I)))) break;
+        if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(c.n_heads, hd)))) break;
+        if ((rc = dev_alloc(s->allocs, &s->argmax_scratch, argmax_scratch_bytes()))) break;
+    } while (0);
+    if (rc) { b2_session_destroy(s); return rc; }
+    // physical pages are handed out in reverse order so the page-table indirection is always exercised
+    std::vector<int32_t> pt(s->n_pages);
+    for (int p = 0; p < s->n_pages; ++p) pt[p] = s->n_pages - 1 - p;
+    cudaError_t e = cudaMemcpy(s->page_table, pt.data(), pt.size() * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(s->attn_scratch, 0, attn_scratch_bytes(c.n_heads, hd));
+    if (e == cudaSuccess) e = cudaMemset(s->argmax_scratch, 0, argmax_scratch_bytes());
+    if (e == cudaSuccess) e = cudaMemset(s->state, 0, sizeof(DevState));
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
+    if (e != cudaSuccess) {
+        b2_set_error("b2_session_create: %s", cudaGetErrorString(e));
+        b2_session_destroy(s);
+        return B2_ECUDA;
+    }
+    *out = s;
+    return B2_OK;
+}
+extern "C" int b2_session_destroy(b2_session *s) {
+    if (!s) return B2_OK;
+    if (s->m && s->m->e) cudaSetDevice(s->m->e->device);
+    drop_graphs(s);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->logits_log) cudaFree(s->logits_log);
+    for (void *p : s->allocs) cudaFree(p);
+    delete s;
+    return B2_OK;
+}
+extern "C" int b2_session_reset(b2_session *s) {
+    B2_CHECK(s, B2_EINVAL, "NULL session");
+    B2_CUDA(cudaSetDevice(s->m->e->device));
+    B2_CUDA(cudaStreamSynchronize(s->m->e->stream));
+    B2_CUDA(cudaMemset(s->state, 0, sizeof(DevState)));
+    s->host_pos = 0;
+    s->have_logits = false;
+    uint64_t launches = s->stats.kernel_launches;
+    s->stats = b2_stats{};
+    s->stats.kernel_launches = launches;
+    return B2_OK;
+}
+extern "C" int b2_session_pos(const b2_session *s, int *pos) {
+    B2_CHECK(s && pos, B2_EINVAL, "NULL");
+    *pos = s->host_pos;
+    return B2_OK;
+}
+extern "C" int b2_session_stats(const b2_session *s, b2_stats *out) {
+    B2_CHECK(s && out, B2_EINVAL, "NULL");
+    *out = s->stats;
+    return B2_OK;
+}
+
+static int ensure_log(b2_session *s, uint64_t floats) {
+    if (floats <= s->logits_log_cap) return B2_OK;
+    B2_CUDA(cudaStreamSynchronize(s->m->e->stream));
+    if (s->logits_log) cudaFree(s->logits_log);
+    s->logits_log = nullptr;
+    s->logits_log_cap = 0;
+    // graphs bake the log pointer: re-capture the ones that use it
+    for (int g : {G_DECODE_LOG, G_FORCED})
+        if (s->graphs[g]) { cudaGraphExecDestroy(s->graphs[g]); s->graphs[g] = nullptr; }
+    cudaError_t e = cudaMalloc((void **)&s->logits_log, floats * 4);
+    if (e != cudaSuccess) { b2_set_error("logits log: cudaMalloc(%llu) failed: %s", (unsigned long long)floats * 4, cudaGetErrorString(e)); return B2_ENOMEM; }
+    s->logits_log_cap = floats;
+    return B2_OK;
+}
+
+static int set_step_counters(b2_session *s) {   // step = 0, prompt_idx = 0, keep pos
+    DevState hs;
+    hs.pos = s->host_pos;
+    hs.step = 0;
+    hs.cur_token = 0;
+    hs.prompt_idx = 0;
+    // cur_token is rewritten by the first kernel of every graph, so overwriting it here is harmless
+    B2_CUDA(cudaMemcpyAsync(s->state, &hs, sizeof hs, cudaMemcpyHostToDevice, s->m->e->stream));
+    return B2_OK;
+}
+
+static int elapsed_ns(b2_session *s, uint64_t *ns) {
+    float ms = 0.f;
+    B2_CUDA(cudaEventSynchronize(s->ev1));
+    B2_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    *ns = (uint64_t)((double)ms * 1e6);
+    return B2_OK;
+}
+
+extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *logits_out) {
+    B2_CHECK(s && tokens && n > 0, B2_EINVAL, "b2_prefill: bad arguments");
+    B2_CHECK(s->host_pos + n <= s->max_ctx, B2_ECTX, "b2_prefill: %d + %d tokens exceed the context window %d", s->host_pos, n, s->max_ctx);
+    int V = s->m->cfg.vocab;
+    for (int i = 0; i < n; ++i) B2_CHECK(tokens[i] >= 0 && tokens[i] < V, B2_EINVAL, "b2_prefill: token %d out of range", tokens[i]);
+    cudaStream_t st = s->m->e->stream;
+    B2_CUDA(cudaSetDevice(s->m->e->device));
+    B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    B2_TRY(set_step_counters(s));
+    B2_CUDA(cudaEventRecord(s->ev0, st));
+    if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1));
+    B2_TRY(run_graph(s, G_PREFILL_LAST, 1));
+    B2_CUDA(cudaEventRecord(s->ev1, st));
+    if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits, (size_t)V * 4, cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    uint64_t ns = 0;
+    B2_TRY(elapsed_ns(s, &ns));
+    s->stats.prompt_eval_count += n;
+    s->stats.prompt_eval_ns += ns;
+    s->host_pos += n;
+    s->have_logits = true;
+    return B2_OK;
+}
+
+extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampler, int32_t *out_tokens, float *logits_out) {
+    B2_CHECK(s && out_tokens && n_steps > 0, B2_EINVAL, "b2_decode: bad arguments");
+    B2_CHECK(s->have_logits, B2_EINVAL, "b2_decode: call b2_prefill first");
+    B2_CHECK(!sampler || sampler->top_k <= 1, B2_EINVAL, "b2_decode: only greedy sampling (top_k <= 1) is wired into the decode loop in this build");
+    B2_CHECK(s->host_pos + n_steps <= s->max_ctx, B2_ECTX, "b2_decode: %d + %d tokens exceed the context window %d", s->host_pos, n_steps, s->max_ctx);
+    B2_CHECK(n_steps <= s->out_cap, B2_EINVAL, "b2_decode: n_steps %d > %d", n_steps, s->out_cap);
+    cudaStream_t st = s->m->e->stream;
+    int V = s->m->cfg.vocab;
+    B2_CUDA(cudaSetDevice(s->m->e->device));
+    if (logits_out) B2_TRY(ensure_log(s, (uint64_t)n_steps * V));
+    B2_TRY(set_step_counters(s));
+    B2_CUDA(cudaEventRecord(s->ev0, st));
+    B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps));
+    B2_CUDA(cudaEventRecord(s->ev1, st));
+    B2_CUDA(cudaMemcpyAsync(out_tokens, s->d_out_tokens, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, st));
+    if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n_steps * V * 4, cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    uint64_t ns = 0;
+    B2_TRY(elapsed_ns(s, &ns));
+    s->stats.eval_count += n_steps;
+    s->stats.eval_ns += ns;
+    s->host_pos += n_steps;
+    return B2_OK;
+}
+
+extern "C" int b2_forward_tokens(b2_session *s, const int32_t *tokens, int n, float *logits_out) {
+    B2_CHECK(s && tokens && n > 0, B2_EINVAL, "b2_forward_tokens: bad arguments");
+    B2_CHECK(s->host_pos + n <= s->max_ctx, B2_ECTX, "b2_forward_tokens: context window %d exceeded", s->max_ctx);
+    B2_CHECK(n <= s->prompt_cap, B2_EINVAL, "b2_forward_tokens: n too large");
+    int V = s->m->cfg.vocab;
+    for (int i = 0; i < n; ++i) B2_CHECK(tokens[i] >= 0 && tokens[i] < V, B2_EINVAL, "b2_forward_tokens: token %d out of range", tokens[i]);
+    cudaStream_t st = s->m->e->stream;
+    B2_CUDA(cudaSetDevice(s->m->e->device));
+    B2_TRY(ensure_log(s, (uint64_t)n * V));
+    B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    B2_TRY(set_step_counters(s));
+    B2_TRY(run_graph(s, G_FORCED, n));
+    if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n * V * 4, cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    s->host_pos += n;
+    s->have_logits = true;
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------ host random init
+extern "C" int b2_randinit_tensor(uint64_t seed, uint32_t tensor_id, int64_t rows, int64_t cols, int type, float sigma, float offset,
+                                  int64_t row0, int64_t nrows, void *out, uint64_t out_bytes) {
+    B2_CHECK(out && rows > 0 && row0 >= 0 && nrows >= 0 && row0 + nrows <= rows, B2_EINVAL, "b2_randinit_tensor: bad arguments");
+    uint64_t key = ri_tensor_key(seed, tensor_id);
+    if (cols == 0 || type == B2_T_F32) {
+        int64_t c = cols == 0 ? 1 : cols;
+        int64_t n = nrows * c;
+        B2_CHECK(out_bytes == (uint64_t)n * 4, B2_EINVAL, "b2_randinit_tensor: out_bytes %llu, expected %llu", (unsigned long long)out_bytes, (unsigned long long)n * 4);
+        float *o = (float *)out;
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) o[i] = ri_add(ri_mul(ri_gauss(key, (uint64_t)(row0 * c + i)), sigma), offset);
+        return B2_OK;
+    }
+    B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_randinit_tensor: type %d not supported", type);
+    B2_CHECK(cols % QK == 0, B2_EINVAL, "b2_randinit_tensor: cols %% 32");
+    int64_t nb = cols / QK, n = nrows * nb;
+    B2_CHECK(out_bytes == (uint64_t)n * 18, B2_EINVAL, "b2_randinit_tensor: out_bytes %llu, expected %llu", (unsigned long long)out_bytes, (unsigned long long)n * 18);
+    uint8_t *o = (uint8_t *)out;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        float x[QK];
+        ri_gauss_block(key, (uint64_t)(row0 * nb + i) * QK, sigma, x);
+        uint16_t dbits;
+        uint32_t w[4];
+        ri_quant_q4_0(x, dbits, w);
+        uint8_t *p = o + i * 18;
+        p[0] = (uint8_t)(dbits & 0xFF);
+        p[1] = (uint8_t)(dbits >> 8);
+        memcpy(p + 2, w, 16);
+    }
+    return B2_OK;
+}
+
+// ------------------------------------------------------------------------------------ device helpers
+extern "C" int b2_dev_alloc(uint64_t nbytes, void **d_out) {
+    B2_CHECK(d_out, B2_EINVAL, "NULL");
+    B2_CUDA(cudaMalloc(d_out, nbytes ? nbytes : 16));
+    return B2_OK;
+}
+extern "C" int b2_dev_free(void *p) {
+    if (p) B2_CUDA(cudaFree(p));
+    return B2_OK;
+}
+extern "C" int b2_dev_upload(void *d_dst, const void *src, uint64_t n) {
+    B2_CUDA(cudaMemcpy(d_dst, src, n, cudaMemcpyHostToDevice));
+    return B2_OK;
+}
+extern "C" int b2_dev_download(void *dst, const void *d_src, uint64_t n) {
+    B2_CUDA(cudaMemcpy(dst, d_src, n, cudaMemcpyDeviceToHost));
+    return B2_OK;
+}
+extern "C" int b2_dev_sync(void) {
+    B2_CUDA(cudaDeviceSynchronize());
+    return B2_OK;
+}

@@ -1,0 +1,450 @@
+// kernels.cu — hand-written sm_100a kernels of the batch-1 decode path.
+// Stage map (Ollama call site experiment/RunnerConfig.py:128-131):
+//   embed_q4_0        a3.1  token embedding row (dequant, gemma sqrt(H) scale)
+//   rmsnorm_quant     a3.2  RMSNorm (gemma 1+w) fused with the activation grid
+//   gemv_q4_0         a3.3/a3.6/a3.7/a3.8  QKV(+bias) / O(+res) / gate,up -> act*mul / down(+res) / LM head
+//   rope_kv           a3.4  RoPE + f16 append into the paged KV cache
+//   attn_decode       a3.5  paged attention over the cache (GQA/MQA/MHA), split over the context
+//   argmax            a3.8  greedy sampler
+#include "kernels.cuh"
+#include "randinit.cuh"
+
+// =============================================================================== weight re-pack
+// GGML Q4_0 row-major blocks (18 B: f16 d | 16 B nibbles) -> packed {uint4 qs[rows][nb] | half d[rows][nb]}.
+// One thread per block.  dst row = dst_row0 + r * dst_row_stride (stride 2 interleaves gate/up rows).
+__global__ void k_pack_q4_0(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, uint4 *__restrict__ qs,
+                            __half *__restrict__ d, int64_t dst_row0, int64_t dst_row_stride) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * nb) return;
+    int64_t r = i / nb, b = i - r * nb;
+    const uint8_t *p = src + i * 18;
+    uint16_t dbits = (uint16_t)p[0] | ((uint16_t)p[1] << 8);
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        w[k] = (uint32_t)p[2 + 4 * k] | ((uint32_t)p[3 + 4 * k] << 8) | ((uint32_t)p[4 + 4 * k] << 16) | ((uint32_t)p[5 + 4 * k] << 24);
+    int64_t o = (dst_row0 + r * dst_row_stride) * nb + b;
+    qs[o] = make_uint4(w[0], w[1], w[2], w[3]);
+    d[o] = __ushort_as_half(dbits);
+}
+void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride,
+                      int64_t total_rows, cudaStream_t st) {
+    int64_t nb = cols / QK, n = rows * nb;
+    PackedQ4_0 v = packed_q4_0_view(d_packed, total_rows, cols);
+    k_pack_q4_0<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, (uint4 *)v.qs, (__half *)v.d, dst_row0, dst_row_stride);
+}
+
+// =============================================================================== random init on device
+// Same recipe as oracle/randinit.py and b2_randinit_tensor (randinit.cuh): integer Irwin-Hall gaussian,
+// then the ggml Q4_0 quantiser with explicitly rounded IEEE ops => byte-identical to the host generator.
+__global__ void k_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t nb, uint4 *__restrict__ qs, __half *__restrict__ d,
+                                int64_t dst_row0, int64_t dst_row_stride) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * nb) return;
+    int64_t r = i / nb, b = i - r * nb;
+    float x[QK];
+    ri_gauss_block(key, (uint64_t)i * QK, sigma, x);
+    uint16_t dbits;
+    uint32_t w[4];
+    ri_quant_q4_0(x, dbits, w);
+    int64_t o = (dst_row0 + r * dst_row_stride) * nb + b;
+    qs[o] = make_uint4(w[0], w[1], w[2], w[3]);
+    d[o] = __ushort_as_half(dbits);
+}
+void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0,
+                          int64_t dst_row_stride, int64_t total_rows, cudaStream_t st) {
+    int64_t nb = cols / QK, n = rows * nb;
+    PackedQ4_0 v = packed_q4_0_view(d_packed, total_rows, cols);
+    k_randinit_q4_0<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, sigma, rows, nb, (uint4 *)v.qs, (__half *)v.d, dst_row0, dst_row_stride);
+}
+__global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *__restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ri_add(ri_mul(ri_gauss(key, (uint64_t)i), sigma), offset);
+}
+void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st) {
+    k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out);
+}
+
+// =============================================================================== embedding row
+__global__ void k_embed_q4_0(const uint4 *__restrict__ qs, const __half *__restrict__ d, int64_t nb, const int *__restrict__ token,
+                             float scale, float *__restrict__ x) {
+    int64_t row = *token;
+    for (int64_t b = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; b < nb; b += (int64_t)gridDim.x * (blockDim.x / 32)) {
+        int lane = threadIdx.x & 31;
+        const uint8_t *q = (const uint8_t *)&qs[row * nb + b];
+        uint8_t byte = q[lane & 15];
+        int v = (lane < 16 ? (byte & 0x0F) : (byte >> 4)) - 8;
+        float val = (float)v * __half2float(d[row * nb + b]);
+        if (scale != 1.0f) val = val * scale;
+        x[b * QK + lane] = val;
+    }
+}
+void launch_embed_q4_0(const void *d_packed, int64_t rows, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st) {
+    PackedQ4_0 v = packed_q4_0_view(d_packed, rows, cols);
+    int64_t nb = cols / QK;
+    k_embed_q4_0<<<(unsigned)((nb + 7) / 8), 256, 0, st>>>(v.qs, v.d, nb, d_token, scale, d_x);
+}
+
+// =============================================================================== activation grid
+__global__ void k_quant_act(const float *__restrict__ x, int64_t n, void *__restrict__ act) {
+    int lane = threadIdx.x & 31;
+    int64_t nb = n / QK;
+    for (int64_t b = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; b < nb; b += (int64_t)gridDim.x * (blockDim.x / 32)) {
+        float s;
+        int X = act_grid_lane(x[b * QK + lane], s);
+        act_store_block(act, n, b, lane, X, s);
+    }
+}
+void launch_quant_act(const float *d_x, int64_t n, void *d_act, cudaStream_t st) {
+    int64_t nb = n / QK;
+    unsigned grid = (unsigned)((nb + 7) / 8);
+    k_quant_act<<<grid, 256, 0, st>>>(d_x, n, d_act);
+}
+
+// RMSNorm fused with the activation grid; one CTA (n <= 16384).  Op order follows oracle/model.py:_norm:
+//   r = 1/sqrt(mean(x^2) + eps);  y = (x * r) * w   or   (x * r) * (1 + w)
+__global__ void __launch_bounds__(1024) k_rmsnorm_quant(const float *__restrict__ x, const float *__restrict__ w, int n, float eps,
+                                                        int plus_one, void *__restrict__ act, float *__restrict__ y_opt) {
+    __shared__ float red[32];
+    __shared__ float s_r;
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { float v = x[i]; ss = fmaf(v, v, ss); }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+        t = warp_sum(t);
+        if (threadIdx.x == 0) s_r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(t, (float)n), eps)));
+    }
+    __syncthreads();
+    float r = s_r;
+    int lane = threadIdx.x & 31;
+    for (int b = threadIdx.x >> 5; b < n / QK; b += blockDim.x >> 5) {
+        int i = b * QK + lane;
+        float wi = w[i];
+        if (plus_one) wi = __fadd_rn(1.0f, wi);
+        float yv = __fmul_rn(__fmul_rn(x[i], r), wi);
+        if (y_opt) y_opt[i] = yv;
+        float s;
+        int X = act_grid_lane(yv, s);
+        act_store_block(act, n, b, lane, X, s);
+    }
+}
+void launch_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt, cudaStream_t st) {
+    int threads = n >= 4096 ? 1024 : (n >= 1024 ? 512 : 256);
+    k_rmsnorm_quant<<<1, threads, 0, st>>>(d_x, d_w, (int)n, eps, plus_one, d_act, d_y_opt);
+}
+
+// =============================================================================== Q4_0 GEMV
+// One warp computes two consecutive rows (a (gate,up) pair in mode 2); lanes stride over the 32-weight
+// blocks of the row with 128-bit loads.  Per block the dot product is exact integer arithmetic:
+//   T = sum_j q_j * X_j - 8 * sum_j X_j,   X = d2*16384 + d1*128 + d0   (three dp4a digit planes)
+//   acc += float(T) * (d_w * 2^e)
+__device__ __forceinline__ float act_fn(float g, int act) {
+    if (act == B2_ACT_SILU) return g / (1.0f + expf(-g));
+    float g3 = 0.044715f * g * g * g;
+    return 0.5f * g * (1.0f + tanhf(0.7978845608028654f * (g + g3)));
+}
+
+__device__ __forceinline__ int q4_block_dot(const uint4 w, const uint4 *D /*6*/, int bsum) {
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+    int S[3] = {0, 0, 0};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const uint32_t dl[4] = {D[2 * c].x, D[2 * c].y, D[2 * c].z, D[2 * c].w};
+        const uint32_t dh[4] = {D[2 * c + 1].x, D[2 * c + 1].y, D[2 * c + 1].z, D[2 * c + 1].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            S[c] = dp4a_us(ww[k] & 0x0F0F0F0Fu, dl[k], S[c]);
+            S[c] = dp4a_us((ww[k] >> 4) & 0x0F0F0F0Fu, dh[k], S[c]);
+        }
+    }
+    return S[2] * 16384 + S[1] * 128 + S[0] - 8 * bsum;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) k_gemv_q4_0(const uint4 *__restrict__ qs, const __half *__restrict__ dw, int rows, int nb,
+                                                   const int8_t *__restrict__ dig, const float *__restrict__ ascale,
+                                                   const int32_t *__restrict__ absum, const float *__restrict__ bias_or_res, int act,
+                                                   float *__restrict__ y) {
+    const int lane = threadIdx.x & 31;
+    const int pair = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int r0 = pair * 2;
+    if (r0 >= rows) return;
+    const bool has1 = (r0 + 1) < rows;
+    const uint4 *q0 = qs + (int64_t)r0 * nb;
+    const uint4 *q1 = qs + (int64_t)(has1 ? r0 + 1 : r0) * nb;
+    const __half *d0 = dw + (int64_t)r0 * nb;
+    const __half *d1 = dw + (int64_t)(has1 ? r0 + 1 : r0) * nb;
+    float acc0 = 0.f, acc1 = 0.f;
+    for (int b = lane; b < nb; b += 32) {
+        uint4 w0 = ldg_stream(q0 + b);
+        uint4 w1 = ldg_stream(q1 + b);
+        float s0 = __half2float(d0[b]);
+        float s1 = __half2float(d1[b]);
+        const uint4 *dp = (const uint4 *)(dig + (int64_t)b * 96);
+        uint4 D[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) D[k] = __ldg(dp + k);
+        float as = __ldg(ascale + b);
+        int bs = __ldg(absum + b);
+        int T0 = q4_block_dot(w0, D, bs);
+        int T1 = q4_block_dot(w1, D, bs);
+        acc0 = fmaf((float)T0, s0 * as, acc0);
+        acc1 = fmaf((float)T1, s1 * as, acc1);
+    }
+    acc0 = warp_sum(acc0);
+    acc1 = warp_sum(acc1);
+    if (lane == 0) {
+        if (MODE == 0) {
+            y[r0] = bias_or_res ? acc0 + bias_or_res[r0] : acc0;
+            if (has1) y[r0 + 1] = bias_or_res ? acc1 + bias_or_res[r0 + 1] : acc1;
+        } else if (MODE == 1) {
+            y[r0] = bias_or_res[r0] + acc0;
+            if (has1) y[r0 + 1] = bias_or_res[r0 + 1] + acc1;
+        } else {
+            y[pair] = act_fn(acc0, act) * acc1;
+        }
+    }
+}
+void launch_gemv_q4_0(const void *d_packed, int64_t rows, int64_t cols, const void *d_act, const float *d_bias_or_res,
+                      int mode, int act, float *d_y, cudaStream_t st) {
+    PackedQ4_0 v = packed_q4_0_view(d_packed, rows, cols);
+    ActView a = act_view(d_act, cols);
+    int nb = (int)(cols / QK);
+    int pairs = (int)((rows + 1) / 2);
+    unsigned grid = (unsigned)((pairs + 7) / 8);
+    if (mode == 0)
+        k_gemv_q4_0<0><<<grid, 256, 0, st>>>(v.qs, v.d, (int)rows, nb, a.dig, a.scale, a.bsum, d_bias_or_res, act, d_y);
+    else if (mode == 1)
+        k_gemv_q4_0<1><<<grid, 256, 0, st>>>(v.qs, v.d, (int)rows, nb, a.dig, a.scale, a.bsum, d_bias_or_res, act, d_y);
+    else
+        k_gemv_q4_0<2><<<grid, 256, 0, st>>>(v.qs, v.d, (int)rows, nb, a.dig, a.scale, a.bsum, d_bias_or_res, act, d_y);
+}
+
+// =============================================================================== RoPE + KV append
+// Block h < nh rotates query head h in place; nh <= h < nh+nkv rotates key head and appends it (f16);
+// the last nkv blocks append the value head.  Rotate-half pairing (j, j+hd/2); products and sums are
+// individually rounded like the oracle's tensor ops (oracle/model.py:_rope).
+__global__ void k_rope_kv(float *__restrict__ qkv, int nh, int nkv, int hd, const int *__restrict__ d_pos, int pos_imm,
+                          const float *__restrict__ cs, const float *__restrict__ sn, __half *__restrict__ kc, __half *__restrict__ vc,
+                          const int32_t *__restrict__ page_table) {
+    const int pos = d_pos ? *d_pos : pos_imm;
+    const int h = blockIdx.x, half = hd >> 1;
+    const int page = page_table[pos / PAGE_TOKENS], slot = pos % PAGE_TOKENS;
+    if (h < nh + nkv) {
+        float *t = qkv + (int64_t)h * hd;   // q heads then k heads are contiguous in the fused QKV output
+        for (int j = threadIdx.x; j < half; j += blockDim.x) {
+            float c = cs[(int64_t)pos * half + j], s = sn[(int64_t)pos * half + j];
+            float a = t[j], b = t[j + half];
+            float ra = __fsub_rn(__fmul_rn(a, c), __fmul_rn(b, s));
+            float rb = __fadd_rn(__fmul_rn(b, c), __fmul_rn(a, s));
+            if (h < nh) {
+                t[j] = ra;
+                t[j + half] = rb;
+            } else {
+                int kvh = h - nh;
+                __half *dst = kc + (((int64_t)page * nkv + kvh) * PAGE_TOKENS + slot) * hd;
+                dst[j] = __float2half_rn(ra);
+                dst[j + half] = __float2half_rn(rb);
+            }
+        }
+    } else {
+        int kvh = h - nh - nkv;
+        const float *t = qkv + (int64_t)(nh + nkv + kvh) * hd;
+        __half *dst = vc + (((int64_t)page * nkv + kvh) * PAGE_TOKENS + slot) * hd;
+        for (int j = threadIdx.x; j < hd; j += blockDim.x) dst[j] = __float2half_rn(t[j]);
+    }
+}
+void launch_rope_kv(float *d_qkv, int nh, int nkv, int hd, const int *d_pos, int pos_imm, const float *d_cos, const float *d_sin,
+                    __half *d_k, __half *d_v, const int32_t *d_page_table, cudaStream_t st) {
+    k_rope_kv<<<nh + 2 * nkv, 128, 0, st>>>(d_qkv, nh, nkv, hd, d_pos, pos_imm, d_cos, d_sin, d_k, d_v, d_page_table);
+}
+
+// =============================================================================== paged attention, decode
+// grid (nh, ATTN_NSPLIT), 128 threads.  Split s covers pages [s*pps, (s+1)*pps) of the context.
+// Phase 1: 8 lanes per key, 16 keys (one page) per iteration, 16-byte f16 loads, scores to smem.
+// Phase 2: thread d accumulates sum_t p_t * V[t][d] (and d+128 for hd 256).
+// Partials (m, l, o[hd]) go to scratch; the last split to finish for a head merges them (ticket counter).
+uint64_t attn_scratch_bytes(int nh, int hd) { return (uint64_t)nh * ATTN_NSPLIT * (hd + 2) * 4 + (uint64_t)nh * 4; }
+
+__global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q, int nh, int nkv, int hd, const int *__restrict__ d_pos,
+                                                     int nctx_imm, const __half *__restrict__ kc, const __half *__restrict__ vc,
+                                                     const int32_t *__restrict__ page_table, float *__restrict__ out,
+                                                     float *__restrict__ part, int *__restrict__ counters) {
+    extern __shared__ float smem[];
+    float *sq = smem;            // hd
+    float *sc = smem + hd;       // scores of this split
+    __shared__ float red[4];
+    __shared__ int s_last;
+    const int n_ctx = d_pos ? (*d_pos + 1) : nctx_imm;
+    const int h = blockIdx.x, split = blockIdx.y, kvh = h / (nh / nkv);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_pages = (n_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const int pps = (n_pages + ATTN_NSPLIT - 1) / ATTN_NSPLIT;
+    const int p0 = split * pps, p1 = min(n_pages, p0 + pps);
+    const int t0 = p0 * PAGE_TOKENS, t1 = min(n_ctx, p1 * PAGE_TOKENS);
+    const int nt = max(0, t1 - t0);
+    const float scale = 1.0f / sqrtf((float)hd);
+    for (int j = tid; j < hd; j += 128) sq[j] = q[(int64_t)h * hd + j];
+    __syncthreads();
+    // ---- phase 1: scores
+    const int key = tid >> 3, sub = tid & 7;
+    const int nchunk = hd >> 3;   // 16-byte chunks per key row
+    float lmax = -INFINITY;
+    for (int p = p0; p < p1; ++p) {
+        const int t = p * PAGE_TOKENS + key;
+        const __half *kr = kc + (((int64_t)page_table[p] * nkv + kvh) * PAGE_TOKENS + key) * hd;
+        float dot = 0.f;
+        if (t < n_ctx) {
+            for (int c = sub; c < nchunk; c += 8) {
+                uint4 raw = __ldg((const uint4 *)(kr + c * 8));
+                const __half2 *h2 = (const __half2 *)&raw;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    float2 f = __half22float2(h2[e]);
+                    dot = fmaf(sq[c * 8 + 2 * e], f.x, dot);
+                    dot = fmaf(sq[c * 8 + 2 * e + 1], f.y, dot);
+                }
+            }
+        }
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        if (t < n_ctx) {
+            float s = dot * scale;
+            if (sub == 0) sc[t - t0] = s;
+            lmax = fmaxf(lmax, s);
+        }
+    }
+    lmax = warp_max(lmax);
+    if (lane == 0) red[warp] = lmax;
+    __syncthreads();
+    const float m = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+    __syncthreads();
+    // ---- softmax numerators
+    float lsum = 0.f;
+    for (int i = tid; i < nt; i += 128) {
+        float pexp = expf(sc[i] - m);
+        sc[i] = pexp;
+        lsum += pexp;
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) red[warp] = lsum;
+    __syncthreads();
+    const float l = red[0] + red[1] + red[2] + red[3];
+    // ---- phase 2: weighted values
+    float o0 = 0.f, o1 = 0.f;
+    const int d0 = tid, d1 = tid + 128;
+    for (int p = p0; p < p1; ++p) {
+        const __half *vr = vc + ((int64_t)page_table[p] * nkv + kvh) * PAGE_TOKENS * hd;
+        const int tb = p * PAGE_TOKENS;
+        const int lim = min(PAGE_TOKENS, n_ctx - tb);
+        for (int k = 0; k < lim; ++k) {
+            float pe = sc[tb + k - t0];
+            if (d0 < hd) o0 = fmaf(pe, __half2float(vr[k * hd + d0]), o0);
+            if (d1 < hd) o1 = fmaf(pe, __half2float(vr[k * hd + d1]), o1);
+        }
+    }
+    float *pp = part + ((int64_t)h * ATTN_NSPLIT + split) * (hd + 2);
+    if (tid == 0) { pp[0] = m; pp[1] = l; }
+    if (d0 < hd) pp[2 + d0] = o0;
+    if (d1 < hd) pp[2 + d1] = o1;
+    // ---- merge by the last split of this head
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        int ticket = atomicAdd(&counters[h], 1);
+        s_last = (ticket == ATTN_NSPLIT - 1);
+        if (s_last) counters[h] = 0;   // leave the counter ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const float *ph = part + (int64_t)h * ATTN_NSPLIT * (hd + 2);
+    float M = -INFINITY;
+#pragma unroll
+    for (int s = 0; s < ATTN_NSPLIT; ++s) M = fmaxf(M, ph[s * (hd + 2)]);
+    float Lt = 0.f, a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int s = 0; s < ATTN_NSPLIT; ++s) {
+        const float *ps = ph + s * (hd + 2);
+        float ls = ps[1];
+        if (ls > 0.f) {
+            float wgt = expf(ps[0] - M);
+            Lt = fmaf(ls, wgt, Lt);
+            if (d0 < hd) a0 = fmaf(ps[2 + d0], wgt, a0);
+            if (d1 < hd) a1 = fmaf(ps[2 + d1], wgt, a1);
+        }
+    }
+    if (d0 < hd) out[(int64_t)h * hd + d0] = a0 / Lt;
+    if (d1 < hd) out[(int64_t)h * hd + d1] = a1 / Lt;
+}
+void launch_attn_decode(const float *d_q, int nh, int nkv, int hd, const int *d_pos, int nctx_imm, const __half *d_k, const __half *d_v,
+                        const int32_t *d_page_table, float *d_out, void *d_scratch, int max_ctx, cudaStream_t st) {
+    float *part = (float *)d_scratch;
+    int *counters = (int *)((char *)d_scratch + (uint64_t)nh * ATTN_NSPLIT * (hd + 2) * 4);
+    int max_pages = (max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    int pps = (max_pages + ATTN_NSPLIT - 1) / ATTN_NSPLIT;
+    size_t smem = (size_t)(hd + pps * PAGE_TOKENS) * sizeof(float);
+    k_attn_decode<<<dim3(nh, ATTN_NSPLIT), 128, smem, st>>>(d_q, nh, nkv, hd, d_pos, nctx_imm, d_k, d_v, d_page_table, d_out, part, counters);
+}
+
+// =============================================================================== greedy sampler
+// Stage 1: ARGMAX_BLOCKS blocks scan strided slices (warp-shuffle arg-reduce, lowest index wins ties);
+// the last block to finish (ticket counter) reduces the per-block partials.
+uint64_t argmax_scratch_bytes() { return ARGMAX_BLOCKS * 8 + 4; }
+
+__device__ __forceinline__ void arg_better(float &v, int &i, float ov, int oi) {
+    if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+}
+__device__ __forceinline__ void warp_argmax(float &v, int &i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        arg_better(v, i, ov, oi);
+    }
+}
+__global__ void __launch_bounds__(256) k_argmax(const float *__restrict__ x, int n, int *__restrict__ out, float *__restrict__ pv,
+                                                int *__restrict__ pi, int *__restrict__ counter) {
+    __shared__ float sv[8];
+    __shared__ int si[8];
+    __shared__ int s_last;
+    float v = -INFINITY;
+    int idx = 0x7fffffff;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) arg_better(v, idx, x[i], i);
+    warp_argmax(v, idx);
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = v; si[threadIdx.x >> 5] = idx; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = threadIdx.x < 8 ? sv[threadIdx.x] : -INFINITY;
+        idx = threadIdx.x < 8 ? si[threadIdx.x] : 0x7fffffff;
+        warp_argmax(v, idx);
+        if (threadIdx.x == 0) {
+            pv[blockIdx.x] = v;
+            pi[blockIdx.x] = idx;
+            __threadfence();
+            int ticket = atomicAdd(counter, 1);
+            s_last = (ticket == (int)gridDim.x - 1);
+            if (s_last) *counter = 0;
+        }
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < 32) {
+        v = -INFINITY;
+        idx = 0x7fffffff;
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += 32) arg_better(v, idx, pv[b], pi[b]);
+        warp_argmax(v, idx);
+        if (threadIdx.x == 0) *out = idx;
+    }
+}
+void launch_argmax(const float *d_logits, int64_t n, int32_t *d_out, void *d_scratch, cudaStream_t st) {
+    float *pv = (float *)d_scratch;
+    int *pi = (int *)((char *)d_scratch + ARGMAX_BLOCKS * 4);
+    int *counter = (int *)((char *)d_scratch + ARGMAX_BLOCKS * 8);
+    k_argmax<<<ARGMAX_BLOCKS, 256, 0, st>>>(d_logits, (int)n, d_out, pv, pi, counter);
+}

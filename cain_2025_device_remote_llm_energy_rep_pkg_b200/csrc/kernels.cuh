@@ -1,0 +1,49 @@
+// kernels.cuh — launchers of the decode-path kernels (all asynchronous on `st`).
+// Each mirrors one stage of Ollama's /api/generate decode loop.
+#pragma once
+#include "common.cuh"
+
+#define ATTN_NSPLIT 8       // KV splits per head in the decode attention kernel
+#define ARGMAX_BLOCKS 128   // stage-1 blocks of the greedy sampler
+
+// device-resident request state: lets a captured CUDA graph be replayed for every token
+struct DevState {
+    int pos;        // tokens already in the KV cache
+    int step;       // decode step counter (index into out_tokens)
+    int cur_token;  // token fed to the next forward
+    int prompt_idx; // next prompt token to feed during prefill
+};
+
+struct PackedQ4_0 {   // view of a packed matrix
+    const uint4 *qs;
+    const __half *d;
+};
+inline PackedQ4_0 packed_q4_0_view(const void *p, int64_t rows, int64_t cols) {
+    PackedQ4_0 v;
+    v.qs = (const uint4 *)p;
+    v.d = (const __half *)((const char *)p + (uint64_t)rows * (cols / QK) * 16);
+    return v;
+}
+
+// weight re-pack / init
+void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride,
+                      int64_t total_rows, cudaStream_t st);
+void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0,
+                          int64_t dst_row_stride, int64_t total_rows, cudaStream_t st);
+void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st);
+
+// stages
+void launch_embed_q4_0(const void *d_packed, int64_t rows, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st);
+void launch_quant_act(const float *d_x, int64_t n, void *d_act, cudaStream_t st);
+void launch_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt, cudaStream_t st);
+void launch_gemv_q4_0(const void *d_packed, int64_t rows, int64_t cols, const void *d_act, const float *d_bias_or_res,
+                      int mode, int act, float *d_y, cudaStream_t st);
+void launch_rope_kv(float *d_qkv, int nh, int nkv, int hd, const int *d_pos, int pos_imm, const float *d_cos, const float *d_sin,
+                    __half *d_k, __half *d_v, const int32_t *d_page_table, cudaStream_t st);
+// scratch: float[nh*ATTN_NSPLIT*(hd+2)] then int counters[nh] (zeroed once; the kernel leaves them zero)
+uint64_t attn_scratch_bytes(int nh, int hd);
+void launch_attn_decode(const float *d_q, int nh, int nkv, int hd, const int *d_pos, int nctx_imm, const __half *d_k, const __half *d_v,
+                        const int32_t *d_page_table, float *d_out, void *d_scratch, int max_ctx, cudaStream_t st);
+// scratch: float[ARGMAX_BLOCKS] + int[ARGMAX_BLOCKS] + int counter (zeroed once)
+uint64_t argmax_scratch_bytes();
+void launch_argmax(const float *d_logits, int64_t n, int32_t *d_out, void *d_scratch, cudaStream_t st);
