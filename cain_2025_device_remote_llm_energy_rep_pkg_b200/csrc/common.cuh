@@ -24,6 +24,14 @@ void b2_set_error(const char *fmt, ...);
 #define B2_TRY(expr)                                                                          \
     do { int _r = (expr); if (_r != B2_OK) return _r; } while (0)
 
+// Every extern "C" entry point opens an ApiScope: it swallows (and, with B2_DEBUG_STALE=1, reports) a
+// non-sticky CUDA error left behind by an earlier call so that it is not blamed on this one.
+struct ApiScope {
+    const char *name;
+    explicit ApiScope(const char *n);
+    ~ApiScope();
+};
+
 // ---------------------------------------------------------------- block geometry
 #define QK        32      // weights per Q4_0 / Q8_0 block and per activation block
 #define QK_K      256     // weights per K-quant super-block

@@ -20,6 +20,20 @@ void b2_set_error(const char *fmt, ...) {
     va_end(ap);
 }
 extern "C" const char *b2_last_error(void) { return g_err; }
+static bool debug_stale() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("B2_DEBUG_STALE"); v = (e && e[0] == '1') ? 1 : 0; }
+    return v == 1;
+}
+ApiScope::ApiScope(const char *n) : name(n) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess && debug_stale()) fprintf(stderr, "[b2llm] stale CUDA error on entry to %s: %s\n", n, cudaGetErrorString(e));
+}
+ApiScope::~ApiScope() {
+    if (!debug_stale()) return;
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) fprintf(stderr, "[b2llm] CUDA error pending on exit from %s: %s\n", name, cudaGetErrorString(e));
+}
 extern "C" const char *b2_version(void) { return "b2llm 0.1 (sm_100a)"; }
 
 // ------------------------------------------------------------------------------------ objects
@@ -87,6 +101,7 @@ static int dev_alloc(std::vector<void *> &owner, void **p, uint64_t n) {
 
 // ------------------------------------------------------------------------------------ engine
 extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, const void *nccl_uid, b2_engine **out) {
+    ApiScope _scope("b2_engine_create");
     (void)nccl_uid;
     B2_CHECK(out, B2_EINVAL, "b2_engine_create: out is NULL");
     B2_CHECK(tp_size == 1 && tp_rank == 0, B2_EINVAL, "b2_engine_create: tensor parallel size %d not supported in this build", tp_size);
@@ -105,6 +120,7 @@ extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, co
     return B2_OK;
 }
 extern "C" int b2_engine_destroy(b2_engine *e) {
+    ApiScope _scope("b2_engine_destroy");
     if (!e) return B2_OK;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -209,6 +225,7 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype,
 }
 
 extern "C" int b2_model_destroy(b2_model *m) {
+    ApiScope _scope("b2_model_destroy");
     if (!m) return B2_OK;
     if (m->e) cudaSetDevice(m->e->device);
     for (void *p : m->allocs) cudaFree(p);
@@ -227,6 +244,7 @@ enum { K_EMBD = 0, K_OUT_NORM, K_OUTPUT, K_ATTN_NORM, K_Q, K_K, K_V, K_QB, K_KB,
 static inline uint32_t tid_of(int kind, uint32_t layer) { return layer * 16 + kind; }
 
 extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint64_t seed, int qtype, int head_qtype, b2_model **out) {
+    ApiScope _scope("b2_model_create_random");
     b2_model *m = nullptr;
     B2_TRY(alloc_model_skeleton(e, cfg, qtype, head_qtype, &m));
     const b2_arch_cfg &c = m->cfg;
@@ -301,6 +319,7 @@ static int upload_vec(b2_model *m, const b2_tensor_desc &t, float *dst, int64_t 
 }
 
 extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_tensor_desc *tensors, int n_tensors, b2_model **out) {
+    ApiScope _scope("b2_model_create");
     B2_CHECK(tensors && n_tensors > 0, B2_EINVAL, "b2_model_create: no tensors");
     std::map<std::string, const b2_tensor_desc *> by_name;
     for (int i = 0; i < n_tensors; ++i) {
@@ -487,6 +506,7 @@ static int run_graph(b2_session *s, int which, int times) {
 }
 
 extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
+    ApiScope _scope("b2_session_create");
     B2_CHECK(m && out, B2_EINVAL, "b2_session_create: NULL");
     B2_CHECK(max_ctx > 0 && max_ctx <= m->cfg.max_ctx, B2_EINVAL, "max_ctx %d out of range (model max %d)", max_ctx, m->cfg.max_ctx);
     B2_CUDA(cudaSetDevice(m->e->device));
@@ -539,6 +559,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     return B2_OK;
 }
 extern "C" int b2_session_destroy(b2_session *s) {
+    ApiScope _scope("b2_session_destroy");
     if (!s) return B2_OK;
     if (s->m && s->m->e) cudaSetDevice(s->m->e->device);
     drop_graphs(s);
@@ -550,6 +571,7 @@ extern "C" int b2_session_destroy(b2_session *s) {
     return B2_OK;
 }
 extern "C" int b2_session_reset(b2_session *s) {
+    ApiScope _scope("b2_session_reset");
     B2_CHECK(s, B2_EINVAL, "NULL session");
     B2_CUDA(cudaSetDevice(s->m->e->device));
     B2_CUDA(cudaStreamSynchronize(s->m->e->stream));
@@ -607,6 +629,7 @@ static int elapsed_ns(b2_session *s, uint64_t *ns) {
 }
 
 extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *logits_out) {
+    ApiScope _scope("b2_prefill");
     B2_CHECK(s && tokens && n > 0, B2_EINVAL, "b2_prefill: bad arguments");
     B2_CHECK(s->host_pos + n <= s->max_ctx, B2_ECTX, "b2_prefill: %d + %d tokens exceed the context window %d", s->host_pos, n, s->max_ctx);
     int V = s->m->cfg.vocab;
@@ -631,6 +654,7 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
 }
 
 extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampler, int32_t *out_tokens, float *logits_out) {
+    ApiScope _scope("b2_decode");
     B2_CHECK(s && out_tokens && n_steps > 0, B2_EINVAL, "b2_decode: bad arguments");
     B2_CHECK(s->have_logits, B2_EINVAL, "b2_decode: call b2_prefill first");
     B2_CHECK(!sampler || sampler->top_k <= 1, B2_EINVAL, "b2_decode: only greedy sampling (top_k <= 1) is wired into the decode loop in this build");
@@ -656,6 +680,7 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
 }
 
 extern "C" int b2_forward_tokens(b2_session *s, const int32_t *tokens, int n, float *logits_out) {
+    ApiScope _scope("b2_forward_tokens");
     B2_CHECK(s && tokens && n > 0, B2_EINVAL, "b2_forward_tokens: bad arguments");
     B2_CHECK(s->host_pos + n <= s->max_ctx, B2_ECTX, "b2_forward_tokens: context window %d exceeded", s->max_ctx);
     B2_CHECK(n <= s->prompt_cap, B2_EINVAL, "b2_forward_tokens: n too large");
@@ -710,23 +735,28 @@ extern "C" int b2_randinit_tensor(uint64_t seed, uint32_t tensor_id, int64_t row
 
 // ------------------------------------------------------------------------------------ device helpers
 extern "C" int b2_dev_alloc(uint64_t nbytes, void **d_out) {
+    ApiScope _scope("b2_dev_alloc");
     B2_CHECK(d_out, B2_EINVAL, "NULL");
     B2_CUDA(cudaMalloc(d_out, nbytes ? nbytes : 16));
     return B2_OK;
 }
 extern "C" int b2_dev_free(void *p) {
+    ApiScope _scope("b2_dev_free");
     if (p) B2_CUDA(cudaFree(p));
     return B2_OK;
 }
 extern "C" int b2_dev_upload(void *d_dst, const void *src, uint64_t n) {
+    ApiScope _scope("b2_dev_upload");
     B2_CUDA(cudaMemcpy(d_dst, src, n, cudaMemcpyHostToDevice));
     return B2_OK;
 }
 extern "C" int b2_dev_download(void *dst, const void *d_src, uint64_t n) {
+    ApiScope _scope("b2_dev_download");
     B2_CUDA(cudaMemcpy(dst, d_src, n, cudaMemcpyDeviceToHost));
     return B2_OK;
 }
 extern "C" int b2_dev_sync(void) {
+    ApiScope _scope("b2_dev_sync");
     B2_CUDA(cudaDeviceSynchronize());
     return B2_OK;
 }

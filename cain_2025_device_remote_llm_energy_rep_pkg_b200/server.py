@@ -1,0 +1,284 @@
+"""Ollama-compatible HTTP front end (drop-in boundary b1).
+
+The unchanged reference issues, per run, `curl http://<host>:11434/api/generate -d '{"model": ..., "prompt": ...,
+"stream": false}'` (`experiment/RunnerConfig.py:128-131`): an HTTP/1.1 POST whose JSON body arrives with
+`Content-Type: application/x-www-form-urlencoded` (curl -d default), so the body is parsed as JSON whatever the
+header says.  The response is Ollama's single JSON object (fields in SURVEY.md §3.3); durations are ns.
+
+The server owns no arithmetic: every token comes from a backend object; `B2Backend` drives libb2llm.so (the
+CUDA engine) through ctypes.  There is no CPU backend in this package.
+"""
+from __future__ import annotations
+
+import argparse
+import datetime
+import json
+import math
+import os
+import re
+import threading
+import time
+from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
+from typing import Dict, Iterator, List, Optional
+
+from . import tokenizer
+from .archs import ARCHS, Arch
+
+DEFAULT_PORT = 11434
+WORDS_RE = re.compile(r"\bIn (\d+) words\b")
+
+
+def default_num_predict(prompt: str) -> int:
+    """Token budget when the request has no options.num_predict.  Random-init weights never emit a meaningful
+    EOS, so the budget follows the reference's prompt grammar "In N words, ..." (RunnerConfig.py:120):
+    ceil(1.33 * N) tokens; 128 for any other prompt."""
+    m = WORDS_RE.search(prompt)
+    return int(math.ceil(1.33 * int(m.group(1)))) if m else 128
+
+
+class GenerationResult:
+    def __init__(self, tokens: List[int], prompt_tokens: List[int], stats: dict, done_reason: str):
+        self.tokens, self.prompt_tokens, self.stats, self.done_reason = tokens, prompt_tokens, stats, done_reason
+
+
+class B2Backend:
+    """Model residency + one serial session per model on one GPU (requests are serialised per backend)."""
+
+    def __init__(self, device: int = 0, seed: int = 1, qtype: str = "q4_0", stream_chunk: int = 16):
+        from .engine import Engine
+        self.engine = Engine(device)
+        self.device, self.seed, self.qtype, self.stream_chunk = device, seed, qtype, stream_chunk
+        self.models: Dict[str, tuple] = {}
+        self.lock = threading.Lock()
+
+    def list_models(self) -> List[str]:
+        return list(ARCHS)
+
+    def loaded(self) -> List[str]:
+        return list(self.models)
+
+    def arch(self, tag: str) -> Arch:
+        if tag not in ARCHS:
+            raise KeyError(tag)
+        return ARCHS[tag]
+
+    def _load(self, tag: str):
+        from .engine import Model
+        if tag not in self.models:
+            a = self.arch(tag)
+            t0 = time.perf_counter_ns()
+            model = Model.random(self.engine, a, seed=self.seed, qtype=self.qtype)
+            sess = model.session(a.max_ctx)
+            self.models[tag] = (model, sess, time.perf_counter_ns() - t0)
+            return self.models[tag], self.models[tag][2]
+        return self.models[tag], 0
+
+    def energy_mj(self) -> Optional[int]:
+        from .engine import nvml_energy_mj
+        try:
+            return nvml_energy_mj(self.device)
+        except Exception:
+            return None
+
+    def generate(self, tag: str, prompt: str, options: dict, raw: bool = False) -> Iterator[dict]:
+        """Yields {"tokens": [...]} chunks, then a final {"done": True, ...stats}."""
+        with self.lock:
+            t_start = time.perf_counter_ns()
+            e0 = self.energy_mj()
+            (model, sess, _), load_ns = self._load(tag)
+            a = model.arch
+            ptoks = tokenizer.encode(prompt, a.V, a.family, template=not raw)
+            budget = int(options.get("num_predict", default_num_predict(prompt)))
+            room = a.max_ctx - len(ptoks)
+            if room <= 0:
+                raise ValueError(f"prompt of {len(ptoks)} tokens does not fit the {a.max_ctx}-token context")
+            reason = "length"
+            if budget < 0 or budget > room:
+                budget = room
+            sess.reset()
+            sess.prefill(ptoks)
+            out: List[int] = []
+            while len(out) < budget:
+                n = min(self.stream_chunk if options.get("_stream") else budget, budget - len(out))
+                toks = [int(t) for t in sess.decode(n)]
+                out += toks
+                yield {"tokens": toks}
+            st = sess.stats()
+            e1 = self.energy_mj()
+            yield {"done": True, "done_reason": reason, "prompt_tokens": ptoks, "tokens": out,
+                   "total_duration": time.perf_counter_ns() - t_start, "load_duration": load_ns,
+                   "prompt_eval_count": st["prompt_eval_count"], "prompt_eval_duration": st["prompt_eval_ns"],
+                   "eval_count": st["eval_count"], "eval_duration": st["eval_ns"],
+                   "energy_mj": (e1 - e0) if (e0 is not None and e1 is not None) else None, "device": self.device}
+
+
+def _now() -> str:
+    return datetime.datetime.now(datetime.timezone.utc).isoformat().replace("+00:00", "Z")
+
+
+class Handler(BaseHTTPRequestHandler):
+    protocol_version = "HTTP/1.1"
+    server_version = "b2llm"
+
+    def log_message(self, fmt, *args):  # requests are logged by the server object
+        self.server.log(fmt % args)
+
+    # ------------------------------------------------------------------ helpers
+    def _send_json(self, code: int, obj, extra_headers=None):
+        body = (json.dumps(obj) if not isinstance(obj, (bytes, str)) else obj)
+        body = body.encode() if isinstance(body, str) else body
+        self.send_response(code)
+        self.send_header("Content-Type", "application/json; charset=utf-8")
+        self.send_header("Content-Length", str(len(body)))
+        for k, v in (extra_headers or {}).items():
+            self.send_header(k, v)
+        self.end_headers()
+        self.wfile.write(body)
+
+    def _error(self, code: int, msg: str):
+        self.server.log(f"error {code}: {msg}")
+        self._send_json(code, {"error": msg})
+
+    def _read_body(self) -> bytes:
+        n = int(self.headers.get("Content-Length") or 0)
+        return self.rfile.read(n) if n else b""
+
+    # ------------------------------------------------------------------ routes
+    def do_GET(self):
+        b = self.server.backend
+        if self.path in ("/", ""):
+            body = b"Ollama is running"
+            self.send_response(200)
+            self.send_header("Content-Type", "text/plain; charset=utf-8")
+            self.send_header("Content-Length", str(len(body)))
+            self.end_headers()
+            self.wfile.write(body)
+        elif self.path == "/api/version":
+            self._send_json(200, {"version": "0.0.0-b2llm"})
+        elif self.path == "/api/tags":
+            self._send_json(200, {"models": [{"name": m, "model": m, "details": {"quantization_level": "Q4_0",
+                                                                                 "family": ARCHS[m].family}} for m in b.list_models()]})
+        elif self.path == "/api/ps":
+            self._send_json(200, {"models": [{"name": m, "model": m} for m in b.loaded()]})
+        elif self.path.startswith("/b2/stats"):
+            self._send_json(200, {"requests": self.server.stats_log[-int(self.server.keep_stats):]})
+        else:
+            self._error(404, f"unknown path {self.path}")
+
+    def do_POST(self):
+        if self.path != "/api/generate":
+            self._read_body()
+            return self._error(404, f"unknown path {self.path}")
+        raw = self._read_body()
+        try:
+            req = json.loads(raw.decode("utf-8"))  # content-type deliberately ignored (curl -d sends form-urlencoded)
+            if not isinstance(req, dict):
+                raise ValueError("body must be a JSON object")
+        except Exception as ex:
+            return self._error(400, f"invalid JSON body: {ex}")
+        model, prompt = req.get("model"), req.get("prompt", "")
+        if not isinstance(model, str) or not model:
+            return self._error(400, "missing field: model")
+        if not isinstance(prompt, str):
+            return self._error(400, "prompt must be a string")
+        backend = self.server.backend
+        if model not in backend.list_models():
+            return self._error(404, f"model '{model}' not found")
+        stream = req.get("stream", True)
+        options = dict(req.get("options") or {})
+        options["_stream"] = bool(stream)
+        try:
+            gen = backend.generate(model, prompt, options, raw=bool(req.get("raw", False)))
+            if stream:
+                self.send_response(200)
+                self.send_header("Content-Type", "application/x-ndjson")
+                self.send_header("Transfer-Encoding", "chunked")
+                self.end_headers()
+                for part in gen:
+                    if part.get("done"):
+                        line = self._final(model, part, "")
+                    else:
+                        line = {"model": model, "created_at": _now(), "response": tokenizer.decode(part["tokens"]), "done": False}
+                    data = (json.dumps(line) + "\n").encode()
+                    self.wfile.write(b"%x\r\n%s\r\n" % (len(data), data))
+                    self.wfile.flush()
+                self.wfile.write(b"0\r\n\r\n")
+            else:
+                final = None
+                for part in gen:
+                    if part.get("done"):
+                        final = part
+                self._send_json(200, self._final(model, final, tokenizer.decode(final["tokens"])))
+        except ValueError as ex:
+            self._error(400, str(ex))
+        except Exception as ex:  # engine failure: Ollama convention is {"error": ...} with a 5xx
+            self._error(500, f"{type(ex).__name__}: {ex}")
+
+    def _final(self, model: str, part: dict, text: str) -> dict:
+        rec = {"model": model, "created_at": _now(), "response": text, "done": True, "done_reason": part["done_reason"],
+               "context": part["prompt_tokens"] + part["tokens"], "total_duration": part["total_duration"],
+               "load_duration": part["load_duration"], "prompt_eval_count": part["prompt_eval_count"],
+               "prompt_eval_duration": part["prompt_eval_duration"], "eval_count": part["eval_count"],
+               "eval_duration": part["eval_duration"]}
+        self.server.record({"t": time.time(), "model": model, "eval_count": part["eval_count"], "eval_duration": part["eval_duration"],
+                            "prompt_eval_count": part["prompt_eval_count"], "prompt_eval_duration": part["prompt_eval_duration"],
+                            "total_duration": part["total_duration"], "load_duration": part["load_duration"],
+                            "energy_mj": part.get("energy_mj"), "device": part.get("device")})
+        return rec
+
+
+class OllamaServer(ThreadingHTTPServer):
+    daemon_threads = True
+    allow_reuse_address = True
+
+    def __init__(self, addr, backend, stats_file: Optional[str] = None, verbose: bool = True):
+        super().__init__(addr, Handler)
+        self.backend, self.stats_file, self.verbose = backend, stats_file, verbose
+        self.stats_log: List[dict] = []
+        self.keep_stats = 64
+        self._lock = threading.Lock()
+
+    def log(self, msg: str):
+        if self.verbose:
+            print(f"[b2llm-server] {msg}", flush=True)
+
+    def record(self, rec: dict):
+        """Side channel for the runner's energy plugin: the reference discards curl's stdout
+        (RunnerConfig.py:131), so token counts reach run_table.csv through this log instead."""
+        with self._lock:
+            self.stats_log.append(rec)
+            del self.stats_log[:-1024]
+            if self.stats_file:
+                with open(self.stats_file, "a") as f:
+                    f.write(json.dumps(rec) + "\n")
+
+
+def serve(backend, host: str = "0.0.0.0", port: int = DEFAULT_PORT, stats_file: Optional[str] = None, verbose: bool = True) -> OllamaServer:
+    srv = OllamaServer((host, port), backend, stats_file, verbose)
+    t = threading.Thread(target=srv.serve_forever, daemon=True)
+    t.start()
+    return srv
+
+
+def main():
+    ap = argparse.ArgumentParser(description="Ollama-compatible /api/generate endpoint on the B200 engine")
+    ap.add_argument("--host", default="0.0.0.0")
+    ap.add_argument("--port", type=int, default=DEFAULT_PORT)
+    ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--stats-file", default=os.environ.get("B2_STATS_FILE"))
+    ap.add_argument("--preload", default="", help="comma-separated model tags to load before serving")
+    a = ap.parse_args()
+    backend = B2Backend(a.device, a.seed)
+    for tag in filter(None, a.preload.split(",")):
+        backend._load(tag)
+    srv = OllamaServer((a.host, a.port), backend, a.stats_file)
+    srv.log(f"listening on {a.host}:{a.port} (device {a.device})")
+    try:
+        srv.serve_forever()
+    except KeyboardInterrupt:
+        pass
+
+
+if __name__ == "__main__":
+    main()

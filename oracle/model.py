@@ -13,7 +13,7 @@ scaling, tied heads, GQA/MQA/MHA) are cross-checked against the Hugging Face mod
 Numerics contract (DESIGN.md "Numerics"), identical on the CUDA path:
   * weights: exact dequantisation of the GGML blocks (oracle/quants.py), fp32;
   * activations are fp32 between ops; the vector entering every quantised matmul is first rounded
-    to a block-fixed-point grid: per 32 elements, step 2^(e-19) with e = floor(log2 max|x|), i.e. 21
+    to a block-fixed-point grid: per 32 elements, step 2^(e-19) with e = max(floor(log2 max|x|), -100) (-100 for an all-zero block), i.e. 21
     significant bits relative to the block maximum (`fxp_round`).  The CUDA kernels carry that
     integer as three int8 digits and do exact integer dot products; here it is a rounding;
   * KV cache holds f16 (round-to-nearest-even) keys (after RoPE) and values;
@@ -45,7 +45,7 @@ def fxp_round(x: torch.Tensor, bits: int = ACT_BITS) -> torch.Tensor:
     xb = x.reshape(-1, 32)
     m = xb.abs().amax(dim=1, keepdim=True)
     _, ex = torch.frexp(m)                       # m = f * 2^ex, f in [0.5, 1)
-    e = torch.clamp(ex - 1, min=-100)
+    e = torch.clamp(torch.where(m == 0, torch.full_like(ex, -100), ex - 1), min=-100)
     s = torch.ldexp(torch.ones_like(m), e - (bits - 1))
     return (torch.round(xb / s) * s).reshape(x.shape)
 
@@ -56,7 +56,7 @@ def fxp_digits(x: np.ndarray, bits: int = ACT_BITS):
     t = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).reshape(-1, 32)
     m = t.abs().amax(dim=1, keepdim=True)
     _, ex = torch.frexp(m)
-    e = torch.clamp(ex - 1, min=-100) - (bits - 1)
+    e = torch.clamp(torch.where(m == 0, torch.full_like(ex, -100), ex - 1), min=-100) - (bits - 1)
     s = torch.ldexp(torch.ones_like(m), e)
     X = torch.round(t / s).to(torch.int64).numpy().reshape(-1)
     d0 = ((X + 64) & 127) - 64

@@ -192,8 +192,8 @@ def test_attn_decode(lib, D, nh, nkv, hd, n_ctx):
     vc = (rng.standard_normal((n_pages + 3, nkv, 16, hd))).astype(np.float16)
     q = (rng.standard_normal((nh, hd)) * 1.5).astype(np.float32)
     dout = D(nh * hd * 4)
-    chk(lib, lib.b2_op_attn_decode(D.from_numpy(q).ptr, nh, nkv, hd, n_ctx, D.from_numpy(kc).ptr, D.from_numpy(vc).ptr,
-                                   D.from_numpy(perm).ptr, 16, dout.ptr))
+    dq, dk, dv, dpt = D.from_numpy(q), D.from_numpy(kc), D.from_numpy(vc), D.from_numpy(perm)   # keep the buffers alive
+    chk(lib, lib.b2_op_attn_decode(dq.ptr, nh, nkv, hd, n_ctx, dk.ptr, dv.ptr, dpt.ptr, 16, dout.ptr))
     out = dout.to_numpy(np.float32, (nh, hd))
     K = torch.from_numpy(kc[perm].transpose(0, 2, 1, 3).reshape(n_pages * 16, nkv, hd)[:n_ctx]).float()
     V = torch.from_numpy(vc[perm].transpose(0, 2, 1, 3).reshape(n_pages * 16, nkv, hd)[:n_ctx]).float()
@@ -222,7 +222,8 @@ def test_argmax_with_ties(lib, D, n):
         if variant == 2:
             x[:] = -np.inf
             x[n - 1] = -1e30
-        chk(lib, lib.b2_op_argmax(D.from_numpy(x).ptr, n, dout.ptr))
+        dx = D.from_numpy(x)
+        chk(lib, lib.b2_op_argmax(dx.ptr, n, dout.ptr))
         assert int(dout.to_numpy(np.int32, (1,))[0]) == osampler.argmax_lowest(x)
 
 
@@ -238,7 +239,8 @@ def test_sample_topk(lib, D, n, k):
         u = float(rng.random())
         T, top_p = 0.8, 0.9 if trial % 2 == 0 else 1.0
         tok, kept, margin = osampler.sample_topk(x, k, T, top_p, u)
-        chk(lib, lib.b2_op_sample_topk(D.from_numpy(x).ptr, n, k, T, top_p, u, dout.ptr))
+        dx = D.from_numpy(x)
+        chk(lib, lib.b2_op_sample_topk(dx.ptr, n, k, T, top_p, u, dout.ptr))
         got = int(dout.to_numpy(np.int32, (1,))[0])
         assert got in set(map(int, kept)) or margin < 1e-5
         if margin > 1e-5:                        # away from a CDF step the draw is identical

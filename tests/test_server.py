@@ -1,0 +1,109 @@
+"""HTTP boundary: the exact request the unchanged reference sends with curl, the Ollama
+response shape, error conventions, streaming, and the stats side channel.  Uses a stub backend (no compute)."""
+import json
+import shlex
+import socket
+import subprocess
+import urllib.request
+
+import pytest
+
+from cain_2025_device_remote_llm_energy_rep_pkg_b200 import server, tokenizer
+from stub_backend import StubBackend
+
+GOLDEN_BODY = ('{"model": "llama3.1:8b", "prompt": "In 100 words, please give me information about Prince Philip, '
+               'Duke of Edinburgh", "stream": false}')
+
+
+@pytest.fixture()
+def srv():
+    s = server.serve(StubBackend(), host="127.0.0.1", port=0, verbose=False)
+    yield s
+    s.shutdown()
+    s.server_close()
+
+
+def url(s, path):
+    return f"http://127.0.0.1:{s.server_address[1]}{path}"
+
+
+def test_reference_curl_command_line(srv):
+    """The reference builds `curl http://host:11434/api/generate -d '{...}'` with shlex (RunnerConfig.py:128-131):
+    curl -d posts the JSON with Content-Type application/x-www-form-urlencoded; the server must parse it anyway."""
+    model, prompt = "llama3.1:8b", "In 100 words, please give me information about Prince Philip, Duke of Edinburgh"
+    data = "'{" + f'"model": "{model}", "prompt": "{prompt}", "stream": false' + "}'"
+    cmd = f'curl -s http://127.0.0.1:{srv.server_address[1]}/api/generate -d {data}'
+    out = subprocess.run(shlex.split(cmd), capture_output=True, timeout=30)
+    assert out.returncode == 0
+    rec = json.loads(out.stdout)
+    for k in ("model", "created_at", "response", "done", "done_reason", "context", "total_duration", "load_duration",
+              "prompt_eval_count", "prompt_eval_duration", "eval_count", "eval_duration"):
+        assert k in rec, k
+    assert rec["model"] == model and rec["done"] is True
+    assert rec["eval_count"] == 133 == len(rec["response"])          # ceil(1.33 * 100)
+    assert srv.backend.requests[-1][1] == prompt
+
+
+def test_golden_wire_request(srv):
+    """Byte-level replay of the captured request: headers as curl 8.5.0 sends them."""
+    body = GOLDEN_BODY.encode()
+    assert len(body) == 134
+    req = (b"POST /api/generate HTTP/1.1\r\nHost: 127.0.0.1\r\nUser-Agent: curl/8.5.0\r\nAccept: */*\r\n"
+           b"Content-Length: 134\r\nContent-Type: application/x-www-form-urlencoded\r\n\r\n" + body)
+    with socket.create_connection(("127.0.0.1", srv.server_address[1]), timeout=10) as c:
+        c.sendall(req)
+        buf = b""
+        while b"\r\n\r\n" not in buf:
+            buf += c.recv(65536)
+        head, _, rest = buf.partition(b"\r\n\r\n")
+        assert head.startswith(b"HTTP/1.1 200")
+        n = int([l for l in head.split(b"\r\n") if l.lower().startswith(b"content-length")][0].split(b":")[1])
+        while len(rest) < n:
+            rest += c.recv(65536)
+    rec = json.loads(rest[:n])
+    assert b"application/json" in head.lower() and rec["done"] and rec["model"] == "llama3.1:8b"
+
+
+def test_errors_follow_ollama_convention(srv):
+    def post(body):
+        r = urllib.request.Request(url(srv, "/api/generate"), data=body, method="POST")
+        try:
+            with urllib.request.urlopen(r, timeout=10) as resp:
+                return resp.status, json.loads(resp.read())
+        except urllib.error.HTTPError as e:
+            return e.code, json.loads(e.read())
+    assert post(b"not json")[0] == 400
+    code, rec = post(json.dumps({"model": "nope:1b", "prompt": "x", "stream": False}).encode())
+    assert code == 404 and "not found" in rec["error"]
+    assert post(json.dumps({"prompt": "x"}).encode())[0] == 400
+    assert post(b"[1,2]")[0] == 400
+
+
+def test_num_predict_option_and_default_budget():
+    assert server.default_num_predict("In 500 words, please give me information about India") == 665
+    assert server.default_num_predict("In 1000 words, please give me information about X") == 1330
+    assert server.default_num_predict("hello") == 128
+
+
+def test_streaming_ndjson_and_aux_endpoints(srv):
+    body = json.dumps({"model": "qwen2:1.5b", "prompt": "hi", "options": {"num_predict": 40}}).encode()   # stream defaults to true
+    with urllib.request.urlopen(urllib.request.Request(url(srv, "/api/generate"), data=body, method="POST"), timeout=10) as r:
+        lines = [json.loads(l) for l in r.read().decode().splitlines() if l.strip()]
+    assert [l["done"] for l in lines] == [False, False, False, True]
+    assert "".join(l["response"] for l in lines[:-1]) and lines[-1]["eval_count"] == 40
+    with urllib.request.urlopen(url(srv, "/api/tags"), timeout=10) as r:
+        tags = {m["name"] for m in json.loads(r.read())["models"]}
+    assert tags == {"llama3.1:8b", "gemma:2b", "gemma:7b", "phi3:3.8b", "qwen2:1.5b", "qwen2:7b", "mistral:7b"}
+    with urllib.request.urlopen(url(srv, "/"), timeout=10) as r:
+        assert r.read() == b"Ollama is running"
+    with urllib.request.urlopen(url(srv, "/b2/stats"), timeout=10) as r:
+        recs = json.loads(r.read())["requests"]
+    assert recs[-1]["model"] == "qwen2:1.5b" and recs[-1]["eval_count"] == 40 and recs[-1]["energy_mj"] == 1234
+
+
+def test_tokenizer_stand_in():
+    ids = tokenizer.encode("In 100 words", 32064, "phi3")
+    assert ids[0] == tokenizer.BOS and all(0 <= i < 32064 for i in ids)
+    assert tokenizer.encode("é", 1000, "", template=False) == [1, 3 + 0xC3, 3 + 0xA9]
+    txt = tokenizer.decode(range(300))
+    assert len(txt) == 300 and json.loads(json.dumps(txt)) == txt and all(32 <= ord(c) < 127 for c in txt)
