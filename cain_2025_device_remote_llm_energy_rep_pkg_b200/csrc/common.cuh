@@ -38,26 +38,6 @@ struct ApiScope {
 #define ACT_BITS  20      // |X| <= 2^20 on the activation grid
 #define PAGE_TOKENS 16    // tokens per KV page
 
-// Activation vector on the block-fixed-point grid (numerics contract):
-// per 32 elements: 3 planes of int8 digits (balanced base 128), scale = 2^e (float), sum of X (int32).
-// Memory image for n elements (nb = n/32):  int8 dig[nb][3][32] | float scale[nb] | int32 bsum[nb]
-struct ActView {
-    const int8_t *dig;
-    const float *scale;
-    const int32_t *bsum;
-};
-__host__ __device__ inline uint64_t act_bytes(int64_t n) { return (uint64_t)(n / QK) * (96 + 8); }
-__host__ __device__ inline ActView act_view(const void *p, int64_t n) {
-    ActView v;
-    v.dig = (const int8_t *)p;
-    v.scale = (const float *)((const char *)p + (n / QK) * 96);
-    v.bsum = (const int32_t *)((const char *)p + (n / QK) * 100);
-    return v;
-}
-
-// Packed Q4_0 matrix: uint4 qs[rows][nb] (GGML nibble order kept) | half d[rows][nb]
-__host__ __device__ inline uint64_t q4_0_packed_bytes(int64_t rows, int64_t cols) { return (uint64_t)rows * (cols / QK) * 18; }
-
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- warp helpers
 __device__ __forceinline__ float warp_sum(float v) {
@@ -105,21 +85,5 @@ __device__ __forceinline__ void act_digits(int X, int &d0, int &d1, int &d2) {
     int X1 = (X - d0) >> 7;
     d1 = ((X1 + 64) & 127) - 64;
     d2 = (X1 - d1) >> 7;
-}
-// store one block (warp-cooperative): lane = element index in block
-__device__ __forceinline__ void act_store_block(void *act, int64_t n, int64_t blk, int lane, int X, float scale) {
-    int d0, d1, d2;
-    act_digits(X, d0, d1, d2);
-    int8_t *dig = (int8_t *)act + blk * 96;
-    dig[lane] = (int8_t)d0;
-    dig[32 + lane] = (int8_t)d1;
-    dig[64 + lane] = (int8_t)d2;
-    int s = X;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) {
-        ((float *)((char *)act + (n / QK) * 96))[blk] = scale;
-        ((int32_t *)((char *)act + (n / QK) * 100))[blk] = s;
-    }
 }
 #endif

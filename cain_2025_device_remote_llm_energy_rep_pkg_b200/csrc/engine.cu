@@ -2,6 +2,7 @@
 // Replaces what happens inside Ollama's POST /api/generate (reference call site
 // experiment/RunnerConfig.py:128-131): model load, prompt evaluation, the batch-1 decode loop.
 #include "kernels.cuh"
+#include "layout.cuh"
 #include "randinit.cuh"
 #include <stdarg.h>
 #include <stdlib.h>
@@ -76,7 +77,11 @@ struct b2_session {
     int out_cap = 0;
     int *d_sampled = nullptr;
     float *x = nullptr, *qkv = nullptr, *attn_out = nullptr, *h = nullptr, *logits = nullptr;
-    void *act_a = nullptr, *act_b = nullptr, *attn_scratch = nullptr, *argmax_scratch = nullptr;
+    void *act_attn = nullptr, *act_h = nullptr, *attn_scratch = nullptr, *argmax_scratch = nullptr;
+    float *pmax = nullptr;
+    int *pidx = nullptr;
+    int head_grid = 0;
+    bool use_pdl = true;
     float *logits_log = nullptr;
     uint64_t logits_log_cap = 0;   // in floats
     cudaGraphExec_t graphs[G_COUNT] = {};
@@ -182,8 +187,11 @@ static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type
     mat.rows = rows;
     mat.cols = cols;
     mat.type = type;
-    return dev_alloc(m->allocs, &mat.packed, q4_0_packed_bytes(rows, cols));
+    B2_TRY(dev_alloc(m->allocs, &mat.packed, packed_q4_0_bytes(rows, cols)));
+    B2_CUDA(cudaMemsetAsync(mat.packed, 0, packed_q4_0_bytes(rows, cols), m->e->stream));   // row / block padding must be zero
+    return B2_OK;
 }
+static inline uint64_t algo_bytes(const Mat &m) { return (uint64_t)m.rows * (m.cols / QK) * 18; }
 
 static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype, int head_qtype, b2_model **out) {
     B2_CHECK(e && out, B2_EINVAL, "NULL engine/out");
@@ -216,9 +224,8 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype,
     if (rc) { b2_model_destroy(m); return rc; }
     // algorithmic bytes per decoded token: every matmul weight once (4.5 bit/weight), LM head included
     uint64_t w = 0;
-    for (auto &ly : m->layers) w += q4_0_packed_bytes(ly.qkv.rows, ly.qkv.cols) + q4_0_packed_bytes(ly.o.rows, ly.o.cols) +
-                                    q4_0_packed_bytes(ly.gateup.rows, ly.gateup.cols) + q4_0_packed_bytes(ly.down.rows, ly.down.cols);
-    w += q4_0_packed_bytes(m->head.rows, m->head.cols);
+    for (auto &ly : m->layers) w += algo_bytes(ly.qkv) + algo_bytes(ly.o) + algo_bytes(ly.gateup) + algo_bytes(ly.down);
+    w += algo_bytes(m->head);
     m->weight_bytes = w;
     *out = m;
     return B2_OK;
@@ -252,26 +259,26 @@ extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
     float nsig = 0.1f, noff = c.norm_plus_one ? 0.0f : 1.0f, wsig = 0.02f, bsig = 0.1f;
     auto key = [&](int kind, uint32_t layer) { return ri_tensor_key(seed, tid_of(kind, layer)); };
-    launch_randinit_q4_0(key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, m->embd.packed, 0, 1, c.vocab, st);
-    if (!c.tied) launch_randinit_q4_0(key(K_OUTPUT, GLOBAL_LAYER), wsig, c.vocab, H, m->head.packed, 0, 1, c.vocab, st);
+    launch_randinit_q4_0(key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, m->embd.packed, 0, 1, st);
+    if (!c.tied) launch_randinit_q4_0(key(K_OUTPUT, GLOBAL_LAYER), wsig, c.vocab, H, m->head.packed, 0, 1, st);
     launch_randinit_f32(key(K_OUT_NORM, GLOBAL_LAYER), nsig, noff, H, m->out_norm, st);
     for (int l = 0; l < c.n_layers; ++l) {
         LayerW &ly = m->layers[l];
         launch_randinit_f32(key(K_ATTN_NORM, l), nsig, noff, H, ly.attn_norm, st);
         launch_randinit_f32(key(K_FFN_NORM, l), nsig, noff, H, ly.ffn_norm, st);
         int64_t tr = qd + 2 * kvd;
-        launch_randinit_q4_0(key(K_Q, l), wsig, qd, H, ly.qkv.packed, 0, 1, tr, st);
-        launch_randinit_q4_0(key(K_K, l), wsig, kvd, H, ly.qkv.packed, qd, 1, tr, st);
-        launch_randinit_q4_0(key(K_V, l), wsig, kvd, H, ly.qkv.packed, qd + kvd, 1, tr, st);
+        launch_randinit_q4_0(key(K_Q, l), wsig, qd, H, ly.qkv.packed, 0, 1, st);
+        launch_randinit_q4_0(key(K_K, l), wsig, kvd, H, ly.qkv.packed, qd, 1, st);
+        launch_randinit_q4_0(key(K_V, l), wsig, kvd, H, ly.qkv.packed, qd + kvd, 1, st);
         if (c.qkv_bias) {
             launch_randinit_f32(key(K_QB, l), bsig, 0.f, qd, ly.qkv_bias, st);
             launch_randinit_f32(key(K_KB, l), bsig, 0.f, kvd, ly.qkv_bias + qd, st);
             launch_randinit_f32(key(K_VB, l), bsig, 0.f, kvd, ly.qkv_bias + qd + kvd, st);
         }
-        launch_randinit_q4_0(key(K_O, l), wsig, H, qd, ly.o.packed, 0, 1, H, st);
-        launch_randinit_q4_0(key(K_GATE, l), wsig, I, H, ly.gateup.packed, 0, 2, 2 * (int64_t)I, st);
-        launch_randinit_q4_0(key(K_UP, l), wsig, I, H, ly.gateup.packed, 1, 2, 2 * (int64_t)I, st);
-        launch_randinit_q4_0(key(K_DOWN, l), wsig, H, I, ly.down.packed, 0, 1, H, st);
+        launch_randinit_q4_0(key(K_O, l), wsig, H, qd, ly.o.packed, 0, 1, st);
+        launch_randinit_q4_0(key(K_GATE, l), wsig, I, H, ly.gateup.packed, 0, 2, st);
+        launch_randinit_q4_0(key(K_UP, l), wsig, I, H, ly.gateup.packed, 1, 2, st);
+        launch_randinit_q4_0(key(K_DOWN, l), wsig, H, I, ly.down.packed, 0, 1, st);
     }
     cudaError_t err = cudaStreamSynchronize(st);
     if (err == cudaSuccess) err = cudaGetLastError();
@@ -307,7 +314,7 @@ static int upload_mat(b2_model *m, Staging &sg, const b2_tensor_desc &t, Mat &ds
     B2_CHECK(src_row0 + nrows <= t.rows, B2_EINVAL, "tensor %s: has %lld rows, need %lld", t.name, (long long)t.rows, (long long)(src_row0 + nrows));
     B2_TRY(sg.ensure(nrows * row_bytes));
     B2_CUDA(cudaMemcpyAsync(sg.buf, (const char *)t.data + src_row0 * row_bytes, nrows * row_bytes, cudaMemcpyHostToDevice, m->e->stream));
-    launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, dst.rows, m->e->stream);
+    launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
     B2_CUDA(cudaStreamSynchronize(m->e->stream));
     return B2_OK;
 }
@@ -424,31 +431,32 @@ static int enqueue_forward(b2_session *s, bool with_head) {
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
-    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
+    const bool pdl = s->use_pdl;
+    int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
     int n = 0;
     float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
-    launch_embed_q4_0(m->embd.packed, m->embd.rows, m->embd.cols, &s->state->cur_token, escale, s->x, st); n++;
+    launch_embed_row(m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, st); n++;
     uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
         LayerW &ly = m->layers[l];
-        launch_rmsnorm_quant(s->x, ly.attn_norm, H, c.rms_eps, c.norm_plus_one, s->act_a, nullptr, st); n++;
-        launch_gemv_q4_0(ly.qkv.packed, ly.qkv.rows, H, s->act_a, ly.qkv_bias, 0, 0, s->qkv, st); n++;
+        launch_gemv(GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                    s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, st, pdl); n++;
         launch_rope_kv(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
                        s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, st); n++;
         launch_attn_decode(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, s->kcache + l * layer_kv, s->vcache + l * layer_kv,
                            s->page_table, s->attn_out, s->attn_scratch, s->max_ctx, st); n++;
-        launch_quant_act(s->attn_out, qd, s->act_b, st); n++;
-        launch_gemv_q4_0(ly.o.packed, H, qd, s->act_b, s->x, 1, 0, s->x, st); n++;
-        launch_rmsnorm_quant(s->x, ly.ffn_norm, H, c.rms_eps, c.norm_plus_one, s->act_a, nullptr, st); n++;
-        launch_gemv_q4_0(ly.gateup.packed, 2 * (int64_t)I, H, s->act_a, nullptr, 2, c.act, s->h, st); n++;
-        launch_quant_act(s->h, I, s->act_b, st); n++;
-        launch_gemv_q4_0(ly.down.packed, H, I, s->act_b, s->x, 1, 0, s->x, st); n++;
+        launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
+        launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
+                    nullptr, nullptr, nullptr, st, pdl); n++;
+        launch_gemv(GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                    nullptr, nullptr, s->act_h, c.act, nullptr, nullptr, nullptr, st, pdl); n++;
+        launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->act_h, s->x, s->x, nullptr, 0,
+                    nullptr, nullptr, nullptr, st, pdl); n++;
     }
     if (with_head) {
-        launch_rmsnorm_quant(s->x, m->out_norm, H, c.rms_eps, c.norm_plus_one, s->act_a, nullptr, st); n++;
-        launch_gemv_q4_0(m->head.packed, c.vocab, H, s->act_a, nullptr, 0, 0, s->logits, st); n++;
+        launch_gemv(GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                    s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, st, pdl); n++;
     }
-    (void)kvd;
     return n;
 }
 
@@ -467,7 +475,7 @@ static int enqueue_graph_body(b2_session *s, int which) {
     case G_DECODE:
     case G_DECODE_LOG:
         if (which == G_DECODE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
-        launch_argmax(s->logits, s->m->cfg.vocab, s->d_sampled, s->argmax_scratch, st); n++;
+        launch_argmax_partials(s->pmax, s->pidx, s->head_grid, s->d_sampled, st); n++;
         k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
         n += enqueue_forward(s, true);
         k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
@@ -517,6 +525,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     s->n_pages = (max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
     const char *ng = getenv("B2_NO_GRAPH");
     s->use_graphs = !(ng && ng[0] == '1');
+    const char *np = getenv("B2_NO_PDL");
+    s->use_pdl = !(np && np[0] == '1');
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
     uint64_t kv_elems = (uint64_t)c.n_layers * s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     int rc = B2_OK;
@@ -535,8 +545,10 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->attn_out, qd * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->h, I * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->logits, (uint64_t)c.vocab * 4))) break;
-        if ((rc = dev_alloc(s->allocs, &s->act_a, act_bytes(H)))) break;
-        if ((rc = dev_alloc(s->allocs, &s->act_b, act_bytes(qd > I ? qd : I)))) break;
+        if ((rc = dev_alloc(s->allocs, &s->act_attn, a3_bytes(qd)))) break;
+        if ((rc = dev_alloc(s->allocs, &s->act_h, a3_bytes(I)))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->pmax, 1024 * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->pidx, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(c.n_heads, hd)))) break;
         if ((rc = dev_alloc(s->allocs, &s->argmax_scratch, argmax_scratch_bytes()))) break;
     } while (0);
@@ -548,6 +560,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     if (e == cudaSuccess) e = cudaMemset(s->attn_scratch, 0, attn_scratch_bytes(c.n_heads, hd));
     if (e == cudaSuccess) e = cudaMemset(s->argmax_scratch, 0, argmax_scratch_bytes());
     if (e == cudaSuccess) e = cudaMemset(s->state, 0, sizeof(DevState));
+    if (e == cudaSuccess) e = cudaMemset(s->act_attn, 0, a3_bytes(qd));   // padding blocks of the A3 vectors stay zero
+    if (e == cudaSuccess) e = cudaMemset(s->act_h, 0, a3_bytes(I));
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
     if (e != cudaSuccess) {

@@ -7,83 +7,7 @@
 //   attn_decode       a3.5  paged attention over the cache (GQA/MQA/MHA), split over the context
 //   argmax            a3.8  greedy sampler
 #include "kernels.cuh"
-#include "randinit.cuh"
-
-// =============================================================================== weight re-pack
-// GGML Q4_0 row-major blocks (18 B: f16 d | 16 B nibbles) -> packed {uint4 qs[rows][nb] | half d[rows][nb]}.
-// One thread per block.  dst row = dst_row0 + r * dst_row_stride (stride 2 interleaves gate/up rows).
-__global__ void k_pack_q4_0(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, uint4 *__restrict__ qs,
-                            __half *__restrict__ d, int64_t dst_row0, int64_t dst_row_stride) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= rows * nb) return;
-    int64_t r = i / nb, b = i - r * nb;
-    const uint8_t *p = src + i * 18;
-    uint16_t dbits = (uint16_t)p[0] | ((uint16_t)p[1] << 8);
-    uint32_t w[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        w[k] = (uint32_t)p[2 + 4 * k] | ((uint32_t)p[3 + 4 * k] << 8) | ((uint32_t)p[4 + 4 * k] << 16) | ((uint32_t)p[5 + 4 * k] << 24);
-    int64_t o = (dst_row0 + r * dst_row_stride) * nb + b;
-    qs[o] = make_uint4(w[0], w[1], w[2], w[3]);
-    d[o] = __ushort_as_half(dbits);
-}
-void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride,
-                      int64_t total_rows, cudaStream_t st) {
-    int64_t nb = cols / QK, n = rows * nb;
-    PackedQ4_0 v = packed_q4_0_view(d_packed, total_rows, cols);
-    k_pack_q4_0<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, (uint4 *)v.qs, (__half *)v.d, dst_row0, dst_row_stride);
-}
-
-// =============================================================================== random init on device
-// Same recipe as oracle/randinit.py and b2_randinit_tensor (randinit.cuh): integer Irwin-Hall gaussian,
-// then the ggml Q4_0 quantiser with explicitly rounded IEEE ops => byte-identical to the host generator.
-__global__ void k_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t nb, uint4 *__restrict__ qs, __half *__restrict__ d,
-                                int64_t dst_row0, int64_t dst_row_stride) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= rows * nb) return;
-    int64_t r = i / nb, b = i - r * nb;
-    float x[QK];
-    ri_gauss_block(key, (uint64_t)i * QK, sigma, x);
-    uint16_t dbits;
-    uint32_t w[4];
-    ri_quant_q4_0(x, dbits, w);
-    int64_t o = (dst_row0 + r * dst_row_stride) * nb + b;
-    qs[o] = make_uint4(w[0], w[1], w[2], w[3]);
-    d[o] = __ushort_as_half(dbits);
-}
-void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0,
-                          int64_t dst_row_stride, int64_t total_rows, cudaStream_t st) {
-    int64_t nb = cols / QK, n = rows * nb;
-    PackedQ4_0 v = packed_q4_0_view(d_packed, total_rows, cols);
-    k_randinit_q4_0<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, sigma, rows, nb, (uint4 *)v.qs, (__half *)v.d, dst_row0, dst_row_stride);
-}
-__global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *__restrict__ out) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = ri_add(ri_mul(ri_gauss(key, (uint64_t)i), sigma), offset);
-}
-void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st) {
-    k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out);
-}
-
-// =============================================================================== embedding row
-__global__ void k_embed_q4_0(const uint4 *__restrict__ qs, const __half *__restrict__ d, int64_t nb, const int *__restrict__ token,
-                             float scale, float *__restrict__ x) {
-    int64_t row = *token;
-    for (int64_t b = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; b < nb; b += (int64_t)gridDim.x * (blockDim.x / 32)) {
-        int lane = threadIdx.x & 31;
-        const uint8_t *q = (const uint8_t *)&qs[row * nb + b];
-        uint8_t byte = q[lane & 15];
-        int v = (lane < 16 ? (byte & 0x0F) : (byte >> 4)) - 8;
-        float val = (float)v * __half2float(d[row * nb + b]);
-        if (scale != 1.0f) val = val * scale;
-        x[b * QK + lane] = val;
-    }
-}
-void launch_embed_q4_0(const void *d_packed, int64_t rows, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st) {
-    PackedQ4_0 v = packed_q4_0_view(d_packed, rows, cols);
-    int64_t nb = cols / QK;
-    k_embed_q4_0<<<(unsigned)((nb + 7) / 8), 256, 0, st>>>(v.qs, v.d, nb, d_token, scale, d_x);
-}
+#include "layout.cuh"
 
 // =============================================================================== activation grid
 __global__ void k_quant_act(const float *__restrict__ x, int64_t n, void *__restrict__ act) {
@@ -92,7 +16,7 @@ __global__ void k_quant_act(const float *__restrict__ x, int64_t n, void *__rest
     for (int64_t b = (int64_t)blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32; b < nb; b += (int64_t)gridDim.x * (blockDim.x / 32)) {
         float s;
         int X = act_grid_lane(x[b * QK + lane], s);
-        act_store_block(act, n, b, lane, X, s);
+        a3_store_block(act, n, b, lane, X, s);
     }
 }
 void launch_quant_act(const float *d_x, int64_t n, void *d_act, cudaStream_t st) {
@@ -128,99 +52,12 @@ __global__ void __launch_bounds__(1024) k_rmsnorm_quant(const float *__restrict_
         if (y_opt) y_opt[i] = yv;
         float s;
         int X = act_grid_lane(yv, s);
-        act_store_block(act, n, b, lane, X, s);
+        a3_store_block(act, n, b, lane, X, s);
     }
 }
 void launch_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt, cudaStream_t st) {
     int threads = n >= 4096 ? 1024 : (n >= 1024 ? 512 : 256);
     k_rmsnorm_quant<<<1, threads, 0, st>>>(d_x, d_w, (int)n, eps, plus_one, d_act, d_y_opt);
-}
-
-// =============================================================================== Q4_0 GEMV
-// One warp computes two consecutive rows (a (gate,up) pair in mode 2); lanes stride over the 32-weight
-// blocks of the row with 128-bit loads.  Per block the dot product is exact integer arithmetic:
-//   T = sum_j q_j * X_j - 8 * sum_j X_j,   X = d2*16384 + d1*128 + d0   (three dp4a digit planes)
-//   acc += float(T) * (d_w * 2^e)
-__device__ __forceinline__ float act_fn(float g, int act) {
-    if (act == B2_ACT_SILU) return g / (1.0f + expf(-g));
-    float g3 = 0.044715f * g * g * g;
-    return 0.5f * g * (1.0f + tanhf(0.7978845608028654f * (g + g3)));
-}
-
-__device__ __forceinline__ int q4_block_dot(const uint4 w, const uint4 *D /*6*/, int bsum) {
-    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-    int S[3] = {0, 0, 0};
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const uint32_t dl[4] = {D[2 * c].x, D[2 * c].y, D[2 * c].z, D[2 * c].w};
-        const uint32_t dh[4] = {D[2 * c + 1].x, D[2 * c + 1].y, D[2 * c + 1].z, D[2 * c + 1].w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            S[c] = dp4a_us(ww[k] & 0x0F0F0F0Fu, dl[k], S[c]);
-            S[c] = dp4a_us((ww[k] >> 4) & 0x0F0F0F0Fu, dh[k], S[c]);
-        }
-    }
-    return S[2] * 16384 + S[1] * 128 + S[0] - 8 * bsum;
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(256) k_gemv_q4_0(const uint4 *__restrict__ qs, const __half *__restrict__ dw, int rows, int nb,
-                                                   const int8_t *__restrict__ dig, const float *__restrict__ ascale,
-                                                   const int32_t *__restrict__ absum, const float *__restrict__ bias_or_res, int act,
-                                                   float *__restrict__ y) {
-    const int lane = threadIdx.x & 31;
-    const int pair = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int r0 = pair * 2;
-    if (r0 >= rows) return;
-    const bool has1 = (r0 + 1) < rows;
-    const uint4 *q0 = qs + (int64_t)r0 * nb;
-    const uint4 *q1 = qs + (int64_t)(has1 ? r0 + 1 : r0) * nb;
-    const __half *d0 = dw + (int64_t)r0 * nb;
-    const __half *d1 = dw + (int64_t)(has1 ? r0 + 1 : r0) * nb;
-    float acc0 = 0.f, acc1 = 0.f;
-    for (int b = lane; b < nb; b += 32) {
-        uint4 w0 = ldg_stream(q0 + b);
-        uint4 w1 = ldg_stream(q1 + b);
-        float s0 = __half2float(d0[b]);
-        float s1 = __half2float(d1[b]);
-        const uint4 *dp = (const uint4 *)(dig + (int64_t)b * 96);
-        uint4 D[6];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) D[k] = __ldg(dp + k);
-        float as = __ldg(ascale + b);
-        int bs = __ldg(absum + b);
-        int T0 = q4_block_dot(w0, D, bs);
-        int T1 = q4_block_dot(w1, D, bs);
-        acc0 = fmaf((float)T0, s0 * as, acc0);
-        acc1 = fmaf((float)T1, s1 * as, acc1);
-    }
-    acc0 = warp_sum(acc0);
-    acc1 = warp_sum(acc1);
-    if (lane == 0) {
-        if (MODE == 0) {
-            y[r0] = bias_or_res ? acc0 + bias_or_res[r0] : acc0;
-            if (has1) y[r0 + 1] = bias_or_res ? acc1 + bias_or_res[r0 + 1] : acc1;
-        } else if (MODE == 1) {
-            y[r0] = bias_or_res[r0] + acc0;
-            if (has1) y[r0 + 1] = bias_or_res[r0 + 1] + acc1;
-        } else {
-            y[pair] = act_fn(acc0, act) * acc1;
-        }
-    }
-}
-void launch_gemv_q4_0(const void *d_packed, int64_t rows, int64_t cols, const void *d_act, const float *d_bias_or_res,
-                      int mode, int act, float *d_y, cudaStream_t st) {
-    PackedQ4_0 v = packed_q4_0_view(d_packed, rows, cols);
-    ActView a = act_view(d_act, cols);
-    int nb = (int)(cols / QK);
-    int pairs = (int)((rows + 1) / 2);
-    unsigned grid = (unsigned)((pairs + 7) / 8);
-    if (mode == 0)
-        k_gemv_q4_0<0><<<grid, 256, 0, st>>>(v.qs, v.d, (int)rows, nb, a.dig, a.scale, a.bsum, d_bias_or_res, act, d_y);
-    else if (mode == 1)
-        k_gemv_q4_0<1><<<grid, 256, 0, st>>>(v.qs, v.d, (int)rows, nb, a.dig, a.scale, a.bsum, d_bias_or_res, act, d_y);
-    else
-        k_gemv_q4_0<2><<<grid, 256, 0, st>>>(v.qs, v.d, (int)rows, nb, a.dig, a.scale, a.bsum, d_bias_or_res, act, d_y);
 }
 
 // =============================================================================== RoPE + KV append
@@ -441,6 +278,16 @@ __global__ void __launch_bounds__(256) k_argmax(const float *__restrict__ x, int
         warp_argmax(v, idx);
         if (threadIdx.x == 0) *out = idx;
     }
+}
+__global__ void k_argmax_partials(const float *__restrict__ pv, const int *__restrict__ pi, int n, int *__restrict__ out) {
+    float v = -INFINITY;
+    int idx = 0x7fffffff;
+    for (int b = threadIdx.x; b < n; b += 32) arg_better(v, idx, pv[b], pi[b]);
+    warp_argmax(v, idx);
+    if (threadIdx.x == 0) *out = idx;
+}
+void launch_argmax_partials(const float *pmax, const int *pidx, int n, int32_t *d_out, cudaStream_t st) {
+    k_argmax_partials<<<1, 32, 0, st>>>(pmax, pidx, n, d_out);
 }
 void launch_argmax(const float *d_logits, int64_t n, int32_t *d_out, void *d_scratch, cudaStream_t st) {
     float *pv = (float *)d_scratch;

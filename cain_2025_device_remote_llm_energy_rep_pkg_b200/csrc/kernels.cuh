@@ -14,30 +14,23 @@ struct DevState {
     int prompt_idx; // next prompt token to feed during prefill
 };
 
-struct PackedQ4_0 {   // view of a packed matrix
-    const uint4 *qs;
-    const __half *d;
-};
-inline PackedQ4_0 packed_q4_0_view(const void *p, int64_t rows, int64_t cols) {
-    PackedQ4_0 v;
-    v.qs = (const uint4 *)p;
-    v.d = (const __half *)((const char *)p + (uint64_t)rows * (cols / QK) * 16);
-    return v;
-}
-
-// weight re-pack / init
-void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride,
-                      int64_t total_rows, cudaStream_t st);
-void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0,
-                          int64_t dst_row_stride, int64_t total_rows, cudaStream_t st);
+// weight re-pack / init into the streaming layout (layout.cuh)
+void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
+void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st);
 
-// stages
-void launch_embed_q4_0(const void *d_packed, int64_t rows, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st);
+// streaming GEMV (gemv.cu)
+enum { GEMV_IN_NORM = 0, GEMV_IN_ACT = 1 };
+enum { GEMV_OUT_BIAS = 0, GEMV_OUT_RES = 1, GEMV_OUT_ACTMUL = 2, GEMV_OUT_LOGITS = 3 };
+int gemv_grid(int n_tiles, int tile_align);
+cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
+                        float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
+                        float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl);
+void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st);
+
+// small stages (kernels.cu)
 void launch_quant_act(const float *d_x, int64_t n, void *d_act, cudaStream_t st);
 void launch_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt, cudaStream_t st);
-void launch_gemv_q4_0(const void *d_packed, int64_t rows, int64_t cols, const void *d_act, const float *d_bias_or_res,
-                      int mode, int act, float *d_y, cudaStream_t st);
 void launch_rope_kv(float *d_qkv, int nh, int nkv, int hd, const int *d_pos, int pos_imm, const float *d_cos, const float *d_sin,
                     __half *d_k, __half *d_v, const int32_t *d_page_table, cudaStream_t st);
 // scratch: float[nh*ATTN_NSPLIT*(hd+2)] then int counters[nh] (zeroed once; the kernel leaves them zero)
@@ -47,3 +40,5 @@ void launch_attn_decode(const float *d_q, int nh, int nkv, int hd, const int *d_
 // scratch: float[ARGMAX_BLOCKS] + int[ARGMAX_BLOCKS] + int counter (zeroed once)
 uint64_t argmax_scratch_bytes();
 void launch_argmax(const float *d_logits, int64_t n, int32_t *d_out, void *d_scratch, cudaStream_t st);
+// final arg-max over the per-CTA partials of the LM-head GEMV, token commit and next-token bookkeeping
+void launch_argmax_partials(const float *pmax, const int *pidx, int n, int32_t *d_out, cudaStream_t st);

@@ -1,0 +1,64 @@
+// layout.cuh — HBM data layouts of the decode path.
+//
+// Activation vector ("A3"), n elements, nbp = blocks of 32 padded up to a multiple of 4:
+//   [0, nbp*96)        int8 digits: block b at b*96, digit plane c (0..2) at +c*32, 8 words in MMA-fragment
+//                      order: word position 2*t+h holds elements h*16+4t .. h*16+4t+3  (t 0..3, h 0..1)
+//   [nbp*96, nbp*100)  float scale[nbp] = 2^(e-19)  (0 for padding blocks)
+//   X = d2*16384 + d1*128 + d0 (balanced base-128 digits), x_hat = X * scale.
+//
+// Q4_0 weight matrix [rows, cols], packed for streaming: rows in tiles of 16, blocks padded to nbp (x4):
+//   tile T at T*nbp*288.  Inside a tile the K dimension is cut into chunks of KC=64 blocks (the last may be
+//   shorter); chunk ck starts at ck*KC*288 and holds cb blocks as
+//     nibbles  cb*256 B : block-group j (4 blocks) at j*1024: [half hf][g 0..7][t 0..3] uint4 =
+//                         word t of blocks 4j..4j+3 of tile row hf*8+g; nibbles stored as two's complement
+//                         of (q-8) (GGML nibble XOR 8), GGML nibble order kept (low nibble = element i,
+//                         high nibble = element i+16 of the block)
+//     scales   cb*32 B  : [block][g] half2 = (d of row g, d of row g+8)
+//   One chunk is one contiguous cp.async.bulk; one warp-wide LDS.128 of the nibble area feeds the A fragments
+//   of four mma.m16n8k32 instructions.
+#pragma once
+#include "common.cuh"
+
+#define TILE_ROWS 16
+#define KC 64                 // blocks per chunk
+#define BLOCK_BYTES 288       // 16 rows * 16 B nibbles + 16 rows * 2 B scales, per 32-wide block column of a tile
+#define CHUNK_BYTES (KC * BLOCK_BYTES)
+
+__host__ __device__ inline int64_t pad4(int64_t nb) { return (nb + 3) & ~(int64_t)3; }
+__host__ __device__ inline int64_t nblocks_padded(int64_t cols) { return pad4((cols + QK - 1) / QK); }
+__host__ __device__ inline int64_t ntiles(int64_t rows) { return (rows + TILE_ROWS - 1) / TILE_ROWS; }
+__host__ __device__ inline uint64_t packed_q4_0_bytes(int64_t rows, int64_t cols) {
+    return (uint64_t)ntiles(rows) * nblocks_padded(cols) * BLOCK_BYTES;
+}
+__host__ __device__ inline uint64_t a3_bytes(int64_t n) { return (uint64_t)nblocks_padded(n) * 100; }
+// byte offset of element e (0..31) inside a 32-byte digit plane
+__host__ __device__ inline int a3_elem_off(int e) { return ((2 * ((e & 15) >> 2) + (e >> 4)) << 2) + (e & 3); }
+
+// location of (row, block) inside the packed matrix: returns byte offsets of the 4-byte nibble word t and of the scale
+struct PackedLoc {
+    uint64_t word0;   // byte offset of word t=0 for this (row, block); word t is at word0 + t*16
+    uint64_t scale;   // byte offset of the half scale
+};
+__host__ __device__ inline PackedLoc packed_loc(int64_t row, int64_t blk, int64_t nbp) {
+    int64_t T = row / TILE_ROWS, r = row % TILE_ROWS, hf = r >> 3, g = r & 7;
+    int64_t ck = blk / KC, bl = blk % KC;
+    int64_t cb = (nbp - ck * KC) < KC ? (nbp - ck * KC) : KC;
+    uint64_t chunk = (uint64_t)T * nbp * BLOCK_BYTES + (uint64_t)ck * KC * BLOCK_BYTES;
+    PackedLoc p;
+    p.word0 = chunk + (uint64_t)(bl >> 2) * 1024 + (uint64_t)(hf * 8 + g) * 64 + (uint64_t)(bl & 3) * 4;
+    p.scale = chunk + (uint64_t)cb * 256 + (uint64_t)bl * 32 + (uint64_t)g * 4 + (uint64_t)hf * 2;
+    return p;
+}
+
+#ifdef __CUDACC__
+// store one activation block (warp-cooperative, lane = element) into an A3 vector of n elements
+__device__ __forceinline__ void a3_store_block(void *act, int64_t n, int64_t blk, int lane, int X, float scale) {
+    int d0, d1, d2;
+    act_digits(X, d0, d1, d2);
+    uint8_t *dst = (uint8_t *)act + blk * 96 + a3_elem_off(lane);
+    dst[0] = (uint8_t)d0;
+    dst[32] = (uint8_t)d1;
+    dst[64] = (uint8_t)d2;
+    if (lane == 0) ((float *)((uint8_t *)act + nblocks_padded(n) * 96))[blk] = scale;
+}
+#endif

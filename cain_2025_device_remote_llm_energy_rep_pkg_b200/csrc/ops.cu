@@ -2,31 +2,33 @@
 // tests, bench.py and ncu can drive each stage of the decode path in isolation; the engine (engine.cu)
 // calls the same launchers on its own stream.
 #include "kernels.cuh"
+#include "layout.cuh"
 #include "sampler.cuh"
 
 extern "C" uint64_t b2_packed_bytes(int type, int64_t rows, int64_t cols) {
     if (type != B2_T_Q4_0 || cols % QK) return 0;
-    return q4_0_packed_bytes(rows, cols);
+    return packed_q4_0_bytes(rows, cols);
 }
-extern "C" uint64_t b2_act_bytes(int64_t n) { return act_bytes(n); }
+extern "C" uint64_t b2_act_bytes(int64_t n) { return a3_bytes(n); }
 
 extern "C" int b2_op_pack_weights(int type, int64_t rows, int64_t cols, const void *src, const void *src2, void *d_packed) {
     ApiScope _scope("b2_op_pack_weights");
     B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_op_pack_weights: type %d not supported", type);
     B2_CHECK(src && d_packed && rows > 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_pack_weights: bad arguments");
     uint64_t bytes = (uint64_t)rows * (cols / QK) * 18;
+    int64_t total = src2 ? 2 * rows : rows, stride = src2 ? 2 : 1;
     void *stg = nullptr;
     B2_CUDA(cudaMalloc(&stg, bytes));
-    int64_t total = src2 ? 2 * rows : rows, stride = src2 ? 2 : 1;
-    cudaError_t e = cudaMemcpy(stg, src, bytes, cudaMemcpyHostToDevice);
+    cudaError_t e = cudaMemset(d_packed, 0, packed_q4_0_bytes(total, cols));
+    if (e == cudaSuccess) e = cudaMemcpy(stg, src, bytes, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
-        launch_pack_q4_0(stg, rows, cols, d_packed, 0, stride, total, 0);
+        launch_pack_q4_0(stg, rows, cols, d_packed, 0, stride, 0);
         e = cudaDeviceSynchronize();
     }
     if (e == cudaSuccess && src2) {
         e = cudaMemcpy(stg, src2, bytes, cudaMemcpyHostToDevice);
         if (e == cudaSuccess) {
-            launch_pack_q4_0(stg, rows, cols, d_packed, 1, stride, total, 0);
+            launch_pack_q4_0(stg, rows, cols, d_packed, 1, stride, 0);
             e = cudaDeviceSynchronize();
         }
     }
@@ -39,6 +41,7 @@ extern "C" int b2_op_quant_act(const float *d_x, int64_t n, void *d_act) {
     ApiScope _scope("b2_op_quant_act");
     B2_CHECK(d_x && d_act && n >= 0 && n % QK == 0, B2_EINVAL, "b2_op_quant_act: n must be a multiple of 32");
     if (n == 0) return B2_OK;
+    B2_CUDA(cudaMemsetAsync(d_act, 0, a3_bytes(n), 0));
     launch_quant_act(d_x, n, d_act, 0);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
@@ -46,6 +49,7 @@ extern "C" int b2_op_quant_act(const float *d_x, int64_t n, void *d_act) {
 extern "C" int b2_op_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt) {
     ApiScope _scope("b2_op_rmsnorm_quant");
     B2_CHECK(d_x && d_w && d_act && n > 0 && n % QK == 0 && n <= 16384, B2_EINVAL, "b2_op_rmsnorm_quant: n must be a multiple of 32 in (0,16384]");
+    B2_CUDA(cudaMemsetAsync(d_act, 0, a3_bytes(n), 0));
     launch_rmsnorm_quant(d_x, d_w, n, eps, plus_one, d_act, d_y_opt, 0);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
@@ -57,9 +61,51 @@ extern "C" int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t 
     B2_CHECK(d_packed && d_act && d_y && rows >= 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_gemv: bad arguments");
     B2_CHECK(mode >= 0 && mode <= 2, B2_EINVAL, "b2_op_gemv: mode %d", mode);
     B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_gemv: mode 1 needs the residual vector");
-    B2_CHECK(mode != 2 || rows % 2 == 0, B2_EINVAL, "b2_op_gemv: mode 2 needs an even row count");
+    B2_CHECK(mode != 2 || rows % 64 == 0, B2_EINVAL, "b2_op_gemv: mode 2 needs rows %% 64 == 0 (32 gate/up pairs per activation block)");
     if (rows == 0) return B2_OK;
-    launch_gemv_q4_0(d_packed, rows, cols, d_act, d_bias_or_res, mode, act, d_y, 0);
+    void *act_out = nullptr;
+    if (mode == 2) {   // the kernel also emits the activation-grid image of h; the op-level caller only wants h
+        B2_CUDA(cudaMalloc(&act_out, a3_bytes(rows / 2)));
+        B2_CUDA(cudaMemset(act_out, 0, a3_bytes(rows / 2)));
+    }
+    cudaError_t e = launch_gemv(GEMV_IN_ACT, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_act, d_y, d_bias_or_res, act_out, act,
+                                nullptr, nullptr, nullptr, 0, false);
+    if (e == cudaSuccess && act_out) e = cudaDeviceSynchronize();
+    if (act_out) cudaFree(act_out);
+    B2_CUDA(e);
+    B2_CUDA(cudaGetLastError());
+    return B2_OK;
+}
+// Fused form used by the engine: RMSNorm + activation grid + GEMV (+ epilogue).  mode 0..2 as b2_op_gemv; mode 3
+// writes logits to d_y and the index of their maximum to d_argmax.  d_act_out (mode 2, optional) receives the
+// activation-grid image of the result (b2_act_bytes(rows/2) bytes).
+extern "C" int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_norm_w, float eps,
+                               int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y, void *d_act_out, int32_t *d_argmax) {
+    ApiScope _scope("b2_op_norm_gemv");
+    B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_op_norm_gemv: type %d not supported", type);
+    B2_CHECK(d_packed && d_x && d_norm_w && rows > 0 && cols > 0 && cols % QK == 0 && cols <= 16384, B2_EINVAL, "b2_op_norm_gemv: bad arguments");
+    B2_CHECK(mode >= 0 && mode <= 3, B2_EINVAL, "b2_op_norm_gemv: mode %d", mode);
+    B2_CHECK(mode == 2 || d_y, B2_EINVAL, "b2_op_norm_gemv: d_y is NULL");
+    B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_norm_gemv: mode 1 needs the residual vector");
+    B2_CHECK(mode != 2 || rows % 64 == 0, B2_EINVAL, "b2_op_norm_gemv: mode 2 needs rows %% 64 == 0");
+    B2_CHECK(mode != 3 || d_argmax, B2_EINVAL, "b2_op_norm_gemv: mode 3 needs d_argmax");
+    void *tmp = nullptr, *act_out = d_act_out;
+    float *pmax = nullptr;
+    int *pidx = nullptr;
+    uint64_t need = (mode == 2 && !d_act_out) ? a3_bytes(rows / 2) : (mode == 3 ? 8192 : 0);
+    if (need) {
+        B2_CUDA(cudaMalloc(&tmp, need));
+        B2_CUDA(cudaMemset(tmp, 0, need));
+        if (mode == 2) act_out = tmp;
+        else { pmax = (float *)tmp; pidx = (int *)((char *)tmp + 4096); }
+    }
+    int grid = 0;
+    cudaError_t e = launch_gemv(GEMV_IN_NORM, mode, d_packed, rows, cols, d_x, d_norm_w, eps, plus_one, nullptr, d_y, d_bias_or_res, act_out, act,
+                                pmax, pidx, &grid, 0, false);
+    if (e == cudaSuccess && mode == 3) launch_argmax_partials(pmax, pidx, grid, d_argmax, 0);
+    if (e == cudaSuccess && tmp) e = cudaDeviceSynchronize();
+    if (tmp) cudaFree(tmp);
+    B2_CUDA(e);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
 }

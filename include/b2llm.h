@@ -150,14 +150,19 @@ int b2_dev_sync(void);
  * `src` and row i of `src2` (gate/up pairing); src2 NULL otherwise. */
 uint64_t b2_packed_bytes(int type, int64_t rows, int64_t cols);
 int b2_op_pack_weights(int type, int64_t rows, int64_t cols, const void *src, const void *src2, void *d_packed);
-/* Activation grid: x f32[n] -> three int8 digit planes + per-32 scale/sum (b2_act_bytes(n) bytes). */
+/* Activation grid: x f32[n] -> three int8 digit planes + per-32 scale (b2_act_bytes(n) bytes; layout in DESIGN.md). */
 uint64_t b2_act_bytes(int64_t n);
 int b2_op_quant_act(const float *d_x, int64_t n, void *d_act);
 int b2_op_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt);
 /* y[rows] = W[rows,cols] * act (+ bias) ; mode 0: y = Wx(+bias); 1: y = res + Wx; 2: rows are (gate,up)
- * pairs, y[rows/2] = act(gate)*up. */
+ * pairs, y[rows/2] = act(gate)*up (rows must be a multiple of 64). */
 int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const void *d_act,
                const float *d_bias_or_res, int mode, int act, float *d_y);
+/* The engine's fused form: RMSNorm(x, norm_w) -> activation grid -> y = W * (.) with the same epilogues; mode 3 writes
+ * logits to d_y and the arg-max index (lowest index on ties) to d_argmax; mode 2 can also return the activation-grid
+ * image of its result in d_act_out (b2_act_bytes(rows/2) bytes, may be NULL). */
+int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_norm_w, float eps,
+                    int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y, void *d_act_out, int32_t *d_argmax);
 /* RoPE (rotate-half) on q[nh,hd] in place and on k, then f16 append of k,v at position pos of a paged cache. */
 int b2_op_rope_kv(float *d_qkv, int nh, int nkv, int hd, int pos, const float *d_cos, const float *d_sin,
                   void *d_kcache, void *d_vcache, const int32_t *d_page_table, int page_tokens);

@@ -36,9 +36,10 @@ def test_struct_layout_matches_header(lib):
 
 
 def test_size_helpers(lib):
-    assert lib.b2_packed_bytes(2, 10, 64) == 10 * 2 * 18
+    assert lib.b2_packed_bytes(2, 10, 64) == 1 * 4 * 288          # 1 tile of 16 rows, 2 blocks padded to 4, 288 B per block column
+    assert lib.b2_packed_bytes(2, 4096, 4096) == 4096 * 4096 // 32 * 18   # no padding at real sizes: 4.5 bit/weight
     assert lib.b2_packed_bytes(2, 10, 33) == 0
-    assert lib.b2_act_bytes(64) == 2 * 104
+    assert lib.b2_act_bytes(64) == 4 * 100
 
 
 @pytest.mark.skipif(HAS_GPU, reason="checks the no-device behaviour")

@@ -24,13 +24,24 @@ def chk(lib, rc):
     assert rc == 0, lib.b2_last_error().decode()
 
 
+def a3_elem_off(e):
+    return ((2 * ((e & 15) >> 2) + (e >> 4)) << 2) + (e & 3)
+
+
+ELEM_OFF = np.array([a3_elem_off(e) for e in range(32)])
+
+
 def read_act(lib, buf, n):
+    """-> (digits int8[3, n] in element order, scale float32[n/32]) from the engine's activation image."""
     nb = n // 32
-    raw = buf.to_numpy(np.uint8, (nb * 104,))
-    dig = raw[: nb * 96].view(np.int8).reshape(nb, 3, 32)
-    scale = raw[nb * 96: nb * 100].view(np.float32)
-    bsum = raw[nb * 100:].view(np.int32)
-    return dig, scale, bsum
+    nbp = (nb + 3) // 4 * 4
+    assert lib.b2_act_bytes(n) == nbp * 100
+    raw = buf.to_numpy(np.uint8, (nbp * 100,))
+    planes = raw[: nbp * 96].view(np.int8).reshape(nbp, 3, 32)
+    assert not planes[nb:].any()                                  # padding blocks are zero
+    dig = planes[:nb][:, :, ELEM_OFF]                             # fragment order -> element order
+    scale = raw[nbp * 96: nbp * 100].view(np.float32)[:nb]
+    return dig.transpose(1, 0, 2).reshape(3, n), scale
 
 
 def make_act(lib, D, x):
@@ -51,12 +62,10 @@ def test_quant_act_bit_exact(lib, D, n):
         x[64] = 2.0                   # exact power-of-two maximum
         x[65:96] = np.float32(2.0) * np.float32(1 - 2 ** -24)
     act = make_act(lib, D, x)
-    dig, scale, bsum = read_act(lib, act, n)
+    dig, scale = read_act(lib, act, n)
     odig, oe = fxp_digits(x)
-    assert np.array_equal(dig.transpose(1, 0, 2).reshape(3, n), odig)
+    assert np.array_equal(dig, odig)
     assert np.array_equal(scale, np.ldexp(np.float32(1), oe).astype(np.float32))
-    X = odig[2].astype(np.int64) * 16384 + odig[1].astype(np.int64) * 128 + odig[0]
-    assert np.array_equal(bsum, X.reshape(-1, 32).sum(1).astype(np.int32))
 
 
 def test_quant_act_rejects_ragged(lib, D):
@@ -81,9 +90,9 @@ def test_rmsnorm_quant(lib, D, n, plus_one):
     # fp32, differs only by the summation order of mean(x^2): 1e-6 relative
     assert np.abs(y - ref.numpy()).max() <= 1e-6 * np.abs(ref.numpy()).max()
     # the digits are exactly the grid of the kernel's own y
-    dig, scale, bsum = read_act(lib, act, n)
+    dig, scale = read_act(lib, act, n)
     odig, oe = fxp_digits(y)
-    assert np.array_equal(dig.transpose(1, 0, 2).reshape(3, n), odig)
+    assert np.array_equal(dig, odig)
     assert np.array_equal(scale, np.ldexp(np.float32(1), oe).astype(np.float32))
 
 
@@ -103,7 +112,7 @@ def ref_gemv(blob, x):
     return W @ xq, np.abs(W) @ np.abs(xq)
 
 
-@pytest.mark.parametrize("rows,cols", [(1, 32), (7, 288), (64, 4096), (33, 1184), (16, 14336), (257, 1536)])
+@pytest.mark.parametrize("rows,cols", [(1, 32), (7, 288), (64, 4096), (33, 1184), (16, 14336), (257, 1536), (4096, 4096), (6000, 2080)])
 def test_gemv_modes(lib, D, rows, cols):
     rng = np.random.default_rng(rows * 131 + cols)
     Wf = (rng.standard_normal((rows, cols)) * 0.02).astype(np.float32)
@@ -145,7 +154,52 @@ def test_gemv_gate_up_pairs(lib, D, act_id, I, H):
     a = gt / (1 + torch.exp(-gt)) if act_id == 0 else 0.5 * gt * (1 + torch.tanh(0.7978845608028654 * (gt + 0.044715 * gt ** 3)))
     ref = a.numpy() * uv
     assert np.abs(y - ref).max() <= 2e-5 * np.abs(ref).max()
-    assert lib.b2_op_gemv(2, dW.ptr, 2 * I + 1, H, act.ptr, None, 2, act_id, dy.ptr) == -1
+    assert lib.b2_op_gemv(2, dW.ptr, 2 * I + 2, H, act.ptr, None, 2, act_id, dy.ptr) == -1
+
+
+@pytest.mark.parametrize("V,H,plus_one", [(1000, 288, 0), (1024, 512, 1), (32064, 3072, 0), (5000, 4096, 0)])
+def test_norm_gemv_logits_and_argmax(lib, D, V, H, plus_one):
+    """The engine's fused head: RMSNorm -> activation grid -> GEMV -> logits + greedy token."""
+    rng = np.random.default_rng(V + H)
+    blob = Q.quantize_q4_0((rng.standard_normal((V, H)) * 0.02).astype(np.float32))
+    x = (rng.standard_normal(H) * 2).astype(np.float32)
+    w = (rng.standard_normal(H) * 0.1 + (0 if plus_one else 1)).astype(np.float32)
+    eps = np.float32(1e-5)
+    dW, dx, dw = pack(lib, D, blob, V, H), D.from_numpy(x), D.from_numpy(w)
+    dy, dtok = D(V * 4), D(4)
+    chk(lib, lib.b2_op_norm_gemv(2, dW.ptr, V, H, dx.ptr, dw.ptr, eps, plus_one, None, 3, 0, dy.ptr, None, dtok.ptr))
+    y = dy.to_numpy(np.float32, (V,))
+    tx = torch.from_numpy(x)
+    xn = (tx * (1.0 / torch.sqrt((tx * tx).mean() + eps))) * ((1.0 + torch.from_numpy(w)) if plus_one else torch.from_numpy(w))
+    ref, mag = ref_gemv(blob, xn.numpy())
+    assert np.all(np.abs(y - ref) <= 6e-6 * mag + 1e-30)
+    assert int(dtok.to_numpy(np.int32, (1,))[0]) == int(np.argmax(y))      # arg-max of the kernel's own logits, lowest index
+
+
+@pytest.mark.parametrize("I,H,act_id", [(416, 288, 0), (1024, 512, 1), (14336, 4096, 0)])
+def test_norm_gemv_gate_up_emits_activation_grid(lib, D, I, H, act_id):
+    rng = np.random.default_rng(I + H)
+    g = Q.quantize_q4_0((rng.standard_normal((I, H)) * 0.05).astype(np.float32))
+    u = Q.quantize_q4_0((rng.standard_normal((I, H)) * 0.05).astype(np.float32))
+    x = rng.standard_normal(H).astype(np.float32)
+    w = np.ones(H, dtype=np.float32)
+    dW, dx, dw = pack(lib, D, g, I, H, u), D.from_numpy(x), D.from_numpy(w)
+    dy, dact = D(I * 4), D(lib.b2_act_bytes(I))
+    dact_zero = np.zeros(lib.b2_act_bytes(I), dtype=np.uint8)
+    chk(lib, lib.b2_dev_upload(dact.ptr, dact_zero.ctypes.data, dact_zero.nbytes))
+    chk(lib, lib.b2_op_norm_gemv(2, dW.ptr, 2 * I, H, dx.ptr, dw.ptr, np.float32(1e-6), 0, None, 2, act_id, dy.ptr, dact.ptr, None))
+    h = dy.to_numpy(np.float32, (I,))
+    dig, scale = read_act(lib, dact, I)
+    odig, oe = fxp_digits(h)                      # the emitted image is exactly the grid of the kernel's own h
+    assert np.array_equal(dig, odig)
+    assert np.array_equal(scale, np.ldexp(np.float32(1), oe).astype(np.float32))
+    tx = torch.from_numpy(x)
+    xn = (tx * (1.0 / torch.sqrt((tx * tx).mean() + np.float32(1e-6)))).numpy()
+    gv, _ = ref_gemv(g, xn)
+    uv, _ = ref_gemv(u, xn)
+    gt = torch.from_numpy(gv)
+    a = gt / (1 + torch.exp(-gt)) if act_id == 0 else 0.5 * gt * (1 + torch.tanh(0.7978845608028654 * (gt + 0.044715 * gt ** 3)))
+    assert np.abs(h - a.numpy() * uv).max() <= 2e-5 * np.abs(a.numpy() * uv).max()
 
 
 def rope_tables(hd, theta, n):
