@@ -82,6 +82,7 @@ struct b2_session {
     int *pidx = nullptr;
     int head_grid = 0;
     bool use_pdl = true;
+    bool fused_attn = true;
     float *logits_log = nullptr;
     uint64_t logits_log_cap = 0;   // in floats
     cudaGraphExec_t graphs[G_COUNT] = {};
@@ -408,6 +409,7 @@ extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_te
 }
 
 // ------------------------------------------------------------------------------------ session
+// (these bookkeeping kernels are plain stream-ordered launches: they start after the previous kernel has completed)
 __global__ void k_load_prompt(DevState *st, const int *prompt) {
     st->cur_token = prompt[st->prompt_idx];
     st->prompt_idx += 1;
@@ -441,11 +443,16 @@ static int enqueue_forward(b2_session *s, bool with_head) {
         LayerW &ly = m->layers[l];
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, st, pdl); n++;
-        launch_rope_kv(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
-                       s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, st); n++;
-        launch_attn_decode(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, s->kcache + l * layer_kv, s->vcache + l * layer_kv,
-                           s->page_table, s->attn_out, s->attn_scratch, s->max_ctx, st); n++;
-        launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
+        if (s->fused_attn) {
+            launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
+                              s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, s->max_ctx, st, pdl); n++;
+        } else {
+            launch_rope_kv(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
+                           s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, st); n++;
+            launch_attn_decode(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, s->kcache + l * layer_kv, s->vcache + l * layer_kv,
+                               s->page_table, s->attn_out, s->attn_scratch, s->max_ctx, st); n++;
+            launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
+        }
         launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, nullptr, st, pdl); n++;
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
@@ -527,6 +534,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     s->use_graphs = !(ng && ng[0] == '1');
     const char *np = getenv("B2_NO_PDL");
     s->use_pdl = !(np && np[0] == '1');
+    const char *nf = getenv("B2_NO_FUSED_ATTN");
+    s->fused_attn = !(nf && nf[0] == '1');
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
     uint64_t kv_elems = (uint64_t)c.n_layers * s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     int rc = B2_OK;

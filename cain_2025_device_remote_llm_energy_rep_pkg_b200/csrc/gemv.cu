@@ -101,19 +101,22 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
 }
 
 // ------------------------------------------------------------------------------------------ the kernel
-#define GEMV_SLOTS 4
+#define GEMV_MAX_SLOTS 6
 #define GEMV_THREADS 288
+#define MMA_MAGIC 0x4B400000          // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
+#define MMA_MAGIC_F 12582912.0f
 
 struct GemvArgs {
     const uint8_t *w;        // packed matrix
     int rows, nbp, n_tiles;  // logical rows, padded blocks per row, tiles
     int tile_align;          // tiles are dealt to CTAs in multiples of this (4 for act*mul so A3 blocks stay whole)
+    int n_slots;             // ring depth (chunks of CHUNK_BYTES)
     // input
     const float *x;          // IN_NORM: residual stream, n_in floats
     const float *norm_w;
     float eps;
     int plus_one, n_in;
-    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory
+    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory (staged into shared memory by the producer)
     // output
     float *y;                // fp32 output (OUT_ACTMUL: optional copy of h)
     const float *bias_or_res;
@@ -132,20 +135,24 @@ __device__ __forceinline__ float act_fn(float g, int act) {
     return 0.5f * g * (1.0f + tanhf(0.7978845608028654f * (g + g3)));
 }
 
+// shared memory map (bytes): [ring n_slots*CHUNK_BYTES][red 4096][hbuf 192][barriers 128][A3 of the input nbp*100]
 template <int IN, int OUT>
 __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *ring = smem;                                                      // GEMV_SLOTS * CHUNK_BYTES
-    float *red = (float *)(smem + GEMV_SLOTS * CHUNK_BYTES);                    // [2][8 warps][16 rows][4]
+    uint8_t *ring = smem;
+    float *red = (float *)(smem + (size_t)a.n_slots * CHUNK_BYTES);            // [2][8 warps][16 rows][4]
     float *hbuf = red + 2 * 8 * 16 * 4;                                         // 32 (+ 8 block-reduce scratch)
     uint64_t *full = (uint64_t *)(hbuf + 48);
-    uint64_t *empty = full + GEMV_SLOTS;
-    uint8_t *sact = (uint8_t *)(empty + GEMV_SLOTS);                            // IN_NORM: A3 of the normalised input
+    uint64_t *empty = full + GEMV_MAX_SLOTS;
+    uint64_t *actbar = empty + GEMV_MAX_SLOTS;
+    uint8_t *sact = (uint8_t *)(full + 16);                                     // A3 image of the input vector
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
+    const int S = a.n_slots;
 
     if (tid == 0) {
-        for (int s = 0; s < GEMV_SLOTS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 8); }
+        for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 8); }
+        mbar_init(actbar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         pdl_launch_dependents();
     }
@@ -162,28 +169,39 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
         // ------------------------------------------------------------------ producer
         if (lane == 0) {
             const uint8_t *base = a.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
-            for (int c = 0; c < n_chunks; ++c) {
-                const int s = c % GEMV_SLOTS;
+            auto issue = [&](int c) {
+                const int s = c % S;
                 const int ck = c % cpt, tile = c / cpt;
                 const int cb = min(KC, a.nbp - ck * KC);
-                if (c >= GEMV_SLOTS) mbar_wait(&empty[s], ((c / GEMV_SLOTS) & 1) ^ 1);
+                if (c >= S) mbar_wait(&empty[s], ((c / S) & 1) ^ 1);
                 mbar_expect_tx(&full[s], (uint32_t)cb * BLOCK_BYTES);
                 bulk_g2s(ring + (size_t)s * CHUNK_BYTES, base + ((uint64_t)tile * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES,
                          (uint32_t)cb * BLOCK_BYTES, &full[s]);
+            };
+            // weights are immutable: fill the ring before waiting for the previous kernel
+            const int pre = min(n_chunks, S);
+            for (int c = 0; c < pre; ++c) issue(c);
+            if (IN == IN_ACT) {
+                pdl_wait();   // the activation vector is the previous kernel's output
+                const uint32_t bytes = (uint32_t)a.nbp * 100;
+                mbar_expect_tx(actbar, bytes);
+                bulk_g2s(sact, a.act_in, bytes, actbar);
             }
+            for (int c = pre; c < n_chunks; ++c) issue(c);
         }
         return;
     }
 
     // ---------------------------------------------------------------------- consumers
-    pdl_wait();   // everything below reads what the previous kernel wrote
-    const uint8_t *adig;
-    const float *ascale;
+    // Vectors written by the previous kernel are read with ld.global.cg (L2): under programmatic dependent launch
+    // this CTA may share its SM's L1 with a still-running CTA of that kernel, so L1 must not be trusted for them.
+    float *sscale = (float *)(sact + (size_t)a.nbp * 96);
     float sfold;   // 1/16 of the nibble trick, folded into the activation scale
     if (IN == IN_NORM) {
+        pdl_wait();   // x is the previous kernel's output
         // RMSNorm (oracle/model.py:_norm op order) + activation grid, redundantly per CTA, into shared memory
         float ss = 0.f;
-        for (int i = tid; i < a.n_in; i += 256) { float v = a.x[i]; ss = fmaf(v, v, ss); }
+        for (int i = tid; i < a.n_in; i += 256) { float v = __ldcg(a.x + i); ss = fmaf(v, v, ss); }
         ss = warp_sum(ss);
         if (lane == 0) hbuf[32 + warp] = ss;
         consumer_sync();
@@ -192,31 +210,27 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
         for (int w8 = 0; w8 < 8; ++w8) tot += hbuf[32 + w8];
         const float r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)a.n_in), a.eps)));
         const int nb_in = a.n_in / QK;
-        float *sscale = (float *)(sact + (size_t)a.nbp * 96);
         for (int b = warp; b < a.nbp; b += 8) {
             float yv = 0.f;
             if (b < nb_in) {
                 float wi = a.norm_w[b * QK + lane];
                 if (a.plus_one) wi = __fadd_rn(1.0f, wi);
-                yv = __fmul_rn(__fmul_rn(a.x[b * QK + lane], r), wi);
+                yv = __fmul_rn(__fmul_rn(__ldcg(a.x + b * QK + lane), r), wi);
             }
             float sc;
             int X = act_grid_lane(yv, sc);
             int d0, d1, d2;
             act_digits(X, d0, d1, d2);
-            uint8_t *dst = sact + (size_t)b * 96 + a3_elem_off(lane);
+            uint8_t *dst = sact + a3_off(b, 0, lane);
             dst[0] = (uint8_t)d0;
-            dst[32] = (uint8_t)d1;
-            dst[64] = (uint8_t)d2;
+            dst[128] = (uint8_t)d1;
+            dst[256] = (uint8_t)d2;
             if (lane == 0) sscale[b] = (b < nb_in) ? sc * 0.0625f : 0.f;
         }
         consumer_sync();
-        adig = sact;
-        ascale = sscale;
         sfold = 1.0f;
     } else {
-        adig = a.act_in;
-        ascale = (const float *)(a.act_in + (size_t)a.nbp * 96);
+        mbar_wait(actbar, 0);
         sfold = 0.0625f;
     }
 
@@ -226,29 +240,45 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
     for (int tile = t0; tile < t1; ++tile) {
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
         for (int ck = 0; ck < cpt; ++ck, ++chunk) {
-            const int s = chunk % GEMV_SLOTS;
+            const int s = chunk % S;
             const int cb = min(KC, a.nbp - ck * KC);
-            mbar_wait(&full[s], (chunk / GEMV_SLOTS) & 1);
+            mbar_wait(&full[s], (chunk / S) & 1);
             const uint8_t *slot = ring + (size_t)s * CHUNK_BYTES;
-            const __half2 *scales = (const __half2 *)(slot + (size_t)cb * 256);
+            const uint4 *sc4 = (const uint4 *)(slot + (size_t)cb * 256);
             for (int bg = warp; bg < (cb >> 2); bg += 8) {
-                const uint4 *nbp4 = (const uint4 *)(slot + (size_t)bg * 1024);
-                const uint4 wa = nbp4[lane], wb = nbp4[32 + lane];
+                const int kbg = ck * (KC / 4) + bg;                              // block-group index along K
+                // ---- all loads of this block-group first (6 x LDS.128)
+                const uint4 *nib = (const uint4 *)(slot + (size_t)bg * 1024);
+                const uint4 wa = nib[lane], wb = nib[32 + lane];
+                const uint4 sd = sc4[bg * 8 + g];                                // half2 (row g, row g+8) x 4 blocks
+                const float4 as4 = *(const float4 *)(sscale + kbg * 4);
+                uint4 b01 = make_uint4(0u, 0u, 0u, 0u), b23 = make_uint4(0u, 0u, 0u, 0u);
+                if (g < 3) {
+                    const uint4 *bp = (const uint4 *)(sact + (size_t)kbg * 384 + g * 128 + t * 32);
+                    b01 = bp[0];
+                    b23 = bp[1];
+                }
                 const uint32_t ua[4] = {wa.x, wa.y, wa.z, wa.w}, ub[4] = {wb.x, wb.y, wb.z, wb.w};
+                const uint32_t bx[4] = {b01.x, b01.z, b23.x, b23.z}, by[4] = {b01.y, b01.w, b23.y, b23.w};
+                const uint32_t sdw[4] = {sd.x, sd.y, sd.z, sd.w};
+                const float asf[4] = {as4.x, as4.y, as4.z, as4.w};
+                // ---- four independent MMAs
+                int c[4][4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const int bl = bg * 4 + j, kb = ck * KC + bl;
-                    uint2 bf = make_uint2(0u, 0u);
-                    if (g < 3) bf = *(const uint2 *)(adig + (size_t)kb * 96 + g * 32 + t * 8);
-                    int c[4] = {0, 0, 0, 0};
-                    mma_s8(c, (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bf.x, bf.y);
-                    const float2 dd = __half22float2(scales[bl * 8 + g]);
-                    const float sb = ascale[kb] * sfold;
+                    c[j][0] = c[j][1] = c[j][2] = c[j][3] = MMA_MAGIC;
+                    mma_s8(c[j], (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bx[j], by[j]);
+                }
+                // ---- scale into the fp32 accumulators
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
+                    const float sb = asf[j] * sfold;
                     const float f0 = dd.x * sb, f1 = dd.y * sb;
-                    acc[0] = fmaf((float)c[0], f0, acc[0]);
-                    acc[1] = fmaf((float)c[1], f0, acc[1]);
-                    acc[2] = fmaf((float)c[2], f1, acc[2]);
-                    acc[3] = fmaf((float)c[3], f1, acc[3]);
+                    acc[0] = fmaf(__int_as_float(c[j][0]) - MMA_MAGIC_F, f0, acc[0]);
+                    acc[1] = fmaf(__int_as_float(c[j][1]) - MMA_MAGIC_F, f0, acc[1]);
+                    acc[2] = fmaf(__int_as_float(c[j][2]) - MMA_MAGIC_F, f1, acc[2]);
+                    acc[3] = fmaf(__int_as_float(c[j][3]) - MMA_MAGIC_F, f1, acc[3]);
                 }
             }
             __syncwarp();
@@ -268,16 +298,17 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
             float v0 = 0.f, v1 = 0.f, v2 = 0.f;
 #pragma unroll
             for (int w8 = 0; w8 < 8; ++w8) {
-                v0 += rb[(w8 * 16 + r) * 4 + 0];
-                v1 += rb[(w8 * 16 + r) * 4 + 1];
-                v2 += rb[(w8 * 16 + r) * 4 + 2];
+                const float4 p = *(const float4 *)(rb + (w8 * 16 + r) * 4);
+                v0 += p.x;
+                v1 += p.y;
+                v2 += p.z;
             }
             const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
             const int row = tile * TILE_ROWS + r;
             if (OUT == OUT_BIAS) {
                 if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res ? yv + a.bias_or_res[row] : yv;
             } else if (OUT == OUT_RES) {
-                if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res[row] + yv;
+                if (lane < 16 && row < a.rows) a.y[row] = __ldcg(a.bias_or_res + row) + yv;
             } else if (OUT == OUT_LOGITS) {
                 if (lane < 16 && row < a.rows) {
                     a.y[row] = yv;
@@ -297,14 +328,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
                     float sc;
                     const float hx = (2 * (blk * 32 + lane) < a.rows) ? hbuf[lane] : 0.f;
                     int X = act_grid_lane(hx, sc);
-                    int d0, d1, d2;
-                    act_digits(X, d0, d1, d2);
-                    const int64_t nbo = nblocks_padded(a.n_out_act);
-                    uint8_t *dst = a.act_out + (size_t)blk * 96 + a3_elem_off(lane);
-                    dst[0] = (uint8_t)d0;
-                    dst[32] = (uint8_t)d1;
-                    dst[64] = (uint8_t)d2;
-                    if (lane == 0) ((float *)(a.act_out + (size_t)nbo * 96))[blk] = sc;
+                    a3_store_block(a.act_out, a.n_out_act, blk, lane, X, sc);
                 }
                 __syncwarp();
             }
@@ -333,17 +357,21 @@ int gemv_grid(int n_tiles, int tile_align) {
     int units = (n_tiles + tile_align - 1) / tile_align;
     return units < g_num_sms ? units : g_num_sms;
 }
-size_t gemv_smem_bytes(int in_mode, int nbp_in) {
-    size_t b = (size_t)GEMV_SLOTS * CHUNK_BYTES + 2 * 8 * 16 * 4 * 4 + 48 * 4 + 2 * GEMV_SLOTS * 8;
-    if (in_mode == IN_NORM) b += (size_t)nbp_in * 100;
-    return b + 128;
+#define GEMV_FIXED_SMEM (4096 + 192 + 128)
+// ring depth: as deep as fits next to the activation image while two CTAs still share an SM (113 KB each)
+static int gemv_slots(int nbp_in) {
+    const int budget = 113 * 1024 - GEMV_FIXED_SMEM - nbp_in * 100 - 256;
+    int s = budget / CHUNK_BYTES;
+    if (s > GEMV_MAX_SLOTS) s = GEMV_MAX_SLOTS;
+    if (s < 3) s = 3;   // very long inputs: one CTA per SM
+    return s;
 }
 
 template <int IN, int OUT>
 static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -370,13 +398,14 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     a.nbp = (int)nblocks_padded(cols);
     a.n_tiles = (int)ntiles(rows);
     a.tile_align = out_mode == OUT_ACTMUL ? 4 : 1;
+    a.n_slots = gemv_slots(a.nbp);
     a.x = x; a.norm_w = norm_w; a.eps = eps; a.plus_one = plus_one; a.n_in = (int)cols;
     a.act_in = (const uint8_t *)act_in;
     a.y = y; a.bias_or_res = bias_or_res; a.act_out = (uint8_t *)act_out; a.n_out_act = (int)(rows / 2); a.act = act;
     a.pmax = pmax; a.pidx = pidx;
     int grid = gemv_grid(a.n_tiles, a.tile_align);
     if (grid_out) *grid_out = grid;
-    size_t smem = gemv_smem_bytes(in_mode, a.nbp);
+    size_t smem = (size_t)a.n_slots * CHUNK_BYTES + GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + 128;
 #define CASE(I, O) if (in_mode == I && out_mode == O) return launch_one<I, O>(a, grid, smem, st, pdl)
     CASE(IN_NORM, OUT_BIAS); CASE(IN_NORM, OUT_RES); CASE(IN_NORM, OUT_ACTMUL); CASE(IN_NORM, OUT_LOGITS);
     CASE(IN_ACT, OUT_BIAS); CASE(IN_ACT, OUT_RES); CASE(IN_ACT, OUT_ACTMUL); CASE(IN_ACT, OUT_LOGITS);
@@ -387,7 +416,7 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
 // ------------------------------------------------------------------------------------------ embedding row
 __global__ void k_embed_row(const uint8_t *__restrict__ w, int64_t nbp, int n, const int *__restrict__ token, float scale, float *__restrict__ x) {
     pdl_wait();
-    const int64_t row = *token;
+    const int64_t row = __ldcg(token);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         float v = packed_elem(w, row, i, nbp);
         x[i] = scale != 1.0f ? v * scale : v;

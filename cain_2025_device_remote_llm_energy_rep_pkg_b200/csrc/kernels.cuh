@@ -42,3 +42,7 @@ uint64_t argmax_scratch_bytes();
 void launch_argmax(const float *d_logits, int64_t n, int32_t *d_out, void *d_scratch, cudaStream_t st);
 // final arg-max over the per-CTA partials of the LM-head GEMV, token commit and next-token bookkeeping
 void launch_argmax_partials(const float *pmax, const int *pidx, int n, int32_t *d_out, cudaStream_t st);
+// fused RoPE + KV append + paged attention + activation grid (attn.cu); one cluster of ATTN_NSPLIT CTAs per head
+cudaError_t launch_attn_fused(const float *d_qkv, int nh, int nkv, int hd, const int *d_pos, int pos_imm, const float *d_cos,
+                              const float *d_sin, __half *d_k, __half *d_v, const int32_t *d_page_table, float *d_out, void *d_act_out,
+                              int max_ctx, cudaStream_t st, bool pdl);

@@ -1,8 +1,9 @@
 // layout.cuh — HBM data layouts of the decode path.
 //
-// Activation vector ("A3"), n elements, nbp = blocks of 32 padded up to a multiple of 4:
-//   [0, nbp*96)        int8 digits: block b at b*96, digit plane c (0..2) at +c*32, 8 words in MMA-fragment
-//                      order: word position 2*t+h holds elements h*16+4t .. h*16+4t+3  (t 0..3, h 0..1)
+// Activation vector ("A3"), n elements, nbp = blocks of 32 padded up to a multiple of 4 (nbp/4 block-groups):
+//   [0, nbp*96)        int8 digits: block-group bg at bg*384, digit plane c (0..2) at +c*128, inside a plane
+//                      [t 0..3][j 0..3] 8 bytes = elements 4t..4t+3 then 16+4t..16+4t+3 of block 4*bg+j, so lane
+//                      (g = c, t) of an MMA warp reads the B fragments of four consecutive blocks as 32 contiguous bytes
 //   [nbp*96, nbp*100)  float scale[nbp] = 2^(e-19)  (0 for padding blocks)
 //   X = d2*16384 + d1*128 + d0 (balanced base-128 digits), x_hat = X * scale.
 //
@@ -13,7 +14,7 @@
 //                         word t of blocks 4j..4j+3 of tile row hf*8+g; nibbles stored as two's complement
 //                         of (q-8) (GGML nibble XOR 8), GGML nibble order kept (low nibble = element i,
 //                         high nibble = element i+16 of the block)
-//     scales   cb*32 B  : [block][g] half2 = (d of row g, d of row g+8)
+//     scales   cb*32 B  : [block-group][g][j] half2 = (d of row g, d of row g+8) of block 4*bg+j
 //   One chunk is one contiguous cp.async.bulk; one warp-wide LDS.128 of the nibble area feeds the A fragments
 //   of four mma.m16n8k32 instructions.
 #pragma once
@@ -31,8 +32,10 @@ __host__ __device__ inline uint64_t packed_q4_0_bytes(int64_t rows, int64_t cols
     return (uint64_t)ntiles(rows) * nblocks_padded(cols) * BLOCK_BYTES;
 }
 __host__ __device__ inline uint64_t a3_bytes(int64_t n) { return (uint64_t)nblocks_padded(n) * 100; }
-// byte offset of element e (0..31) inside a 32-byte digit plane
-__host__ __device__ inline int a3_elem_off(int e) { return ((2 * ((e & 15) >> 2) + (e >> 4)) << 2) + (e & 3); }
+// byte offset of (block blk, digit plane c, element e 0..31) inside the digit area
+__host__ __device__ inline int64_t a3_off(int64_t blk, int c, int e) {
+    return (blk >> 2) * 384 + c * 128 + ((((e & 15) >> 2) * 4 + (blk & 3)) << 3) + ((e >> 4) << 2) + (e & 3);
+}
 
 // location of (row, block) inside the packed matrix: returns byte offsets of the 4-byte nibble word t and of the scale
 struct PackedLoc {
@@ -46,7 +49,7 @@ __host__ __device__ inline PackedLoc packed_loc(int64_t row, int64_t blk, int64_
     uint64_t chunk = (uint64_t)T * nbp * BLOCK_BYTES + (uint64_t)ck * KC * BLOCK_BYTES;
     PackedLoc p;
     p.word0 = chunk + (uint64_t)(bl >> 2) * 1024 + (uint64_t)(hf * 8 + g) * 64 + (uint64_t)(bl & 3) * 4;
-    p.scale = chunk + (uint64_t)cb * 256 + (uint64_t)bl * 32 + (uint64_t)g * 4 + (uint64_t)hf * 2;
+    p.scale = chunk + (uint64_t)cb * 256 + (uint64_t)(bl >> 2) * 128 + (uint64_t)g * 16 + (uint64_t)(bl & 3) * 4 + (uint64_t)hf * 2;
     return p;
 }
 
@@ -55,10 +58,10 @@ __host__ __device__ inline PackedLoc packed_loc(int64_t row, int64_t blk, int64_
 __device__ __forceinline__ void a3_store_block(void *act, int64_t n, int64_t blk, int lane, int X, float scale) {
     int d0, d1, d2;
     act_digits(X, d0, d1, d2);
-    uint8_t *dst = (uint8_t *)act + blk * 96 + a3_elem_off(lane);
+    uint8_t *dst = (uint8_t *)act + a3_off(blk, 0, lane);
     dst[0] = (uint8_t)d0;
-    dst[32] = (uint8_t)d1;
-    dst[64] = (uint8_t)d2;
+    dst[128] = (uint8_t)d1;
+    dst[256] = (uint8_t)d2;
     if (lane == 0) ((float *)((uint8_t *)act + nblocks_padded(n) * 96))[blk] = scale;
 }
 #endif

@@ -138,6 +138,18 @@ extern "C" int b2_op_attn_decode(const float *d_q, int nh, int nkv, int hd, int 
     B2_CUDA(e);
     return B2_OK;
 }
+extern "C" int b2_op_attn_fused(const float *d_qkv, int nh, int nkv, int hd, int pos, const float *d_cos, const float *d_sin, void *d_kcache,
+                                void *d_vcache, const int32_t *d_page_table, int page_tokens, int max_ctx, float *d_out, void *d_act_out) {
+    ApiScope _scope("b2_op_attn_fused");
+    B2_CHECK(page_tokens == PAGE_TOKENS, B2_EINVAL, "b2_op_attn_fused: page_tokens must be %d", PAGE_TOKENS);
+    B2_CHECK(d_qkv && d_cos && d_sin && d_kcache && d_vcache && d_page_table && (d_out || d_act_out), B2_EINVAL, "b2_op_attn_fused: NULL pointer");
+    B2_CHECK(pos >= 0 && pos < max_ctx && max_ctx <= 65536, B2_EINVAL, "b2_op_attn_fused: pos %d / max_ctx %d out of range", pos, max_ctx);
+    B2_CHECK(hd % 32 == 0 && hd >= 32 && hd <= 256 && nh > 0 && nkv > 0 && nh % nkv == 0, B2_EINVAL, "b2_op_attn_fused: bad head geometry");
+    B2_CUDA(launch_attn_fused(d_qkv, nh, nkv, hd, nullptr, pos, d_cos, d_sin, (__half *)d_kcache, (__half *)d_vcache, d_page_table, d_out,
+                              d_act_out, max_ctx, 0, false));
+    B2_CUDA(cudaGetLastError());
+    return B2_OK;
+}
 extern "C" int b2_op_argmax(const float *d_logits, int64_t n, int32_t *d_out_index) {
     ApiScope _scope("b2_op_argmax");
     B2_CHECK(d_logits && d_out_index && n > 0 && n < (1ll << 31), B2_EINVAL, "b2_op_argmax: bad arguments");

@@ -169,6 +169,11 @@ int b2_op_rope_kv(float *d_qkv, int nh, int nkv, int hd, int pos, const float *d
 /* softmax(q k^T / sqrt(hd)) v over positions [0,n_ctx) of the paged f16 cache; out f32[nh*hd]. */
 int b2_op_attn_decode(const float *d_q, int nh, int nkv, int hd, int n_ctx, const void *d_kcache, const void *d_vcache,
                       const int32_t *d_page_table, int page_tokens, float *d_out);
+/* The engine's fused form of the two calls above: rotates q and the new k from the UN-rotated QKV output, appends k,v at
+ * `pos`, attends over positions [0,pos], and writes the result as f32 (d_out, may be NULL) and/or on the activation grid
+ * (d_act_out, b2_act_bytes(nh*hd) bytes, may be NULL).  max_ctx sizes the kernel's shared-memory score buffer. */
+int b2_op_attn_fused(const float *d_qkv, int nh, int nkv, int hd, int pos, const float *d_cos, const float *d_sin, void *d_kcache,
+                     void *d_vcache, const int32_t *d_page_table, int page_tokens, int max_ctx, float *d_out, void *d_act_out);
 /* Greedy sampler: index of the maximum (lowest index on ties) of f32[n]. */
 int b2_op_argmax(const float *d_logits, int64_t n, int32_t *d_out_index);
 /* Top-k / temperature / top-p sampler with a caller-supplied uniform u in [0,1). */

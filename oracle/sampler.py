@@ -32,5 +32,5 @@ def sample_topk(logits: np.ndarray, k: int, temperature: float, top_p: float, u:
     hit = run >= target
     j = int(np.argmax(hit)) if hit.any() else keep - 1
     margin = float(np.min(np.abs(run - target)) / mass)
-    cut_margin = float(np.min(np.abs(cum - np.float32(top_p))))
+    cut_margin = float(np.min(np.abs(cum - np.float32(top_p)))) if top_p < 1.0 else float("inf")
     return int(idx[j]), idx[:keep], min(margin, cut_margin)

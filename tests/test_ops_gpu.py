@@ -257,6 +257,47 @@ def test_attn_decode(lib, D, nh, nkv, hd, n_ctx):
     assert np.abs(out - ref).max() <= 2e-5 * max(1.0, np.abs(ref).max())   # fp32, order of summation only
 
 
+@pytest.mark.parametrize("nh,nkv,hd,pos", [(4, 1, 128, 0), (4, 1, 128, 16), (3, 3, 96, 129), (2, 2, 256, 299),
+                                           (32, 8, 128, 2047), (7, 1, 128, 999), (8, 1, 256, 128)])
+def test_attn_fused_matches_unfused_semantics(lib, D, nh, nkv, hd, pos):
+    """RoPE + append + attention + activation grid in one kernel == oracle ops on the same inputs."""
+    rng = np.random.default_rng(nh + hd + pos)
+    max_ctx = 2048
+    n_pages = max_ctx // 16
+    perm = rng.permutation(n_pages).astype(np.int32)
+    kc = rng.standard_normal((n_pages, nkv, 16, hd)).astype(np.float16)
+    vc = rng.standard_normal((n_pages, nkv, 16, hd)).astype(np.float16)
+    qkv = (rng.standard_normal((nh + 2 * nkv) * hd) * 1.5).astype(np.float32)
+    cs, sn = rope_tables(hd, 1e4, max_ctx)
+    dq, dk, dv, dpt, dcs, dsn = (D.from_numpy(x) for x in (qkv, kc, vc, perm, cs, sn))
+    dout, dact = D(nh * hd * 4), D(lib.b2_act_bytes(nh * hd))
+    z = np.zeros(lib.b2_act_bytes(nh * hd), dtype=np.uint8)
+    chk(lib, lib.b2_dev_upload(dact.ptr, z.ctypes.data, z.nbytes))
+    chk(lib, lib.b2_op_attn_fused(dq.ptr, nh, nkv, hd, pos, dcs.ptr, dsn.ptr, dk.ptr, dv.ptr, dpt.ptr, 16, max_ctx, dout.ptr, dact.ptr))
+    out = dout.to_numpy(np.float32, (nh, hd))
+    # oracle: rotate, append (f16), attend
+    t = torch.from_numpy(qkv[: (nh + nkv) * hd]).reshape(nh + nkv, hd)
+    c, s = torch.from_numpy(cs[pos]), torch.from_numpy(sn[pos])
+    t1, t2 = t[:, : hd // 2], t[:, hd // 2:]
+    rot = torch.cat([t1 * c - t2 * s, t2 * c + t1 * s], dim=1)
+    kk, vv = kc.copy(), vc.copy()
+    kk[perm[pos // 16], :, pos % 16] = rot[nh:].numpy().astype(np.float16)
+    vv[perm[pos // 16], :, pos % 16] = qkv[(nh + nkv) * hd:].reshape(nkv, hd).astype(np.float16)
+    assert np.array_equal(dk.to_numpy(np.float16, kc.shape), kk)            # append is bit-exact, nothing else touched
+    assert np.array_equal(dv.to_numpy(np.float16, vc.shape), vv)
+    n_ctx = pos + 1
+    K = torch.from_numpy(kk[perm].transpose(0, 2, 1, 3).reshape(n_pages * 16, nkv, hd)[:n_ctx]).float()
+    V = torch.from_numpy(vv[perm].transpose(0, 2, 1, 3).reshape(n_pages * 16, nkv, hd)[:n_ctx]).float()
+    qg = rot[:nh].reshape(nkv, nh // nkv, hd)
+    sc = torch.einsum("ngd,tnd->ngt", qg, K) * np.float32(1.0 / math.sqrt(hd))
+    ref = torch.einsum("ngt,tnd->ngd", torch.softmax(sc, -1), V).reshape(nh, hd).numpy()
+    assert np.abs(out - ref).max() <= 2e-5 * max(1.0, np.abs(ref).max())
+    dig, scale = read_act(lib, dact, nh * hd)                                # the image is the grid of the kernel's own output
+    odig, oe = fxp_digits(out.reshape(-1))
+    assert np.array_equal(dig, odig)
+    assert np.array_equal(scale, np.ldexp(np.float32(1), oe).astype(np.float32))
+
+
 def test_attn_decode_rejects_bad_geometry(lib, D):
     d = D(4096)
     assert lib.b2_op_attn_decode(d.ptr, 4, 3, 128, 5, d.ptr, d.ptr, d.ptr, 16, d.ptr) == -1

@@ -241,6 +241,21 @@ int main() {
             CK(cudaEventElapsedTime(&ms, e0, e1));
             printf("bulk ring slots=%d chunk=%d touch=%d: %.1f GB/s\n", slots, chunk, touch, per * sms / ms / 1e6);
         };
+        // per-SM streaming ceiling: fewer CTAs, same ring (does an SM go faster when its neighbours are idle?)
+        for (int grid : {16, 37, 74, 111}) {
+            auto kern = k_bw_bulk<12, 16384>;
+            size_t smem = (size_t)12 * 16384 + 12 * 16;
+            CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            size_t per = ((size_t)1 << 30) / grid / 16384 * 16384;
+            for (int rep = 0; rep < 2; ++rep) {
+                CK(cudaEventRecord(e0, st));
+                kern<<<grid, 288, smem, st>>>(buf, per, dout, 1);
+                CK(cudaEventRecord(e1, st));
+                CK(cudaEventSynchronize(e1));
+            }
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            printf("bulk ring 12x16K touch=1 grid=%d: %.1f GB/s total, %.1f GB/s per SM\n", grid, per * grid / ms / 1e6, per / ms / 1e6);
+        }
         runb(k_bw_bulk<4, 16384>, 4, 16384, 0);
         runb(k_bw_bulk<8, 16384>, 8, 16384, 0);
         runb(k_bw_bulk<12, 16384>, 12, 16384, 0);
