@@ -24,11 +24,9 @@ def chk(lib, rc):
     assert rc == 0, lib.b2_last_error().decode()
 
 
-def a3_elem_off(e):
-    return ((2 * ((e & 15) >> 2) + (e >> 4)) << 2) + (e & 3)
-
-
-ELEM_OFF = np.array([a3_elem_off(e) for e in range(32)])
+def a3_off(blk, c, e):
+    """Byte offset of (block, digit plane, element) in the engine's activation image (csrc/layout.cuh)."""
+    return (blk >> 2) * 384 + c * 128 + ((((e & 15) >> 2) * 4 + (blk & 3)) << 3) + ((e >> 4) << 2) + (e & 3)
 
 
 def read_act(lib, buf, n):
@@ -37,11 +35,11 @@ def read_act(lib, buf, n):
     nbp = (nb + 3) // 4 * 4
     assert lib.b2_act_bytes(n) == nbp * 100
     raw = buf.to_numpy(np.uint8, (nbp * 100,))
-    planes = raw[: nbp * 96].view(np.int8).reshape(nbp, 3, 32)
+    blk, c, e = np.meshgrid(np.arange(nbp), np.arange(3), np.arange(32), indexing="ij")
+    planes = raw[: nbp * 96].view(np.int8)[a3_off(blk, c, e)]     # [nbp, 3, 32] in element order
     assert not planes[nb:].any()                                  # padding blocks are zero
-    dig = planes[:nb][:, :, ELEM_OFF]                             # fragment order -> element order
     scale = raw[nbp * 96: nbp * 100].view(np.float32)[:nb]
-    return dig.transpose(1, 0, 2).reshape(3, n), scale
+    return planes[:nb].transpose(1, 0, 2).reshape(3, n), scale
 
 
 def make_act(lib, D, x):
