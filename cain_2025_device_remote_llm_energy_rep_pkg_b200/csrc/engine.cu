@@ -148,7 +148,7 @@ static int check_cfg(const b2_arch_cfg *c) {
     B2_CHECK(c->n_heads > 0 && c->n_kv_heads > 0 && c->n_heads % c->n_kv_heads == 0, B2_EINVAL, "heads %d / kv heads %d", c->n_heads, c->n_kv_heads);
     B2_CHECK(c->n_layers > 0 && c->vocab > 0, B2_EINVAL, "layers %d vocab %d", c->n_layers, c->vocab);
     B2_CHECK(c->max_ctx > 0, B2_EINVAL, "max_ctx %d", c->max_ctx);
-    B2_CHECK(c->hidden <= 16384, B2_EINVAL, "hidden %d too large", c->hidden);
+    B2_CHECK(c->hidden <= 4096, B2_EINVAL, "hidden %d too large (the fused RMSNorm prologue holds at most 4096)", c->hidden);
     return B2_OK;
 }
 
@@ -436,13 +436,16 @@ static int enqueue_forward(b2_session *s, bool with_head) {
     const bool pdl = s->use_pdl;
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
     int n = 0;
+    auto bytes_of = [](const Mat &mt) { return packed_q4_0_bytes(mt.rows, mt.cols); };
     float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
     launch_embed_row(m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, st); n++;
     uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
         LayerW &ly = m->layers[l];
+        // each GEMV hints the matrix the next GEMV will stream (L2 prefetch of the head of every CTA's share)
+        const Mat *after_down = (l + 1 < c.n_layers) ? &m->layers[l + 1].qkv : (with_head ? &m->head : nullptr);
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, st, pdl); n++;
+                    s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), st, pdl); n++;
         if (s->fused_attn) {
             launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
                               s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, s->max_ctx, st, pdl); n++;
@@ -454,15 +457,15 @@ static int enqueue_forward(b2_session *s, bool with_head) {
             launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
         }
         launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
-                    nullptr, nullptr, nullptr, st, pdl); n++;
+                    nullptr, nullptr, nullptr, ly.gateup.packed, bytes_of(ly.gateup), st, pdl); n++;
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    nullptr, nullptr, s->act_h, c.act, nullptr, nullptr, nullptr, st, pdl); n++;
+                    nullptr, nullptr, s->act_h, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), st, pdl); n++;
         launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->act_h, s->x, s->x, nullptr, 0,
-                    nullptr, nullptr, nullptr, st, pdl); n++;
+                    nullptr, nullptr, nullptr, after_down ? after_down->packed : nullptr, after_down ? bytes_of(*after_down) : 0, st, pdl); n++;
     }
     if (with_head) {
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, st, pdl); n++;
+                    s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, m->layers[0].qkv.packed, bytes_of(m->layers[0].qkv), st, pdl); n++;
     }
     return n;
 }

@@ -1,15 +1,17 @@
 // gemv.cu — the streaming Q4_0 GEMV of the decode path (stages a3.3 QKV, a3.6 O, a3.7 gate/up+act*mul,
 // a3.8 down and LM head of Ollama's /api/generate loop; SURVEY.md §3.3, call site experiment/RunnerConfig.py:128-131).
 //
-// One persistent CTA per SM.  Warp 8 lane 0 is the producer: it streams the CTA's contiguous range of
-// weight tiles from HBM into a shared-memory ring with cp.async.bulk (UBLKCP), one 18 KB chunk per copy,
-// completion on an mbarrier.  Weights do not depend on the previous kernel, so the producer starts before
-// griddepcontrol.wait: under programmatic dependent launch the ring fills while the previous kernel drains.
-// Warps 0-7 are consumers: per 32-wide block they rebuild int8 A fragments from the nibbles (two's-complement
-// nibble in the high half of each byte = 16*(q-8): 3 ALU ops per 8 weights), load the activation digits as the
-// B fragment and issue mma.sync.m16n8k32.s8.s8.s32: 16 rows x 32 weights x 3 digit planes of exact integer
-// dot products per instruction.  The int32 results are scaled by d_w * 2^e / 16 into fp32 accumulators; the
-// eight warps split the K dimension and are reduced through shared memory at the end of each 16-row tile.
+// One persistent CTA of 16 warps per SM; the CTA owns a contiguous range of 16-row weight tiles.  A tile is
+// cut along K into chunks of 64 blocks = 16 block-groups; warp w owns block-group w of every chunk, so its
+// weight stream is a sequence of 1 KB (nibbles) + 128 B (scales) pieces that it loads straight into registers
+// with 128-bit streaming loads (ld.global.nc.L1::no_allocate), GEMV_DEPTH pieces in flight.  The first loads are
+// issued before griddepcontrol.wait: weights do not depend on the previous kernel.  The activation digits a
+// warp needs (the B fragments of its block-groups) are held in registers, so the inner loop touches no shared
+// memory.  Per block-group: rebuild int8 A fragments from the nibbles (two's-complement nibble in the high
+// half of each byte = 16*(q-8): 3 ALU ops per 8 weights), four mma.sync.m16n8k32.s8.s8.s32 (16 rows x 32 weights
+// x 3 digit planes of exact integer dot products each), scale by d_w * 2^e / 16 into fp32 accumulators.
+// The sixteen warps split K and meet in shared memory once per tile.  Measured alone (tools/microbench3.cu)
+// this structure streams 6.3-6.8 TB/s from HBM with the arithmetic included.
 #include "kernels.cuh"
 #include "layout.cuh"
 #include "randinit.cuh"
@@ -31,13 +33,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
         "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
 }
+__device__ __forceinline__ bool mbar_test(uint64_t *b, uint32_t parity) {   // non-blocking
+    uint32_t ok;
+    asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                  : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
@@ -101,22 +108,27 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
 }
 
 // ------------------------------------------------------------------------------------------ the kernel
-#define GEMV_MAX_SLOTS 6
-#define GEMV_THREADS 288
-#define MMA_MAGIC 0x4B400000          // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
+#define GEMV_CWARPS 16                       // one block-group of a 64-block chunk each
+#define GEMV_THREADS (GEMV_CWARPS * 32)
+#define GEMV_DEPTH 4                         // weight pieces (1152 B per warp) in flight per warp
+#define GEMV_NORM_MAX 4096                   // longest vector the fused RMSNorm prologue keeps in registers
+#define GEMV_MAXT 2                          // K-outer order: tiles per CTA whose accumulators stay in registers
+#define MMA_MAGIC 0x4B400000                 // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
 #define MMA_MAGIC_F 12582912.0f
+#define L2_PREFETCH_BYTES (128 * 1024)       // of the next kernel's weights, per CTA
+#define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
 
 struct GemvArgs {
     const uint8_t *w;        // packed matrix
     int rows, nbp, n_tiles;  // logical rows, padded blocks per row, tiles
     int tile_align;          // tiles are dealt to CTAs in multiples of this (4 for act*mul so A3 blocks stay whole)
-    int n_slots;             // ring depth (chunks of CHUNK_BYTES)
+    int k_outer;             // 1: loop chunks outermost (long K, <= GEMV_MAXT tiles per CTA); 0: tiles outermost (K <= 2 chunks)
     // input
     const float *x;          // IN_NORM: residual stream, n_in floats
     const float *norm_w;
     float eps;
     int plus_one, n_in;
-    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory (staged into shared memory by the producer)
+    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory
     // output
     float *y;                // fp32 output (OUT_ACTMUL: optional copy of h)
     const float *bias_or_res;
@@ -125,6 +137,8 @@ struct GemvArgs {
     int act;
     float *pmax;             // OUT_LOGITS: per-CTA arg-max partials
     int *pidx;
+    const uint8_t *pf_ptr;   // weights the NEXT kernel will stream: each CTA pulls the head of its share into L2
+    uint64_t pf_total;
 };
 enum { IN_NORM = 0, IN_ACT = 1 };
 enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3 };
@@ -134,175 +148,224 @@ __device__ __forceinline__ float act_fn(float g, int act) {
     float g3 = 0.044715f * g * g * g;
     return 0.5f * g * (1.0f + tanhf(0.7978845608028654f * (g + g3)));
 }
+__device__ __forceinline__ void cta_sync() { __syncthreads(); }
+__device__ __forceinline__ void l2_prefetch(const void *p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint4 ldg_stream4(const void *p) {   // weights: read once, keep out of L1
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint4 ldcg4(const void *p) {         // activations written by the previous kernel: L2
+    uint4 r;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
 
-// shared memory map (bytes): [ring n_slots*CHUNK_BYTES][red 4096][hbuf 192][barriers 128][A3 of the input nbp*100]
+struct WPiece { uint4 wa, wb, sd; };                 // one block-group of weights for this lane: rows g / g+8, 4 blocks, + their scales
+struct BFrag { uint4 b01, b23; float4 as; };         // activation digits (B fragments of 4 blocks) + block scales (already / 16)
+
+__device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&acc)[4]) {
+    const uint32_t ua[4] = {r.wa.x, r.wa.y, r.wa.z, r.wa.w}, ub[4] = {r.wb.x, r.wb.y, r.wb.z, r.wb.w};
+    const uint32_t bx[4] = {b.b01.x, b.b01.z, b.b23.x, b.b23.z}, by[4] = {b.b01.y, b.b01.w, b.b23.y, b.b23.w};
+    const uint32_t sdw[4] = {r.sd.x, r.sd.y, r.sd.z, r.sd.w};
+    const float asf[4] = {b.as.x, b.as.y, b.as.z, b.as.w};
+    int c[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {   // four independent MMAs
+        c[j][0] = c[j][1] = c[j][2] = c[j][3] = MMA_MAGIC;
+        mma_s8(c[j], (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bx[j], by[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {   // scale into the fp32 accumulators
+        const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
+        const float f0 = dd.x * asf[j], f1 = dd.y * asf[j];
+        acc[0] = fmaf(__int_as_float(c[j][0]) - MMA_MAGIC_F, f0, acc[0]);
+        acc[1] = fmaf(__int_as_float(c[j][1]) - MMA_MAGIC_F, f0, acc[1]);
+        acc[2] = fmaf(__int_as_float(c[j][2]) - MMA_MAGIC_F, f1, acc[2]);
+        acc[3] = fmaf(__int_as_float(c[j][3]) - MMA_MAGIC_F, f1, acc[3]);
+    }
+}
+
+// shared memory map (bytes): [red GEMV_RB*16*16*4*4 = 32768][hbuf GEMV_RB*8 floats + 64 scratch = 512][A3 of the input nbp*100]
+#define GEMV_FIXED_SMEM (GEMV_RB * 4096 + 512)
 template <int IN, int OUT>
-__global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
+__global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *ring = smem;
-    float *red = (float *)(smem + (size_t)a.n_slots * CHUNK_BYTES);            // [2][8 warps][16 rows][4]
-    float *hbuf = red + 2 * 8 * 16 * 4;                                         // 32 (+ 8 block-reduce scratch)
-    uint64_t *full = (uint64_t *)(hbuf + 48);
-    uint64_t *empty = full + GEMV_MAX_SLOTS;
-    uint64_t *actbar = empty + GEMV_MAX_SLOTS;
-    uint8_t *sact = (uint8_t *)(full + 16);                                     // A3 image of the input vector
+    float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
+    float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
+    float *scratch = hbuf + GEMV_RB * 8;
+    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
-    const int S = a.n_slots;
-
-    if (tid == 0) {
-        for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 8); }
-        mbar_init(actbar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        pdl_launch_dependents();
-    }
-    __syncthreads();
+    if (tid == 0) pdl_launch_dependents();
 
     // contiguous, aligned share of the tiles
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
     const int u0 = (int)((int64_t)units * blockIdx.x / gridDim.x), u1 = (int)((int64_t)units * (blockIdx.x + 1) / gridDim.x);
     const int t0 = u0 * a.tile_align, t1 = min(a.n_tiles, u1 * a.tile_align);
+    const int nt = t1 - t0;
     const int cpt = (a.nbp + KC - 1) / KC;                                      // chunks per tile
-    const int n_chunks = (t1 - t0) * cpt;
+    const int n_items = nt * cpt;                                               // (tile, chunk) pairs of this CTA
+    const uint8_t *base = a.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
+    const uint64_t tile_bytes = (uint64_t)a.nbp * BLOCK_BYTES;
+    const int k_outer = a.k_outer;
 
-    if (warp == 8) {
-        // ------------------------------------------------------------------ producer
-        if (lane == 0) {
-            const uint8_t *base = a.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
-            auto issue = [&](int c) {
-                const int s = c % S;
-                const int ck = c % cpt, tile = c / cpt;
-                const int cb = min(KC, a.nbp - ck * KC);
-                if (c >= S) mbar_wait(&empty[s], ((c / S) & 1) ^ 1);
-                mbar_expect_tx(&full[s], (uint32_t)cb * BLOCK_BYTES);
-                bulk_g2s(ring + (size_t)s * CHUNK_BYTES, base + ((uint64_t)tile * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES,
-                         (uint32_t)cb * BLOCK_BYTES, &full[s]);
-            };
-            // weights are immutable: fill the ring before waiting for the previous kernel
-            const int pre = min(n_chunks, S);
-            for (int c = 0; c < pre; ++c) issue(c);
-            if (IN == IN_ACT) {
-                pdl_wait();   // the activation vector is the previous kernel's output
-                const uint32_t bytes = (uint32_t)a.nbp * 100;
-                mbar_expect_tx(actbar, bytes);
-                bulk_g2s(sact, a.act_in, bytes, actbar);
+    // Load cursor: walks the (tile, chunk) items of this CTA in processing order without divisions.
+    //   tiles outermost: item i = ti*cpt + ck (the CTA's byte range is one contiguous run of chunks)
+    //   chunks outermost: item i = ck*nt + ti
+    int l_ti = 0, l_ck = 0, l_i = 0;
+    auto load_next = [&](WPiece &r) {
+        if (l_i < n_items) {
+            const int cb = min(KC, a.nbp - l_ck * KC);
+            if (warp < (cb >> 2)) {
+                const uint8_t *ch = base + (uint64_t)l_ti * tile_bytes + (uint64_t)l_ck * (KC * BLOCK_BYTES);
+                r.wa = ldg_stream4(ch + (size_t)warp * 1024 + lane * 16);
+                r.wb = ldg_stream4(ch + (size_t)warp * 1024 + 512 + lane * 16);
+                r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * 128 + g * 16);
             }
-            for (int c = pre; c < n_chunks; ++c) issue(c);
+            ++l_i;
+            if (k_outer) { if (++l_ti == nt) { l_ti = 0; ++l_ck; } }
+            else         { if (++l_ck == cpt) { l_ck = 0; ++l_ti; } }
         }
-        return;
-    }
+    };
+    // ---- the weight stream starts now: it does not depend on the previous kernel
+    WPiece buf[GEMV_DEPTH];
+#pragma unroll
+    for (int d = 0; d < GEMV_DEPTH; ++d) load_next(buf[d]);
 
-    // ---------------------------------------------------------------------- consumers
-    // Vectors written by the previous kernel are read with ld.global.cg (L2): under programmatic dependent launch
-    // this CTA may share its SM's L1 with a still-running CTA of that kernel, so L1 must not be trusted for them.
-    float *sscale = (float *)(sact + (size_t)a.nbp * 96);
-    float sfold;   // 1/16 of the nibble trick, folded into the activation scale
+    // ---- everything below reads what the previous kernel wrote (ld.global.cg: under programmatic dependent launch
+    //      a CTA of that kernel may have shared this SM's L1)
+    pdl_wait();
+    const uint8_t *adig;      // digit planes of the input vector
+    const float *ascale;      // per-block scales
+    float sfold;              // the 1/16 of the nibble trick
     if (IN == IN_NORM) {
-        pdl_wait();   // x is the previous kernel's output
-        // RMSNorm (oracle/model.py:_norm op order) + activation grid, redundantly per CTA, into shared memory
+        // RMSNorm (oracle/model.py:_norm op order) + activation grid, redundantly per CTA, straight into shared memory.
+        // Thread tid owns float4 #(tid + 512*i): every load is issued before the first use; a 32-element block is
+        // 8 consecutive threads of one iteration, so the block maximum is three shuffles.
+        float *sscale = (float *)(sact + (size_t)a.nbp * 96);
+        constexpr int NI = GEMV_NORM_MAX / 4 / GEMV_THREADS;
+        const int n4 = a.n_in >> 2;
+        float4 xv[NI], wv[NI];
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int q = tid + GEMV_THREADS * i;
+            xv[i] = q < n4 ? __ldcg((const float4 *)a.x + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+            wv[i] = q < n4 ? __ldg((const float4 *)a.norm_w + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         float ss = 0.f;
-        for (int i = tid; i < a.n_in; i += 256) { float v = __ldcg(a.x + i); ss = fmaf(v, v, ss); }
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            ss = fmaf(xv[i].x, xv[i].x, ss); ss = fmaf(xv[i].y, xv[i].y, ss);
+            ss = fmaf(xv[i].z, xv[i].z, ss); ss = fmaf(xv[i].w, xv[i].w, ss);
+        }
         ss = warp_sum(ss);
-        if (lane == 0) hbuf[32 + warp] = ss;
-        consumer_sync();
+        if (lane == 0) scratch[warp] = ss;
+        cta_sync();
         float tot = 0.f;
 #pragma unroll
-        for (int w8 = 0; w8 < 8; ++w8) tot += hbuf[32 + w8];
+        for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
         const float r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)a.n_in), a.eps)));
-        const int nb_in = a.n_in / QK;
-        for (int b = warp; b < a.nbp; b += 8) {
-            float yv = 0.f;
-            if (b < nb_in) {
-                float wi = a.norm_w[b * QK + lane];
-                if (a.plus_one) wi = __fadd_rn(1.0f, wi);
-                yv = __fmul_rn(__fmul_rn(__ldcg(a.x + b * QK + lane), r), wi);
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int q = tid + GEMV_THREADS * i;            // float4 index; block = q / 8, word-in-block = q % 8
+            float yv[4];
+            const float xs[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w}, ws[4] = {wv[i].x, wv[i].y, wv[i].z, wv[i].w};
+            float m = 0.f;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float wi = a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e];
+                yv[e] = __fmul_rn(__fmul_rn(xs[e], r), wi);
+                m = fmaxf(m, fabsf(yv[e]));
             }
-            float sc;
-            int X = act_grid_lane(yv, sc);
-            int d0, d1, d2;
-            act_digits(X, d0, d1, d2);
-            uint8_t *dst = sact + a3_off(b, 0, lane);
-            dst[0] = (uint8_t)d0;
-            dst[128] = (uint8_t)d1;
-            dst[256] = (uint8_t)d2;
-            if (lane == 0) sscale[b] = (b < nb_in) ? sc * 0.0625f : 0.f;
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+            if (q < (a.nbp << 3)) {
+                int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
+                const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
+                const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
+                uint32_t w0 = 0, w1 = 0, w2 = 0;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    int d0, d1, d2;
+                    act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
+                    w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
+                    w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
+                    w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
+                }
+                const int b = q >> 3, k = q & 7;                // elements 4k..4k+3 of block b
+                uint8_t *dst = sact + a3_off(b, 0, 4 * k);
+                *(uint32_t *)dst = w0;
+                *(uint32_t *)(dst + 128) = w1;
+                *(uint32_t *)(dst + 256) = w2;
+                if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
+            }
         }
-        consumer_sync();
-        sfold = 1.0f;
+        cta_sync();
+        adig = sact;
+        ascale = sscale;
     } else {
-        mbar_wait(actbar, 0);
-        sfold = 0.0625f;
+        // the activation image (digits + scales, nbp*100 bytes) is copied once into shared memory
+        const int n16 = (a.nbp * 100) >> 4;
+        for (int i = tid; i < n16; i += GEMV_THREADS) ((uint4 *)sact)[i] = ldcg4(a.act_in + (size_t)i * 16);
+        cta_sync();
+        adig = sact;
+        ascale = (const float *)(sact + (size_t)a.nbp * 96);
     }
+    sfold = 0.0625f;
+    // B fragments of block-group column `warp` of chunk ck (register resident; shared memory or L2 is read once per use below)
+    auto load_b = [&](int ck, BFrag &b) {
+        const int kbg = ck * (KC / 4) + warp;
+        b.b01 = make_uint4(0u, 0u, 0u, 0u);
+        b.b23 = make_uint4(0u, 0u, 0u, 0u);
+        b.as = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (kbg * 4 < a.nbp) {
+            if (g < 3) {
+                const uint4 *bp = (const uint4 *)(adig + (size_t)kbg * 384 + g * 128 + t * 32);
+                b.b01 = bp[0];
+                b.b23 = bp[1];
+            }
+            b.as = *(const float4 *)(ascale + kbg * 4);
+            b.as.x *= sfold; b.as.y *= sfold; b.as.z *= sfold; b.as.w *= sfold;
+        }
+    };
 
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
-    int chunk = 0;
-    for (int tile = t0; tile < t1; ++tile) {
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int ck = 0; ck < cpt; ++ck, ++chunk) {
-            const int s = chunk % S;
-            const int cb = min(KC, a.nbp - ck * KC);
-            mbar_wait(&full[s], (chunk / S) & 1);
-            const uint8_t *slot = ring + (size_t)s * CHUNK_BYTES;
-            const uint4 *sc4 = (const uint4 *)(slot + (size_t)cb * 256);
-            for (int bg = warp; bg < (cb >> 2); bg += 8) {
-                const int kbg = ck * (KC / 4) + bg;                              // block-group index along K
-                // ---- all loads of this block-group first (6 x LDS.128)
-                const uint4 *nib = (const uint4 *)(slot + (size_t)bg * 1024);
-                const uint4 wa = nib[lane], wb = nib[32 + lane];
-                const uint4 sd = sc4[bg * 8 + g];                                // half2 (row g, row g+8) x 4 blocks
-                const float4 as4 = *(const float4 *)(sscale + kbg * 4);
-                uint4 b01 = make_uint4(0u, 0u, 0u, 0u), b23 = make_uint4(0u, 0u, 0u, 0u);
-                if (g < 3) {
-                    const uint4 *bp = (const uint4 *)(sact + (size_t)kbg * 384 + g * 128 + t * 32);
-                    b01 = bp[0];
-                    b23 = bp[1];
-                }
-                const uint32_t ua[4] = {wa.x, wa.y, wa.z, wa.w}, ub[4] = {wb.x, wb.y, wb.z, wb.w};
-                const uint32_t bx[4] = {b01.x, b01.z, b23.x, b23.z}, by[4] = {b01.y, b01.w, b23.y, b23.w};
-                const uint32_t sdw[4] = {sd.x, sd.y, sd.z, sd.w};
-                const float asf[4] = {as4.x, as4.y, as4.z, as4.w};
-                // ---- four independent MMAs
-                int c[4][4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    c[j][0] = c[j][1] = c[j][2] = c[j][3] = MMA_MAGIC;
-                    mma_s8(c[j], (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bx[j], by[j]);
-                }
-                // ---- scale into the fp32 accumulators
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
-                    const float sb = asf[j] * sfold;
-                    const float f0 = dd.x * sb, f1 = dd.y * sb;
-                    acc[0] = fmaf(__int_as_float(c[j][0]) - MMA_MAGIC_F, f0, acc[0]);
-                    acc[1] = fmaf(__int_as_float(c[j][1]) - MMA_MAGIC_F, f0, acc[1]);
-                    acc[2] = fmaf(__int_as_float(c[j][2]) - MMA_MAGIC_F, f1, acc[2]);
-                    acc[3] = fmaf(__int_as_float(c[j][3]) - MMA_MAGIC_F, f1, acc[3]);
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
-        }
-        // ---- cross-warp reduction of the tile (double-buffered scratch: one barrier per tile)
-        float *rb = red + (size_t)(tile & 1) * (8 * 16 * 4);
+    // Finished tiles are parked in shared memory (every warp its K-partial of the 16 rows x 3 digit planes) and reduced
+    // GEMV_RB tiles at a time: two CTA-wide barriers per batch instead of one per tile, so the weight stream of the sixteen
+    // warps is not re-synchronised on memory latency every other piece.
+    int batch_first = t0, batch_n = 0;
+    auto park_tile = [&](const float (&acc)[4]) {
+        float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
         if (t < 2) {
-            rb[(warp * 16 + g) * 4 + 2 * t] = acc[0];
-            rb[(warp * 16 + g) * 4 + 2 * t + 1] = acc[1];
-            rb[(warp * 16 + g + 8) * 4 + 2 * t] = acc[2];
-            rb[(warp * 16 + g + 8) * 4 + 2 * t + 1] = acc[3];
+            *(float2 *)(rb + (warp * 16 + g) * 4 + 2 * t) = make_float2(acc[0], acc[1]);
+            *(float2 *)(rb + (warp * 16 + g + 8) * 4 + 2 * t) = make_float2(acc[2], acc[3]);
         }
-        consumer_sync();
-        if (warp == 0) {
-            const int r = lane & 15;
+        ++batch_n;
+    };
+    auto flush_batch = [&]() {
+        cta_sync();
+        if (warp < batch_n) {
+            // warp w finalises tile batch_first + w.  lane = (half, row): each lane adds 8 of the 16 warp partials of its
+            // row in a fixed order, the halves meet by shuffle.
+            const int tile = batch_first + warp;
+            const float *rb = red + (size_t)warp * (GEMV_CWARPS * 16 * 4);
+            const int r = lane & 15, hf = lane >> 4;
             float v0 = 0.f, v1 = 0.f, v2 = 0.f;
 #pragma unroll
-            for (int w8 = 0; w8 < 8; ++w8) {
-                const float4 p = *(const float4 *)(rb + (w8 * 16 + r) * 4);
-                v0 += p.x;
-                v1 += p.y;
-                v2 += p.z;
+            for (int w8 = 0; w8 < GEMV_CWARPS / 2; ++w8) {
+                const float4 p4 = *(const float4 *)(rb + ((hf * (GEMV_CWARPS / 2) + w8) * 16 + r) * 4);
+                v0 += p4.x;
+                v1 += p4.y;
+                v2 += p4.z;
             }
+            v0 += __shfl_xor_sync(0xffffffffu, v0, 16);
+            v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
+            v2 += __shfl_xor_sync(0xffffffffu, v2, 16);
             const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
             const int row = tile * TILE_ROWS + r;
             if (OUT == OUT_BIAS) {
@@ -319,29 +382,138 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) k_gemv(const GemvArgs a) {
                 const float hv = act_fn(yv, a.act) * up;
                 const int pair = tile * 8 + (r >> 1);
                 if (lane < 16 && !(r & 1)) {
-                    hbuf[(tile & 3) * 8 + (r >> 1)] = hv;
+                    hbuf[warp * 8 + (r >> 1)] = hv;
                     if (a.y && 2 * pair < a.rows) a.y[pair] = hv;
                 }
-                __syncwarp();
-                if ((tile & 3) == 3) {   // 32 consecutive h values are complete: put them on the activation grid
-                    const int blk = tile >> 2;
-                    float sc;
-                    const float hx = (2 * (blk * 32 + lane) < a.rows) ? hbuf[lane] : 0.f;
-                    int X = act_grid_lane(hx, sc);
-                    a3_store_block(a.act_out, a.n_out_act, blk, lane, X, sc);
-                }
-                __syncwarp();
             }
         }
+        cta_sync();   // the parked partials may be overwritten from here on; hbuf is complete
+        if (OUT == OUT_ACTMUL && warp < (batch_n >> 2)) {
+            // 32 consecutive h values (4 tiles) -> one block on the activation grid.  batch_first is a multiple of 4.
+            const int blk = (batch_first >> 2) + warp;
+            float sc;
+            const float hx = (2 * (blk * 32 + lane) < a.rows) ? hbuf[warp * 32 + lane] : 0.f;
+            int X = act_grid_lane(hx, sc);
+            a3_store_block(a.act_out, a.n_out_act, blk, lane, X, sc);
+        }
+        batch_first += batch_n;
+        batch_n = 0;
+    };
+    auto finish_tile = [&](const float (&acc)[4]) {
+        park_tile(acc);
+        if (batch_n == GEMV_RB) flush_batch();
+    };
+    // when the CTA's last piece has been requested, pull the head of the next kernel's weights into L2
+    auto prefetch_next = [&]() {
+        if (tid == 0 && a.pf_ptr) {
+            const uint64_t share = (a.pf_total / gridDim.x) & ~(uint64_t)127;
+            const uint8_t *p0 = a.pf_ptr + share * blockIdx.x;
+            const uint64_t n = share < L2_PREFETCH_BYTES ? share : L2_PREFETCH_BYTES;
+            for (uint64_t o = 0; o + 16384 <= n; o += 16384) l2_prefetch(p0 + o, 16384);
+        }
+    };
+    bool pf_done = false;
+    const int cb_last = a.nbp - (cpt - 1) * KC;                  // blocks in the last chunk of a tile
+    const bool act_full = warp < (KC >> 2) && cpt > 1;           // this warp has work in a full chunk / in the last chunk
+    const bool act_last = warp < (cb_last >> 2);
+
+    if (!k_outer) {
+        // ---- tiles outermost; K spans at most two chunks, whose B fragments stay in registers for the whole kernel.
+        //      GEMV_DEPTH is even, so the chunk index of slot d is d & 1 when cpt == 2: no per-item index arithmetic.
+        BFrag bf0, bf1;
+        load_b(0, bf0);
+        load_b(1, bf1);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        if (cpt == 2) {
+            for (int i0 = 0; i0 < n_items; i0 += GEMV_DEPTH) {
+#pragma unroll
+                for (int d = 0; d < GEMV_DEPTH; ++d) {
+                    if (i0 + d < n_items) {
+                        if (d & 1) { if (act_last) bg_mma(buf[d], bf1, acc); }
+                        else       { if (act_full) bg_mma(buf[d], bf0, acc); }
+                        load_next(buf[d]);
+                        if (d & 1) {
+                            finish_tile(acc);
+                            acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+                        }
+                    }
+                }
+                if (!pf_done && l_i >= n_items) { prefetch_next(); pf_done = true; }
+            }
+        } else {
+            for (int i0 = 0; i0 < n_items; i0 += GEMV_DEPTH) {
+#pragma unroll
+                for (int d = 0; d < GEMV_DEPTH; ++d) {
+                    if (i0 + d < n_items) {
+                        if (act_last) bg_mma(buf[d], bf0, acc);
+                        load_next(buf[d]);
+                        finish_tile(acc);
+                        acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+                    }
+                }
+                if (!pf_done && l_i >= n_items) { prefetch_next(); pf_done = true; }
+            }
+        }
+    } else {
+        // ---- chunks outermost (long K, at most GEMV_MAXT tiles per CTA): the B fragments of one chunk at a time,
+        //      the accumulators of every tile of the CTA in registers
+        float accs[GEMV_MAXT][4];
+#pragma unroll
+        for (int q = 0; q < GEMV_MAXT; ++q) accs[q][0] = accs[q][1] = accs[q][2] = accs[q][3] = 0.f;
+        BFrag bcur, bnxt;
+        load_b(0, bcur);
+        if (cpt > 1) load_b(1, bnxt);
+        int ti = 0, ck = 0;
+        for (int i0 = 0; i0 < n_items; i0 += GEMV_DEPTH) {
+#pragma unroll
+            for (int d = 0; d < GEMV_DEPTH; ++d) {
+                if (i0 + d < n_items) {
+                    const bool active = (ck == cpt - 1) ? act_last : act_full;
+                    if (active) {
+#pragma unroll
+                        for (int q = 0; q < GEMV_MAXT; ++q)
+                            if (q == ti) bg_mma(buf[d], bcur, accs[q]);
+                    }
+                    load_next(buf[d]);
+                    if (++ti == nt) {   // chunk finished: rotate the B fragments, fetch the one after next
+                        ti = 0;
+                        ++ck;
+                        bcur = bnxt;
+                        if (ck + 1 < cpt) load_b(ck + 1, bnxt);
+                    }
+                }
+            }
+            if (!pf_done && l_i >= n_items) { prefetch_next(); pf_done = true; }
+        }
+#pragma unroll
+        for (int q = 0; q < GEMV_MAXT; ++q)
+            if (q < nt) finish_tile(accs[q]);
     }
-    if (OUT == OUT_LOGITS && warp == 0) {
+    if (batch_n > 0) flush_batch();
+    if (!pf_done) prefetch_next();
+    if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima
+        float *sv = scratch;
+        int *si = (int *)(scratch + 16);
+        cta_sync();
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) {
             float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
             int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
             if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
         }
-        if (lane == 0) { a.pmax[blockIdx.x] = best_v; a.pidx[blockIdx.x] = best_i; }
+        if (lane == 0) { sv[warp] = best_v; si[warp] = best_i; }
+        cta_sync();
+        if (warp == 0) {
+            best_v = lane < GEMV_CWARPS ? sv[lane] : -INFINITY;
+            best_i = lane < GEMV_CWARPS ? si[lane] : 0x7fffffff;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+                int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+                if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
+            }
+            if (lane == 0) { a.pmax[blockIdx.x] = best_v; a.pidx[blockIdx.x] = best_i; }
+        }
     }
 }
 
@@ -357,21 +529,12 @@ int gemv_grid(int n_tiles, int tile_align) {
     int units = (n_tiles + tile_align - 1) / tile_align;
     return units < g_num_sms ? units : g_num_sms;
 }
-#define GEMV_FIXED_SMEM (4096 + 192 + 128)
-// ring depth: as deep as fits next to the activation image while two CTAs still share an SM (113 KB each)
-static int gemv_slots(int nbp_in) {
-    const int budget = 113 * 1024 - GEMV_FIXED_SMEM - nbp_in * 100 - 256;
-    int s = budget / CHUNK_BYTES;
-    if (s > GEMV_MAX_SLOTS) s = GEMV_MAX_SLOTS;
-    if (s < 3) s = 3;   // very long inputs: one CTA per SM
-    return s;
-}
 
 template <int IN, int OUT>
 static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -389,28 +552,58 @@ static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStre
 }
 
 // in_mode IN_NORM: (x, norm_w, eps, plus_one) ; IN_ACT: act_in.  out_mode selects the epilogue.
+// next_w / next_bytes: the packed matrix the following kernel streams (L2 prefetch hint), or nullptr.
 cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                         float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
-                        float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl) {
+                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, cudaStream_t st, bool pdl) {
     GemvArgs a = {};
     a.w = (const uint8_t *)d_packed;
     a.rows = (int)rows;
     a.nbp = (int)nblocks_padded(cols);
     a.n_tiles = (int)ntiles(rows);
     a.tile_align = out_mode == OUT_ACTMUL ? 4 : 1;
-    a.n_slots = gemv_slots(a.nbp);
+    if (in_mode == IN_NORM && cols > GEMV_NORM_MAX) return cudaErrorInvalidValue;
     a.x = x; a.norm_w = norm_w; a.eps = eps; a.plus_one = plus_one; a.n_in = (int)cols;
     a.act_in = (const uint8_t *)act_in;
     a.y = y; a.bias_or_res = bias_or_res; a.act_out = (uint8_t *)act_out; a.n_out_act = (int)(rows / 2); a.act = act;
     a.pmax = pmax; a.pidx = pidx;
+    a.pf_ptr = (const uint8_t *)next_w; a.pf_total = next_bytes;
     int grid = gemv_grid(a.n_tiles, a.tile_align);
+    const int cpt = (a.nbp + KC - 1) / KC;
+    const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
+    int max_tiles = ((units + grid - 1) / grid) * a.tile_align;
+    a.k_outer = cpt > 2;
     if (grid_out) *grid_out = grid;
-    size_t smem = (size_t)a.n_slots * CHUNK_BYTES + GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + 128;
-#define CASE(I, O) if (in_mode == I && out_mode == O) return launch_one<I, O>(a, grid, smem, st, pdl)
-    CASE(IN_NORM, OUT_BIAS); CASE(IN_NORM, OUT_RES); CASE(IN_NORM, OUT_ACTMUL); CASE(IN_NORM, OUT_LOGITS);
-    CASE(IN_ACT, OUT_BIAS); CASE(IN_ACT, OUT_RES); CASE(IN_ACT, OUT_ACTMUL); CASE(IN_ACT, OUT_LOGITS);
+    size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + 128;
+#define CASE(I, O) if (in_mode == I && out_mode == O) return launch_one<I, O>(aa, grid, smem, st, pdl)
+    if (!a.k_outer || max_tiles <= GEMV_MAXT) {
+        const GemvArgs &aa = a;
+        CASE(IN_NORM, OUT_BIAS); CASE(IN_NORM, OUT_RES); CASE(IN_NORM, OUT_ACTMUL); CASE(IN_NORM, OUT_LOGITS);
+        CASE(IN_ACT, OUT_BIAS); CASE(IN_ACT, OUT_RES); CASE(IN_ACT, OUT_ACTMUL); CASE(IN_ACT, OUT_LOGITS);
+        return cudaErrorInvalidValue;
+    }
+    // long K and many rows (no matrix of the seven models; kept for generality): the accumulators of a CTA's tiles live in
+    // registers, so cover the rows with several launches of at most GEMV_MAXT tiles per CTA
+    if (out_mode == OUT_LOGITS || out_mode == OUT_ACTMUL) return cudaErrorInvalidValue;
+    const int per_launch = g_num_sms * GEMV_MAXT;
+    for (int tbeg = 0; tbeg < a.n_tiles; tbeg += per_launch) {
+        GemvArgs aa = a;
+        const int tn = a.n_tiles - tbeg < per_launch ? a.n_tiles - tbeg : per_launch;
+        aa.w = a.w + (uint64_t)tbeg * a.nbp * BLOCK_BYTES;
+        aa.n_tiles = tn;
+        aa.rows = (int)(rows - (int64_t)tbeg * TILE_ROWS < (int64_t)tn * TILE_ROWS ? rows - (int64_t)tbeg * TILE_ROWS : (int64_t)tn * TILE_ROWS);
+        aa.y = y + (int64_t)tbeg * TILE_ROWS;
+        aa.bias_or_res = bias_or_res ? bias_or_res + (int64_t)tbeg * TILE_ROWS : nullptr;
+        grid = gemv_grid(tn, 1);
+        cudaError_t e = cudaErrorInvalidValue;
+        if (in_mode == IN_NORM && out_mode == OUT_BIAS) e = launch_one<IN_NORM, OUT_BIAS>(aa, grid, smem, st, pdl);
+        if (in_mode == IN_NORM && out_mode == OUT_RES) e = launch_one<IN_NORM, OUT_RES>(aa, grid, smem, st, pdl);
+        if (in_mode == IN_ACT && out_mode == OUT_BIAS) e = launch_one<IN_ACT, OUT_BIAS>(aa, grid, smem, st, pdl);
+        if (in_mode == IN_ACT && out_mode == OUT_RES) e = launch_one<IN_ACT, OUT_RES>(aa, grid, smem, st, pdl);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 #undef CASE
-    return cudaErrorInvalidValue;
 }
 
 // ------------------------------------------------------------------------------------------ embedding row

@@ -25,7 +25,7 @@ enum { GEMV_OUT_BIAS = 0, GEMV_OUT_RES = 1, GEMV_OUT_ACTMUL = 2, GEMV_OUT_LOGITS
 int gemv_grid(int n_tiles, int tile_align);
 cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                         float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
-                        float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl);
+                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, cudaStream_t st, bool pdl);
 void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st);
 
 // small stages (kernels.cu)

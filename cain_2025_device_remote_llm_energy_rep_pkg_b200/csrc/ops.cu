@@ -69,7 +69,7 @@ extern "C" int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t 
         B2_CUDA(cudaMemset(act_out, 0, a3_bytes(rows / 2)));
     }
     cudaError_t e = launch_gemv(GEMV_IN_ACT, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_act, d_y, d_bias_or_res, act_out, act,
-                                nullptr, nullptr, nullptr, 0, false);
+                                nullptr, nullptr, nullptr, nullptr, 0, 0, false);
     if (e == cudaSuccess && act_out) e = cudaDeviceSynchronize();
     if (act_out) cudaFree(act_out);
     B2_CUDA(e);
@@ -83,7 +83,7 @@ extern "C" int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int
                                int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y, void *d_act_out, int32_t *d_argmax) {
     ApiScope _scope("b2_op_norm_gemv");
     B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_op_norm_gemv: type %d not supported", type);
-    B2_CHECK(d_packed && d_x && d_norm_w && rows > 0 && cols > 0 && cols % QK == 0 && cols <= 16384, B2_EINVAL, "b2_op_norm_gemv: bad arguments");
+    B2_CHECK(d_packed && d_x && d_norm_w && rows > 0 && cols > 0 && cols % QK == 0 && cols <= 4096, B2_EINVAL, "b2_op_norm_gemv: bad arguments (cols must be a multiple of 32, at most 4096)");
     B2_CHECK(mode >= 0 && mode <= 3, B2_EINVAL, "b2_op_norm_gemv: mode %d", mode);
     B2_CHECK(mode == 2 || d_y, B2_EINVAL, "b2_op_norm_gemv: d_y is NULL");
     B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_norm_gemv: mode 1 needs the residual vector");
@@ -101,7 +101,7 @@ extern "C" int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int
     }
     int grid = 0;
     cudaError_t e = launch_gemv(GEMV_IN_NORM, mode, d_packed, rows, cols, d_x, d_norm_w, eps, plus_one, nullptr, d_y, d_bias_or_res, act_out, act,
-                                pmax, pidx, &grid, 0, false);
+                                pmax, pidx, &grid, nullptr, 0, 0, false);
     if (e == cudaSuccess && mode == 3) launch_argmax_partials(pmax, pidx, grid, d_argmax, 0);
     if (e == cudaSuccess && tmp) e = cudaDeviceSynchronize();
     if (tmp) cudaFree(tmp);

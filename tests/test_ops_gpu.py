@@ -110,7 +110,7 @@ def ref_gemv(blob, x):
     return W @ xq, np.abs(W) @ np.abs(xq)
 
 
-@pytest.mark.parametrize("rows,cols", [(1, 32), (7, 288), (64, 4096), (33, 1184), (16, 14336), (257, 1536), (4096, 4096), (6000, 2080)])
+@pytest.mark.parametrize("rows,cols", [(1, 32), (7, 288), (64, 4096), (33, 1184), (16, 14336), (257, 1536), (4096, 4096), (6000, 2080), (9600, 8192)])
 def test_gemv_modes(lib, D, rows, cols):
     rng = np.random.default_rng(rows * 131 + cols)
     Wf = (rng.standard_normal((rows, cols)) * 0.02).astype(np.float32)

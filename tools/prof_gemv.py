@@ -29,8 +29,24 @@ h = DevBuf.from_numpy(rng.standard_normal(I).astype(np.float32))
 act_h = DevBuf(lib.b2_act_bytes(I))
 chk(lib.b2_op_quant_act(h.ptr, I, act_h.ptr))
 y, hh, act_o = DevBuf(H * 4), DevBuf(I * 4), DevBuf(lib.b2_act_bytes(I))
+dbg = DevBuf(148 * 8 * 8)
+prof = False
+
+
+def report(name):
+    if not prof:
+        return
+    chk(lib.b2_dev_sync())
+    d = dbg.to_numpy(np.int64, (148, 8))
+    print(f"{name}: cycles per CTA (warp 1) median total {np.median(d[:,0]):.0f} prologue {np.median(d[:,1]):.0f} wait_full {np.median(d[:,2]):.0f} "
+          f"compute {np.median(d[:,3]):.0f} reduce {np.median(d[:,4]):.0f} | producer wait_empty {np.median(d[:,5]):.0f} chunks {np.median(d[:,6]):.0f} "
+          f"| max total {d[:,0].max()} min {d[:,0].min()}")
+
+
 for _ in range(reps):
     chk(lib.b2_op_gemv(2, w_down.ptr, H, I, act_h.ptr, x.ptr, 1, 0, y.ptr))
+    report("down 4096x14336 (IN_ACT, RES)")
     chk(lib.b2_op_norm_gemv(2, w_gu.ptr, 2 * I, H, x.ptr, nw.ptr, np.float32(1e-5), 0, None, 2, 0, hh.ptr, act_o.ptr, None))
+    report("gate/up 28672x4096 (IN_NORM, ACTMUL)")
 chk(lib.b2_dev_sync())
 print("ok", float(np.abs(y.to_numpy(np.float32, (H,))).max()))
