@@ -148,7 +148,7 @@ static int check_cfg(const b2_arch_cfg *c) {
     B2_CHECK(c->n_heads > 0 && c->n_kv_heads > 0 && c->n_heads % c->n_kv_heads == 0, B2_EINVAL, "heads %d / kv heads %d", c->n_heads, c->n_kv_heads);
     B2_CHECK(c->n_layers > 0 && c->vocab > 0, B2_EINVAL, "layers %d vocab %d", c->n_layers, c->vocab);
     B2_CHECK(c->max_ctx > 0, B2_EINVAL, "max_ctx %d", c->max_ctx);
-    B2_CHECK(c->hidden <= 4096, B2_EINVAL, "hidden %d too large (the fused RMSNorm prologue holds at most 4096)", c->hidden);
+    B2_CHECK(c->hidden <= 8192, B2_EINVAL, "hidden %d too large (the fused RMSNorm prologue stages at most 8192)", c->hidden);
     return B2_OK;
 }
 
@@ -459,8 +459,8 @@ static int enqueue_forward(b2_session *s, bool with_head) {
         launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, nullptr, ly.gateup.packed, bytes_of(ly.gateup), st, pdl); n++;
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    nullptr, nullptr, s->act_h, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), st, pdl); n++;
-        launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->act_h, s->x, s->x, nullptr, 0,
+                    s->h, nullptr, nullptr, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), st, pdl); n++;
+        launch_gemv(GEMV_IN_F32, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->h, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, nullptr, after_down ? after_down->packed : nullptr, after_down ? bytes_of(*after_down) : 0, st, pdl); n++;
     }
     if (with_head) {

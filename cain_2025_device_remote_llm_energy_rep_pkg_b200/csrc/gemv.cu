@@ -111,11 +111,12 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
 #define GEMV_CWARPS 16                       // one block-group of a 64-block chunk each
 #define GEMV_THREADS (GEMV_CWARPS * 32)
 #define GEMV_DEPTH 4                         // weight pieces (1152 B per warp) in flight per warp
-#define GEMV_NORM_MAX 4096                   // longest vector the fused RMSNorm prologue keeps in registers
+#define GEMV_NORM_MAX 8192                   // longest vector the fused RMSNorm prologue keeps in registers
 #define GEMV_MAXT 2                          // K-outer order: tiles per CTA whose accumulators stay in registers
 #define MMA_MAGIC 0x4B400000                 // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
 #define MMA_MAGIC_F 12582912.0f
 #define L2_PREFETCH_BYTES (128 * 1024)       // of the next kernel's weights, per CTA
+#define L2_WINDOW_BYTES (256 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
 #define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
 
 struct GemvArgs {
@@ -128,7 +129,7 @@ struct GemvArgs {
     const float *norm_w;
     float eps;
     int plus_one, n_in;
-    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory
+    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory; IN_F32: fp32 vector of n_in elements (put on the grid here)
     // output
     float *y;                // fp32 output (OUT_ACTMUL: optional copy of h)
     const float *bias_or_res;
@@ -139,8 +140,9 @@ struct GemvArgs {
     int *pidx;
     const uint8_t *pf_ptr;   // weights the NEXT kernel will stream: each CTA pulls the head of its share into L2
     uint64_t pf_total;
+    long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
 };
-enum { IN_NORM = 0, IN_ACT = 1 };
+enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2 };
 enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3 };
 
 __device__ __forceinline__ float act_fn(float g, int act) {
@@ -187,19 +189,178 @@ __device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&
         acc[3] = fmaf(__int_as_float(c[j][3]) - MMA_MAGIC_F, f1, acc[3]);
     }
 }
+// one piece of the stream: block-group column `warp` of the chunk at `ch` (cb blocks)
+__device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, int lane, WPiece &r) {
+    r.wa = ldg_stream4(ch + (size_t)warp * 1024 + lane * 16);
+    r.wb = ldg_stream4(ch + (size_t)warp * 1024 + 512 + lane * 16);
+    r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * 128 + (lane >> 2) * 16);
+}
 
 // shared memory map (bytes): [red GEMV_RB*16*16*4*4 = 32768][hbuf GEMV_RB*8 floats + 64 scratch = 512][A3 of the input nbp*100]
 #define GEMV_FIXED_SMEM (GEMV_RB * 4096 + 512)
+
+// ---- Input staging.  The previous kernel's output reaches shared memory through cp.async.bulk (the TMA path): ordinary loads
+// would queue behind the ~70 KB of weight loads this SM already has in flight.  Shared memory map of the input area:
+//   [A3 image nbp*100][staging: fp32 vector n_in*4][IN_NORM only: norm weights n_in*4]
+// One thread issues the copies and everybody waits on the mbarrier; then the vector is normalised (IN_NORM, op order of
+// oracle/model.py:_norm) and put on the activation grid: a 32-element block is 8 consecutive threads' float4s, so the block
+// maximum is three shuffles and a thread stores one 32-bit word per digit plane.
+template <int IN>
+__device__ __noinline__ void stage_input_smem(const GemvArgs &a, uint8_t *sact, float *scratch, uint64_t *bar) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (IN == IN_ACT) {
+        if (tid == 0) {
+            const uint32_t bytes = (uint32_t)a.nbp * 100;
+            mbar_expect_tx(bar, bytes);
+            bulk_g2s(sact, a.act_in, bytes, bar);
+        }
+        mbar_wait(bar, 0);
+        return;
+    }
+    float *sx = (float *)(sact + (size_t)a.nbp * 100);
+    float *sw = sx + a.n_in;
+    float *sscale = (float *)(sact + (size_t)a.nbp * 96);
+    if (tid == 0) {
+        const uint32_t bytes = (uint32_t)a.n_in * 4;
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(sx, IN == IN_NORM ? (const void *)a.x : (const void *)a.act_in, bytes, bar);
+    }
+    mbar_wait(bar, 0);
+    const int n4 = a.n_in >> 2;
+    float r = 1.0f;
+    if (IN == IN_NORM) {
+        float ss = 0.f;
+        for (int q = tid; q < n4; q += GEMV_THREADS) {
+            const float4 v = ((const float4 *)sx)[q];
+            ss = fmaf(v.x, v.x, ss); ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
+        }
+        ss = warp_sum(ss);
+        if (lane == 0) scratch[warp] = ss;
+        __syncthreads();
+        float tot = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
+        r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)a.n_in), a.eps)));
+        mbar_wait(bar + 1, 0);   // the norm weights (requested before griddepcontrol.wait)
+    }
+    const int nq = a.nbp << 3;   // float4 slots including the zero padding blocks
+    for (int q0 = 0; q0 < nq; q0 += GEMV_THREADS) {
+        const int q = q0 + tid;  // float4 index; block = q / 8, word-in-block = q % 8
+        float yv[4] = {0.f, 0.f, 0.f, 0.f};
+        if (q < n4) {
+            const float4 v = ((const float4 *)sx)[q];
+            if (IN == IN_NORM) {
+                const float4 w = ((const float4 *)sw)[q];
+                const float xs[4] = {v.x, v.y, v.z, v.w}, ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) yv[e] = __fmul_rn(__fmul_rn(xs[e], r), a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e]);
+            } else {
+                yv[0] = v.x; yv[1] = v.y; yv[2] = v.z; yv[3] = v.w;
+            }
+        }
+        float m = fmaxf(fmaxf(fabsf(yv[0]), fabsf(yv[1])), fmaxf(fabsf(yv[2]), fabsf(yv[3])));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+        if (q < nq) {
+            const int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
+            const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
+            const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
+            uint32_t w0 = 0, w1 = 0, w2 = 0;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                int d0, d1, d2;
+                act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
+                w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
+                w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
+                w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
+            }
+            const int b = q >> 3, k = q & 7;                // elements 4k..4k+3 of block b
+            uint8_t *dst = sact + a3_off(b, 0, 4 * k);
+            *(uint32_t *)dst = w0;
+            *(uint32_t *)(dst + 128) = w1;
+            *(uint32_t *)(dst + 256) = w2;
+            if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
+        }
+    }
+    __syncthreads();
+}
+
+// ---- reduction + epilogue of the `batch_n` finished tiles parked in shared memory (called by all threads).
+// Every warp parked its K-partial of the 16 rows x 3 digit planes; warp w finalises tile batch_first + w.
+// Two CTA-wide barriers per GEMV_RB tiles instead of one per tile: the weight streams of the sixteen warps are not
+// re-synchronised on memory latency every other piece.
+template <int OUT>
+__device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    __syncthreads();
+    if (warp < batch_n) {
+        // lane = (half, row): each lane adds 8 of the 16 warp partials of its row in a fixed order, the halves meet by shuffle
+        const int tile = batch_first + warp;
+        const float *rb = red + (size_t)warp * (GEMV_CWARPS * 16 * 4);
+        const int r = lane & 15, hf = lane >> 4;
+        float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < GEMV_CWARPS / 2; ++w8) {
+            const float4 p4 = *(const float4 *)(rb + ((hf * (GEMV_CWARPS / 2) + w8) * 16 + r) * 4);
+            v0 += p4.x;
+            v1 += p4.y;
+            v2 += p4.z;
+        }
+        v0 += __shfl_xor_sync(0xffffffffu, v0, 16);
+        v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
+        v2 += __shfl_xor_sync(0xffffffffu, v2, 16);
+        const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
+        const int row = tile * TILE_ROWS + r;
+        if (OUT == OUT_BIAS) {
+            if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res ? yv + a.bias_or_res[row] : yv;
+        } else if (OUT == OUT_RES) {
+            if (lane < 16 && row < a.rows) a.y[row] = __ldcg(a.bias_or_res + row) + yv;
+        } else if (OUT == OUT_LOGITS) {
+            if (lane < 16 && row < a.rows) {
+                a.y[row] = yv;
+                if (yv > best_v || (yv == best_v && row < best_i)) { best_v = yv; best_i = row; }
+            }
+        } else {   // OUT_ACTMUL: rows (2j, 2j+1) = (gate_j, up_j)
+            const float up = __shfl_down_sync(0xffffffffu, yv, 1);
+            const float hv = act_fn(yv, a.act) * up;
+            const int pair = tile * 8 + (r >> 1);
+            if (lane < 16 && !(r & 1) && 2 * pair < a.rows) a.y[pair] = hv;
+        }
+    }
+    __syncthreads();   // the parked partials may be overwritten from here on
+}
+
 template <int IN, int OUT>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
     float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
     float *scratch = hbuf + GEMV_RB * 8;
-    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector
+    uint64_t *bars = (uint64_t *)(hbuf + 96);                                   // [0] input vector, [1] norm weights
+    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector (+ fp32 staging)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
-    if (tid == 0) pdl_launch_dependents();
+    if (tid == 0) {
+        pdl_launch_dependents();
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (IN == IN_NORM) {   // the norm weights are immutable: request them before waiting for the previous kernel
+            float *sw = (float *)(sact + (size_t)a.nbp * 100) + a.n_in;
+            mbar_expect_tx(&bars[1], (uint32_t)a.n_in * 4);
+            bulk_g2s(sw, a.norm_w, (uint32_t)a.n_in * 4, &bars[1]);
+        }
+    }
+    __syncthreads();
+    auto stamp = [&](int k) {
+        if (a.dbg && tid == 0) {
+            long long tt;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+            a.dbg[blockIdx.x * 8 + k] = tt;
+        }
+    };
+    stamp(0);
 
     // contiguous, aligned share of the tiles
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
@@ -207,116 +368,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     const int t0 = u0 * a.tile_align, t1 = min(a.n_tiles, u1 * a.tile_align);
     const int nt = t1 - t0;
     const int cpt = (a.nbp + KC - 1) / KC;                                      // chunks per tile
-    const int n_items = nt * cpt;                                               // (tile, chunk) pairs of this CTA
     const uint8_t *base = a.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
-    const uint64_t tile_bytes = (uint64_t)a.nbp * BLOCK_BYTES;
-    const int k_outer = a.k_outer;
+    const uint32_t tile_bytes = (uint32_t)a.nbp * BLOCK_BYTES;
+    const int cb_last = a.nbp - (cpt - 1) * KC;                                 // blocks in the last chunk of a tile
+    const bool act_full = warp < (KC >> 2);                                     // this warp has a block-group in a full chunk ...
+    const bool act_last = warp < (cb_last >> 2);                                // ... in the last chunk of a tile
 
-    // Load cursor: walks the (tile, chunk) items of this CTA in processing order without divisions.
-    //   tiles outermost: item i = ti*cpt + ck (the CTA's byte range is one contiguous run of chunks)
-    //   chunks outermost: item i = ck*nt + ti
-    int l_ti = 0, l_ck = 0, l_i = 0;
-    auto load_next = [&](WPiece &r) {
-        if (l_i < n_items) {
-            const int cb = min(KC, a.nbp - l_ck * KC);
-            if (warp < (cb >> 2)) {
-                const uint8_t *ch = base + (uint64_t)l_ti * tile_bytes + (uint64_t)l_ck * (KC * BLOCK_BYTES);
-                r.wa = ldg_stream4(ch + (size_t)warp * 1024 + lane * 16);
-                r.wb = ldg_stream4(ch + (size_t)warp * 1024 + 512 + lane * 16);
-                r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * 128 + g * 16);
-            }
-            ++l_i;
-            if (k_outer) { if (++l_ti == nt) { l_ti = 0; ++l_ck; } }
-            else         { if (++l_ck == cpt) { l_ck = 0; ++l_ti; } }
-        }
-    };
-    // ---- the weight stream starts now: it does not depend on the previous kernel
-    WPiece buf[GEMV_DEPTH];
-#pragma unroll
-    for (int d = 0; d < GEMV_DEPTH; ++d) load_next(buf[d]);
-
-    // ---- everything below reads what the previous kernel wrote (ld.global.cg: under programmatic dependent launch
-    //      a CTA of that kernel may have shared this SM's L1)
-    pdl_wait();
-    const uint8_t *adig;      // digit planes of the input vector
-    const float *ascale;      // per-block scales
-    float sfold;              // the 1/16 of the nibble trick
-    if (IN == IN_NORM) {
-        // RMSNorm (oracle/model.py:_norm op order) + activation grid, redundantly per CTA, straight into shared memory.
-        // Thread tid owns float4 #(tid + 512*i): every load is issued before the first use; a 32-element block is
-        // 8 consecutive threads of one iteration, so the block maximum is three shuffles.
-        float *sscale = (float *)(sact + (size_t)a.nbp * 96);
-        constexpr int NI = GEMV_NORM_MAX / 4 / GEMV_THREADS;
-        const int n4 = a.n_in >> 2;
-        float4 xv[NI], wv[NI];
-#pragma unroll
-        for (int i = 0; i < NI; ++i) {
-            const int q = tid + GEMV_THREADS * i;
-            xv[i] = q < n4 ? __ldcg((const float4 *)a.x + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-            wv[i] = q < n4 ? __ldg((const float4 *)a.norm_w + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        float ss = 0.f;
-#pragma unroll
-        for (int i = 0; i < NI; ++i) {
-            ss = fmaf(xv[i].x, xv[i].x, ss); ss = fmaf(xv[i].y, xv[i].y, ss);
-            ss = fmaf(xv[i].z, xv[i].z, ss); ss = fmaf(xv[i].w, xv[i].w, ss);
-        }
-        ss = warp_sum(ss);
-        if (lane == 0) scratch[warp] = ss;
-        cta_sync();
-        float tot = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
-        const float r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)a.n_in), a.eps)));
-#pragma unroll
-        for (int i = 0; i < NI; ++i) {
-            const int q = tid + GEMV_THREADS * i;            // float4 index; block = q / 8, word-in-block = q % 8
-            float yv[4];
-            const float xs[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w}, ws[4] = {wv[i].x, wv[i].y, wv[i].z, wv[i].w};
-            float m = 0.f;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float wi = a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e];
-                yv[e] = __fmul_rn(__fmul_rn(xs[e], r), wi);
-                m = fmaxf(m, fabsf(yv[e]));
-            }
-            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
-            if (q < (a.nbp << 3)) {
-                int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
-                const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
-                const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
-                uint32_t w0 = 0, w1 = 0, w2 = 0;
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    int d0, d1, d2;
-                    act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
-                    w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
-                    w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
-                    w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
-                }
-                const int b = q >> 3, k = q & 7;                // elements 4k..4k+3 of block b
-                uint8_t *dst = sact + a3_off(b, 0, 4 * k);
-                *(uint32_t *)dst = w0;
-                *(uint32_t *)(dst + 128) = w1;
-                *(uint32_t *)(dst + 256) = w2;
-                if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
-            }
-        }
-        cta_sync();
-        adig = sact;
-        ascale = sscale;
-    } else {
-        // the activation image (digits + scales, nbp*100 bytes) is copied once into shared memory
-        const int n16 = (a.nbp * 100) >> 4;
-        for (int i = tid; i < n16; i += GEMV_THREADS) ((uint4 *)sact)[i] = ldcg4(a.act_in + (size_t)i * 16);
-        cta_sync();
-        adig = sact;
-        ascale = (const float *)(sact + (size_t)a.nbp * 96);
-    }
-    sfold = 0.0625f;
-    // B fragments of block-group column `warp` of chunk ck (register resident; shared memory or L2 is read once per use below)
+    // B fragments of block-group column `warp` of chunk ck, from the shared-memory activation image
     auto load_b = [&](int ck, BFrag &b) {
         const int kbg = ck * (KC / 4) + warp;
         b.b01 = make_uint4(0u, 0u, 0u, 0u);
@@ -324,84 +382,37 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
         b.as = make_float4(0.f, 0.f, 0.f, 0.f);
         if (kbg * 4 < a.nbp) {
             if (g < 3) {
-                const uint4 *bp = (const uint4 *)(adig + (size_t)kbg * 384 + g * 128 + t * 32);
+                const uint4 *bp = (const uint4 *)(sact + (size_t)kbg * 384 + g * 128 + t * 32);
                 b.b01 = bp[0];
                 b.b23 = bp[1];
             }
-            b.as = *(const float4 *)(ascale + kbg * 4);
-            b.as.x *= sfold; b.as.y *= sfold; b.as.z *= sfold; b.as.w *= sfold;
+            b.as = *(const float4 *)(sact + (size_t)a.nbp * 96 + kbg * 16);
+            b.as.x *= 0.0625f; b.as.y *= 0.0625f; b.as.z *= 0.0625f; b.as.w *= 0.0625f;   // the 1/16 of the nibble trick
         }
     };
-
+    auto stage_input = [&]() {
+        stamp(1);
+        pdl_wait();
+        stamp(2);   // everything from here reads what the previous kernel wrote (ld.global.cg: under programmatic
+                      // dependent launch a CTA of that kernel may have shared this SM's L1)
+        stage_input_smem<IN>(a, sact, scratch, bars);
+        stamp(3);
+    };
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
-    // Finished tiles are parked in shared memory (every warp its K-partial of the 16 rows x 3 digit planes) and reduced
-    // GEMV_RB tiles at a time: two CTA-wide barriers per batch instead of one per tile, so the weight stream of the sixteen
-    // warps is not re-synchronised on memory latency every other piece.
     int batch_first = t0, batch_n = 0;
-    auto park_tile = [&](const float (&acc)[4]) {
+    auto park = [&](float (&acc)[4]) {   // park the finished tile's partial; reduce when GEMV_RB tiles are waiting
         float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
         if (t < 2) {
             *(float2 *)(rb + (warp * 16 + g) * 4 + 2 * t) = make_float2(acc[0], acc[1]);
             *(float2 *)(rb + (warp * 16 + g + 8) * 4 + 2 * t) = make_float2(acc[2], acc[3]);
         }
-        ++batch_n;
-    };
-    auto flush_batch = [&]() {
-        cta_sync();
-        if (warp < batch_n) {
-            // warp w finalises tile batch_first + w.  lane = (half, row): each lane adds 8 of the 16 warp partials of its
-            // row in a fixed order, the halves meet by shuffle.
-            const int tile = batch_first + warp;
-            const float *rb = red + (size_t)warp * (GEMV_CWARPS * 16 * 4);
-            const int r = lane & 15, hf = lane >> 4;
-            float v0 = 0.f, v1 = 0.f, v2 = 0.f;
-#pragma unroll
-            for (int w8 = 0; w8 < GEMV_CWARPS / 2; ++w8) {
-                const float4 p4 = *(const float4 *)(rb + ((hf * (GEMV_CWARPS / 2) + w8) * 16 + r) * 4);
-                v0 += p4.x;
-                v1 += p4.y;
-                v2 += p4.z;
-            }
-            v0 += __shfl_xor_sync(0xffffffffu, v0, 16);
-            v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
-            v2 += __shfl_xor_sync(0xffffffffu, v2, 16);
-            const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
-            const int row = tile * TILE_ROWS + r;
-            if (OUT == OUT_BIAS) {
-                if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res ? yv + a.bias_or_res[row] : yv;
-            } else if (OUT == OUT_RES) {
-                if (lane < 16 && row < a.rows) a.y[row] = __ldcg(a.bias_or_res + row) + yv;
-            } else if (OUT == OUT_LOGITS) {
-                if (lane < 16 && row < a.rows) {
-                    a.y[row] = yv;
-                    if (yv > best_v || (yv == best_v && row < best_i)) { best_v = yv; best_i = row; }
-                }
-            } else {   // OUT_ACTMUL: rows (2j, 2j+1) = (gate_j, up_j)
-                const float up = __shfl_down_sync(0xffffffffu, yv, 1);
-                const float hv = act_fn(yv, a.act) * up;
-                const int pair = tile * 8 + (r >> 1);
-                if (lane < 16 && !(r & 1)) {
-                    hbuf[warp * 8 + (r >> 1)] = hv;
-                    if (a.y && 2 * pair < a.rows) a.y[pair] = hv;
-                }
-            }
+        acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
+        if (++batch_n == GEMV_RB) {
+            flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i);
+            batch_first += batch_n;
+            batch_n = 0;
         }
-        cta_sync();   // the parked partials may be overwritten from here on; hbuf is complete
-        if (OUT == OUT_ACTMUL && warp < (batch_n >> 2)) {
-            // 32 consecutive h values (4 tiles) -> one block on the activation grid.  batch_first is a multiple of 4.
-            const int blk = (batch_first >> 2) + warp;
-            float sc;
-            const float hx = (2 * (blk * 32 + lane) < a.rows) ? hbuf[warp * 32 + lane] : 0.f;
-            int X = act_grid_lane(hx, sc);
-            a3_store_block(a.act_out, a.n_out_act, blk, lane, X, sc);
-        }
-        batch_first += batch_n;
-        batch_n = 0;
-    };
-    auto finish_tile = [&](const float (&acc)[4]) {
-        park_tile(acc);
-        if (batch_n == GEMV_RB) flush_batch();
     };
     // when the CTA's last piece has been requested, pull the head of the next kernel's weights into L2
     auto prefetch_next = [&]() {
@@ -412,89 +423,123 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
             for (uint64_t o = 0; o + 16384 <= n; o += 16384) l2_prefetch(p0 + o, 16384);
         }
     };
-    bool pf_done = false;
-    const int cb_last = a.nbp - (cpt - 1) * KC;                  // blocks in the last chunk of a tile
-    const bool act_full = warp < (KC >> 2) && cpt > 1;           // this warp has work in a full chunk / in the last chunk
-    const bool act_last = warp < (cb_last >> 2);
 
-    if (!k_outer) {
-        // ---- tiles outermost; K spans at most two chunks, whose B fragments stay in registers for the whole kernel.
-        //      GEMV_DEPTH is even, so the chunk index of slot d is d & 1 when cpt == 2: no per-item index arithmetic.
-        BFrag bf0, bf1;
-        load_b(0, bf0);
-        load_b(1, bf1);
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    WPiece buf0, buf1, buf2, buf3;      // GEMV_DEPTH = 4 pieces in flight per warp
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    if (!a.k_outer) {
+        // ================= tiles outermost: the CTA's bytes are one contiguous run of chunks; K spans one or two chunks whose
+        // B fragments stay in registers for the whole kernel.  With two chunks per tile the even pieces are full chunks and
+        // the odd ones the (possibly shorter) last chunk of a tile: no index arithmetic in the loop.
+        const uint8_t *lp = base;
+        int l_rem = nt * cpt;            // pieces not requested yet
+        // L2 prefetch cursor (thread 0): cp.async.bulk.prefetch.L2 keeps the CTA's contiguous byte range L2_WINDOW_BYTES ahead of
+        // the register loads, so those hit L2 (short latency) while HBM streams at its own pace from the first cycle
+        const uint8_t *pf = base, *pf_end = base + (size_t)nt * tile_bytes;
+        auto l2_window = [&]() {
+            if (tid == 0) {
+                const uint8_t *lim = lp + L2_WINDOW_BYTES < pf_end ? lp + L2_WINDOW_BYTES : pf_end;
+                while (pf + 16384 <= lim) { l2_prefetch(pf, 16384); pf += 16384; }
+                if (lim == pf_end && pf < pf_end) { l2_prefetch(pf, (uint32_t)(pf_end - pf) & ~15u); pf = pf_end; }
+            }
+        };
+        l2_window();
+        auto load_full = [&](WPiece &r) {
+            if (l_rem > 0) { if (act_full) load_piece(lp, KC, warp, lane, r); lp += KC * BLOCK_BYTES; --l_rem; }
+        };
+        auto load_last = [&](WPiece &r) {
+            if (l_rem > 0) { if (act_last) load_piece(lp, cb_last, warp, lane, r); lp += cb_last * BLOCK_BYTES; --l_rem; }
+        };
         if (cpt == 2) {
-            for (int i0 = 0; i0 < n_items; i0 += GEMV_DEPTH) {
-#pragma unroll
-                for (int d = 0; d < GEMV_DEPTH; ++d) {
-                    if (i0 + d < n_items) {
-                        if (d & 1) { if (act_last) bg_mma(buf[d], bf1, acc); }
-                        else       { if (act_full) bg_mma(buf[d], bf0, acc); }
-                        load_next(buf[d]);
-                        if (d & 1) {
-                            finish_tile(acc);
-                            acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
-                        }
-                    }
+            load_full(buf0); load_last(buf1); load_full(buf2); load_last(buf3);     // the stream starts before the wait
+            stage_input();
+            BFrag bf0, bf1;
+            load_b(0, bf0);
+            load_b(1, bf1);
+            for (int rem = nt; rem > 0; rem -= 2) {
+                if (act_full) bg_mma(buf0, bf0, acc);
+                load_full(buf0);
+                if (act_last) bg_mma(buf1, bf1, acc);
+                load_last(buf1);
+                park(acc);
+                if (rem > 1) {
+                    if (act_full) bg_mma(buf2, bf0, acc);
+                    load_full(buf2);
+                    if (act_last) bg_mma(buf3, bf1, acc);
+                    load_last(buf3);
+                    park(acc);
                 }
-                if (!pf_done && l_i >= n_items) { prefetch_next(); pf_done = true; }
+                l2_window();
+                if (l_rem == 0) { prefetch_next(); l_rem = -1; }
             }
         } else {
-            for (int i0 = 0; i0 < n_items; i0 += GEMV_DEPTH) {
-#pragma unroll
-                for (int d = 0; d < GEMV_DEPTH; ++d) {
-                    if (i0 + d < n_items) {
-                        if (act_last) bg_mma(buf[d], bf0, acc);
-                        load_next(buf[d]);
-                        finish_tile(acc);
-                        acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
-                    }
-                }
-                if (!pf_done && l_i >= n_items) { prefetch_next(); pf_done = true; }
+            load_last(buf0); load_last(buf1); load_last(buf2); load_last(buf3);
+            stage_input();
+            BFrag bf0;
+            load_b(0, bf0);
+            for (int rem = nt; rem > 0; rem -= 4) {
+                if (act_last) bg_mma(buf0, bf0, acc);
+                load_last(buf0);
+                park(acc);
+                if (rem > 1) { if (act_last) bg_mma(buf1, bf0, acc); load_last(buf1); park(acc); }
+                if (rem > 2) { if (act_last) bg_mma(buf2, bf0, acc); load_last(buf2); park(acc); }
+                if (rem > 3) { if (act_last) bg_mma(buf3, bf0, acc); load_last(buf3); park(acc); }
+                l2_window();
+                if (l_rem == 0) { prefetch_next(); l_rem = -1; }
             }
         }
+        if (l_rem == 0) prefetch_next();
     } else {
-        // ---- chunks outermost (long K, at most GEMV_MAXT tiles per CTA): the B fragments of one chunk at a time,
-        //      the accumulators of every tile of the CTA in registers
-        float accs[GEMV_MAXT][4];
-#pragma unroll
-        for (int q = 0; q < GEMV_MAXT; ++q) accs[q][0] = accs[q][1] = accs[q][2] = accs[q][3] = 0.f;
+        // ================= chunks outermost (K longer than two chunks; a CTA owns one or two tiles whose accumulators stay in
+        // registers).  A step is chunk ck of both tiles; the B fragments of a step are read from shared memory one step ahead.
+        float acc1[4] = {0.f, 0.f, 0.f, 0.f};
+        const bool two = nt > 1;
+        int l_ck = 0;                     // chunk of the next step to request
+        auto load_step = [&](WPiece &r0, WPiece &r1) {
+            if (l_ck < cpt) {
+                const bool last = l_ck == cpt - 1;
+                if (last ? act_last : act_full) {
+                    const uint8_t *ch = base + (size_t)l_ck * (KC * BLOCK_BYTES);
+                    load_piece(ch, last ? cb_last : KC, warp, lane, r0);
+                    if (two) load_piece(ch + tile_bytes, last ? cb_last : KC, warp, lane, r1);
+                }
+                ++l_ck;
+            }
+        };
+        if (tid == 0) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once
+            for (uint32_t o = 0; o + 16384 <= (uint32_t)nt * tile_bytes; o += 16384) l2_prefetch(base + o, 16384);
+        }
+        load_step(buf0, buf1);
+        load_step(buf2, buf3);
+        stage_input();
         BFrag bcur, bnxt;
         load_b(0, bcur);
-        if (cpt > 1) load_b(1, bnxt);
-        int ti = 0, ck = 0;
-        for (int i0 = 0; i0 < n_items; i0 += GEMV_DEPTH) {
-#pragma unroll
-            for (int d = 0; d < GEMV_DEPTH; ++d) {
-                if (i0 + d < n_items) {
-                    const bool active = (ck == cpt - 1) ? act_last : act_full;
-                    if (active) {
-#pragma unroll
-                        for (int q = 0; q < GEMV_MAXT; ++q)
-                            if (q == ti) bg_mma(buf[d], bcur, accs[q]);
-                    }
-                    load_next(buf[d]);
-                    if (++ti == nt) {   // chunk finished: rotate the B fragments, fetch the one after next
-                        ti = 0;
-                        ++ck;
-                        bcur = bnxt;
-                        if (ck + 1 < cpt) load_b(ck + 1, bnxt);
-                    }
-                }
+        for (int ck = 0; ck < cpt; ck += 2) {
+            load_b(ck + 1, bnxt);
+            if ((ck == cpt - 1) ? act_last : act_full) {
+                bg_mma(buf0, bcur, acc);
+                if (two) bg_mma(buf1, bcur, acc1);
             }
-            if (!pf_done && l_i >= n_items) { prefetch_next(); pf_done = true; }
+            load_step(buf0, buf1);
+            if (ck + 1 < cpt) {
+                load_b(ck + 2, bcur);
+                if ((ck + 1 == cpt - 1) ? act_last : act_full) {
+                    bg_mma(buf2, bnxt, acc);
+                    if (two) bg_mma(buf3, bnxt, acc1);
+                }
+                load_step(buf2, buf3);
+            }
+            if (l_ck == cpt) { prefetch_next(); l_ck = cpt + 1; }
         }
-#pragma unroll
-        for (int q = 0; q < GEMV_MAXT; ++q)
-            if (q < nt) finish_tile(accs[q]);
+        if (nt > 0) park(acc);
+        if (two) park(acc1);
     }
-    if (batch_n > 0) flush_batch();
-    if (!pf_done) prefetch_next();
+    stamp(4);
+    if (batch_n > 0) flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i);
+    stamp(5);
     if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima
         float *sv = scratch;
         int *si = (int *)(scratch + 16);
-        cta_sync();
+        __syncthreads();
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) {
             float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
@@ -502,7 +547,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
             if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
         }
         if (lane == 0) { sv[warp] = best_v; si[warp] = best_i; }
-        cta_sync();
+        __syncthreads();
         if (warp == 0) {
             best_v = lane < GEMV_CWARPS ? sv[lane] : -INFINITY;
             best_i = lane < GEMV_CWARPS ? si[lane] : 0x7fffffff;
@@ -519,6 +564,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
 
 // ------------------------------------------------------------------------------------------ launcher
 static int g_num_sms = 0;
+static long long *g_gemv_dbg = nullptr;   // set by b2dbg_gemv_profile (development aid): ring of `slots` x [148][8] stamps
+static int g_gemv_dbg_slots = 1, g_gemv_dbg_next = 0;
+extern "C" void b2dbg_gemv_profile(long long *d_buf) { g_gemv_dbg = d_buf; g_gemv_dbg_slots = 1; }
+extern "C" void b2dbg_gemv_profile_ring(long long *d_buf, int slots) { g_gemv_dbg = d_buf; g_gemv_dbg_slots = slots; g_gemv_dbg_next = 0; }
 int gemv_grid(int n_tiles, int tile_align) {
     if (!g_num_sms) {
         int dev = 0;
@@ -534,7 +583,7 @@ template <int IN, int OUT>
 static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -561,25 +610,28 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     a.rows = (int)rows;
     a.nbp = (int)nblocks_padded(cols);
     a.n_tiles = (int)ntiles(rows);
-    a.tile_align = out_mode == OUT_ACTMUL ? 4 : 1;
+    a.tile_align = 1;
     if (in_mode == IN_NORM && cols > GEMV_NORM_MAX) return cudaErrorInvalidValue;
     a.x = x; a.norm_w = norm_w; a.eps = eps; a.plus_one = plus_one; a.n_in = (int)cols;
     a.act_in = (const uint8_t *)act_in;
     a.y = y; a.bias_or_res = bias_or_res; a.act_out = (uint8_t *)act_out; a.n_out_act = (int)(rows / 2); a.act = act;
     a.pmax = pmax; a.pidx = pidx;
     a.pf_ptr = (const uint8_t *)next_w; a.pf_total = next_bytes;
+    a.dbg = g_gemv_dbg ? g_gemv_dbg + (size_t)(g_gemv_dbg_next++ % g_gemv_dbg_slots) * 148 * 8 : nullptr;
     int grid = gemv_grid(a.n_tiles, a.tile_align);
     const int cpt = (a.nbp + KC - 1) / KC;
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
     int max_tiles = ((units + grid - 1) / grid) * a.tile_align;
     a.k_outer = cpt > 2;
     if (grid_out) *grid_out = grid;
-    size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + 128;
+    size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 * (in_mode == IN_NORM ? 2 : 1)) + 128;
+    if (smem > 227 * 1024) return cudaErrorInvalidValue;
 #define CASE(I, O) if (in_mode == I && out_mode == O) return launch_one<I, O>(aa, grid, smem, st, pdl)
     if (!a.k_outer || max_tiles <= GEMV_MAXT) {
         const GemvArgs &aa = a;
         CASE(IN_NORM, OUT_BIAS); CASE(IN_NORM, OUT_RES); CASE(IN_NORM, OUT_ACTMUL); CASE(IN_NORM, OUT_LOGITS);
-        CASE(IN_ACT, OUT_BIAS); CASE(IN_ACT, OUT_RES); CASE(IN_ACT, OUT_ACTMUL); CASE(IN_ACT, OUT_LOGITS);
+        CASE(IN_ACT, OUT_BIAS); CASE(IN_ACT, OUT_RES); CASE(IN_ACT, OUT_ACTMUL);
+        CASE(IN_F32, OUT_BIAS); CASE(IN_F32, OUT_RES);
         return cudaErrorInvalidValue;
     }
     // long K and many rows (no matrix of the seven models; kept for generality): the accumulators of a CTA's tiles live in
@@ -600,6 +652,8 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
         if (in_mode == IN_NORM && out_mode == OUT_RES) e = launch_one<IN_NORM, OUT_RES>(aa, grid, smem, st, pdl);
         if (in_mode == IN_ACT && out_mode == OUT_BIAS) e = launch_one<IN_ACT, OUT_BIAS>(aa, grid, smem, st, pdl);
         if (in_mode == IN_ACT && out_mode == OUT_RES) e = launch_one<IN_ACT, OUT_RES>(aa, grid, smem, st, pdl);
+        if (in_mode == IN_F32 && out_mode == OUT_BIAS) e = launch_one<IN_F32, OUT_BIAS>(aa, grid, smem, st, pdl);
+        if (in_mode == IN_F32 && out_mode == OUT_RES) e = launch_one<IN_F32, OUT_RES>(aa, grid, smem, st, pdl);
         if (e != cudaSuccess) return e;
     }
     return cudaSuccess;

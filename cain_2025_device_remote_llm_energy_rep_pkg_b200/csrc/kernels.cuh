@@ -20,7 +20,7 @@ void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols,
 void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st);
 
 // streaming GEMV (gemv.cu)
-enum { GEMV_IN_NORM = 0, GEMV_IN_ACT = 1 };
+enum { GEMV_IN_NORM = 0, GEMV_IN_ACT = 1, GEMV_IN_F32 = 2 };
 enum { GEMV_OUT_BIAS = 0, GEMV_OUT_RES = 1, GEMV_OUT_ACTMUL = 2, GEMV_OUT_LOGITS = 3 };
 int gemv_grid(int n_tiles, int tile_align);
 cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,

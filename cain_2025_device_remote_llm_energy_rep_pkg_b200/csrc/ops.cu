@@ -61,17 +61,25 @@ extern "C" int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t 
     B2_CHECK(d_packed && d_act && d_y && rows >= 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_gemv: bad arguments");
     B2_CHECK(mode >= 0 && mode <= 2, B2_EINVAL, "b2_op_gemv: mode %d", mode);
     B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_gemv: mode 1 needs the residual vector");
-    B2_CHECK(mode != 2 || rows % 64 == 0, B2_EINVAL, "b2_op_gemv: mode 2 needs rows %% 64 == 0 (32 gate/up pairs per activation block)");
+    B2_CHECK(mode != 2 || rows % 2 == 0, B2_EINVAL, "b2_op_gemv: mode 2 needs an even row count (gate/up pairs)");
     if (rows == 0) return B2_OK;
-    void *act_out = nullptr;
-    if (mode == 2) {   // the kernel also emits the activation-grid image of h; the op-level caller only wants h
-        B2_CUDA(cudaMalloc(&act_out, a3_bytes(rows / 2)));
-        B2_CUDA(cudaMemset(act_out, 0, a3_bytes(rows / 2)));
-    }
-    cudaError_t e = launch_gemv(GEMV_IN_ACT, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_act, d_y, d_bias_or_res, act_out, act,
+    cudaError_t e = launch_gemv(GEMV_IN_ACT, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_act, d_y, d_bias_or_res, nullptr, act,
                                 nullptr, nullptr, nullptr, nullptr, 0, 0, false);
-    if (e == cudaSuccess && act_out) e = cudaDeviceSynchronize();
-    if (act_out) cudaFree(act_out);
+    B2_CUDA(e);
+    B2_CUDA(cudaGetLastError());
+    return B2_OK;
+}
+// y = W * grid(x) (+bias / +res) with the fp32 input vector put on the activation grid inside the kernel (the engine's down
+// projection consumes act(gate)*up this way).  mode 0 or 1 as b2_op_gemv.
+extern "C" int b2_op_gemv_f32(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_bias_or_res,
+                              int mode, float *d_y) {
+    ApiScope _scope("b2_op_gemv_f32");
+    B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_op_gemv_f32: type %d not supported", type);
+    B2_CHECK(d_packed && d_x && d_y && rows > 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_gemv_f32: bad arguments");
+    B2_CHECK(mode == 0 || (mode == 1 && d_bias_or_res), B2_EINVAL, "b2_op_gemv_f32: mode must be 0, or 1 with a residual vector");
+    cudaError_t e = launch_gemv(GEMV_IN_F32, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_x, d_y, d_bias_or_res, nullptr, 0,
+                                nullptr, nullptr, nullptr, nullptr, 0, 0, false);
+    B2_CHECK(e != cudaErrorInvalidValue, B2_EINVAL, "b2_op_gemv_f32: cols %lld too long for the shared-memory staging", (long long)cols);
     B2_CUDA(e);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
@@ -83,26 +91,29 @@ extern "C" int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int
                                int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y, void *d_act_out, int32_t *d_argmax) {
     ApiScope _scope("b2_op_norm_gemv");
     B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_op_norm_gemv: type %d not supported", type);
-    B2_CHECK(d_packed && d_x && d_norm_w && rows > 0 && cols > 0 && cols % QK == 0 && cols <= 4096, B2_EINVAL, "b2_op_norm_gemv: bad arguments (cols must be a multiple of 32, at most 4096)");
+    B2_CHECK(d_packed && d_x && d_norm_w && rows > 0 && cols > 0 && cols % QK == 0 && cols <= 8192, B2_EINVAL, "b2_op_norm_gemv: bad arguments (cols must be a multiple of 32, at most 8192)");
     B2_CHECK(mode >= 0 && mode <= 3, B2_EINVAL, "b2_op_norm_gemv: mode %d", mode);
-    B2_CHECK(mode == 2 || d_y, B2_EINVAL, "b2_op_norm_gemv: d_y is NULL");
+    B2_CHECK(d_y, B2_EINVAL, "b2_op_norm_gemv: d_y is NULL");
     B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_norm_gemv: mode 1 needs the residual vector");
-    B2_CHECK(mode != 2 || rows % 64 == 0, B2_EINVAL, "b2_op_norm_gemv: mode 2 needs rows %% 64 == 0");
+    B2_CHECK(mode != 2 || rows % 64 == 0, B2_EINVAL, "b2_op_norm_gemv: mode 2 needs rows %% 64 == 0 (32 gate/up pairs per activation block)");
     B2_CHECK(mode != 3 || d_argmax, B2_EINVAL, "b2_op_norm_gemv: mode 3 needs d_argmax");
-    void *tmp = nullptr, *act_out = d_act_out;
+    void *tmp = nullptr;
     float *pmax = nullptr;
     int *pidx = nullptr;
-    uint64_t need = (mode == 2 && !d_act_out) ? a3_bytes(rows / 2) : (mode == 3 ? 8192 : 0);
-    if (need) {
-        B2_CUDA(cudaMalloc(&tmp, need));
-        B2_CUDA(cudaMemset(tmp, 0, need));
-        if (mode == 2) act_out = tmp;
-        else { pmax = (float *)tmp; pidx = (int *)((char *)tmp + 4096); }
+    if (mode == 3) {
+        B2_CUDA(cudaMalloc(&tmp, 8192));
+        B2_CUDA(cudaMemset(tmp, 0, 8192));
+        pmax = (float *)tmp;
+        pidx = (int *)((char *)tmp + 4096);
     }
     int grid = 0;
-    cudaError_t e = launch_gemv(GEMV_IN_NORM, mode, d_packed, rows, cols, d_x, d_norm_w, eps, plus_one, nullptr, d_y, d_bias_or_res, act_out, act,
+    cudaError_t e = launch_gemv(GEMV_IN_NORM, mode, d_packed, rows, cols, d_x, d_norm_w, eps, plus_one, nullptr, d_y, d_bias_or_res, nullptr, act,
                                 pmax, pidx, &grid, nullptr, 0, 0, false);
     if (e == cudaSuccess && mode == 3) launch_argmax_partials(pmax, pidx, grid, d_argmax, 0);
+    if (e == cudaSuccess && mode == 2 && d_act_out) {   // the engine's next GEMV puts h on the grid itself; offered here for callers that want the image
+        e = cudaMemsetAsync(d_act_out, 0, a3_bytes(rows / 2), 0);
+        if (e == cudaSuccess) launch_quant_act(d_y, rows / 2, d_act_out, 0);
+    }
     if (e == cudaSuccess && tmp) e = cudaDeviceSynchronize();
     if (tmp) cudaFree(tmp);
     B2_CUDA(e);

@@ -155,9 +155,13 @@ uint64_t b2_act_bytes(int64_t n);
 int b2_op_quant_act(const float *d_x, int64_t n, void *d_act);
 int b2_op_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n, float eps, int plus_one, void *d_act, float *d_y_opt);
 /* y[rows] = W[rows,cols] * act (+ bias) ; mode 0: y = Wx(+bias); 1: y = res + Wx; 2: rows are (gate,up)
- * pairs, y[rows/2] = act(gate)*up (rows must be a multiple of 64). */
+ * pairs, y[rows/2] = act(gate)*up. */
 int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const void *d_act,
                const float *d_bias_or_res, int mode, int act, float *d_y);
+/* Same product with an f32 input vector: the kernel puts x on the activation grid itself (the engine's down projection
+ * consumes act(gate)*up this way).  mode 0 (+bias) or 1 (+residual). */
+int b2_op_gemv_f32(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_bias_or_res,
+                   int mode, float *d_y);
 /* The engine's fused form: RMSNorm(x, norm_w) -> activation grid -> y = W * (.) with the same epilogues; mode 3 writes
  * logits to d_y and the arg-max index (lowest index on ties) to d_argmax; mode 2 can also return the activation-grid
  * image of its result in d_act_out (b2_act_bytes(rows/2) bytes, may be NULL). */

@@ -135,6 +135,27 @@ def test_gemv_modes(lib, D, rows, cols):
     assert np.all(np.abs(dres.to_numpy(np.float32, (rows,)) - (ref + bias)) <= tol + 1e-6 * np.abs(bias))
 
 
+@pytest.mark.parametrize("rows,cols", [(7, 288), (4096, 14336), (3072, 24576), (100, 32)])
+def test_gemv_f32_input_is_gridded_in_kernel(lib, D, rows, cols):
+    """The engine's down projection: fp32 vector in, activation grid applied inside the kernel."""
+    rng = np.random.default_rng(rows + cols)
+    blob = Q.quantize_q4_0((rng.standard_normal((rows, cols)) * 0.02).astype(np.float32))
+    x = (rng.standard_normal(cols) * np.exp(rng.standard_normal(cols))).astype(np.float32)
+    res = rng.standard_normal(rows).astype(np.float32)
+    dW, dx, dres, dy = pack(lib, D, blob, rows, cols), D.from_numpy(x), D.from_numpy(res), D(rows * 4)
+    ref, mag = ref_gemv(blob, x)
+    chk(lib, lib.b2_op_gemv_f32(2, dW.ptr, rows, cols, dx.ptr, None, 0, dy.ptr))
+    assert np.all(np.abs(dy.to_numpy(np.float32, (rows,)) - ref) <= 4e-6 * mag + 1e-30)
+    chk(lib, lib.b2_op_gemv_f32(2, dW.ptr, rows, cols, dx.ptr, dres.ptr, 1, dres.ptr))
+    assert np.all(np.abs(dres.to_numpy(np.float32, (rows,)) - (ref + res)) <= 4e-6 * mag + 1e-6 * np.abs(res))
+    # it is the same function as gridding first and calling the activation-image entry point: bit-identical
+    act = make_act(lib, D, x)
+    dy2 = D(rows * 4)
+    chk(lib, lib.b2_op_gemv(2, dW.ptr, rows, cols, act.ptr, None, 0, 0, dy2.ptr))
+    chk(lib, lib.b2_op_gemv_f32(2, dW.ptr, rows, cols, dx.ptr, None, 0, dy.ptr))
+    assert np.array_equal(dy.to_numpy(np.float32, (rows,)), dy2.to_numpy(np.float32, (rows,)))
+
+
 @pytest.mark.parametrize("act_id,I,H", [(0, 416, 288), (1, 512, 256), (0, 1024, 4096)])
 def test_gemv_gate_up_pairs(lib, D, act_id, I, H):
     rng = np.random.default_rng(I + H)
@@ -152,7 +173,7 @@ def test_gemv_gate_up_pairs(lib, D, act_id, I, H):
     a = gt / (1 + torch.exp(-gt)) if act_id == 0 else 0.5 * gt * (1 + torch.tanh(0.7978845608028654 * (gt + 0.044715 * gt ** 3)))
     ref = a.numpy() * uv
     assert np.abs(y - ref).max() <= 2e-5 * np.abs(ref).max()
-    assert lib.b2_op_gemv(2, dW.ptr, 2 * I + 2, H, act.ptr, None, 2, act_id, dy.ptr) == -1
+    assert lib.b2_op_gemv(2, dW.ptr, 2 * I + 1, H, act.ptr, None, 2, act_id, dy.ptr) == -1
 
 
 @pytest.mark.parametrize("V,H,plus_one", [(1000, 288, 0), (1024, 512, 1), (32064, 3072, 0), (5000, 4096, 0)])

@@ -30,17 +30,22 @@ act_h = DevBuf(lib.b2_act_bytes(I))
 chk(lib.b2_op_quant_act(h.ptr, I, act_h.ptr))
 y, hh, act_o = DevBuf(H * 4), DevBuf(I * 4), DevBuf(lib.b2_act_bytes(I))
 dbg = DevBuf(148 * 8 * 8)
-prof = False
+prof = os.environ.get("B2_PROF") == "1"
+if prof:
+    lib.b2dbg_gemv_profile.argtypes = [C.c_void_p]
+    lib.b2dbg_gemv_profile(dbg.ptr)
 
 
 def report(name):
     if not prof:
         return
     chk(lib.b2_dev_sync())
-    d = dbg.to_numpy(np.int64, (148, 8))
-    print(f"{name}: cycles per CTA (warp 1) median total {np.median(d[:,0]):.0f} prologue {np.median(d[:,1]):.0f} wait_full {np.median(d[:,2]):.0f} "
-          f"compute {np.median(d[:,3]):.0f} reduce {np.median(d[:,4]):.0f} | producer wait_empty {np.median(d[:,5]):.0f} chunks {np.median(d[:,6]):.0f} "
-          f"| max total {d[:,0].max()} min {d[:,0].min()}")
+    d = dbg.to_numpy(np.int64, (148, 8)).astype(np.float64)
+    t0 = d[:, 0].min()
+    rel = d[:, :6] - t0
+    names = ["start", "loads issued", "wait done", "input staged", "stream done", "flushed"]
+    print(name + ": ns since first CTA start (median / max over CTAs): " +
+          ", ".join(f"{n} {np.median(rel[:, i]):.0f}/{rel[:, i].max():.0f}" for i, n in enumerate(names)))
 
 
 for _ in range(reps):
