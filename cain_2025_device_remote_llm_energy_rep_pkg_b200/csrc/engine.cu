@@ -80,13 +80,14 @@ struct b2_session {
     void *act_attn = nullptr, *act_h = nullptr, *attn_scratch = nullptr, *argmax_scratch = nullptr;
     float *pmax = nullptr;
     int *pidx = nullptr;
+    float *xsq = nullptr;          // per-CTA partial sums of squares of the residual stream (input of the next RMSNorm)
     int head_grid = 0;
     bool use_pdl = true;
     bool fused_attn = true;
     float *logits_log = nullptr;
     uint64_t logits_log_cap = 0;   // in floats
-    cudaGraphExec_t graphs[G_COUNT] = {};
-    int graph_launches[G_COUNT] = {};
+    cudaGraphExec_t graphs[G_COUNT][2] = {};   // [..][0]: positions below ATTN_SHORT_CTX (one attention CTA per head), [..][1]: longer contexts
+    int graph_launches[G_COUNT][2] = {};
     bool use_graphs = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     b2_stats stats{};
@@ -429,7 +430,7 @@ __global__ void k_copy_logits(const float *logits, int n, float *log, const DevS
 }
 
 // enqueue one forward pass for the token in state->cur_token at position state->pos; returns #launches
-static int enqueue_forward(b2_session *s, bool with_head) {
+static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
@@ -438,17 +439,19 @@ static int enqueue_forward(b2_session *s, bool with_head) {
     int n = 0;
     auto bytes_of = [](const Mat &mt) { return packed_q4_0_bytes(mt.rows, mt.cols); };
     float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
-    launch_embed_row(m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, st); n++;
+    launch_embed_row(m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, s->xsq, st); n++;
+    int xsq_n = 1;   // how many partial sums of squares the producer of the current x left in s->xsq
     uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
         LayerW &ly = m->layers[l];
+        int g = 0;
         // each GEMV hints the matrix the next GEMV will stream (L2 prefetch of the head of every CTA's share)
         const Mat *after_down = (l + 1 < c.n_layers) ? &m->layers[l + 1].qkv : (with_head ? &m->head : nullptr);
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), st, pdl); n++;
+                    s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), s->xsq, xsq_n, nullptr, st, pdl); n++;
         if (s->fused_attn) {
             launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
-                              s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, s->max_ctx, st, pdl); n++;
+                              s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, attn_ctx, st, pdl); n++;
         } else {
             launch_rope_kv(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
                            s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, st); n++;
@@ -456,21 +459,25 @@ static int enqueue_forward(b2_session *s, bool with_head) {
                                s->page_table, s->attn_out, s->attn_scratch, s->max_ctx, st); n++;
             launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
         }
+        // two partial-sum buffers alternate: a kernel reads the partials of its input while writing those of its output
         launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
-                    nullptr, nullptr, nullptr, ly.gateup.packed, bytes_of(ly.gateup), st, pdl); n++;
+                    nullptr, nullptr, &g, ly.gateup.packed, bytes_of(ly.gateup), nullptr, 0, s->xsq + 512, st, pdl); n++;
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    s->h, nullptr, nullptr, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), st, pdl); n++;
+                    s->h, nullptr, nullptr, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), s->xsq + 512, g, nullptr, st, pdl); n++;
         launch_gemv(GEMV_IN_F32, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->h, s->x, s->x, nullptr, 0,
-                    nullptr, nullptr, nullptr, after_down ? after_down->packed : nullptr, after_down ? bytes_of(*after_down) : 0, st, pdl); n++;
+                    nullptr, nullptr, &g, after_down ? after_down->packed : nullptr, after_down ? bytes_of(*after_down) : 0, nullptr, 0, s->xsq, st, pdl); n++;
+        xsq_n = g;
     }
     if (with_head) {
         launch_gemv(GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, m->layers[0].qkv.packed, bytes_of(m->layers[0].qkv), st, pdl); n++;
+                    s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, m->layers[0].qkv.packed, bytes_of(m->layers[0].qkv),
+                    s->xsq, xsq_n, nullptr, st, pdl); n++;
     }
     return n;
 }
 
-static int enqueue_graph_body(b2_session *s, int which) {
+static int enqueue_graph_body(b2_session *s, int which, int variant) {
+    const int attn_ctx = (variant == 0 && s->max_ctx > ATTN_SHORT_CTX) ? ATTN_SHORT_CTX : s->max_ctx;
     cudaStream_t st = s->m->e->stream;
     int n = 0;
     switch (which) {
@@ -478,7 +485,7 @@ static int enqueue_graph_body(b2_session *s, int which) {
     case G_PREFILL_LAST:
     case G_FORCED:
         k_load_prompt<<<1, 1, 0, st>>>(s->state, s->d_prompt); n++;
-        n += enqueue_forward(s, which != G_PREFILL_BODY);
+        n += enqueue_forward(s, which != G_PREFILL_BODY, attn_ctx);
         if (which == G_FORCED) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
         k_advance<<<1, 1, 0, st>>>(s->state, which == G_FORCED ? 1 : 0); n++;
         break;
@@ -487,7 +494,7 @@ static int enqueue_graph_body(b2_session *s, int which) {
         if (which == G_DECODE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
         launch_argmax_partials(s->pmax, s->pidx, s->head_grid, s->d_sampled, st); n++;
         k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
-        n += enqueue_forward(s, true);
+        n += enqueue_forward(s, true, attn_ctx);
         k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
         break;
     }
@@ -496,30 +503,34 @@ static int enqueue_graph_body(b2_session *s, int which) {
 
 static void drop_graphs(b2_session *s) {
     for (int g = 0; g < G_COUNT; ++g)
-        if (s->graphs[g]) { cudaGraphExecDestroy(s->graphs[g]); s->graphs[g] = nullptr; }
+        for (int v = 0; v < 2; ++v)
+            if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
 }
 
-// run graph `which` `times` times (captured lazily; plain launches when B2_NO_GRAPH=1)
-static int run_graph(b2_session *s, int which, int times) {
+// run graph `which` for `times` consecutive positions starting at `pos0` (captured lazily; plain launches when B2_NO_GRAPH=1).
+// Positions below ATTN_SHORT_CTX use the variant whose attention runs one CTA per head.
+static int run_graph(b2_session *s, int which, int times, int pos0) {
     cudaStream_t st = s->m->e->stream;
-    if (!s->use_graphs) {
-        for (int i = 0; i < times; ++i) s->graph_launches[which] = enqueue_graph_body(s, which);
-        B2_CUDA(cudaGetLastError());
-        s->stats.kernel_launches += (uint64_t)times * s->graph_launches[which];
-        return B2_OK;
+    for (int i = 0; i < times; ++i) {
+        const int v = (pos0 + i) < ATTN_SHORT_CTX ? 0 : 1;
+        if (!s->use_graphs) {
+            s->graph_launches[which][v] = enqueue_graph_body(s, which, v);
+            B2_CUDA(cudaGetLastError());
+        } else {
+            if (!s->graphs[which][v]) {
+                cudaGraph_t g = nullptr;
+                B2_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                s->graph_launches[which][v] = enqueue_graph_body(s, which, v);
+                cudaError_t e1 = cudaStreamEndCapture(st, &g);
+                if (e1 != cudaSuccess) { b2_set_error("graph capture failed: %s", cudaGetErrorString(e1)); return B2_ECUDA; }
+                cudaError_t e2 = cudaGraphInstantiate(&s->graphs[which][v], g, 0);
+                cudaGraphDestroy(g);
+                if (e2 != cudaSuccess) { b2_set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return B2_ECUDA; }
+            }
+            B2_CUDA(cudaGraphLaunch(s->graphs[which][v], st));
+        }
+        s->stats.kernel_launches += (uint64_t)s->graph_launches[which][v];
     }
-    if (!s->graphs[which]) {
-        cudaGraph_t g = nullptr;
-        B2_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        s->graph_launches[which] = enqueue_graph_body(s, which);
-        cudaError_t e1 = cudaStreamEndCapture(st, &g);
-        if (e1 != cudaSuccess) { b2_set_error("graph capture failed: %s", cudaGetErrorString(e1)); return B2_ECUDA; }
-        cudaError_t e2 = cudaGraphInstantiate(&s->graphs[which], g, 0);
-        cudaGraphDestroy(g);
-        if (e2 != cudaSuccess) { b2_set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return B2_ECUDA; }
-    }
-    for (int i = 0; i < times; ++i) B2_CUDA(cudaGraphLaunch(s->graphs[which], st));
-    s->stats.kernel_launches += (uint64_t)times * s->graph_launches[which];
     return B2_OK;
 }
 
@@ -561,6 +572,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, &s->act_h, a3_bytes(I)))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->pmax, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->pidx, 1024 * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->xsq, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(c.n_heads, hd)))) break;
         if ((rc = dev_alloc(s->allocs, &s->argmax_scratch, argmax_scratch_bytes()))) break;
     } while (0);
@@ -628,7 +640,8 @@ static int ensure_log(b2_session *s, uint64_t floats) {
     s->logits_log_cap = 0;
     // graphs bake the log pointer: re-capture the ones that use it
     for (int g : {G_DECODE_LOG, G_FORCED})
-        if (s->graphs[g]) { cudaGraphExecDestroy(s->graphs[g]); s->graphs[g] = nullptr; }
+        for (int v = 0; v < 2; ++v)
+            if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
     cudaError_t e = cudaMalloc((void **)&s->logits_log, floats * 4);
     if (e != cudaSuccess) { b2_set_error("logits log: cudaMalloc(%llu) failed: %s", (unsigned long long)floats * 4, cudaGetErrorString(e)); return B2_ENOMEM; }
     s->logits_log_cap = floats;
@@ -665,8 +678,8 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1));
-    B2_TRY(run_graph(s, G_PREFILL_LAST, 1));
+    if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1, s->host_pos));
+    B2_TRY(run_graph(s, G_PREFILL_LAST, 1, s->host_pos + n - 1));
     B2_CUDA(cudaEventRecord(s->ev1, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits, (size_t)V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
@@ -692,7 +705,7 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
     if (logits_out) B2_TRY(ensure_log(s, (uint64_t)n_steps * V));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps));
+    B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps, s->host_pos));
     B2_CUDA(cudaEventRecord(s->ev1, st));
     B2_CUDA(cudaMemcpyAsync(out_tokens, s->d_out_tokens, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n_steps * V * 4, cudaMemcpyDeviceToHost, st));
@@ -717,7 +730,7 @@ extern "C" int b2_forward_tokens(b2_session *s, const int32_t *tokens, int n, fl
     B2_TRY(ensure_log(s, (uint64_t)n * V));
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
-    B2_TRY(run_graph(s, G_FORCED, n));
+    B2_TRY(run_graph(s, G_FORCED, n, s->host_pos));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n * V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
     s->host_pos += n;

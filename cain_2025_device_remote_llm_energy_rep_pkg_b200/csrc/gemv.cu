@@ -115,8 +115,8 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
 #define GEMV_MAXT 2                          // K-outer order: tiles per CTA whose accumulators stay in registers
 #define MMA_MAGIC 0x4B400000                 // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
 #define MMA_MAGIC_F 12582912.0f
-#define L2_PREFETCH_BYTES (128 * 1024)       // of the next kernel's weights, per CTA
-#define L2_WINDOW_BYTES (256 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
+#define L2_PREFETCH_BYTES (512 * 1024)       // of the next kernel's weights, per CTA (its whole share for every per-layer matrix)
+#define L2_WINDOW_BYTES (128 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
 #define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
 
 struct GemvArgs {
@@ -138,6 +138,9 @@ struct GemvArgs {
     int act;
     float *pmax;             // OUT_LOGITS: per-CTA arg-max partials
     int *pidx;
+    const float *xsq_in;     // IN_NORM: partial sums of x^2 left by the kernel that produced x (fixed order => deterministic)
+    int xsq_n;
+    float *xsq_out;          // OUT_RES: this CTA's partial sum of squares of the rows it wrote, at [blockIdx.x]
     const uint8_t *pf_ptr;   // weights the NEXT kernel will stream: each CTA pulls the head of its share into L2
     uint64_t pf_total;
     long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
@@ -199,58 +202,42 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
 // shared memory map (bytes): [red GEMV_RB*16*16*4*4 = 32768][hbuf GEMV_RB*8 floats + 64 scratch = 512][A3 of the input nbp*100]
 #define GEMV_FIXED_SMEM (GEMV_RB * 4096 + 512)
 
-// ---- Input staging.  The previous kernel's output reaches shared memory through cp.async.bulk (the TMA path): ordinary loads
-// would queue behind the ~70 KB of weight loads this SM already has in flight.  Shared memory map of the input area:
-//   [A3 image nbp*100][staging: fp32 vector n_in*4][IN_NORM only: norm weights n_in*4]
-// One thread issues the copies and everybody waits on the mbarrier; then the vector is normalised (IN_NORM, op order of
-// oracle/model.py:_norm) and put on the activation grid: a 32-element block is 8 consecutive threads' float4s, so the block
-// maximum is three shuffles and a thread stores one 32-bit word per digit plane.
+// ---- Input staging.  What the previous kernel wrote reaches shared memory through cp.async.bulk (the TMA path): an ordinary load
+// would complete only after the ~70 KB of weight loads this SM already has in flight (the L1 load queue is a FIFO).  Thread 0 issues
+// the copies after griddepcontrol.wait; every thread waits on the mbarrier, no CTA barrier.  Then the work is warp-local: warp w only
+// ever multiplies block-group column w of every chunk, i.e. the input elements [128*kbg, 128*kbg+128) with kbg = ck*16 + w.  It
+// normalises exactly those (IN_NORM: the sum of squares arrives as per-CTA partials from the producer of x, added in a fixed order;
+// op order of oracle/model.py:_norm), puts them on the activation grid (a 32-element block is 8 consecutive lanes: three shuffles
+// for the block maximum) and writes its own block-groups of the shared-memory activation image.
+// Shared memory of the input area: [A3 image nbp*100][staging: fp32 vector n_in*4][xsq partials 1 KB]
 template <int IN>
-__device__ __noinline__ void stage_input_smem(const GemvArgs &a, uint8_t *sact, float *scratch, uint64_t *bar) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (IN == IN_ACT) {
-        if (tid == 0) {
-            const uint32_t bytes = (uint32_t)a.nbp * 100;
-            mbar_expect_tx(bar, bytes);
-            bulk_g2s(sact, a.act_in, bytes, bar);
-        }
+__device__ __forceinline__ void stage_warp_input(const GemvArgs &a, uint8_t *sact, uint64_t *bar, int cpt, int warp, int lane,
+                                                 const float4 (&wn)[2]) {
+    if (IN == IN_ACT) {   // already on the grid: the image itself was copied
         mbar_wait(bar, 0);
         return;
     }
-    float *sx = (float *)(sact + (size_t)a.nbp * 100);
-    float *sw = sx + a.n_in;
+    const float *sx = (const float *)(sact + (size_t)a.nbp * 100);
+    const float *sq = sx + a.n_in;
     float *sscale = (float *)(sact + (size_t)a.nbp * 96);
-    if (tid == 0) {
-        const uint32_t bytes = (uint32_t)a.n_in * 4;
-        mbar_expect_tx(bar, bytes);
-        bulk_g2s(sx, IN == IN_NORM ? (const void *)a.x : (const void *)a.act_in, bytes, bar);
-    }
     mbar_wait(bar, 0);
-    const int n4 = a.n_in >> 2;
     float r = 1.0f;
     if (IN == IN_NORM) {
         float ss = 0.f;
-        for (int q = tid; q < n4; q += GEMV_THREADS) {
-            const float4 v = ((const float4 *)sx)[q];
-            ss = fmaf(v.x, v.x, ss); ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
-        }
+        for (int i = lane; i < a.xsq_n; i += 32) ss += sq[i];
         ss = warp_sum(ss);
-        if (lane == 0) scratch[warp] = ss;
-        __syncthreads();
-        float tot = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
-        r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)a.n_in), a.eps)));
-        mbar_wait(bar + 1, 0);   // the norm weights (requested before griddepcontrol.wait)
+        r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)a.n_in), a.eps)));
     }
-    const int nq = a.nbp << 3;   // float4 slots including the zero padding blocks
-    for (int q0 = 0; q0 < nq; q0 += GEMV_THREADS) {
-        const int q = q0 + tid;  // float4 index; block = q / 8, word-in-block = q % 8
+    const int n4 = a.n_in >> 2;
+    for (int ck = 0; ck < cpt; ++ck) {
+        const int kbg = ck * (KC / 4) + warp;
+        if (kbg * 4 >= a.nbp) break;
+        const int q = kbg * 32 + lane;   // float4 index: block = q / 8, word-in-block = q % 8
         float yv[4] = {0.f, 0.f, 0.f, 0.f};
         if (q < n4) {
             const float4 v = ((const float4 *)sx)[q];
             if (IN == IN_NORM) {
-                const float4 w = ((const float4 *)sw)[q];
+                const float4 w = ck < 2 ? wn[ck] : __ldg((const float4 *)a.norm_w + q);
                 const float xs[4] = {v.x, v.y, v.z, v.w}, ws[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) yv[e] = __fmul_rn(__fmul_rn(xs[e], r), a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e]);
@@ -262,28 +249,26 @@ __device__ __noinline__ void stage_input_smem(const GemvArgs &a, uint8_t *sact, 
         m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
         m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
         m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
-        if (q < nq) {
-            const int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
-            const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
-            const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
-            uint32_t w0 = 0, w1 = 0, w2 = 0;
+        const int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
+        const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
+        const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
+        uint32_t w0 = 0, w1 = 0, w2 = 0;
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                int d0, d1, d2;
-                act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
-                w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
-                w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
-                w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
-            }
-            const int b = q >> 3, k = q & 7;                // elements 4k..4k+3 of block b
-            uint8_t *dst = sact + a3_off(b, 0, 4 * k);
-            *(uint32_t *)dst = w0;
-            *(uint32_t *)(dst + 128) = w1;
-            *(uint32_t *)(dst + 256) = w2;
-            if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
+        for (int e = 0; e < 4; ++e) {
+            int d0, d1, d2;
+            act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
+            w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
+            w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
+            w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
         }
+        const int b = q >> 3, k = q & 7;                    // elements 4k..4k+3 of block b
+        uint8_t *dst = sact + a3_off(b, 0, 4 * k);
+        *(uint32_t *)dst = w0;
+        *(uint32_t *)(dst + 128) = w1;
+        *(uint32_t *)(dst + 256) = w2;
+        if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
     }
-    __syncthreads();
+    __syncwarp();
 }
 
 // ---- reduction + epilogue of the `batch_n` finished tiles parked in shared memory (called by all threads).
@@ -291,7 +276,8 @@ __device__ __noinline__ void stage_input_smem(const GemvArgs &a, uint8_t *sact, 
 // Two CTA-wide barriers per GEMV_RB tiles instead of one per tile: the weight streams of the sixteen warps are not
 // re-synchronised on memory latency every other piece.
 template <int OUT>
-__device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i) {
+__device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i,
+                                         float &sumsq) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __syncthreads();
     if (warp < batch_n) {
@@ -315,7 +301,11 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *h
         if (OUT == OUT_BIAS) {
             if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res ? yv + a.bias_or_res[row] : yv;
         } else if (OUT == OUT_RES) {
-            if (lane < 16 && row < a.rows) a.y[row] = __ldcg(a.bias_or_res + row) + yv;
+            if (lane < 16 && row < a.rows) {
+                const float xn = __ldcg(a.bias_or_res + row) + yv;
+                a.y[row] = xn;
+                sumsq = fmaf(xn, xn, sumsq);
+            }
         } else if (OUT == OUT_LOGITS) {
             if (lane < 16 && row < a.rows) {
                 a.y[row] = yv;
@@ -337,22 +327,15 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
     float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
     float *scratch = hbuf + GEMV_RB * 8;
-    uint64_t *bars = (uint64_t *)(hbuf + 96);                                   // [0] input vector, [1] norm weights
-    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector (+ fp32 staging)
+    uint64_t *bar = (uint64_t *)(hbuf + 96);                                    // completion of the input copies
+    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector (+ fp32 staging, partials)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
     if (tid == 0) {
         pdl_launch_dependents();
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
+        mbar_init(bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        if (IN == IN_NORM) {   // the norm weights are immutable: request them before waiting for the previous kernel
-            float *sw = (float *)(sact + (size_t)a.nbp * 100) + a.n_in;
-            mbar_expect_tx(&bars[1], (uint32_t)a.n_in * 4);
-            bulk_g2s(sw, a.norm_w, (uint32_t)a.n_in * 4, &bars[1]);
-        }
     }
-    __syncthreads();
     auto stamp = [&](int k) {
         if (a.dbg && tid == 0) {
             long long tt;
@@ -364,7 +347,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
 
     // contiguous, aligned share of the tiles
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
-    const int u0 = (int)((int64_t)units * blockIdx.x / gridDim.x), u1 = (int)((int64_t)units * (blockIdx.x + 1) / gridDim.x);
+    const int u0 = (int)(((uint32_t)units * blockIdx.x) / gridDim.x), u1 = (int)(((uint32_t)units * (blockIdx.x + 1)) / gridDim.x);
     const int t0 = u0 * a.tile_align, t1 = min(a.n_tiles, u1 * a.tile_align);
     const int nt = t1 - t0;
     const int cpt = (a.nbp + KC - 1) / KC;                                      // chunks per tile
@@ -390,13 +373,49 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
             b.as.x *= 0.0625f; b.as.y *= 0.0625f; b.as.z *= 0.0625f; b.as.w *= 0.0625f;   // the 1/16 of the nibble trick
         }
     };
+    // pull this CTA's share of the next kernel's weights into L2 (lane 0 of every warp, 16 KB per instruction)
+    auto prefetch_next = [&]() {
+        if (lane == 0 && a.pf_ptr) {
+            const uint64_t share = (a.pf_total / gridDim.x) & ~(uint64_t)127;
+            const uint8_t *p0 = a.pf_ptr + share * blockIdx.x;
+            const uint64_t n = share < L2_PREFETCH_BYTES ? share : L2_PREFETCH_BYTES;
+            for (uint64_t o = (uint64_t)warp * 16384; o + 16384 <= n; o += GEMV_CWARPS * 16384) l2_prefetch(p0 + o, 16384);
+        }
+    };
+
+    float sumsq = 0.f;
     auto stage_input = [&]() {
         stamp(1);
-        pdl_wait();
+        // the norm weights of this warp's columns are immutable: fetch them before waiting for the previous kernel
+        float4 wn[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+        if (IN == IN_NORM) {
+#pragma unroll
+            for (int ck = 0; ck < 2; ++ck) {
+                const int q = (ck * (KC / 4) + warp) * 32 + lane;
+                if (ck < cpt && q < (a.n_in >> 2)) wn[ck] = __ldg((const float4 *)a.norm_w + q);
+            }
+        }
+        __syncthreads();   // everybody has issued its first weight loads; the mbarrier thread 0 initialised is visible
+        if (tid == 0) {
+            pdl_wait();    // the copies below read what the previous kernel wrote
+            if (IN == IN_ACT) {
+                const uint32_t bytes = (uint32_t)a.nbp * 100;
+                mbar_expect_tx(bar, bytes);
+                bulk_g2s(sact, a.act_in, bytes, bar);
+            } else {
+                float *sx = (float *)(sact + (size_t)a.nbp * 100);
+                const uint32_t bytes = (uint32_t)a.n_in * 4;
+                const uint32_t qbytes = IN == IN_NORM ? (uint32_t)((a.xsq_n + 3) & ~3) * 4 : 0;
+                mbar_expect_tx(bar, bytes + qbytes);
+                bulk_g2s(sx, IN == IN_NORM ? (const void *)a.x : (const void *)a.act_in, bytes, bar);
+                if (qbytes) bulk_g2s(sx + a.n_in, a.xsq_in, qbytes, bar);
+            }
+        }
         stamp(2);   // everything from here reads what the previous kernel wrote (ld.global.cg: under programmatic
                       // dependent launch a CTA of that kernel may have shared this SM's L1)
-        stage_input_smem<IN>(a, sact, scratch, bars);
+        stage_warp_input<IN>(a, sact, bar, cpt, warp, lane, wn);
         stamp(3);
+        prefetch_next();   // the next kernel's weights start flowing HBM -> L2 while this kernel works through its own
     };
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
@@ -409,21 +428,11 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == GEMV_RB) {
-            flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i);
+            flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
             batch_first += batch_n;
             batch_n = 0;
         }
     };
-    // when the CTA's last piece has been requested, pull the head of the next kernel's weights into L2
-    auto prefetch_next = [&]() {
-        if (tid == 0 && a.pf_ptr) {
-            const uint64_t share = (a.pf_total / gridDim.x) & ~(uint64_t)127;
-            const uint8_t *p0 = a.pf_ptr + share * blockIdx.x;
-            const uint64_t n = share < L2_PREFETCH_BYTES ? share : L2_PREFETCH_BYTES;
-            for (uint64_t o = 0; o + 16384 <= n; o += 16384) l2_prefetch(p0 + o, 16384);
-        }
-    };
-
     WPiece buf0, buf1, buf2, buf3;      // GEMV_DEPTH = 4 pieces in flight per warp
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     if (!a.k_outer) {
@@ -434,12 +443,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
         int l_rem = nt * cpt;            // pieces not requested yet
         // L2 prefetch cursor (thread 0): cp.async.bulk.prefetch.L2 keeps the CTA's contiguous byte range L2_WINDOW_BYTES ahead of
         // the register loads, so those hit L2 (short latency) while HBM streams at its own pace from the first cycle
-        const uint8_t *pf = base, *pf_end = base + (size_t)nt * tile_bytes;
+        // (lane 0 of warp w owns the 16 KB blocks w, w+16, ... of the range: one instruction per warp per 256 KB of progress)
+        const uint8_t *pf = base + (size_t)warp * 16384, *pf_end = base + (size_t)nt * tile_bytes;
         auto l2_window = [&]() {
-            if (tid == 0) {
-                const uint8_t *lim = lp + L2_WINDOW_BYTES < pf_end ? lp + L2_WINDOW_BYTES : pf_end;
-                while (pf + 16384 <= lim) { l2_prefetch(pf, 16384); pf += 16384; }
-                if (lim == pf_end && pf < pf_end) { l2_prefetch(pf, (uint32_t)(pf_end - pf) & ~15u); pf = pf_end; }
+            if (lane == 0 && pf < pf_end && pf < lp + L2_WINDOW_BYTES) {
+                const size_t left = (size_t)(pf_end - pf);
+                l2_prefetch(pf, left < 16384 ? (uint32_t)left & ~15u : 16384u);
+                pf += GEMV_CWARPS * 16384;
             }
         };
         l2_window();
@@ -469,7 +479,6 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
                     park(acc);
                 }
                 l2_window();
-                if (l_rem == 0) { prefetch_next(); l_rem = -1; }
             }
         } else {
             load_last(buf0); load_last(buf1); load_last(buf2); load_last(buf3);
@@ -484,10 +493,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
                 if (rem > 2) { if (act_last) bg_mma(buf2, bf0, acc); load_last(buf2); park(acc); }
                 if (rem > 3) { if (act_last) bg_mma(buf3, bf0, acc); load_last(buf3); park(acc); }
                 l2_window();
-                if (l_rem == 0) { prefetch_next(); l_rem = -1; }
             }
         }
-        if (l_rem == 0) prefetch_next();
     } else {
         // ================= chunks outermost (K longer than two chunks; a CTA owns one or two tiles whose accumulators stay in
         // registers).  A step is chunk ck of both tiles; the B fragments of a step are read from shared memory one step ahead.
@@ -505,8 +512,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
                 ++l_ck;
             }
         };
-        if (tid == 0) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once
-            for (uint32_t o = 0; o + 16384 <= (uint32_t)nt * tile_bytes; o += 16384) l2_prefetch(base + o, 16384);
+        if (lane == 0) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
+            for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
         }
         load_step(buf0, buf1);
         load_step(buf2, buf3);
@@ -528,14 +535,25 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
                 }
                 load_step(buf2, buf3);
             }
-            if (l_ck == cpt) { prefetch_next(); l_ck = cpt + 1; }
         }
         if (nt > 0) park(acc);
         if (two) park(acc1);
     }
     stamp(4);
-    if (batch_n > 0) flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i);
+    if (batch_n > 0) flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
     stamp(5);
+    if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
+        sumsq = warp_sum(sumsq);
+        __syncthreads();
+        if (lane == 0) scratch[warp] = sumsq;
+        __syncthreads();
+        if (tid == 0) {
+            float tot = 0.f;
+#pragma unroll
+            for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
+            a.xsq_out[blockIdx.x] = tot;
+        }
+    }
     if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima
         float *sv = scratch;
         int *si = (int *)(scratch + 16);
@@ -604,14 +622,16 @@ static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStre
 // next_w / next_bytes: the packed matrix the following kernel streams (L2 prefetch hint), or nullptr.
 cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                         float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
-                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, cudaStream_t st, bool pdl) {
+                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
+                        float *xsq_out, cudaStream_t st, bool pdl) {
     GemvArgs a = {};
+    a.xsq_in = xsq_in; a.xsq_n = xsq_n; a.xsq_out = xsq_out;
     a.w = (const uint8_t *)d_packed;
     a.rows = (int)rows;
     a.nbp = (int)nblocks_padded(cols);
     a.n_tiles = (int)ntiles(rows);
     a.tile_align = 1;
-    if (in_mode == IN_NORM && cols > GEMV_NORM_MAX) return cudaErrorInvalidValue;
+    if (in_mode == IN_NORM && (!xsq_in || xsq_n <= 0)) return cudaErrorInvalidValue;
     a.x = x; a.norm_w = norm_w; a.eps = eps; a.plus_one = plus_one; a.n_in = (int)cols;
     a.act_in = (const uint8_t *)act_in;
     a.y = y; a.bias_or_res = bias_or_res; a.act_out = (uint8_t *)act_out; a.n_out_act = (int)(rows / 2); a.act = act;
@@ -624,7 +644,7 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     int max_tiles = ((units + grid - 1) / grid) * a.tile_align;
     a.k_outer = cpt > 2;
     if (grid_out) *grid_out = grid;
-    size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 * (in_mode == IN_NORM ? 2 : 1)) + 128;
+    size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
 #define CASE(I, O) if (in_mode == I && out_mode == O) return launch_one<I, O>(aa, grid, smem, st, pdl)
     if (!a.k_outer || max_tiles <= GEMV_MAXT) {
@@ -646,6 +666,7 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
         aa.rows = (int)(rows - (int64_t)tbeg * TILE_ROWS < (int64_t)tn * TILE_ROWS ? rows - (int64_t)tbeg * TILE_ROWS : (int64_t)tn * TILE_ROWS);
         aa.y = y + (int64_t)tbeg * TILE_ROWS;
         aa.bias_or_res = bias_or_res ? bias_or_res + (int64_t)tbeg * TILE_ROWS : nullptr;
+        aa.xsq_out = nullptr;
         grid = gemv_grid(tn, 1);
         cudaError_t e = cudaErrorInvalidValue;
         if (in_mode == IN_NORM && out_mode == OUT_BIAS) e = launch_one<IN_NORM, OUT_BIAS>(aa, grid, smem, st, pdl);
@@ -661,14 +682,42 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
 }
 
 // ------------------------------------------------------------------------------------------ embedding row
-__global__ void k_embed_row(const uint8_t *__restrict__ w, int64_t nbp, int n, const int *__restrict__ token, float scale, float *__restrict__ x) {
-    pdl_wait();
+// x = embedding row of the current token (gemma: * sqrt(H)); also leaves sum(x^2) for the first RMSNorm.  One block.
+__global__ void __launch_bounds__(1024) k_embed_row(const uint8_t *__restrict__ w, int64_t nbp, int n, const int *__restrict__ token, float scale,
+                                                    float *__restrict__ x, float *__restrict__ xsq) {
+    __shared__ float red[32];
     const int64_t row = __ldcg(token);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
         float v = packed_elem(w, row, i, nbp);
-        x[i] = scale != 1.0f ? v * scale : v;
+        if (scale != 1.0f) v = v * scale;
+        x[i] = v;
+        ss = fmaf(v, v, ss);
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float tv = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+        tv = warp_sum(tv);
+        if (threadIdx.x == 0) xsq[0] = tv;
     }
 }
-void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st) {
-    k_embed_row<<<(unsigned)((cols + 255) / 256), 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x);
+void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st) {
+    k_embed_row<<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
 }
+// sum of squares of an f32 vector into xsq[0] (op-level entry points that run the fused RMSNorm on a caller's vector)
+__global__ void __launch_bounds__(1024) k_sumsq(const float *__restrict__ x, int n, float *__restrict__ xsq) {
+    __shared__ float red[32];
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { const float v = x[i]; ss = fmaf(v, v, ss); }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float tv = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+        tv = warp_sum(tv);
+        if (threadIdx.x == 0) xsq[0] = tv;
+    }
+}
+void launch_sumsq(const float *d_x, int64_t n, float *d_xsq, cudaStream_t st) { k_sumsq<<<1, 1024, 0, st>>>(d_x, (int)n, d_xsq); }

@@ -4,6 +4,7 @@
 #include "common.cuh"
 
 #define ATTN_NSPLIT 8       // KV splits per head in the decode attention kernel
+#define ATTN_SHORT_CTX 96   // up to this many positions the fused attention runs one CTA per head (no cluster)
 #define ARGMAX_BLOCKS 128   // stage-1 blocks of the greedy sampler
 
 // device-resident request state: lets a captured CUDA graph be replayed for every token
@@ -25,8 +26,10 @@ enum { GEMV_OUT_BIAS = 0, GEMV_OUT_RES = 1, GEMV_OUT_ACTMUL = 2, GEMV_OUT_LOGITS
 int gemv_grid(int n_tiles, int tile_align);
 cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                         float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
-                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, cudaStream_t st, bool pdl);
-void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, cudaStream_t st);
+                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
+                        float *xsq_out, cudaStream_t st, bool pdl);
+void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);
+void launch_sumsq(const float *d_x, int64_t n, float *d_xsq, cudaStream_t st);
 
 // small stages (kernels.cu)
 void launch_quant_act(const float *d_x, int64_t n, void *d_act, cudaStream_t st);

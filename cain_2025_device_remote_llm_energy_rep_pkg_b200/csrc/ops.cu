@@ -64,7 +64,7 @@ extern "C" int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t 
     B2_CHECK(mode != 2 || rows % 2 == 0, B2_EINVAL, "b2_op_gemv: mode 2 needs an even row count (gate/up pairs)");
     if (rows == 0) return B2_OK;
     cudaError_t e = launch_gemv(GEMV_IN_ACT, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_act, d_y, d_bias_or_res, nullptr, act,
-                                nullptr, nullptr, nullptr, nullptr, 0, 0, false);
+                                nullptr, nullptr, nullptr, nullptr, 0, nullptr, 0, nullptr, 0, false);
     B2_CUDA(e);
     B2_CUDA(cudaGetLastError());
     return B2_OK;
@@ -78,7 +78,7 @@ extern "C" int b2_op_gemv_f32(int type, const void *d_packed, int64_t rows, int6
     B2_CHECK(d_packed && d_x && d_y && rows > 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_gemv_f32: bad arguments");
     B2_CHECK(mode == 0 || (mode == 1 && d_bias_or_res), B2_EINVAL, "b2_op_gemv_f32: mode must be 0, or 1 with a residual vector");
     cudaError_t e = launch_gemv(GEMV_IN_F32, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_x, d_y, d_bias_or_res, nullptr, 0,
-                                nullptr, nullptr, nullptr, nullptr, 0, 0, false);
+                                nullptr, nullptr, nullptr, nullptr, 0, nullptr, 0, nullptr, 0, false);
     B2_CHECK(e != cudaErrorInvalidValue, B2_EINVAL, "b2_op_gemv_f32: cols %lld too long for the shared-memory staging", (long long)cols);
     B2_CUDA(e);
     B2_CUDA(cudaGetLastError());
@@ -98,24 +98,22 @@ extern "C" int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int
     B2_CHECK(mode != 2 || rows % 64 == 0, B2_EINVAL, "b2_op_norm_gemv: mode 2 needs rows %% 64 == 0 (32 gate/up pairs per activation block)");
     B2_CHECK(mode != 3 || d_argmax, B2_EINVAL, "b2_op_norm_gemv: mode 3 needs d_argmax");
     void *tmp = nullptr;
-    float *pmax = nullptr;
-    int *pidx = nullptr;
-    if (mode == 3) {
-        B2_CUDA(cudaMalloc(&tmp, 8192));
-        B2_CUDA(cudaMemset(tmp, 0, 8192));
-        pmax = (float *)tmp;
-        pidx = (int *)((char *)tmp + 4096);
-    }
+    B2_CUDA(cudaMalloc(&tmp, 8192 + 16));
+    B2_CUDA(cudaMemset(tmp, 0, 8192 + 16));
+    float *pmax = (float *)tmp;
+    int *pidx = (int *)((char *)tmp + 4096);
+    float *xsq = (float *)((char *)tmp + 8192);
+    launch_sumsq(d_x, cols, xsq, 0);   // the engine gets this sum from the kernel that produced x
     int grid = 0;
     cudaError_t e = launch_gemv(GEMV_IN_NORM, mode, d_packed, rows, cols, d_x, d_norm_w, eps, plus_one, nullptr, d_y, d_bias_or_res, nullptr, act,
-                                pmax, pidx, &grid, nullptr, 0, 0, false);
+                                mode == 3 ? pmax : nullptr, mode == 3 ? pidx : nullptr, &grid, nullptr, 0, xsq, 1, nullptr, 0, false);
     if (e == cudaSuccess && mode == 3) launch_argmax_partials(pmax, pidx, grid, d_argmax, 0);
     if (e == cudaSuccess && mode == 2 && d_act_out) {   // the engine's next GEMV puts h on the grid itself; offered here for callers that want the image
         e = cudaMemsetAsync(d_act_out, 0, a3_bytes(rows / 2), 0);
         if (e == cudaSuccess) launch_quant_act(d_y, rows / 2, d_act_out, 0);
     }
-    if (e == cudaSuccess && tmp) e = cudaDeviceSynchronize();
-    if (tmp) cudaFree(tmp);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaFree(tmp);
     B2_CUDA(e);
     B2_CUDA(cudaGetLastError());
     return B2_OK;

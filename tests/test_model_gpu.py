@@ -42,6 +42,20 @@ def test_tiny_arch_logits_and_greedy_256(pk, gpu_engine, key):
     assert st["prompt_eval_count"] == len(PROMPT) and st["eval_count"] == 256 and st["kernel_launches"] > 0
 
 
+def test_attention_variant_switch_across_the_short_context_limit(pk, gpu_engine):
+    """Positions below ATTN_SHORT_CTX (96) use the one-CTA-per-head attention, later ones the cluster kernel: the greedy stream must not
+    notice (oracle comparison across the boundary)."""
+    archs, engine = pk
+    a = archs.TINY["llama3.1:8b"]
+    tensors = engine.host_random_tensors(a, seed=5)
+    model = engine.Model.from_tensors(gpu_engine, a, tensors, max_ctx=160)
+    om = OracleModel(OTINY["llama3.1:8b"], tensors)
+    prompt = [(7 * i + 3) % a.V for i in range(80)]
+    got = model.session(160).generate_greedy(prompt, 40)
+    want = om.session(160).generate_greedy(prompt, 40)
+    assert list(map(int, got)) == want
+
+
 def test_device_random_init_equals_host_blobs(pk, gpu_engine):
     archs, engine = pk
     for key in ("qwen2:1.5b", "gemma:7b", "llama3.1:8b"):
