@@ -15,6 +15,7 @@
 #include "kernels.cuh"
 #include "layout.cuh"
 #include "randinit.cuh"
+#include <stdlib.h>
 
 // ------------------------------------------------------------------------------------------ PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -143,6 +144,8 @@ struct GemvArgs {
     float *xsq_out;          // OUT_RES: this CTA's partial sum of squares of the rows it wrote, at [blockIdx.x]
     const uint8_t *pf_ptr;   // weights the NEXT kernel will stream: each CTA pulls the head of its share into L2
     uint64_t pf_total;
+    uint32_t l2_window;      // bytes the CTA's L2 prefetch cursor runs ahead of its register loads (0: off)
+    uint32_t pf_bytes;       // bytes of the next kernel's weights each CTA pulls into L2 (0: off)
     long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
 };
 enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2 };
@@ -378,7 +381,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
         if (lane == 0 && a.pf_ptr) {
             const uint64_t share = (a.pf_total / gridDim.x) & ~(uint64_t)127;
             const uint8_t *p0 = a.pf_ptr + share * blockIdx.x;
-            const uint64_t n = share < L2_PREFETCH_BYTES ? share : L2_PREFETCH_BYTES;
+            const uint64_t n = share < a.pf_bytes ? share : a.pf_bytes;
             for (uint64_t o = (uint64_t)warp * 16384; o + 16384 <= n; o += GEMV_CWARPS * 16384) l2_prefetch(p0 + o, 16384);
         }
     };
@@ -446,7 +449,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
         // (lane 0 of warp w owns the 16 KB blocks w, w+16, ... of the range: one instruction per warp per 256 KB of progress)
         const uint8_t *pf = base + (size_t)warp * 16384, *pf_end = base + (size_t)nt * tile_bytes;
         auto l2_window = [&]() {
-            if (lane == 0 && pf < pf_end && pf < lp + L2_WINDOW_BYTES) {
+            if (lane == 0 && pf < pf_end && pf < lp + a.l2_window) {
                 const size_t left = (size_t)(pf_end - pf);
                 l2_prefetch(pf, left < 16384 ? (uint32_t)left & ~15u : 16384u);
                 pf += GEMV_CWARPS * 16384;
@@ -512,7 +515,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
                 ++l_ck;
             }
         };
-        if (lane == 0) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
+        if (lane == 0 && a.l2_window) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
             for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
         }
         load_step(buf0, buf1);
@@ -637,6 +640,14 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     a.y = y; a.bias_or_res = bias_or_res; a.act_out = (uint8_t *)act_out; a.n_out_act = (int)(rows / 2); a.act = act;
     a.pmax = pmax; a.pidx = pidx;
     a.pf_ptr = (const uint8_t *)next_w; a.pf_total = next_bytes;
+    static int env_win = -1, env_pf = -1;   // tuning knobs: B2_L2_WINDOW / B2_PF_NEXT (bytes)
+    if (env_win < 0) {
+        const char *e1 = getenv("B2_L2_WINDOW"), *e2 = getenv("B2_PF_NEXT");
+        env_win = e1 ? atoi(e1) : L2_WINDOW_BYTES;
+        env_pf = e2 ? atoi(e2) : L2_PREFETCH_BYTES;
+    }
+    a.l2_window = (uint32_t)env_win;
+    a.pf_bytes = (uint32_t)env_pf;
     a.dbg = g_gemv_dbg ? g_gemv_dbg + (size_t)(g_gemv_dbg_next++ % g_gemv_dbg_slots) * 148 * 8 : nullptr;
     int grid = gemv_grid(a.n_tiles, a.tile_align);
     const int cpt = (a.nbp + KC - 1) / KC;
