@@ -116,7 +116,7 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
 #define GEMV_MAXT 2                          // K-outer order: tiles per CTA whose accumulators stay in registers
 #define MMA_MAGIC 0x4B400000                 // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
 #define MMA_MAGIC_F 12582912.0f
-#define L2_PREFETCH_BYTES (512 * 1024)       // of the next kernel's weights, per CTA (its whole share for every per-layer matrix)
+#define L2_PREFETCH_BYTES 0                  // of the NEXT kernel's weights, per CTA: off (measured: no gain once the own-stream window is on; B2_PF_NEXT re-enables)
 #define L2_WINDOW_BYTES (128 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
 #define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
 
