@@ -78,6 +78,7 @@ SIGNATURES = {
     "b2_op_attn_decode": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, i32, vp]),
     "b2_op_attn_fused": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp]),
     "b2_op_argmax": (i32, [vp, i64, vp]),
+    "b2_op_argmax_noalloc": (i32, [vp, i64, vp]),
     "b2_op_sample_topk": (i32, [vp, i64, i32, f32, f32, f32, vp]),
 }
 

@@ -180,6 +180,16 @@ int b2_op_attn_fused(const float *d_qkv, int nh, int nkv, int hd, int pos, const
                      void *d_vcache, const int32_t *d_page_table, int page_tokens, int max_ctx, float *d_out, void *d_act_out);
 /* Greedy sampler: index of the maximum (lowest index on ties) of f32[n]. */
 int b2_op_argmax(const float *d_logits, int64_t n, int32_t *d_out_index);
+/* No counterpart in the reference.  Same result as b2_op_argmax, for callers that must not allocate device memory: the
+ * sampling thread of a server while a measured request is decoding (cudaMalloc/cudaFree stall the whole device and would
+ * end up in the recorded time and energy) and processes that have already filled the card with weights and KV cache.
+ * The scratch is a 2 KB array inside the library image, present on every GPU that loads the library until exit; the
+ * call uses no cudaMalloc, cudaFree or allocating library routine.  n may be at most B2_ARGMAX_NOALLOC_MAX_N; larger
+ * inputs are refused with B2_EINVAL.  The first call on a device looks the array up (cudaGetSymbolAddress, with that
+ * device current): make it before any stream capture begins.  All calls on a device share the array: calls whose GPU
+ * work overlaps (different streams or threads) race; this entry point runs on the default stream, asynchronously. */
+#define B2_ARGMAX_NOALLOC_MAX_N 1048576
+int b2_op_argmax_noalloc(const float *d_logits, int64_t n, int32_t *d_out_index);
 /* Top-k / temperature / top-p sampler with a caller-supplied uniform u in [0,1). */
 int b2_op_sample_topk(const float *d_logits, int64_t n, int top_k, float temperature, float top_p, float u, int32_t *d_out_index);
 
