@@ -56,62 +56,73 @@ def prompt_tokens(n, vocab):
 
 
 # ------------------------------------------------------------------------------------------ CPU arm
+class CpuSample:
+    """The oracle on a bounded sample of the workload: 2 real-size layers + the LM head of the named architecture, built
+    once (model load, not timed); every `run` decodes a few tokens and extrapolates the layer time to the full depth."""
+
+    def __init__(self, model_key: str, threads: int | None = None):
+        import dataclasses
+        import torch
+        from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
+        from cain_2025_device_remote_llm_energy_rep_pkg_b200.engine import host_random_tensors
+        from oracle.archs import ARCHS as OARCHS
+        from oracle.model import OracleModel
+        self.torch = torch
+        self.cores = threads or os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        self.key, self.a = model_key, ARCHS[model_key]
+        self.sub_l = min(2, self.a.L)
+        sub = dataclasses.replace(self.a, L=self.sub_l)
+        self.osub = dataclasses.replace(OARCHS[model_key], L=self.sub_l)
+        self.om = OracleModel(self.osub, host_random_tensors(sub, seed=1))
+        self.sess = self.om.session(2048)
+        self.tok = 1
+        self.om.head(self.sess.hidden(self.tok))   # first call dequantises and caches the weights
+
+    def run(self, n_tokens: int) -> dict:
+        torch = self.torch
+        if self.sess.pos + n_tokens >= self.sess.max_ctx:
+            self.sess.reset()
+        t_layers = t_head = 0.0
+        for _ in range(n_tokens):
+            t0 = time.perf_counter()
+            h = self.sess.hidden(self.tok)
+            t1 = time.perf_counter()
+            self.tok = int(torch.argmax(self.om.head(h)))
+            t2 = time.perf_counter()
+            t_layers += t1 - t0
+            t_head += t2 - t1
+        per_token = (t_layers / n_tokens) / self.sub_l * self.a.L + t_head / n_tokens
+        return {"value": 1.0 / per_token, "unit": "tokens/s", "cores": self.cores, "kind": "port",
+                "sample": f"{self.sub_l} of {self.a.L} real-size layers + LM head of {self.key} ({self.osub.matmul_weights() / 1e6:.0f}M weights), "
+                          f"{n_tokens} decode tokens, PyTorch fp32 oracle, extrapolated to {self.a.L} layers"}
+
+
 def cpu_sample(model_key: str, n_tokens: int, threads: int | None = None):
-    """Times the oracle on a bounded sample of the workload and extrapolates to the full depth."""
-    import dataclasses
-    import numpy as np
-    import torch
-    from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
-    from cain_2025_device_remote_llm_energy_rep_pkg_b200.engine import host_random_tensors
-    from oracle.archs import ARCHS as OARCHS
-    from oracle.model import OracleModel
-    cores = threads or os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    a = ARCHS[model_key]
-    sub_l = min(2, a.L)
-    sub = dataclasses.replace(a, L=sub_l)
-    osub = dataclasses.replace(OARCHS[model_key], L=sub_l)
-    tensors = host_random_tensors(sub, seed=1)
-    om = OracleModel(osub, tensors)
-    s = om.session(64)
-    tok = 1
-    h = s.hidden(tok)          # first call dequantises and caches the weights (model load, not timed)
-    om.head(h)
-    t_layers = t_head = 0.0
-    for _ in range(n_tokens):
-        t0 = time.perf_counter()
-        h = s.hidden(tok)
-        t1 = time.perf_counter()
-        lg = om.head(h)
-        tok = int(torch.argmax(lg))
-        t2 = time.perf_counter()
-        t_layers += t1 - t0
-        t_head += t2 - t1
-    per_token = (t_layers / n_tokens) / sub_l * a.L + t_head / n_tokens
-    return {"value": 1.0 / per_token, "unit": "tokens/s", "cores": cores, "kind": "port",
-            "sample": f"{sub_l} of {a.L} real-size layers + LM head of {model_key} ({osub.matmul_weights() / 1e6:.0f}M weights), "
-                      f"{n_tokens} decode tokens, PyTorch fp32 oracle, extrapolated to {a.L} layers"}
+    return CpuSample(model_key, threads).run(n_tokens)
 
 
 def run_reference(args):
+    """The CPU restatement of the path on all host cores; under torchrun only rank 0 works, the others exit 0."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    vals = []
-    info = None
+    cs = CpuSample(args.model)
+    vals, info = [], None
+    t0 = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        info = cpu_sample(args.model, args.cpu_tokens)
+        info = cs.run(args.cpu_tokens)
         if i >= args.warmup:
             vals.append(info["value"])
-        if i == 0 and args.warmup > 0:
-            pass
     v = sum(vals) / len(vals)
     info["value"] = v
     line = {"metric": "decode_tokens_per_s", "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1000.0 * args.new_tokens / v, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1000.0 * (time.perf_counter() - t0) / (args.warmup + args.steps),
+            "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"{args.model} {args.qtype} batch-1 greedy decode, random-init weights", "new_tokens": args.new_tokens,
-                       "prompt_len": args.prompt_len},
+            "config": {"workload": f"{args.model} {args.qtype} batch-1 greedy decode, random-init weights, one replica per GPU",
+                       "new_tokens": args.new_tokens, "prompt_len": args.prompt_len, "requests_per_step_per_gpu": 1,
+                       "step": f"bounded sample: {args.cpu_tokens} decode tokens of the oracle per step"},
             "cpu_baseline": info, "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -203,6 +214,18 @@ def bench_model(eng, key, args, lib, dev, dist, steps, warmup):
     return res
 
 
+def aggregate(dist, wall_s, eval_s, tokens, launches, energy_j, device="cuda"):
+    """Whole-job numbers from per-rank ones: MAX of the timed quantities, SUM of tokens / launches / joules.
+    No collective is on the data path (replicas are independent); this is the only place ranks talk."""
+    import torch
+    vec = torch.tensor([wall_s, eval_s], dtype=torch.float64, device=device)
+    tot = torch.tensor([tokens, launches, energy_j or 0.0], dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(vec, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    return vec.tolist(), tot.tolist()
+
+
 def run_ours(args):
     import torch
     import __graft_entry__ as g
@@ -222,14 +245,7 @@ def run_ours(args):
         dist = dist_mod
     eng = Engine(local)
     r = bench_model(eng, args.model, args, lib, local, dist, args.steps, args.warmup)
-    # max over ranks of the timed quantities, sum of tokens / launches / energy
-    vec = torch.tensor([r["wall_s"], r["eval_s"]], dtype=torch.float64, device="cuda")
-    tot = torch.tensor([r["tokens"], r["launches"], r["energy_j"] or 0.0], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(vec, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    wall, eval_s = vec.tolist()
-    tokens, launches, energy = tot.tolist()
+    (wall, eval_s), (tokens, launches, energy) = aggregate(dist, r["wall_s"], r["eval_s"], r["tokens"], r["launches"], r["energy_j"])
     per_model = None
     if args.all_models and rank == 0 and world == 1:
         per_model = {}

@@ -1,0 +1,61 @@
+"""N>1 host logic on CPU (gloo, world_size 2): the rank aggregation of bench.py (max of times, sum of tokens), the
+run-table sharding by model, and the reference arm's "rank 0 only" rule.  The data path itself has no collective."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import ROOT
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    import bench
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # rank r: wall 1+r s, device time 0.5+r s, 100*(r+1) tokens, 10 launches, 2.5 J
+    (wall, ev), (tok, launches, joules) = bench.aggregate(dist, 1.0 + rank, 0.5 + rank, 100 * (rank + 1), 10, 2.5, device="cpu")
+    dist.barrier()
+    if rank == 0:
+        json.dump({"wall": wall, "eval": ev, "tokens": tok, "launches": launches, "joules": joules}, open(out, "w"))
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_aggregate_max_time_sum_tokens_world2(tmp_path):
+    out = str(tmp_path / "agg.json")
+    mp.spawn(_worker, args=(2, free_port(), out), nprocs=2, join=True)
+    r = json.load(open(out))
+    assert r == {"wall": 2.0, "eval": 1.5, "tokens": 300.0, "launches": 20.0, "joules": 5.0}
+    # value = all tokens / max time: whole-job throughput, not a per-GPU mean
+    assert r["tokens"] / r["eval"] == 200.0
+
+
+def test_reference_arm_other_ranks_exit_quietly():
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, env=env, timeout=120)
+    assert p.returncode == 0 and p.stdout.strip() == ""
+
+
+def test_replica_sharding_covers_every_model_once():
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200.runner import launch
+    for n in (2, 4, 8):
+        groups = launch.shard_models(launch.MODELS, n)
+        flat = sum(groups, [])
+        assert sorted(flat) == sorted(launch.MODELS) and len(groups) == min(n, 7)
+    # heaviest models are spread first: gemma:7b and llama3.1:8b never share a shard when there are >= 2
+    g2 = launch.shard_models(launch.MODELS, 2)
+    assert not any({"gemma:7b", "llama3.1:8b"} <= set(g) for g in g2)
