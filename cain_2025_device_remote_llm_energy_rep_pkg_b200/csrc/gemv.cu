@@ -12,44 +12,9 @@
 // x 3 digit planes of exact integer dot products each), scale by d_w * 2^e / 16 into fp32 accumulators.
 // The sixteen warps split K and meet in shared memory once per tile.  Measured alone (tools/microbench3.cu)
 // this structure streams 6.3-6.8 TB/s from HBM with the arithmetic included.
-#include "kernels.cuh"
-#include "layout.cuh"
+#include "gemv_dev.cuh"
 #include "randinit.cuh"
 #include <stdlib.h>
-
-// ------------------------------------------------------------------------------------------ PTX helpers
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *b, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *b) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
-    asm volatile(
-        "{\n.reg .pred p;\nWAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ bool mbar_test(uint64_t *b, uint32_t parity) {   // non-blocking
-    uint32_t ok;
-    asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
-}
 
 // ------------------------------------------------------------------------------------------ pack / init
 // GGML Q4_0 row-major blocks (18 B: f16 d | 16 B nibbles) -> streaming layout (layout.cuh). One thread per block.
@@ -109,478 +74,11 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
 }
 
 // ------------------------------------------------------------------------------------------ the kernel
-#define GEMV_CWARPS 16                       // one block-group of a 64-block chunk each
-#define GEMV_THREADS (GEMV_CWARPS * 32)
-#define GEMV_DEPTH 4                         // weight pieces (1152 B per warp) in flight per warp
-#define GEMV_NORM_MAX 8192                   // longest vector the fused RMSNorm prologue keeps in registers
-#define GEMV_MAXT 2                          // K-outer order: tiles per CTA whose accumulators stay in registers
-#define MMA_MAGIC 0x4B400000                 // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
-#define MMA_MAGIC_F 12582912.0f
-#define L2_PREFETCH_BYTES 0                  // of the NEXT kernel's weights, per CTA: off (measured: no gain once the own-stream window is on; B2_PF_NEXT re-enables)
-#define L2_WINDOW_BYTES (128 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
-#define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
-
-struct GemvArgs {
-    const uint8_t *w;        // packed matrix
-    int rows, nbp, n_tiles;  // logical rows, padded blocks per row, tiles
-    int tile_align;          // tiles are dealt to CTAs in multiples of this (4 for act*mul so A3 blocks stay whole)
-    int k_outer;             // 1: loop chunks outermost (long K, <= GEMV_MAXT tiles per CTA); 0: tiles outermost (K <= 2 chunks)
-    // input
-    const float *x;          // IN_NORM: residual stream, n_in floats
-    const float *norm_w;
-    float eps;
-    int plus_one, n_in;
-    const uint8_t *act_in;   // IN_ACT: A3 vector in global memory; IN_F32: fp32 vector of n_in elements (put on the grid here)
-    // output
-    float *y;                // fp32 output (OUT_ACTMUL: optional copy of h)
-    const float *bias_or_res;
-    uint8_t *act_out;        // OUT_ACTMUL: A3 of h
-    int n_out_act;           // elements of the A3 output vector (for its scale area offset)
-    int act;
-    float *pmax;             // OUT_LOGITS: per-CTA arg-max partials
-    int *pidx;
-    const float *xsq_in;     // IN_NORM: partial sums of x^2 left by the kernel that produced x (fixed order => deterministic)
-    int xsq_n;
-    float *xsq_out;          // OUT_RES: this CTA's partial sum of squares of the rows it wrote, at [blockIdx.x]
-    const uint8_t *pf_ptr;   // weights the NEXT kernel will stream: each CTA pulls the head of its share into L2
-    uint64_t pf_total;
-    uint32_t l2_window;      // bytes the CTA's L2 prefetch cursor runs ahead of its register loads (0: off)
-    uint32_t pf_bytes;       // bytes of the next kernel's weights each CTA pulls into L2 (0: off)
-    long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
-};
-enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2 };
-enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3 };
-
-__device__ __forceinline__ float act_fn(float g, int act) {
-    if (act == B2_ACT_SILU) return g / (1.0f + expf(-g));
-    float g3 = 0.044715f * g * g * g;
-    return 0.5f * g * (1.0f + tanhf(0.7978845608028654f * (g + g3)));
-}
-__device__ __forceinline__ void cta_sync() { __syncthreads(); }
-__device__ __forceinline__ void l2_prefetch(const void *p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ uint4 ldg_stream4(const void *p) {   // weights: read once, keep out of L1
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
-__device__ __forceinline__ uint4 ldcg4(const void *p) {         // activations written by the previous kernel: L2
-    uint4 r;
-    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    return r;
-}
-
-struct WPiece { uint4 wa, wb, sd; };                 // one block-group of weights for this lane: rows g / g+8, 4 blocks, + their scales
-struct BFrag { uint4 b01, b23; float4 as; };         // activation digits (B fragments of 4 blocks) + block scales (already / 16)
-
-__device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&acc)[4]) {
-    const uint32_t ua[4] = {r.wa.x, r.wa.y, r.wa.z, r.wa.w}, ub[4] = {r.wb.x, r.wb.y, r.wb.z, r.wb.w};
-    const uint32_t bx[4] = {b.b01.x, b.b01.z, b.b23.x, b.b23.z}, by[4] = {b.b01.y, b.b01.w, b.b23.y, b.b23.w};
-    const uint32_t sdw[4] = {r.sd.x, r.sd.y, r.sd.z, r.sd.w};
-    const float asf[4] = {b.as.x, b.as.y, b.as.z, b.as.w};
-    int c[4][4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {   // four independent MMAs
-        c[j][0] = c[j][1] = c[j][2] = c[j][3] = MMA_MAGIC;
-        mma_s8(c[j], (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bx[j], by[j]);
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {   // scale into the fp32 accumulators
-        const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
-        const float f0 = dd.x * asf[j], f1 = dd.y * asf[j];
-        acc[0] = fmaf(__int_as_float(c[j][0]) - MMA_MAGIC_F, f0, acc[0]);
-        acc[1] = fmaf(__int_as_float(c[j][1]) - MMA_MAGIC_F, f0, acc[1]);
-        acc[2] = fmaf(__int_as_float(c[j][2]) - MMA_MAGIC_F, f1, acc[2]);
-        acc[3] = fmaf(__int_as_float(c[j][3]) - MMA_MAGIC_F, f1, acc[3]);
-    }
-}
-// one piece of the stream: block-group column `warp` of the chunk at `ch` (cb blocks)
-__device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, int lane, WPiece &r) {
-    r.wa = ldg_stream4(ch + (size_t)warp * 1024 + lane * 16);
-    r.wb = ldg_stream4(ch + (size_t)warp * 1024 + 512 + lane * 16);
-    r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * 128 + (lane >> 2) * 16);
-}
-
-// shared memory map (bytes): [red GEMV_RB*16*16*4*4 = 32768][hbuf GEMV_RB*8 floats + 64 scratch = 512][A3 of the input nbp*100]
-#define GEMV_FIXED_SMEM (GEMV_RB * 4096 + 512)
-
-// ---- Input staging.  What the previous kernel wrote reaches shared memory through cp.async.bulk (the TMA path): an ordinary load
-// would complete only after the ~70 KB of weight loads this SM already has in flight (the L1 load queue is a FIFO).  Thread 0 issues
-// the copies after griddepcontrol.wait; every thread waits on the mbarrier, no CTA barrier.  Then the work is warp-local: warp w only
-// ever multiplies block-group column w of every chunk, i.e. the input elements [128*kbg, 128*kbg+128) with kbg = ck*16 + w.  It
-// normalises exactly those (IN_NORM: the sum of squares arrives as per-CTA partials from the producer of x, added in a fixed order;
-// op order of oracle/model.py:_norm), puts them on the activation grid (a 32-element block is 8 consecutive lanes: three shuffles
-// for the block maximum) and writes its own block-groups of the shared-memory activation image.
-// Shared memory of the input area: [A3 image nbp*100][staging: fp32 vector n_in*4][xsq partials 1 KB]
-template <int IN>
-__device__ __forceinline__ void stage_warp_input(const GemvArgs &a, uint8_t *sact, uint64_t *bar, int cpt, int warp, int lane,
-                                                 const float4 (&wn)[2]) {
-    if (IN == IN_ACT) {   // already on the grid: the image itself was copied
-        mbar_wait(bar, 0);
-        return;
-    }
-    const float *sx = (const float *)(sact + (size_t)a.nbp * 100);
-    const float *sq = sx + a.n_in;
-    float *sscale = (float *)(sact + (size_t)a.nbp * 96);
-    mbar_wait(bar, 0);
-    float r = 1.0f;
-    if (IN == IN_NORM) {
-        float ss = 0.f;
-        for (int i = lane; i < a.xsq_n; i += 32) ss += sq[i];
-        ss = warp_sum(ss);
-        r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)a.n_in), a.eps)));
-    }
-    const int n4 = a.n_in >> 2;
-    for (int ck = 0; ck < cpt; ++ck) {
-        const int kbg = ck * (KC / 4) + warp;
-        if (kbg * 4 >= a.nbp) break;
-        const int q = kbg * 32 + lane;   // float4 index: block = q / 8, word-in-block = q % 8
-        float yv[4] = {0.f, 0.f, 0.f, 0.f};
-        if (q < n4) {
-            const float4 v = ((const float4 *)sx)[q];
-            if (IN == IN_NORM) {
-                const float4 w = ck < 2 ? wn[ck] : __ldg((const float4 *)a.norm_w + q);
-                const float xs[4] = {v.x, v.y, v.z, v.w}, ws[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) yv[e] = __fmul_rn(__fmul_rn(xs[e], r), a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e]);
-            } else {
-                yv[0] = v.x; yv[1] = v.y; yv[2] = v.z; yv[3] = v.w;
-            }
-        }
-        float m = fmaxf(fmaxf(fabsf(yv[0]), fabsf(yv[1])), fmaxf(fabsf(yv[2]), fabsf(yv[3])));
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-        m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
-        const int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
-        const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
-        const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
-        uint32_t w0 = 0, w1 = 0, w2 = 0;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            int d0, d1, d2;
-            act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
-            w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
-            w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
-            w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
-        }
-        const int b = q >> 3, k = q & 7;                    // elements 4k..4k+3 of block b
-        uint8_t *dst = sact + a3_off(b, 0, 4 * k);
-        *(uint32_t *)dst = w0;
-        *(uint32_t *)(dst + 128) = w1;
-        *(uint32_t *)(dst + 256) = w2;
-        if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
-    }
-    __syncwarp();
-}
-
-// ---- reduction + epilogue of the `batch_n` finished tiles parked in shared memory (called by all threads).
-// Every warp parked its K-partial of the 16 rows x 3 digit planes; warp w finalises tile batch_first + w.
-// Two CTA-wide barriers per GEMV_RB tiles instead of one per tile: the weight streams of the sixteen warps are not
-// re-synchronised on memory latency every other piece.
-template <int OUT>
-__device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i,
-                                         float &sumsq) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    __syncthreads();
-    if (warp < batch_n) {
-        // lane = (half, row): each lane adds 8 of the 16 warp partials of its row in a fixed order, the halves meet by shuffle
-        const int tile = batch_first + warp;
-        const float *rb = red + (size_t)warp * (GEMV_CWARPS * 16 * 4);
-        const int r = lane & 15, hf = lane >> 4;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f;
-#pragma unroll
-        for (int w8 = 0; w8 < GEMV_CWARPS / 2; ++w8) {
-            const float4 p4 = *(const float4 *)(rb + ((hf * (GEMV_CWARPS / 2) + w8) * 16 + r) * 4);
-            v0 += p4.x;
-            v1 += p4.y;
-            v2 += p4.z;
-        }
-        v0 += __shfl_xor_sync(0xffffffffu, v0, 16);
-        v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
-        v2 += __shfl_xor_sync(0xffffffffu, v2, 16);
-        const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
-        const int row = tile * TILE_ROWS + r;
-        if (OUT == OUT_BIAS) {
-            if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res ? yv + a.bias_or_res[row] : yv;
-        } else if (OUT == OUT_RES) {
-            if (lane < 16 && row < a.rows) {
-                const float xn = __ldcg(a.bias_or_res + row) + yv;
-                a.y[row] = xn;
-                sumsq = fmaf(xn, xn, sumsq);
-            }
-        } else if (OUT == OUT_LOGITS) {
-            if (lane < 16 && row < a.rows) {
-                a.y[row] = yv;
-                if (yv > best_v || (yv == best_v && row < best_i)) { best_v = yv; best_i = row; }
-            }
-        } else {   // OUT_ACTMUL: rows (2j, 2j+1) = (gate_j, up_j)
-            const float up = __shfl_down_sync(0xffffffffu, yv, 1);
-            const float hv = act_fn(yv, a.act) * up;
-            const int pair = tile * 8 + (r >> 1);
-            if (lane < 16 && !(r & 1) && 2 * pair < a.rows) a.y[pair] = hv;
-        }
-    }
-    __syncthreads();   // the parked partials may be overwritten from here on
-}
-
 template <int IN, int OUT>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
-    float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
-    float *scratch = hbuf + GEMV_RB * 8;
-    uint64_t *bar = (uint64_t *)(hbuf + 96);                                    // completion of the input copies
-    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector (+ fp32 staging, partials)
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int g = lane >> 2, t = lane & 3;
-    if (tid == 0) {
-        pdl_launch_dependents();
-        mbar_init(bar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    auto stamp = [&](int k) {
-        if (a.dbg && tid == 0) {
-            long long tt;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
-            a.dbg[blockIdx.x * 8 + k] = tt;
-        }
-    };
-    stamp(0);
-
-    // contiguous, aligned share of the tiles
-    const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
-    const int u0 = (int)(((uint32_t)units * blockIdx.x) / gridDim.x), u1 = (int)(((uint32_t)units * (blockIdx.x + 1)) / gridDim.x);
-    const int t0 = u0 * a.tile_align, t1 = min(a.n_tiles, u1 * a.tile_align);
-    const int nt = t1 - t0;
-    const int cpt = (a.nbp + KC - 1) / KC;                                      // chunks per tile
-    const uint8_t *base = a.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
-    const uint32_t tile_bytes = (uint32_t)a.nbp * BLOCK_BYTES;
-    const int cb_last = a.nbp - (cpt - 1) * KC;                                 // blocks in the last chunk of a tile
-    const bool act_full = warp < (KC >> 2);                                     // this warp has a block-group in a full chunk ...
-    const bool act_last = warp < (cb_last >> 2);                                // ... in the last chunk of a tile
-
-    // B fragments of block-group column `warp` of chunk ck, from the shared-memory activation image
-    auto load_b = [&](int ck, BFrag &b) {
-        const int kbg = ck * (KC / 4) + warp;
-        b.b01 = make_uint4(0u, 0u, 0u, 0u);
-        b.b23 = make_uint4(0u, 0u, 0u, 0u);
-        b.as = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (kbg * 4 < a.nbp) {
-            if (g < 3) {
-                const uint4 *bp = (const uint4 *)(sact + (size_t)kbg * 384 + g * 128 + t * 32);
-                b.b01 = bp[0];
-                b.b23 = bp[1];
-            }
-            b.as = *(const float4 *)(sact + (size_t)a.nbp * 96 + kbg * 16);
-            b.as.x *= 0.0625f; b.as.y *= 0.0625f; b.as.z *= 0.0625f; b.as.w *= 0.0625f;   // the 1/16 of the nibble trick
-        }
-    };
-    // pull this CTA's share of the next kernel's weights into L2 (lane 0 of every warp, 16 KB per instruction)
-    auto prefetch_next = [&]() {
-        if (lane == 0 && a.pf_ptr) {
-            const uint64_t share = (a.pf_total / gridDim.x) & ~(uint64_t)127;
-            const uint8_t *p0 = a.pf_ptr + share * blockIdx.x;
-            const uint64_t n = share < a.pf_bytes ? share : a.pf_bytes;
-            for (uint64_t o = (uint64_t)warp * 16384; o + 16384 <= n; o += GEMV_CWARPS * 16384) l2_prefetch(p0 + o, 16384);
-        }
-    };
-
-    float sumsq = 0.f;
-    auto stage_input = [&]() {
-        stamp(1);
-        // the norm weights of this warp's columns are immutable: fetch them before waiting for the previous kernel
-        float4 wn[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
-        if (IN == IN_NORM) {
-#pragma unroll
-            for (int ck = 0; ck < 2; ++ck) {
-                const int q = (ck * (KC / 4) + warp) * 32 + lane;
-                if (ck < cpt && q < (a.n_in >> 2)) wn[ck] = __ldg((const float4 *)a.norm_w + q);
-            }
-        }
-        __syncthreads();   // everybody has issued its first weight loads; the mbarrier thread 0 initialised is visible
-        if (tid == 0) {
-            pdl_wait();    // the copies below read what the previous kernel wrote
-            if (IN == IN_ACT) {
-                const uint32_t bytes = (uint32_t)a.nbp * 100;
-                mbar_expect_tx(bar, bytes);
-                bulk_g2s(sact, a.act_in, bytes, bar);
-            } else {
-                float *sx = (float *)(sact + (size_t)a.nbp * 100);
-                const uint32_t bytes = (uint32_t)a.n_in * 4;
-                const uint32_t qbytes = IN == IN_NORM ? (uint32_t)((a.xsq_n + 3) & ~3) * 4 : 0;
-                mbar_expect_tx(bar, bytes + qbytes);
-                bulk_g2s(sx, IN == IN_NORM ? (const void *)a.x : (const void *)a.act_in, bytes, bar);
-                if (qbytes) bulk_g2s(sx + a.n_in, a.xsq_in, qbytes, bar);
-            }
-        }
-        stamp(2);   // everything from here reads what the previous kernel wrote (ld.global.cg: under programmatic
-                      // dependent launch a CTA of that kernel may have shared this SM's L1)
-        stage_warp_input<IN>(a, sact, bar, cpt, warp, lane, wn);
-        stamp(3);
-        prefetch_next();   // the next kernel's weights start flowing HBM -> L2 while this kernel works through its own
-    };
-    float best_v = -INFINITY;
-    int best_i = 0x7fffffff;
-    int batch_first = t0, batch_n = 0;
-    auto park = [&](float (&acc)[4]) {   // park the finished tile's partial; reduce when GEMV_RB tiles are waiting
-        float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
-        if (t < 2) {
-            *(float2 *)(rb + (warp * 16 + g) * 4 + 2 * t) = make_float2(acc[0], acc[1]);
-            *(float2 *)(rb + (warp * 16 + g + 8) * 4 + 2 * t) = make_float2(acc[2], acc[3]);
-        }
-        acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
-        if (++batch_n == GEMV_RB) {
-            flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
-            batch_first += batch_n;
-            batch_n = 0;
-        }
-    };
-    WPiece buf0, buf1, buf2, buf3;      // GEMV_DEPTH = 4 pieces in flight per warp
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    if (!a.k_outer) {
-        // ================= tiles outermost: the CTA's bytes are one contiguous run of chunks; K spans one or two chunks whose
-        // B fragments stay in registers for the whole kernel.  With two chunks per tile the even pieces are full chunks and
-        // the odd ones the (possibly shorter) last chunk of a tile: no index arithmetic in the loop.
-        const uint8_t *lp = base;
-        int l_rem = nt * cpt;            // pieces not requested yet
-        // L2 prefetch cursor (thread 0): cp.async.bulk.prefetch.L2 keeps the CTA's contiguous byte range L2_WINDOW_BYTES ahead of
-        // the register loads, so those hit L2 (short latency) while HBM streams at its own pace from the first cycle
-        // (lane 0 of warp w owns the 16 KB blocks w, w+16, ... of the range: one instruction per warp per 256 KB of progress)
-        const uint8_t *pf = base + (size_t)warp * 16384, *pf_end = base + (size_t)nt * tile_bytes;
-        auto l2_window = [&]() {
-            if (lane == 0 && pf < pf_end && pf < lp + a.l2_window) {
-                const size_t left = (size_t)(pf_end - pf);
-                l2_prefetch(pf, left < 16384 ? (uint32_t)left & ~15u : 16384u);
-                pf += GEMV_CWARPS * 16384;
-            }
-        };
-        l2_window();
-        auto load_full = [&](WPiece &r) {
-            if (l_rem > 0) { if (act_full) load_piece(lp, KC, warp, lane, r); lp += KC * BLOCK_BYTES; --l_rem; }
-        };
-        auto load_last = [&](WPiece &r) {
-            if (l_rem > 0) { if (act_last) load_piece(lp, cb_last, warp, lane, r); lp += cb_last * BLOCK_BYTES; --l_rem; }
-        };
-        if (cpt == 2) {
-            load_full(buf0); load_last(buf1); load_full(buf2); load_last(buf3);     // the stream starts before the wait
-            stage_input();
-            BFrag bf0, bf1;
-            load_b(0, bf0);
-            load_b(1, bf1);
-            for (int rem = nt; rem > 0; rem -= 2) {
-                if (act_full) bg_mma(buf0, bf0, acc);
-                load_full(buf0);
-                if (act_last) bg_mma(buf1, bf1, acc);
-                load_last(buf1);
-                park(acc);
-                if (rem > 1) {
-                    if (act_full) bg_mma(buf2, bf0, acc);
-                    load_full(buf2);
-                    if (act_last) bg_mma(buf3, bf1, acc);
-                    load_last(buf3);
-                    park(acc);
-                }
-                l2_window();
-            }
-        } else {
-            load_last(buf0); load_last(buf1); load_last(buf2); load_last(buf3);
-            stage_input();
-            BFrag bf0;
-            load_b(0, bf0);
-            for (int rem = nt; rem > 0; rem -= 4) {
-                if (act_last) bg_mma(buf0, bf0, acc);
-                load_last(buf0);
-                park(acc);
-                if (rem > 1) { if (act_last) bg_mma(buf1, bf0, acc); load_last(buf1); park(acc); }
-                if (rem > 2) { if (act_last) bg_mma(buf2, bf0, acc); load_last(buf2); park(acc); }
-                if (rem > 3) { if (act_last) bg_mma(buf3, bf0, acc); load_last(buf3); park(acc); }
-                l2_window();
-            }
-        }
-    } else {
-        // ================= chunks outermost (K longer than two chunks; a CTA owns one or two tiles whose accumulators stay in
-        // registers).  A step is chunk ck of both tiles; the B fragments of a step are read from shared memory one step ahead.
-        float acc1[4] = {0.f, 0.f, 0.f, 0.f};
-        const bool two = nt > 1;
-        int l_ck = 0;                     // chunk of the next step to request
-        auto load_step = [&](WPiece &r0, WPiece &r1) {
-            if (l_ck < cpt) {
-                const bool last = l_ck == cpt - 1;
-                if (last ? act_last : act_full) {
-                    const uint8_t *ch = base + (size_t)l_ck * (KC * BLOCK_BYTES);
-                    load_piece(ch, last ? cb_last : KC, warp, lane, r0);
-                    if (two) load_piece(ch + tile_bytes, last ? cb_last : KC, warp, lane, r1);
-                }
-                ++l_ck;
-            }
-        };
-        if (lane == 0 && a.l2_window) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
-            for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
-        }
-        load_step(buf0, buf1);
-        load_step(buf2, buf3);
-        stage_input();
-        BFrag bcur, bnxt;
-        load_b(0, bcur);
-        for (int ck = 0; ck < cpt; ck += 2) {
-            load_b(ck + 1, bnxt);
-            if ((ck == cpt - 1) ? act_last : act_full) {
-                bg_mma(buf0, bcur, acc);
-                if (two) bg_mma(buf1, bcur, acc1);
-            }
-            load_step(buf0, buf1);
-            if (ck + 1 < cpt) {
-                load_b(ck + 2, bcur);
-                if ((ck + 1 == cpt - 1) ? act_last : act_full) {
-                    bg_mma(buf2, bnxt, acc);
-                    if (two) bg_mma(buf3, bnxt, acc1);
-                }
-                load_step(buf2, buf3);
-            }
-        }
-        if (nt > 0) park(acc);
-        if (two) park(acc1);
-    }
-    stamp(4);
-    if (batch_n > 0) flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
-    stamp(5);
-    if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
-        sumsq = warp_sum(sumsq);
-        __syncthreads();
-        if (lane == 0) scratch[warp] = sumsq;
-        __syncthreads();
-        if (tid == 0) {
-            float tot = 0.f;
-#pragma unroll
-            for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
-            a.xsq_out[blockIdx.x] = tot;
-        }
-    }
-    if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima
-        float *sv = scratch;
-        int *si = (int *)(scratch + 16);
-        __syncthreads();
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
-            int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
-            if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
-        }
-        if (lane == 0) { sv[warp] = best_v; si[warp] = best_i; }
-        __syncthreads();
-        if (warp == 0) {
-            best_v = lane < GEMV_CWARPS ? sv[lane] : -INFINITY;
-            best_i = lane < GEMV_CWARPS ? si[lane] : 0x7fffffff;
-#pragma unroll
-            for (int o = 8; o > 0; o >>= 1) {
-                float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
-                int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
-                if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
-            }
-            if (lane == 0) { a.pmax[blockIdx.x] = best_v; a.pidx[blockIdx.x] = best_i; }
-        }
-    }
+    uint32_t parity = 0;
+    gemv_phase<IN, OUT, false>(a, smem, parity);
 }
 
 // ------------------------------------------------------------------------------------------ launcher
