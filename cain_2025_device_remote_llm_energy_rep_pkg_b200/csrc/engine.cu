@@ -2,6 +2,7 @@
 // Replaces what happens inside Ollama's POST /api/generate (reference call site
 // experiment/RunnerConfig.py:128-131): model load, prompt evaluation, the batch-1 decode loop.
 #include "kernels.cuh"
+#include "mega.cuh"
 #include "layout.cuh"
 #include "randinit.cuh"
 #include <stdarg.h>
@@ -86,6 +87,11 @@ struct b2_session {
     bool fused_attn = true;
     float *logits_log = nullptr;
     uint64_t logits_log_cap = 0;   // in floats
+    // persistent token kernel (mega.cu): plan, grid and shared memory; use_mega = false falls back to one kernel per stage
+    MegaPlan *plan = nullptr;
+    bool use_mega = false;
+    int mega_grid_n = 0;
+    size_t mega_smem = 0;
     cudaGraphExec_t graphs[G_COUNT][2] = {};   // [..][0]: positions below ATTN_SHORT_CTX (one attention CTA per head), [..][1]: longer contexts
     int graph_launches[G_COUNT][2] = {};
     bool use_graphs = true;
@@ -534,6 +540,81 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
     return B2_OK;
 }
 
+// ------------------------------------------------------------------------------------ persistent token kernel
+// Build the constant-memory plan of the session (mega.cuh).  Returns false (and leaves use_mega off) when a shape does not fit
+// the persistent kernel; the session then runs one kernel per stage under CUDA graphs.
+static bool build_mega_plan(b2_session *s) {
+    b2_model *m = s->m;
+    const b2_arch_cfg &c = m->cfg;
+    if (c.n_layers > MEGA_MAX_LAYERS || !s->fused_attn) return false;
+    const int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
+    MegaPlan *P = new MegaPlan();
+    memset(P, 0, sizeof *P);
+    size_t smem = 0, sm1 = 0;
+    // the grid is what the kernel's shared memory allows co-resident: fixed point of (plan -> smem -> grid); one CTA per SM
+    const int max_pages = (s->max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const int pps_short = (ATTN_SHORT_CTX + PAGE_TOKENS - 1) / PAGE_TOKENS, pps_long = (max_pages + ATTN_NSPLIT - 1) / ATTN_NSPLIT;
+    const int pps_max = pps_short > pps_long ? pps_short : pps_long;
+    const LayerW &l0 = m->layers[0];
+    int grid = m->e->sm_count > 0 ? m->e->sm_count : 148;
+    bool ok = true;
+    auto mk = [&](GemvArgs &a, int in_mode, const Mat &mt, const float *x, const float *norm_w, const void *act_in, float *y, const float *bias_or_res,
+                  int act, float *pmax, int *pidx, const float *xsq_in, float *xsq_out) {
+        if (gemv_make_args(a, in_mode, mt.packed, mt.rows, mt.cols, x, norm_w, c.rms_eps, c.norm_plus_one, act_in, y, bias_or_res, nullptr, act, pmax,
+                           pidx, nullptr, 0, xsq_in, xsq_in ? grid : 0, xsq_out, &sm1) != cudaSuccess) { ok = false; return; }
+        if (a.k_outer && (a.n_tiles + grid - 1) / grid > GEMV_MAXT) ok = false;   // accumulators of a CTA's tiles must fit its registers
+        if (sm1 > smem) smem = sm1;
+    };
+    mk(P->qkv, GEMV_IN_NORM, l0.qkv, s->x, l0.attn_norm, nullptr, s->qkv, l0.qkv_bias, 0, nullptr, nullptr, s->xsq, nullptr);
+    mk(P->o, GEMV_IN_ACT, l0.o, nullptr, nullptr, s->act_attn, s->x, s->x, 0, nullptr, nullptr, nullptr, s->xsq + 512);
+    mk(P->gateup, GEMV_IN_NORM, l0.gateup, s->x, l0.ffn_norm, nullptr, s->h, nullptr, c.act, nullptr, nullptr, s->xsq + 512, nullptr);
+    mk(P->down, GEMV_IN_F32, l0.down, nullptr, nullptr, s->h, s->x, s->x, 0, nullptr, nullptr, nullptr, s->xsq);
+    mk(P->head, GEMV_IN_NORM, m->head, s->x, m->out_norm, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, s->xsq, nullptr);
+    const size_t attn_smem = GEMV_FIXED_SMEM + (size_t)4 * attn_group_floats(hd, pps_max) * 4;
+    if (attn_smem > smem) smem = attn_smem;
+    if (c.n_heads * ATTN_NSPLIT > 4 * grid || grid > 512 || (H % QK) != 0) ok = false;   // one attention item per 128-thread group; xsq halves hold 512 partials
+    int g2 = 0;
+    if (ok && mega_grid(smem, &g2) != cudaSuccess) { ok = false; cudaGetLastError(); }
+    if (ok && g2 != grid) ok = false;
+    if (!ok) { delete P; return false; }
+    AttnArgs &A = P->attn;
+    A.qkv = s->qkv; A.nh = c.n_heads; A.nkv = c.n_kv_heads; A.hd = hd; A.d_pos = nullptr; A.pos_imm = 0;
+    A.cs = m->rope_cos; A.sn = m->rope_sin; A.kc = s->kcache; A.vc = s->vcache; A.page_table = s->page_table;
+    A.out = nullptr; A.act_out = (uint8_t *)s->act_attn; A.pps_max = pps_max;
+    A.g_part = (float *)s->attn_scratch;
+    A.g_cnt = (int *)((float *)s->attn_scratch + (size_t)c.n_heads * ATTN_NSPLIT * (hd + 2));
+    P->n_layers = c.n_layers; P->n_embd = H; P->vocab = c.vocab; P->n_part = grid;
+    P->embd_w = (const uint8_t *)m->embd.packed; P->embd_nbp = (int)nblocks_padded(m->embd.cols);
+    P->embd_scale = c.embed_scale ? sqrtf((float)H) : 1.0f;
+    P->x = s->x; P->xsq = s->xsq; P->logits = s->logits; P->pmax = s->pmax; P->pidx = s->pidx;
+    const uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    for (int l = 0; l < c.n_layers; ++l) {
+        const LayerW &ly = m->layers[l];
+        MegaLayer &L = P->layers[l];
+        L.qkv_w = (const uint8_t *)ly.qkv.packed; L.o_w = (const uint8_t *)ly.o.packed;
+        L.gateup_w = (const uint8_t *)ly.gateup.packed; L.down_w = (const uint8_t *)ly.down.packed;
+        L.attn_norm = ly.attn_norm; L.ffn_norm = ly.ffn_norm; L.qkv_bias = ly.qkv_bias;
+        L.kc = s->kcache + l * layer_kv; L.vc = s->vcache + l * layer_kv;
+    }
+    (void)I; (void)qd;
+    s->plan = P;
+    s->mega_grid_n = grid;
+    s->mega_smem = smem;
+    s->head_grid = grid;
+    return true;
+}
+
+// n consecutive tokens in one cooperative launch
+static int run_mega(b2_session *s, int mode, int n, int head_from, float *logits_log) {
+    MegaRun r;
+    r.mode = mode; r.n_tokens = n; r.head_from = head_from; r.pos0 = s->host_pos;
+    r.prompt = s->d_prompt; r.out_tokens = s->d_out_tokens; r.logits_log = logits_log; r.state = s->state;
+    cudaError_t e = launch_mega(s->plan, s, r, s->mega_grid_n, s->mega_smem, s->m->e->stream);
+    if (e != cudaSuccess) { b2_set_error("token kernel launch failed: %s", cudaGetErrorString(e)); cudaGetLastError(); return B2_ECUDA; }
+    s->stats.kernel_launches += 1;
+    return B2_OK;
+}
+
 extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     ApiScope _scope("b2_session_create");
     B2_CHECK(m && out, B2_EINVAL, "b2_session_create: NULL");
@@ -593,6 +674,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         b2_session_destroy(s);
         return B2_ECUDA;
     }
+    const char *mg = getenv("B2_MEGA");
+    if (mg && mg[0] == '1') s->use_mega = build_mega_plan(s);
     *out = s;
     return B2_OK;
 }
@@ -601,6 +684,8 @@ extern "C" int b2_session_destroy(b2_session *s) {
     if (!s) return B2_OK;
     if (s->m && s->m->e) cudaSetDevice(s->m->e->device);
     drop_graphs(s);
+    mega_forget(s);
+    delete s->plan;
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->logits_log) cudaFree(s->logits_log);
@@ -678,8 +763,12 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1, s->host_pos));
-    B2_TRY(run_graph(s, G_PREFILL_LAST, 1, s->host_pos + n - 1));
+    if (s->use_mega) {
+        B2_TRY(run_mega(s, MEGA_PROMPT, n, n - 1, nullptr));
+    } else {
+        if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1, s->host_pos));
+        B2_TRY(run_graph(s, G_PREFILL_LAST, 1, s->host_pos + n - 1));
+    }
     B2_CUDA(cudaEventRecord(s->ev1, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits, (size_t)V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
@@ -705,7 +794,8 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
     if (logits_out) B2_TRY(ensure_log(s, (uint64_t)n_steps * V));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps, s->host_pos));
+    if (s->use_mega) B2_TRY(run_mega(s, MEGA_DECODE, n_steps, 0, logits_out ? s->logits_log : nullptr));
+    else B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps, s->host_pos));
     B2_CUDA(cudaEventRecord(s->ev1, st));
     B2_CUDA(cudaMemcpyAsync(out_tokens, s->d_out_tokens, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n_steps * V * 4, cudaMemcpyDeviceToHost, st));
@@ -730,7 +820,8 @@ extern "C" int b2_forward_tokens(b2_session *s, const int32_t *tokens, int n, fl
     B2_TRY(ensure_log(s, (uint64_t)n * V));
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
-    B2_TRY(run_graph(s, G_FORCED, n, s->host_pos));
+    if (s->use_mega) B2_TRY(run_mega(s, MEGA_PROMPT, n, 0, s->logits_log));
+    else B2_TRY(run_graph(s, G_FORCED, n, s->host_pos));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n * V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
     s->host_pos += n;

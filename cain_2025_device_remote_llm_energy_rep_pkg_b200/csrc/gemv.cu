@@ -63,22 +63,13 @@ __global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t 
 void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st) {
     k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out);
 }
-// one row of a packed matrix, dequantised (token embedding lookup and tests)
-__device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int64_t col, int64_t nbp) {
-    PackedLoc loc = packed_loc(row, col / QK, nbp);
-    int e = (int)(col % QK);
-    uint32_t word = *(const uint32_t *)(w + loc.word0 + ((e & 15) >> 2) * 16);
-    int nib = (word >> (8 * (e & 3) + ((e >> 4) << 2))) & 0xF;    // two's complement of q-8
-    int v = (nib ^ 8) - 8;
-    return (float)v * __half2float(__ushort_as_half(*(const uint16_t *)(w + loc.scale)));
-}
-
 // ------------------------------------------------------------------------------------------ the kernel
 template <int IN, int OUT>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint32_t parity = 0;
-    gemv_phase<IN, OUT, false>(a, smem, parity);
+    const GemvPtrs pv = {a.w, a.norm_w, a.bias_or_res};
+    gemv_phase<IN, OUT, false>(a, pv, smem, parity);
 }
 
 // ------------------------------------------------------------------------------------------ launcher
@@ -119,13 +110,12 @@ static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStre
     return cudaLaunchKernelEx(&cfg, k_gemv<IN, OUT>, a);
 }
 
-// in_mode IN_NORM: (x, norm_w, eps, plus_one) ; IN_ACT: act_in.  out_mode selects the epilogue.
-// next_w / next_bytes: the packed matrix the following kernel streams (L2 prefetch hint), or nullptr.
-cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
-                        float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
-                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
-                        float *xsq_out, cudaStream_t st, bool pdl) {
-    GemvArgs a = {};
+// Fill the argument block of one GEMV (everything but the debug pointer) and report the dynamic shared memory it needs.
+cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
+                           float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
+                           float *pmax, int *pidx, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n, float *xsq_out,
+                           size_t *smem_out) {
+    a = GemvArgs{};
     a.xsq_in = xsq_in; a.xsq_n = xsq_n; a.xsq_out = xsq_out;
     a.w = (const uint8_t *)d_packed;
     a.rows = (int)rows;
@@ -146,15 +136,29 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     }
     a.l2_window = (uint32_t)env_win;
     a.pf_bytes = (uint32_t)env_pf;
+    a.k_outer = (a.nbp + KC - 1) / KC > 2;
+    const size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
+    if (smem > 227 * 1024) return cudaErrorInvalidValue;
+    if (smem_out) *smem_out = smem;
+    return cudaSuccess;
+}
+
+// in_mode IN_NORM: (x, norm_w, eps, plus_one) ; IN_ACT: act_in.  out_mode selects the epilogue.
+// next_w / next_bytes: the packed matrix the following kernel streams (L2 prefetch hint), or nullptr.
+cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
+                        float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
+                        float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
+                        float *xsq_out, cudaStream_t st, bool pdl) {
+    GemvArgs a;
+    size_t smem = 0;
+    cudaError_t em = gemv_make_args(a, in_mode, d_packed, rows, cols, x, norm_w, eps, plus_one, act_in, y, bias_or_res, act_out, act, pmax, pidx,
+                                    next_w, next_bytes, xsq_in, xsq_n, xsq_out, &smem);
+    if (em != cudaSuccess) return em;
     a.dbg = g_gemv_dbg ? g_gemv_dbg + (size_t)(g_gemv_dbg_next++ % g_gemv_dbg_slots) * 148 * 8 : nullptr;
     int grid = gemv_grid(a.n_tiles, a.tile_align);
-    const int cpt = (a.nbp + KC - 1) / KC;
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
     int max_tiles = ((units + grid - 1) / grid) * a.tile_align;
-    a.k_outer = cpt > 2;
     if (grid_out) *grid_out = grid;
-    size_t smem = GEMV_FIXED_SMEM + (size_t)a.nbp * 100 + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
-    if (smem > 227 * 1024) return cudaErrorInvalidValue;
 #define CASE(I, O) if (in_mode == I && out_mode == O) return launch_one<I, O>(aa, grid, smem, st, pdl)
     if (!a.k_outer || max_tiles <= GEMV_MAXT) {
         const GemvArgs &aa = a;

@@ -5,7 +5,14 @@
 #include "layout.cuh"
 #include <cooperative_groups.h>
 
-__device__ __forceinline__ void grid_barrier() { cooperative_groups::this_grid().sync(); }
+// Grid-wide barrier of the persistent token kernel.  The proxy fences order this thread's ordinary loads/stores against the bulk
+// (async-proxy) copies issued on either side of the barrier: vectors written with st.global are read by cp.async.bulk after it,
+// and shared memory read with ld.shared before it is overwritten by cp.async.bulk after it.
+__device__ __forceinline__ void grid_barrier() {
+    asm volatile("fence.proxy.async;" ::: "memory");
+    cooperative_groups::this_grid().sync();
+    asm volatile("fence.proxy.async;" ::: "memory");
+}
 
 // ------------------------------------------------------------------------------------------ PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -51,6 +58,9 @@ __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, ui
 #define MMA_MAGIC_F 12582912.0f
 #define L2_PREFETCH_BYTES 0                  // of the NEXT kernel's weights, per CTA: off (measured: no gain once the own-stream window is on; B2_PF_NEXT re-enables)
 #define L2_WINDOW_BYTES (128 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
+#ifndef MMA_GROUP
+#define MMA_GROUP 2                          // independent MMAs in flight per warp before their results are scaled (4 costs 8 more registers)
+#endif
 #define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
 
 struct GemvArgs {
@@ -81,8 +91,33 @@ struct GemvArgs {
     uint32_t pf_bytes;       // bytes of the next kernel's weights each CTA pulls into L2 (0: off)
     long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
 };
+// The three pointers that differ from layer to layer travel beside the block: in the persistent kernel the block itself is a
+// __constant__ object shared by all layers (its fields are instruction operands; taking a per-layer copy would put it in local
+// memory, whose loads queue behind the weight stream).  The device code reads these three from GemvPtrs, never from GemvArgs.
+struct GemvPtrs {
+    const uint8_t *w;
+    const float *norm_w;
+    const float *bias_or_res;
+};
 enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2 };
 enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3 };
+
+// host side (gemv.cu): fill the argument block of one GEMV and report its dynamic shared memory
+cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
+                           float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
+                           float *pmax, int *pidx, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n, float *xsq_out,
+                           size_t *smem_out);
+
+// one row of a packed matrix, dequantised (token embedding lookup and tests)
+__device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int64_t col, int64_t nbp) {
+    PackedLoc loc = packed_loc(row, col / QK, nbp);
+    int e = (int)(col % QK);
+    uint32_t word = *(const uint32_t *)(w + loc.word0 + ((e & 15) >> 2) * 16);
+    int nib = (word >> (8 * (e & 3) + ((e >> 4) << 2))) & 0xF;    // two's complement of q-8
+    int v = (nib ^ 8) - 8;
+    return (float)v * __half2float(__ushort_as_half(*(const uint16_t *)(w + loc.scale)));
+}
+
 
 __device__ __forceinline__ float act_fn(float g, int act) {
     if (act == B2_ACT_SILU) return g / (1.0f + expf(-g));
@@ -112,20 +147,25 @@ __device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&
     const uint32_t bx[4] = {b.b01.x, b.b01.z, b.b23.x, b.b23.z}, by[4] = {b.b01.y, b.b01.w, b.b23.y, b.b23.w};
     const uint32_t sdw[4] = {r.sd.x, r.sd.y, r.sd.z, r.sd.w};
     const float asf[4] = {b.as.x, b.as.y, b.as.z, b.as.w};
-    int c[4][4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {   // four independent MMAs
-        c[j][0] = c[j][1] = c[j][2] = c[j][3] = MMA_MAGIC;
-        mma_s8(c[j], (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bx[j], by[j]);
-    }
+    for (int jh = 0; jh < 4; jh += MMA_GROUP) {   // MMA_GROUP independent MMAs at a time, then their scaling into the fp32 accumulators
+        int c[MMA_GROUP][4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {   // scale into the fp32 accumulators
-        const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
-        const float f0 = dd.x * asf[j], f1 = dd.y * asf[j];
-        acc[0] = fmaf(__int_as_float(c[j][0]) - MMA_MAGIC_F, f0, acc[0]);
-        acc[1] = fmaf(__int_as_float(c[j][1]) - MMA_MAGIC_F, f0, acc[1]);
-        acc[2] = fmaf(__int_as_float(c[j][2]) - MMA_MAGIC_F, f1, acc[2]);
-        acc[3] = fmaf(__int_as_float(c[j][3]) - MMA_MAGIC_F, f1, acc[3]);
+        for (int u = 0; u < MMA_GROUP; ++u) {
+            const int j = jh + u;
+            c[u][0] = c[u][1] = c[u][2] = c[u][3] = MMA_MAGIC;
+            mma_s8(c[u], (ua[j] << 4) & 0xF0F0F0F0u, (ub[j] << 4) & 0xF0F0F0F0u, ua[j] & 0xF0F0F0F0u, ub[j] & 0xF0F0F0F0u, bx[j], by[j]);
+        }
+#pragma unroll
+        for (int u = 0; u < MMA_GROUP; ++u) {
+            const int j = jh + u;
+            const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
+            const float f0 = dd.x * asf[j], f1 = dd.y * asf[j];
+            acc[0] = fmaf(__int_as_float(c[u][0]) - MMA_MAGIC_F, f0, acc[0]);
+            acc[1] = fmaf(__int_as_float(c[u][1]) - MMA_MAGIC_F, f0, acc[1]);
+            acc[2] = fmaf(__int_as_float(c[u][2]) - MMA_MAGIC_F, f1, acc[2]);
+            acc[3] = fmaf(__int_as_float(c[u][3]) - MMA_MAGIC_F, f1, acc[3]);
+        }
     }
 }
 // one piece of the stream: block-group column `warp` of the chunk at `ch` (cb blocks)
@@ -147,7 +187,7 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
 // for the block maximum) and writes its own block-groups of the shared-memory activation image.
 // Shared memory of the input area: [A3 image nbp*100][staging: fp32 vector n_in*4][xsq partials 1 KB]
 template <int IN>
-__device__ __forceinline__ void stage_warp_input(const GemvArgs &a, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
+__device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPtrs &pv, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
                                                  const float4 (&wn)[2]) {
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
         mbar_wait(bar, parity);
@@ -173,7 +213,7 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, uint8_t *sac
         if (q < n4) {
             const float4 v = ((const float4 *)sx)[q];
             if (IN == IN_NORM) {
-                const float4 w = ck < 2 ? wn[ck] : __ldg((const float4 *)a.norm_w + q);
+                const float4 w = ck < 2 ? wn[ck] : __ldg((const float4 *)pv.norm_w + q);
                 const float xs[4] = {v.x, v.y, v.z, v.w}, ws[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) yv[e] = __fmul_rn(__fmul_rn(xs[e], r), a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e]);
@@ -212,7 +252,7 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, uint8_t *sac
 // Two CTA-wide barriers per GEMV_RB tiles instead of one per tile: the weight streams of the sixteen warps are not
 // re-synchronised on memory latency every other piece.
 template <int OUT>
-__device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i,
+__device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or_res, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i,
                                          float &sumsq) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __syncthreads();
@@ -235,10 +275,10 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *h
         const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
         const int row = tile * TILE_ROWS + r;
         if (OUT == OUT_BIAS) {
-            if (lane < 16 && row < a.rows) a.y[row] = a.bias_or_res ? yv + a.bias_or_res[row] : yv;
+            if (lane < 16 && row < a.rows) a.y[row] = bias_or_res ? yv + bias_or_res[row] : yv;
         } else if (OUT == OUT_RES) {
             if (lane < 16 && row < a.rows) {
-                const float xn = __ldcg(a.bias_or_res + row) + yv;
+                const float xn = __ldcg(bias_or_res + row) + yv;
                 a.y[row] = xn;
                 sumsq = fmaf(xn, xn, sumsq);
             }
@@ -261,13 +301,14 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, float *red, float *h
 // previous kernel by griddepcontrol.wait).  MEGA = true: a phase of the persistent token kernel (mega.cu): ordered after the
 // previous phase by a grid-wide barrier; the mbarrier of the input copies lives across phases (bar_parity flips per use).
 template <int IN, int OUT, bool MEGA>
-__device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uint32_t &bar_parity) {
+__device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
     float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
     float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
     float *scratch = hbuf + GEMV_RB * 8;
     uint64_t *bar = (uint64_t *)(hbuf + 96);                                    // completion of the input copies
     uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector (+ fp32 staging, partials)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int bid = blockIdx.x;
     const int g = lane >> 2, t = lane & 3;
     if (!MEGA && tid == 0) {
         pdl_launch_dependents();
@@ -278,18 +319,18 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
         if (a.dbg && tid == 0) {
             long long tt;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
-            a.dbg[blockIdx.x * 8 + k] = tt;
+            a.dbg[bid * 8 + k] = tt;
         }
     };
     stamp(0);
 
     // contiguous, aligned share of the tiles
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
-    const int u0 = (int)(((uint32_t)units * blockIdx.x) / gridDim.x), u1 = (int)(((uint32_t)units * (blockIdx.x + 1)) / gridDim.x);
+    const int u0 = (int)(((uint32_t)units * bid) / gridDim.x), u1 = (int)(((uint32_t)units * (bid + 1)) / gridDim.x);
     const int t0 = u0 * a.tile_align, t1 = min(a.n_tiles, u1 * a.tile_align);
     const int nt = t1 - t0;
     const int cpt = (a.nbp + KC - 1) / KC;                                      // chunks per tile
-    const uint8_t *base = a.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
+    const uint8_t *base = pv.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
     const uint32_t tile_bytes = (uint32_t)a.nbp * BLOCK_BYTES;
     const int cb_last = a.nbp - (cpt - 1) * KC;                                 // blocks in the last chunk of a tile
     const bool act_full = warp < (KC >> 2);                                     // this warp has a block-group in a full chunk ...
@@ -315,7 +356,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
     auto prefetch_next = [&]() {
         if (lane == 0 && a.pf_ptr) {
             const uint64_t share = (a.pf_total / gridDim.x) & ~(uint64_t)127;
-            const uint8_t *p0 = a.pf_ptr + share * blockIdx.x;
+            const uint8_t *p0 = a.pf_ptr + share * bid;
             const uint64_t n = share < a.pf_bytes ? share : a.pf_bytes;
             for (uint64_t o = (uint64_t)warp * 16384; o + 16384 <= n; o += GEMV_CWARPS * 16384) l2_prefetch(p0 + o, 16384);
         }
@@ -330,7 +371,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
 #pragma unroll
             for (int ck = 0; ck < 2; ++ck) {
                 const int q = (ck * (KC / 4) + warp) * 32 + lane;
-                if (ck < cpt && q < (a.n_in >> 2)) wn[ck] = __ldg((const float4 *)a.norm_w + q);
+                if (ck < cpt && q < (a.n_in >> 2)) wn[ck] = __ldg((const float4 *)pv.norm_w + q);
             }
         }
         if (MEGA) grid_barrier();   // the previous phase is complete on every SM (this CTA's first weight loads are already in flight)
@@ -352,7 +393,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
         }
         stamp(2);   // everything from here reads what the previous kernel wrote (ld.global.cg: under programmatic
                       // dependent launch a CTA of that kernel may have shared this SM's L1)
-        stage_warp_input<IN>(a, sact, bar, bar_parity, cpt, warp, lane, wn);
+        stage_warp_input<IN>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn);
         bar_parity ^= 1;
         stamp(3);
         prefetch_next();   // the next kernel's weights start flowing HBM -> L2 while this kernel works through its own
@@ -368,12 +409,16 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == GEMV_RB) {
-            flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
+            flush_batch<OUT>(a, pv.bias_or_res, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
             batch_first += batch_n;
             batch_n = 0;
         }
     };
-    WPiece buf0, buf1, buf2, buf3;      // GEMV_DEPTH = 4 pieces in flight per warp
+    // GEMV_DEPTH = 4 pieces in flight per warp.  Defined on every path (a warp without work in a piece skips the load): a register
+    // that is read-before-written on some path counts as live around the enclosing token/layer loops of the persistent kernel,
+    // i.e. through every OTHER stage, and the stages then spill each other's pipelines.
+    const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+    WPiece buf0 = {z4, z4, z4}, buf1 = {z4, z4, z4}, buf2 = {z4, z4, z4}, buf3 = {z4, z4, z4};
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     if (!a.k_outer) {
         // ================= tiles outermost: the CTA's bytes are one contiguous run of chunks; K spans one or two chunks whose
@@ -480,7 +525,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
         if (two) park(acc1);
     }
     stamp(4);
-    if (batch_n > 0) flush_batch<OUT>(a, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
+    if (batch_n > 0) flush_batch<OUT>(a, pv.bias_or_res, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
     stamp(5);
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
         sumsq = warp_sum(sumsq);
@@ -491,7 +536,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
             float tot = 0.f;
 #pragma unroll
             for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
-            a.xsq_out[blockIdx.x] = tot;
+            a.xsq_out[bid] = tot;
         }
     }
     if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima
@@ -515,7 +560,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, uint8_t *smem, uin
                 int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
                 if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
             }
-            if (lane == 0) { a.pmax[blockIdx.x] = best_v; a.pidx[blockIdx.x] = best_i; }
+            if (lane == 0) { a.pmax[bid] = best_v; a.pidx[bid] = best_i; }
         }
     }
 }
