@@ -5,16 +5,32 @@
 #include "layout.cuh"
 #include <cooperative_groups.h>
 
-// Grid-wide barrier of the persistent token kernel.  The proxy fences order this thread's ordinary loads/stores against the bulk
-// (async-proxy) copies issued on either side of the barrier: vectors written with st.global are read by cp.async.bulk after it,
-// and shared memory read with ld.shared before it is overwritten by cp.async.bulk after it.
-__device__ __forceinline__ void grid_barrier() {
-    asm volatile("fence.proxy.async;" ::: "memory");
-    cooperative_groups::this_grid().sync();
-    asm volatile("fence.proxy.async;" ::: "memory");
+#ifdef MEGA_PROF
+// development aid (build with EXTRA=-DMEGA_PROF, tools/prof_mega.py): %globaltimer stamps of thread 0 of every CTA,
+// [stage sequence number][CTA][8]
+__constant__ long long *g_prof;   // constant bank: a stamp must not wait for a global load
+__constant__ int g_prof_cap;
+__shared__ int s_prof_seq;
+__device__ __forceinline__ void prof_stamp(int k) {
+    if (threadIdx.x == 0 && g_prof && s_prof_seq < g_prof_cap) {
+        long long tt;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+        g_prof[((size_t)s_prof_seq * gridDim.x + blockIdx.x) * 8 + k] = tt;
+    }
 }
+__device__ __forceinline__ void prof_next() { if (threadIdx.x == 0) s_prof_seq++; }
+#else
+__device__ __forceinline__ void prof_stamp(int) {}
+__device__ __forceinline__ void prof_next() {}
+#endif
 
-// ------------------------------------------------------------------------------------------ PTX helpers
+// Grid-wide barrier of the persistent token kernel.  Vectors written with st.global before it are read by cp.async.bulk (the
+// async proxy) after it: the thread that issues those copies runs proxy_fence_async() between the barrier and the copy, which
+// extends the ordering it acquired through the barrier to the async proxy.  (A fence in every thread on both sides of the
+// barrier cost 7 % of the kernel: it waits for all of the thread's outstanding memory operations.)
+__device__ __forceinline__ void grid_barrier() { cooperative_groups::this_grid().sync(); }
+__device__ __forceinline__ void proxy_fence_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *b, int count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
@@ -58,6 +74,9 @@ __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, ui
 #define MMA_MAGIC_F 12582912.0f
 #define L2_PREFETCH_BYTES 0                  // of the NEXT kernel's weights, per CTA: off (measured: no gain once the own-stream window is on; B2_PF_NEXT re-enables)
 #define L2_WINDOW_BYTES (128 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
+#ifndef MEGA_ORDER
+#define MEGA_ORDER 2                         // persistent kernel: 2 = barrier, staging, first register loads (see stage_input)
+#endif
 #ifndef MMA_GROUP
 #define MMA_GROUP 2                          // independent MMAs in flight per warp before their results are scaled (4 costs 8 more registers)
 #endif
@@ -191,12 +210,14 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
                                                  const float4 (&wn)[2]) {
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
         mbar_wait(bar, parity);
+        prof_stamp(6);
         return;
     }
     const float *sx = (const float *)(sact + (size_t)a.nbp * 100);
     const float *sq = sx + a.n_in;
     float *sscale = (float *)(sact + (size_t)a.nbp * 96);
     mbar_wait(bar, parity);
+    prof_stamp(6);
     float r = 1.0f;
     if (IN == IN_NORM) {
         float ss = 0.f;
@@ -316,6 +337,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     auto stamp = [&](int k) {
+        if (MEGA) { prof_stamp(k); return; }
         if (a.dbg && tid == 0) {
             long long tt;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
@@ -363,10 +385,11 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     };
 
     float sumsq = 0.f;
-    auto stage_input = [&]() {
+    // The norm weights of this warp's columns are immutable: they are fetched before waiting for the producer of the input.
+    float4 wn[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+    // Wait for the producer of the input vector and start its copy into shared memory (thread 0, cp.async.bulk onto `bar`).
+    auto input_wait_copy = [&]() {
         stamp(1);
-        // the norm weights of this warp's columns are immutable: fetch them before waiting for the previous kernel
-        float4 wn[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
         if (IN == IN_NORM) {
 #pragma unroll
             for (int ck = 0; ck < 2; ++ck) {
@@ -374,29 +397,65 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
                 if (ck < cpt && q < (a.n_in >> 2)) wn[ck] = __ldg((const float4 *)pv.norm_w + q);
             }
         }
-        if (MEGA) grid_barrier();   // the previous phase is complete on every SM (this CTA's first weight loads are already in flight)
+        if (MEGA) grid_barrier();   // the previous stage is complete on every SM
         else __syncthreads();       // everybody has issued its first weight loads; the mbarrier thread 0 initialised is visible
         if (tid == 0) {
-            if (!MEGA) pdl_wait();  // the copies below read what the previous kernel wrote
+            if (MEGA) proxy_fence_async();
+            else pdl_wait();        // the copies below read what the previous kernel wrote
+            // Every CTA copies the same vector at the same moment: each starts at a different 128-byte-aligned offset (and wraps
+            // around) so the 148 copies do not walk the L2 slices in lock step.
+            auto rot_copy = [&](uint8_t *dst, const uint8_t *src, uint32_t bytes) {
+                const uint32_t lines = bytes >> 7;
+                const uint32_t rot = MEGA && lines > 1 ? (((uint32_t)bid * 2654435761u) >> 8) % lines * 128u : 0u;
+                if (rot) {
+                    bulk_g2s(dst + rot, src + rot, bytes - rot, bar);
+                    bulk_g2s(dst, src, rot, bar);
+                } else {
+                    bulk_g2s(dst, src, bytes, bar);
+                }
+            };
             if (IN == IN_ACT) {
                 const uint32_t bytes = (uint32_t)a.nbp * 100;
                 mbar_expect_tx(bar, bytes);
-                bulk_g2s(sact, a.act_in, bytes, bar);
+                rot_copy(sact, a.act_in, bytes);
             } else {
                 float *sx = (float *)(sact + (size_t)a.nbp * 100);
                 const uint32_t bytes = (uint32_t)a.n_in * 4;
                 const uint32_t qbytes = IN == IN_NORM ? (uint32_t)((a.xsq_n + 3) & ~3) * 4 : 0;
                 mbar_expect_tx(bar, bytes + qbytes);
-                bulk_g2s(sx, IN == IN_NORM ? (const void *)a.x : (const void *)a.act_in, bytes, bar);
+                rot_copy((uint8_t *)sx, IN == IN_NORM ? (const uint8_t *)a.x : (const uint8_t *)a.act_in, bytes);
                 if (qbytes) bulk_g2s(sx + a.n_in, a.xsq_in, qbytes, bar);
             }
         }
         stamp(2);   // everything from here reads what the previous kernel wrote (ld.global.cg: under programmatic
                       // dependent launch a CTA of that kernel may have shared this SM's L1)
+    };
+    // Wait for the copy and put this warp's columns of the input on the activation grid.
+    auto input_stage = [&]() {
         stage_warp_input<IN>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn);
         bar_parity ^= 1;
         stamp(3);
-        prefetch_next();   // the next kernel's weights start flowing HBM -> L2 while this kernel works through its own
+    };
+    // Order of the first weight requests, the wait and the staging.  Stand-alone kernel: the requests go out first (weights
+    // never depend on the previous kernel) and are in flight while griddepcontrol.wait blocks.  Persistent kernel: before the
+    // grid barrier only the L2 prefetch of the CTA's first bytes is issued; the register loads follow the STAGING.  Measured
+    // (tools/prof_mega.py): shared-memory loads and stores of the staging complete in order behind the global loads this SM
+    // has in flight, and right after a barrier those wait in the HBM queue behind every SM's prefetch (staging took 2-9 us
+    // instead of ~0.5); issued after the staging, the register loads find their bytes in L2.
+    auto stage_input = [&](auto &&first_loads) {
+        if (MEGA && MEGA_ORDER == 2) {
+            input_wait_copy();
+            input_stage();
+            first_loads();
+        } else if (MEGA && MEGA_ORDER == 1) {
+            input_wait_copy();
+            first_loads();
+            input_stage();
+        } else {
+            first_loads();
+            input_wait_copy();
+            input_stage();
+        }
     };
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
@@ -445,8 +504,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
             if (l_rem > 0) { if (act_last) load_piece(lp, cb_last, warp, lane, r); lp += cb_last * BLOCK_BYTES; --l_rem; }
         };
         if (cpt == 2) {
-            load_full(buf0); load_last(buf1); load_full(buf2); load_last(buf3);     // the stream starts before the wait
-            stage_input();
+            stage_input([&]() { load_full(buf0); load_last(buf1); load_full(buf2); load_last(buf3); });
             BFrag bf0, bf1;
             load_b(0, bf0);
             load_b(1, bf1);
@@ -466,8 +524,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
                 l2_window();
             }
         } else {
-            load_last(buf0); load_last(buf1); load_last(buf2); load_last(buf3);
-            stage_input();
+            stage_input([&]() { load_last(buf0); load_last(buf1); load_last(buf2); load_last(buf3); });
             BFrag bf0;
             load_b(0, bf0);
             for (int rem = nt; rem > 0; rem -= 4) {
@@ -500,9 +557,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
         if (lane == 0 && a.l2_window) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
             for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
         }
-        load_step(buf0, buf1);
-        load_step(buf2, buf3);
-        stage_input();
+        stage_input([&]() { load_step(buf0, buf1); load_step(buf2, buf3); });
         BFrag bcur, bnxt;
         load_b(0, bcur);
         for (int ck = 0; ck < cpt; ck += 2) {
@@ -525,8 +580,12 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
         if (two) park(acc1);
     }
     stamp(4);
+    // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
+    // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
+    prefetch_next();
     if (batch_n > 0) flush_batch<OUT>(a, pv.bias_or_res, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
     stamp(5);
+    if (MEGA) prof_next();
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
         sumsq = warp_sum(sumsq);
         __syncthreads();

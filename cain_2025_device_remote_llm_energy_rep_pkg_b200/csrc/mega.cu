@@ -46,12 +46,16 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_token_loop(const MegaRun r)
         mbar_init(bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+#ifdef MEGA_PROF
+    if (tid == 0) s_prof_seq = 0;
+#endif
     __syncthreads();
     uint32_t parity = 0;
     for (int i = 0; i < r.n_tokens; ++i) {
         const int pos = r.pos0 + i;
         if (i > 0) grid_barrier();   // the LM head (or the last down-projection) of the previous token is complete
         // ---------------- token begin
+        prof_stamp(0);
         int cur;
         if (r.mode == MEGA_DECODE) {
             if (warp == 0) {
@@ -97,6 +101,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_token_loop(const MegaRun r)
                 for (int w = 0; w < GEMV_CWARPS; ++w) tot += scratch[w];
                 P.xsq[blockIdx.x] = tot;
             }
+            prof_stamp(5);
+            prof_next();
         }
         // ---------------- layers
         for (int l = 0; l < P.n_layers; ++l) {
@@ -114,9 +120,14 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_token_loop(const MegaRun r)
                 const int h = item / nsplit, split = item - h * nsplit;
                 const AttnSmem as = attn_carve((float *)(smem + GEMV_FIXED_SMEM) + grp * attn_group_floats(A.hd, A.pps_max), A.hd, A.pps_max);
                 __syncthreads();   // every warp of this CTA has left the QKV phase: its shared memory is free
+                prof_stamp(0);
                 if (active) attn_pages(A, as, gt, h, split, nsplit, pos);
+                prof_stamp(1);
                 grid_barrier();    // q, k, v of this token are complete
+                prof_stamp(2);
                 if (active) attn_main<MERGE_GLOBAL>(A, as, gt, h, split, nsplit, pos, 1 + grp);
+                prof_stamp(5);
+                prof_next();
             }
             {
                 gemv_stage<IN_ACT, OUT_RES, ST_O>(L.o_w, nullptr, nullptr, smem, parity);
@@ -183,4 +194,16 @@ cudaError_t launch_mega(const MegaPlan *host_plan, const void *owner, const Mega
     cfg.attrs = at;
     cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, k_token_loop, run);
+}
+
+// development aid: stamp buffer of the profiling build (EXTRA=-DMEGA_PROF); -1 in a normal build
+extern "C" int b2dbg_mega_profile(long long *d_buf, int cap_stages) {
+#ifdef MEGA_PROF
+    if (cudaMemcpyToSymbol(g_prof, &d_buf, sizeof d_buf) != cudaSuccess) return -2;
+    if (cudaMemcpyToSymbol(g_prof_cap, &cap_stages, sizeof cap_stages) != cudaSuccess) return -2;
+    return 0;
+#else
+    (void)d_buf; (void)cap_stages;
+    return -1;
+#endif
 }
