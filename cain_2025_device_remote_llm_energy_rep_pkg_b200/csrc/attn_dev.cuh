@@ -85,10 +85,59 @@ __device__ __forceinline__ void attn_pages(const AttnArgs &a, const AttnSmem &s,
     }
 }
 
+// What an item can fetch before the producer of qkv has finished (stand-alone kernel: before griddepcontrol.wait): the RoPE
+// table row of this position, and the cached K rows (first four pages of the item's range) and V rows (first eight tokens per
+// thread) of OLDER tokens.  With contexts up to 64 positions per split that is everything but q and the newest k/v, so the
+// critical path after the wait is one L2 round trip for q plus arithmetic, not three dependent round trips.
+struct AttnRegs {
+    float c, s;        // cos/sin of this thread's rotation pair (threads < hd/2)
+    uint4 kv[4][4];    // phase 1, first batch: [page][chunk]
+    uint4 vv[8];       // phase 2, first batch
+};
+__device__ __forceinline__ void attn_preload(const AttnArgs &a, const AttnSmem &s, int tid, int h, int split, int nsplit, int pos, int bar_id, AttnRegs &R) {
+    const int hd = a.hd, half = hd >> 1;
+    const int kvh = h / (a.nh / a.nkv);
+    const int n_ctx = pos + 1;
+    const int n_pages = (n_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const int pps = (n_pages + nsplit - 1) / nsplit;
+    const int p0 = split * pps, p1 = min(n_pages, p0 + pps);
+    const int t0 = p0 * PAGE_TOKENS, t1 = min(n_ctx, p1 * PAGE_TOKENS);
+    const int nt = max(0, t1 - t0);
+    R.c = 1.f; R.s = 0.f;
+    if (tid < half) {   // the loops below give pair j to thread j % 128: hd <= 256
+        R.c = __ldg(a.cs + (int64_t)pos * half + tid);
+        R.s = __ldg(a.sn + (int64_t)pos * half + tid);
+    }
+    group_sync(bar_id);   // page ids (attn_pages) are in shared memory
+    const int key = tid >> 3, sub = tid & 7, nchunk = hd >> 3;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int p = p0 + u, tk = p * PAGE_TOKENS + key;
+        const bool ld = p < p1 && tk < n_ctx && tk != pos;
+        const __half *kr = a.kc + (((int64_t)(ld ? s.spage[p - p0] : 0) * a.nkv + kvh) * PAGE_TOKENS + key) * hd;
+#pragma unroll
+        for (int c4 = 0; c4 < 4; ++c4) {
+            const int c = sub + 8 * c4;
+            R.kv[u][c4] = make_uint4(0u, 0u, 0u, 0u);
+            if (ld && c < nchunk) R.kv[u][c4] = __ldcg((const uint4 *)(kr + c * 8));
+        }
+    }
+    const int tpt = hd >> 3, ngrp = 128 / tpt;
+    const int grp = tid / tpt, dq = tid - grp * tpt;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const int i = grp + u * ngrp, tk = t0 + i;
+        R.vv[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (grp < ngrp && i < nt && tk != pos)
+            R.vv[u] = __ldcg((const uint4 *)(a.vc + (((int64_t)s.spage[tk / PAGE_TOKENS - p0] * a.nkv + kvh) * PAGE_TOKENS + (tk % PAGE_TOKENS)) * hd + dq * 8));
+    }
+}
+
 // Part 2: RoPE on q (and on the new k), KV append, scores, softmax, weighted values, merge of the splits, activation grid.
 // All 128 threads of the group call it with the same (h, split, nsplit, pos).
-template <int MERGE>
-__device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, int tid, int h, int split, int nsplit, int pos, int bar_id) {
+// PRE: the first batches of K and V and the RoPE row were fetched by attn_preload into R.
+template <int MERGE, bool PRE>
+__device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, int tid, int h, int split, int nsplit, int pos, int bar_id, AttnRegs &R) {
     const int hd = a.hd, half = hd >> 1;
     float *sq = s.sq, *part = s.part, *og = s.og, *sc = s.sc, *red = s.red;
     __half *knew = s.knew, *vnew = s.vnew;
@@ -106,7 +155,7 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
     // ---- RoPE on the query (every split), on the new key (the split that owns position pos)
     const float *cs = a.cs + (int64_t)pos * half, *sn = a.sn + (int64_t)pos * half;
     for (int j = tid; j < half; j += 128) {
-        const float c = cs[j], sv = sn[j];
+        const float c = PRE ? R.c : cs[j], sv = PRE ? R.s : sn[j];
         const float qa = __ldcg(a.qkv + (int64_t)h * hd + j), qb = __ldcg(a.qkv + (int64_t)h * hd + j + half);   // L2: written by the previous kernel/phase
         sq[j] = __fsub_rn(__fmul_rn(qa, c), __fmul_rn(qb, sv));
         sq[j + half] = __fadd_rn(__fmul_rn(qb, c), __fmul_rn(qa, sv));
@@ -136,18 +185,17 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int p = pb + u, tk = p * PAGE_TOKENS + key;
-            if (p < p1 && tk < n_ctx) {
-                const bool fresh = tk == pos;
-                const __half *kr = fresh ? knew : a.kc + (((int64_t)spage[p - p0] * a.nkv + kvh) * PAGE_TOKENS + key) * hd;
+            const bool valid = p < p1 && tk < n_ctx, fresh = tk == pos;
+            const bool pre = PRE && pb == p0;   // older tokens of the first batch are already in registers
+            const __half *kr = fresh ? knew : a.kc + (((int64_t)((valid && !pre) ? spage[p - p0] : 0) * a.nkv + kvh) * PAGE_TOKENS + key) * hd;
 #pragma unroll
-                for (int c4 = 0; c4 < 4; ++c4) {
-                    const int c = sub + 8 * c4;
-                    kv[u][c4] = make_uint4(0u, 0u, 0u, 0u);   // defined on every path (see the note on buf0..3 in gemv_dev.cuh)
-                    if (c < nchunk) kv[u][c4] = fresh ? *(const uint4 *)(kr + c * 8) : __ldcg((const uint4 *)(kr + c * 8));
+            for (int c4 = 0; c4 < 4; ++c4) {
+                const int c = sub + 8 * c4;
+                kv[u][c4] = pre ? R.kv[u][c4] : make_uint4(0u, 0u, 0u, 0u);   // defined on every path (see the note on buf0..3 in gemv_dev.cuh)
+                if (valid && c < nchunk) {
+                    if (fresh) kv[u][c4] = *(const uint4 *)(kr + c * 8);
+                    else if (!pre) kv[u][c4] = __ldcg((const uint4 *)(kr + c * 8));
                 }
-            } else {
-#pragma unroll
-                for (int c4 = 0; c4 < 4; ++c4) kv[u][c4] = make_uint4(0u, 0u, 0u, 0u);
             }
         }
 #pragma unroll
@@ -206,11 +254,12 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const int i = ib + u * ngrp;
-                vv[u] = make_uint4(0u, 0u, 0u, 0u);
+                const bool pre = PRE && ib == grp;
+                vv[u] = pre ? R.vv[u] : make_uint4(0u, 0u, 0u, 0u);
                 if (i < nt) {
                     const int tk = t0 + i;
                     if (tk == pos) vv[u] = *(const uint4 *)(vnew + dq * 8);
-                    else
+                    else if (!pre)
                         vv[u] = __ldcg((const uint4 *)(a.vc + (((int64_t)spage[tk / PAGE_TOKENS - p0] * a.nkv + kvh) * PAGE_TOKENS + (tk % PAGE_TOKENS)) * hd + dq * 8));
                 }
             }
