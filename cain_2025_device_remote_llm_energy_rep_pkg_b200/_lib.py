@@ -74,6 +74,7 @@ SIGNATURES = {
     "b2_op_gemv": (i32, [i32, vp, i64, i64, vp, vp, i32, i32, vp]),
     "b2_op_gemv_f32": (i32, [i32, vp, i64, i64, vp, vp, i32, vp]),
     "b2_op_norm_gemv": (i32, [i32, vp, i64, i64, vp, vp, f32, i32, vp, i32, i32, vp, vp, vp]),
+    "b2_op_prefill_gemm": (i32, [i32, vp, i64, i64, vp, i32, vp, f32, i32, vp, i32, i32, vp]),
     "b2_op_rope_kv": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32]),
     "b2_op_attn_decode": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, i32, vp]),
     "b2_op_attn_fused": (i32, [vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, i32, i32, vp, vp]),

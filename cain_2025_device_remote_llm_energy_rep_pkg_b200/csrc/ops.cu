@@ -2,6 +2,7 @@
 // tests, bench.py and ncu can drive each stage of the decode path in isolation; the engine (engine.cu)
 // calls the same launchers on its own stream.
 #include "kernels.cuh"
+#include "prefill.cuh"
 #include "layout.cuh"
 #include "sampler.cuh"
 
@@ -188,6 +189,37 @@ extern "C" int b2_op_sample_topk(const float *d_logits, int64_t n, int top_k, fl
     }
     cudaFree(scratch);
     if (rc) return rc;
+    B2_CUDA(e);
+    return B2_OK;
+}
+
+// Batched form of b2_op_norm_gemv / b2_op_gemv_f32 for M tokens (the prompt-evaluation GEMM on tcgen05 tensor cores, prefill.cu):
+// y[m] = W * grid(RMSNorm(x[m]))  (d_norm_w NULL: no norm) with mode 0 (+bias[rows], may be NULL), 1 (+res[m][rows]) or
+// 2 (act(gate)*up, y has rows/2 columns).  x is [M][cols], y [M][rows or rows/2], both dense row-major.
+extern "C" int b2_op_prefill_gemm(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, int M, const float *d_norm_w,
+                                  float eps, int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y) {
+    ApiScope _scope("b2_op_prefill_gemm");
+    B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "b2_op_prefill_gemm: type %d not supported", type);
+    B2_CHECK(d_packed && d_x && d_y && rows > 0 && cols > 0 && cols % QK == 0 && M > 0, B2_EINVAL, "b2_op_prefill_gemm: bad arguments");
+    B2_CHECK(mode >= 0 && mode <= 2, B2_EINVAL, "b2_op_prefill_gemm: mode %d", mode);
+    B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_prefill_gemm: mode 1 needs the residual matrix");
+    B2_CHECK(mode != 2 || rows % 2 == 0, B2_EINVAL, "b2_op_prefill_gemm: mode 2 needs an even number of rows");
+    int dev = 0, sms = 0;
+    B2_CUDA(cudaGetDevice(&dev));
+    B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    void *pb = nullptr;
+    B2_CUDA(cudaMalloc(&pb, pb_bytes(64, cols)));
+    const int64_t ldy = mode == 2 ? rows / 2 : rows;
+    cudaError_t e = cudaSuccess;
+    for (int m0 = 0; m0 < M && e == cudaSuccess; m0 += 64) {
+        const int mb = M - m0 < 64 ? M - m0 : 64, T = pf_batch(mb);
+        e = launch_prefill_quant(d_norm_w ? PF_IN_NORM : PF_IN_F32, d_x + (int64_t)m0 * cols, cols, mb, T, cols, d_norm_w, eps, plus_one, pb, 0);
+        if (e == cudaSuccess)
+            e = launch_prefill_gemm(mode, d_packed, rows, cols, pb, mb, T, d_y + (int64_t)m0 * ldy, ldy,
+                                    mode == 1 ? d_bias_or_res + (int64_t)m0 * ldy : d_bias_or_res, act, sms, 0);
+    }
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaFree(pb);
     B2_CUDA(e);
     return B2_OK;
 }

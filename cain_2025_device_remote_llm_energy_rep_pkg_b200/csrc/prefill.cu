@@ -1,0 +1,335 @@
+// prefill.cu — batched prompt evaluation on tcgen05 tensor cores (see prefill.cuh for the data layout and the numerics).
+//
+// k_prefill_gemm: one CTA per SM, persistent over groups of 128 weight rows; ten warps in four roles:
+//   warps 4-7  stream the packed Q4_0 rows of the group from HBM (the decode layout, layout.cuh), turn the nibbles into int8
+//              (16*(q-8): nibble in the high half of the byte) and store them in shared memory as the A operand
+//              (K-major core matrices), one block-group (4 blocks = 128 k) per stage, with the rows' f16 scales as floats
+//   warp 9     copies the B operand of the stage (activation digits of T tokens, already in operand layout) and the
+//              activation scales with cp.async.bulk
+//   warp 8     one thread issues tcgen05.mma.kind::i8 (M=128, N=3T, K=32) per block, accumulate OFF, into one of two tensor-memory
+//              buffers and commits to mbarriers
+//   warps 0-3  read the int32 dot products with tcgen05.ld (thread = weight row, one TMEM lane quadrant per warp), combine the
+//              three digit planes, scale by d_w * s_act and accumulate T fp32 sums per thread; after the last block they apply
+//              the epilogue (+bias, +residual, act(gate)*up) and write y
+// The per-block scales of Q4_0 are the reason the accumulation across K cannot stay in tensor memory.
+#include "prefill.cuh"
+#include "gemv_dev.cuh"
+
+// ------------------------------------------------------------------------------------------ activation batch -> PB
+template <int IN>
+__global__ void __launch_bounds__(256) k_prefill_quant(const float *__restrict__ x, int64_t ldx, int M, int T, int n, int nbp,
+                                                       const float *__restrict__ norm_w, float eps, int plus_one, uint8_t *__restrict__ pb) {
+    __shared__ float red[8];
+    __shared__ float s_r;
+    const int m = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    float *sa = (float *)(pb + pb_scale_off(T, nbp));
+    const bool live = m < M;
+    const float *xr = x + (int64_t)(live ? m : 0) * ldx;
+    float r = 1.0f;
+    if (IN == PF_IN_NORM && live) {
+        float ss = 0.f;
+        for (int i = tid; i < n; i += 256) { const float v = xr[i]; ss = fmaf(v, v, ss); }
+        ss = warp_sum(ss);
+        if (lane == 0) red[warp] = ss;
+        __syncthreads();
+        if (tid == 0) {
+            float tot = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) tot += red[w];
+            s_r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)n), eps)));   // op order of oracle/model.py:_norm
+        }
+        __syncthreads();
+        r = s_r;
+    }
+    for (int kb = warp; kb < nbp; kb += 8) {
+        const int i = kb * QK + lane;
+        float y = 0.f;
+        if (live && i < n) {
+            y = xr[i];
+            if (IN == PF_IN_NORM) {
+                const float w = norm_w[i];
+                y = __fmul_rn(__fmul_rn(y, r), plus_one ? __fadd_rn(1.0f, w) : w);
+            }
+        }
+        float sc;
+        const int X = act_grid_lane(y, sc);
+        int d0, d1, d2;
+        act_digits(X, d0, d1, d2);
+        pb[pb_off(T, kb, 0, m, lane)] = (uint8_t)d0;
+        pb[pb_off(T, kb, 1, m, lane)] = (uint8_t)d1;
+        pb[pb_off(T, kb, 2, m, lane)] = (uint8_t)d2;
+        if (lane == 0) sa[(int64_t)kb * T + m] = (live && kb * QK < n) ? sc * 0.0625f : 0.f;
+    }
+}
+
+cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M, int T, int64_t n, const float *norm_w, float eps, int plus_one,
+                                 void *pb, cudaStream_t st) {
+    if (M <= 0 || M > T || (T != 16 && T != 32 && T != 64) || n <= 0) return cudaErrorInvalidValue;
+    const int nbp = (int)nblocks_padded(n);
+    if (in_mode == PF_IN_NORM) k_prefill_quant<PF_IN_NORM><<<T, 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, norm_w, eps, plus_one, (uint8_t *)pb);
+    else k_prefill_quant<PF_IN_F32><<<T, 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, nullptr, 0.f, 0, (uint8_t *)pb);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------ tcgen05 helpers
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t cols) {   // one whole warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {      // the same warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem] = A[smem] * B[smem], int8 x int8 -> int32, M = 128, K = 32 (one 32-element block), no accumulate
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(0u), "r"(0u) : "memory");
+}
+// the mbarrier gets one arrival when every MMA this thread has issued so far has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 16 consecutive 32-bit columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld16(uint32_t addr, int (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                   "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// shared-memory matrix descriptor: K-major, no swizzle; core matrix = 8 rows x 16 bytes (128 contiguous bytes), the two 16-byte
+// K halves of a 32-byte row 128 bytes apart (leading-dimension offset), 8-row groups 256 bytes apart (stride offset)
+__device__ __forceinline__ uint64_t umma_desc(const void *smem) {
+    return (uint64_t)((smem_u32(smem) >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46);
+}
+// instruction descriptor: D s32, A and B signed int8, both K-major, N = n, M = 128
+__host__ __device__ inline uint32_t umma_idesc_i8(int n) {
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(PF_ROWS >> 4) << 24);
+}
+
+struct PfArgs {
+    const uint8_t *w;        // packed Q4_0 matrix (layout.cuh)
+    int rows, nbp, n_tiles;
+    const uint8_t *pb;       // B operand of the batch (prefill.cuh)
+    int M;                   // live tokens (<= T)
+    float *y;
+    int64_t ldy;
+    const float *bias_or_res;
+    int act;
+};
+
+// shared memory: [A stages: PF_STAGES x 4 blocks x 4 KB][B stages: PF_STAGES x 4 x N*32][dw: PF_STAGES x 4 x 128 floats]
+//                [sa: PF_STAGES x 4 x T floats][barriers]
+template <int T>
+struct PfSmem {
+    static constexpr int N = 3 * T;
+    static constexpr int A_STAGE = 4 * PF_ROWS * 32;
+    static constexpr int B_STAGE = 4 * N * 32;
+    static constexpr int A_OFF = 0;
+    static constexpr int B_OFF = A_OFF + PF_STAGES * A_STAGE;
+    static constexpr int DW_OFF = B_OFF + PF_STAGES * B_STAGE;
+    static constexpr int SA_OFF = DW_OFF + PF_STAGES * 4 * PF_ROWS * 4;
+    static constexpr int BAR_OFF = SA_OFF + PF_STAGES * 4 * T * 4;
+    static constexpr int TOTAL = BAR_OFF + 128;
+};
+
+template <int T, int OUT>
+__global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) {
+    using S = PfSmem<T>;
+    constexpr int N = S::N;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t *full = (uint64_t *)(smem + S::BAR_OFF);   // [stage] A unpacked (4 warp arrivals) + B copied (1 arrival + bytes)
+    uint64_t *empty = full + PF_STAGES;                 // [stage] MMAs of the stage done (commit) + scales read (4 epilogue warps)
+    uint64_t *tfull = empty + PF_STAGES;                // [buf]   dot products of one block are in tensor memory
+    uint64_t *tempty = tfull + 2;                       // [buf]   the four epilogue warps have read them
+    uint32_t *tmem_ptr = (uint32_t *)(tempty + 2);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < PF_STAGES; ++s) { mbar_init(full + s, 5); mbar_init(empty + s, 5); }
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 8) tmem_alloc(tmem_ptr, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_ptr;
+    const int n_groups = (a.n_tiles + 7) >> 3;
+    const int nbg = a.nbp >> 2;   // block-groups (stages) along K
+
+    if (warp < 4) {
+        // ===================== epilogue: thread = weight row, T fp32 sums
+        const int row_l = warp * 32 + lane;
+        const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
+        int it = 0, kbi = 0;
+        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+            float acc[T];
+#pragma unroll
+            for (int m = 0; m < T; ++m) acc[m] = 0.f;
+            for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+                const int slot = it % PF_STAGES;
+                const float *dws = (const float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
+                const float *sas = (const float *)(smem + S::SA_OFF) + slot * 4 * T;
+                mbar_wait(full + slot, (it / PF_STAGES) & 1);   // scales of the stage are in shared memory
+#pragma unroll 1
+                for (int b = 0; b < 4; ++b, ++kbi) {
+                    const int buf = kbi & 1;
+                    mbar_wait(tfull + buf, (kbi >> 1) & 1);
+                    tc_fence_after();
+                    const float dw = dws[b * PF_ROWS + row_l];
+#pragma unroll
+                    for (int t0 = 0; t0 < T; t0 += 16) {
+                        int c0[16], c1[16], c2[16];
+                        tmem_ld16(tlane + buf * 256 + t0, c0);
+                        tmem_ld16(tlane + buf * 256 + T + t0, c1);
+                        tmem_ld16(tlane + buf * 256 + 2 * T + t0, c2);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) {
+                            const float xf = fmaf(16384.0f, (float)c2[u], fmaf(128.0f, (float)c1[u], (float)c0[u]));
+                            acc[t0 + u] = fmaf(xf, dw * sas[b * T + t0 + u], acc[t0 + u]);
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty + buf);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty + slot);
+            }
+            const int row = grp * PF_ROWS + row_l;
+#pragma unroll
+            for (int m = 0; m < T; ++m) {
+                if (m < a.M) {   // uniform
+                    if (OUT == PF_OUT_ACTMUL) {   // rows (2j, 2j+1) = (gate_j, up_j)
+                        const float up = __shfl_down_sync(0xffffffffu, acc[m], 1);
+                        if (!(row & 1) && row < a.rows) a.y[(int64_t)m * a.ldy + (row >> 1)] = act_fn(acc[m], a.act) * up;
+                    } else if (row < a.rows) {
+                        if (OUT == PF_OUT_RES) a.y[(int64_t)m * a.ldy + row] = a.bias_or_res[(int64_t)m * a.ldy + row] + acc[m];
+                        else a.y[(int64_t)m * a.ldy + row] = a.bias_or_res ? acc[m] + a.bias_or_res[row] : acc[m];
+                    }
+                }
+            }
+        }
+    } else if (warp < 8) {
+        // ===================== weights: packed nibbles -> int8 A operand.  Warp lw unpacks (tile, half) pairs 4*lw .. 4*lw+3 of the
+        // group; lane (g, t) holds word t of four consecutive blocks of tile row half*8 + g (one LDG.128, as the decode GEMV).
+        const int lw = warp - 4, g = lane >> 2, t = lane & 3;
+        int it = 0;
+        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+            for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+                const int slot = it % PF_STAGES;
+                const int ck = bgi >> 4, j = bgi & 15;
+                const int cb = min(KC, a.nbp - ck * KC);
+                uint4 v[4];
+                uint32_t sc[2] = {0u, 0u};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1, tg = grp * 8 + til;
+                    v[i] = make_uint4(0u, 0u, 0u, 0u);
+                    if (tg < a.n_tiles) {
+                        const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES;
+                        v[i] = ldg_stream4(chunk + (size_t)j * 1024 + hf * 512 + lane * 16);
+                        if (hf == 0) sc[i >> 1] = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * 128 + lane * 4));
+                    }
+                }
+                mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
+                uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
+                float *dws = (float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1;
+                    const uint32_t wd[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+                    uint8_t *dst = As + (til * 2 + hf) * 256 + g * 16 + t * 4;
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        *(uint32_t *)(dst + jj * 4096) = (wd[jj] << 4) & 0xF0F0F0F0u;        // elements 4t..4t+3   (k half 0)
+                        *(uint32_t *)(dst + jj * 4096 + 128) = wd[jj] & 0xF0F0F0F0u;         // elements 16+4t..    (k half 1)
+                    }
+                    if (hf == 0) {   // lane = (row g, block jj = t): half2 = (d of row g, d of row g+8)
+                        const float2 d2 = __half22float2(*(const __half2 *)&sc[i >> 1]);
+                        dws[t * PF_ROWS + til * 16 + g] = d2.x;
+                        dws[t * PF_ROWS + til * 16 + g + 8] = d2.y;
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tensor core reads these stores through the async proxy
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full + slot);
+            }
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issue (one thread)
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_i8(N);
+            int it = 0, kbi = 0;
+            for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+                for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+                    const int slot = it % PF_STAGES;
+                    mbar_wait(full + slot, (it / PF_STAGES) & 1);
+                    tc_fence_after();
+                    const uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE, *Bs = smem + S::B_OFF + slot * S::B_STAGE;
+#pragma unroll 1
+                    for (int b = 0; b < 4; ++b, ++kbi) {
+                        const int buf = kbi & 1;
+                        mbar_wait(tempty + buf, ((kbi >> 1) & 1) ^ 1);
+                        tc_fence_after();
+                        umma_i8(tmem + buf * 256, umma_desc(As + b * 4096), umma_desc(Bs + b * (N * 32)), idesc);
+                        umma_commit(tfull + buf);
+                    }
+                    umma_commit(empty + slot);
+                }
+            }
+        }
+    } else {
+        // ===================== B operand + activation scales of the stage: two bulk copies
+        if (lane == 0) {
+            const uint8_t *pbs = a.pb + pb_scale_off(T, a.nbp);
+            int it = 0;
+            for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+                for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+                    const int slot = it % PF_STAGES;
+                    mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
+                    mbar_expect_tx(full + slot, (uint32_t)(S::B_STAGE + 4 * T * 4));
+                    bulk_g2s(smem + S::B_OFF + slot * S::B_STAGE, a.pb + (size_t)bgi * S::B_STAGE, (uint32_t)S::B_STAGE, full + slot);
+                    bulk_g2s(smem + S::SA_OFF + slot * 4 * T * 4, pbs + (size_t)bgi * 4 * T * 4, (uint32_t)(4 * T * 4), full + slot);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) tmem_dealloc(tmem, 512);
+}
+
+template <int T, int OUT>
+static cudaError_t launch_pf(const PfArgs &a, int grid, cudaStream_t st) {
+    using S = PfSmem<T>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_prefill_gemm<T, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    k_prefill_gemm<T, OUT><<<grid, PF_THREADS, S::TOTAL, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
+                                const float *bias_or_res, int act, int sm_count, cudaStream_t st) {
+    if (M <= 0 || M > T || rows <= 0 || cols <= 0) return cudaErrorInvalidValue;
+    if (out_mode == PF_OUT_RES && !bias_or_res) return cudaErrorInvalidValue;
+    PfArgs a;
+    a.w = (const uint8_t *)d_packed; a.rows = (int)rows; a.nbp = (int)nblocks_padded(cols); a.n_tiles = (int)ntiles(rows);
+    a.pb = (const uint8_t *)pb; a.M = M; a.y = y; a.ldy = ldy; a.bias_or_res = bias_or_res; a.act = act;
+    const int n_groups = (a.n_tiles + 7) / 8;
+    const int grid = n_groups < sm_count ? n_groups : sm_count;
+#define PF_CASE(TT, OO) if (T == TT && out_mode == OO) return launch_pf<TT, OO>(a, grid, st)
+    PF_CASE(16, PF_OUT_BIAS); PF_CASE(16, PF_OUT_RES); PF_CASE(16, PF_OUT_ACTMUL);
+    PF_CASE(32, PF_OUT_BIAS); PF_CASE(32, PF_OUT_RES); PF_CASE(32, PF_OUT_ACTMUL);
+    PF_CASE(64, PF_OUT_BIAS); PF_CASE(64, PF_OUT_RES); PF_CASE(64, PF_OUT_ACTMUL);
+#undef PF_CASE
+    return cudaErrorInvalidValue;
+}

@@ -167,6 +167,11 @@ int b2_op_gemv_f32(int type, const void *d_packed, int64_t rows, int64_t cols, c
  * image of its result in d_act_out (b2_act_bytes(rows/2) bytes, may be NULL). */
 int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_norm_w, float eps,
                     int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y, void *d_act_out, int32_t *d_argmax);
+/* Batched form of b2_op_norm_gemv / b2_op_gemv_f32 for M prompt tokens: one pass over the weights on the tcgen05 tensor cores
+ * (prompt evaluation of Ollama's /api/generate; no reference file).  d_x [M][cols], d_norm_w NULL = no
+ * RMSNorm; mode 0: + d_bias_or_res[rows] (may be NULL); 1: + d_bias_or_res[M][rows]; 2: act(gate)*up, d_y is [M][rows/2]. */
+int b2_op_prefill_gemm(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, int M, const float *d_norm_w,
+                       float eps, int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y);
 /* RoPE (rotate-half) on q[nh,hd] in place and on k, then f16 append of k,v at position pos of a paged cache. */
 int b2_op_rope_kv(float *d_qkv, int nh, int nkv, int hd, int pos, const float *d_cos, const float *d_sin,
                   void *d_kcache, void *d_vcache, const int32_t *d_page_table, int page_tokens);
