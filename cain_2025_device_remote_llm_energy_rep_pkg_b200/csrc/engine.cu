@@ -3,12 +3,14 @@
 // experiment/RunnerConfig.py:128-131): model load, prompt evaluation, the batch-1 decode loop.
 #include "kernels.cuh"
 #include "mega.cuh"
+#include "prefill.cuh"
 #include "layout.cuh"
 #include "randinit.cuh"
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
+#include <algorithm>
 #include <vector>
 #include <string>
 #include <map>
@@ -87,6 +89,10 @@ struct b2_session {
     bool fused_attn = true;
     float *logits_log = nullptr;
     uint64_t logits_log_cap = 0;   // in floats
+    // batched prompt evaluation (prefill.cu): activations of up to 64 prompt tokens and the GEMM's B operand
+    float *pf_x = nullptr, *pf_qkv = nullptr, *pf_attn = nullptr, *pf_h = nullptr;
+    void *pf_pb = nullptr;
+    bool use_pf_gemm = true;
     // persistent token kernel (mega.cu): plan, grid and shared memory; use_mega = false falls back to one kernel per stage
     MegaPlan *plan = nullptr;
     bool use_mega = false;
@@ -631,6 +637,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     s->use_pdl = !(np && np[0] == '1');
     const char *nf = getenv("B2_NO_FUSED_ATTN");
     s->fused_attn = !(nf && nf[0] == '1');
+    const char *npg = getenv("B2_NO_PREFILL_GEMM");
+    s->use_pf_gemm = !(npg && npg[0] == '1');
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
     uint64_t kv_elems = (uint64_t)c.n_layers * s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     int rc = B2_OK;
@@ -656,6 +664,14 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->xsq, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(c.n_heads, hd)))) break;
         if ((rc = dev_alloc(s->allocs, &s->argmax_scratch, argmax_scratch_bytes()))) break;
+        if (s->use_pf_gemm) {
+            const int64_t widest = std::max<int64_t>(std::max<int64_t>(H, I), qd);
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_x, (uint64_t)64 * H * 4))) break;
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_qkv, (uint64_t)64 * (qd + 2 * kvd) * 4))) break;
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_attn, (uint64_t)64 * qd * 4))) break;
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_h, (uint64_t)64 * I * 4))) break;
+            if ((rc = dev_alloc(s->allocs, &s->pf_pb, pb_bytes(64, widest)))) break;
+        }
     } while (0);
     if (rc) { b2_session_destroy(s); return rc; }
     // physical pages are handed out in reverse order so the page-table indirection is always exercised
@@ -752,6 +768,52 @@ static int elapsed_ns(b2_session *s, uint64_t *ns) {
     return B2_OK;
 }
 
+// ------------------------------------------------------------------------------------ batched prompt evaluation
+// n prompt tokens (already in s->d_prompt) at positions host_pos.. : every weight matrix is read once per batch of up to 64 tokens
+// (tcgen05 GEMM, prefill.cu) instead of once per token; the LM head runs for the last token only, through the decode GEMV, and
+// leaves logits and arg-max partials exactly where b2_decode expects them.
+static int prefill_batched(b2_session *s, int n) {
+    b2_model *m = s->m;
+    const b2_arch_cfg &c = m->cfg;
+    cudaStream_t st = m->e->stream;
+    const int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim, sms = m->e->sm_count;
+    const int64_t ldq = qd + 2 * kvd;
+    const float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
+    const uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    int launches = 0;
+    for (int m0 = 0; m0 < n; m0 += 64) {
+        const int mb = n - m0 < 64 ? n - m0 : 64, T = pf_batch(mb), pos0 = s->host_pos + m0;
+        launch_prefill_embed(m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
+        for (int l = 0; l < c.n_layers; ++l) {
+            LayerW &ly = m->layers[l];
+            B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.attn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, st));
+            B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, c.n_heads, c.n_kv_heads, hd, pos0, m->rope_cos, m->rope_sin,
+                                             s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, s->pf_attn, qd, st));
+            B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_attn, qd, mb, T, qd, nullptr, 0.f, 0, s->pf_pb, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, st));
+            B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.ffn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, st));
+            B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_h, I, mb, T, I, nullptr, 0.f, 0, s->pf_pb, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, st));
+            launches += 10;
+        }
+        if (m0 + mb == n) {   // LM head for the last token of the prompt
+            B2_CUDA(cudaMemcpyAsync(s->x, s->pf_x + (int64_t)(mb - 1) * H, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
+            launch_sumsq(s->x, H, s->xsq, st);
+            launch_fill_partials(s->pmax, s->pidx, 1024, st);
+            int grid = 0;
+            B2_CUDA(launch_gemv(GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                                s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &grid, nullptr, 0, s->xsq, 1, nullptr, st, false));
+            if (!s->use_mega) s->head_grid = grid;
+            launches += 3;
+        }
+    }
+    B2_CUDA(cudaGetLastError());
+    s->stats.kernel_launches += (uint64_t)launches;
+    return B2_OK;
+}
+
 extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *logits_out) {
     ApiScope _scope("b2_prefill");
     B2_CHECK(s && tokens && n > 0, B2_EINVAL, "b2_prefill: bad arguments");
@@ -763,7 +825,9 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (s->use_mega) {
+    if (s->use_pf_gemm && n >= 3) {
+        B2_TRY(prefill_batched(s, n));
+    } else if (s->use_mega) {
         B2_TRY(run_mega(s, MEGA_PROMPT, n, n - 1, nullptr));
     } else {
         if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1, s->host_pos));

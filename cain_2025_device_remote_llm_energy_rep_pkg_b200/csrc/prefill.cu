@@ -333,3 +333,143 @@ cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows
 #undef PF_CASE
     return cudaErrorInvalidValue;
 }
+
+// ------------------------------------------------------------------------------------------ the other stages of a prompt batch
+// token embedding rows of M tokens (gemma: * sqrt(H)); grid (M)
+__global__ void __launch_bounds__(256) k_prefill_embed(const uint8_t *__restrict__ w, int64_t nbp, int n, const int *__restrict__ tokens, float scale,
+                                                       float *__restrict__ x) {
+    const int m = blockIdx.x;
+    const int64_t row = tokens[m];
+    for (int i = threadIdx.x; i < n; i += 256) {
+        float v = packed_elem(w, row, i, nbp);
+        if (scale != 1.0f) v = v * scale;
+        x[(int64_t)m * n + i] = v;
+    }
+}
+void launch_prefill_embed(const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st) {
+    k_prefill_embed<<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
+}
+
+// RoPE + KV append for M tokens at positions pos0..pos0+M-1: grid (nh + 2 nkv, M).  Same arithmetic as the decode kernels
+// (oracle/model.py:_rope): q rotated in place in the QKV batch, k rotated and v rounded to f16 into the paged cache.
+__global__ void __launch_bounds__(128) k_prefill_rope_kv(float *__restrict__ qkv, int64_t ld, int nh, int nkv, int hd, int pos0,
+                                                         const float *__restrict__ cs, const float *__restrict__ sn, __half *__restrict__ kc,
+                                                         __half *__restrict__ vc, const int32_t *__restrict__ page_table) {
+    const int m = blockIdx.y, pos = pos0 + m, h = blockIdx.x, half = hd >> 1;
+    const int page = page_table[pos / PAGE_TOKENS], slot = pos % PAGE_TOKENS;
+    float *base = qkv + (int64_t)m * ld;
+    if (h < nh + nkv) {
+        float *t = base + (int64_t)h * hd;   // q heads then k heads are contiguous in the fused QKV output
+        for (int j = threadIdx.x; j < half; j += blockDim.x) {
+            const float c = cs[(int64_t)pos * half + j], s = sn[(int64_t)pos * half + j];
+            const float a = t[j], b = t[j + half];
+            const float ra = __fsub_rn(__fmul_rn(a, c), __fmul_rn(b, s));
+            const float rb = __fadd_rn(__fmul_rn(b, c), __fmul_rn(a, s));
+            if (h < nh) {
+                t[j] = ra;
+                t[j + half] = rb;
+            } else {
+                __half *dst = kc + (((int64_t)page * nkv + (h - nh)) * PAGE_TOKENS + slot) * hd;
+                dst[j] = __float2half_rn(ra);
+                dst[j + half] = __float2half_rn(rb);
+            }
+        }
+    } else {
+        const int kvh = h - nh - nkv;
+        const float *t = base + (int64_t)(nh + nkv + kvh) * hd;
+        __half *dst = vc + (((int64_t)page * nkv + kvh) * PAGE_TOKENS + slot) * hd;
+        for (int j = threadIdx.x; j < hd; j += blockDim.x) dst[j] = __float2half_rn(t[j]);
+    }
+}
+
+// Causal attention of a prompt batch over the paged f16 cache: grid (nh, M), query (head h, token m) sees positions
+// [0, pos0 + m].  One CTA per query, scores in shared memory (max_ctx floats), fp32 softmax as in the decode kernel.
+__global__ void __launch_bounds__(128) k_prefill_attn(const float *__restrict__ qkv, int64_t ld, int nh, int nkv, int hd, int pos0,
+                                                      const __half *__restrict__ kc, const __half *__restrict__ vc,
+                                                      const int32_t *__restrict__ page_table, float *__restrict__ out, int64_t ldo) {
+    extern __shared__ float psm[];
+    float *sq = psm;          // hd
+    float *sc = psm + hd;     // n_ctx scores
+    __shared__ float red[4];
+    const int h = blockIdx.x, m = blockIdx.y, kvh = h / (nh / nkv);
+    const int n_ctx = pos0 + m + 1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_pages = (n_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
+    const float scale = 1.0f / sqrtf((float)hd);
+    for (int j = tid; j < hd; j += 128) sq[j] = qkv[(int64_t)m * ld + (int64_t)h * hd + j];
+    __syncthreads();
+    const int key = tid >> 3, sub = tid & 7, nchunk = hd >> 3;
+    float lmax = -INFINITY;
+    for (int p = 0; p < n_pages; ++p) {
+        const int t = p * PAGE_TOKENS + key;
+        const __half *kr = kc + (((int64_t)page_table[p] * nkv + kvh) * PAGE_TOKENS + key) * hd;
+        float dot = 0.f;
+        if (t < n_ctx) {
+            for (int c = sub; c < nchunk; c += 8) {
+                const uint4 raw = *(const uint4 *)(kr + c * 8);
+                const __half2 *h2 = (const __half2 *)&raw;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = __half22float2(h2[e]);
+                    dot = fmaf(sq[c * 8 + 2 * e], f.x, dot);
+                    dot = fmaf(sq[c * 8 + 2 * e + 1], f.y, dot);
+                }
+            }
+        }
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        if (t < n_ctx) {
+            const float s = dot * scale;
+            if (sub == 0) sc[t] = s;
+            lmax = fmaxf(lmax, s);
+        }
+    }
+    lmax = warp_max(lmax);
+    if (lane == 0) red[warp] = lmax;
+    __syncthreads();
+    const float mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+    __syncthreads();
+    float lsum = 0.f;
+    for (int i = tid; i < n_ctx; i += 128) {
+        const float pe = expf(sc[i] - mx);
+        sc[i] = pe;
+        lsum += pe;
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) red[warp] = lsum;
+    __syncthreads();
+    const float l = red[0] + red[1] + red[2] + red[3];
+    float o0 = 0.f, o1 = 0.f;
+    const int d0 = tid, d1 = tid + 128;
+    for (int p = 0; p < n_pages; ++p) {
+        const __half *vr = vc + ((int64_t)page_table[p] * nkv + kvh) * PAGE_TOKENS * hd;
+        const int tb = p * PAGE_TOKENS, lim = min(PAGE_TOKENS, n_ctx - tb);
+        for (int k = 0; k < lim; ++k) {
+            const float pe = sc[tb + k];
+            if (d0 < hd) o0 = fmaf(pe, __half2float(vr[k * hd + d0]), o0);
+            if (d1 < hd) o1 = fmaf(pe, __half2float(vr[k * hd + d1]), o1);
+        }
+    }
+    if (d0 < hd) out[(int64_t)m * ldo + (int64_t)h * hd + d0] = o0 / l;
+    if (d1 < hd) out[(int64_t)m * ldo + (int64_t)h * hd + d1] = o1 / l;
+}
+
+cudaError_t launch_prefill_attention(float *d_qkv, int64_t ld, int M, int nh, int nkv, int hd, int pos0, const float *d_cos, const float *d_sin,
+                                     __half *d_k, __half *d_v, const int32_t *d_page_table, float *d_out, int64_t ldo, cudaStream_t st) {
+    k_prefill_rope_kv<<<dim3(nh + 2 * nkv, M), 128, 0, st>>>(d_qkv, ld, nh, nkv, hd, pos0, d_cos, d_sin, d_k, d_v, d_page_table);
+    const size_t smem = (size_t)(hd + pos0 + M) * sizeof(float);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_prefill_attn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    k_prefill_attn<<<dim3(nh, M), 128, smem, st>>>(d_qkv, ld, nh, nkv, hd, pos0, d_k, d_v, d_page_table, d_out, ldo);
+    return cudaGetLastError();
+}
+
+// -inf / max-int in every arg-max partial (the LM-head GEMV after a prompt batch fills only its own grid's entries)
+__global__ void k_fill_partials(float *pmax, int *pidx, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { pmax[i] = -INFINITY; pidx[i] = 0x7fffffff; }
+}
+void launch_fill_partials(float *pmax, int *pidx, int n, cudaStream_t st) { k_fill_partials<<<(n + 255) / 256, 256, 0, st>>>(pmax, pidx, n); }
