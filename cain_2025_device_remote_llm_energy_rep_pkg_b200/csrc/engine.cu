@@ -92,6 +92,8 @@ struct b2_session {
     // batched prompt evaluation (prefill.cu): activations of up to 64 prompt tokens and the GEMM's B operand
     float *pf_x = nullptr, *pf_qkv = nullptr, *pf_attn = nullptr, *pf_h = nullptr;
     void *pf_pb = nullptr;
+    float *pf_part = nullptr;      // split-K partial sums
+    uint64_t pf_part_floats = 0;
     bool use_pf_gemm = true;
     // persistent token kernel (mega.cu): plan, grid and shared memory; use_mega = false falls back to one kernel per stage
     MegaPlan *plan = nullptr;
@@ -671,6 +673,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_attn, (uint64_t)64 * qd * 4))) break;
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_h, (uint64_t)64 * I * 4))) break;
             if ((rc = dev_alloc(s->allocs, &s->pf_pb, pb_bytes(64, widest)))) break;
+            s->pf_part_floats = (uint64_t)8 * 64 * std::max<int64_t>(H, qd + 2 * kvd);
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_part, s->pf_part_floats * 4))) break;
         }
     } while (0);
     if (rc) { b2_session_destroy(s); return rc; }
@@ -787,15 +791,15 @@ static int prefill_batched(b2_session *s, int n) {
         for (int l = 0; l < c.n_layers; ++l) {
             LayerW &ly = m->layers[l];
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.attn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, c.n_heads, c.n_kv_heads, hd, pos0, m->rope_cos, m->rope_sin,
                                              s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, s->pf_attn, qd, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_attn, qd, mb, T, qd, nullptr, 0.f, 0, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.ffn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_h, I, mb, T, I, nullptr, 0.f, 0, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, st));
+            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             launches += 10;
         }
         if (m0 + mb == n) {   // LM head for the last token of the prompt

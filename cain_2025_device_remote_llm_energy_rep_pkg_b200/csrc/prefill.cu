@@ -1,14 +1,15 @@
 // prefill.cu — batched prompt evaluation on tcgen05 tensor cores (see prefill.cuh for the data layout and the numerics).
 //
-// k_prefill_gemm: one CTA per SM, persistent over groups of 128 weight rows; ten warps in four roles:
-//   warps 4-7  stream the packed Q4_0 rows of the group from HBM (the decode layout, layout.cuh), turn the nibbles into int8
+// k_prefill_gemm: one CTA per SM, persistent over groups of 128 weight rows; fourteen warps in four roles:
+//   warps 8-11 stream the packed Q4_0 rows of the group from HBM (the decode layout, layout.cuh), turn the nibbles into int8
 //              (16*(q-8): nibble in the high half of the byte) and store them in shared memory as the A operand
 //              (K-major core matrices), one block-group (4 blocks = 128 k) per stage, with the rows' f16 scales as floats
-//   warp 9     copies the B operand of the stage (activation digits of T tokens, already in operand layout) and the
+//   warp 13    copies the B operand of the stage (activation digits of T tokens, already in operand layout) and the
 //              activation scales with cp.async.bulk
-//   warp 8     one thread issues tcgen05.mma.kind::i8 (M=128, N=3T, K=32) per block, accumulate OFF, into one of two tensor-memory
+//   warp 12    one thread issues tcgen05.mma.kind::i8 (M=128, N=3T, K=32) per block, accumulate OFF, into one of two tensor-memory
 //              buffers and commits to mbarriers
-//   warps 0-3  read the int32 dot products with tcgen05.ld (thread = weight row, one TMEM lane quadrant per warp), combine the
+//   warps 0-7  read the int32 dot products with tcgen05.ld (thread = weight row, TMEM lane quadrant = warp % 4; for T >= 32 the
+//              tokens are split between warps 0-3 and 4-7), combine the
 //              three digit planes, scale by d_w * s_act and accumulate T fp32 sums per thread; after the last block they apply
 //              the epilogue (+bias, +residual, act(gate)*up) and write y
 // The per-block scales of Q4_0 are the reason the accumulation across K cannot stay in tensor memory.
@@ -119,6 +120,8 @@ struct PfArgs {
     int64_t ldy;
     const float *bias_or_res;
     int act;
+    int ksplit;              // > 1: the K range of a row group is cut into ksplit pieces, one work item each; raw sums go to `part`
+    float *part;             // [ksplit][T][rows] fp32 partial sums (k_prefill_finish adds them in a fixed order)
 };
 
 // shared memory: [A stages: PF_STAGES x 4 blocks x 4 KB][B stages: PF_STAGES x 4 x N*32][dw: PF_STAGES x 4 x 128 floats]
@@ -147,29 +150,35 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
     uint64_t *tempty = tfull + 2;                       // [buf]   the four epilogue warps have read them
     uint32_t *tmem_ptr = (uint32_t *)(tempty + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    constexpr int EPI_SETS = T >= 32 ? 2 : 1;   // epilogue warp sets, each with T / EPI_SETS tokens of all 128 rows
+    constexpr int TS = T / EPI_SETS;
     if (tid == 0) {
-        for (int s = 0; s < PF_STAGES; ++s) { mbar_init(full + s, 5); mbar_init(empty + s, 5); }
-        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
+        for (int s = 0; s < PF_STAGES; ++s) { mbar_init(full + s, 5); mbar_init(empty + s, 1 + 4 * EPI_SETS); }
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4 * EPI_SETS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 8) tmem_alloc(tmem_ptr, 512);
+    if (warp == 12) tmem_alloc(tmem_ptr, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_ptr;
-    const int n_groups = (a.n_tiles + 7) >> 3;
-    const int nbg = a.nbp >> 2;   // block-groups (stages) along K
+    const int n_items = ((a.n_tiles + 7) >> 3) * a.ksplit;   // work item = (row group, K piece)
+    const int nbg_all = a.nbp >> 2;                          // block-groups (stages) along K
 
-    if (warp < 4) {
-        // ===================== epilogue: thread = weight row, T fp32 sums
-        const int row_l = warp * 32 + lane;
-        const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
+    if (warp < 8) {
+        if (warp >= 4 * EPI_SETS) goto done;
+        // ===================== epilogue: thread = (weight row, token set), TS fp32 sums
+        const int quad = warp & 3, tset = warp >> 2, tk0 = tset * TS;
+        const int row_l = quad * 32 + lane;
+        const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
         int it = 0, kbi = 0;
-        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
-            float acc[T];
+        for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
+            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
+            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+            float acc[TS];
 #pragma unroll
-            for (int m = 0; m < T; ++m) acc[m] = 0.f;
-            for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+            for (int m = 0; m < TS; ++m) acc[m] = 0.f;
+            for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
                 const int slot = it % PF_STAGES;
                 const float *dws = (const float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
                 const float *sas = (const float *)(smem + S::SA_OFF) + slot * 4 * T;
@@ -181,16 +190,20 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                     tc_fence_after();
                     const float dw = dws[b * PF_ROWS + row_l];
 #pragma unroll
-                    for (int t0 = 0; t0 < T; t0 += 16) {
+                    for (int t0 = 0; t0 < TS; t0 += 16) {
                         int c0[16], c1[16], c2[16];
-                        tmem_ld16(tlane + buf * 256 + t0, c0);
-                        tmem_ld16(tlane + buf * 256 + T + t0, c1);
-                        tmem_ld16(tlane + buf * 256 + 2 * T + t0, c2);
+                        tmem_ld16(tlane + buf * 256 + tk0 + t0, c0);
+                        tmem_ld16(tlane + buf * 256 + T + tk0 + t0, c1);
+                        tmem_ld16(tlane + buf * 256 + 2 * T + tk0 + t0, c2);
                         tmem_ld_wait();
 #pragma unroll
                         for (int u = 0; u < 16; ++u) {
-                            const float xf = fmaf(16384.0f, (float)c2[u], fmaf(128.0f, (float)c1[u], (float)c0[u]));
-                            acc[t0 + u] = fmaf(xf, dw * sas[b * T + t0 + u], acc[t0 + u]);
+                            // |c| <= 2^18: int -> float as an integer add and a float subtract (I2F runs at a quarter of their rate)
+                            const float f0 = __int_as_float(c0[u] + 0x4B400000) - 12582912.0f;
+                            const float f1 = __int_as_float(c1[u] + 0x4B400000) - 12582912.0f;
+                            const float f2 = __int_as_float(c2[u] + 0x4B400000) - 12582912.0f;
+                            const float xf = fmaf(16384.0f, f2, fmaf(128.0f, f1, f0));
+                            acc[t0 + u] = fmaf(xf, dw * sas[b * T + tk0 + t0 + u], acc[t0 + u]);
                         }
                     }
                     tc_fence_before();
@@ -201,72 +214,122 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                 if (lane == 0) mbar_arrive(empty + slot);
             }
             const int row = grp * PF_ROWS + row_l;
+            if (a.ksplit > 1) {
 #pragma unroll
-            for (int m = 0; m < T; ++m) {
+                for (int u = 0; u < TS; ++u)
+                    if (tk0 + u < a.M && row < a.rows) a.part[((int64_t)ks * T + tk0 + u) * a.rows + row] = acc[u];
+                continue;
+            }
+#pragma unroll
+            for (int u = 0; u < TS; ++u) {
+                const int m = tk0 + u;
                 if (m < a.M) {   // uniform
                     if (OUT == PF_OUT_ACTMUL) {   // rows (2j, 2j+1) = (gate_j, up_j)
-                        const float up = __shfl_down_sync(0xffffffffu, acc[m], 1);
-                        if (!(row & 1) && row < a.rows) a.y[(int64_t)m * a.ldy + (row >> 1)] = act_fn(acc[m], a.act) * up;
+                        const float up = __shfl_down_sync(0xffffffffu, acc[u], 1);
+                        if (!(row & 1) && row < a.rows) a.y[(int64_t)m * a.ldy + (row >> 1)] = act_fn(acc[u], a.act) * up;
                     } else if (row < a.rows) {
-                        if (OUT == PF_OUT_RES) a.y[(int64_t)m * a.ldy + row] = a.bias_or_res[(int64_t)m * a.ldy + row] + acc[m];
-                        else a.y[(int64_t)m * a.ldy + row] = a.bias_or_res ? acc[m] + a.bias_or_res[row] : acc[m];
+                        if (OUT == PF_OUT_RES) a.y[(int64_t)m * a.ldy + row] = a.bias_or_res[(int64_t)m * a.ldy + row] + acc[u];
+                        else a.y[(int64_t)m * a.ldy + row] = a.bias_or_res ? acc[u] + a.bias_or_res[row] : acc[u];
                     }
                 }
             }
         }
-    } else if (warp < 8) {
+    } else if (warp < 12) {
         // ===================== weights: packed nibbles -> int8 A operand.  Warp lw unpacks (tile, half) pairs 4*lw .. 4*lw+3 of the
         // group; lane (g, t) holds word t of four consecutive blocks of tile row half*8 + g (one LDG.128, as the decode GEMV).
-        const int lw = warp - 4, g = lane >> 2, t = lane & 3;
-        int it = 0;
-        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
-            for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
-                const int slot = it % PF_STAGES;
-                const int ck = bgi >> 4, j = bgi & 15;
-                const int cb = min(KC, a.nbp - ck * KC);
-                uint4 v[4];
-                uint32_t sc[2] = {0u, 0u};
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1, tg = grp * 8 + til;
-                    v[i] = make_uint4(0u, 0u, 0u, 0u);
-                    if (tg < a.n_tiles) {
-                        const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES;
-                        v[i] = ldg_stream4(chunk + (size_t)j * 1024 + hf * 512 + lane * 16);
-                        if (hf == 0) sc[i >> 1] = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * 128 + lane * 4));
-                    }
+        const int lw = warp - 8, g = lane >> 2, t = lane & 3;
+        // the weights of a work item go HBM -> L2 one item ahead (lane 0, one bulk prefetch per tile and chunk), so the loads below
+        // are L2 hits; the register loads of the next stage are issued before the current stage is unpacked
+        auto prefetch_item = [&](int wi) {
+            if (lane != 0 || wi >= n_items) return;
+            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
+            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+            for (int til = lw * 2; til < lw * 2 + 2; ++til) {
+                const int tg = grp * 8 + til;
+                if (tg >= a.n_tiles) continue;
+                for (int ck = bg0 >> 4; ck <= (bg1 - 1) >> 4; ++ck) {
+                    const int cb = min(KC, a.nbp - ck * KC);
+                    l2_prefetch(a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES, (uint32_t)cb * BLOCK_BYTES);
                 }
-                mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
-                uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
-                float *dws = (float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1;
-                    const uint32_t wd[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-                    uint8_t *dst = As + (til * 2 + hf) * 256 + g * 16 + t * 4;
-#pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        *(uint32_t *)(dst + jj * 4096) = (wd[jj] << 4) & 0xF0F0F0F0u;        // elements 4t..4t+3   (k half 0)
-                        *(uint32_t *)(dst + jj * 4096 + 128) = wd[jj] & 0xF0F0F0F0u;         // elements 16+4t..    (k half 1)
-                    }
-                    if (hf == 0) {   // lane = (row g, block jj = t): half2 = (d of row g, d of row g+8)
-                        const float2 d2 = __half22float2(*(const __half2 *)&sc[i >> 1]);
-                        dws[t * PF_ROWS + til * 16 + g] = d2.x;
-                        dws[t * PF_ROWS + til * 16 + g + 8] = d2.y;
-                    }
-                }
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tensor core reads these stores through the async proxy
-                __syncwarp();
-                if (lane == 0) mbar_arrive(full + slot);
             }
+        };
+        auto issue = [&](int grp, int bgi, uint4 (&v)[4], uint32_t (&sc)[2]) {
+            const int ck = bgi >> 4, j = bgi & 15;
+            const int cb = min(KC, a.nbp - ck * KC);
+            sc[0] = sc[1] = 0u;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1, tg = grp * 8 + til;
+                v[i] = make_uint4(0u, 0u, 0u, 0u);
+                if (tg < a.n_tiles) {
+                    const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES;
+                    v[i] = ldg_stream4(chunk + (size_t)j * 1024 + hf * 512 + lane * 16);
+                    if (hf == 0) sc[i >> 1] = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * 128 + lane * 4));
+                }
+            }
+        };
+        auto item_range = [&](int wi, int &grp, int &bg0, int &bg1) {
+            grp = wi / a.ksplit;
+            const int ks = wi - grp * a.ksplit;
+            bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit);
+            bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+        };
+        int it = 0;
+        int wi = blockIdx.x, grp = 0, bgi = 0, bg1 = 0;
+        uint4 v[4], vn[4];
+        uint32_t sc[2], scn[2];
+        prefetch_item(wi);
+        if (wi < n_items) {
+            item_range(wi, grp, bgi, bg1);
+            prefetch_item(wi + gridDim.x);
+            issue(grp, bgi, v, sc);
         }
-    } else if (warp == 8) {
+        while (wi < n_items) {
+            // the stage after this one (possibly the first of the next work item)
+            int nwi = wi, ngrp = grp, nbgi = bgi + 1, nbg1 = bg1;
+            if (nbgi >= bg1) {
+                nwi = wi + gridDim.x;
+                if (nwi < n_items) { item_range(nwi, ngrp, nbgi, nbg1); prefetch_item(nwi + gridDim.x); }
+            }
+            if (nwi < n_items) issue(ngrp, nbgi, vn, scn);
+            const int slot = it % PF_STAGES;
+            mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
+            uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
+            float *dws = (float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1;
+                const uint32_t wd[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+                uint8_t *dst = As + (til * 2 + hf) * 256 + g * 16 + t * 4;
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    *(uint32_t *)(dst + jj * 4096) = (wd[jj] << 4) & 0xF0F0F0F0u;        // elements 4t..4t+3   (k half 0)
+                    *(uint32_t *)(dst + jj * 4096 + 128) = wd[jj] & 0xF0F0F0F0u;         // elements 16+4t..    (k half 1)
+                }
+                if (hf == 0) {   // lane = (row g, block jj = t): half2 = (d of row g, d of row g+8)
+                    const float2 d2 = __half22float2(*(const __half2 *)&sc[i >> 1]);
+                    dws[t * PF_ROWS + til * 16 + g] = d2.x;
+                    dws[t * PF_ROWS + til * 16 + g + 8] = d2.y;
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tensor core reads these stores through the async proxy
+            __syncwarp();
+            if (lane == 0) mbar_arrive(full + slot);
+            ++it;
+            wi = nwi; grp = ngrp; bgi = nbgi; bg1 = nbg1;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) v[i] = vn[i];
+            sc[0] = scn[0]; sc[1] = scn[1];
+        }
+    } else if (warp == 12) {
         // ===================== MMA issue (one thread)
         if (lane == 0) {
             const uint32_t idesc = umma_idesc_i8(N);
             int it = 0, kbi = 0;
-            for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
-                for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+            for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
+            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
+            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+                for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
                     const int slot = it % PF_STAGES;
                     mbar_wait(full + slot, (it / PF_STAGES) & 1);
                     tc_fence_after();
@@ -288,8 +351,10 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         if (lane == 0) {
             const uint8_t *pbs = a.pb + pb_scale_off(T, a.nbp);
             int it = 0;
-            for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
-                for (int bgi = 0; bgi < nbg; ++bgi, ++it) {
+            for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
+            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
+            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+                for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
                     const int slot = it % PF_STAGES;
                     mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
                     mbar_expect_tx(full + slot, (uint32_t)(S::B_STAGE + 4 * T * 4));
@@ -299,9 +364,22 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
             }
         }
     }
+done:
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) tmem_dealloc(tmem, 512);
+    if (warp == 12) tmem_dealloc(tmem, 512);
+}
+
+// y = sum of the K-split partials in a fixed order, then the epilogue (+bias | +residual)
+__global__ void __launch_bounds__(256) k_prefill_finish(const float *__restrict__ part, int ksplit, int T, int M, int rows, float *__restrict__ y,
+                                                        int64_t ldy, const float *__restrict__ bias_or_res, int out_mode) {
+    const int row = blockIdx.x * 256 + threadIdx.x, m = blockIdx.y;
+    if (row >= rows || m >= M) return;
+    float v = 0.f;
+    for (int s = 0; s < ksplit; ++s) v += part[((int64_t)s * T + m) * rows + row];
+    if (out_mode == PF_OUT_RES) v += bias_or_res[(int64_t)m * ldy + row];
+    else if (bias_or_res) v += bias_or_res[row];
+    y[(int64_t)m * ldy + row] = v;
 }
 
 template <int T, int OUT>
@@ -318,20 +396,35 @@ static cudaError_t launch_pf(const PfArgs &a, int grid, cudaStream_t st) {
 }
 
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
-                                const float *bias_or_res, int act, int sm_count, cudaStream_t st) {
+                                const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st) {
     if (M <= 0 || M > T || rows <= 0 || cols <= 0) return cudaErrorInvalidValue;
     if (out_mode == PF_OUT_RES && !bias_or_res) return cudaErrorInvalidValue;
     PfArgs a;
     a.w = (const uint8_t *)d_packed; a.rows = (int)rows; a.nbp = (int)nblocks_padded(cols); a.n_tiles = (int)ntiles(rows);
     a.pb = (const uint8_t *)pb; a.M = M; a.y = y; a.ldy = ldy; a.bias_or_res = bias_or_res; a.act = act;
     const int n_groups = (a.n_tiles + 7) / 8;
-    const int grid = n_groups < sm_count ? n_groups : sm_count;
-#define PF_CASE(TT, OO) if (T == TT && out_mode == OO) return launch_pf<TT, OO>(a, grid, st)
+    // matrices with few row groups (O, down, QKV) leave most SMs idle: cut K so that there are about as many work items as SMs
+    int ksplit = 1;
+    if (part && out_mode != PF_OUT_ACTMUL && n_groups * 2 <= sm_count) {
+        ksplit = sm_count / n_groups;
+        const int nbg = a.nbp >> 2;
+        if (ksplit > nbg / 8) ksplit = nbg / 8;   // at least 8 stages per item
+        if (ksplit > 8) ksplit = 8;
+        while (ksplit > 1 && (uint64_t)ksplit * T * rows > part_floats) --ksplit;
+        if (ksplit < 1) ksplit = 1;
+    }
+    a.ksplit = ksplit; a.part = part;
+    const int n_items = n_groups * ksplit;
+    const int grid = n_items < sm_count ? n_items : sm_count;
+    cudaError_t e = cudaErrorInvalidValue;
+#define PF_CASE(TT, OO) if (T == TT && out_mode == OO) e = launch_pf<TT, OO>(a, grid, st)
     PF_CASE(16, PF_OUT_BIAS); PF_CASE(16, PF_OUT_RES); PF_CASE(16, PF_OUT_ACTMUL);
     PF_CASE(32, PF_OUT_BIAS); PF_CASE(32, PF_OUT_RES); PF_CASE(32, PF_OUT_ACTMUL);
     PF_CASE(64, PF_OUT_BIAS); PF_CASE(64, PF_OUT_RES); PF_CASE(64, PF_OUT_ACTMUL);
 #undef PF_CASE
-    return cudaErrorInvalidValue;
+    if (e != cudaSuccess || ksplit == 1) return e;
+    k_prefill_finish<<<dim3((unsigned)((rows + 255) / 256), M), 256, 0, st>>>(part, ksplit, T, M, (int)rows, y, ldy, bias_or_res, out_mode);
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------ the other stages of a prompt batch

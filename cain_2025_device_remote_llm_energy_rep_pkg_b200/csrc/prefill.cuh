@@ -18,7 +18,7 @@
 
 #define PF_ROWS 128          // weight rows per CTA tile (UMMA M)
 #define PF_STAGES 3          // shared-memory stages of one block-group (4 blocks = 128 k) each
-#define PF_THREADS 320       // warps 0-3 epilogue (TMEM quadrants), 4-7 weight unpack, 8 MMA issue, 9 B-operand copies
+#define PF_THREADS 448       // warps 0-7 epilogue (TMEM quadrant = warp % 4, token half = warp / 4), 8-11 weight unpack, 12 MMA issue, 13 B-operand copies
 
 __host__ __device__ inline size_t pb_block_bytes(int T) { return (size_t)3 * T * 32; }
 __host__ __device__ inline size_t pb_scale_off(int T, int64_t nbp) { return (size_t)nbp * pb_block_bytes(T); }
@@ -39,9 +39,10 @@ enum { PF_OUT_BIAS = 0, PF_OUT_RES = 1, PF_OUT_ACTMUL = 2 };
 // x[M][n] fp32 (row stride ldx) -> PB for T tokens.  in_mode PF_IN_NORM: RMSNorm with norm_w first.
 cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M, int T, int64_t n, const float *norm_w, float eps, int plus_one,
                                  void *pb, cudaStream_t st);
+// `part` (may be NULL): scratch of part_floats floats for split-K partial sums (up to 8 * T * rows are used)
 // y[m][row] (row stride ldy) = sum_k W[row][k] * grid(x[m])[k]  (+ bias[row] | + res[m][row] | act(gate)*up with ldy = rows/2)
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
-                                const float *bias_or_res, int act, int sm_count, cudaStream_t st);
+                                const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
 void launch_prefill_embed(const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st);
 // RoPE (q in place) + KV append of M tokens at pos0.., then causal attention over the cache; out[m][nh*hd] fp32
 cudaError_t launch_prefill_attention(float *d_qkv, int64_t ld, int M, int nh, int nkv, int hd, int pos0, const float *d_cos, const float *d_sin,
