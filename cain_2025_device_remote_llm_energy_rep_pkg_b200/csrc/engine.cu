@@ -4,6 +4,7 @@
 #include "kernels.cuh"
 #include "mega.cuh"
 #include "prefill.cuh"
+#include "sampler.cuh"
 #include "layout.cuh"
 #include "randinit.cuh"
 #include <stdarg.h>
@@ -67,7 +68,7 @@ struct b2_model {
     int q_dim() const { return cfg.n_heads * cfg.head_dim; }
     int kv_dim() const { return cfg.n_kv_heads * cfg.head_dim; }
 };
-enum { G_PREFILL_BODY = 0, G_PREFILL_LAST, G_DECODE, G_DECODE_LOG, G_FORCED, G_COUNT };
+enum { G_PREFILL_BODY = 0, G_PREFILL_LAST, G_DECODE, G_DECODE_LOG, G_FORCED, G_SAMPLE, G_SAMPLE_LOG, G_COUNT };
 struct b2_session {
     b2_model *m = nullptr;
     int max_ctx = 0, n_pages = 0;
@@ -89,6 +90,12 @@ struct b2_session {
     bool fused_attn = true;
     float *logits_log = nullptr;
     uint64_t logits_log_cap = 0;   // in floats
+    // top-k / top-p / temperature sampling inside the decode loop (sampler.cu): scratch, the uniform of the current draw, and
+    // {seed, draw counter} on the device; the graphs bake k/T/p, so they are re-captured when those change
+    void *sample_scratch = nullptr;
+    float *d_u = nullptr;
+    uint64_t *d_draw = nullptr;
+    b2_sampler_cfg graph_sampler{};
     // batched prompt evaluation (prefill.cu): activations of up to 64 prompt tokens and the GEMM's B operand
     float *pf_x = nullptr, *pf_qkv = nullptr, *pf_attn = nullptr, *pf_h = nullptr;
     void *pf_pb = nullptr;
@@ -438,6 +445,12 @@ __global__ void k_advance(DevState *st, int inc_step) {
     st->pos += 1;
     st->step += inc_step;
 }
+// uniform of draw i of a session: top 24 bits of splitmix64(splitmix64(seed) + i)  (oracle/sampler.py:uniform)
+__global__ void k_make_u(uint64_t *draw, float *u) {
+    const uint64_t h = ri_splitmix64(ri_splitmix64(draw[0]) + draw[1]);
+    *u = (float)(h >> 40) * 5.9604644775390625e-08f;
+    draw[1] += 1;
+}
 __global__ void k_copy_logits(const float *logits, int n, float *log, const DevState *st) {
     float *dst = log + (int64_t)st->step * n;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = logits[i];
@@ -502,6 +515,17 @@ static int enqueue_graph_body(b2_session *s, int which, int variant) {
         n += enqueue_forward(s, which != G_PREFILL_BODY, attn_ctx);
         if (which == G_FORCED) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
         k_advance<<<1, 1, 0, st>>>(s->state, which == G_FORCED ? 1 : 0); n++;
+        break;
+    case G_SAMPLE:
+    case G_SAMPLE_LOG:
+        if (which == G_SAMPLE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
+        k_make_u<<<1, 1, 0, st>>>(s->d_draw, s->d_u); n++;
+        launch_sample_topk(s->logits, s->m->cfg.vocab, s->graph_sampler.top_k, s->graph_sampler.temperature, s->graph_sampler.top_p, s->d_u, 0.f,
+                           s->d_sampled, s->sample_scratch, st); n++;
+        k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
+        launch_fill_partials(s->pmax, s->pidx, 1024, st); n++;   // a later greedy step reads every partial slot
+        n += enqueue_forward(s, true, attn_ctx);
+        k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
         break;
     case G_DECODE:
     case G_DECODE_LOG:
@@ -666,6 +690,9 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->xsq, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(c.n_heads, hd)))) break;
         if ((rc = dev_alloc(s->allocs, &s->argmax_scratch, argmax_scratch_bytes()))) break;
+        if ((rc = dev_alloc(s->allocs, &s->sample_scratch, sample_scratch_bytes(SAMPLE_MAX_K)))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->d_u, 16))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->d_draw, 16))) break;
         if (s->use_pf_gemm) {
             const int64_t widest = std::max<int64_t>(std::max<int64_t>(H, I), qd);
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_x, (uint64_t)64 * H * 4))) break;
@@ -684,6 +711,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     cudaError_t e = cudaMemcpy(s->page_table, pt.data(), pt.size() * 4, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemset(s->attn_scratch, 0, attn_scratch_bytes(c.n_heads, hd));
     if (e == cudaSuccess) e = cudaMemset(s->argmax_scratch, 0, argmax_scratch_bytes());
+    if (e == cudaSuccess) e = cudaMemset(s->sample_scratch, 0, sample_scratch_bytes(SAMPLE_MAX_K));
+    if (e == cudaSuccess) e = cudaMemset(s->d_draw, 0, 16);
     if (e == cudaSuccess) e = cudaMemset(s->state, 0, sizeof(DevState));
     if (e == cudaSuccess) e = cudaMemset(s->act_attn, 0, a3_bytes(qd));   // padding blocks of the A3 vectors stay zero
     if (e == cudaSuccess) e = cudaMemset(s->act_h, 0, a3_bytes(I));
@@ -719,6 +748,7 @@ extern "C" int b2_session_reset(b2_session *s) {
     B2_CUDA(cudaSetDevice(s->m->e->device));
     B2_CUDA(cudaStreamSynchronize(s->m->e->stream));
     B2_CUDA(cudaMemset(s->state, 0, sizeof(DevState)));
+    B2_CUDA(cudaMemset(s->d_draw, 0, 16));
     s->host_pos = 0;
     s->have_logits = false;
     uint64_t launches = s->stats.kernel_launches;
@@ -744,7 +774,7 @@ static int ensure_log(b2_session *s, uint64_t floats) {
     s->logits_log = nullptr;
     s->logits_log_cap = 0;
     // graphs bake the log pointer: re-capture the ones that use it
-    for (int g : {G_DECODE_LOG, G_FORCED})
+    for (int g : {G_DECODE_LOG, G_FORCED, G_SAMPLE_LOG})
         for (int v = 0; v < 2; ++v)
             if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
     cudaError_t e = cudaMalloc((void **)&s->logits_log, floats * 4);
@@ -853,7 +883,12 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
     ApiScope _scope("b2_decode");
     B2_CHECK(s && out_tokens && n_steps > 0, B2_EINVAL, "b2_decode: bad arguments");
     B2_CHECK(s->have_logits, B2_EINVAL, "b2_decode: call b2_prefill first");
-    B2_CHECK(!sampler || sampler->top_k <= 1, B2_EINVAL, "b2_decode: only greedy sampling (top_k <= 1) is wired into the decode loop in this build");
+    const bool sampling = sampler && sampler->top_k > 1;
+    if (sampling) {
+        B2_CHECK(sampler->top_k <= SAMPLE_MAX_K, B2_EINVAL, "b2_decode: top_k %d > %d", sampler->top_k, SAMPLE_MAX_K);
+        B2_CHECK(sampler->temperature > 0.f, B2_EINVAL, "b2_decode: temperature must be > 0 (use top_k <= 1 for greedy)");
+        B2_CHECK(sampler->top_p > 0.f && sampler->top_p <= 1.0f, B2_EINVAL, "b2_decode: top_p must be in (0, 1]");
+    }
     B2_CHECK(s->host_pos + n_steps <= s->max_ctx, B2_ECTX, "b2_decode: %d + %d tokens exceed the context window %d", s->host_pos, n_steps, s->max_ctx);
     B2_CHECK(n_steps <= s->out_cap, B2_EINVAL, "b2_decode: n_steps %d > %d", n_steps, s->out_cap);
     cudaStream_t st = s->m->e->stream;
@@ -862,7 +897,20 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
     if (logits_out) B2_TRY(ensure_log(s, (uint64_t)n_steps * V));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (s->use_mega) B2_TRY(run_mega(s, MEGA_DECODE, n_steps, 0, logits_out ? s->logits_log : nullptr));
+    if (sampling) {
+        // k / T / p are kernel arguments inside the captured graphs: new values -> new graphs.  The seed travels through device
+        // memory; the draw counter continues across calls (reset by b2_session_reset).
+        if (sampler->top_k != s->graph_sampler.top_k || sampler->temperature != s->graph_sampler.temperature ||
+            sampler->top_p != s->graph_sampler.top_p) {
+            B2_CUDA(cudaStreamSynchronize(st));
+            for (int g : {G_SAMPLE, G_SAMPLE_LOG})
+                for (int v = 0; v < 2; ++v)
+                    if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
+            s->graph_sampler = *sampler;
+        }
+        B2_CUDA(cudaMemcpyAsync(s->d_draw, &sampler->seed, 8, cudaMemcpyHostToDevice, st));
+        B2_TRY(run_graph(s, logits_out ? G_SAMPLE_LOG : G_SAMPLE, n_steps, s->host_pos));
+    } else if (s->use_mega) B2_TRY(run_mega(s, MEGA_DECODE, n_steps, 0, logits_out ? s->logits_log : nullptr));
     else B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps, s->host_pos));
     B2_CUDA(cudaEventRecord(s->ev1, st));
     B2_CUDA(cudaMemcpyAsync(out_tokens, s->d_out_tokens, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, st));

@@ -36,6 +36,45 @@ def default_num_predict(prompt: str) -> int:
     return int(math.ceil(1.33 * int(m.group(1)))) if m else 128
 
 
+# Ollama's defaults when a request asks for sampling without giving every knob (external, unpinned)
+OLLAMA_TOP_K, OLLAMA_TOP_P, OLLAMA_TEMPERATURE = 40, 0.9, 0.8
+
+
+def sampler_from_options(options: dict, default_sampling: bool = False):
+    """options.{temperature, top_k, top_p, seed} -> (top_k, temperature, top_p, seed) or None for greedy.
+    A request without any of them is greedy (deterministic, what the parity tests pin) unless the server was started
+    with --ollama-sampling, which applies Ollama's stochastic defaults as the reference's requests got them."""
+    keys = ("temperature", "top_k", "top_p", "seed")
+    if not default_sampling and not any(k in options for k in keys):
+        return None
+    try:
+        temperature = float(options.get("temperature", OLLAMA_TEMPERATURE))
+        top_k = int(options.get("top_k", OLLAMA_TOP_K))
+        top_p = float(options.get("top_p", OLLAMA_TOP_P))
+        seed = int(options.get("seed", 0))
+    except (TypeError, ValueError) as ex:
+        raise ValueError(f"bad sampling option: {ex}")
+    if temperature <= 0.0 or top_k == 1:
+        return None                      # Ollama: temperature 0 = greedy
+    if top_k <= 0 or top_k > 64:
+        top_k = 64                       # the device sampler keeps at most 64 candidates (0 = "disabled" in Ollama)
+    if not (0.0 < top_p <= 1.0):
+        top_p = 1.0
+    return top_k, temperature, top_p, seed & 0xFFFFFFFFFFFFFFFF
+
+
+def chat_prompt(messages) -> str:
+    """/api/chat: the conversation flattened into one prompt (the byte-level stand-in tokenizer has no chat template)."""
+    if not isinstance(messages, list) or not messages:
+        raise ValueError("messages must be a non-empty list")
+    parts = []
+    for m in messages:
+        if not isinstance(m, dict) or not isinstance(m.get("content", ""), str):
+            raise ValueError("each message needs a string 'content'")
+        parts.append(f"{m.get('role', 'user')}: {m.get('content', '')}")
+    return "\n".join(parts) + "\nassistant:"
+
+
 class GenerationResult:
     def __init__(self, tokens: List[int], prompt_tokens: List[int], stats: dict, done_reason: str):
         self.tokens, self.prompt_tokens, self.stats, self.done_reason = tokens, prompt_tokens, stats, done_reason
@@ -44,10 +83,11 @@ class GenerationResult:
 class B2Backend:
     """Model residency + one serial session per model on one GPU (requests are serialised per backend)."""
 
-    def __init__(self, device: int = 0, seed: int = 1, qtype: str = "q4_0", stream_chunk: int = 16):
+    def __init__(self, device: int = 0, seed: int = 1, qtype: str = "q4_0", stream_chunk: int = 16, default_sampling: bool = False):
         from .engine import Engine
         self.engine = Engine(device)
         self.device, self.seed, self.qtype, self.stream_chunk = device, seed, qtype, stream_chunk
+        self.default_sampling = default_sampling
         self.models: Dict[str, tuple] = {}
         self.lock = threading.Lock()
 
@@ -95,12 +135,17 @@ class B2Backend:
             reason = "length"
             if budget < 0 or budget > room:
                 budget = room
+            samp = sampler_from_options(options, self.default_sampling)
+            cfg = None
+            if samp is not None:
+                from ._lib import SamplerCfg
+                cfg = SamplerCfg(top_k=samp[0], temperature=samp[1], top_p=samp[2], seed=samp[3])
             sess.reset()
             sess.prefill(ptoks)
             out: List[int] = []
             while len(out) < budget:
                 n = min(self.stream_chunk if options.get("_stream") else budget, budget - len(out))
-                toks = [int(t) for t in sess.decode(n)]
+                toks = [int(t) for t in sess.decode(n, sampler=cfg)]
                 out += toks
                 yield {"tokens": toks}
             st = sess.stats()
@@ -166,9 +211,10 @@ class Handler(BaseHTTPRequestHandler):
             self._error(404, f"unknown path {self.path}")
 
     def do_POST(self):
-        if self.path != "/api/generate":
+        if self.path not in ("/api/generate", "/api/chat"):
             self._read_body()
             return self._error(404, f"unknown path {self.path}")
+        chat = self.path == "/api/chat"
         raw = self._read_body()
         try:
             req = json.loads(raw.decode("utf-8"))  # content-type deliberately ignored (curl -d sends form-urlencoded)
@@ -179,6 +225,11 @@ class Handler(BaseHTTPRequestHandler):
         model, prompt = req.get("model"), req.get("prompt", "")
         if not isinstance(model, str) or not model:
             return self._error(400, "missing field: model")
+        if chat:
+            try:
+                prompt = chat_prompt(req.get("messages"))
+            except ValueError as ex:
+                return self._error(400, str(ex))
         if not isinstance(prompt, str):
             return self._error(400, "prompt must be a string")
         backend = self.server.backend
@@ -196,7 +247,10 @@ class Handler(BaseHTTPRequestHandler):
                 self.end_headers()
                 for part in gen:
                     if part.get("done"):
-                        line = self._final(model, part, "")
+                        line = self._final(model, part, "", chat)
+                    elif chat:
+                        line = {"model": model, "created_at": _now(), "message": {"role": "assistant", "content": tokenizer.decode(part["tokens"])},
+                                "done": False}
                     else:
                         line = {"model": model, "created_at": _now(), "response": tokenizer.decode(part["tokens"]), "done": False}
                     data = (json.dumps(line) + "\n").encode()
@@ -208,18 +262,21 @@ class Handler(BaseHTTPRequestHandler):
                 for part in gen:
                     if part.get("done"):
                         final = part
-                self._send_json(200, self._final(model, final, tokenizer.decode(final["tokens"])))
+                self._send_json(200, self._final(model, final, tokenizer.decode(final["tokens"]), chat))
         except ValueError as ex:
             self._error(400, str(ex))
         except Exception as ex:  # engine failure: Ollama convention is {"error": ...} with a 5xx
             self._error(500, f"{type(ex).__name__}: {ex}")
 
-    def _final(self, model: str, part: dict, text: str) -> dict:
+    def _final(self, model: str, part: dict, text: str, chat: bool = False) -> dict:
         rec = {"model": model, "created_at": _now(), "response": text, "done": True, "done_reason": part["done_reason"],
                "context": part["prompt_tokens"] + part["tokens"], "total_duration": part["total_duration"],
                "load_duration": part["load_duration"], "prompt_eval_count": part["prompt_eval_count"],
                "prompt_eval_duration": part["prompt_eval_duration"], "eval_count": part["eval_count"],
                "eval_duration": part["eval_duration"]}
+        if chat:   # /api/chat answers with a message object instead of response/context
+            rec["message"] = {"role": "assistant", "content": rec.pop("response")}
+            rec.pop("context")
         self.server.record({"t": time.time(), "model": model, "eval_count": part["eval_count"], "eval_duration": part["eval_duration"],
                             "prompt_eval_count": part["prompt_eval_count"], "prompt_eval_duration": part["prompt_eval_duration"],
                             "total_duration": part["total_duration"], "load_duration": part["load_duration"],
@@ -268,8 +325,10 @@ def main():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--stats-file", default=os.environ.get("B2_STATS_FILE"))
     ap.add_argument("--preload", default="", help="comma-separated model tags to load before serving")
+    ap.add_argument("--ollama-sampling", action="store_true",
+                    help="requests without sampling options use Ollama's stochastic defaults (top_k 40, top_p 0.9, temperature 0.8) instead of greedy")
     a = ap.parse_args()
-    backend = B2Backend(a.device, a.seed)
+    backend = B2Backend(a.device, a.seed, default_sampling=a.ollama_sampling)
     for tag in filter(None, a.preload.split(",")):
         backend._load(tag)
     srv = OllamaServer((a.host, a.port), backend, a.stats_file)

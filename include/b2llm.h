@@ -78,10 +78,10 @@ typedef struct b2_tensor_desc {
 } b2_tensor_desc;
 
 typedef struct b2_sampler_cfg {
-    int32_t  top_k;          /* 0 or 1: greedy argmax (lowest index wins ties) */
-    float    temperature;    /* used when top_k > 1 */
-    float    top_p;          /* 1.0 disables */
-    uint64_t seed;           /* counter-based: draw i of a session uses (seed, i) */
+    int32_t  top_k;          /* 0 or 1: greedy argmax (lowest index wins ties); 2..64: sample among the k largest logits */
+    float    temperature;    /* used when top_k > 1; must be > 0 */
+    float    top_p;          /* (0,1]; 1.0 disables the nucleus cut */
+    uint64_t seed;           /* counter-based: draw i of a session (since create/reset) uses the uniform of (seed, i) */
 } b2_sampler_cfg;
 
 typedef struct b2_stats {

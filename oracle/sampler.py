@@ -34,3 +34,16 @@ def sample_topk(logits: np.ndarray, k: int, temperature: float, top_p: float, u:
     margin = float(np.min(np.abs(run - target)) / mass)
     cut_margin = float(np.min(np.abs(cum - np.float32(top_p)))) if top_p < 1.0 else float("inf")
     return int(idx[j]), idx[:keep], min(margin, cut_margin)
+
+
+def _splitmix64(z: int) -> int:
+    z = (z + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return z ^ (z >> 31)
+
+
+def uniform(seed: int, i: int) -> float:
+    """The uniform of draw i of a session (csrc/engine.cu:k_make_u): top 24 bits of splitmix64(splitmix64(seed) + i)."""
+    h = _splitmix64((_splitmix64(seed & 0xFFFFFFFFFFFFFFFF) + i) & 0xFFFFFFFFFFFFFFFF)
+    return float(np.float32(h >> 40) * np.float32(2.0 ** -24))

@@ -117,3 +117,41 @@ def test_nvml_energy_counter(pk, lib):
     _, engine = pk
     e0 = engine.nvml_energy_mj(0)
     assert e0 > 0
+
+
+def test_decode_with_topk_sampler_follows_the_sampler_contract(pk, gpu_engine):
+    """Ollama's default request samples (top-k 40, top-p 0.9, temperature 0.8): the decode loop draws on the device from
+    the logits it returns; every draw equals oracle/sampler.py on those logits with the session's counter-based uniform."""
+    archs, engine = pk
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200._lib import SamplerCfg
+    from oracle import sampler as osampler
+    a = archs.TINY["llama3.1:8b"]
+    m = engine.Model.random(gpu_engine, a, seed=5, max_ctx=96)
+    cfg = SamplerCfg(top_k=40, temperature=0.8, top_p=0.9, seed=1234)
+    s = m.session(96)
+    s.prefill(PROMPT)
+    toks, lg = s.decode(12, want_logits=True, sampler=cfg)
+    toks2, lg2 = s.decode(12, want_logits=True, sampler=cfg)          # the draw counter continues across calls
+    checked = 0
+    for i, (t, l) in enumerate(list(zip(toks, lg)) + list(zip(toks2, lg2))):
+        want, _, margin = osampler.sample_topk(l, 40, 0.8, 0.9, osampler.uniform(1234, i))
+        if margin > 1e-5:
+            assert int(t) == want, f"draw {i}"
+            checked += 1
+    assert checked >= 16
+    # same seed, fresh session -> the same sequence; other seed -> another one; greedy unaffected
+    s.reset()
+    s.prefill(PROMPT)
+    again = s.decode(24, sampler=cfg)
+    assert np.array_equal(again, np.concatenate([toks, toks2]))
+    s.reset()
+    s.prefill(PROMPT)
+    other = s.decode(24, sampler=SamplerCfg(top_k=40, temperature=0.8, top_p=0.9, seed=99))
+    assert not np.array_equal(other, again)
+    s.reset()
+    s.prefill(PROMPT)
+    g1 = s.decode(8)
+    s.reset()
+    s.prefill(PROMPT)
+    g2 = s.decode(8, sampler=SamplerCfg(top_k=1, temperature=1.0, top_p=1.0, seed=7))
+    assert np.array_equal(g1, g2)

@@ -107,3 +107,33 @@ def test_tokenizer_stand_in():
     assert tokenizer.encode("é", 1000, "", template=False) == [1, 3 + 0xC3, 3 + 0xA9]
     txt = tokenizer.decode(range(300))
     assert len(txt) == 300 and json.loads(json.dumps(txt)) == txt and all(32 <= ord(c) < 127 for c in txt)
+
+
+def test_sampling_options_map_to_the_device_sampler():
+    f = server.sampler_from_options
+    assert f({}) is None                                            # no options: greedy (what parity pins)
+    assert f({}, default_sampling=True) == (40, 0.8, 0.9, 0)        # --ollama-sampling: Ollama's stochastic defaults
+    assert f({"temperature": 0}) is None                            # Ollama: temperature 0 = greedy
+    assert f({"top_k": 1, "temperature": 0.7}) is None
+    assert f({"seed": 42}) == (40, 0.8, 0.9, 42)
+    assert f({"temperature": 1.5, "top_k": 500, "top_p": 2.0, "seed": -1}) == (64, 1.5, 1.0, 0xFFFFFFFFFFFFFFFF)
+    with pytest.raises(ValueError):
+        f({"temperature": "hot"})
+
+
+def test_chat_endpoint(srv):
+    body = json.dumps({"model": "qwen2:1.5b", "stream": False, "options": {"num_predict": 5},
+                       "messages": [{"role": "system", "content": "be brief"}, {"role": "user", "content": "hello"}]}).encode()
+    rec = json.loads(urllib.request.urlopen(urllib.request.Request(url(srv, "/api/chat"), data=body), timeout=30).read())
+    assert rec["done"] is True and rec["message"]["role"] == "assistant" and isinstance(rec["message"]["content"], str)
+    assert "response" not in rec and rec["eval_count"] == 5
+    tag, prompt, _ = srv.backend.requests[-1]
+    assert prompt == "system: be brief\nuser: hello\nassistant:"
+    bad = urllib.request.Request(url(srv, "/api/chat"), data=json.dumps({"model": "qwen2:1.5b", "messages": []}).encode())
+    with pytest.raises(urllib.error.HTTPError) as e:
+        urllib.request.urlopen(bad, timeout=30)
+    assert e.value.code == 400 and "error" in json.loads(e.value.read())
+    # streaming chat: NDJSON lines carry message objects
+    body = json.dumps({"model": "qwen2:1.5b", "options": {"num_predict": 20}, "messages": [{"role": "user", "content": "hi"}]}).encode()
+    lines = [json.loads(l) for l in urllib.request.urlopen(urllib.request.Request(url(srv, "/api/chat"), data=body), timeout=30).read().splitlines()]
+    assert lines[-1]["done"] is True and all("message" in l for l in lines) and len(lines) >= 3
