@@ -10,13 +10,14 @@
 // Numerics follow oracle/model.py: fp32 scores/softmax over f16-rounded K and V (the newest token included).
 #include "attn_dev.cuh"
 #include <stdlib.h>
+#define ATTN_PRE_DEFAULT 0
 
 __device__ __forceinline__ void pdl_wait_a() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_a() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // NSPLIT = ATTN_NSPLIT: one cluster per head (long contexts).  NSPLIT = 1: one plain CTA per head (contexts up to
 // ATTN_SHORT_CTX), no cluster barrier, no remote reads.  The work itself is attn_dev.cuh.
-template <int NSPLIT, bool PRE>
+template <int NSPLIT, int PRE>
 __global__ void __launch_bounds__(128) k_attn_fused(const AttnArgs a) {
     extern __shared__ __align__(16) float sm[];
     const AttnSmem s = attn_carve(sm, a.hd, a.pps_max);
@@ -25,8 +26,9 @@ __global__ void __launch_bounds__(128) k_attn_fused(const AttnArgs a) {
     const int pos = a.d_pos ? __ldcg(a.d_pos) : a.pos_imm;
     attn_pages(a, s, tid, h, split, NSPLIT, pos);
     AttnRegs R;
-    if (PRE) attn_preload(a, s, tid, h, split, NSPLIT, pos, 0, R);
+    if (PRE == 1) attn_preload<false>(a, s, tid, h, split, NSPLIT, pos, 0, R);
     pdl_wait_a();
+    if (PRE == 2) attn_preload<true>(a, s, tid, h, split, NSPLIT, pos, 0, R);
     attn_main<NSPLIT == 1 ? MERGE_NONE : MERGE_CLUSTER, PRE>(a, s, tid, h, split, NSPLIT, pos, 0, R);
 }
 
@@ -46,13 +48,14 @@ cudaError_t launch_attn_fused(const float *d_qkv, int nh, int nkv, int hd, const
     int max_pages = (max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
     a.pps_max = (max_pages + nsplit - 1) / nsplit;
     size_t smem = attn_fused_smem(hd, a.pps_max);
-    // B2_ATTN_PRE=1: fetch K/V of older tokens into registers before the dependency wait.  Off by default: measured 535 vs 567
-    // tokens/s (llama3.1:8b) -- the QKV GEMV owns every SM until it exits, so this kernel's CTAs start when there is nothing left
-    // to wait for, and the early loads (HBM misses: the weights evict the cache between tokens) only delay q behind them.
+    // B2_ATTN_PRE: 0 = loads in dependency order (q, then K, then V); 1 = K/V of older tokens fetched into registers BEFORE the
+    // dependency wait (measured slower: the QKV GEMV owns every SM until it exits, there is no window before the wait);
+    // 2 = after the wait, q first and then all of K and V in one burst, so the three round trips overlap.
     static int pre = -1;
-    if (pre < 0) { const char *e = getenv("B2_ATTN_PRE"); pre = (e && e[0] == '1'); }
-    const void *fn = one ? (pre ? (const void *)k_attn_fused<1, true> : (const void *)k_attn_fused<1, false>)
-                         : (pre ? (const void *)k_attn_fused<ATTN_NSPLIT, true> : (const void *)k_attn_fused<ATTN_NSPLIT, false>);
+    if (pre < 0) { const char *e = getenv("B2_ATTN_PRE"); pre = e ? atoi(e) : ATTN_PRE_DEFAULT; if (pre < 0 || pre > 2) pre = 0; }
+    const void *fn = nullptr;
+    if (one) fn = pre == 2 ? (const void *)k_attn_fused<1, 2> : pre == 1 ? (const void *)k_attn_fused<1, 1> : (const void *)k_attn_fused<1, 0>;
+    else fn = pre == 2 ? (const void *)k_attn_fused<ATTN_NSPLIT, 2> : pre == 1 ? (const void *)k_attn_fused<ATTN_NSPLIT, 1> : (const void *)k_attn_fused<ATTN_NSPLIT, 0>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

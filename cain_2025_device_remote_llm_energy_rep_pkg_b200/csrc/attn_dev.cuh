@@ -91,9 +91,11 @@ __device__ __forceinline__ void attn_pages(const AttnArgs &a, const AttnSmem &s,
 // critical path after the wait is one L2 round trip for q plus arithmetic, not three dependent round trips.
 struct AttnRegs {
     float c, s;        // cos/sin of this thread's rotation pair (threads < hd/2)
+    float qa, qb, ka, kb, va, vb;   // q, and the newest k and v, of that pair (AFTER_WAIT only: they come from the QKV kernel)
     uint4 kv[4][4];    // phase 1, first batch: [page][chunk]
     uint4 vv[8];       // phase 2, first batch
 };
+template <bool AFTER_WAIT>
 __device__ __forceinline__ void attn_preload(const AttnArgs &a, const AttnSmem &s, int tid, int h, int split, int nsplit, int pos, int bar_id, AttnRegs &R) {
     const int hd = a.hd, half = hd >> 1;
     const int kvh = h / (a.nh / a.nkv);
@@ -104,7 +106,18 @@ __device__ __forceinline__ void attn_preload(const AttnArgs &a, const AttnSmem &
     const int t0 = p0 * PAGE_TOKENS, t1 = min(n_ctx, p1 * PAGE_TOKENS);
     const int nt = max(0, t1 - t0);
     R.c = 1.f; R.s = 0.f;
+    R.qa = R.qb = R.ka = R.kb = R.va = R.vb = 0.f;
     if (tid < half) {   // the loops below give pair j to thread j % 128: hd <= 256
+        if (AFTER_WAIT) {   // q first: everything after it in this SM's load queue returns after it
+            const bool has_new = pos >= t0 && pos < t1;
+            R.qa = __ldcg(a.qkv + (int64_t)h * hd + tid);
+            R.qb = __ldcg(a.qkv + (int64_t)h * hd + tid + half);
+            if (has_new) {
+                const float *kr = a.qkv + (int64_t)(a.nh + kvh) * hd, *vr = a.qkv + (int64_t)(a.nh + a.nkv + kvh) * hd;
+                R.ka = __ldcg(kr + tid); R.kb = __ldcg(kr + tid + half);
+                R.va = __ldcg(vr + tid); R.vb = __ldcg(vr + tid + half);
+            }
+        }
         R.c = __ldg(a.cs + (int64_t)pos * half + tid);
         R.s = __ldg(a.sn + (int64_t)pos * half + tid);
     }
@@ -136,7 +149,7 @@ __device__ __forceinline__ void attn_preload(const AttnArgs &a, const AttnSmem &
 // Part 2: RoPE on q (and on the new k), KV append, scores, softmax, weighted values, merge of the splits, activation grid.
 // All 128 threads of the group call it with the same (h, split, nsplit, pos).
 // PRE: the first batches of K and V and the RoPE row were fetched by attn_preload into R.
-template <int MERGE, bool PRE>
+template <int MERGE, int PRE>   // PRE: 0 no preload, 1 attn_preload<false> before the wait, 2 attn_preload<true> after it (q, k, v in R too)
 __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, int tid, int h, int split, int nsplit, int pos, int bar_id, AttnRegs &R) {
     const int hd = a.hd, half = hd >> 1;
     float *sq = s.sq, *part = s.part, *og = s.og, *sc = s.sc, *red = s.red;
@@ -155,17 +168,17 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
     // ---- RoPE on the query (every split), on the new key (the split that owns position pos)
     const float *cs = a.cs + (int64_t)pos * half, *sn = a.sn + (int64_t)pos * half;
     for (int j = tid; j < half; j += 128) {
-        const float c = PRE ? R.c : cs[j], sv = PRE ? R.s : sn[j];
-        const float qa = __ldcg(a.qkv + (int64_t)h * hd + j), qb = __ldcg(a.qkv + (int64_t)h * hd + j + half);   // L2: written by the previous kernel/phase
+        const float c = PRE != 0 ? R.c : cs[j], sv = PRE != 0 ? R.s : sn[j];
+        const float qa = PRE == 2 ? R.qa : __ldcg(a.qkv + (int64_t)h * hd + j), qb = PRE == 2 ? R.qb : __ldcg(a.qkv + (int64_t)h * hd + j + half);   // L2: written by the previous kernel/phase
         sq[j] = __fsub_rn(__fmul_rn(qa, c), __fmul_rn(qb, sv));
         sq[j + half] = __fadd_rn(__fmul_rn(qb, c), __fmul_rn(qa, sv));
         if (has_new) {
             const float *kr = a.qkv + (int64_t)(a.nh + kvh) * hd, *vr = a.qkv + (int64_t)(a.nh + a.nkv + kvh) * hd;
-            const float ka = __ldcg(kr + j), kb = __ldcg(kr + j + half);
+            const float ka = PRE == 2 ? R.ka : __ldcg(kr + j), kb = PRE == 2 ? R.kb : __ldcg(kr + j + half);
             knew[j] = __float2half_rn(__fsub_rn(__fmul_rn(ka, c), __fmul_rn(kb, sv)));
             knew[j + half] = __float2half_rn(__fadd_rn(__fmul_rn(kb, c), __fmul_rn(ka, sv)));
-            vnew[j] = __float2half_rn(__ldcg(vr + j));
-            vnew[j + half] = __float2half_rn(__ldcg(vr + j + half));
+            vnew[j] = __float2half_rn(PRE == 2 ? R.va : __ldcg(vr + j));
+            vnew[j + half] = __float2half_rn(PRE == 2 ? R.vb : __ldcg(vr + j + half));
         }
     }
     group_sync(bar_id);
@@ -186,7 +199,7 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
         for (int u = 0; u < 4; ++u) {
             const int p = pb + u, tk = p * PAGE_TOKENS + key;
             const bool valid = p < p1 && tk < n_ctx, fresh = tk == pos;
-            const bool pre = PRE && pb == p0;   // older tokens of the first batch are already in registers
+            const bool pre = PRE != 0 && pb == p0;   // older tokens of the first batch are already in registers
             const __half *kr = fresh ? knew : a.kc + (((int64_t)((valid && !pre) ? spage[p - p0] : 0) * a.nkv + kvh) * PAGE_TOKENS + key) * hd;
 #pragma unroll
             for (int c4 = 0; c4 < 4; ++c4) {
@@ -254,7 +267,7 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const int i = ib + u * ngrp;
-                const bool pre = PRE && ib == grp;
+                const bool pre = PRE != 0 && ib == grp;
                 vv[u] = pre ? R.vv[u] : make_uint4(0u, 0u, 0u, 0u);
                 if (i < nt) {
                     const int tk = t0 + i;

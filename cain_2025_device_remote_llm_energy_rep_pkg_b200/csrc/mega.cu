@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_token_loop(const MegaRun r)
                 prof_stamp(1);
                 grid_barrier();    // q, k, v of this token are complete
                 prof_stamp(2);
-                if (active) { AttnRegs R; attn_main<MERGE_GLOBAL, false>(A, as, gt, h, split, nsplit, pos, 1 + grp, R); }
+                if (active) { AttnRegs R; attn_main<MERGE_GLOBAL, 0>(A, as, gt, h, split, nsplit, pos, 1 + grp, R); }
                 prof_stamp(5);
                 prof_next();
             }
