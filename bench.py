@@ -226,6 +226,26 @@ def aggregate(dist, wall_s, eval_s, tokens, launches, energy_j, device="cuda"):
     return vec.tolist(), tot.tolist()
 
 
+def ncu_traffic_per_token(model: str):
+    """DRAM bytes (read + write) of one decoded token from the committed ncu launch list (profiles/r01b_launches_summary.csv,
+    captured on llama3.1:8b): per-launch bytes of every kernel x its launches per token.  None for other workloads."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01b_launches_summary.csv")
+    if model != "llama3.1:8b" or not os.path.exists(path):
+        return None
+    import csv
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
+    per_layer = ("k_gemv<0, 2>", "k_gemv<2, 1>", "k_gemv<0, 0>", "k_gemv<1, 1>", "k_attn_fused")
+    once = ("k_gemv<0, 3>", "k_embed_row", "k_argmax_partials", "k_commit_sample", "k_advance")
+    total = 0.0
+    for r in csv.DictReader(open(path)):
+        b = (float(r["dram_read_MB_per_launch"]) + float(r["dram_write_MB_per_launch"])) * 1e6
+        if any(k in r["kernel"] for k in per_layer):
+            total += b * ARCHS[model].L
+        elif any(k in r["kernel"] for k in once):
+            total += b
+    return total or None
+
+
 def run_ours(args):
     import torch
     import __graft_entry__ as g
@@ -261,6 +281,7 @@ def run_ours(args):
         a = ARCHS[args.model]
         peak, peak_src = peaks()
         value = tokens / eval_s
+        traffic = ncu_traffic_per_token(args.model)
         step_bytes = r["weight_bytes"] + r["kv_bytes_per_token"]
         ach = step_bytes * (r["tokens"] / r["eval_s"]) / 1e9   # per GPU: every replica reads its own copy
         line = {
@@ -275,7 +296,7 @@ def run_ours(args):
                     "note": "host-timed b2_session_reset+b2_prefill+b2_decode per request; includes prompt evaluation"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "decode token step (CUDA graph; GEMV k_gemv_q4_0 dominates)", "achieved": ach,
-                         "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_launch": step_bytes, "launch": "one decoded token", "avg_launch_us": 1e6 * r["eval_s"] / r["tokens"]},
             "clocks": r["clocks"],
             "joules_per_token": (energy / tokens) if energy else None,
