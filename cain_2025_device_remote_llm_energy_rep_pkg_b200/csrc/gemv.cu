@@ -64,12 +64,12 @@ void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, flo
     k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out);
 }
 // ------------------------------------------------------------------------------------------ the kernel
-template <int IN, int OUT>
+template <int IN, int OUT, int PATH>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint32_t parity = 0;
     const GemvPtrs pv = {a.w, a.norm_w, a.bias_or_res};
-    gemv_phase<IN, OUT, false>(a, pv, smem, parity);
+    gemv_phase<IN, OUT, false, PATH>(a, pv, smem, parity);
 }
 
 // ------------------------------------------------------------------------------------------ launcher
@@ -89,11 +89,11 @@ int gemv_grid(int n_tiles, int tile_align) {
     return units < g_num_sms ? units : g_num_sms;
 }
 
-template <int IN, int OUT>
-static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
+template <int IN, int OUT, int PATH>
+static cudaError_t launch_path(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT, PATH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -107,7 +107,14 @@ static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStre
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, k_gemv<IN, OUT>, a);
+    return cudaLaunchKernelEx(&cfg, k_gemv<IN, OUT, PATH>, a);
+}
+template <int IN, int OUT>
+static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
+    const int cpt = (a.nbp + KC - 1) / KC;
+    if (a.k_outer) return launch_path<IN, OUT, 2>(a, grid, smem, st, pdl);
+    if (cpt == 2) return launch_path<IN, OUT, 0>(a, grid, smem, st, pdl);
+    return launch_path<IN, OUT, 1>(a, grid, smem, st, pdl);
 }
 
 // Fill the argument block of one GEMV (everything but the debug pointer) and report the dynamic shared memory it needs.

@@ -321,7 +321,11 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
 // One GEMV phase executed by a whole 512-thread CTA.  MEGA = false: the body of the stand-alone kernel k_gemv (ordered after the
 // previous kernel by griddepcontrol.wait).  MEGA = true: a phase of the persistent token kernel (mega.cu): ordered after the
 // previous phase by a grid-wide barrier; the mbarrier of the input copies lives across phases (bar_parity flips per use).
-template <int IN, int OUT, bool MEGA>
+// PATH: -1 = all three loop orders compiled in and chosen at run time (persistent kernel: shapes are per model);
+//       0 / 1 / 2 = only tiles-outermost with two chunks per tile / with one chunk / chunks-outermost.  The stand-alone
+//       kernels are instantiated per path: a third of the code per kernel means fewer instruction-cache misses at every
+//       kernel start (no_instructions was 4-13 % of the warp samples of these 10-30 us kernels).
+template <int IN, int OUT, bool MEGA, int PATH = -1>
 __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
     float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
     float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
@@ -479,7 +483,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
     WPiece buf0 = {z4, z4, z4}, buf1 = {z4, z4, z4}, buf2 = {z4, z4, z4}, buf3 = {z4, z4, z4};
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    if (!a.k_outer) {
+    if (PATH == -1 ? !a.k_outer : PATH != 2) {
         // ================= tiles outermost: the CTA's bytes are one contiguous run of chunks; K spans one or two chunks whose
         // B fragments stay in registers for the whole kernel.  With two chunks per tile the even pieces are full chunks and
         // the odd ones the (possibly shorter) last chunk of a tile: no index arithmetic in the loop.
@@ -503,7 +507,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
         auto load_last = [&](WPiece &r) {
             if (l_rem > 0) { if (act_last) load_piece(lp, cb_last, warp, lane, r); lp += cb_last * BLOCK_BYTES; --l_rem; }
         };
-        if (cpt == 2) {
+        if (PATH == -1 ? cpt == 2 : PATH == 0) {
             stage_input([&]() { load_full(buf0); load_last(buf1); load_full(buf2); load_last(buf3); });
             BFrag bf0, bf1;
             load_b(0, bf0);
