@@ -602,7 +602,7 @@ static bool build_mega_plan(b2_session *s) {
     mk(P->gateup, GEMV_IN_NORM, l0.gateup, s->x, l0.ffn_norm, nullptr, s->h, nullptr, c.act, nullptr, nullptr, s->xsq + 512, nullptr);
     mk(P->down, GEMV_IN_F32, l0.down, nullptr, nullptr, s->h, s->x, s->x, 0, nullptr, nullptr, nullptr, s->xsq);
     mk(P->head, GEMV_IN_NORM, m->head, s->x, m->out_norm, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, s->xsq, nullptr);
-    const size_t attn_smem = GEMV_FIXED_SMEM + (size_t)4 * attn_group_floats(hd, pps_max) * 4;
+    const size_t attn_smem = GEMV_FIXED_SMEM(GEMV_RB_MAX) + (size_t)4 * attn_group_floats(hd, pps_max) * 4;
     if (attn_smem > smem) smem = attn_smem;
     if (c.n_heads * ATTN_NSPLIT > 4 * grid || grid > 512 || (H % QK) != 0) ok = false;   // one attention item per 128-thread group; xsq halves hold 512 partials
     int g2 = 0;

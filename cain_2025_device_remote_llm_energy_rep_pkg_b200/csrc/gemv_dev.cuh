@@ -80,12 +80,12 @@ __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, ui
 #ifndef MMA_GROUP
 #define MMA_GROUP 2                          // independent MMAs in flight per warp before their results are scaled (4 costs 8 more registers)
 #endif
-#define GEMV_RB 8                            // finished tiles buffered in shared memory between two CTA-wide reductions
 
 struct GemvArgs {
     const uint8_t *w;        // packed matrix
     int rows, nbp, n_tiles;  // logical rows, padded blocks per row, tiles
     int tile_align;          // tiles are dealt to CTAs in multiples of this (4 for act*mul so A3 blocks stay whole)
+    int rb;                  // finished tiles parked in shared memory between two CTA-wide reductions (<= GEMV_RB_MAX; 2 when k_outer)
     int k_outer;             // 1: loop chunks outermost (long K, <= GEMV_MAXT tiles per CTA); 0: tiles outermost (K <= 2 chunks)
     // input
     const float *x;          // IN_NORM: residual stream, n_in floats
@@ -194,8 +194,11 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
     r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * 128 + (lane >> 2) * 16);
 }
 
-// shared memory map (bytes): [red GEMV_RB*16*16*4*4 = 32768][hbuf GEMV_RB*8 floats + 64 scratch = 512][A3 of the input nbp*100]
-#define GEMV_FIXED_SMEM (GEMV_RB * 4096 + 512)
+// shared memory map (bytes): [header 512: 64 floats of scratch, the input-copy mbarrier at +256][red rb*16*16*4*4 = rb*4096]
+//                            [A3 of the input nbp*100 (+ fp32 staging)]     rb = GemvArgs::rb, tiles parked between two reductions
+#define GEMV_HDR_SMEM 512
+#define GEMV_RB_MAX 16                       // one warp finalises one parked tile
+#define GEMV_FIXED_SMEM(rb) (GEMV_HDR_SMEM + (rb) * 4096)
 
 // ---- Input staging.  What the previous kernel wrote reaches shared memory through cp.async.bulk (the TMA path): an ordinary load
 // would complete only after the ~70 KB of weight loads this SM already has in flight (the L1 load queue is a FIFO).  Thread 0 issues
@@ -270,10 +273,10 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
 
 // ---- reduction + epilogue of the `batch_n` finished tiles parked in shared memory (called by all threads).
 // Every warp parked its K-partial of the 16 rows x 3 digit planes; warp w finalises tile batch_first + w.
-// Two CTA-wide barriers per GEMV_RB tiles instead of one per tile: the weight streams of the sixteen warps are not
+// Two CTA-wide barriers per a.rb tiles instead of one per tile: the weight streams of the sixteen warps are not
 // re-synchronised on memory latency every other piece.
 template <int OUT>
-__device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or_res, float *red, float *hbuf, int batch_first, int batch_n, float &best_v, int &best_i,
+__device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or_res, float *red, int batch_first, int batch_n, float &best_v, int &best_i,
                                          float &sumsq) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __syncthreads();
@@ -327,11 +330,10 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
 //       kernel start (no_instructions was 4-13 % of the warp samples of these 10-30 us kernels).
 template <int IN, int OUT, bool MEGA, int PATH = -1>
 __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
-    float *red = (float *)smem;                                                 // [GEMV_RB tiles][16 warps][16 rows][4]
-    float *hbuf = red + GEMV_RB * GEMV_CWARPS * 16 * 4;                         // GEMV_RB*8 h values, then 64 floats of scratch
-    float *scratch = hbuf + GEMV_RB * 8;
-    uint64_t *bar = (uint64_t *)(hbuf + 96);                                    // completion of the input copies
-    uint8_t *sact = (uint8_t *)(hbuf + 128);                                    // A3 image of the input vector (+ fp32 staging, partials)
+    float *scratch = (float *)smem;                                             // 64 floats
+    uint64_t *bar = (uint64_t *)(smem + 256);                                   // completion of the input copies
+    float *red = (float *)(smem + GEMV_HDR_SMEM);                               // [rb tiles][16 warps][16 rows][4]
+    uint8_t *sact = smem + GEMV_FIXED_SMEM(a.rb);                               // A3 image of the input vector (+ fp32 staging, partials)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int bid = blockIdx.x;
     const int g = lane >> 2, t = lane & 3;
@@ -464,15 +466,15 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
     int batch_first = t0, batch_n = 0;
-    auto park = [&](float (&acc)[4]) {   // park the finished tile's partial; reduce when GEMV_RB tiles are waiting
+    auto park = [&](float (&acc)[4]) {   // park the finished tile's partial; reduce when a.rb tiles are waiting
         float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
         if (t < 2) {
             *(float2 *)(rb + (warp * 16 + g) * 4 + 2 * t) = make_float2(acc[0], acc[1]);
             *(float2 *)(rb + (warp * 16 + g + 8) * 4 + 2 * t) = make_float2(acc[2], acc[3]);
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
-        if (++batch_n == GEMV_RB) {
-            flush_batch<OUT>(a, pv.bias_or_res, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
+        if (++batch_n == a.rb) {
+            flush_batch<OUT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
             batch_first += batch_n;
             batch_n = 0;
         }
@@ -587,7 +589,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
     prefetch_next();
-    if (batch_n > 0) flush_batch<OUT>(a, pv.bias_or_res, red, hbuf, batch_first, batch_n, best_v, best_i, sumsq);
+    if (batch_n > 0) flush_batch<OUT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
     stamp(5);
     if (MEGA) prof_next();
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)

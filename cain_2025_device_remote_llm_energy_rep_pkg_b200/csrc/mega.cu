@@ -40,8 +40,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_token_loop(const MegaRun r)
     __shared__ int s_tok;
     const MegaPlan &P = c_plan;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    float *scratch = (float *)smem + GEMV_RB * GEMV_CWARPS * 16 * 4 + GEMV_RB * 8;   // the scratch floats of gemv_phase
-    uint64_t *bar = (uint64_t *)((float *)smem + GEMV_RB * GEMV_CWARPS * 16 * 4 + 96);   // its input-copy mbarrier
+    float *scratch = (float *)smem;              // the scratch floats of gemv_phase
+    uint64_t *bar = (uint64_t *)(smem + 256);    // its input-copy mbarrier
     if (tid == 0) {
         mbar_init(bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_token_loop(const MegaRun r)
                 const int item = grp * gridDim.x + blockIdx.x;          // items spread over the SMs first, then over the groups of a CTA
                 const bool active = item < A.nh * nsplit;
                 const int h = item / nsplit, split = item - h * nsplit;
-                const AttnSmem as = attn_carve((float *)(smem + GEMV_FIXED_SMEM) + grp * attn_group_floats(A.hd, A.pps_max), A.hd, A.pps_max);
+                const AttnSmem as = attn_carve((float *)(smem + GEMV_FIXED_SMEM(GEMV_RB_MAX)) + grp * attn_group_floats(A.hd, A.pps_max), A.hd, A.pps_max);
                 __syncthreads();   // every warp of this CTA has left the QKV phase: its shared memory is free
                 prof_stamp(0);
                 if (active) attn_pages(A, as, gt, h, split, nsplit, pos);
