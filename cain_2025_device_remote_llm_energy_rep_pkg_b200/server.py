@@ -83,21 +83,27 @@ class GenerationResult:
 class B2Backend:
     """Model residency + one serial session per model on one GPU (requests are serialised per backend)."""
 
-    def __init__(self, device: int = 0, seed: int = 1, qtype: str = "q4_0", stream_chunk: int = 16, default_sampling: bool = False):
+    def __init__(self, device: int = 0, seed: int = 1, qtype: str = "q4_0", stream_chunk: int = 16, default_sampling: bool = False,
+                 gguf: Optional[Dict[str, str]] = None, requantize: bool = False):
         from .engine import Engine
         self.engine = Engine(device)
         self.device, self.seed, self.qtype, self.stream_chunk = device, seed, qtype, stream_chunk
         self.default_sampling = default_sampling
+        self.gguf = dict(gguf or {})          # tag -> GGUF file: real weights and tokenizer instead of random init + byte stand-in
+        self.requantize = requantize
+        self.tokenizers: Dict[str, object] = {}
         self.models: Dict[str, tuple] = {}
         self.lock = threading.Lock()
 
     def list_models(self) -> List[str]:
-        return list(ARCHS)
+        return list(ARCHS) + [t for t in self.gguf if t not in ARCHS]
 
     def loaded(self) -> List[str]:
         return list(self.models)
 
     def arch(self, tag: str) -> Arch:
+        if tag in self.models:
+            return self.models[tag][0].arch
         if tag not in ARCHS:
             raise KeyError(tag)
         return ARCHS[tag]
@@ -105,9 +111,17 @@ class B2Backend:
     def _load(self, tag: str):
         from .engine import Model
         if tag not in self.models:
-            a = self.arch(tag)
             t0 = time.perf_counter_ns()
-            model = Model.random(self.engine, a, seed=self.seed, qtype=self.qtype)
+            if tag in self.gguf:
+                from . import gguf_io
+                g = gguf_io.load(self.gguf[tag], requantize=self.requantize, name=tag)
+                a = g.arch
+                model = Model.from_tensors(self.engine, a, g.tensors)
+                if g.tokenizer.tokens:
+                    self.tokenizers[tag] = tokenizer.GGUFTokenizer(g.tokenizer, a.family)
+            else:
+                a = self.arch(tag)
+                model = Model.random(self.engine, a, seed=self.seed, qtype=self.qtype)
             sess = model.session(a.max_ctx)
             self.models[tag] = (model, sess, time.perf_counter_ns() - t0)
             return self.models[tag], self.models[tag][2]
@@ -127,7 +141,9 @@ class B2Backend:
             e0 = self.energy_mj()
             (model, sess, _), load_ns = self._load(tag)
             a = model.arch
-            ptoks = tokenizer.encode(prompt, a.V, a.family, template=not raw)
+            tk = self.tokenizers.get(tag)
+            ptoks = tk.encode(prompt, template=not raw) if tk else tokenizer.encode(prompt, a.V, a.family, template=not raw)
+            detok = tk.decode if tk else tokenizer.decode
             budget = int(options.get("num_predict", default_num_predict(prompt)))
             room = a.max_ctx - len(ptoks)
             if room <= 0:
@@ -146,11 +162,16 @@ class B2Backend:
             while len(out) < budget:
                 n = min(self.stream_chunk if options.get("_stream") else budget, budget - len(out))
                 toks = [int(t) for t in sess.decode(n, sampler=cfg)]
+                if tk and any(tk.is_eos(t) for t in toks):       # a real vocabulary has a real end-of-sequence token
+                    toks = toks[:next(i for i, t in enumerate(toks) if tk.is_eos(t))]
+                    reason = "stop"
                 out += toks
-                yield {"tokens": toks}
+                yield {"tokens": toks, "text": detok(toks)}
+                if reason == "stop":
+                    break
             st = sess.stats()
             e1 = self.energy_mj()
-            yield {"done": True, "done_reason": reason, "prompt_tokens": ptoks, "tokens": out,
+            yield {"done": True, "done_reason": reason, "prompt_tokens": ptoks, "tokens": out, "text": detok(out),
                    "total_duration": time.perf_counter_ns() - t_start, "load_duration": load_ns,
                    "prompt_eval_count": st["prompt_eval_count"], "prompt_eval_duration": st["prompt_eval_ns"],
                    "eval_count": st["eval_count"], "eval_duration": st["eval_ns"],
@@ -249,10 +270,10 @@ class Handler(BaseHTTPRequestHandler):
                     if part.get("done"):
                         line = self._final(model, part, "", chat)
                     elif chat:
-                        line = {"model": model, "created_at": _now(), "message": {"role": "assistant", "content": tokenizer.decode(part["tokens"])},
+                        line = {"model": model, "created_at": _now(), "message": {"role": "assistant", "content": part.get("text", tokenizer.decode(part["tokens"]))},
                                 "done": False}
                     else:
-                        line = {"model": model, "created_at": _now(), "response": tokenizer.decode(part["tokens"]), "done": False}
+                        line = {"model": model, "created_at": _now(), "response": part.get("text", tokenizer.decode(part["tokens"])), "done": False}
                     data = (json.dumps(line) + "\n").encode()
                     self.wfile.write(b"%x\r\n%s\r\n" % (len(data), data))
                     self.wfile.flush()
@@ -262,7 +283,7 @@ class Handler(BaseHTTPRequestHandler):
                 for part in gen:
                     if part.get("done"):
                         final = part
-                self._send_json(200, self._final(model, final, tokenizer.decode(final["tokens"]), chat))
+                self._send_json(200, self._final(model, final, final.get("text", tokenizer.decode(final["tokens"])), chat))
         except ValueError as ex:
             self._error(400, str(ex))
         except Exception as ex:  # engine failure: Ollama convention is {"error": ...} with a 5xx
@@ -327,8 +348,12 @@ def main():
     ap.add_argument("--preload", default="", help="comma-separated model tags to load before serving")
     ap.add_argument("--ollama-sampling", action="store_true",
                     help="requests without sampling options use Ollama's stochastic defaults (top_k 40, top_p 0.9, temperature 0.8) instead of greedy")
+    ap.add_argument("--gguf", action="append", default=[], metavar="TAG=PATH",
+                    help="serve TAG from a GGUF file (Q4_0 matrices; real tokenizer and EOS) instead of random-init weights")
+    ap.add_argument("--requantize", action="store_true", help="convert non-Q4_0 matrices of a GGUF file to Q4_0 at load (lossy)")
     a = ap.parse_args()
-    backend = B2Backend(a.device, a.seed, default_sampling=a.ollama_sampling)
+    backend = B2Backend(a.device, a.seed, default_sampling=a.ollama_sampling,
+                        gguf=dict(x.split("=", 1) for x in a.gguf), requantize=a.requantize)
     for tag in filter(None, a.preload.split(",")):
         backend._load(tag)
     srv = OllamaServer((a.host, a.port), backend, a.stats_file)
