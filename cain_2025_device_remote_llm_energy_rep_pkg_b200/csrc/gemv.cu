@@ -36,6 +36,41 @@ void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_pac
     int64_t nb = cols / QK, n = rows * nb;
     k_pack_q4_0<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
 }
+// GGML Q4_K row-major super-blocks (144 B: f16 d | f16 dmin | 12 B packed 6-bit scales/mins | 128 B nibbles) -> streaming
+// layout (layout.cuh).  One thread per 32-element sub-block.  ggml: sub-blocks 2p and 2p+1 share the bytes qs[32p..32p+31]
+// (low / high nibbles); scale and min of sub-block j follow get_scale_min_k4.
+__global__ void k_pack_q4_k(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
+                            int64_t dst_row0, int64_t dst_row_stride) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * nb) return;
+    const int64_t r = i / nb, b = i - r * nb;
+    const int j = (int)(b & 7);
+    const uint8_t *p = src + (r * (nb >> 3) + (b >> 3)) * 144;
+    const uint8_t *q = p + 4, *qs = p + 16 + 32 * (j >> 1);
+    uint8_t sc, m;
+    if (j < 4) { sc = q[j] & 63; m = q[j + 4] & 63; }
+    else { sc = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4); m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
+    const int sh = 4 * (j & 1);
+    PackedLocK loc = packed_loc_k(dst_row0 + r * dst_row_stride, b, nbp);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        uint32_t w = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int e = 4 * t + k;
+            const uint32_t lo = (qs[e] >> sh) & 0xF, hi = (qs[e + 16] >> sh) & 0xF;
+            w |= (lo | (hi << 4)) << (8 * k);
+        }
+        *(uint32_t *)(dst + loc.word0 + t * 16) = w ^ 0x88888888u;
+    }
+    dst[loc.scm] = sc;
+    dst[loc.scm + 1] = m;
+    *(uint32_t *)(dst + loc.dm) = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);   // every sub-block writes the same value
+}
+void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+    int64_t nb = cols / QK, n = rows * nb;
+    k_pack_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+}
 // Deterministic random init straight into the streaming layout; same bytes as b2_randinit_tensor + pack.
 __global__ void k_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
                                 int64_t dst_row0, int64_t dst_row_stride) {
@@ -64,12 +99,12 @@ void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, flo
     k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out);
 }
 // ------------------------------------------------------------------------------------------ the kernel
-template <int IN, int OUT, int PATH>
+template <int IN, int OUT, int PATH, int QT>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint32_t parity = 0;
     const GemvPtrs pv = {a.w, a.norm_w, a.bias_or_res};
-    gemv_phase<IN, OUT, false, PATH>(a, pv, smem, parity);
+    gemv_phase<IN, OUT, false, PATH, QT>(a, pv, smem, parity);
 }
 
 // ------------------------------------------------------------------------------------------ launcher
@@ -89,11 +124,11 @@ int gemv_grid(int n_tiles, int tile_align) {
     return units < g_num_sms ? units : g_num_sms;
 }
 
-template <int IN, int OUT, int PATH>
+template <int IN, int OUT, int PATH, int QT>
 static cudaError_t launch_path(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT, PATH>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT, PATH, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -107,22 +142,27 @@ static cudaError_t launch_path(const GemvArgs &a, int grid, size_t smem, cudaStr
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, k_gemv<IN, OUT, PATH>, a);
+    return cudaLaunchKernelEx(&cfg, k_gemv<IN, OUT, PATH, QT>, a);
+}
+template <int IN, int OUT, int QT>
+static cudaError_t launch_qt(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
+    const int cpt = (a.nbp + KC - 1) / KC;
+    if (a.k_outer) return launch_path<IN, OUT, 2, QT>(a, grid, smem, st, pdl);
+    if (cpt == 2) return launch_path<IN, OUT, 0, QT>(a, grid, smem, st, pdl);
+    return launch_path<IN, OUT, 1, QT>(a, grid, smem, st, pdl);
 }
 template <int IN, int OUT>
 static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
-    const int cpt = (a.nbp + KC - 1) / KC;
-    if (a.k_outer) return launch_path<IN, OUT, 2>(a, grid, smem, st, pdl);
-    if (cpt == 2) return launch_path<IN, OUT, 0>(a, grid, smem, st, pdl);
-    return launch_path<IN, OUT, 1>(a, grid, smem, st, pdl);
+    return a.qt ? launch_qt<IN, OUT, 1>(a, grid, smem, st, pdl) : launch_qt<IN, OUT, 0>(a, grid, smem, st, pdl);
 }
 
 // Fill the argument block of one GEMV (everything but the debug pointer) and report the dynamic shared memory it needs.
 cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                            float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
                            float *pmax, int *pidx, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n, float *xsq_out,
-                           size_t *smem_out) {
+                           size_t *smem_out, int qt) {
     a = GemvArgs{};
+    a.qt = qt;
     a.xsq_in = xsq_in; a.xsq_n = xsq_n; a.xsq_out = xsq_out;
     a.w = (const uint8_t *)d_packed;
     a.rows = (int)rows;
@@ -147,7 +187,7 @@ cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64
     // a flush costs two CTA barriers and stalls all sixteen streams: park as many tiles as there are warps to finalise them
     // (LM head 62.5 -> 60.3 us, +1.7 % tokens/s against 8); with chunks outermost a CTA has at most GEMV_MAXT tiles
     a.rb = a.k_outer ? GEMV_MAXT : GEMV_RB_MAX;
-    const size_t smem = GEMV_FIXED_SMEM(a.rb) + (size_t)a.nbp * 100 + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
+    const size_t smem = GEMV_FIXED_SMEM(a.rb) + (size_t)a.nbp * (qt ? 104 : 100) + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
     if (smem_out) *smem_out = smem;
     return cudaSuccess;
@@ -159,10 +199,18 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
                         float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
                         float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
                         float *xsq_out, cudaStream_t st, bool pdl) {
+    return launch_gemv_qt(0, in_mode, out_mode, d_packed, rows, cols, x, norm_w, eps, plus_one, act_in, y, bias_or_res, act_out, act, pmax, pidx,
+                          grid_out, next_w, next_bytes, xsq_in, xsq_n, xsq_out, st, pdl);
+}
+// qt: 0 = Q4_0 matrix, 1 = Q4_K matrix (layout.cuh)
+cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
+                           float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
+                           float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
+                           float *xsq_out, cudaStream_t st, bool pdl) {
     GemvArgs a;
     size_t smem = 0;
     cudaError_t em = gemv_make_args(a, in_mode, d_packed, rows, cols, x, norm_w, eps, plus_one, act_in, y, bias_or_res, act_out, act, pmax, pidx,
-                                    next_w, next_bytes, xsq_in, xsq_n, xsq_out, &smem);
+                                    next_w, next_bytes, xsq_in, xsq_n, xsq_out, &smem, qt);
     if (em != cudaSuccess) return em;
     a.dbg = g_gemv_dbg ? g_gemv_dbg + (size_t)(g_gemv_dbg_next++ % g_gemv_dbg_slots) * 148 * 8 : nullptr;
     int grid = gemv_grid(a.n_tiles, a.tile_align);
@@ -184,7 +232,7 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     for (int tbeg = 0; tbeg < a.n_tiles; tbeg += per_launch) {
         GemvArgs aa = a;
         const int tn = a.n_tiles - tbeg < per_launch ? a.n_tiles - tbeg : per_launch;
-        aa.w = a.w + (uint64_t)tbeg * a.nbp * BLOCK_BYTES;
+        aa.w = a.w + (uint64_t)tbeg * a.nbp * (a.qt ? BLOCK_BYTES_K : BLOCK_BYTES);
         aa.n_tiles = tn;
         aa.rows = (int)(rows - (int64_t)tbeg * TILE_ROWS < (int64_t)tn * TILE_ROWS ? rows - (int64_t)tbeg * TILE_ROWS : (int64_t)tn * TILE_ROWS);
         aa.y = y + (int64_t)tbeg * TILE_ROWS;

@@ -85,6 +85,7 @@ struct GemvArgs {
     const uint8_t *w;        // packed matrix
     int rows, nbp, n_tiles;  // logical rows, padded blocks per row, tiles
     int tile_align;          // tiles are dealt to CTAs in multiples of this (4 for act*mul so A3 blocks stay whole)
+    int qt;                  // 0: Q4_0 matrix, 1: Q4_K matrix
     int rb;                  // finished tiles parked in shared memory between two CTA-wide reductions (<= GEMV_RB_MAX; 2 when k_outer)
     int k_outer;             // 1: loop chunks outermost (long K, <= GEMV_MAXT tiles per CTA); 0: tiles outermost (K <= 2 chunks)
     // input
@@ -125,7 +126,7 @@ enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3 };
 cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                            float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
                            float *pmax, int *pidx, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n, float *xsq_out,
-                           size_t *smem_out);
+                           size_t *smem_out, int qt = 0);
 
 // one row of a packed matrix, dequantised (token embedding lookup and tests)
 __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int64_t col, int64_t nbp) {
@@ -135,6 +136,17 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
     int nib = (word >> (8 * (e & 3) + ((e >> 4) << 2))) & 0xF;    // two's complement of q-8
     int v = (nib ^ 8) - 8;
     return (float)v * __half2float(__ushort_as_half(*(const uint16_t *)(w + loc.scale)));
+}
+// the same for a Q4_K matrix: d1 = d*sc, m1 = dmin*m, value = q*d1 - m1, each op rounded (gguf-py / oracle/quants.py order)
+__device__ __forceinline__ float packed_elem_k(const uint8_t *w, int64_t row, int64_t col, int64_t nbp) {
+    PackedLocK loc = packed_loc_k(row, col / QK, nbp);
+    int e = (int)(col % QK);
+    uint32_t word = *(const uint32_t *)(w + loc.word0 + ((e & 15) >> 2) * 16);
+    int nib = (word >> (8 * (e & 3) + ((e >> 4) << 2))) & 0xF;    // two's complement of q-8
+    int q = ((nib ^ 8) - 8) + 8;
+    const float2 dm = __half22float2(*(const __half2 *)(w + loc.dm));
+    const float d1 = __fmul_rn(dm.x, (float)w[loc.scm]), m1 = __fmul_rn(dm.y, (float)w[loc.scm + 1]);
+    return __fsub_rn(__fmul_rn((float)q, d1), m1);
 }
 
 
@@ -158,10 +170,24 @@ __device__ __forceinline__ uint4 ldcg4(const void *p) {         // activations w
     return r;
 }
 
-struct WPiece { uint4 wa, wb, sd; };                 // one block-group of weights for this lane: rows g / g+8, 4 blocks, + their scales
-struct BFrag { uint4 b01, b23; float4 as; };         // activation digits (B fragments of 4 blocks) + block scales (already / 16)
+// QT = 0: Q4_0 matrix, QT = 1: Q4_K matrix (layout.cuh).
+// One block-group of weights for this lane: rows g / g+8, 4 blocks, + their scales (Q4_0: half2 (d_g, d_g+8) per block;
+// Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) per block and dm = half2 (d, dmin) of row g, of row g+8).
+template <int QT> struct WPieceT { uint4 wa, wb, sd; };
+template <> struct WPieceT<1> { uint4 wa, wb, sd; uint2 dm; };
+// Activation digits (B fragments of 4 blocks) + block scales (already / 16); Q4_K also needs ts = the sum of the gridded
+// activations of block 4*bg + t (this lane's share of the "- dmin*m" term, which multiplies a block SUM, not a dot product).
+template <int QT> struct BFragT { uint4 b01, b23; float4 as; };
+template <> struct BFragT<1> { uint4 b01, b23; float4 as; float ts; };
+template <int QT> struct WLay { static constexpr int BB = QT ? BLOCK_BYTES_K : BLOCK_BYTES, SC = QT ? 192 : 128; };
+// small unsigned byte k of `word` as a float without I2F: 0x4B0000bb is 8388608 + bb
+__device__ __forceinline__ float byte_to_float(uint32_t word, int k) {
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u | (uint32_t)k)) - 8388608.0f;
+}
 
-__device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&acc)[4]) {
+// off[0..1] (Q4_K): running sums of (8A - B) * block sum for rows g / g+8, this lane's block (j = t) of every block-group
+template <int QT>
+__device__ __forceinline__ void bg_mma(const WPieceT<QT> &r, const BFragT<QT> &b, float (&acc)[4], float (&off)[2], int t) {
     const uint32_t ua[4] = {r.wa.x, r.wa.y, r.wa.z, r.wa.w}, ub[4] = {r.wb.x, r.wb.y, r.wb.z, r.wb.w};
     const uint32_t bx[4] = {b.b01.x, b.b01.z, b.b23.x, b.b23.z}, by[4] = {b.b01.y, b.b01.w, b.b23.y, b.b23.w};
     const uint32_t sdw[4] = {r.sd.x, r.sd.y, r.sd.z, r.sd.w};
@@ -178,7 +204,14 @@ __device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&
 #pragma unroll
         for (int u = 0; u < MMA_GROUP; ++u) {
             const int j = jh + u;
-            const float2 dd = __half22float2(*(const __half2 *)&sdw[j]);
+            float2 dd;
+            if constexpr (QT == 0) {
+                dd = __half22float2(*(const __half2 *)&sdw[j]);
+            } else {   // A = d * sc per row (fp32, as the oracle's dequantisation)
+                const float2 dg = __half22float2(*(const __half2 *)&r.dm.x), dg8 = __half22float2(*(const __half2 *)&r.dm.y);
+                dd.x = __fmul_rn(dg.x, byte_to_float(sdw[j], 0));
+                dd.y = __fmul_rn(dg8.x, byte_to_float(sdw[j], 2));
+            }
             const float f0 = dd.x * asf[j], f1 = dd.y * asf[j];
             acc[0] = fmaf(__int_as_float(c[u][0]) - MMA_MAGIC_F, f0, acc[0]);
             acc[1] = fmaf(__int_as_float(c[u][1]) - MMA_MAGIC_F, f0, acc[1]);
@@ -186,12 +219,27 @@ __device__ __forceinline__ void bg_mma(const WPiece &r, const BFrag &b, float (&
             acc[3] = fmaf(__int_as_float(c[u][3]) - MMA_MAGIC_F, f1, acc[3]);
         }
     }
+    if constexpr (QT == 1) {   // w = A*(q-8) + (8A - B): the second term times the block's sum of activations, block j = t
+        const uint32_t w = t == 0 ? r.sd.x : t == 1 ? r.sd.y : t == 2 ? r.sd.z : r.sd.w;
+        const float2 dg = __half22float2(*(const __half2 *)&r.dm.x), dg8 = __half22float2(*(const __half2 *)&r.dm.y);
+        const float c0 = __fsub_rn(8.0f * __fmul_rn(dg.x, byte_to_float(w, 0)), __fmul_rn(dg.y, byte_to_float(w, 1)));
+        const float c1 = __fsub_rn(8.0f * __fmul_rn(dg8.x, byte_to_float(w, 2)), __fmul_rn(dg8.y, byte_to_float(w, 3)));
+        off[0] = fmaf(c0, b.ts, off[0]);
+        off[1] = fmaf(c1, b.ts, off[1]);
+    }
 }
 // one piece of the stream: block-group column `warp` of the chunk at `ch` (cb blocks)
-__device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, int lane, WPiece &r) {
+__device__ __forceinline__ uint2 ldg_stream2(const void *p) {
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+template <int QT>
+__device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, int lane, WPieceT<QT> &r) {
     r.wa = ldg_stream4(ch + (size_t)warp * 1024 + lane * 16);
     r.wb = ldg_stream4(ch + (size_t)warp * 1024 + 512 + lane * 16);
-    r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * 128 + (lane >> 2) * 16);
+    r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * WLay<QT>::SC + (lane >> 2) * 16);
+    if constexpr (QT == 1) r.dm = ldg_stream2(ch + (size_t)cb * 256 + warp * WLay<QT>::SC + 128 + (lane >> 2) * 8);
 }
 
 // shared memory map (bytes): [header 512: 64 floats of scratch, the input-copy mbarrier at +256][red rb*16*16*4*4 = rb*4096]
@@ -208,15 +256,33 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
 // op order of oracle/model.py:_norm), puts them on the activation grid (a 32-element block is 8 consecutive lanes: three shuffles
 // for the block maximum) and writes its own block-groups of the shared-memory activation image.
 // Shared memory of the input area: [A3 image nbp*100][staging: fp32 vector n_in*4][xsq partials 1 KB]
-template <int IN>
+// Q4_K adds float ts[nbp] after the scales: ts[b] = sum of the gridded activations of block b (staging area moves up by nbp*4).
+template <int IN, int QT>
 __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPtrs &pv, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
                                                  const float4 (&wn)[2]) {
+    constexpr int A3S = QT ? 104 : 100;
+    float *sts = (float *)(sact + (size_t)a.nbp * 100);
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
         mbar_wait(bar, parity);
         prof_stamp(6);
+        if constexpr (QT == 1) {   // block sums from the digits: lane = (t, j, half) reads one word of each plane of its block-group
+            const float *sscale = (const float *)(sact + (size_t)a.nbp * 96);
+            for (int ck = 0; ck < cpt; ++ck) {
+                const int kbg = ck * (KC / 4) + warp;
+                if (kbg * 4 >= a.nbp) break;
+                const uint32_t *pl = (const uint32_t *)(sact + (size_t)kbg * 384) + lane;
+                int xs = __dp4a((int)pl[0], 0x01010101, 0) + 128 * __dp4a((int)pl[32], 0x01010101, 0) + 16384 * __dp4a((int)pl[64], 0x01010101, 0);
+                xs += __shfl_xor_sync(0xffffffffu, xs, 1);
+                xs += __shfl_xor_sync(0xffffffffu, xs, 8);
+                xs += __shfl_xor_sync(0xffffffffu, xs, 16);
+                const int j = (lane >> 1) & 3;
+                if ((lane & 0x19) == 0) sts[kbg * 4 + j] = (float)xs * sscale[kbg * 4 + j];
+            }
+            __syncwarp();
+        }
         return;
     }
-    const float *sx = (const float *)(sact + (size_t)a.nbp * 100);
+    const float *sx = (const float *)(sact + (size_t)a.nbp * A3S);
     const float *sq = sx + a.n_in;
     float *sscale = (float *)(sact + (size_t)a.nbp * 96);
     mbar_wait(bar, parity);
@@ -253,10 +319,13 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
         const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
         const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
         uint32_t w0 = 0, w1 = 0, w2 = 0;
+        int xsum = 0;
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             int d0, d1, d2;
-            act_digits(__float2int_rn(yv[e] * inv), d0, d1, d2);
+            const int X = __float2int_rn(yv[e] * inv);
+            xsum += X;
+            act_digits(X, d0, d1, d2);
             w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
             w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
             w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
@@ -267,6 +336,12 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
         *(uint32_t *)(dst + 128) = w1;
         *(uint32_t *)(dst + 256) = w2;
         if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
+        if constexpr (QT == 1) {
+            xsum += __shfl_xor_sync(0xffffffffu, xsum, 1);
+            xsum += __shfl_xor_sync(0xffffffffu, xsum, 2);
+            xsum += __shfl_xor_sync(0xffffffffu, xsum, 4);
+            if (k == 0) sts[b] = (q < n4) ? (float)xsum * sc : 0.f;
+        }
     }
     __syncwarp();
 }
@@ -275,7 +350,7 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
 // Every warp parked its K-partial of the 16 rows x 3 digit planes; warp w finalises tile batch_first + w.
 // Two CTA-wide barriers per a.rb tiles instead of one per tile: the weight streams of the sixteen warps are not
 // re-synchronised on memory latency every other piece.
-template <int OUT>
+template <int OUT, int QT>
 __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or_res, float *red, int batch_first, int batch_n, float &best_v, int &best_i,
                                          float &sumsq) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -285,18 +360,20 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
         const int tile = batch_first + warp;
         const float *rb = red + (size_t)warp * (GEMV_CWARPS * 16 * 4);
         const int r = lane & 15, hf = lane >> 4;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
 #pragma unroll
         for (int w8 = 0; w8 < GEMV_CWARPS / 2; ++w8) {
             const float4 p4 = *(const float4 *)(rb + ((hf * (GEMV_CWARPS / 2) + w8) * 16 + r) * 4);
             v0 += p4.x;
             v1 += p4.y;
             v2 += p4.z;
+            if (QT == 1) v3 += p4.w;   // Q4_K: the "(8A - B) * block sum" term
         }
         v0 += __shfl_xor_sync(0xffffffffu, v0, 16);
         v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
         v2 += __shfl_xor_sync(0xffffffffu, v2, 16);
-        const float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
+        float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
+        if (QT == 1) yv += v3 + __shfl_xor_sync(0xffffffffu, v3, 16);
         const int row = tile * TILE_ROWS + r;
         if (OUT == OUT_BIAS) {
             if (lane < 16 && row < a.rows) a.y[row] = bias_or_res ? yv + bias_or_res[row] : yv;
@@ -328,7 +405,7 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
 //       0 / 1 / 2 = only tiles-outermost with two chunks per tile / with one chunk / chunks-outermost.  The stand-alone
 //       kernels are instantiated per path: a third of the code per kernel means fewer instruction-cache misses at every
 //       kernel start (no_instructions was 4-13 % of the warp samples of these 10-30 us kernels).
-template <int IN, int OUT, bool MEGA, int PATH = -1>
+template <int IN, int OUT, bool MEGA, int PATH = -1, int QT = 0>
 __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
     float *scratch = (float *)smem;                                             // 64 floats
     uint64_t *bar = (uint64_t *)(smem + 256);                                   // completion of the input copies
@@ -358,14 +435,14 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     const int t0 = u0 * a.tile_align, t1 = min(a.n_tiles, u1 * a.tile_align);
     const int nt = t1 - t0;
     const int cpt = (a.nbp + KC - 1) / KC;                                      // chunks per tile
-    const uint8_t *base = pv.w + (uint64_t)t0 * a.nbp * BLOCK_BYTES;
-    const uint32_t tile_bytes = (uint32_t)a.nbp * BLOCK_BYTES;
+    const uint8_t *base = pv.w + (uint64_t)t0 * a.nbp * WLay<QT>::BB;
+    const uint32_t tile_bytes = (uint32_t)a.nbp * WLay<QT>::BB;
     const int cb_last = a.nbp - (cpt - 1) * KC;                                 // blocks in the last chunk of a tile
     const bool act_full = warp < (KC >> 2);                                     // this warp has a block-group in a full chunk ...
     const bool act_last = warp < (cb_last >> 2);                                // ... in the last chunk of a tile
 
     // B fragments of block-group column `warp` of chunk ck, from the shared-memory activation image
-    auto load_b = [&](int ck, BFrag &b) {
+    auto load_b = [&](int ck, BFragT<QT> &b) {
         const int kbg = ck * (KC / 4) + warp;
         b.b01 = make_uint4(0u, 0u, 0u, 0u);
         b.b23 = make_uint4(0u, 0u, 0u, 0u);
@@ -379,6 +456,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
             b.as = *(const float4 *)(sact + (size_t)a.nbp * 96 + kbg * 16);
             b.as.x *= 0.0625f; b.as.y *= 0.0625f; b.as.z *= 0.0625f; b.as.w *= 0.0625f;   // the 1/16 of the nibble trick
         }
+        if constexpr (QT == 1) b.ts = (kbg * 4 < a.nbp) ? *(const float *)(sact + (size_t)a.nbp * 100 + (kbg * 4 + t) * 4) : 0.f;
     };
     // pull this CTA's share of the next kernel's weights into L2 (lane 0 of every warp, 16 KB per instruction)
     auto prefetch_next = [&]() {
@@ -425,7 +503,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
                 mbar_expect_tx(bar, bytes);
                 rot_copy(sact, a.act_in, bytes);
             } else {
-                float *sx = (float *)(sact + (size_t)a.nbp * 100);
+                float *sx = (float *)(sact + (size_t)a.nbp * (QT ? 104 : 100));
                 const uint32_t bytes = (uint32_t)a.n_in * 4;
                 const uint32_t qbytes = IN == IN_NORM ? (uint32_t)((a.xsq_n + 3) & ~3) * 4 : 0;
                 mbar_expect_tx(bar, bytes + qbytes);
@@ -438,7 +516,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     };
     // Wait for the copy and put this warp's columns of the input on the activation grid.
     auto input_stage = [&]() {
-        stage_warp_input<IN>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn);
+        stage_warp_input<IN, QT>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn);
         bar_parity ^= 1;
         stamp(3);
     };
@@ -466,15 +544,22 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     float best_v = -INFINITY;
     int best_i = 0x7fffffff;
     int batch_first = t0, batch_n = 0;
-    auto park = [&](float (&acc)[4]) {   // park the finished tile's partial; reduce when a.rb tiles are waiting
+    auto park = [&](float (&acc)[4], float (&off)[2]) {   // park the finished tile's partial; reduce when a.rb tiles are waiting
         float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
+        if constexpr (QT == 1) {   // the four t lanes covered one block each: their sum rides in the unused fourth column (plane "3")
+            float o0 = off[0], o1 = off[1];
+            o0 += __shfl_xor_sync(0xffffffffu, o0, 1); o0 += __shfl_xor_sync(0xffffffffu, o0, 2);
+            o1 += __shfl_xor_sync(0xffffffffu, o1, 1); o1 += __shfl_xor_sync(0xffffffffu, o1, 2);
+            if (t == 1) { acc[1] = o0; acc[3] = o1; }
+            off[0] = off[1] = 0.f;
+        }
         if (t < 2) {
             *(float2 *)(rb + (warp * 16 + g) * 4 + 2 * t) = make_float2(acc[0], acc[1]);
             *(float2 *)(rb + (warp * 16 + g + 8) * 4 + 2 * t) = make_float2(acc[2], acc[3]);
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == a.rb) {
-            flush_batch<OUT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
+            flush_batch<OUT, QT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
             batch_first += batch_n;
             batch_n = 0;
         }
@@ -483,7 +568,10 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     // that is read-before-written on some path counts as live around the enclosing token/layer loops of the persistent kernel,
     // i.e. through every OTHER stage, and the stages then spill each other's pipelines.
     const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
-    WPiece buf0 = {z4, z4, z4}, buf1 = {z4, z4, z4}, buf2 = {z4, z4, z4}, buf3 = {z4, z4, z4};
+    WPieceT<QT> buf0, buf1, buf2, buf3;
+    buf0.wa = buf0.wb = buf0.sd = z4; buf1 = buf0; buf2 = buf0; buf3 = buf0;
+    if constexpr (QT == 1) { buf0.dm = make_uint2(0u, 0u); buf1.dm = buf0.dm; buf2.dm = buf0.dm; buf3.dm = buf0.dm; }
+    float off[2] = {0.f, 0.f}, off1[2] = {0.f, 0.f};   // Q4_K: the "- dmin*m" sums of the tile(s) in flight
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     if (PATH == -1 ? !a.k_outer : PATH != 2) {
         // ================= tiles outermost: the CTA's bytes are one contiguous run of chunks; K spans one or two chunks whose
@@ -503,43 +591,43 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
             }
         };
         l2_window();
-        auto load_full = [&](WPiece &r) {
-            if (l_rem > 0) { if (act_full) load_piece(lp, KC, warp, lane, r); lp += KC * BLOCK_BYTES; --l_rem; }
+        auto load_full = [&](WPieceT<QT> &r) {
+            if (l_rem > 0) { if (act_full) load_piece<QT>(lp, KC, warp, lane, r); lp += KC * WLay<QT>::BB; --l_rem; }
         };
-        auto load_last = [&](WPiece &r) {
-            if (l_rem > 0) { if (act_last) load_piece(lp, cb_last, warp, lane, r); lp += cb_last * BLOCK_BYTES; --l_rem; }
+        auto load_last = [&](WPieceT<QT> &r) {
+            if (l_rem > 0) { if (act_last) load_piece<QT>(lp, cb_last, warp, lane, r); lp += cb_last * WLay<QT>::BB; --l_rem; }
         };
         if (PATH == -1 ? cpt == 2 : PATH == 0) {
             stage_input([&]() { load_full(buf0); load_last(buf1); load_full(buf2); load_last(buf3); });
-            BFrag bf0, bf1;
+            BFragT<QT> bf0, bf1;
             load_b(0, bf0);
             load_b(1, bf1);
             for (int rem = nt; rem > 0; rem -= 2) {
-                if (act_full) bg_mma(buf0, bf0, acc);
+                if (act_full) bg_mma<QT>(buf0, bf0, acc, off, t);
                 load_full(buf0);
-                if (act_last) bg_mma(buf1, bf1, acc);
+                if (act_last) bg_mma<QT>(buf1, bf1, acc, off, t);
                 load_last(buf1);
-                park(acc);
+                park(acc, off);
                 if (rem > 1) {
-                    if (act_full) bg_mma(buf2, bf0, acc);
+                    if (act_full) bg_mma<QT>(buf2, bf0, acc, off, t);
                     load_full(buf2);
-                    if (act_last) bg_mma(buf3, bf1, acc);
+                    if (act_last) bg_mma<QT>(buf3, bf1, acc, off, t);
                     load_last(buf3);
-                    park(acc);
+                    park(acc, off);
                 }
                 l2_window();
             }
         } else {
             stage_input([&]() { load_last(buf0); load_last(buf1); load_last(buf2); load_last(buf3); });
-            BFrag bf0;
+            BFragT<QT> bf0;
             load_b(0, bf0);
             for (int rem = nt; rem > 0; rem -= 4) {
-                if (act_last) bg_mma(buf0, bf0, acc);
+                if (act_last) bg_mma<QT>(buf0, bf0, acc, off, t);
                 load_last(buf0);
-                park(acc);
-                if (rem > 1) { if (act_last) bg_mma(buf1, bf0, acc); load_last(buf1); park(acc); }
-                if (rem > 2) { if (act_last) bg_mma(buf2, bf0, acc); load_last(buf2); park(acc); }
-                if (rem > 3) { if (act_last) bg_mma(buf3, bf0, acc); load_last(buf3); park(acc); }
+                park(acc, off);
+                if (rem > 1) { if (act_last) bg_mma<QT>(buf1, bf0, acc, off, t); load_last(buf1); park(acc, off); }
+                if (rem > 2) { if (act_last) bg_mma<QT>(buf2, bf0, acc, off, t); load_last(buf2); park(acc, off); }
+                if (rem > 3) { if (act_last) bg_mma<QT>(buf3, bf0, acc, off, t); load_last(buf3); park(acc, off); }
                 l2_window();
             }
         }
@@ -549,13 +637,13 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
         float acc1[4] = {0.f, 0.f, 0.f, 0.f};
         const bool two = nt > 1;
         int l_ck = 0;                     // chunk of the next step to request
-        auto load_step = [&](WPiece &r0, WPiece &r1) {
+        auto load_step = [&](WPieceT<QT> &r0, WPieceT<QT> &r1) {
             if (l_ck < cpt) {
                 const bool last = l_ck == cpt - 1;
                 if (last ? act_last : act_full) {
-                    const uint8_t *ch = base + (size_t)l_ck * (KC * BLOCK_BYTES);
-                    load_piece(ch, last ? cb_last : KC, warp, lane, r0);
-                    if (two) load_piece(ch + tile_bytes, last ? cb_last : KC, warp, lane, r1);
+                    const uint8_t *ch = base + (size_t)l_ck * (KC * WLay<QT>::BB);
+                    load_piece<QT>(ch, last ? cb_last : KC, warp, lane, r0);
+                    if (two) load_piece<QT>(ch + tile_bytes, last ? cb_last : KC, warp, lane, r1);
                 }
                 ++l_ck;
             }
@@ -564,32 +652,32 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
             for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
         }
         stage_input([&]() { load_step(buf0, buf1); load_step(buf2, buf3); });
-        BFrag bcur, bnxt;
+        BFragT<QT> bcur, bnxt;
         load_b(0, bcur);
         for (int ck = 0; ck < cpt; ck += 2) {
             load_b(ck + 1, bnxt);
             if ((ck == cpt - 1) ? act_last : act_full) {
-                bg_mma(buf0, bcur, acc);
-                if (two) bg_mma(buf1, bcur, acc1);
+                bg_mma<QT>(buf0, bcur, acc, off, t);
+                if (two) bg_mma<QT>(buf1, bcur, acc1, off1, t);
             }
             load_step(buf0, buf1);
             if (ck + 1 < cpt) {
                 load_b(ck + 2, bcur);
                 if ((ck + 1 == cpt - 1) ? act_last : act_full) {
-                    bg_mma(buf2, bnxt, acc);
-                    if (two) bg_mma(buf3, bnxt, acc1);
+                    bg_mma<QT>(buf2, bnxt, acc, off, t);
+                    if (two) bg_mma<QT>(buf3, bnxt, acc1, off1, t);
                 }
                 load_step(buf2, buf3);
             }
         }
-        if (nt > 0) park(acc);
-        if (two) park(acc1);
+        if (nt > 0) park(acc, off);
+        if (two) park(acc1, off1);
     }
     stamp(4);
     // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
     prefetch_next();
-    if (batch_n > 0) flush_batch<OUT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
+    if (batch_n > 0) flush_batch<OUT, QT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
     stamp(5);
     if (MEGA) prof_next();
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)

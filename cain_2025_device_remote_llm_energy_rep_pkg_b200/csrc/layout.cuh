@@ -53,6 +53,34 @@ __host__ __device__ inline PackedLoc packed_loc(int64_t row, int64_t blk, int64_
     return p;
 }
 
+// ---- Q4_K matrices (GGML super-blocks of 256: f16 d, f16 dmin, eight 6-bit (scale, min) pairs, 128 B of nibbles;
+// w = d*sc*q - dmin*m).  Same tiles, chunks and nibble area as Q4_0 (nibbles stored as q-8, so the int8 MMA path is shared and
+// w = A*(q-8) + (8A - B) with A = d*sc, B = dmin*m); the scale area of a block-group grows from 128 to 192 bytes:
+//     [g 0..7] 16 B : word j = (sc of row g, m of row g, sc of row g+8, m of row g+8) of block 4*bg+j
+//     [g 0..7]  8 B : half2 (d, dmin) of row g, half2 (d, dmin) of row g+8 -- of the super-block this block-group lies in
+// 304 bytes per 32-wide block column of a tile = 4.75 bit per weight (GGML: 4.5).
+#define BLOCK_BYTES_K 304
+__host__ __device__ inline uint64_t packed_q4_k_bytes(int64_t rows, int64_t cols) {
+    return (uint64_t)ntiles(rows) * nblocks_padded(cols) * BLOCK_BYTES_K;
+}
+struct PackedLocK {
+    uint64_t word0;   // as PackedLoc
+    uint64_t scm;     // byte offset of sc (m follows at +1)
+    uint64_t dm;      // byte offset of the half2 (d, dmin)
+};
+__host__ __device__ inline PackedLocK packed_loc_k(int64_t row, int64_t blk, int64_t nbp) {
+    int64_t T = row / TILE_ROWS, r = row % TILE_ROWS, hf = r >> 3, g = r & 7;
+    int64_t ck = blk / KC, bl = blk % KC;
+    int64_t cb = (nbp - ck * KC) < KC ? (nbp - ck * KC) : KC;
+    uint64_t chunk = (uint64_t)T * nbp * BLOCK_BYTES_K + (uint64_t)ck * KC * BLOCK_BYTES_K;
+    uint64_t sc = chunk + (uint64_t)cb * 256 + (uint64_t)(bl >> 2) * 192;
+    PackedLocK p;
+    p.word0 = chunk + (uint64_t)(bl >> 2) * 1024 + (uint64_t)(hf * 8 + g) * 64 + (uint64_t)(bl & 3) * 4;
+    p.scm = sc + (uint64_t)g * 16 + (uint64_t)(bl & 3) * 4 + (uint64_t)hf * 2;
+    p.dm = sc + 128 + (uint64_t)g * 8 + (uint64_t)hf * 4;
+    return p;
+}
+
 #ifdef __CUDACC__
 // store one activation block (warp-cooperative, lane = element) into an A3 vector of n elements
 __device__ __forceinline__ void a3_store_block(void *act, int64_t n, int64_t blk, int lane, int X, float scale) {

@@ -1,0 +1,87 @@
+"""Q4_K matrices (GGML super-blocks) through the streaming GEMV: the device re-pack keeps every bit of
+the blocks, and y = W x agrees with the pinned dequantisation (oracle/quants.py, checked against gguf-py) to fp32 summation order."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import quants as Q
+from oracle.model import fxp_round
+from test_ops_gpu import chk, D  # noqa: F401
+
+pytestmark = pytest.mark.gpu
+Q4K = 12
+
+
+def pack_k(lib, D, blob, rows, cols, blob2=None):
+    total = rows * (2 if blob2 is not None else 1)
+    d = D(lib.b2_packed_bytes(Q4K, total, cols))
+    b1 = np.ascontiguousarray(blob)
+    b2 = np.ascontiguousarray(blob2) if blob2 is not None else None
+    chk(lib, lib.b2_op_pack_weights(Q4K, rows, cols, b1.ctypes.data, b2.ctypes.data if b2 is not None else None, d.ptr))
+    return d
+
+
+def ref(blob, x):
+    W = Q.dequantize_q4_k(blob).astype(np.float64)
+    xq = fxp_round(torch.from_numpy(x)).numpy().astype(np.float64)
+    return W @ xq, np.abs(W) @ np.abs(xq)
+
+
+def rand_blob(rng, rows, cols, scale=0.02):
+    return Q.quantize_q4_k((rng.standard_normal((rows, cols)) * scale + 0.003).astype(np.float32))
+
+
+@pytest.mark.parametrize("rows,cols", [(16, 256), (100, 512), (256, 4096), (64, 14336), (1000, 1536)])
+def test_q4k_gemv_f32_input(lib, D, rows, cols):
+    rng = np.random.default_rng(rows + cols)
+    blob = rand_blob(rng, rows, cols)
+    x = (rng.standard_normal(cols) * np.exp(rng.standard_normal(cols))).astype(np.float32)
+    res = rng.standard_normal(rows).astype(np.float32)
+    dW, dx, dres, dy = pack_k(lib, D, blob, rows, cols), D.from_numpy(x), D.from_numpy(res), D(rows * 4)
+    want, mag = ref(blob, x)
+    chk(lib, lib.b2_op_gemv_f32(Q4K, dW.ptr, rows, cols, dx.ptr, None, 0, dy.ptr))
+    y = dy.to_numpy(np.float32, (rows,))
+    assert np.all(np.abs(y - want) <= 8e-6 * mag + 1e-30)
+    chk(lib, lib.b2_op_gemv_f32(Q4K, dW.ptr, rows, cols, dx.ptr, dres.ptr, 1, dres.ptr))
+    assert np.all(np.abs(dres.to_numpy(np.float32, (rows,)) - (want + res)) <= 8e-6 * mag + 1e-6 * np.abs(res))
+    # activation-image input (the O projection's path): block sums are rebuilt from the digits
+    act = D(lib.b2_act_bytes(cols))
+    chk(lib, lib.b2_op_quant_act(dx.ptr, cols, act.ptr))
+    dy2 = D(rows * 4)
+    chk(lib, lib.b2_op_gemv(Q4K, dW.ptr, rows, cols, act.ptr, None, 0, 0, dy2.ptr))
+    assert np.all(np.abs(dy2.to_numpy(np.float32, (rows,)) - want) <= 8e-6 * mag + 1e-30)
+
+
+@pytest.mark.parametrize("V,H,plus_one", [(1000, 512, 0), (5000, 4096, 1)])
+def test_q4k_norm_gemv_logits(lib, D, V, H, plus_one):
+    rng = np.random.default_rng(V + H)
+    blob = rand_blob(rng, V, H)
+    x = (rng.standard_normal(H) * 2).astype(np.float32)
+    w = (rng.standard_normal(H) * 0.1 + (0 if plus_one else 1)).astype(np.float32)
+    eps = np.float32(1e-5)
+    dW, dx, dw = pack_k(lib, D, blob, V, H), D.from_numpy(x), D.from_numpy(w)
+    dy, dtok = D(V * 4), D(4)
+    chk(lib, lib.b2_op_norm_gemv(Q4K, dW.ptr, V, H, dx.ptr, dw.ptr, eps, plus_one, None, 3, 0, dy.ptr, None, dtok.ptr))
+    y = dy.to_numpy(np.float32, (V,))
+    tx = torch.from_numpy(x)
+    xn = (tx * (1.0 / torch.sqrt((tx * tx).mean() + eps))) * ((1.0 + torch.from_numpy(w)) if plus_one else torch.from_numpy(w))
+    want, mag = ref(blob, xn.numpy())
+    assert np.all(np.abs(y - want) <= 1e-5 * mag + 1e-30)
+    assert int(dtok.to_numpy(np.int32, (1,))[0]) == int(np.argmax(y))
+
+
+def test_q4k_gate_up(lib, D):
+    rng = np.random.default_rng(5)
+    I, H = 512, 1024
+    g, u = rand_blob(rng, I, H, 0.05), rand_blob(rng, I, H, 0.05)
+    x = rng.standard_normal(H).astype(np.float32)
+    dW, dx, dw = pack_k(lib, D, g, I, H, u), D.from_numpy(x), D.from_numpy(np.ones(H, dtype=np.float32))
+    dy = D(I * 4)
+    chk(lib, lib.b2_op_norm_gemv(Q4K, dW.ptr, 2 * I, H, dx.ptr, dw.ptr, np.float32(1e-6), 0, None, 2, 0, dy.ptr, None, None))
+    tx = torch.from_numpy(x)
+    xn = (tx * (1.0 / torch.sqrt((tx * tx).mean() + np.float32(1e-6)))).numpy()
+    gv, _ = ref(g, xn)
+    uv, _ = ref(u, xn)
+    gt = torch.from_numpy(gv)
+    want = (gt / (1 + torch.exp(-gt))).numpy() * uv
+    assert np.abs(dy.to_numpy(np.float32, (I,)) - want).max() <= 3e-5 * np.abs(want).max()
