@@ -64,6 +64,7 @@ struct b2_model {
     std::vector<LayerW> layers;
     float *rope_cos = nullptr, *rope_sin = nullptr;
     uint64_t weight_bytes = 0;
+    bool all_q4_0 = true;          // the tcgen05 prompt GEMM and the persistent kernel take Q4_0 matrices only
     std::vector<void *> allocs;
     int q_dim() const { return cfg.n_heads * cfg.head_dim; }
     int kv_dim() const { return cfg.n_kv_heads * cfg.head_dim; }
@@ -205,15 +206,21 @@ static int build_rope(b2_model *m) {
     return B2_OK;
 }
 
+static inline uint64_t packed_bytes_of(int type, int64_t rows, int64_t cols) {
+    return type == B2_T_Q4_K ? packed_q4_k_bytes(rows, cols) : packed_q4_0_bytes(rows, cols);
+}
 static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type) {
-    B2_CHECK(type == B2_T_Q4_0, B2_EINVAL, "tensor type %d not supported (Q4_0 only in this build)", type);
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "tensor type %d not supported (Q4_0 and Q4_K matrices in this build)", type);
+    B2_CHECK(type != B2_T_Q4_K || cols % 256 == 0, B2_EINVAL, "Q4_K needs a multiple of 256 columns, got %lld", (long long)cols);
     mat.rows = rows;
     mat.cols = cols;
     mat.type = type;
-    B2_TRY(dev_alloc(m->allocs, &mat.packed, packed_q4_0_bytes(rows, cols)));
-    B2_CUDA(cudaMemsetAsync(mat.packed, 0, packed_q4_0_bytes(rows, cols), m->e->stream));   // row / block padding must be zero
+    if (type != B2_T_Q4_0) m->all_q4_0 = false;
+    B2_TRY(dev_alloc(m->allocs, &mat.packed, packed_bytes_of(type, rows, cols)));
+    B2_CUDA(cudaMemsetAsync(mat.packed, 0, packed_bytes_of(type, rows, cols), m->e->stream));   // row / block padding must be zero
     return B2_OK;
 }
+// GGML bytes of the matrix (what a token has to read): Q4_0 18 B / 32 weights, Q4_K 144 B / 256 weights -- both 4.5 bit
 static inline uint64_t algo_bytes(const Mat &m) { return (uint64_t)m.rows * (m.cols / QK) * 18; }
 
 static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype, int head_qtype, b2_model **out) {
@@ -282,26 +289,32 @@ extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
     float nsig = 0.1f, noff = c.norm_plus_one ? 0.0f : 1.0f, wsig = 0.02f, bsig = 0.1f;
     auto key = [&](int kind, uint32_t layer) { return ri_tensor_key(seed, tid_of(kind, layer)); };
-    launch_randinit_q4_0(key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, m->embd.packed, 0, 1, st);
-    if (!c.tied) launch_randinit_q4_0(key(K_OUTPUT, GLOBAL_LAYER), wsig, c.vocab, H, m->head.packed, 0, 1, st);
+    // Q4_0: gaussian weights through ggml's quantiser (bit-identical to b2_randinit_tensor and oracle/randinit.py);
+    // Q4_K: synthetic blocks (gemv.cu:k_randinit_q4_k), for benchmarks only
+    auto ri = [&](const Mat &mt, uint64_t k, float sig, int64_t rows, int64_t cols, int64_t row0, int64_t stride) {
+        if (mt.type == B2_T_Q4_K) launch_randinit_q4_k(k, rows, cols, mt.packed, row0, stride, st);
+        else launch_randinit_q4_0(k, sig, rows, cols, mt.packed, row0, stride, st);
+    };
+    ri(m->embd, key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, 0, 1);
+    if (!c.tied) ri(m->head, key(K_OUTPUT, GLOBAL_LAYER), wsig, c.vocab, H, 0, 1);
     launch_randinit_f32(key(K_OUT_NORM, GLOBAL_LAYER), nsig, noff, H, m->out_norm, st);
     for (int l = 0; l < c.n_layers; ++l) {
         LayerW &ly = m->layers[l];
         launch_randinit_f32(key(K_ATTN_NORM, l), nsig, noff, H, ly.attn_norm, st);
         launch_randinit_f32(key(K_FFN_NORM, l), nsig, noff, H, ly.ffn_norm, st);
         int64_t tr = qd + 2 * kvd;
-        launch_randinit_q4_0(key(K_Q, l), wsig, qd, H, ly.qkv.packed, 0, 1, st);
-        launch_randinit_q4_0(key(K_K, l), wsig, kvd, H, ly.qkv.packed, qd, 1, st);
-        launch_randinit_q4_0(key(K_V, l), wsig, kvd, H, ly.qkv.packed, qd + kvd, 1, st);
+        ri(ly.qkv, key(K_Q, l), wsig, qd, H, 0, 1);
+        ri(ly.qkv, key(K_K, l), wsig, kvd, H, qd, 1);
+        ri(ly.qkv, key(K_V, l), wsig, kvd, H, qd + kvd, 1);
         if (c.qkv_bias) {
             launch_randinit_f32(key(K_QB, l), bsig, 0.f, qd, ly.qkv_bias, st);
             launch_randinit_f32(key(K_KB, l), bsig, 0.f, kvd, ly.qkv_bias + qd, st);
             launch_randinit_f32(key(K_VB, l), bsig, 0.f, kvd, ly.qkv_bias + qd + kvd, st);
         }
-        launch_randinit_q4_0(key(K_O, l), wsig, H, qd, ly.o.packed, 0, 1, st);
-        launch_randinit_q4_0(key(K_GATE, l), wsig, I, H, ly.gateup.packed, 0, 2, st);
-        launch_randinit_q4_0(key(K_UP, l), wsig, I, H, ly.gateup.packed, 1, 2, st);
-        launch_randinit_q4_0(key(K_DOWN, l), wsig, H, I, ly.down.packed, 0, 1, st);
+        ri(ly.o, key(K_O, l), wsig, H, qd, 0, 1);
+        ri(ly.gateup, key(K_GATE, l), wsig, I, H, 0, 2);
+        ri(ly.gateup, key(K_UP, l), wsig, I, H, 1, 2);
+        ri(ly.down, key(K_DOWN, l), wsig, H, I, 0, 1);
     }
     cudaError_t err = cudaStreamSynchronize(st);
     if (err == cudaSuccess) err = cudaGetLastError();
@@ -330,14 +343,15 @@ struct Staging {
 };
 
 static int upload_mat(b2_model *m, Staging &sg, const b2_tensor_desc &t, Mat &dst, int64_t dst_row0, int64_t stride, int64_t src_row0, int64_t nrows) {
-    B2_CHECK(t.type == B2_T_Q4_0, B2_EINVAL, "tensor %s: type %d not supported (Q4_0 only in this build)", t.name, t.type);
+    B2_CHECK(t.type == dst.type, B2_EINVAL, "tensor %s: type %d, but the matrix it belongs to is type %d (all parts of a fused matrix share one format)", t.name, t.type, dst.type);
     B2_CHECK(t.cols == dst.cols, B2_EINVAL, "tensor %s: cols %lld, expected %lld", t.name, (long long)t.cols, (long long)dst.cols);
-    uint64_t row_bytes = (uint64_t)(t.cols / QK) * 18;
+    uint64_t row_bytes = t.type == B2_T_Q4_K ? (uint64_t)(t.cols / 256) * 144 : (uint64_t)(t.cols / QK) * 18;
     B2_CHECK(t.nbytes == (uint64_t)t.rows * row_bytes, B2_EINVAL, "tensor %s: %llu bytes, expected %llu", t.name, (unsigned long long)t.nbytes, (unsigned long long)(t.rows * row_bytes));
     B2_CHECK(src_row0 + nrows <= t.rows, B2_EINVAL, "tensor %s: has %lld rows, need %lld", t.name, (long long)t.rows, (long long)(src_row0 + nrows));
     B2_TRY(sg.ensure(nrows * row_bytes));
     B2_CUDA(cudaMemcpyAsync(sg.buf, (const char *)t.data + src_row0 * row_bytes, nrows * row_bytes, cudaMemcpyHostToDevice, m->e->stream));
-    launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
+    if (t.type == B2_T_Q4_K) launch_pack_q4_k(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
+    else launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
     B2_CUDA(cudaStreamSynchronize(m->e->stream));
     return B2_OK;
 }
@@ -464,9 +478,9 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
     const bool pdl = s->use_pdl;
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
     int n = 0;
-    auto bytes_of = [](const Mat &mt) { return packed_q4_0_bytes(mt.rows, mt.cols); };
+    auto bytes_of = [](const Mat &mt) { return packed_bytes_of(mt.type, mt.rows, mt.cols); };
     float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
-    launch_embed_row(m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, s->xsq, st); n++;
+    launch_embed_row(m->embd.type == B2_T_Q4_K, m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, s->xsq, st); n++;
     int xsq_n = 1;   // how many partial sums of squares the producer of the current x left in s->xsq
     uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
@@ -474,7 +488,7 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
         int g = 0;
         // each GEMV hints the matrix the next GEMV will stream (L2 prefetch of the head of every CTA's share)
         const Mat *after_down = (l + 1 < c.n_layers) ? &m->layers[l + 1].qkv : (with_head ? &m->head : nullptr);
-        launch_gemv(GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+        launch_gemv_qt(ly.qkv.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), s->xsq, xsq_n, nullptr, st, pdl); n++;
         if (s->fused_attn) {
             launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
@@ -487,16 +501,16 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
             launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
         }
         // two partial-sum buffers alternate: a kernel reads the partials of its input while writing those of its output
-        launch_gemv(GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
+        launch_gemv_qt(ly.o.type == B2_T_Q4_K, GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, &g, ly.gateup.packed, bytes_of(ly.gateup), nullptr, 0, s->xsq + 512, st, pdl); n++;
-        launch_gemv(GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+        launch_gemv_qt(ly.gateup.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->h, nullptr, nullptr, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), s->xsq + 512, g, nullptr, st, pdl); n++;
-        launch_gemv(GEMV_IN_F32, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->h, s->x, s->x, nullptr, 0,
+        launch_gemv_qt(ly.down.type == B2_T_Q4_K, GEMV_IN_F32, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->h, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, &g, after_down ? after_down->packed : nullptr, after_down ? bytes_of(*after_down) : 0, nullptr, 0, s->xsq, st, pdl); n++;
         xsq_n = g;
     }
     if (with_head) {
-        launch_gemv(GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
+        launch_gemv_qt(m->head.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, m->layers[0].qkv.packed, bytes_of(m->layers[0].qkv),
                     s->xsq, xsq_n, nullptr, st, pdl); n++;
     }
@@ -578,7 +592,7 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
 static bool build_mega_plan(b2_session *s) {
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
-    if (c.n_layers > MEGA_MAX_LAYERS || !s->fused_attn) return false;
+    if (c.n_layers > MEGA_MAX_LAYERS || !s->fused_attn || !m->all_q4_0) return false;
     const int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
     MegaPlan *P = new MegaPlan();
     memset(P, 0, sizeof *P);
@@ -859,7 +873,7 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (s->use_pf_gemm && n >= 3) {
+    if (s->use_pf_gemm && s->m->all_q4_0 && n >= 3) {
         B2_TRY(prefill_batched(s, n));
     } else if (s->use_mega) {
         B2_TRY(run_mega(s, MEGA_PROMPT, n, n - 1, nullptr));

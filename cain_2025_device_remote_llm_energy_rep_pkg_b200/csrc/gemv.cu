@@ -91,6 +91,32 @@ void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols,
     int64_t nb = cols / QK, n = rows * nb;
     k_randinit_q4_0<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, sigma, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
 }
+// Synthetic Q4_K blocks straight into the streaming layout (benchmarks of SURVEY.md 8d config 4; no checkpoint exists offline
+// and ggml's Q4_K search quantiser is not worth running over 8 G weights): per super-block d = f16(9e-5 * (0.75 + u/2)),
+// dmin = 8 d; per sub-block sc in [32, 63], m = round(7.5 sc / 8) so that d*sc*q - dmin*m is centred; nibbles from the hash.
+// The dequantised weights have mean ~0 and standard deviation ~0.02 like the Q4_0 initialiser's.
+__global__ void k_randinit_q4_k(uint64_t key, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst, int64_t dst_row0, int64_t dst_row_stride) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * nb) return;
+    const int64_t r = i / nb, b = i - r * nb;
+    const uint64_t hs = ri_splitmix64(key ^ (0x5bd1e995ull * (uint64_t)(r * (nb >> 3) + (b >> 3) + 1)));   // per super-block
+    const uint64_t h0 = ri_splitmix64(key + 2 * (uint64_t)i), h1 = ri_splitmix64(key + 2 * (uint64_t)i + 1);
+    const float d = 9e-5f * (0.75f + 0.5f * (float)(hs & 0xFFFF) * (1.0f / 65536.0f));
+    const __half dh = __float2half_rn(d), dmh = __float2half_rn(8.0f * __half2float(dh));
+    const uint32_t sc = 32u + (uint32_t)((hs >> (16 + 5 * (b & 7))) & 31u), mn = (15u * sc + 8u) >> 4;
+    PackedLocK loc = packed_loc_k(dst_row0 + r * dst_row_stride, b, nbp);
+    *(uint32_t *)(dst + loc.word0) = (uint32_t)h0;
+    *(uint32_t *)(dst + loc.word0 + 16) = (uint32_t)(h0 >> 32);
+    *(uint32_t *)(dst + loc.word0 + 32) = (uint32_t)h1;
+    *(uint32_t *)(dst + loc.word0 + 48) = (uint32_t)(h1 >> 32);
+    dst[loc.scm] = (uint8_t)sc;
+    dst[loc.scm + 1] = (uint8_t)mn;
+    *(__half2 *)(dst + loc.dm) = __halves2half2(dh, dmh);
+}
+void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+    int64_t nb = cols / QK, n = rows * nb;
+    k_randinit_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+}
 __global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *__restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = ri_add(ri_mul(ri_gauss(key, (uint64_t)i), sigma), offset);
@@ -254,13 +280,14 @@ cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_pack
 
 // ------------------------------------------------------------------------------------------ embedding row
 // x = embedding row of the current token (gemma: * sqrt(H)); also leaves sum(x^2) for the first RMSNorm.  One block.
+template <int QT>
 __global__ void __launch_bounds__(1024) k_embed_row(const uint8_t *__restrict__ w, int64_t nbp, int n, const int *__restrict__ token, float scale,
                                                     float *__restrict__ x, float *__restrict__ xsq) {
     __shared__ float red[32];
     const int64_t row = __ldcg(token);
     float ss = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        float v = packed_elem(w, row, i, nbp);
+        float v = QT ? packed_elem_k(w, row, i, nbp) : packed_elem(w, row, i, nbp);
         if (scale != 1.0f) v = v * scale;
         x[i] = v;
         ss = fmaf(v, v, ss);
@@ -274,8 +301,9 @@ __global__ void __launch_bounds__(1024) k_embed_row(const uint8_t *__restrict__ 
         if (threadIdx.x == 0) xsq[0] = tv;
     }
 }
-void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st) {
-    k_embed_row<<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
+void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st) {
+    if (qt) k_embed_row<1><<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
+    else k_embed_row<0><<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
 }
 // sum of squares of an f32 vector into xsq[0] (op-level entry points that run the fused RMSNorm on a caller's vector)
 __global__ void __launch_bounds__(1024) k_sumsq(const float *__restrict__ x, int n, float *__restrict__ xsq) {

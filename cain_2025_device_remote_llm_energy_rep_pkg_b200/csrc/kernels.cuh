@@ -19,6 +19,7 @@ struct DevState {
 void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
+void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st);
 
 // streaming GEMV (gemv.cu)
@@ -33,7 +34,7 @@ cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_pack
                            float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
                            float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
                            float *xsq_out, cudaStream_t st, bool pdl);
-void launch_embed_row(const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);
+void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);
 void launch_sumsq(const float *d_x, int64_t n, float *d_xsq, cudaStream_t st);
 
 // small stages (kernels.cu)

@@ -85,3 +85,27 @@ def test_q4k_gate_up(lib, D):
     gt = torch.from_numpy(gv)
     want = (gt / (1 + torch.exp(-gt))).numpy() * uv
     assert np.abs(dy.to_numpy(np.float32, (I,)) - want).max() <= 3e-5 * np.abs(want).max()
+
+
+@pytest.mark.parametrize("key,head_qtype", [("qwen2:1.5b", "q4_k"), ("gemma:2b", "q4_0"), ("mistral:7b", "q4_k")])
+def test_q4k_model_matches_oracle(key, head_qtype, gpu_engine):
+    """The whole decode path on Q4_K layer matrices (and a Q4_K or Q4_0 head): teacher-forced logits and greedy tokens
+    against the PyTorch oracle on the same GGML blocks (oracle/randinit.make_model quantises with the restated llama.cpp search)."""
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200 import archs, engine
+    from oracle import archs as oarchs
+    from oracle import randinit as orand
+    from oracle.model import OracleModel
+    a = archs.TINY[key]
+    if a.H % 256 or a.I % 256 or a.q_dim % 256:
+        pytest.skip("Q4_K needs 256-element super-blocks along K")
+    tensors = orand.make_model(oarchs.TINY[key], seed=21, qtype="q4_k", head_qtype=head_qtype)
+    m = engine.Model.from_tensors(gpu_engine, a, tensors, max_ctx=96)
+    om = OracleModel(oarchs.TINY[key], tensors)
+    prompt = [1, 5, 77, 300, 12, 9, 640, 2]
+    got = m.session(96).forward_tokens(prompt)
+    os_ = om.session(96)
+    want = np.stack([os_.step(t).numpy() for t in prompt])
+    assert np.abs(got - want).max() <= 2e-4 * np.abs(want).max()
+    s = m.session(96)
+    toks = s.generate_greedy(prompt, 40)
+    assert list(map(int, toks)) == om.session(96).generate_greedy(prompt, 40)
