@@ -8,9 +8,10 @@ llama.cpp's converters that differ from the engine's (which follows the Hugging 
     rotate-half; they are permuted back here (rows are quantised independently, so this is exact);
   * gemma: the converter already stored (1 + w) in the norm weights -> norm_plus_one is off for GGUF gemma;
   * llama 3.1: the RoPE frequency scaling travels as the tensor rope_freqs.weight -> the Llama-3.1 constants are assumed.
-The engine's kernels take Q4_0 matrices and F32 vectors.  Other block formats (llama.cpp keeps output.weight in Q6_K even in
-"Q4_0" files) are refused unless `requantize=True`, which dequantises and re-quantises them to Q4_0 with the gguf package's
-own reference code (lossy; reported in `notes`)."""
+The engine's kernels take Q4_0 and Q4_K matrices (the parts of a fused QKV or gate/up matrix must share one format) and F32
+vectors.  Other block formats (llama.cpp keeps output.weight in Q6_K even in "Q4_0" files, and Q4_K_M mixes Q6_K into
+attn_v / ffn_down) are refused unless `requantize=True`, which dequantises every non-Q4_0 matrix and re-quantises it to Q4_0
+with the gguf package's own reference code (lossy; reported in `notes`)."""
 from __future__ import annotations
 
 from dataclasses import dataclass, field
@@ -120,12 +121,16 @@ def load(path: str, requantize: bool = False, name: Optional[str] = None) -> GGU
             out[t.name] = ("f32", np.ascontiguousarray(vec.reshape(-1)))
             continue
         cols, rows = int(t.shape[0]), int(t.shape[1])
+        qt_name = "q4_0"
         if t.tensor_type == QT.Q4_0:
             raw = np.ascontiguousarray(data).reshape(rows, cols // Q4_0_BLOCK * Q4_0_BYTES).view(np.uint8)
+        elif t.tensor_type == QT.Q4_K and not requantize:      # native in the decode GEMV (csrc/layout.cuh)
+            raw = np.ascontiguousarray(data).reshape(rows, cols // 256 * 144).view(np.uint8)
+            qt_name = "q4_k"
         else:
             if not requantize:
-                raise ValueError(f"{t.name} is {t.tensor_type.name}; the engine's matrices are Q4_0 "
-                                 f"(pass requantize=True to convert, lossy)")
+                raise ValueError(f"{t.name} is {t.tensor_type.name}; the engine's matrices are Q4_0 or Q4_K "
+                                 f"(pass requantize=True to convert everything else to Q4_0, lossy)")
             if t.tensor_type in (QT.F32, QT.F16):
                 dense = data.astype(np.float32).reshape(rows, cols)
             else:
@@ -137,7 +142,7 @@ def load(path: str, requantize: bool = False, name: Optional[str] = None) -> GGU
                 raw = _unpermute_rows(raw, nh)
             elif t.name.endswith("attn_k.weight"):
                 raw = _unpermute_rows(raw, nkv)
-        out[t.name] = ("q4_0", raw)
+        out[t.name] = (qt_name, raw)
     if family in ("llama", "mistral") and arch.qkv_bias:
         for l in range(L):
             for nm, n in (("attn_q.bias", nh), ("attn_k.bias", nkv)):
