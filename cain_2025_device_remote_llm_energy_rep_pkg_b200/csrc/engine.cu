@@ -831,19 +831,19 @@ static int prefill_batched(b2_session *s, int n) {
     int launches = 0;
     for (int m0 = 0; m0 < n; m0 += 64) {
         const int mb = n - m0 < 64 ? n - m0 : 64, T = pf_batch(mb), pos0 = s->host_pos + m0;
-        launch_prefill_embed(m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
+        launch_prefill_embed(m->embd.type == B2_T_Q4_K, m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
         for (int l = 0; l < c.n_layers; ++l) {
             LayerW &ly = m->layers[l];
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.attn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, s->pf_part, s->pf_part_floats, st));
+            B2_CUDA(launch_prefill_gemm_qt(ly.qkv.type == B2_T_Q4_K, PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, c.n_heads, c.n_kv_heads, hd, pos0, m->rope_cos, m->rope_sin,
                                              s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, s->pf_attn, qd, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_attn, qd, mb, T, qd, nullptr, 0.f, 0, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
+            B2_CUDA(launch_prefill_gemm_qt(ly.o.type == B2_T_Q4_K, PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.ffn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
+            B2_CUDA(launch_prefill_gemm_qt(ly.gateup.type == B2_T_Q4_K, PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_h, I, mb, T, I, nullptr, 0.f, 0, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm(PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
+            B2_CUDA(launch_prefill_gemm_qt(ly.down.type == B2_T_Q4_K, PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             launches += 10;
         }
         if (m0 + mb == n) {   // LM head for the last token of the prompt
@@ -851,7 +851,7 @@ static int prefill_batched(b2_session *s, int n) {
             launch_sumsq(s->x, H, s->xsq, st);
             launch_fill_partials(s->pmax, s->pidx, 1024, st);
             int grid = 0;
-            B2_CUDA(launch_gemv(GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
+            B2_CUDA(launch_gemv_qt(m->head.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
                                 s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &grid, nullptr, 0, s->xsq, 1, nullptr, st, false));
             if (!s->use_mega) s->head_grid = grid;
             launches += 3;
@@ -873,7 +873,7 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (s->use_pf_gemm && s->m->all_q4_0 && n >= 3) {
+    if (s->use_pf_gemm && n >= 3) {
         B2_TRY(prefill_batched(s, n));
     } else if (s->use_mega) {
         B2_TRY(run_mega(s, MEGA_PROMPT, n, n - 1, nullptr));

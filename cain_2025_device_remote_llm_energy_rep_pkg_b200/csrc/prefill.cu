@@ -59,7 +59,14 @@ __global__ void __launch_bounds__(256) k_prefill_quant(const float *__restrict__
         pb[pb_off(T, kb, 0, m, lane)] = (uint8_t)d0;
         pb[pb_off(T, kb, 1, m, lane)] = (uint8_t)d1;
         pb[pb_off(T, kb, 2, m, lane)] = (uint8_t)d2;
-        if (lane == 0) sa[(int64_t)kb * T + m] = (live && kb * QK < n) ? sc * 0.0625f : 0.f;
+        int xs = X;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) xs += __shfl_xor_sync(0xffffffffu, xs, o);
+        if (lane == 0) {
+            const bool on = live && kb * QK < n;
+            sa[(int64_t)kb * 2 * T + m] = on ? sc * 0.0625f : 0.f;
+            sa[(int64_t)kb * 2 * T + T + m] = on ? (float)xs * sc : 0.f;
+        }
     }
 }
 
@@ -134,12 +141,14 @@ struct PfSmem {
     static constexpr int A_OFF = 0;
     static constexpr int B_OFF = A_OFF + PF_STAGES * A_STAGE;
     static constexpr int DW_OFF = B_OFF + PF_STAGES * B_STAGE;
-    static constexpr int SA_OFF = DW_OFF + PF_STAGES * 4 * PF_ROWS * 4;
-    static constexpr int BAR_OFF = SA_OFF + PF_STAGES * 4 * T * 4;
+    static constexpr int CW_OFF = DW_OFF + PF_STAGES * 4 * PF_ROWS * 4;     // Q4_K: 8A - B per (block, row)
+    static constexpr int SA_OFF = CW_OFF + PF_STAGES * 4 * PF_ROWS * 4;
+    static constexpr int SA_STAGE = 4 * 2 * T * 4;                          // per block: sa[T], ts[T]
+    static constexpr int BAR_OFF = SA_OFF + PF_STAGES * SA_STAGE;
     static constexpr int TOTAL = BAR_OFF + 128;
 };
 
-template <int T, int OUT>
+template <int T, int OUT, int QT>
 __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) {
     using S = PfSmem<T>;
     constexpr int N = S::N;
@@ -181,7 +190,8 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
             for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
                 const int slot = it % PF_STAGES;
                 const float *dws = (const float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
-                const float *sas = (const float *)(smem + S::SA_OFF) + slot * 4 * T;
+                const float *sas = (const float *)(smem + S::SA_OFF + slot * S::SA_STAGE);
+                const float *cws = (const float *)(smem + S::CW_OFF) + slot * 4 * PF_ROWS;
                 mbar_wait(full + slot, (it / PF_STAGES) & 1);   // scales of the stage are in shared memory
 #pragma unroll 1
                 for (int b = 0; b < 4; ++b, ++kbi) {
@@ -189,6 +199,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                     mbar_wait(tfull + buf, (kbi >> 1) & 1);
                     tc_fence_after();
                     const float dw = dws[b * PF_ROWS + row_l];
+                    const float cw = QT ? cws[b * PF_ROWS + row_l] : 0.f;
 #pragma unroll
                     for (int t0 = 0; t0 < TS; t0 += 16) {
                         int c0[16], c1[16], c2[16];
@@ -203,7 +214,8 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                             const float f1 = __int_as_float(c1[u] + 0x4B400000) - 12582912.0f;
                             const float f2 = __int_as_float(c2[u] + 0x4B400000) - 12582912.0f;
                             const float xf = fmaf(16384.0f, f2, fmaf(128.0f, f1, f0));
-                            acc[t0 + u] = fmaf(xf, dw * sas[b * T + tk0 + t0 + u], acc[t0 + u]);
+                            acc[t0 + u] = fmaf(xf, dw * sas[b * 2 * T + tk0 + t0 + u], acc[t0 + u]);
+                            if (QT) acc[t0 + u] = fmaf(cw, sas[b * 2 * T + T + tk0 + t0 + u], acc[t0 + u]);
                         }
                     }
                     tc_fence_before();
@@ -249,22 +261,27 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                 if (tg >= a.n_tiles) continue;
                 for (int ck = bg0 >> 4; ck <= (bg1 - 1) >> 4; ++ck) {
                     const int cb = min(KC, a.nbp - ck * KC);
-                    l2_prefetch(a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES, (uint32_t)cb * BLOCK_BYTES);
+                    l2_prefetch(a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * (QT ? BLOCK_BYTES_K : BLOCK_BYTES), (uint32_t)cb * (QT ? BLOCK_BYTES_K : BLOCK_BYTES));
                 }
             }
         };
-        auto issue = [&](int grp, int bgi, uint4 (&v)[4], uint32_t (&sc)[2]) {
+        constexpr int BB = QT ? BLOCK_BYTES_K : BLOCK_BYTES, SCB = QT ? 192 : 128;
+        auto issue = [&](int grp, int bgi, uint4 (&v)[4], uint32_t (&sc)[2], uint2 (&dm)[2]) {
             const int ck = bgi >> 4, j = bgi & 15;
             const int cb = min(KC, a.nbp - ck * KC);
             sc[0] = sc[1] = 0u;
+            dm[0] = dm[1] = make_uint2(0u, 0u);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1, tg = grp * 8 + til;
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
                 if (tg < a.n_tiles) {
-                    const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BLOCK_BYTES;
+                    const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BB;
                     v[i] = ldg_stream4(chunk + (size_t)j * 1024 + hf * 512 + lane * 16);
-                    if (hf == 0) sc[i >> 1] = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * 128 + lane * 4));
+                    if (hf == 0) {   // Q4_0: half2 (d_g, d_g+8); Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) and half2 (d, dmin) of both rows
+                        sc[i >> 1] = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * SCB + lane * 4));
+                        if (QT) dm[i >> 1] = __ldg((const uint2 *)(chunk + (size_t)cb * 256 + j * SCB + 128 + (lane >> 2) * 8));
+                    }
                 }
             }
         };
@@ -278,11 +295,12 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         int wi = blockIdx.x, grp = 0, bgi = 0, bg1 = 0;
         uint4 v[4], vn[4];
         uint32_t sc[2], scn[2];
+        uint2 dm[2], dmn[2];
         prefetch_item(wi);
         if (wi < n_items) {
             item_range(wi, grp, bgi, bg1);
             prefetch_item(wi + gridDim.x);
-            issue(grp, bgi, v, sc);
+            issue(grp, bgi, v, sc, dm);
         }
         while (wi < n_items) {
             // the stage after this one (possibly the first of the next work item)
@@ -291,11 +309,12 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                 nwi = wi + gridDim.x;
                 if (nwi < n_items) { item_range(nwi, ngrp, nbgi, nbg1); prefetch_item(nwi + gridDim.x); }
             }
-            if (nwi < n_items) issue(ngrp, nbgi, vn, scn);
+            if (nwi < n_items) issue(ngrp, nbgi, vn, scn, dmn);
             const int slot = it % PF_STAGES;
             mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
             uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
             float *dws = (float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
+            float *cws = (float *)(smem + S::CW_OFF) + slot * 4 * PF_ROWS;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1;
@@ -306,10 +325,20 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                     *(uint32_t *)(dst + jj * 4096) = (wd[jj] << 4) & 0xF0F0F0F0u;        // elements 4t..4t+3   (k half 0)
                     *(uint32_t *)(dst + jj * 4096 + 128) = wd[jj] & 0xF0F0F0F0u;         // elements 16+4t..    (k half 1)
                 }
-                if (hf == 0) {   // lane = (row g, block jj = t): half2 = (d of row g, d of row g+8)
-                    const float2 d2 = __half22float2(*(const __half2 *)&sc[i >> 1]);
-                    dws[t * PF_ROWS + til * 16 + g] = d2.x;
-                    dws[t * PF_ROWS + til * 16 + g + 8] = d2.y;
+                if (hf == 0) {   // lane = (row g, block jj = t)
+                    if (QT == 0) {   // half2 = (d of row g, d of row g+8)
+                        const float2 d2 = __half22float2(*(const __half2 *)&sc[i >> 1]);
+                        dws[t * PF_ROWS + til * 16 + g] = d2.x;
+                        dws[t * PF_ROWS + til * 16 + g + 8] = d2.y;
+                    } else {         // A = d*sc, C = 8A - dmin*m (the same roundings as the decode GEMV)
+                        const uint32_t w = sc[i >> 1];
+                        const float2 dg = __half22float2(*(const __half2 *)&dm[i >> 1].x), dg8 = __half22float2(*(const __half2 *)&dm[i >> 1].y);
+                        const float a0 = __fmul_rn(dg.x, byte_to_float(w, 0)), a1 = __fmul_rn(dg8.x, byte_to_float(w, 2));
+                        dws[t * PF_ROWS + til * 16 + g] = a0;
+                        dws[t * PF_ROWS + til * 16 + g + 8] = a1;
+                        cws[t * PF_ROWS + til * 16 + g] = __fsub_rn(8.0f * a0, __fmul_rn(dg.y, byte_to_float(w, 1)));
+                        cws[t * PF_ROWS + til * 16 + g + 8] = __fsub_rn(8.0f * a1, __fmul_rn(dg8.y, byte_to_float(w, 3)));
+                    }
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tensor core reads these stores through the async proxy
@@ -320,6 +349,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
 #pragma unroll
             for (int i = 0; i < 4; ++i) v[i] = vn[i];
             sc[0] = scn[0]; sc[1] = scn[1];
+            dm[0] = dmn[0]; dm[1] = dmn[1];
         }
     } else if (warp == 12) {
         // ===================== MMA issue (one thread)
@@ -357,9 +387,9 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                 for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
                     const int slot = it % PF_STAGES;
                     mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
-                    mbar_expect_tx(full + slot, (uint32_t)(S::B_STAGE + 4 * T * 4));
+                    mbar_expect_tx(full + slot, (uint32_t)(S::B_STAGE + S::SA_STAGE));
                     bulk_g2s(smem + S::B_OFF + slot * S::B_STAGE, a.pb + (size_t)bgi * S::B_STAGE, (uint32_t)S::B_STAGE, full + slot);
-                    bulk_g2s(smem + S::SA_OFF + slot * 4 * T * 4, pbs + (size_t)bgi * 4 * T * 4, (uint32_t)(4 * T * 4), full + slot);
+                    bulk_g2s(smem + S::SA_OFF + slot * S::SA_STAGE, pbs + (size_t)bgi * S::SA_STAGE, (uint32_t)S::SA_STAGE, full + slot);
                 }
             }
         }
@@ -382,21 +412,29 @@ __global__ void __launch_bounds__(256) k_prefill_finish(const float *__restrict_
     y[(int64_t)m * ldy + row] = v;
 }
 
-template <int T, int OUT>
-static cudaError_t launch_pf(const PfArgs &a, int grid, cudaStream_t st) {
+template <int T, int OUT, int QT>
+static cudaError_t launch_pf_qt(const PfArgs &a, int grid, cudaStream_t st) {
     using S = PfSmem<T>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_prefill_gemm<T, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
+        cudaError_t e = cudaFuncSetAttribute(k_prefill_gemm<T, OUT, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    k_prefill_gemm<T, OUT><<<grid, PF_THREADS, S::TOTAL, st>>>(a);
+    k_prefill_gemm<T, OUT, QT><<<grid, PF_THREADS, S::TOTAL, st>>>(a);
     return cudaGetLastError();
+}
+template <int T, int OUT>
+static cudaError_t launch_pf(const PfArgs &a, int qt, int grid, cudaStream_t st) {
+    return qt ? launch_pf_qt<T, OUT, 1>(a, grid, st) : launch_pf_qt<T, OUT, 0>(a, grid, st);
 }
 
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
                                 const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st) {
+    return launch_prefill_gemm_qt(0, out_mode, d_packed, rows, cols, pb, M, T, y, ldy, bias_or_res, act, sm_count, part, part_floats, st);
+}
+cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
+                                   const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st) {
     if (M <= 0 || M > T || rows <= 0 || cols <= 0) return cudaErrorInvalidValue;
     if (out_mode == PF_OUT_RES && !bias_or_res) return cudaErrorInvalidValue;
     PfArgs a;
@@ -417,7 +455,7 @@ cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows
     const int n_items = n_groups * ksplit;
     const int grid = n_items < sm_count ? n_items : sm_count;
     cudaError_t e = cudaErrorInvalidValue;
-#define PF_CASE(TT, OO) if (T == TT && out_mode == OO) e = launch_pf<TT, OO>(a, grid, st)
+#define PF_CASE(TT, OO) if (T == TT && out_mode == OO) e = launch_pf<TT, OO>(a, qt, grid, st)
     PF_CASE(16, PF_OUT_BIAS); PF_CASE(16, PF_OUT_RES); PF_CASE(16, PF_OUT_ACTMUL);
     PF_CASE(32, PF_OUT_BIAS); PF_CASE(32, PF_OUT_RES); PF_CASE(32, PF_OUT_ACTMUL);
     PF_CASE(64, PF_OUT_BIAS); PF_CASE(64, PF_OUT_RES); PF_CASE(64, PF_OUT_ACTMUL);
@@ -429,18 +467,20 @@ cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows
 
 // ------------------------------------------------------------------------------------------ the other stages of a prompt batch
 // token embedding rows of M tokens (gemma: * sqrt(H)); grid (M)
+template <int QT>
 __global__ void __launch_bounds__(256) k_prefill_embed(const uint8_t *__restrict__ w, int64_t nbp, int n, const int *__restrict__ tokens, float scale,
                                                        float *__restrict__ x) {
     const int m = blockIdx.x;
     const int64_t row = tokens[m];
     for (int i = threadIdx.x; i < n; i += 256) {
-        float v = packed_elem(w, row, i, nbp);
+        float v = QT ? packed_elem_k(w, row, i, nbp) : packed_elem(w, row, i, nbp);
         if (scale != 1.0f) v = v * scale;
         x[(int64_t)m * n + i] = v;
     }
 }
-void launch_prefill_embed(const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st) {
-    k_prefill_embed<<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
+void launch_prefill_embed(int qt, const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st) {
+    if (qt) k_prefill_embed<1><<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
+    else k_prefill_embed<0><<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
 }
 
 // RoPE + KV append for M tokens at positions pos0..pos0+M-1: grid (nh + 2 nkv, M).  Same arithmetic as the decode kernels

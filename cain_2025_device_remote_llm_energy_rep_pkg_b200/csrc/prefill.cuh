@@ -11,7 +11,8 @@
 //   [kb 0..nbp)  one image of N rows x 32 bytes per 32-element block, already in the shared-memory layout tcgen05.mma wants
 //                (K-major, no swizzle: 8-row x 16-byte core matrices; row n = d*T + m for digit plane d of token m):
 //                byte of (n, k) at kb*N*32 + (n>>3)*256 + (k>>4)*128 + (n&7)*16 + (k&15)  -- one cp.async.bulk per stage
-//   then float sa[kb][T] = 2^(e-19)/16 (the 1/16 undoes the weights' x16), 0 for padding blocks and tokens >= M.
+//   then per block kb 2T floats: sa[T] = 2^(e-19)/16 (the 1/16 undoes the weights' x16; 0 for padding blocks and tokens >= M)
+//   and ts[T] = the sum of the token's gridded activations over the block (the Q4_K "- dmin*m" term multiplies it).
 #pragma once
 #include "kernels.cuh"
 #include "layout.cuh"
@@ -24,7 +25,7 @@ __host__ __device__ inline size_t pb_block_bytes(int T) { return (size_t)3 * T *
 __host__ __device__ inline size_t pb_scale_off(int T, int64_t nbp) { return (size_t)nbp * pb_block_bytes(T); }
 __host__ __device__ inline size_t pb_bytes(int T, int64_t n) {
     const int64_t nbp = nblocks_padded(n);
-    return pb_scale_off(T, nbp) + (size_t)nbp * T * 4;
+    return pb_scale_off(T, nbp) + (size_t)nbp * T * 8;
 }
 __host__ __device__ inline size_t pb_off(int T, int64_t kb, int d, int m, int k) {
     const int n = d * T + m;
@@ -41,9 +42,12 @@ cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M
                                  void *pb, cudaStream_t st);
 // `part` (may be NULL): scratch of part_floats floats for split-K partial sums (up to 8 * T * rows are used)
 // y[m][row] (row stride ldy) = sum_k W[row][k] * grid(x[m])[k]  (+ bias[row] | + res[m][row] | act(gate)*up with ldy = rows/2)
+// qt: 0 = Q4_0 matrix, 1 = Q4_K matrix
+cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
+                                   const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
                                 const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
-void launch_prefill_embed(const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st);
+void launch_prefill_embed(int qt, const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st);
 // RoPE (q in place) + KV append of M tokens at pos0.., then causal attention over the cache; out[m][nh*hd] fp32
 cudaError_t launch_prefill_attention(float *d_qkv, int64_t ld, int M, int nh, int nkv, int hd, int pos0, const float *d_cos, const float *d_sin,
                                      __half *d_k, __half *d_v, const int32_t *d_page_table, float *d_out, int64_t ldo, cudaStream_t st);

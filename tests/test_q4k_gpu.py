@@ -109,3 +109,22 @@ def test_q4k_model_matches_oracle(key, head_qtype, gpu_engine):
     s = m.session(96)
     toks = s.generate_greedy(prompt, 40)
     assert list(map(int, toks)) == om.session(96).generate_greedy(prompt, 40)
+
+
+@pytest.mark.parametrize("rows,cols,M", [(128, 256, 3), (1000, 512, 17), (4096, 4096, 33), (256, 14336, 64)])
+def test_q4k_prefill_gemm(lib, D, rows, cols, M):
+    """The tcgen05 prompt GEMM on a Q4_K matrix against the decode GEMV and the dequantised reference."""
+    rng = np.random.default_rng(rows + cols + M)
+    blob = rand_blob(rng, rows, cols)
+    x = (rng.standard_normal((M, cols)) * np.exp(rng.standard_normal((M, cols)))).astype(np.float32)
+    dW, dx = pack_k(lib, D, blob, rows, cols), D.from_numpy(x)
+    dy = D(M * rows * 4)
+    chk(lib, lib.b2_op_prefill_gemm(Q4K, dW.ptr, rows, cols, dx.ptr, M, None, 0.0, 0, None, 0, 0, dy.ptr))
+    y = dy.to_numpy(np.float32, (M, rows))
+    dy1, dx1 = D(rows * 4), D(cols * 4)
+    for m in sorted({0, M // 2, M - 1}):
+        want, mag = ref(blob, x[m])
+        assert np.all(np.abs(y[m] - want) <= 8e-6 * mag + 1e-30), f"token {m} vs reference"
+        chk(lib, lib.b2_dev_upload(dx1.ptr, x[m].ctypes.data, cols * 4))
+        chk(lib, lib.b2_op_gemv_f32(Q4K, dW.ptr, rows, cols, dx1.ptr, None, 0, dy1.ptr))
+        assert np.all(np.abs(y[m] - dy1.to_numpy(np.float32, (rows,))) <= 3e-6 * mag + 1e-30), f"token {m} vs decode kernel"
