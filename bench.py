@@ -32,7 +32,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="llama3.1:8b")
-    ap.add_argument("--qtype", default="q4_0")
+    ap.add_argument("--qtype", default="q4_0", help="format of the layer matrices: q4_0 (default, the north-star config) or q4_k")
+    ap.add_argument("--head-qtype", default=None, help="format of the LM head / embedding (default: as --qtype; q6_k is what llama.cpp writes)")
     ap.add_argument("--new-tokens", type=int, default=256)
     ap.add_argument("--prompt-len", type=int, default=32)
     ap.add_argument("--all-models", action="store_true", help="also report per-model tokens/s and J/token for all seven tags")
@@ -120,7 +121,7 @@ def run_reference(args):
             "warmup": args.warmup, "ms_per_step": 1000.0 * (time.perf_counter() - t0) / (args.warmup + args.steps),
             "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"{args.model} {args.qtype} batch-1 greedy decode, random-init weights, one replica per GPU",
+            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, one replica per GPU",
                        "new_tokens": args.new_tokens, "prompt_len": args.prompt_len, "requests_per_step_per_gpu": 1,
                        "step": f"bounded sample: {args.cpu_tokens} decode tokens of the oracle per step"},
             "cpu_baseline": info, "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -165,7 +166,7 @@ def bench_model(eng, key, args, lib, dev, dist, steps, warmup):
     from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
     from cain_2025_device_remote_llm_energy_rep_pkg_b200.engine import Model
     a = ARCHS[key]
-    model = Model.random(eng, a, seed=1, qtype=args.qtype)
+    model = Model.random(eng, a, seed=1, qtype=args.qtype, head_qtype=args.head_qtype)
     sess = model.session(a.max_ctx)
     prompt = prompt_tokens(args.prompt_len, a.V)
     T = args.new_tokens
@@ -288,7 +289,7 @@ def run_ours(args):
             "metric": "decode_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1000.0 * wall / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int4 weights x 21-bit fixed-point activations, int32/fp32 accumulate", "data": "synthetic",
-            "config": {"workload": f"{args.model} {args.qtype} batch-1 greedy decode, random-init weights, one replica per GPU",
+            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, one replica per GPU",
                        "new_tokens": args.new_tokens, "prompt_len": args.prompt_len, "requests_per_step_per_gpu": 1,
                        "l2": "inputs larger than L2 (weights %.0f MB per token)" % (r["weight_bytes"] / 1e6)},
             "e2e": {"value": tokens / wall, "unit": "tokens/s", "h2d_bytes_per_step": args.prompt_len * 4 + 16 * (1 + 1),

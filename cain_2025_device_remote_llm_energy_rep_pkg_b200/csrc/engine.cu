@@ -64,7 +64,8 @@ struct b2_model {
     std::vector<LayerW> layers;
     float *rope_cos = nullptr, *rope_sin = nullptr;
     uint64_t weight_bytes = 0;
-    bool all_q4_0 = true;          // the tcgen05 prompt GEMM and the persistent kernel take Q4_0 matrices only
+    bool all_q4_0 = true;          // the persistent kernel takes Q4_0 matrices only
+    bool layers_q4 = true;         // the tcgen05 prompt GEMM takes Q4_0 / Q4_K layer matrices (a Q6_K head is fine: it runs as a GEMV)
     std::vector<void *> allocs;
     int q_dim() const { return cfg.n_heads * cfg.head_dim; }
     int kv_dim() const { return cfg.n_kv_heads * cfg.head_dim; }
@@ -207,15 +208,16 @@ static int build_rope(b2_model *m) {
 }
 
 static inline uint64_t packed_bytes_of(int type, int64_t rows, int64_t cols) {
-    return type == B2_T_Q4_K ? packed_q4_k_bytes(rows, cols) : packed_q4_0_bytes(rows, cols);
+    return type == B2_T_Q6_K ? packed_q6_k_bytes(rows, cols) : type == B2_T_Q4_K ? packed_q4_k_bytes(rows, cols) : packed_q4_0_bytes(rows, cols);
 }
 static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type) {
-    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "tensor type %d not supported (Q4_0 and Q4_K matrices in this build)", type);
-    B2_CHECK(type != B2_T_Q4_K || cols % 256 == 0, B2_EINVAL, "Q4_K needs a multiple of 256 columns, got %lld", (long long)cols);
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K || type == B2_T_Q6_K, B2_EINVAL, "tensor type %d not supported (Q4_0, Q4_K and Q6_K matrices in this build)", type);
+    B2_CHECK(type == B2_T_Q4_0 || cols % 256 == 0, B2_EINVAL, "K-quants need a multiple of 256 columns, got %lld", (long long)cols);
     mat.rows = rows;
     mat.cols = cols;
     mat.type = type;
     if (type != B2_T_Q4_0) m->all_q4_0 = false;
+    if (type == B2_T_Q6_K && &mat != &m->embd && &mat != &m->head) m->layers_q4 = false;
     B2_TRY(dev_alloc(m->allocs, &mat.packed, packed_bytes_of(type, rows, cols)));
     B2_CUDA(cudaMemsetAsync(mat.packed, 0, packed_bytes_of(type, rows, cols), m->e->stream));   // row / block padding must be zero
     return B2_OK;
@@ -292,7 +294,8 @@ extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint
     // Q4_0: gaussian weights through ggml's quantiser (bit-identical to b2_randinit_tensor and oracle/randinit.py);
     // Q4_K: synthetic blocks (gemv.cu:k_randinit_q4_k), for benchmarks only
     auto ri = [&](const Mat &mt, uint64_t k, float sig, int64_t rows, int64_t cols, int64_t row0, int64_t stride) {
-        if (mt.type == B2_T_Q4_K) launch_randinit_q4_k(k, rows, cols, mt.packed, row0, stride, st);
+        if (mt.type == B2_T_Q6_K) launch_randinit_q6_k(k, rows, cols, mt.packed, row0, stride, st);
+        else if (mt.type == B2_T_Q4_K) launch_randinit_q4_k(k, rows, cols, mt.packed, row0, stride, st);
         else launch_randinit_q4_0(k, sig, rows, cols, mt.packed, row0, stride, st);
     };
     ri(m->embd, key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, 0, 1);
@@ -345,12 +348,13 @@ struct Staging {
 static int upload_mat(b2_model *m, Staging &sg, const b2_tensor_desc &t, Mat &dst, int64_t dst_row0, int64_t stride, int64_t src_row0, int64_t nrows) {
     B2_CHECK(t.type == dst.type, B2_EINVAL, "tensor %s: type %d, but the matrix it belongs to is type %d (all parts of a fused matrix share one format)", t.name, t.type, dst.type);
     B2_CHECK(t.cols == dst.cols, B2_EINVAL, "tensor %s: cols %lld, expected %lld", t.name, (long long)t.cols, (long long)dst.cols);
-    uint64_t row_bytes = t.type == B2_T_Q4_K ? (uint64_t)(t.cols / 256) * 144 : (uint64_t)(t.cols / QK) * 18;
+    uint64_t row_bytes = t.type == B2_T_Q6_K ? (uint64_t)(t.cols / 256) * 210 : t.type == B2_T_Q4_K ? (uint64_t)(t.cols / 256) * 144 : (uint64_t)(t.cols / QK) * 18;
     B2_CHECK(t.nbytes == (uint64_t)t.rows * row_bytes, B2_EINVAL, "tensor %s: %llu bytes, expected %llu", t.name, (unsigned long long)t.nbytes, (unsigned long long)(t.rows * row_bytes));
     B2_CHECK(src_row0 + nrows <= t.rows, B2_EINVAL, "tensor %s: has %lld rows, need %lld", t.name, (long long)t.rows, (long long)(src_row0 + nrows));
     B2_TRY(sg.ensure(nrows * row_bytes));
     B2_CUDA(cudaMemcpyAsync(sg.buf, (const char *)t.data + src_row0 * row_bytes, nrows * row_bytes, cudaMemcpyHostToDevice, m->e->stream));
-    if (t.type == B2_T_Q4_K) launch_pack_q4_k(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
+    if (t.type == B2_T_Q6_K) launch_pack_q6_k(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
+    else if (t.type == B2_T_Q4_K) launch_pack_q4_k(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
     else launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
     B2_CUDA(cudaStreamSynchronize(m->e->stream));
     return B2_OK;
@@ -480,7 +484,7 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
     int n = 0;
     auto bytes_of = [](const Mat &mt) { return packed_bytes_of(mt.type, mt.rows, mt.cols); };
     float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
-    launch_embed_row(m->embd.type == B2_T_Q4_K, m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, s->xsq, st); n++;
+    launch_embed_row(qt_of(m->embd.type), m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, s->xsq, st); n++;
     int xsq_n = 1;   // how many partial sums of squares the producer of the current x left in s->xsq
     uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
@@ -488,7 +492,7 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
         int g = 0;
         // each GEMV hints the matrix the next GEMV will stream (L2 prefetch of the head of every CTA's share)
         const Mat *after_down = (l + 1 < c.n_layers) ? &m->layers[l + 1].qkv : (with_head ? &m->head : nullptr);
-        launch_gemv_qt(ly.qkv.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+        launch_gemv_qt(qt_of(ly.qkv.type), GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), s->xsq, xsq_n, nullptr, st, pdl); n++;
         if (s->fused_attn) {
             launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
@@ -501,16 +505,16 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
             launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
         }
         // two partial-sum buffers alternate: a kernel reads the partials of its input while writing those of its output
-        launch_gemv_qt(ly.o.type == B2_T_Q4_K, GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
+        launch_gemv_qt(qt_of(ly.o.type), GEMV_IN_ACT, GEMV_OUT_RES, ly.o.packed, H, qd, nullptr, nullptr, 0.f, 0, s->act_attn, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, &g, ly.gateup.packed, bytes_of(ly.gateup), nullptr, 0, s->xsq + 512, st, pdl); n++;
-        launch_gemv_qt(ly.gateup.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+        launch_gemv_qt(qt_of(ly.gateup.type), GEMV_IN_NORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->x, ly.ffn_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->h, nullptr, nullptr, c.act, nullptr, nullptr, nullptr, ly.down.packed, bytes_of(ly.down), s->xsq + 512, g, nullptr, st, pdl); n++;
-        launch_gemv_qt(ly.down.type == B2_T_Q4_K, GEMV_IN_F32, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->h, s->x, s->x, nullptr, 0,
+        launch_gemv_qt(qt_of(ly.down.type), GEMV_IN_F32, GEMV_OUT_RES, ly.down.packed, H, I, nullptr, nullptr, 0.f, 0, s->h, s->x, s->x, nullptr, 0,
                     nullptr, nullptr, &g, after_down ? after_down->packed : nullptr, after_down ? bytes_of(*after_down) : 0, nullptr, 0, s->xsq, st, pdl); n++;
         xsq_n = g;
     }
     if (with_head) {
-        launch_gemv_qt(m->head.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
+        launch_gemv_qt(qt_of(m->head.type), GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
                     s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &s->head_grid, m->layers[0].qkv.packed, bytes_of(m->layers[0].qkv),
                     s->xsq, xsq_n, nullptr, st, pdl); n++;
     }
@@ -831,7 +835,7 @@ static int prefill_batched(b2_session *s, int n) {
     int launches = 0;
     for (int m0 = 0; m0 < n; m0 += 64) {
         const int mb = n - m0 < 64 ? n - m0 : 64, T = pf_batch(mb), pos0 = s->host_pos + m0;
-        launch_prefill_embed(m->embd.type == B2_T_Q4_K, m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
+        launch_prefill_embed(qt_of(m->embd.type), m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
         for (int l = 0; l < c.n_layers; ++l) {
             LayerW &ly = m->layers[l];
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.attn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
@@ -851,7 +855,7 @@ static int prefill_batched(b2_session *s, int n) {
             launch_sumsq(s->x, H, s->xsq, st);
             launch_fill_partials(s->pmax, s->pidx, 1024, st);
             int grid = 0;
-            B2_CUDA(launch_gemv_qt(m->head.type == B2_T_Q4_K, GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
+            B2_CUDA(launch_gemv_qt(qt_of(m->head.type), GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
                                 s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &grid, nullptr, 0, s->xsq, 1, nullptr, st, false));
             if (!s->use_mega) s->head_grid = grid;
             launches += 3;
@@ -873,7 +877,7 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (s->use_pf_gemm && n >= 3) {
+    if (s->use_pf_gemm && s->m->layers_q4 && n >= 3) {
         B2_TRY(prefill_batched(s, n));
     } else if (s->use_mega) {
         B2_TRY(run_mega(s, MEGA_PROMPT, n, n - 1, nullptr));

@@ -71,6 +71,41 @@ void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_pac
     int64_t nb = cols / QK, n = rows * nb;
     k_pack_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
 }
+// GGML Q6_K row-major super-blocks (210 B: ql[128] | qh[64] | int8 scales[16] | f16 d) -> streaming layout (layout.cuh).
+// One thread per 32-element block jb of a super-block: jb = 4n + k covers elements l = 0..31 of ggml's group (n, k):
+// low nibble from ql[64n + 32(k&1) + l] (low half for k < 2, high half otherwise), high bits from (qh[32n + l] >> 2k) & 3.
+__global__ void k_pack_q6_k(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
+                            int64_t dst_row0, int64_t dst_row_stride) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * nb) return;
+    const int64_t r = i / nb, b = i - r * nb;
+    const int jb = (int)(b & 7), n = jb >> 2, k = jb & 3;
+    const uint8_t *p = src + (r * (nb >> 3) + (b >> 3)) * 210;
+    const uint8_t *ql = p + 64 * n + 32 * (k & 1), *qh = p + 128 + 32 * n;
+    const int lsh = (k >> 1) * 4, hsh = 2 * k;
+    PackedLoc6 loc = packed_loc_6(dst_row0 + r * dst_row_stride, b, nbp);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        uint32_t w = 0, hb = 0;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const int e = 4 * t + kk;
+            const uint32_t lo = (ql[e] >> lsh) & 0xF, lo2 = (ql[e + 16] >> lsh) & 0xF;
+            w |= (lo | (lo2 << 4)) << (8 * kk);
+            hb |= (((uint32_t)qh[e] >> hsh) & 3u) << (2 * kk);
+            hb |= (((uint32_t)qh[e + 16] >> hsh) & 3u) << (8 + 2 * kk);
+        }
+        *(uint32_t *)(dst + loc.word0 + t * 16) = w ^ 0x88888888u;
+        *(uint16_t *)(dst + loc.hi + t * 16) = (uint16_t)hb;
+    }
+    dst[loc.sc] = p[192 + 2 * jb];
+    dst[loc.sc + 1] = p[192 + 2 * jb + 1];
+    *(uint16_t *)(dst + loc.d) = (uint16_t)p[208] | ((uint16_t)p[209] << 8);
+}
+void launch_pack_q6_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+    int64_t nb = cols / QK, n = rows * nb;
+    k_pack_q6_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+}
 // Deterministic random init straight into the streaming layout; same bytes as b2_randinit_tensor + pack.
 __global__ void k_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
                                 int64_t dst_row0, int64_t dst_row_stride) {
@@ -116,6 +151,30 @@ __global__ void k_randinit_q4_k(uint64_t key, int64_t rows, int64_t nb, int64_t 
 void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
     int64_t nb = cols / QK, n = rows * nb;
     k_randinit_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+}
+// Synthetic Q6_K blocks (benchmarks with a Q6_K LM head, as in llama.cpp's "Q4_0" files): random 6-bit values, int8 scales in
+// [32, 127], d ~ 1.35e-5 so that d*sc*(q-32) has standard deviation ~0.02.
+__global__ void k_randinit_q6_k(uint64_t key, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst, int64_t dst_row0, int64_t dst_row_stride) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * nb) return;
+    const int64_t r = i / nb, b = i - r * nb;
+    const uint64_t hs = ri_splitmix64(key ^ (0x5bd1e995ull * (uint64_t)(r * (nb >> 3) + (b >> 3) + 1)));   // per super-block
+    const uint64_t h0 = ri_splitmix64(key + 3 * (uint64_t)i), h1 = ri_splitmix64(key + 3 * (uint64_t)i + 1), h2 = ri_splitmix64(key + 3 * (uint64_t)i + 2);
+    const float d = 1.35e-5f * (0.75f + 0.5f * (float)(hs & 0xFFFF) * (1.0f / 65536.0f));
+    PackedLoc6 loc = packed_loc_6(dst_row0 + r * dst_row_stride, b, nbp);
+    *(uint32_t *)(dst + loc.word0) = (uint32_t)h0;
+    *(uint32_t *)(dst + loc.word0 + 16) = (uint32_t)(h0 >> 32);
+    *(uint32_t *)(dst + loc.word0 + 32) = (uint32_t)h1;
+    *(uint32_t *)(dst + loc.word0 + 48) = (uint32_t)(h1 >> 32);
+#pragma unroll
+    for (int t = 0; t < 4; ++t) *(uint16_t *)(dst + loc.hi + t * 16) = (uint16_t)(h2 >> (16 * t));
+    dst[loc.sc] = (uint8_t)(32u + (uint32_t)((hs >> 16) & 63u) + (uint32_t)((hs >> (22 + 4 * (b & 7))) & 31u));
+    dst[loc.sc + 1] = (uint8_t)(32u + (uint32_t)((hs >> 19) & 63u) + (uint32_t)((hs >> (24 + 4 * (b & 7))) & 31u));
+    *(__half *)(dst + loc.d) = __float2half_rn(d);
+}
+void launch_randinit_q6_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+    int64_t nb = cols / QK, n = rows * nb;
+    k_randinit_q6_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
 }
 __global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *__restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -179,6 +238,7 @@ static cudaError_t launch_qt(const GemvArgs &a, int grid, size_t smem, cudaStrea
 }
 template <int IN, int OUT>
 static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
+    if (a.qt == 2) return launch_qt<IN, OUT, 2>(a, grid, smem, st, pdl);
     return a.qt ? launch_qt<IN, OUT, 1>(a, grid, smem, st, pdl) : launch_qt<IN, OUT, 0>(a, grid, smem, st, pdl);
 }
 
@@ -213,7 +273,7 @@ cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64
     // a flush costs two CTA barriers and stalls all sixteen streams: park as many tiles as there are warps to finalise them
     // (LM head 62.5 -> 60.3 us, +1.7 % tokens/s against 8); with chunks outermost a CTA has at most GEMV_MAXT tiles
     a.rb = a.k_outer ? GEMV_MAXT : GEMV_RB_MAX;
-    const size_t smem = GEMV_FIXED_SMEM(a.rb) + (size_t)a.nbp * (qt ? 104 : 100) + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
+    const size_t smem = GEMV_FIXED_SMEM(a.rb) + (size_t)a.nbp * (100 + 4 * qt) + (in_mode == IN_ACT ? 0 : (size_t)cols * 4 + 1024) + 128;
     if (smem > 227 * 1024) return cudaErrorInvalidValue;
     if (smem_out) *smem_out = smem;
     return cudaSuccess;
@@ -228,7 +288,7 @@ cudaError_t launch_gemv(int in_mode, int out_mode, const void *d_packed, int64_t
     return launch_gemv_qt(0, in_mode, out_mode, d_packed, rows, cols, x, norm_w, eps, plus_one, act_in, y, bias_or_res, act_out, act, pmax, pidx,
                           grid_out, next_w, next_bytes, xsq_in, xsq_n, xsq_out, st, pdl);
 }
-// qt: 0 = Q4_0 matrix, 1 = Q4_K matrix (layout.cuh)
+// qt: 0 = Q4_0 matrix, 1 = Q4_K, 2 = Q6_K (layout.cuh)
 cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
                            float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
                            float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
@@ -258,7 +318,7 @@ cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_pack
     for (int tbeg = 0; tbeg < a.n_tiles; tbeg += per_launch) {
         GemvArgs aa = a;
         const int tn = a.n_tiles - tbeg < per_launch ? a.n_tiles - tbeg : per_launch;
-        aa.w = a.w + (uint64_t)tbeg * a.nbp * (a.qt ? BLOCK_BYTES_K : BLOCK_BYTES);
+        aa.w = a.w + (uint64_t)tbeg * a.nbp * (a.qt == 2 ? BLOCK_BYTES_6 : a.qt ? BLOCK_BYTES_K : BLOCK_BYTES);
         aa.n_tiles = tn;
         aa.rows = (int)(rows - (int64_t)tbeg * TILE_ROWS < (int64_t)tn * TILE_ROWS ? rows - (int64_t)tbeg * TILE_ROWS : (int64_t)tn * TILE_ROWS);
         aa.y = y + (int64_t)tbeg * TILE_ROWS;
@@ -287,7 +347,7 @@ __global__ void __launch_bounds__(1024) k_embed_row(const uint8_t *__restrict__ 
     const int64_t row = __ldcg(token);
     float ss = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        float v = QT ? packed_elem_k(w, row, i, nbp) : packed_elem(w, row, i, nbp);
+        float v = QT == 2 ? packed_elem_6(w, row, i, nbp) : QT ? packed_elem_k(w, row, i, nbp) : packed_elem(w, row, i, nbp);
         if (scale != 1.0f) v = v * scale;
         x[i] = v;
         ss = fmaf(v, v, ss);
@@ -302,7 +362,8 @@ __global__ void __launch_bounds__(1024) k_embed_row(const uint8_t *__restrict__ 
     }
 }
 void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st) {
-    if (qt) k_embed_row<1><<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
+    if (qt == 2) k_embed_row<2><<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
+    else if (qt) k_embed_row<1><<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
     else k_embed_row<0><<<1, 1024, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_token, scale, d_x, d_xsq);
 }
 // sum of squares of an f32 vector into xsq[0] (op-level entry points that run the fused RMSNorm on a caller's vector)

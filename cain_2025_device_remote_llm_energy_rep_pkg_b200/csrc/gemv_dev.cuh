@@ -137,6 +137,19 @@ __device__ __forceinline__ float packed_elem(const uint8_t *w, int64_t row, int6
     int v = (nib ^ 8) - 8;
     return (float)v * __half2float(__ushort_as_half(*(const uint16_t *)(w + loc.scale)));
 }
+// the same for a Q6_K matrix: value = (d * sc) * (q - 32), each product rounded (gguf-py / oracle/quants.py order)
+__device__ __forceinline__ float packed_elem_6(const uint8_t *w, int64_t row, int64_t col, int64_t nbp) {
+    PackedLoc6 loc = packed_loc_6(row, col / QK, nbp);
+    const int e = (int)(col % QK), t = (e & 15) >> 2, kk = e & 3, half = e >> 4;
+    const uint32_t word = *(const uint32_t *)(w + loc.word0 + t * 16);
+    const int lo = (((word >> (8 * kk + 4 * half)) & 0xF) ^ 8);                 // stored as (q & 15) - 8
+    const uint32_t hb = *(const uint16_t *)(w + loc.hi + t * 16);
+    const int hi = (hb >> (8 * half + 2 * kk)) & 3;
+    const int q = (lo | (hi << 4)) - 32;
+    const float d = __half2float(*(const __half *)(w + loc.d));
+    const float dsc = __fmul_rn(d, (float)(int)(int8_t)w[loc.sc + half]);
+    return __fmul_rn(dsc, (float)q);
+}
 // the same for a Q4_K matrix: d1 = d*sc, m1 = dmin*m, value = q*d1 - m1, each op rounded (gguf-py / oracle/quants.py order)
 __device__ __forceinline__ float packed_elem_k(const uint8_t *w, int64_t row, int64_t col, int64_t nbp) {
     PackedLocK loc = packed_loc_k(row, col / QK, nbp);
@@ -173,21 +186,78 @@ __device__ __forceinline__ uint4 ldcg4(const void *p) {         // activations w
 // QT = 0: Q4_0 matrix, QT = 1: Q4_K matrix (layout.cuh).
 // One block-group of weights for this lane: rows g / g+8, 4 blocks, + their scales (Q4_0: half2 (d_g, d_g+8) per block;
 // Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) per block and dm = half2 (d, dmin) of row g, of row g+8).
+// Q6_K: wa/wb low nibbles, wh the 2 high bits of the same elements, sd int8 (sc_lo, sc_hi) x (row g, row g+8) per block,
+// dd = half2 (d of row g, d of row g+8).
 template <int QT> struct WPieceT { uint4 wa, wb, sd; };
 template <> struct WPieceT<1> { uint4 wa, wb, sd; uint2 dm; };
+template <> struct WPieceT<2> { uint4 wa, wb, sd, wh; uint32_t dd; };
 // Activation digits (B fragments of 4 blocks) + block scales (already / 16); Q4_K also needs ts = the sum of the gridded
 // activations of block 4*bg + t (this lane's share of the "- dmin*m" term, which multiplies a block SUM, not a dot product).
 template <int QT> struct BFragT { uint4 b01, b23; float4 as; };
 template <> struct BFragT<1> { uint4 b01, b23; float4 as; float ts; };
-template <int QT> struct WLay { static constexpr int BB = QT ? BLOCK_BYTES_K : BLOCK_BYTES, SC = QT ? 192 : 128; };
+template <> struct BFragT<2> { uint4 b01, b23; float4 as; float2 ts2; };   // Q6_K: sums of the two 16-element halves
+template <int QT> struct WLay {
+    static constexpr int BB = QT == 2 ? BLOCK_BYTES_6 : QT == 1 ? BLOCK_BYTES_K : BLOCK_BYTES;   // bytes per block column of a tile
+    static constexpr int SC = QT == 2 ? 160 : QT == 1 ? 192 : 128;                                  // scale bytes per block-group
+    static constexpr int SC0 = QT == 2 ? 384 : 256;                                                 // scale area offset = cb * SC0
+};
+// four 2-bit fields of a byte -> the low 2 bits of four bytes (multiplications by 0x1001 and 65 are shift-adds without overlap)
+__device__ __forceinline__ uint32_t spread2(uint32_t b) {
+    const uint32_t x = (b * 0x1001u) & 0x000F000Fu;
+    return (x * 65u) & 0x03030303u;
+}
+__device__ __forceinline__ void mma_s8_k16(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
+}
 // small unsigned byte k of `word` as a float without I2F: 0x4B0000bb is 8388608 + bb
 __device__ __forceinline__ float byte_to_float(uint32_t word, int k) {
     return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u | (uint32_t)k)) - 8388608.0f;
 }
 
+// Q6_K: q - 32 = (lo - 8) + 16 u - 24 with lo the low nibble and u = 0..3 the high bits.  Per 16-element half of a block (its
+// own int8 scale) two m16n8k16 MMAs: A = 16 (lo - 8) (the nibble trick) and A = u; then
+// sum (q-32) X = (D_lo + 256 D_u) / 16 - 24 sum X, the last term through the half-block sums of the activations (ts2).
+__device__ __forceinline__ void bg_mma_q6(const WPieceT<2> &r, const BFragT<2> &b, float (&acc)[4], float (&off)[2], int t) {
+    const uint32_t ua[4] = {r.wa.x, r.wa.y, r.wa.z, r.wa.w}, ub[4] = {r.wb.x, r.wb.y, r.wb.z, r.wb.w};
+    const uint32_t bx[4] = {b.b01.x, b.b01.z, b.b23.x, b.b23.z}, by[4] = {b.b01.y, b.b01.w, b.b23.y, b.b23.w};
+    const uint32_t sdw[4] = {r.sd.x, r.sd.y, r.sd.z, r.sd.w};
+    const uint32_t hg[4] = {r.wh.x & 0xFFFFu, r.wh.x >> 16, r.wh.y & 0xFFFFu, r.wh.y >> 16};      // row g, blocks 0..3
+    const uint32_t hg8[4] = {r.wh.z & 0xFFFFu, r.wh.z >> 16, r.wh.w & 0xFFFFu, r.wh.w >> 16};     // row g+8
+    const float asf[4] = {b.as.x, b.as.y, b.as.z, b.as.w};
+    const float2 dd = __half22float2(*(const __half2 *)&r.dd);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t sw = sdw[j] ^ 0x80808080u;   // int8 + 128 as unsigned bytes
+        const float s0g = __fmul_rn(dd.x, byte_to_float(sw, 0) - 128.0f), s1g = __fmul_rn(dd.x, byte_to_float(sw, 1) - 128.0f);
+        const float s0h = __fmul_rn(dd.y, byte_to_float(sw, 2) - 128.0f), s1h = __fmul_rn(dd.y, byte_to_float(sw, 3) - 128.0f);
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+            int cl[4] = {MMA_MAGIC, MMA_MAGIC, MMA_MAGIC, MMA_MAGIC}, ch[4] = {MMA_MAGIC, MMA_MAGIC, MMA_MAGIC, MMA_MAGIC};
+            const uint32_t al0 = hf ? (ua[j] & 0xF0F0F0F0u) : ((ua[j] << 4) & 0xF0F0F0F0u);
+            const uint32_t al1 = hf ? (ub[j] & 0xF0F0F0F0u) : ((ub[j] << 4) & 0xF0F0F0F0u);
+            const uint32_t ah0 = spread2((hg[j] >> (8 * hf)) & 0xFFu), ah1 = spread2((hg8[j] >> (8 * hf)) & 0xFFu);
+            const uint32_t bb = hf ? by[j] : bx[j];
+            mma_s8_k16(cl, al0, al1, bb);
+            mma_s8_k16(ch, ah0, ah1, bb);
+            const float f0 = (hf ? s1g : s0g) * asf[j], f1 = (hf ? s1h : s0h) * asf[j];
+            acc[0] = fmaf(fmaf(256.0f, __int_as_float(ch[0]) - MMA_MAGIC_F, __int_as_float(cl[0]) - MMA_MAGIC_F), f0, acc[0]);
+            acc[1] = fmaf(fmaf(256.0f, __int_as_float(ch[1]) - MMA_MAGIC_F, __int_as_float(cl[1]) - MMA_MAGIC_F), f0, acc[1]);
+            acc[2] = fmaf(fmaf(256.0f, __int_as_float(ch[2]) - MMA_MAGIC_F, __int_as_float(cl[2]) - MMA_MAGIC_F), f1, acc[2]);
+            acc[3] = fmaf(fmaf(256.0f, __int_as_float(ch[3]) - MMA_MAGIC_F, __int_as_float(cl[3]) - MMA_MAGIC_F), f1, acc[3]);
+        }
+        if (j == t) {   // this lane's block of the "- 24 sum X" term
+            off[0] = fmaf(-24.0f, fmaf(s0g, b.ts2.x, s1g * b.ts2.y), off[0]);
+            off[1] = fmaf(-24.0f, fmaf(s0h, b.ts2.x, s1h * b.ts2.y), off[1]);
+        }
+    }
+}
 // off[0..1] (Q4_K): running sums of (8A - B) * block sum for rows g / g+8, this lane's block (j = t) of every block-group
 template <int QT>
 __device__ __forceinline__ void bg_mma(const WPieceT<QT> &r, const BFragT<QT> &b, float (&acc)[4], float (&off)[2], int t) {
+    if constexpr (QT == 2) {
+        bg_mma_q6(r, b, acc, off, t);
+    } else {
     const uint32_t ua[4] = {r.wa.x, r.wa.y, r.wa.z, r.wa.w}, ub[4] = {r.wb.x, r.wb.y, r.wb.z, r.wb.w};
     const uint32_t bx[4] = {b.b01.x, b.b01.z, b.b23.x, b.b23.z}, by[4] = {b.b01.y, b.b01.w, b.b23.y, b.b23.w};
     const uint32_t sdw[4] = {r.sd.x, r.sd.y, r.sd.z, r.sd.w};
@@ -227,6 +297,7 @@ __device__ __forceinline__ void bg_mma(const WPieceT<QT> &r, const BFragT<QT> &b
         off[0] = fmaf(c0, b.ts, off[0]);
         off[1] = fmaf(c1, b.ts, off[1]);
     }
+    }
 }
 // one piece of the stream: block-group column `warp` of the chunk at `ch` (cb blocks)
 __device__ __forceinline__ uint2 ldg_stream2(const void *p) {
@@ -238,8 +309,12 @@ template <int QT>
 __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, int lane, WPieceT<QT> &r) {
     r.wa = ldg_stream4(ch + (size_t)warp * 1024 + lane * 16);
     r.wb = ldg_stream4(ch + (size_t)warp * 1024 + 512 + lane * 16);
-    r.sd = ldg_stream4(ch + (size_t)cb * 256 + warp * WLay<QT>::SC + (lane >> 2) * 16);
+    r.sd = ldg_stream4(ch + (size_t)cb * WLay<QT>::SC0 + warp * WLay<QT>::SC + (lane >> 2) * 16);
     if constexpr (QT == 1) r.dm = ldg_stream2(ch + (size_t)cb * 256 + warp * WLay<QT>::SC + 128 + (lane >> 2) * 8);
+    if constexpr (QT == 2) {
+        r.wh = ldg_stream4(ch + (size_t)cb * 256 + (size_t)warp * 512 + lane * 16);
+        r.dd = __ldg((const uint32_t *)(ch + (size_t)cb * 384 + warp * 160 + 128 + (lane >> 2) * 4));
+    }
 }
 
 // shared memory map (bytes): [header 512: 64 floats of scratch, the input-copy mbarrier at +256][red rb*16*16*4*4 = rb*4096]
@@ -260,23 +335,24 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
 template <int IN, int QT>
 __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPtrs &pv, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
                                                  const float4 (&wn)[2]) {
-    constexpr int A3S = QT ? 104 : 100;
+    constexpr int A3S = 100 + 4 * QT;   // Q4_K: one block sum per block after the scales, Q6_K: two half-block sums
     float *sts = (float *)(sact + (size_t)a.nbp * 100);
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
         mbar_wait(bar, parity);
         prof_stamp(6);
-        if constexpr (QT == 1) {   // block sums from the digits: lane = (t, j, half) reads one word of each plane of its block-group
+        if constexpr (QT != 0) {   // block sums from the digits: lane = (t, j, half) reads one word of each plane of its block-group
             const float *sscale = (const float *)(sact + (size_t)a.nbp * 96);
             for (int ck = 0; ck < cpt; ++ck) {
                 const int kbg = ck * (KC / 4) + warp;
                 if (kbg * 4 >= a.nbp) break;
                 const uint32_t *pl = (const uint32_t *)(sact + (size_t)kbg * 384) + lane;
                 int xs = __dp4a((int)pl[0], 0x01010101, 0) + 128 * __dp4a((int)pl[32], 0x01010101, 0) + 16384 * __dp4a((int)pl[64], 0x01010101, 0);
-                xs += __shfl_xor_sync(0xffffffffu, xs, 1);
+                if (QT == 1) xs += __shfl_xor_sync(0xffffffffu, xs, 1);   // Q6_K keeps the two 16-element halves apart
                 xs += __shfl_xor_sync(0xffffffffu, xs, 8);
                 xs += __shfl_xor_sync(0xffffffffu, xs, 16);
                 const int j = (lane >> 1) & 3;
-                if ((lane & 0x19) == 0) sts[kbg * 4 + j] = (float)xs * sscale[kbg * 4 + j];
+                if (QT == 1) { if ((lane & 0x19) == 0) sts[kbg * 4 + j] = (float)xs * sscale[kbg * 4 + j]; }
+                else if ((lane & 0x18) == 0) sts[(kbg * 4 + j) * 2 + (lane & 1)] = (float)xs * sscale[kbg * 4 + j];
             }
             __syncwarp();
         }
@@ -336,11 +412,15 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
         *(uint32_t *)(dst + 128) = w1;
         *(uint32_t *)(dst + 256) = w2;
         if (k == 0) sscale[b] = (q < n4) ? sc : 0.f;
-        if constexpr (QT == 1) {
+        if constexpr (QT != 0) {
             xsum += __shfl_xor_sync(0xffffffffu, xsum, 1);
             xsum += __shfl_xor_sync(0xffffffffu, xsum, 2);
-            xsum += __shfl_xor_sync(0xffffffffu, xsum, 4);
-            if (k == 0) sts[b] = (q < n4) ? (float)xsum * sc : 0.f;
+            if (QT == 1) {
+                xsum += __shfl_xor_sync(0xffffffffu, xsum, 4);
+                if (k == 0) sts[b] = (q < n4) ? (float)xsum * sc : 0.f;
+            } else if ((k & 3) == 0) {   // lanes k = 0..3 hold elements 0..15, k = 4..7 elements 16..31
+                sts[2 * b + (k >> 2)] = (q < n4) ? (float)xsum * sc : 0.f;
+            }
         }
     }
     __syncwarp();
@@ -367,13 +447,13 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
             v0 += p4.x;
             v1 += p4.y;
             v2 += p4.z;
-            if (QT == 1) v3 += p4.w;   // Q4_K: the "(8A - B) * block sum" term
+            if (QT != 0) v3 += p4.w;   // Q4_K / Q6_K: the term that multiplies block sums of the activations
         }
         v0 += __shfl_xor_sync(0xffffffffu, v0, 16);
         v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
         v2 += __shfl_xor_sync(0xffffffffu, v2, 16);
         float yv = fmaf(16384.0f, v2, fmaf(128.0f, v1, v0));
-        if (QT == 1) yv += v3 + __shfl_xor_sync(0xffffffffu, v3, 16);
+        if (QT != 0) yv += v3 + __shfl_xor_sync(0xffffffffu, v3, 16);
         const int row = tile * TILE_ROWS + r;
         if (OUT == OUT_BIAS) {
             if (lane < 16 && row < a.rows) a.y[row] = bias_or_res ? yv + bias_or_res[row] : yv;
@@ -457,6 +537,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
             b.as.x *= 0.0625f; b.as.y *= 0.0625f; b.as.z *= 0.0625f; b.as.w *= 0.0625f;   // the 1/16 of the nibble trick
         }
         if constexpr (QT == 1) b.ts = (kbg * 4 < a.nbp) ? *(const float *)(sact + (size_t)a.nbp * 100 + (kbg * 4 + t) * 4) : 0.f;
+        if constexpr (QT == 2) b.ts2 = (kbg * 4 < a.nbp) ? *(const float2 *)(sact + (size_t)a.nbp * 100 + (kbg * 4 + t) * 8) : make_float2(0.f, 0.f);
     };
     // pull this CTA's share of the next kernel's weights into L2 (lane 0 of every warp, 16 KB per instruction)
     auto prefetch_next = [&]() {
@@ -503,7 +584,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
                 mbar_expect_tx(bar, bytes);
                 rot_copy(sact, a.act_in, bytes);
             } else {
-                float *sx = (float *)(sact + (size_t)a.nbp * (QT ? 104 : 100));
+                float *sx = (float *)(sact + (size_t)a.nbp * (100 + 4 * QT));
                 const uint32_t bytes = (uint32_t)a.n_in * 4;
                 const uint32_t qbytes = IN == IN_NORM ? (uint32_t)((a.xsq_n + 3) & ~3) * 4 : 0;
                 mbar_expect_tx(bar, bytes + qbytes);
@@ -546,7 +627,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     int batch_first = t0, batch_n = 0;
     auto park = [&](float (&acc)[4], float (&off)[2]) {   // park the finished tile's partial; reduce when a.rb tiles are waiting
         float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
-        if constexpr (QT == 1) {   // the four t lanes covered one block each: their sum rides in the unused fourth column (plane "3")
+        if constexpr (QT != 0) {   // the four t lanes covered one block each: their sum rides in the unused fourth column (plane "3")
             float o0 = off[0], o1 = off[1];
             o0 += __shfl_xor_sync(0xffffffffu, o0, 1); o0 += __shfl_xor_sync(0xffffffffu, o0, 2);
             o1 += __shfl_xor_sync(0xffffffffu, o1, 1); o1 += __shfl_xor_sync(0xffffffffu, o1, 2);
@@ -571,6 +652,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     WPieceT<QT> buf0, buf1, buf2, buf3;
     buf0.wa = buf0.wb = buf0.sd = z4; buf1 = buf0; buf2 = buf0; buf3 = buf0;
     if constexpr (QT == 1) { buf0.dm = make_uint2(0u, 0u); buf1.dm = buf0.dm; buf2.dm = buf0.dm; buf3.dm = buf0.dm; }
+    if constexpr (QT == 2) { buf0.wh = z4; buf0.dd = 0u; buf1 = buf0; buf2 = buf0; buf3 = buf0; }
     float off[2] = {0.f, 0.f}, off1[2] = {0.f, 0.f};   // Q4_K: the "- dmin*m" sums of the tile(s) in flight
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     if (PATH == -1 ? !a.k_outer : PATH != 2) {

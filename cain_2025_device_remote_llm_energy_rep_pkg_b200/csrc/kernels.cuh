@@ -18,10 +18,14 @@ struct DevState {
 // weight re-pack / init into the streaming layout (layout.cuh)
 void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
+void launch_pack_q6_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
+void launch_randinit_q6_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
 void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st);
 
+// matrix format index of the kernels: 0 = Q4_0, 1 = Q4_K, 2 = Q6_K
+static inline int qt_of(int type) { return type == B2_T_Q6_K ? 2 : type == B2_T_Q4_K ? 1 : 0; }
 // streaming GEMV (gemv.cu)
 enum { GEMV_IN_NORM = 0, GEMV_IN_ACT = 1, GEMV_IN_F32 = 2 };
 enum { GEMV_OUT_BIAS = 0, GEMV_OUT_RES = 1, GEMV_OUT_ACTMUL = 2, GEMV_OUT_LOGITS = 3 };

@@ -81,6 +81,40 @@ __host__ __device__ inline PackedLocK packed_loc_k(int64_t row, int64_t blk, int
     return p;
 }
 
+// ---- Q6_K matrices (GGML super-blocks of 256: 4 low bits + 2 high bits per weight, sixteen int8 scales for 16-element
+// sub-blocks, f16 d; w = d*sc*(q-32)).  llama.cpp keeps output.weight (and a tied token_embd.weight) in this format even in
+// "Q4_0" files.  Same tiles and chunks; per chunk of cb blocks:
+//     low nibbles  cb*256 B : as Q4_0, nibble = (q & 15) - 8 in two's complement
+//     high bits    cb*128 B : block-group j at j*512: [lane = g*4+t] uint4 = {row g blocks 4j,4j+1 | row g blocks 4j+2,4j+3 |
+//                             row g+8 blocks 4j,4j+1 | row g+8 blocks 4j+2,4j+3}; 16 bits per (row, block): 2 bits per element
+//                             4t..4t+3 (low byte) and 16+4t..16+4t+3 (high byte) -- exactly the elements of this lane's A fragments
+//     scales       per block-group 160 B: [g] 16 B: word j = int8 (sc_lo, sc_hi of row g, sc_lo, sc_hi of row g+8) of block 4*bg+j
+//                             (sc_lo: elements 0..15, sc_hi: 16..31), then [g] 4 B: half2 (d of row g, d of row g+8)
+// 424 bytes per 32-wide block column of a tile = 6.625 bit per weight (GGML: 6.5625).
+#define BLOCK_BYTES_6 424
+__host__ __device__ inline uint64_t packed_q6_k_bytes(int64_t rows, int64_t cols) {
+    return (uint64_t)ntiles(rows) * nblocks_padded(cols) * BLOCK_BYTES_6;
+}
+struct PackedLoc6 {
+    uint64_t word0;   // low-nibble word t = 0 (word t at +16*t), as PackedLoc
+    uint64_t hi;      // byte offset of the 16-bit high-bit field of lane t = 0 for this (row, block); lane t at +16*t
+    uint64_t sc;      // byte offset of sc_lo (sc_hi at +1)
+    uint64_t d;       // byte offset of the half d
+};
+__host__ __device__ inline PackedLoc6 packed_loc_6(int64_t row, int64_t blk, int64_t nbp) {
+    int64_t T = row / TILE_ROWS, r = row % TILE_ROWS, hf = r >> 3, g = r & 7;
+    int64_t ck = blk / KC, bl = blk % KC;
+    int64_t cb = (nbp - ck * KC) < KC ? (nbp - ck * KC) : KC;
+    uint64_t chunk = (uint64_t)T * nbp * BLOCK_BYTES_6 + (uint64_t)ck * KC * BLOCK_BYTES_6;
+    uint64_t sa = chunk + (uint64_t)cb * 384 + (uint64_t)(bl >> 2) * 160;
+    PackedLoc6 p;
+    p.word0 = chunk + (uint64_t)(bl >> 2) * 1024 + (uint64_t)(hf * 8 + g) * 64 + (uint64_t)(bl & 3) * 4;
+    p.hi = chunk + (uint64_t)cb * 256 + (uint64_t)(bl >> 2) * 512 + (uint64_t)g * 64 + (uint64_t)hf * 8 + (uint64_t)(bl & 3) * 2;
+    p.sc = sa + (uint64_t)g * 16 + (uint64_t)(bl & 3) * 4 + (uint64_t)hf * 2;
+    p.d = sa + 128 + (uint64_t)g * 4 + (uint64_t)hf * 2;
+    return p;
+}
+
 #ifdef __CUDACC__
 // store one activation block (warp-cooperative, lane = element) into an A3 vector of n elements
 __device__ __forceinline__ void a3_store_block(void *act, int64_t n, int64_t blk, int lane, int X, float scale) {

@@ -8,6 +8,7 @@
 
 extern "C" uint64_t b2_packed_bytes(int type, int64_t rows, int64_t cols) {
     if (type == B2_T_Q4_K && cols % 256 == 0) return packed_q4_k_bytes(rows, cols);
+    if (type == B2_T_Q6_K && cols % 256 == 0) return packed_q6_k_bytes(rows, cols);
     if (type != B2_T_Q4_0 || cols % QK) return 0;
     return packed_q4_0_bytes(rows, cols);
 }
@@ -15,18 +16,19 @@ extern "C" uint64_t b2_act_bytes(int64_t n) { return a3_bytes(n); }
 
 extern "C" int b2_op_pack_weights(int type, int64_t rows, int64_t cols, const void *src, const void *src2, void *d_packed) {
     ApiScope _scope("b2_op_pack_weights");
-    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "b2_op_pack_weights: type %d not supported", type);
-    const bool kq = type == B2_T_Q4_K;
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K || type == B2_T_Q6_K, B2_EINVAL, "b2_op_pack_weights: type %d not supported", type);
+    const bool kq = type != B2_T_Q4_0;
     B2_CHECK(src && d_packed && rows > 0 && cols > 0 && cols % (kq ? 256 : QK) == 0, B2_EINVAL, "b2_op_pack_weights: bad arguments");
-    uint64_t bytes = kq ? (uint64_t)rows * (cols / 256) * 144 : (uint64_t)rows * (cols / QK) * 18;
+    uint64_t bytes = type == B2_T_Q6_K ? (uint64_t)rows * (cols / 256) * 210 : kq ? (uint64_t)rows * (cols / 256) * 144 : (uint64_t)rows * (cols / QK) * 18;
     auto pack = [&](void *stg, int64_t row0, int64_t stride) {
-        if (kq) launch_pack_q4_k(stg, rows, cols, d_packed, row0, stride, 0);
+        if (type == B2_T_Q6_K) launch_pack_q6_k(stg, rows, cols, d_packed, row0, stride, 0);
+        else if (kq) launch_pack_q4_k(stg, rows, cols, d_packed, row0, stride, 0);
         else launch_pack_q4_0(stg, rows, cols, d_packed, row0, stride, 0);
     };
     int64_t total = src2 ? 2 * rows : rows, stride = src2 ? 2 : 1;
     void *stg = nullptr;
     B2_CUDA(cudaMalloc(&stg, bytes));
-    cudaError_t e = cudaMemset(d_packed, 0, kq ? packed_q4_k_bytes(total, cols) : packed_q4_0_bytes(total, cols));
+    cudaError_t e = cudaMemset(d_packed, 0, b2_packed_bytes(type, total, cols));
     if (e == cudaSuccess) e = cudaMemcpy(stg, src, bytes, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         pack(stg, 0, stride);
@@ -64,8 +66,8 @@ extern "C" int b2_op_rmsnorm_quant(const float *d_x, const float *d_w, int64_t n
 extern "C" int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const void *d_act, const float *d_bias_or_res,
                           int mode, int act, float *d_y) {
     ApiScope _scope("b2_op_gemv");
-    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "b2_op_gemv: type %d not supported", type);
-    const int qt = type == B2_T_Q4_K;
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K || type == B2_T_Q6_K, B2_EINVAL, "b2_op_gemv: type %d not supported", type);
+    const int qt = qt_of(type);
     B2_CHECK(d_packed && d_act && d_y && rows >= 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_gemv: bad arguments");
     B2_CHECK(mode >= 0 && mode <= 2, B2_EINVAL, "b2_op_gemv: mode %d", mode);
     B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_gemv: mode 1 needs the residual vector");
@@ -82,8 +84,8 @@ extern "C" int b2_op_gemv(int type, const void *d_packed, int64_t rows, int64_t 
 extern "C" int b2_op_gemv_f32(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_bias_or_res,
                               int mode, float *d_y) {
     ApiScope _scope("b2_op_gemv_f32");
-    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "b2_op_gemv_f32: type %d not supported", type);
-    const int qt = type == B2_T_Q4_K;
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K || type == B2_T_Q6_K, B2_EINVAL, "b2_op_gemv_f32: type %d not supported", type);
+    const int qt = qt_of(type);
     B2_CHECK(d_packed && d_x && d_y && rows > 0 && cols > 0 && cols % QK == 0, B2_EINVAL, "b2_op_gemv_f32: bad arguments");
     B2_CHECK(mode == 0 || (mode == 1 && d_bias_or_res), B2_EINVAL, "b2_op_gemv_f32: mode must be 0, or 1 with a residual vector");
     cudaError_t e = launch_gemv_qt(qt, GEMV_IN_F32, mode, d_packed, rows, cols, nullptr, nullptr, 0.f, 0, d_x, d_y, d_bias_or_res, nullptr, 0,
@@ -99,8 +101,8 @@ extern "C" int b2_op_gemv_f32(int type, const void *d_packed, int64_t rows, int6
 extern "C" int b2_op_norm_gemv(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, const float *d_norm_w, float eps,
                                int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y, void *d_act_out, int32_t *d_argmax) {
     ApiScope _scope("b2_op_norm_gemv");
-    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "b2_op_norm_gemv: type %d not supported", type);
-    const int qt = type == B2_T_Q4_K;
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K || type == B2_T_Q6_K, B2_EINVAL, "b2_op_norm_gemv: type %d not supported", type);
+    const int qt = qt_of(type);
     B2_CHECK(d_packed && d_x && d_norm_w && rows > 0 && cols > 0 && cols % QK == 0 && cols <= 8192, B2_EINVAL, "b2_op_norm_gemv: bad arguments (cols must be a multiple of 32, at most 8192)");
     B2_CHECK(mode >= 0 && mode <= 3, B2_EINVAL, "b2_op_norm_gemv: mode %d", mode);
     B2_CHECK(d_y, B2_EINVAL, "b2_op_norm_gemv: d_y is NULL");

@@ -473,13 +473,14 @@ __global__ void __launch_bounds__(256) k_prefill_embed(const uint8_t *__restrict
     const int m = blockIdx.x;
     const int64_t row = tokens[m];
     for (int i = threadIdx.x; i < n; i += 256) {
-        float v = QT ? packed_elem_k(w, row, i, nbp) : packed_elem(w, row, i, nbp);
+        float v = QT == 2 ? packed_elem_6(w, row, i, nbp) : QT ? packed_elem_k(w, row, i, nbp) : packed_elem(w, row, i, nbp);
         if (scale != 1.0f) v = v * scale;
         x[(int64_t)m * n + i] = v;
     }
 }
 void launch_prefill_embed(int qt, const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st) {
-    if (qt) k_prefill_embed<1><<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
+    if (qt == 2) k_prefill_embed<2><<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
+    else if (qt) k_prefill_embed<1><<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
     else k_prefill_embed<0><<<M, 256, 0, st>>>((const uint8_t *)d_packed, nblocks_padded(cols), (int)cols, d_tokens, scale, d_x);
 }
 
