@@ -31,7 +31,8 @@ extern "C" {
 #define B2_ENVML        -5   /* NVML unavailable or failed */
 #define B2_ENCCL        -6
 
-/* GGML tensor types understood by the engine (same numeric values as ggml/gguf). */
+/* GGML tensor types understood by the engine (same numeric values as ggml/gguf).  Matrices: Q4_0 and Q4_K for the layers
+ * (the parts of a fused QKV / gate-up matrix share one type), Q4_0 / Q4_K / Q6_K for token_embd / output; vectors: F32. */
 #define B2_T_F32   0
 #define B2_T_Q4_0  2
 #define B2_T_Q8_0  8
@@ -103,7 +104,8 @@ int b2_engine_device(const b2_engine *e, int *device_ordinal);
  * Uploads the tensors once and re-packs them into the engine's HBM layout. */
 int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_tensor_desc *tensors, int n_tensors, b2_model **out);
 /* Same model, but the deterministic random-init weights (oracle/randinit.py recipe) are generated and
- * quantised on the device; byte-identical to b2_randinit_tensor + b2_model_create.  qtype/head_qtype: B2_T_*. */
+ * quantised on the device; byte-identical to b2_randinit_tensor + b2_model_create for Q4_0.  qtype/head_qtype: B2_T_*;
+ * Q4_K / Q6_K get synthetic blocks with the same weight statistics (benchmarks only, no host counterpart). */
 int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint64_t seed, int qtype, int head_qtype, b2_model **out);
 int b2_model_destroy(b2_model *m);
 /* Bytes of matmul weights one decoded token reads (the roofline's algorithmic bytes). */
