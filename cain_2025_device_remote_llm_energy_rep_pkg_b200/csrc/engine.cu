@@ -55,6 +55,20 @@ struct Mat {
 struct LayerW {
     float *attn_norm = nullptr, *ffn_norm = nullptr, *qkv_bias = nullptr;
     Mat qkv, o, gateup, down;
+    // attn_q / attn_k / attn_v in different formats (llama.cpp's Q4_K_M keeps attn_v in Q6_K): three matrices, three GEMVs
+    bool split_qkv = false;
+    Mat qkv_part[3];
+};
+struct LayerTypes { int q, k, v, o, gateup, down; };
+struct ModelTypes {
+    int embd, head;
+    std::vector<LayerTypes> layers;
+    static ModelTypes uniform(int n_layers, int qtype, int head_qtype) {
+        ModelTypes t;
+        t.embd = t.head = head_qtype;
+        t.layers.assign(n_layers, LayerTypes{qtype, qtype, qtype, qtype, qtype, qtype});
+        return t;
+    }
 };
 struct b2_model {
     b2_engine *e = nullptr;
@@ -223,9 +237,11 @@ static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type
     return B2_OK;
 }
 // GGML bytes of the matrix (what a token has to read): Q4_0 18 B / 32 weights, Q4_K 144 B / 256 weights -- both 4.5 bit
-static inline uint64_t algo_bytes(const Mat &m) { return (uint64_t)m.rows * (m.cols / QK) * 18; }
+static inline uint64_t algo_bytes(const Mat &m) {
+    return m.type == B2_T_Q6_K ? (uint64_t)m.rows * (m.cols / 256) * 210 : (uint64_t)m.rows * (m.cols / QK) * 18;
+}
 
-static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype, int head_qtype, b2_model **out) {
+static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, const ModelTypes &mt, b2_model **out) {
     B2_CHECK(e && out, B2_EINVAL, "NULL engine/out");
     B2_TRY(check_cfg(cfg));
     B2_CUDA(cudaSetDevice(e->device));
@@ -236,19 +252,29 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype,
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
     int rc = B2_OK;
     do {
-        if ((rc = alloc_mat(m, m->embd, c.vocab, H, head_qtype))) break;
+        if ((rc = alloc_mat(m, m->embd, c.vocab, H, mt.embd))) break;
         if (c.tied) m->head = m->embd;
-        else if ((rc = alloc_mat(m, m->head, c.vocab, H, head_qtype))) break;
+        else if ((rc = alloc_mat(m, m->head, c.vocab, H, mt.head))) break;
         if ((rc = dev_alloc(m->allocs, (void **)&m->out_norm, H * 4))) break;
         m->layers.resize(c.n_layers);
-        for (auto &ly : m->layers) {
+        for (size_t li = 0; li < m->layers.size(); ++li) {
+            LayerW &ly = m->layers[li];
+            const LayerTypes &lt = mt.layers[li];
             if ((rc = dev_alloc(m->allocs, (void **)&ly.attn_norm, H * 4))) break;
             if ((rc = dev_alloc(m->allocs, (void **)&ly.ffn_norm, H * 4))) break;
             if (c.qkv_bias && (rc = dev_alloc(m->allocs, (void **)&ly.qkv_bias, (qd + 2 * kvd) * 4))) break;
-            if ((rc = alloc_mat(m, ly.qkv, qd + 2 * kvd, H, qtype))) break;
-            if ((rc = alloc_mat(m, ly.o, H, qd, qtype))) break;
-            if ((rc = alloc_mat(m, ly.gateup, 2 * (int64_t)I, H, qtype))) break;
-            if ((rc = alloc_mat(m, ly.down, H, I, qtype))) break;
+            if (lt.q == lt.k && lt.k == lt.v) {
+                if ((rc = alloc_mat(m, ly.qkv, qd + 2 * kvd, H, lt.q))) break;
+            } else {
+                ly.split_qkv = true;
+                m->all_q4_0 = m->layers_q4 = false;   // the tcgen05 prompt GEMM and the persistent kernel take the fused matrix
+                if ((rc = alloc_mat(m, ly.qkv_part[0], qd, H, lt.q))) break;
+                if ((rc = alloc_mat(m, ly.qkv_part[1], kvd, H, lt.k))) break;
+                if ((rc = alloc_mat(m, ly.qkv_part[2], kvd, H, lt.v))) break;
+            }
+            if ((rc = alloc_mat(m, ly.o, H, qd, lt.o))) break;
+            if ((rc = alloc_mat(m, ly.gateup, 2 * (int64_t)I, H, lt.gateup))) break;
+            if ((rc = alloc_mat(m, ly.down, H, I, lt.down))) break;
         }
         if (rc) break;
         if ((rc = build_rope(m))) break;
@@ -256,7 +282,9 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, int qtype,
     if (rc) { b2_model_destroy(m); return rc; }
     // algorithmic bytes per decoded token: every matmul weight once (4.5 bit/weight), LM head included
     uint64_t w = 0;
-    for (auto &ly : m->layers) w += algo_bytes(ly.qkv) + algo_bytes(ly.o) + algo_bytes(ly.gateup) + algo_bytes(ly.down);
+    for (auto &ly : m->layers)
+        w += (ly.split_qkv ? algo_bytes(ly.qkv_part[0]) + algo_bytes(ly.qkv_part[1]) + algo_bytes(ly.qkv_part[2]) : algo_bytes(ly.qkv)) +
+             algo_bytes(ly.o) + algo_bytes(ly.gateup) + algo_bytes(ly.down);
     w += algo_bytes(m->head);
     m->weight_bytes = w;
     *out = m;
@@ -285,7 +313,7 @@ static inline uint32_t tid_of(int kind, uint32_t layer) { return layer * 16 + ki
 extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint64_t seed, int qtype, int head_qtype, b2_model **out) {
     ApiScope _scope("b2_model_create_random");
     b2_model *m = nullptr;
-    B2_TRY(alloc_model_skeleton(e, cfg, qtype, head_qtype, &m));
+    B2_TRY(alloc_model_skeleton(e, cfg, ModelTypes::uniform(cfg ? cfg->n_layers : 0, qtype, head_qtype), &m));
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = e->stream;
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
@@ -384,7 +412,21 @@ extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_te
     if (!l0) l0 = find("blk.0.attn_qkv.weight");
     B2_CHECK(l0, B2_EINVAL, "missing tensor blk.0.attn_q.weight / blk.0.attn_qkv.weight");
     b2_model *m = nullptr;
-    B2_TRY(alloc_model_skeleton(e, cfg, l0->type, te->type, &m));
+    B2_CHECK(cfg && cfg->n_layers > 0 && cfg->n_layers < 4096, B2_EINVAL, "b2_model_create: bad config");
+    // every matrix keeps the format its tensor has in the file (llama.cpp mixes formats inside one model)
+    ModelTypes mt = ModelTypes::uniform(cfg->n_layers, l0->type, te->type);
+    if (const b2_tensor_desc *ow = find("output.weight")) mt.head = ow->type;
+    for (int l = 0; l < cfg->n_layers; ++l) {
+        const std::string p = "blk." + std::to_string(l) + ".";
+        LayerTypes &lt = mt.layers[l];
+        auto ty = [&](const char *n, int dflt) { const b2_tensor_desc *t = find(p + n); return t ? t->type : dflt; };
+        if (const b2_tensor_desc *f = find(p + "attn_qkv.weight")) lt.q = lt.k = lt.v = f->type;
+        else { lt.q = ty("attn_q.weight", lt.q); lt.k = ty("attn_k.weight", lt.q); lt.v = ty("attn_v.weight", lt.q); }
+        lt.o = ty("attn_output.weight", lt.q);
+        lt.gateup = ty("ffn_up.weight", lt.q);
+        lt.down = ty("ffn_down.weight", lt.q);
+    }
+    B2_TRY(alloc_model_skeleton(e, cfg, mt, &m));
     const b2_arch_cfg &c = m->cfg;
     int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
     Staging sg;
@@ -414,9 +456,15 @@ extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_te
                     NEED(tq, p + "attn_q.weight");
                     NEED(tk, p + "attn_k.weight");
                     NEED(tv, p + "attn_v.weight");
-                    if ((rc = upload_mat(m, sg, *tq, ly.qkv, 0, 1, 0, qd))) break;
-                    if ((rc = upload_mat(m, sg, *tk, ly.qkv, qd, 1, 0, kvd))) break;
-                    if ((rc = upload_mat(m, sg, *tv, ly.qkv, qd + kvd, 1, 0, kvd))) break;
+                    if (ly.split_qkv) {
+                        if ((rc = upload_mat(m, sg, *tq, ly.qkv_part[0], 0, 1, 0, qd))) break;
+                        if ((rc = upload_mat(m, sg, *tk, ly.qkv_part[1], 0, 1, 0, kvd))) break;
+                        if ((rc = upload_mat(m, sg, *tv, ly.qkv_part[2], 0, 1, 0, kvd))) break;
+                    } else {
+                        if ((rc = upload_mat(m, sg, *tq, ly.qkv, 0, 1, 0, qd))) break;
+                        if ((rc = upload_mat(m, sg, *tk, ly.qkv, qd, 1, 0, kvd))) break;
+                        if ((rc = upload_mat(m, sg, *tv, ly.qkv, qd + kvd, 1, 0, kvd))) break;
+                    }
                 }
                 if (c.qkv_bias) {
                     NEED(bq, p + "attn_q.bias");
@@ -492,8 +540,19 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
         int g = 0;
         // each GEMV hints the matrix the next GEMV will stream (L2 prefetch of the head of every CTA's share)
         const Mat *after_down = (l + 1 < c.n_layers) ? &m->layers[l + 1].qkv : (with_head ? &m->head : nullptr);
-        launch_gemv_qt(qt_of(ly.qkv.type), GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
-                    s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), s->xsq, xsq_n, nullptr, st, pdl); n++;
+        if (ly.split_qkv) {   // q, k, v in different formats: three GEMVs into the same QKV vector
+            int64_t row0 = 0;
+            for (int part = 0; part < 3; ++part) {
+                const Mat &pm = ly.qkv_part[part];
+                launch_gemv_qt(qt_of(pm.type), GEMV_IN_NORM, GEMV_OUT_BIAS, pm.packed, pm.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                               s->qkv + row0, ly.qkv_bias ? ly.qkv_bias + row0 : nullptr, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, s->xsq, xsq_n,
+                               nullptr, st, pdl); n++;
+                row0 += pm.rows;
+            }
+        } else {
+                    launch_gemv_qt(qt_of(ly.qkv.type), GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->x, ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                        s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), s->xsq, xsq_n, nullptr, st, pdl); n++;
+        }
         if (s->fused_attn) {
             launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
                               s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, attn_ctx, st, pdl); n++;

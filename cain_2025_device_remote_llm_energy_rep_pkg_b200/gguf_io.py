@@ -8,9 +8,10 @@ llama.cpp's converters that differ from the engine's (which follows the Hugging 
     rotate-half; they are permuted back here (rows are quantised independently, so this is exact);
   * gemma: the converter already stored (1 + w) in the norm weights -> norm_plus_one is off for GGUF gemma;
   * llama 3.1: the RoPE frequency scaling travels as the tensor rope_freqs.weight -> the Llama-3.1 constants are assumed.
-The engine's kernels take Q4_0 and Q4_K layer matrices (the parts of a fused QKV or gate/up matrix must share one format), a
-Q4_0 / Q4_K / Q6_K LM head and embedding (llama.cpp keeps output.weight -- and a tied token_embd.weight -- in Q6_K even in
-"Q4_0" files) and F32 vectors.  Other combinations (Q4_K_M mixes Q6_K into attn_v / ffn_down) are refused unless `requantize=True`, which dequantises every non-Q4_0 matrix and re-quantises it to Q4_0
+The engine's kernels take Q4_0, Q4_K and Q6_K matrices -- what llama.cpp's Q4_0 and Q4_K_S/M files contain (output.weight and a
+tied token_embd.weight in Q6_K, Q4_K_M with Q6_K attn_v / ffn_down; q, k, v of different formats run as three GEMVs; gate and up
+must share one format) -- and F32 vectors.  Models with Q6_K layer matrices evaluate the prompt token by token.  Other formats
+(Q5_K, Q8_0, F16 matrices, ...) are refused unless `requantize=True`, which dequantises every non-Q4_0 matrix and re-quantises it to Q4_0
 with the gguf package's own reference code (lossy; reported in `notes`)."""
 from __future__ import annotations
 
@@ -127,12 +128,12 @@ def load(path: str, requantize: bool = False, name: Optional[str] = None) -> GGU
         elif t.tensor_type == QT.Q4_K and not requantize:      # native in the decode GEMV (csrc/layout.cuh)
             raw = np.ascontiguousarray(data).reshape(rows, cols // 256 * 144).view(np.uint8)
             qt_name = "q4_k"
-        elif t.tensor_type == QT.Q6_K and not requantize and t.name in ("output.weight", "token_embd.weight"):
-            raw = np.ascontiguousarray(data).reshape(rows, cols // 256 * 210).view(np.uint8)     # llama.cpp's format for the LM head
+        elif t.tensor_type == QT.Q6_K and not requantize:       # llama.cpp's format for the LM head, and Q4_K_M's for attn_v / ffn_down
+            raw = np.ascontiguousarray(data).reshape(rows, cols // 256 * 210).view(np.uint8)
             qt_name = "q6_k"
         else:
             if not requantize:
-                raise ValueError(f"{t.name} is {t.tensor_type.name}; the engine's matrices are Q4_0 or Q4_K "
+                raise ValueError(f"{t.name} is {t.tensor_type.name}; the engine's matrices are Q4_0, Q4_K or Q6_K "
                                  f"(pass requantize=True to convert everything else to Q4_0, lossy)")
             if t.tensor_type in (QT.F32, QT.F16):
                 dense = data.astype(np.float32).reshape(rows, cols)

@@ -126,6 +126,17 @@ def _cat_rows(parts):
     return qts.pop(), np.concatenate([np.ascontiguousarray(p[1]).reshape(p[1].shape[0], -1) for p in parts], axis=0)
 
 
+class QCat:
+    """Row-wise concatenation of matrices in DIFFERENT block formats (llama.cpp's Q4_K_M keeps attn_v in Q6_K next to Q4_K
+    attn_q / attn_k): y = [W0 x; W1 x; ...]."""
+
+    def __init__(self, parts):
+        self.parts = parts
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        return torch.cat([p(x) for p in self.parts])
+
+
 class OracleModel:
     def __init__(self, arch: Arch, tensors: dict, cache_dense: bool = True, act_bits: int = ACT_BITS):
         a = self.a = arch
@@ -139,15 +150,21 @@ class OracleModel:
         self.layers = []
         for i in range(a.L):
             p = f"blk.{i}."
+            qkv_lin = None
             if p + "attn_qkv.weight" in tensors:
                 qkv = g(p + "attn_qkv.weight")
             else:
-                qkv = _cat_rows([g(p + "attn_q.weight"), g(p + "attn_k.weight"), g(p + "attn_v.weight")])
+                parts = [g(p + "attn_q.weight"), g(p + "attn_k.weight"), g(p + "attn_v.weight")]
+                if len({t[0] for t in parts}) == 1:
+                    qkv = _cat_rows(parts)
+                else:
+                    qkv = None
+                    qkv_lin = QCat([lin(*t, r, a.H) for t, r in zip(parts, (a.q_dim, a.kv_dim, a.kv_dim))])
             bias = None
             if a.qkv_bias:
                 bias = torch.cat([vec(p + "attn_q.bias"), vec(p + "attn_k.bias"), vec(p + "attn_v.bias")])
             self.layers.append(dict(
-                attn_norm=vec(p + "attn_norm.weight"), qkv=lin(*qkv, a.q_dim + 2 * a.kv_dim, a.H), qkv_bias=bias,
+                attn_norm=vec(p + "attn_norm.weight"), qkv=qkv_lin if qkv_lin is not None else lin(*qkv, a.q_dim + 2 * a.kv_dim, a.H), qkv_bias=bias,
                 o=lin(*g(p + "attn_output.weight"), a.H, a.q_dim), ffn_norm=vec(p + "ffn_norm.weight"),
                 gate=lin(*g(p + "ffn_gate.weight"), a.I, a.H), up=lin(*g(p + "ffn_up.weight"), a.I, a.H),
                 down=lin(*g(p + "ffn_down.weight"), a.H, a.I)))

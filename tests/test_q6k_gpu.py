@@ -78,3 +78,26 @@ def test_model_with_q6k_head_matches_oracle(key, qtype, gpu_engine):
     assert np.abs(got - want).max() <= 2e-4 * np.abs(want).max()
     s = m.session(96)
     assert list(map(int, s.generate_greedy(prompt, 40))) == om.session(96).generate_greedy(prompt, 40)
+
+
+def test_q4_k_m_style_mixed_formats_match_oracle(gpu_engine):
+    """llama.cpp's Q4_K_M: Q4_K everywhere except Q6_K for attn_v, ffn_down and the head: q/k/v then run as three GEMVs."""
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200 import archs, engine
+    from oracle import archs as oarchs
+    from oracle import randinit as orand
+    from oracle.model import OracleModel
+    key = "mistral:7b"
+    a, oa = archs.TINY[key], oarchs.TINY[key]
+    tensors = orand.make_model(oa, seed=44, qtype="q4_k", head_qtype="q6_k")
+    for name, kind, layer, rows, cols in oarchs.tensor_table(oa):
+        if kind in ("attn_v", "ffn_down") and (kind == "attn_v" or layer % 2 == 0):
+            tensors[name] = ("q6_k", orand.make_tensor(oa, 44, kind, layer, rows, cols, "q6_k"))
+    m = engine.Model.from_tensors(gpu_engine, a, tensors, max_ctx=96)
+    om = OracleModel(oa, tensors)
+    prompt = [1, 5, 77, 300, 12, 9, 640, 2]
+    got = m.session(96).forward_tokens(prompt)
+    os_ = om.session(96)
+    want = np.stack([os_.step(t).numpy() for t in prompt])
+    assert np.abs(got - want).max() <= 2e-4 * np.abs(want).max()
+    s = m.session(96)
+    assert list(map(int, s.generate_greedy(prompt, 40))) == om.session(96).generate_greedy(prompt, 40)
