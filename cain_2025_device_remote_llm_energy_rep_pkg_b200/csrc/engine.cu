@@ -786,6 +786,9 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     std::vector<int32_t> pt(s->n_pages);
     for (int p = 0; p < s->n_pages; ++p) pt[p] = s->n_pages - 1 - p;
     cudaError_t e = cudaMemcpy(s->page_table, pt.data(), pt.size() * 4, cudaMemcpyHostToDevice);
+    // cache slots beyond the current position are read (and masked) by the tiled prompt attention: they must hold finite values
+    if (e == cudaSuccess) e = cudaMemset(s->kcache, 0, kv_elems * 2);
+    if (e == cudaSuccess) e = cudaMemset(s->vcache, 0, kv_elems * 2);
     if (e == cudaSuccess) e = cudaMemset(s->attn_scratch, 0, attn_scratch_bytes(c.n_heads, hd));
     if (e == cudaSuccess) e = cudaMemset(s->argmax_scratch, 0, argmax_scratch_bytes());
     if (e == cudaSuccess) e = cudaMemset(s->sample_scratch, 0, sample_scratch_bytes(SAMPLE_MAX_K));
