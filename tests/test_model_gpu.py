@@ -155,3 +155,18 @@ def test_decode_with_topk_sampler_follows_the_sampler_contract(pk, gpu_engine):
     s.prefill(PROMPT)
     g2 = s.decode(8, sampler=SamplerCfg(top_k=1, temperature=1.0, top_p=1.0, seed=7))
     assert np.array_equal(g1, g2)
+
+
+@pytest.mark.parametrize("key", ["llama3.1:8b", "phi3:3.8b"])
+def test_long_prompt_batches_match_token_by_token(pk, gpu_engine, key):
+    """A 330-token prompt: six batches through the tcgen05 GEMM, the tiled causal attention over the growing cache (contexts
+    above 256), against the decode kernels fed token by token."""
+    archs, engine = pk
+    a = archs.TINY[key]
+    m = engine.Model.random(gpu_engine, a, seed=8, max_ctx=512)
+    prompt = [1 + (i * 37) % (a.V - 1) for i in range(330)]
+    s1, s2 = m.session(512), m.session(512)
+    lg = s1.prefill(prompt, want_logits=True)
+    forced = s2.forward_tokens(prompt)[-1]
+    assert np.abs(lg - forced).max() <= 2e-4 * np.abs(forced).max()
+    assert np.array_equal(s1.decode(24), s2.decode(24))
