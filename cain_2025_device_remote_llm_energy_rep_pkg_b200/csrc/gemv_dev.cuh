@@ -172,9 +172,19 @@ __device__ __forceinline__ void cta_sync() { __syncthreads(); }
 __device__ __forceinline__ void l2_prefetch(const void *p, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
+#ifndef STREAM_EVICT_FIRST
+#define STREAM_EVICT_FIRST 0
+#endif
 __device__ __forceinline__ uint4 ldg_stream4(const void *p) {   // weights: read once, keep out of L1
     uint4 r;
+#if STREAM_EVICT_FIRST
+    // the line is dead once read: mark it first in line for eviction from L2 so that lines the prefetch cursor brought in survive
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+#else
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+#endif
     return r;
 }
 __device__ __forceinline__ uint4 ldcg4(const void *p) {         // activations written by the previous kernel: L2
@@ -255,6 +265,9 @@ __device__ __forceinline__ void bg_mma_q6(const WPieceT<2> &r, const BFragT<2> &
 // off[0..1] (Q4_K): running sums of (8A - B) * block sum for rows g / g+8, this lane's block (j = t) of every block-group
 template <int QT>
 __device__ __forceinline__ void bg_mma(const WPieceT<QT> &r, const BFragT<QT> &b, float (&acc)[4], float (&off)[2], int t) {
+#ifdef GEMV_EXP_NOMMA
+    if (true) { acc[0] += __uint_as_float((r.wa.x ^ r.wb.y ^ r.sd.z) & 0x3fffffu); return; }   // experiment: the loop without its arithmetic
+#endif
     if constexpr (QT == 2) {
         bg_mma_q6(r, b, acc, off, t);
     } else {
