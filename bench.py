@@ -37,6 +37,8 @@ def parse():
     ap.add_argument("--new-tokens", type=int, default=256)
     ap.add_argument("--prompt-len", type=int, default=32)
     ap.add_argument("--all-models", action="store_true", help="also report per-model tokens/s and J/token for all seven tags")
+    ap.add_argument("--tp", action="store_true", help="the N ranks form ONE tensor-parallel group that serves one request stream "
+                    "(default: N independent model replicas, the run table's natural grain)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-tokens", type=int, default=6)
     return ap.parse_args()
@@ -119,9 +121,9 @@ def run_reference(args):
     info["value"] = v
     line = {"metric": "decode_tokens_per_s", "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1000.0 * (time.perf_counter() - t0) / (args.warmup + args.steps),
-            "higher_is_better": True, "scaling": "weak",
+            "higher_is_better": True, "scaling": "strong" if tp else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, one replica per GPU",
+            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, " + (f"one request stream over a tensor-parallel group of {world} GPUs (partial sums exchanged through peer memory inside the GEMV kernels)" if tp else "one replica per GPU"),
                        "new_tokens": args.new_tokens, "prompt_len": args.prompt_len, "requests_per_step_per_gpu": 1,
                        "step": f"bounded sample: {args.cpu_tokens} decode tokens of the oracle per step"},
             "cpu_baseline": info, "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -264,9 +266,18 @@ def run_ours(args):
         import torch.distributed as dist_mod
         dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_mod
-    eng = Engine(local)
+    tp = args.tp and world > 1
+    if tp:   # one group, one request stream: every rank holds 1/N of each layer and returns the same tokens
+        eng = Engine(local, tp_rank=rank, tp_size=world)
+        eng.tp_connect_torch()
+    else:
+        eng = Engine(local)
     r = bench_model(eng, args.model, args, lib, local, dist, args.steps, args.warmup)
+    if tp:
+        r["kv_bytes_per_token"] /= world
     (wall, eval_s), (tokens, launches, energy) = aggregate(dist, r["wall_s"], r["eval_s"], r["tokens"], r["launches"], r["energy_j"])
+    if tp:
+        tokens = r["tokens"]   # the ranks produced the same tokens once, not N times
     per_model = None
     if args.all_models and rank == 0 and world == 1:
         per_model = {}
@@ -287,9 +298,9 @@ def run_ours(args):
         ach = step_bytes * (r["tokens"] / r["eval_s"]) / 1e9   # per GPU: every replica reads its own copy
         line = {
             "metric": "decode_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1000.0 * wall / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1000.0 * wall / args.steps, "higher_is_better": True, "scaling": "strong" if tp else "weak",
             "vs_baseline": None, "dtype": "int4 weights x 21-bit fixed-point activations, int32/fp32 accumulate", "data": "synthetic",
-            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, one replica per GPU",
+            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, " + (f"one request stream over a tensor-parallel group of {world} GPUs (partial sums exchanged through peer memory inside the GEMV kernels)" if tp else "one replica per GPU"),
                        "new_tokens": args.new_tokens, "prompt_len": args.prompt_len, "requests_per_step_per_gpu": 1,
                        "l2": "inputs larger than L2 (weights %.0f MB per token)" % (r["weight_bytes"] / 1e6)},
             "e2e": {"value": tokens / wall, "unit": "tokens/s", "h2d_bytes_per_step": args.prompt_len * 4 + 16 * (1 + 1),

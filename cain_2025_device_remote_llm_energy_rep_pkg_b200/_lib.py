@@ -44,6 +44,8 @@ SIGNATURES = {
     "b2_engine_create": (i32, [i32, i32, i32, vp, P(vp)]),
     "b2_engine_destroy": (i32, [vp]),
     "b2_engine_device": (i32, [vp, P(i32)]),
+    "b2_engine_tp_handle": (i32, [vp, vp]),
+    "b2_engine_tp_connect": (i32, [vp, vp]),
     "b2_model_create": (i32, [vp, P(CArchCfg), P(TensorDesc), i32, P(vp)]),
     "b2_model_create_random": (i32, [vp, P(CArchCfg), u64, i32, i32, P(vp)]),
     "b2_model_destroy": (i32, [vp]),

@@ -42,10 +42,33 @@ ApiScope::~ApiScope() {
 extern "C" const char *b2_version(void) { return "b2llm 0.1 (sm_100a)"; }
 
 // ------------------------------------------------------------------------------------ objects
+// Exchange memory of a tensor-parallel group (one engine = one rank = one process = one GPU).  Every rank allocates one block,
+// hands its CUDA IPC handle to the others (b2_engine_tp_handle / b2_engine_tp_connect) and maps theirs.  Layout of a block:
+//   float slots[2 buffers][8 source ranks][TP_MAX_VEC]   partial sums pushed by the peers (and by this rank, into its own slot)
+//   u64   arrivals[2 buffers][8 source ranks]            CTAs of the producing kernel that have stored their rows, ever increasing
+//   u64   forwards                                       forward passes this rank has completed
+//   u32   error                                          1 + rank that did not arrive in time (sticky)
+// Buffer 0 carries the O-projection rounds, buffer 1 the down-projection rounds, so a rank that is one exchange ahead never
+// overwrites slots a slower rank still reads (a rank cannot be two exchanges ahead: each exchange waits for every rank).
+#define TP_MAX_VEC 8192
+#define TP_MAX_RANKS 8
+struct TpLink {
+    int n = 1, rank = 0;
+    void *local = nullptr;
+    void *peer[TP_MAX_RANKS] = {};
+    bool connected = false;
+    static constexpr size_t slots_bytes() { return (size_t)2 * TP_MAX_RANKS * TP_MAX_VEC * 4; }
+    static constexpr size_t bytes() { return slots_bytes() + 2 * TP_MAX_RANKS * 8 + 8 + 8 + 240; }
+    float *slot(int on_rank, int buf, int src) const { return (float *)peer[on_rank] + ((size_t)buf * TP_MAX_RANKS + src) * TP_MAX_VEC; }
+    unsigned long long *arrivals(int on_rank, int buf) const { return (unsigned long long *)((char *)peer[on_rank] + slots_bytes()) + buf * TP_MAX_RANKS; }
+    unsigned long long *forwards() const { return (unsigned long long *)((char *)local + slots_bytes()) + 2 * TP_MAX_RANKS; }
+    unsigned int *error() const { return (unsigned int *)(forwards() + 1); }
+};
 struct b2_engine {
     int device = 0, tp_rank = 0, tp_size = 1;
     cudaStream_t stream = nullptr;
     int sm_count = 0;
+    TpLink tp;
 };
 struct Mat {
     void *packed = nullptr;
@@ -81,8 +104,14 @@ struct b2_model {
     bool all_q4_0 = true;          // the persistent kernel takes Q4_0 matrices only
     bool layers_q4 = true;         // the tcgen05 prompt GEMM takes Q4_0 / Q4_K layer matrices (a Q6_K head is fine: it runs as a GEMV)
     std::vector<void *> allocs;
-    int q_dim() const { return cfg.n_heads * cfg.head_dim; }
-    int kv_dim() const { return cfg.n_kv_heads * cfg.head_dim; }
+    // a rank of a tensor-parallel group holds n_heads / tp query heads, n_kv_heads / tp KV heads and ffn / tp rows of gate / up
+    // (column-parallel QKV, gate, up; row-parallel O, down); norms, embedding and LM head are replicated.  tp = 1: everything.
+    int tp = 1, tp_rank = 0;
+    int heads() const { return cfg.n_heads / tp; }
+    int kv_heads() const { return cfg.n_kv_heads / tp; }
+    int ffn() const { return cfg.ffn / tp; }
+    int q_dim() const { return heads() * cfg.head_dim; }
+    int kv_dim() const { return kv_heads() * cfg.head_dim; }
 };
 enum { G_PREFILL_BODY = 0, G_PREFILL_LAST, G_DECODE, G_DECODE_LOG, G_FORCED, G_SAMPLE, G_SAMPLE_LOG, G_COUNT };
 struct b2_session {
@@ -130,6 +159,7 @@ struct b2_session {
     b2_stats stats{};
     int host_pos = 0;
     bool have_logits = false;
+    cudaError_t enqueue_error = cudaSuccess;   // first launch error of the tensor-parallel pass (reported by run_graph)
     std::vector<void *> allocs;
 };
 
@@ -146,9 +176,10 @@ static int dev_alloc(std::vector<void *> &owner, void **p, uint64_t n) {
 // ------------------------------------------------------------------------------------ engine
 extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, const void *nccl_uid, b2_engine **out) {
     ApiScope _scope("b2_engine_create");
-    (void)nccl_uid;
+    (void)nccl_uid;   // the exchange runs over peer memory mapped with b2_engine_tp_connect, not over a NCCL communicator
     B2_CHECK(out, B2_EINVAL, "b2_engine_create: out is NULL");
-    B2_CHECK(tp_size == 1 && tp_rank == 0, B2_EINVAL, "b2_engine_create: tensor parallel size %d not supported in this build", tp_size);
+    B2_CHECK(tp_size == 1 || tp_size == 2 || tp_size == 4 || tp_size == 8, B2_EINVAL, "b2_engine_create: tensor parallel size %d (1, 2, 4 or 8)", tp_size);
+    B2_CHECK(tp_rank >= 0 && tp_rank < tp_size, B2_EINVAL, "b2_engine_create: rank %d of %d", tp_rank, tp_size);
     int n = 0;
     B2_CUDA(cudaGetDeviceCount(&n));
     B2_CHECK(device_ordinal >= 0 && device_ordinal < n, B2_EINVAL, "b2_engine_create: device %d of %d", device_ordinal, n);
@@ -159,14 +190,61 @@ extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, co
     b2_engine *e = new b2_engine();
     e->device = device_ordinal;
     e->sm_count = prop.multiProcessorCount;
+    e->tp_rank = tp_rank;
+    e->tp_size = tp_size;
+    e->tp.n = tp_size;
+    e->tp.rank = tp_rank;
     B2_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     *out = e;
+    return B2_OK;
+}
+// The exchange block of this rank (allocated and zeroed on the first call) as a CUDA IPC handle for the other ranks' processes.
+extern "C" int b2_engine_tp_handle(b2_engine *e, void *handle_out) {
+    ApiScope _scope("b2_engine_tp_handle");
+    B2_CHECK(e && handle_out, B2_EINVAL, "b2_engine_tp_handle: NULL");
+    B2_CHECK(e->tp_size > 1, B2_EINVAL, "b2_engine_tp_handle: the engine was created with tp_size 1");
+    static_assert(sizeof(cudaIpcMemHandle_t) == B2_TP_HANDLE_BYTES, "handle size");
+    B2_CUDA(cudaSetDevice(e->device));
+    if (!e->tp.local) {
+        B2_CUDA(cudaMalloc(&e->tp.local, TpLink::bytes()));
+        B2_CUDA(cudaMemset(e->tp.local, 0, TpLink::bytes()));
+        B2_CUDA(cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t h;
+    B2_CUDA(cudaIpcGetMemHandle(&h, e->tp.local));
+    memcpy(handle_out, &h, sizeof h);
+    return B2_OK;
+}
+// handles: tp_size consecutive handles, entry r from rank r's b2_engine_tp_handle (this rank's own entry is not opened).
+extern "C" int b2_engine_tp_connect(b2_engine *e, const void *handles) {
+    ApiScope _scope("b2_engine_tp_connect");
+    B2_CHECK(e && handles, B2_EINVAL, "b2_engine_tp_connect: NULL");
+    B2_CHECK(e->tp_size > 1 && e->tp.local, B2_EINVAL, "b2_engine_tp_connect: call b2_engine_tp_handle first");
+    B2_CHECK(!e->tp.connected, B2_EINVAL, "b2_engine_tp_connect: already connected");
+    B2_CUDA(cudaSetDevice(e->device));
+    for (int r = 0; r < e->tp_size; ++r) {
+        if (r == e->tp_rank) { e->tp.peer[r] = e->tp.local; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char *)handles + (size_t)r * sizeof h, sizeof h);
+        cudaError_t err = cudaIpcOpenMemHandle(&e->tp.peer[r], h, cudaIpcMemLazyEnablePeerAccess);
+        if (err != cudaSuccess) {
+            cudaGetLastError();
+            b2_set_error("b2_engine_tp_connect: cannot map the exchange block of rank %d (%s); tensor parallelism needs peer access between the GPUs", r,
+                         cudaGetErrorString(err));
+            return B2_ECUDA;
+        }
+    }
+    e->tp.connected = true;
     return B2_OK;
 }
 extern "C" int b2_engine_destroy(b2_engine *e) {
     ApiScope _scope("b2_engine_destroy");
     if (!e) return B2_OK;
     cudaSetDevice(e->device);
+    if (e->tp.connected)
+        for (int r = 0; r < e->tp_size; ++r)
+            if (r != e->tp_rank && e->tp.peer[r]) cudaIpcCloseMemHandle(e->tp.peer[r]);
+    if (e->tp.local) cudaFree(e->tp.local);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
     return B2_OK;
@@ -245,11 +323,26 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, const Mode
     B2_CHECK(e && out, B2_EINVAL, "NULL engine/out");
     B2_TRY(check_cfg(cfg));
     B2_CUDA(cudaSetDevice(e->device));
+    const int tp = e->tp_size;
+    if (tp > 1) {
+        B2_CHECK(e->tp.connected, B2_EINVAL, "tensor parallel engine: call b2_engine_tp_connect before creating a model");
+        B2_CHECK(cfg->n_kv_heads % tp == 0, B2_EINVAL, "%d KV heads do not split over %d ranks", cfg->n_kv_heads, tp);
+        B2_CHECK(cfg->ffn % (QK * tp) == 0, B2_EINVAL, "ffn %d does not split over %d ranks in whole blocks", cfg->ffn, tp);
+        B2_CHECK(cfg->hidden <= TP_MAX_VEC, B2_EINVAL, "hidden %d exceeds the exchange slots (%d)", cfg->hidden, TP_MAX_VEC);
+        bool kq = mt.embd != B2_T_Q4_0 && false;
+        for (const LayerTypes &lt : mt.layers) kq = kq || lt.o != B2_T_Q4_0 || lt.down != B2_T_Q4_0;
+        if (kq) {   // a column window of a K-quant matrix must start and end on a 256-element super-block
+            B2_CHECK((cfg->n_heads / tp * cfg->head_dim) % 256 == 0 && (cfg->ffn / tp) % 256 == 0, B2_EINVAL,
+                     "K-quant O / down matrices do not split over %d ranks in whole super-blocks", tp);
+        }
+    }
     b2_model *m = new b2_model();
     m->e = e;
     m->cfg = *cfg;
+    m->tp = tp;
+    m->tp_rank = e->tp_rank;
     const b2_arch_cfg &c = m->cfg;
-    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
+    int H = c.hidden, I = m->ffn(), qd = m->q_dim(), kvd = m->kv_dim();
     int rc = B2_OK;
     do {
         if ((rc = alloc_mat(m, m->embd, c.vocab, H, mt.embd))) break;
@@ -316,16 +409,19 @@ extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint
     B2_TRY(alloc_model_skeleton(e, cfg, ModelTypes::uniform(cfg ? cfg->n_layers : 0, qtype, head_qtype), &m));
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = e->stream;
-    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
+    int H = c.hidden, I = m->ffn(), qd = m->q_dim(), kvd = m->kv_dim();
     float nsig = 0.1f, noff = c.norm_plus_one ? 0.0f : 1.0f, wsig = 0.02f, bsig = 0.1f;
     auto key = [&](int kind, uint32_t layer) { return ri_tensor_key(seed, tid_of(kind, layer)); };
     // Q4_0: gaussian weights through ggml's quantiser (bit-identical to b2_randinit_tensor and oracle/randinit.py);
     // Q4_K: synthetic blocks (gemv.cu:k_randinit_q4_k), for benchmarks only
-    auto ri = [&](const Mat &mt, uint64_t k, float sig, int64_t rows, int64_t cols, int64_t row0, int64_t stride) {
-        if (mt.type == B2_T_Q6_K) launch_randinit_q6_k(k, rows, cols, mt.packed, row0, stride, st);
-        else if (mt.type == B2_T_Q4_K) launch_randinit_q4_k(k, rows, cols, mt.packed, row0, stride, st);
-        else launch_randinit_q4_0(k, sig, rows, cols, mt.packed, row0, stride, st);
+    // (rows x cols) window at (src_row0, src_col0) of the whole tensor, whose rows are src_cols wide, into rows dst_row0, +stride, ...
+    auto ri = [&](const Mat &mt, uint64_t k, float sig, int64_t rows, int64_t cols, int64_t row0, int64_t stride, int64_t src_row0 = 0,
+                  int64_t src_cols = 0, int64_t src_col0 = 0) {
+        if (mt.type == B2_T_Q6_K) launch_randinit_q6_k(k, rows, cols, mt.packed, row0, stride, st, src_row0, src_cols, src_col0);
+        else if (mt.type == B2_T_Q4_K) launch_randinit_q4_k(k, rows, cols, mt.packed, row0, stride, st, src_row0, src_cols, src_col0);
+        else launch_randinit_q4_0(k, sig, rows, cols, mt.packed, row0, stride, st, src_row0, src_cols, src_col0);
     };
+    const int64_t rk = m->tp_rank, qd_full = (int64_t)c.n_heads * c.head_dim, I_full = c.ffn;
     ri(m->embd, key(K_EMBD, GLOBAL_LAYER), wsig, c.vocab, H, 0, 1);
     if (!c.tied) ri(m->head, key(K_OUTPUT, GLOBAL_LAYER), wsig, c.vocab, H, 0, 1);
     launch_randinit_f32(key(K_OUT_NORM, GLOBAL_LAYER), nsig, noff, H, m->out_norm, st);
@@ -333,19 +429,18 @@ extern "C" int b2_model_create_random(b2_engine *e, const b2_arch_cfg *cfg, uint
         LayerW &ly = m->layers[l];
         launch_randinit_f32(key(K_ATTN_NORM, l), nsig, noff, H, ly.attn_norm, st);
         launch_randinit_f32(key(K_FFN_NORM, l), nsig, noff, H, ly.ffn_norm, st);
-        int64_t tr = qd + 2 * kvd;
-        ri(ly.qkv, key(K_Q, l), wsig, qd, H, 0, 1);
-        ri(ly.qkv, key(K_K, l), wsig, kvd, H, qd, 1);
-        ri(ly.qkv, key(K_V, l), wsig, kvd, H, qd + kvd, 1);
+        ri(ly.qkv, key(K_Q, l), wsig, qd, H, 0, 1, rk * qd);
+        ri(ly.qkv, key(K_K, l), wsig, kvd, H, qd, 1, rk * kvd);
+        ri(ly.qkv, key(K_V, l), wsig, kvd, H, qd + kvd, 1, rk * kvd);
         if (c.qkv_bias) {
-            launch_randinit_f32(key(K_QB, l), bsig, 0.f, qd, ly.qkv_bias, st);
-            launch_randinit_f32(key(K_KB, l), bsig, 0.f, kvd, ly.qkv_bias + qd, st);
-            launch_randinit_f32(key(K_VB, l), bsig, 0.f, kvd, ly.qkv_bias + qd + kvd, st);
+            launch_randinit_f32(key(K_QB, l), bsig, 0.f, qd, ly.qkv_bias, st, rk * qd);
+            launch_randinit_f32(key(K_KB, l), bsig, 0.f, kvd, ly.qkv_bias + qd, st, rk * kvd);
+            launch_randinit_f32(key(K_VB, l), bsig, 0.f, kvd, ly.qkv_bias + qd + kvd, st, rk * kvd);
         }
-        ri(ly.o, key(K_O, l), wsig, H, qd, 0, 1);
-        ri(ly.gateup, key(K_GATE, l), wsig, I, H, 0, 2);
-        ri(ly.gateup, key(K_UP, l), wsig, I, H, 1, 2);
-        ri(ly.down, key(K_DOWN, l), wsig, H, I, 0, 1);
+        ri(ly.o, key(K_O, l), wsig, H, qd, 0, 1, 0, qd_full, rk * qd);
+        ri(ly.gateup, key(K_GATE, l), wsig, I, H, 0, 2, rk * I);
+        ri(ly.gateup, key(K_UP, l), wsig, I, H, 1, 2, rk * I);
+        ri(ly.down, key(K_DOWN, l), wsig, H, I, 0, 1, 0, I_full, rk * I);
     }
     cudaError_t err = cudaStreamSynchronize(st);
     if (err == cudaSuccess) err = cudaGetLastError();
@@ -373,23 +468,28 @@ struct Staging {
     }
 };
 
-static int upload_mat(b2_model *m, Staging &sg, const b2_tensor_desc &t, Mat &dst, int64_t dst_row0, int64_t stride, int64_t src_row0, int64_t nrows) {
+// rows [src_row0, src_row0 + nrows) of the tensor; src_col0 >= 0: only its columns [src_col0, src_col0 + dst.cols) (a rank's K slice)
+static int upload_mat(b2_model *m, Staging &sg, const b2_tensor_desc &t, Mat &dst, int64_t dst_row0, int64_t stride, int64_t src_row0, int64_t nrows,
+                      int64_t src_col0 = -1) {
     B2_CHECK(t.type == dst.type, B2_EINVAL, "tensor %s: type %d, but the matrix it belongs to is type %d (all parts of a fused matrix share one format)", t.name, t.type, dst.type);
-    B2_CHECK(t.cols == dst.cols, B2_EINVAL, "tensor %s: cols %lld, expected %lld", t.name, (long long)t.cols, (long long)dst.cols);
+    if (src_col0 < 0) B2_CHECK(t.cols == dst.cols, B2_EINVAL, "tensor %s: cols %lld, expected %lld", t.name, (long long)t.cols, (long long)dst.cols);
+    else B2_CHECK(src_col0 + dst.cols <= t.cols, B2_EINVAL, "tensor %s: cols %lld, need %lld", t.name, (long long)t.cols, (long long)(src_col0 + dst.cols));
     uint64_t row_bytes = t.type == B2_T_Q6_K ? (uint64_t)(t.cols / 256) * 210 : t.type == B2_T_Q4_K ? (uint64_t)(t.cols / 256) * 144 : (uint64_t)(t.cols / QK) * 18;
     B2_CHECK(t.nbytes == (uint64_t)t.rows * row_bytes, B2_EINVAL, "tensor %s: %llu bytes, expected %llu", t.name, (unsigned long long)t.nbytes, (unsigned long long)(t.rows * row_bytes));
     B2_CHECK(src_row0 + nrows <= t.rows, B2_EINVAL, "tensor %s: has %lld rows, need %lld", t.name, (long long)t.rows, (long long)(src_row0 + nrows));
     B2_TRY(sg.ensure(nrows * row_bytes));
     B2_CUDA(cudaMemcpyAsync(sg.buf, (const char *)t.data + src_row0 * row_bytes, nrows * row_bytes, cudaMemcpyHostToDevice, m->e->stream));
-    if (t.type == B2_T_Q6_K) launch_pack_q6_k(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
-    else if (t.type == B2_T_Q4_K) launch_pack_q4_k(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
-    else launch_pack_q4_0(sg.buf, nrows, t.cols, dst.packed, dst_row0, stride, m->e->stream);
+    const int64_t wc = src_col0 < 0 ? 0 : t.cols, c0 = src_col0 < 0 ? 0 : src_col0;
+    if (t.type == B2_T_Q6_K) launch_pack_q6_k(sg.buf, nrows, dst.cols, dst.packed, dst_row0, stride, m->e->stream, wc, c0);
+    else if (t.type == B2_T_Q4_K) launch_pack_q4_k(sg.buf, nrows, dst.cols, dst.packed, dst_row0, stride, m->e->stream, wc, c0);
+    else launch_pack_q4_0(sg.buf, nrows, dst.cols, dst.packed, dst_row0, stride, m->e->stream, wc, c0);
     B2_CUDA(cudaStreamSynchronize(m->e->stream));
     return B2_OK;
 }
-static int upload_vec(b2_model *m, const b2_tensor_desc &t, float *dst, int64_t n) {
-    B2_CHECK(t.type == B2_T_F32 && t.rows == n && t.nbytes == (uint64_t)n * 4, B2_EINVAL, "tensor %s: expected f32[%lld]", t.name, (long long)n);
-    B2_CUDA(cudaMemcpy(dst, t.data, n * 4, cudaMemcpyHostToDevice));
+static int upload_vec(b2_model *m, const b2_tensor_desc &t, float *dst, int64_t n, int64_t src0 = 0, int64_t full = -1) {
+    if (full < 0) full = n;
+    B2_CHECK(t.type == B2_T_F32 && t.rows == full && t.nbytes == (uint64_t)full * 4, B2_EINVAL, "tensor %s: expected f32[%lld]", t.name, (long long)full);
+    B2_CUDA(cudaMemcpy(dst, (const float *)t.data + src0, n * 4, cudaMemcpyHostToDevice));
     (void)m;
     return B2_OK;
 }
@@ -428,9 +528,12 @@ extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_te
     }
     B2_TRY(alloc_model_skeleton(e, cfg, mt, &m));
     const b2_arch_cfg &c = m->cfg;
-    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim();
+    int H = c.hidden, I = m->ffn(), qd = m->q_dim(), kvd = m->kv_dim();
     Staging sg;
     int rc = B2_OK;
+    // a tensor-parallel rank takes its rows of q / k / v / gate / up and its columns of attn_output / ffn_down
+    const int64_t rk = m->tp_rank, qdF = (int64_t)c.n_heads * c.head_dim, kvdF = (int64_t)c.n_kv_heads * c.head_dim, IF = c.ffn;
+    const int64_t ocol = m->tp > 1 ? rk * qd : -1, dcol = m->tp > 1 ? rk * I : -1;
 #define NEED(var, name)                                                        \
     const b2_tensor_desc *var = find(name);                                    \
     if (!var) { b2_set_error("missing tensor %s", std::string(name).c_str()); rc = B2_EINVAL; break; }
@@ -451,42 +554,42 @@ extern "C" int b2_model_create(b2_engine *e, const b2_arch_cfg *cfg, const b2_te
                 NEED(fn, p + "ffn_norm.weight");
                 if ((rc = upload_vec(m, *fn, ly.ffn_norm, H))) break;
                 if (const b2_tensor_desc *f = find(p + "attn_qkv.weight")) {
-                    if ((rc = upload_mat(m, sg, *f, ly.qkv, 0, 1, 0, qd + 2 * kvd))) break;
+                    if ((rc = (m->tp > 1 ? (upload_mat(m, sg, *f, ly.qkv, 0, 1, rk * qd, qd) || upload_mat(m, sg, *f, ly.qkv, qd, 1, qdF + rk * kvd, kvd) || upload_mat(m, sg, *f, ly.qkv, qd + kvd, 1, qdF + kvdF + rk * kvd, kvd)) : upload_mat(m, sg, *f, ly.qkv, 0, 1, 0, qd + 2 * kvd)))) break;
                 } else {
                     NEED(tq, p + "attn_q.weight");
                     NEED(tk, p + "attn_k.weight");
                     NEED(tv, p + "attn_v.weight");
                     if (ly.split_qkv) {
-                        if ((rc = upload_mat(m, sg, *tq, ly.qkv_part[0], 0, 1, 0, qd))) break;
-                        if ((rc = upload_mat(m, sg, *tk, ly.qkv_part[1], 0, 1, 0, kvd))) break;
-                        if ((rc = upload_mat(m, sg, *tv, ly.qkv_part[2], 0, 1, 0, kvd))) break;
+                        if ((rc = upload_mat(m, sg, *tq, ly.qkv_part[0], 0, 1, rk * qd, qd))) break;
+                        if ((rc = upload_mat(m, sg, *tk, ly.qkv_part[1], 0, 1, rk * kvd, kvd))) break;
+                        if ((rc = upload_mat(m, sg, *tv, ly.qkv_part[2], 0, 1, rk * kvd, kvd))) break;
                     } else {
-                        if ((rc = upload_mat(m, sg, *tq, ly.qkv, 0, 1, 0, qd))) break;
-                        if ((rc = upload_mat(m, sg, *tk, ly.qkv, qd, 1, 0, kvd))) break;
-                        if ((rc = upload_mat(m, sg, *tv, ly.qkv, qd + kvd, 1, 0, kvd))) break;
+                        if ((rc = upload_mat(m, sg, *tq, ly.qkv, 0, 1, rk * qd, qd))) break;
+                        if ((rc = upload_mat(m, sg, *tk, ly.qkv, qd, 1, rk * kvd, kvd))) break;
+                        if ((rc = upload_mat(m, sg, *tv, ly.qkv, qd + kvd, 1, rk * kvd, kvd))) break;
                     }
                 }
                 if (c.qkv_bias) {
                     NEED(bq, p + "attn_q.bias");
                     NEED(bk, p + "attn_k.bias");
                     NEED(bv, p + "attn_v.bias");
-                    if ((rc = upload_vec(m, *bq, ly.qkv_bias, qd))) break;
-                    if ((rc = upload_vec(m, *bk, ly.qkv_bias + qd, kvd))) break;
-                    if ((rc = upload_vec(m, *bv, ly.qkv_bias + qd + kvd, kvd))) break;
+                    if ((rc = upload_vec(m, *bq, ly.qkv_bias, qd, rk * qd, qdF))) break;
+                    if ((rc = upload_vec(m, *bk, ly.qkv_bias + qd, kvd, rk * kvd, kvdF))) break;
+                    if ((rc = upload_vec(m, *bv, ly.qkv_bias + qd + kvd, kvd, rk * kvd, kvdF))) break;
                 }
                 NEED(to, p + "attn_output.weight");
-                if ((rc = upload_mat(m, sg, *to, ly.o, 0, 1, 0, H))) break;
+                if ((rc = upload_mat(m, sg, *to, ly.o, 0, 1, 0, H, ocol))) break;
                 const b2_tensor_desc *tg = find(p + "ffn_gate.weight");
                 NEED(tu, p + "ffn_up.weight");
                 if (tg) {
-                    if ((rc = upload_mat(m, sg, *tg, ly.gateup, 0, 2, 0, I))) break;
-                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 1, 2, 0, I))) break;
+                    if ((rc = upload_mat(m, sg, *tg, ly.gateup, 0, 2, rk * I, I))) break;
+                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 1, 2, rk * I, I))) break;
                 } else {   // phi3-style fused [gate; up]
-                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 0, 2, 0, I))) break;
-                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 1, 2, I, I))) break;
+                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 0, 2, rk * I, I))) break;
+                    if ((rc = upload_mat(m, sg, *tu, ly.gateup, 1, 2, IF + rk * I, I))) break;
                 }
                 NEED(td, p + "ffn_down.weight");
-                if ((rc = upload_mat(m, sg, *td, ly.down, 0, 1, 0, H))) break;
+                if ((rc = upload_mat(m, sg, *td, ly.down, 0, 1, 0, H, dcol))) break;
             } while (0);
         }
     } while (0);
@@ -522,19 +625,89 @@ __global__ void k_copy_logits(const float *logits, int n, float *log, const DevS
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = logits[i];
 }
 
+// The same pass on one rank of a tensor-parallel group.  Per layer: QKV of this rank's heads, attention over them, O projection
+// of this rank's columns (partial rows -> every rank's slots, buffer 0), gate/up of this rank's rows (its prologue forms
+// x = residual + sum of the slots), down projection of this rank's columns (-> buffer 1), consumed by the next layer's QKV or by
+// the LM head (replicated: every rank computes all logits from the same x, so all ranks sample the same token without a further
+// exchange).  The residual alternates between two buffers: a consumer's CTA 0 writes the new one while the others read the old.
+static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
+    b2_model *m = s->m;
+    const b2_arch_cfg &c = m->cfg;
+    const TpLink &L = m->e->tp;
+    cudaStream_t st = m->e->stream;
+    const bool pdl = s->use_pdl;
+    const int H = c.hidden, I = m->ffn(), qd = m->q_dim(), hd = c.head_dim, N = L.n, rk = L.rank;
+    int n = 0;
+    float *X[2] = {s->x, s->x + H};
+    int cur = 0;
+    const float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
+    launch_embed_row(qt_of(m->embd.type), m->embd.packed, m->embd.cols, &s->state->cur_token, escale, X[0], s->xsq, st); n++;
+    const uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
+    const int per_round = gemv_grid((int)ntiles(H), 1), rounds = c.n_layers;
+    auto producer = [&](int buf) {
+        GemvTp t;
+        t.n = N;
+        for (int p = 0; p < N; ++p) { t.dst[p] = L.slot(p, buf, rk); t.sig[p] = L.arrivals(p, buf) + rk; }
+        return t;
+    };
+    auto consumer = [&](int buf, int round) {
+        GemvTp t;
+        t.n = N;
+        t.res = X[cur]; t.xout = X[cur ^ 1];
+        t.slots = L.slot(rk, buf, 0); t.slot_stride = TP_MAX_VEC;
+        t.cnt = L.arrivals(rk, buf); t.fwd = L.forwards();
+        t.round = round; t.rounds = rounds; t.per_round = per_round;
+        t.err = L.error();
+        cur ^= 1;
+        return t;
+    };
+    cudaError_t e = cudaSuccess;
+    for (int l = 0; l < c.n_layers && e == cudaSuccess; ++l) {
+        LayerW &ly = m->layers[l];
+        if (l == 0)
+            e = launch_gemv_qt(qt_of(ly.qkv.type), GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, X[0], ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
+                               s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, s->xsq, 1, nullptr, st, pdl);
+        else
+            e = launch_gemv_tp(consumer(1, l - 1), qt_of(ly.qkv.type), GEMV_IN_TPNORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, ly.attn_norm, c.rms_eps,
+                               c.norm_plus_one, nullptr, s->qkv, ly.qkv_bias, 0, nullptr, nullptr, nullptr, st, pdl);
+        n++;
+        if (e != cudaSuccess) break;
+        e = launch_attn_fused(s->qkv, m->heads(), m->kv_heads(), hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
+                              s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, attn_ctx, st, pdl); n++;
+        if (e != cudaSuccess) break;
+        e = launch_gemv_tp(producer(0), qt_of(ly.o.type), GEMV_IN_ACT, GEMV_OUT_TPPART, ly.o.packed, H, qd, nullptr, 0.f, 0, s->act_attn, nullptr, nullptr, 0,
+                           nullptr, nullptr, nullptr, st, pdl); n++;
+        if (e != cudaSuccess) break;
+        e = launch_gemv_tp(consumer(0, l), qt_of(ly.gateup.type), GEMV_IN_TPNORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, ly.ffn_norm, c.rms_eps,
+                           c.norm_plus_one, nullptr, s->h, nullptr, c.act, nullptr, nullptr, nullptr, st, pdl); n++;
+        if (e != cudaSuccess) break;
+        e = launch_gemv_tp(producer(1), qt_of(ly.down.type), GEMV_IN_F32, GEMV_OUT_TPPART, ly.down.packed, H, I, nullptr, 0.f, 0, s->h, nullptr, nullptr, 0,
+                           nullptr, nullptr, nullptr, st, pdl); n++;
+    }
+    if (e == cudaSuccess && with_head) {
+        e = launch_gemv_tp(consumer(1, c.n_layers - 1), qt_of(m->head.type), GEMV_IN_TPNORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, m->out_norm, c.rms_eps,
+                           c.norm_plus_one, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, &s->head_grid, st, pdl); n++;
+    }
+    if (e != cudaSuccess) { s->enqueue_error = e; return n; }
+    // a pass without the LM head still has to see the last round complete before the next pass reuses the slots
+    launch_tp_close(L.arrivals(rk, 1), N, L.forwards(), rounds, c.n_layers - 1, per_round, !with_head, L.error(), st); n++;
+    return n;
+}
+
 // enqueue one forward pass for the token in state->cur_token at position state->pos; returns #launches
 static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
+    if (s->m->tp > 1) return enqueue_forward_tp(s, with_head, attn_ctx);
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
     const bool pdl = s->use_pdl;
-    int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
+    int H = c.hidden, I = m->ffn(), qd = m->q_dim(), hd = c.head_dim;
     int n = 0;
     auto bytes_of = [](const Mat &mt) { return packed_bytes_of(mt.type, mt.rows, mt.cols); };
     float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
     launch_embed_row(qt_of(m->embd.type), m->embd.packed, m->embd.cols, &s->state->cur_token, escale, s->x, s->xsq, st); n++;
     int xsq_n = 1;   // how many partial sums of squares the producer of the current x left in s->xsq
-    uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
         LayerW &ly = m->layers[l];
         int g = 0;
@@ -554,12 +727,12 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
                         s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, ly.o.packed, bytes_of(ly.o), s->xsq, xsq_n, nullptr, st, pdl); n++;
         }
         if (s->fused_attn) {
-            launch_attn_fused(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
+            launch_attn_fused(s->qkv, m->heads(), m->kv_heads(), hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
                               s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, attn_ctx, st, pdl); n++;
         } else {
-            launch_rope_kv(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
+            launch_rope_kv(s->qkv, m->heads(), m->kv_heads(), hd, &s->state->pos, 0, m->rope_cos, m->rope_sin,
                            s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, st); n++;
-            launch_attn_decode(s->qkv, c.n_heads, c.n_kv_heads, hd, &s->state->pos, 0, s->kcache + l * layer_kv, s->vcache + l * layer_kv,
+            launch_attn_decode(s->qkv, m->heads(), m->kv_heads(), hd, &s->state->pos, 0, s->kcache + l * layer_kv, s->vcache + l * layer_kv,
                                s->page_table, s->attn_out, s->attn_scratch, s->max_ctx, st); n++;
             launch_quant_act(s->attn_out, qd, s->act_attn, st); n++;
         }
@@ -631,12 +804,14 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
         if (!s->use_graphs) {
             s->graph_launches[which][v] = enqueue_graph_body(s, which, v);
             B2_CUDA(cudaGetLastError());
+            B2_CUDA(s->enqueue_error);
         } else {
             if (!s->graphs[which][v]) {
                 cudaGraph_t g = nullptr;
                 B2_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
                 s->graph_launches[which][v] = enqueue_graph_body(s, which, v);
                 cudaError_t e1 = cudaStreamEndCapture(st, &g);
+                if (e1 == cudaSuccess && s->enqueue_error != cudaSuccess) { e1 = s->enqueue_error; cudaGraphDestroy(g); }
                 if (e1 != cudaSuccess) { b2_set_error("graph capture failed: %s", cudaGetErrorString(e1)); return B2_ECUDA; }
                 cudaError_t e2 = cudaGraphInstantiate(&s->graphs[which][v], g, 0);
                 cudaGraphDestroy(g);
@@ -656,7 +831,7 @@ static bool build_mega_plan(b2_session *s) {
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     if (c.n_layers > MEGA_MAX_LAYERS || !s->fused_attn || !m->all_q4_0) return false;
-    const int H = c.hidden, I = c.ffn, qd = m->q_dim(), hd = c.head_dim;
+    const int H = c.hidden, I = m->ffn(), qd = m->q_dim(), hd = c.head_dim;
     MegaPlan *P = new MegaPlan();
     memset(P, 0, sizeof *P);
     size_t smem = 0, sm1 = 0;
@@ -681,22 +856,22 @@ static bool build_mega_plan(b2_session *s) {
     mk(P->head, GEMV_IN_NORM, m->head, s->x, m->out_norm, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, s->xsq, nullptr);
     const size_t attn_smem = GEMV_FIXED_SMEM(GEMV_RB_MAX) + (size_t)4 * attn_group_floats(hd, pps_max) * 4;
     if (attn_smem > smem) smem = attn_smem;
-    if (c.n_heads * ATTN_NSPLIT > 4 * grid || grid > 512 || (H % QK) != 0) ok = false;   // one attention item per 128-thread group; xsq halves hold 512 partials
+    if (m->heads() * ATTN_NSPLIT > 4 * grid || grid > 512 || (H % QK) != 0) ok = false;   // one attention item per 128-thread group; xsq halves hold 512 partials
     int g2 = 0;
     if (ok && mega_grid(smem, &g2) != cudaSuccess) { ok = false; cudaGetLastError(); }
     if (ok && g2 != grid) ok = false;
     if (!ok) { delete P; return false; }
     AttnArgs &A = P->attn;
-    A.qkv = s->qkv; A.nh = c.n_heads; A.nkv = c.n_kv_heads; A.hd = hd; A.d_pos = nullptr; A.pos_imm = 0;
+    A.qkv = s->qkv; A.nh = m->heads(); A.nkv = m->kv_heads(); A.hd = hd; A.d_pos = nullptr; A.pos_imm = 0;
     A.cs = m->rope_cos; A.sn = m->rope_sin; A.kc = s->kcache; A.vc = s->vcache; A.page_table = s->page_table;
     A.out = nullptr; A.act_out = (uint8_t *)s->act_attn; A.pps_max = pps_max;
     A.g_part = (float *)s->attn_scratch;
-    A.g_cnt = (int *)((float *)s->attn_scratch + (size_t)c.n_heads * ATTN_NSPLIT * (hd + 2));
+    A.g_cnt = (int *)((float *)s->attn_scratch + (size_t)m->heads() * ATTN_NSPLIT * (hd + 2));
     P->n_layers = c.n_layers; P->n_embd = H; P->vocab = c.vocab; P->n_part = grid;
     P->embd_w = (const uint8_t *)m->embd.packed; P->embd_nbp = (int)nblocks_padded(m->embd.cols);
     P->embd_scale = c.embed_scale ? sqrtf((float)H) : 1.0f;
     P->x = s->x; P->xsq = s->xsq; P->logits = s->logits; P->pmax = s->pmax; P->pidx = s->pidx;
-    const uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    const uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
     for (int l = 0; l < c.n_layers; ++l) {
         const LayerW &ly = m->layers[l];
         MegaLayer &L = P->layers[l];
@@ -742,8 +917,14 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     s->fused_attn = !(nf && nf[0] == '1');
     const char *npg = getenv("B2_NO_PREFILL_GEMM");
     s->use_pf_gemm = !(npg && npg[0] == '1');
-    int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
-    uint64_t kv_elems = (uint64_t)c.n_layers * s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    if (m->tp > 1) {   // the tensor-parallel pass exists for the per-stage decode kernels: prompts go through it token by token
+        s->use_pf_gemm = false;
+        s->fused_attn = true;
+        for (const LayerW &ly : m->layers)
+            if (ly.split_qkv) { delete s; b2_set_error("tensor parallel sessions need q, k and v of a layer in one format"); return B2_EINVAL; }
+    }
+    int H = c.hidden, I = m->ffn(), qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim;
+    uint64_t kv_elems = (uint64_t)c.n_layers * s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
     int rc = B2_OK;
     do {
         if ((rc = dev_alloc(s->allocs, (void **)&s->kcache, kv_elems * 2))) break;
@@ -755,7 +936,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_prompt, s->prompt_cap * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_out_tokens, s->out_cap * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_sampled, 4))) break;
-        if ((rc = dev_alloc(s->allocs, (void **)&s->x, H * 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->x, H * 4 * 2))) break;   // tensor parallel: the residual alternates between the halves
         if ((rc = dev_alloc(s->allocs, (void **)&s->qkv, (qd + 2 * kvd) * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->attn_out, qd * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->h, I * 4))) break;
@@ -765,7 +946,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->pmax, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->pidx, 1024 * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->xsq, 1024 * 4))) break;
-        if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(c.n_heads, hd)))) break;
+        if ((rc = dev_alloc(s->allocs, &s->attn_scratch, attn_scratch_bytes(m->heads(), hd)))) break;
         if ((rc = dev_alloc(s->allocs, &s->argmax_scratch, argmax_scratch_bytes()))) break;
         if ((rc = dev_alloc(s->allocs, &s->sample_scratch, sample_scratch_bytes(SAMPLE_MAX_K)))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_u, 16))) break;
@@ -789,7 +970,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     // cache slots beyond the current position are read (and masked) by the tiled prompt attention: they must hold finite values
     if (e == cudaSuccess) e = cudaMemset(s->kcache, 0, kv_elems * 2);
     if (e == cudaSuccess) e = cudaMemset(s->vcache, 0, kv_elems * 2);
-    if (e == cudaSuccess) e = cudaMemset(s->attn_scratch, 0, attn_scratch_bytes(c.n_heads, hd));
+    if (e == cudaSuccess) e = cudaMemset(s->attn_scratch, 0, attn_scratch_bytes(m->heads(), hd));
     if (e == cudaSuccess) e = cudaMemset(s->argmax_scratch, 0, argmax_scratch_bytes());
     if (e == cudaSuccess) e = cudaMemset(s->sample_scratch, 0, sample_scratch_bytes(SAMPLE_MAX_K));
     if (e == cudaSuccess) e = cudaMemset(s->d_draw, 0, 16);
@@ -804,7 +985,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         return B2_ECUDA;
     }
     const char *mg = getenv("B2_MEGA");
-    if (mg && mg[0] == '1') s->use_mega = build_mega_plan(s);
+    if (mg && mg[0] == '1' && m->tp == 1) s->use_mega = build_mega_plan(s);
     *out = s;
     return B2_OK;
 }
@@ -874,6 +1055,15 @@ static int set_step_counters(b2_session *s) {   // step = 0, prompt_idx = 0, kee
     return B2_OK;
 }
 
+// tensor-parallel sessions: a rank that waited in vain for a peer left a mark instead of hanging
+static int tp_check(b2_session *s) {
+    if (s->m->tp == 1) return B2_OK;
+    unsigned int err = 0;
+    B2_CUDA(cudaMemcpy(&err, s->m->e->tp.error(), 4, cudaMemcpyDeviceToHost));
+    B2_CHECK(err == 0, B2_ENCCL, "tensor parallel exchange: rank %u did not arrive within 2 s (every rank must make the same calls with the same arguments)", err - 1);
+    return B2_OK;
+}
+
 static int elapsed_ns(b2_session *s, uint64_t *ns) {
     float ms = 0.f;
     B2_CUDA(cudaEventSynchronize(s->ev1));
@@ -890,10 +1080,10 @@ static int prefill_batched(b2_session *s, int n) {
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
-    const int H = c.hidden, I = c.ffn, qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim, sms = m->e->sm_count;
+    const int H = c.hidden, I = m->ffn(), qd = m->q_dim(), kvd = m->kv_dim(), hd = c.head_dim, sms = m->e->sm_count;
     const int64_t ldq = qd + 2 * kvd;
     const float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
-    const uint64_t layer_kv = (uint64_t)s->n_pages * c.n_kv_heads * PAGE_TOKENS * hd;
+    const uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
     int launches = 0;
     for (int m0 = 0; m0 < n; m0 += 64) {
         const int mb = n - m0 < 64 ? n - m0 : 64, T = pf_batch(mb), pos0 = s->host_pos + m0;
@@ -902,7 +1092,7 @@ static int prefill_batched(b2_session *s, int n) {
             LayerW &ly = m->layers[l];
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.attn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
             B2_CUDA(launch_prefill_gemm_qt(ly.qkv.type == B2_T_Q4_K, PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, s->pf_part, s->pf_part_floats, st));
-            B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, c.n_heads, c.n_kv_heads, hd, pos0, m->rope_cos, m->rope_sin,
+            B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, m->heads(), m->kv_heads(), hd, pos0, m->rope_cos, m->rope_sin,
                                              s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, s->pf_attn, qd, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_attn, qd, mb, T, qd, nullptr, 0.f, 0, s->pf_pb, st));
             B2_CUDA(launch_prefill_gemm_qt(ly.o.type == B2_T_Q4_K, PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
@@ -950,6 +1140,7 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaEventRecord(s->ev1, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits, (size_t)V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
+    B2_TRY(tp_check(s));
     uint64_t ns = 0;
     B2_TRY(elapsed_ns(s, &ns));
     s->stats.prompt_eval_count += n;
@@ -996,6 +1187,7 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
     B2_CUDA(cudaMemcpyAsync(out_tokens, s->d_out_tokens, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n_steps * V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
+    B2_TRY(tp_check(s));
     uint64_t ns = 0;
     B2_TRY(elapsed_ns(s, &ns));
     s->stats.eval_count += n_steps;
@@ -1020,6 +1212,7 @@ extern "C" int b2_forward_tokens(b2_session *s, const int32_t *tokens, int n, fl
     else B2_TRY(run_graph(s, G_FORCED, n, s->host_pos));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n * V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
+    B2_TRY(tp_check(s));
     s->host_pos += n;
     s->have_logits = true;
     return B2_OK;

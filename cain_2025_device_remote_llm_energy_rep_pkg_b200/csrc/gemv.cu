@@ -12,18 +12,18 @@
 // x 3 digit planes of exact integer dot products each), scale by d_w * 2^e / 16 into fp32 accumulators.
 // The sixteen warps split K and meet in shared memory once per tile.  Measured alone (tools/microbench3.cu)
 // this structure streams 6.3-6.8 TB/s from HBM with the arithmetic included.
-#include "gemv_dev.cuh"
+#include "gemv_launch.cuh"
 #include "randinit.cuh"
 #include <stdlib.h>
 
 // ------------------------------------------------------------------------------------------ pack / init
 // GGML Q4_0 row-major blocks (18 B: f16 d | 16 B nibbles) -> streaming layout (layout.cuh). One thread per block.
 __global__ void k_pack_q4_0(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
-                            int64_t dst_row0, int64_t dst_row_stride) {
+                            int64_t dst_row0, int64_t dst_row_stride, int64_t snb, int64_t sb0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * nb) return;
     int64_t r = i / nb, b = i - r * nb;
-    const uint8_t *p = src + i * 18;
+    const uint8_t *p = src + (r * snb + sb0 + b) * 18;
     PackedLoc loc = packed_loc(dst_row0 + r * dst_row_stride, b, nbp);
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
@@ -32,20 +32,22 @@ __global__ void k_pack_q4_0(const uint8_t *__restrict__ src, int64_t rows, int64
     }
     *(uint16_t *)(dst + loc.scale) = (uint16_t)p[0] | ((uint16_t)p[1] << 8);
 }
-void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                      int64_t src_cols, int64_t src_col0) {
     int64_t nb = cols / QK, n = rows * nb;
-    k_pack_q4_0<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+    const int64_t snb = src_cols ? src_cols / QK : nb, sb0 = src_col0 / QK;   // the source rows are snb blocks long; take blocks [sb0, sb0 + nb)
+    k_pack_q4_0<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride, snb, sb0);
 }
 // GGML Q4_K row-major super-blocks (144 B: f16 d | f16 dmin | 12 B packed 6-bit scales/mins | 128 B nibbles) -> streaming
 // layout (layout.cuh).  One thread per 32-element sub-block.  ggml: sub-blocks 2p and 2p+1 share the bytes qs[32p..32p+31]
 // (low / high nibbles); scale and min of sub-block j follow get_scale_min_k4.
 __global__ void k_pack_q4_k(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
-                            int64_t dst_row0, int64_t dst_row_stride) {
+                            int64_t dst_row0, int64_t dst_row_stride, int64_t snb, int64_t sb0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * nb) return;
     const int64_t r = i / nb, b = i - r * nb;
-    const int j = (int)(b & 7);
-    const uint8_t *p = src + (r * (nb >> 3) + (b >> 3)) * 144;
+    const int j = (int)(b & 7);   // sb0 is a multiple of 8: a column window starts on a super-block
+    const uint8_t *p = src + (r * (snb >> 3) + ((sb0 + b) >> 3)) * 144;
     const uint8_t *q = p + 4, *qs = p + 16 + 32 * (j >> 1);
     uint8_t sc, m;
     if (j < 4) { sc = q[j] & 63; m = q[j + 4] & 63; }
@@ -67,20 +69,22 @@ __global__ void k_pack_q4_k(const uint8_t *__restrict__ src, int64_t rows, int64
     dst[loc.scm + 1] = m;
     *(uint32_t *)(dst + loc.dm) = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);   // every sub-block writes the same value
 }
-void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                      int64_t src_cols, int64_t src_col0) {
     int64_t nb = cols / QK, n = rows * nb;
-    k_pack_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+    const int64_t snb = src_cols ? src_cols / QK : nb, sb0 = src_col0 / QK;   // the source rows are snb blocks long; take blocks [sb0, sb0 + nb)
+    k_pack_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride, snb, sb0);
 }
 // GGML Q6_K row-major super-blocks (210 B: ql[128] | qh[64] | int8 scales[16] | f16 d) -> streaming layout (layout.cuh).
 // One thread per 32-element block jb of a super-block: jb = 4n + k covers elements l = 0..31 of ggml's group (n, k):
 // low nibble from ql[64n + 32(k&1) + l] (low half for k < 2, high half otherwise), high bits from (qh[32n + l] >> 2k) & 3.
 __global__ void k_pack_q6_k(const uint8_t *__restrict__ src, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
-                            int64_t dst_row0, int64_t dst_row_stride) {
+                            int64_t dst_row0, int64_t dst_row_stride, int64_t snb, int64_t sb0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * nb) return;
     const int64_t r = i / nb, b = i - r * nb;
     const int jb = (int)(b & 7), n = jb >> 2, k = jb & 3;
-    const uint8_t *p = src + (r * (nb >> 3) + (b >> 3)) * 210;
+    const uint8_t *p = src + (r * (snb >> 3) + ((sb0 + b) >> 3)) * 210;
     const uint8_t *ql = p + 64 * n + 32 * (k & 1), *qh = p + 128 + 32 * n;
     const int lsh = (k >> 1) * 4, hsh = 2 * k;
     PackedLoc6 loc = packed_loc_6(dst_row0 + r * dst_row_stride, b, nbp);
@@ -102,18 +106,20 @@ __global__ void k_pack_q6_k(const uint8_t *__restrict__ src, int64_t rows, int64
     dst[loc.sc + 1] = p[192 + 2 * jb + 1];
     *(uint16_t *)(dst + loc.d) = (uint16_t)p[208] | ((uint16_t)p[209] << 8);
 }
-void launch_pack_q6_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+void launch_pack_q6_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                      int64_t src_cols, int64_t src_col0) {
     int64_t nb = cols / QK, n = rows * nb;
-    k_pack_q6_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+    const int64_t snb = src_cols ? src_cols / QK : nb, sb0 = src_col0 / QK;   // the source rows are snb blocks long; take blocks [sb0, sb0 + nb)
+    k_pack_q6_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uint8_t *)d_src, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride, snb, sb0);
 }
 // Deterministic random init straight into the streaming layout; same bytes as b2_randinit_tensor + pack.
 __global__ void k_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst,
-                                int64_t dst_row0, int64_t dst_row_stride) {
+                                int64_t dst_row0, int64_t dst_row_stride, int64_t sr0, int64_t snb, int64_t sb0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * nb) return;
     int64_t r = i / nb, b = i - r * nb;
     float x[QK];
-    ri_gauss_block(key, (uint64_t)i * QK, sigma, x);
+    ri_gauss_block(key, (uint64_t)((sr0 + r) * snb + sb0 + b) * QK, sigma, x);   // block (sr0 + r, sb0 + b) of the whole tensor
     uint16_t dbits;
     uint32_t w[4];
     ri_quant_q4_0(x, dbits, w);
@@ -122,23 +128,28 @@ __global__ void k_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t
     for (int t = 0; t < 4; ++t) *(uint32_t *)(dst + loc.word0 + t * 16) = w[t] ^ 0x88888888u;
     *(uint16_t *)(dst + loc.scale) = dbits;
 }
-void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                          int64_t src_row0, int64_t src_cols, int64_t src_col0) {
     int64_t nb = cols / QK, n = rows * nb;
-    k_randinit_q4_0<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, sigma, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+    k_randinit_q4_0<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(key, sigma, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride,
+                                                                 src_row0, src_cols ? src_cols / QK : nb, src_col0 / QK);
 }
 // Synthetic Q4_K blocks straight into the streaming layout (benchmarks of SURVEY.md 8d config 4; no checkpoint exists offline
 // and ggml's Q4_K search quantiser is not worth running over 8 G weights): per super-block d = f16(9e-5 * (0.75 + u/2)),
 // dmin = 8 d; per sub-block sc in [32, 63], m = round(7.5 sc / 8) so that d*sc*q - dmin*m is centred; nibbles from the hash.
 // The dequantised weights have mean ~0 and standard deviation ~0.02 like the Q4_0 initialiser's.
-__global__ void k_randinit_q4_k(uint64_t key, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst, int64_t dst_row0, int64_t dst_row_stride) {
+__global__ void k_randinit_q4_k(uint64_t key, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst, int64_t dst_row0, int64_t dst_row_stride,
+                                int64_t sr0, int64_t snb, int64_t sb0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * nb) return;
     const int64_t r = i / nb, b = i - r * nb;
-    const uint64_t hs = ri_splitmix64(key ^ (0x5bd1e995ull * (uint64_t)(r * (nb >> 3) + (b >> 3) + 1)));   // per super-block
+    const int64_t fr = sr0 + r, fb = sb0 + b;   // coordinates in the whole tensor (a rank of a tensor-parallel model fills its window)
+    i = fr * snb + fb;
+    const uint64_t hs = ri_splitmix64(key ^ (0x5bd1e995ull * (uint64_t)(fr * (snb >> 3) + (fb >> 3) + 1)));   // per super-block
     const uint64_t h0 = ri_splitmix64(key + 2 * (uint64_t)i), h1 = ri_splitmix64(key + 2 * (uint64_t)i + 1);
     const float d = 9e-5f * (0.75f + 0.5f * (float)(hs & 0xFFFF) * (1.0f / 65536.0f));
     const __half dh = __float2half_rn(d), dmh = __float2half_rn(8.0f * __half2float(dh));
-    const uint32_t sc = 32u + (uint32_t)((hs >> (16 + 5 * (b & 7))) & 31u), mn = (15u * sc + 8u) >> 4;
+    const uint32_t sc = 32u + (uint32_t)((hs >> (16 + 5 * (fb & 7))) & 31u), mn = (15u * sc + 8u) >> 4;
     PackedLocK loc = packed_loc_k(dst_row0 + r * dst_row_stride, b, nbp);
     *(uint32_t *)(dst + loc.word0) = (uint32_t)h0;
     *(uint32_t *)(dst + loc.word0 + 16) = (uint32_t)(h0 >> 32);
@@ -148,17 +159,22 @@ __global__ void k_randinit_q4_k(uint64_t key, int64_t rows, int64_t nb, int64_t 
     dst[loc.scm + 1] = (uint8_t)mn;
     *(__half2 *)(dst + loc.dm) = __halves2half2(dh, dmh);
 }
-void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                          int64_t src_row0, int64_t src_cols, int64_t src_col0) {
     int64_t nb = cols / QK, n = rows * nb;
-    k_randinit_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+    k_randinit_q4_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride,
+                                                                 src_row0, src_cols ? src_cols / QK : nb, src_col0 / QK);
 }
 // Synthetic Q6_K blocks (benchmarks with a Q6_K LM head, as in llama.cpp's "Q4_0" files): random 6-bit values, int8 scales in
 // [32, 127], d ~ 1.35e-5 so that d*sc*(q-32) has standard deviation ~0.02.
-__global__ void k_randinit_q6_k(uint64_t key, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst, int64_t dst_row0, int64_t dst_row_stride) {
+__global__ void k_randinit_q6_k(uint64_t key, int64_t rows, int64_t nb, int64_t nbp, uint8_t *__restrict__ dst, int64_t dst_row0, int64_t dst_row_stride,
+                                int64_t sr0, int64_t snb, int64_t sb0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rows * nb) return;
     const int64_t r = i / nb, b = i - r * nb;
-    const uint64_t hs = ri_splitmix64(key ^ (0x5bd1e995ull * (uint64_t)(r * (nb >> 3) + (b >> 3) + 1)));   // per super-block
+    const int64_t fr = sr0 + r, fb = sb0 + b;   // coordinates in the whole tensor (a rank of a tensor-parallel model fills its window)
+    i = fr * snb + fb;
+    const uint64_t hs = ri_splitmix64(key ^ (0x5bd1e995ull * (uint64_t)(fr * (snb >> 3) + (fb >> 3) + 1)));   // per super-block
     const uint64_t h0 = ri_splitmix64(key + 3 * (uint64_t)i), h1 = ri_splitmix64(key + 3 * (uint64_t)i + 1), h2 = ri_splitmix64(key + 3 * (uint64_t)i + 2);
     const float d = 1.35e-5f * (0.75f + 0.5f * (float)(hs & 0xFFFF) * (1.0f / 65536.0f));
     PackedLoc6 loc = packed_loc_6(dst_row0 + r * dst_row_stride, b, nbp);
@@ -168,30 +184,23 @@ __global__ void k_randinit_q6_k(uint64_t key, int64_t rows, int64_t nb, int64_t 
     *(uint32_t *)(dst + loc.word0 + 48) = (uint32_t)(h1 >> 32);
 #pragma unroll
     for (int t = 0; t < 4; ++t) *(uint16_t *)(dst + loc.hi + t * 16) = (uint16_t)(h2 >> (16 * t));
-    dst[loc.sc] = (uint8_t)(32u + (uint32_t)((hs >> 16) & 63u) + (uint32_t)((hs >> (22 + 4 * (b & 7))) & 31u));
-    dst[loc.sc + 1] = (uint8_t)(32u + (uint32_t)((hs >> 19) & 63u) + (uint32_t)((hs >> (24 + 4 * (b & 7))) & 31u));
+    dst[loc.sc] = (uint8_t)(32u + (uint32_t)((hs >> 16) & 63u) + (uint32_t)((hs >> (22 + 4 * (fb & 7))) & 31u));
+    dst[loc.sc + 1] = (uint8_t)(32u + (uint32_t)((hs >> 19) & 63u) + (uint32_t)((hs >> (24 + 4 * (fb & 7))) & 31u));
     *(__half *)(dst + loc.d) = __float2half_rn(d);
 }
-void launch_randinit_q6_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st) {
+void launch_randinit_q6_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                          int64_t src_row0, int64_t src_cols, int64_t src_col0) {
     int64_t nb = cols / QK, n = rows * nb;
-    k_randinit_q6_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride);
+    k_randinit_q6_k<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, rows, nb, nblocks_padded(cols), (uint8_t *)d_packed, dst_row0, dst_row_stride,
+                                                                 src_row0, src_cols ? src_cols / QK : nb, src_col0 / QK);
 }
-__global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *__restrict__ out) {
+__global__ void k_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *__restrict__ out, int64_t i0) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = ri_add(ri_mul(ri_gauss(key, (uint64_t)i), sigma), offset);
+    if (i < n) out[i] = ri_add(ri_mul(ri_gauss(key, (uint64_t)(i0 + i)), sigma), offset);
 }
-void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st) {
-    k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out);
+void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st, int64_t i0) {
+    k_randinit_f32<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(key, sigma, offset, n, d_out, i0);
 }
-// ------------------------------------------------------------------------------------------ the kernel
-template <int IN, int OUT, int PATH, int QT>
-__global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const GemvArgs a) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint32_t parity = 0;
-    const GemvPtrs pv = {a.w, a.norm_w, a.bias_or_res};
-    gemv_phase<IN, OUT, false, PATH, QT>(a, pv, smem, parity);
-}
-
 // ------------------------------------------------------------------------------------------ launcher
 static int g_num_sms = 0;
 static long long *g_gemv_dbg = nullptr;   // set by b2dbg_gemv_profile (development aid): ring of `slots` x [148][8] stamps
@@ -207,39 +216,6 @@ int gemv_grid(int n_tiles, int tile_align) {
     }
     int units = (n_tiles + tile_align - 1) / tile_align;
     return units < g_num_sms ? units : g_num_sms;
-}
-
-template <int IN, int OUT, int PATH, int QT>
-static cudaError_t launch_path(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT, PATH, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(GEMV_THREADS);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, k_gemv<IN, OUT, PATH, QT>, a);
-}
-template <int IN, int OUT, int QT>
-static cudaError_t launch_qt(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
-    const int cpt = (a.nbp + KC - 1) / KC;
-    if (a.k_outer) return launch_path<IN, OUT, 2, QT>(a, grid, smem, st, pdl);
-    if (cpt == 2) return launch_path<IN, OUT, 0, QT>(a, grid, smem, st, pdl);
-    return launch_path<IN, OUT, 1, QT>(a, grid, smem, st, pdl);
-}
-template <int IN, int OUT>
-static cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
-    if (a.qt == 2) return launch_qt<IN, OUT, 2>(a, grid, smem, st, pdl);
-    return a.qt ? launch_qt<IN, OUT, 1>(a, grid, smem, st, pdl) : launch_qt<IN, OUT, 0>(a, grid, smem, st, pdl);
 }
 
 // Fill the argument block of one GEMV (everything but the debug pointer) and report the dynamic shared memory it needs.

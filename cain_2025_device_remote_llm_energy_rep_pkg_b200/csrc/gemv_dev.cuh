@@ -119,8 +119,39 @@ struct GemvPtrs {
     const float *norm_w;
     const float *bias_or_res;
 };
-enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2 };
-enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3 };
+struct GemvArgsTp : GemvArgs {
+    // ---- tensor-parallel decode (engine.cu: TpLink; one process per GPU, exchange buffers mapped into each other over NVLink).
+    // OUT_TPPART: this rank multiplied its share of K, so its rows are partial sums.  They are stored into slot [tp_rank] of
+    // EVERY rank's exchange buffer (tp_dst[p]: peer memory, plain stores), then each CTA adds 1 to every rank's arrival counter
+    // tp_sig[p].  IN_TPNORM: the consumer on each rank waits until its tp_n local counters reach the value of this round, copies
+    // the residual and the tp_n slots into shared memory (its own memory only) and forms x = res + slot_0 + ... + slot_{n-1} in
+    // that order on every rank, so all ranks hold bit-identical x; CTA 0 also writes x to tp_xout.  The all-reduce is the pair
+    // (epilogue of one GEMV, prologue of the next): no kernel of its own.
+    float *tp_dst[8];
+    unsigned long long *tp_sig[8];
+    int tp_n;
+    const float *tp_res;                 // residual stream before the exchange (n_in floats)
+    const float *tp_slots;               // local exchange buffer of this round: slot r at r * tp_slot_stride floats
+    int tp_slot_stride;
+    const unsigned long long *tp_cnt;    // local arrival counters of this buffer, one per source rank (never reset)
+    const unsigned long long *tp_fwd;    // forward passes completed so far on this engine (device counter)
+    int tp_round, tp_rounds, tp_per_round;   // counter value of this round = tp_per_round * (*tp_fwd * tp_rounds + tp_round + 1)
+    float *tp_xout;
+    unsigned int *tp_err;                // set to 1 + rank when a peer did not arrive within TP_TIMEOUT_NS (no hang: the caller reports it)
+};
+enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2, IN_TPNORM = 3 };
+enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3, OUT_TPPART = 4 };
+#define TP_TIMEOUT_NS 2000000000ll
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ long long global_timer_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 // host side (gemv.cu): fill the argument block of one GEMV and report its dynamic shared memory
 cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64_t rows, int64_t cols, const float *x, const float *norm_w,
@@ -345,9 +376,9 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
 // for the block maximum) and writes its own block-groups of the shared-memory activation image.
 // Shared memory of the input area: [A3 image nbp*100][staging: fp32 vector n_in*4][xsq partials 1 KB]
 // Q4_K adds float ts[nbp] after the scales: ts[b] = sum of the gridded activations of block b (staging area moves up by nbp*4).
-template <int IN, int QT>
-__device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPtrs &pv, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
-                                                 const float4 (&wn)[2]) {
+template <int IN, int QT, class A>
+__device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
+                                                 const float4 (&wn)[2], float *scratch) {
     constexpr int A3S = 100 + 4 * QT;   // Q4_K: one block sum per block after the scales, Q6_K: two half-block sums
     float *sts = (float *)(sact + (size_t)a.nbp * 100);
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
@@ -377,6 +408,37 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
     mbar_wait(bar, parity);
     prof_stamp(6);
     float r = 1.0f;
+    if constexpr (IN == IN_TPNORM) {
+        // x = res + slot_0 + ... : this warp's columns, in place; the sum of squares needs every warp's share
+        float4 *sx4 = (float4 *)(sact + (size_t)a.nbp * A3S);
+        const float4 *sl4 = (const float4 *)(sx + a.n_in + 256);   // the slots follow the (unused) partials area
+        const int n4s = a.n_in >> 2;
+        float ss = 0.f;
+        for (int ck = 0; ck < cpt; ++ck) {
+            const int kbg = ck * (KC / 4) + warp;
+            if (kbg * 4 >= a.nbp) break;
+            const int q = kbg * 32 + lane;
+            if (q < n4s) {
+                float4 v = sx4[q];
+#pragma unroll
+                for (int p = 0; p < 8; ++p)
+                    if (p < a.tp_n) {
+                        const float4 u = sl4[(size_t)p * n4s + q];
+                        v.x = __fadd_rn(v.x, u.x); v.y = __fadd_rn(v.y, u.y); v.z = __fadd_rn(v.z, u.z); v.w = __fadd_rn(v.w, u.w);
+                    }
+                sx4[q] = v;
+                if (blockIdx.x == 0) __stcg((float4 *)a.tp_xout + q, v);
+                ss = fmaf(v.x, v.x, ss); ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
+            }
+        }
+        ss = warp_sum(ss);
+        if (lane == 0) scratch[warp] = ss;
+        __syncthreads();
+        float tot = 0.f;
+#pragma unroll
+        for (int w8 = 0; w8 < GEMV_CWARPS; ++w8) tot += scratch[w8];
+        r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, (float)a.n_in), a.eps)));
+    }
     if (IN == IN_NORM) {
         float ss = 0.f;
         for (int i = lane; i < a.xsq_n; i += 32) ss += sq[i];
@@ -391,7 +453,7 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
         float yv[4] = {0.f, 0.f, 0.f, 0.f};
         if (q < n4) {
             const float4 v = ((const float4 *)sx)[q];
-            if (IN == IN_NORM) {
+            if (IN == IN_NORM || IN == IN_TPNORM) {
                 const float4 w = ck < 2 ? wn[ck] : __ldg((const float4 *)pv.norm_w + q);
                 const float xs[4] = {v.x, v.y, v.z, v.w}, ws[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
@@ -443,8 +505,23 @@ __device__ __forceinline__ void stage_warp_input(const GemvArgs &a, const GemvPt
 // Every warp parked its K-partial of the 16 rows x 3 digit planes; warp w finalises tile batch_first + w.
 // Two CTA-wide barriers per a.rb tiles instead of one per tile: the weight streams of the sixteen warps are not
 // re-synchronised on memory latency every other piece.
+// What the epilogue needs from the argument block, by value: a reference to the kernel parameter would force the whole block
+// into local memory of every thread (this function is not inlined).
+template <bool TP> struct FlushArgs { float *y; int rows, act; };
+template <> struct FlushArgs<true> { float *y; int rows, act; float *tp_dst[8]; int tp_n; };
+template <int OUT, class A>
+__device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A &a) {
+    FlushArgs<OUT == OUT_TPPART> f;
+    f.y = a.y; f.rows = a.rows; f.act = a.act;
+    if constexpr (OUT == OUT_TPPART) {
+#pragma unroll
+        for (int p = 0; p < 8; ++p) f.tp_dst[p] = a.tp_dst[p];
+        f.tp_n = a.tp_n;
+    }
+    return f;
+}
 template <int OUT, int QT>
-__device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or_res, float *red, int batch_first, int batch_n, float &best_v, int &best_i,
+__device__ __noinline__ void flush_batch(const FlushArgs<OUT == OUT_TPPART> a, const float *bias_or_res, float *red, int batch_first, int batch_n, float &best_v, int &best_i,
                                          float &sumsq) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __syncthreads();
@@ -476,6 +553,12 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
                 a.y[row] = xn;
                 sumsq = fmaf(xn, xn, sumsq);
             }
+        } else if constexpr (OUT == OUT_TPPART) {
+            if (lane < 16 && row < a.rows) {   // this rank's partial sum into its slot on every rank (16 lanes = 64 contiguous bytes per rank)
+#pragma unroll
+                for (int p = 0; p < 8; ++p)
+                    if (p < a.tp_n) a.tp_dst[p][row] = yv;
+            }
         } else if (OUT == OUT_LOGITS) {
             if (lane < 16 && row < a.rows) {
                 a.y[row] = yv;
@@ -498,8 +581,8 @@ __device__ __noinline__ void flush_batch(const GemvArgs &a, const float *bias_or
 //       0 / 1 / 2 = only tiles-outermost with two chunks per tile / with one chunk / chunks-outermost.  The stand-alone
 //       kernels are instantiated per path: a third of the code per kernel means fewer instruction-cache misses at every
 //       kernel start (no_instructions was 4-13 % of the warp samples of these 10-30 us kernels).
-template <int IN, int OUT, bool MEGA, int PATH = -1, int QT = 0>
-__device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
+template <int IN, int OUT, bool MEGA, int PATH = -1, int QT = 0, class A = GemvArgs>
+__device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
     float *scratch = (float *)smem;                                             // 64 floats
     uint64_t *bar = (uint64_t *)(smem + 256);                                   // completion of the input copies
     float *red = (float *)(smem + GEMV_HDR_SMEM);                               // [rb tiles][16 warps][16 rows][4]
@@ -568,7 +651,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     // Wait for the producer of the input vector and start its copy into shared memory (thread 0, cp.async.bulk onto `bar`).
     auto input_wait_copy = [&]() {
         stamp(1);
-        if (IN == IN_NORM) {
+        if (IN == IN_NORM || IN == IN_TPNORM) {
 #pragma unroll
             for (int ck = 0; ck < 2; ++ck) {
                 const int q = (ck * (KC / 4) + warp) * 32 + lane;
@@ -592,7 +675,23 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
                     bulk_g2s(dst, src, bytes, bar);
                 }
             };
-            if (IN == IN_ACT) {
+            if constexpr (IN == IN_TPNORM) {
+                // every rank's partial sums of this round must have landed in this GPU's exchange buffer
+                const unsigned long long target =
+                    (unsigned long long)a.tp_per_round * (__ldcg(a.tp_fwd) * (unsigned long long)a.tp_rounds + (unsigned long long)a.tp_round + 1ull);
+                const long long t_begin = global_timer_ns();
+                for (int p = 0; p < a.tp_n; ++p) {
+                    while (ld_acquire_sys_u64(a.tp_cnt + p) < target) {
+                        if (global_timer_ns() - t_begin > TP_TIMEOUT_NS) { atomicExch(a.tp_err, 1u + (unsigned)p); break; }
+                    }
+                }
+                proxy_fence_async();   // the bulk copies below (async proxy) read what the peers stored (generic proxy)
+                float *sx = (float *)(sact + (size_t)a.nbp * (100 + 4 * QT));
+                const uint32_t bytes = (uint32_t)a.n_in * 4;
+                mbar_expect_tx(bar, bytes * (uint32_t)(1 + a.tp_n));
+                bulk_g2s(sx, a.tp_res, bytes, bar);
+                for (int p = 0; p < a.tp_n; ++p) bulk_g2s(sx + a.n_in + 256 + (size_t)p * a.n_in, a.tp_slots + (size_t)p * a.tp_slot_stride, bytes, bar);
+            } else if (IN == IN_ACT) {
                 const uint32_t bytes = (uint32_t)a.nbp * 100;
                 mbar_expect_tx(bar, bytes);
                 rot_copy(sact, a.act_in, bytes);
@@ -610,7 +709,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     };
     // Wait for the copy and put this warp's columns of the input on the activation grid.
     auto input_stage = [&]() {
-        stage_warp_input<IN, QT>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn);
+        stage_warp_input<IN, QT>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn, scratch);
         bar_parity ^= 1;
         stamp(3);
     };
@@ -653,7 +752,7 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == a.rb) {
-            flush_batch<OUT, QT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
+            flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
             batch_first += batch_n;
             batch_n = 0;
         }
@@ -772,9 +871,17 @@ __device__ __forceinline__ void gemv_phase(const GemvArgs &a, const GemvPtrs pv,
     // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
     prefetch_next();
-    if (batch_n > 0) flush_batch<OUT, QT>(a, pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
+    if (batch_n > 0) flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
     stamp(5);
     if (MEGA) prof_next();
+    if constexpr (OUT == OUT_TPPART) if (tid == 0) {
+        // flush_batch ended with a CTA barrier: every row this CTA stored is ordered before this fence, which makes them
+        // visible system-wide before the arrival counts below
+        __threadfence_system();
+#pragma unroll
+        for (int p = 0; p < 8; ++p)
+            if (p < a.tp_n) atomicAdd_system(a.tp_sig[p], 1ull);
+    }
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
         sumsq = warp_sum(sumsq);
         __syncthreads();

@@ -16,13 +16,21 @@ struct DevState {
 };
 
 // weight re-pack / init into the streaming layout (layout.cuh)
-void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
-void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
-void launch_pack_q6_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
-void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
-void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
-void launch_randinit_q6_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st);
-void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st);
+// src_cols / src_col0 (0 / 0 = the whole row): the source rows are src_cols wide and columns [src_col0, src_col0 + cols) are taken;
+// src_row0 of the initialisers: first row of the window inside the whole tensor (tensor-parallel ranks fill their share).
+void launch_pack_q4_0(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                      int64_t src_cols = 0, int64_t src_col0 = 0);
+void launch_pack_q4_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                      int64_t src_cols = 0, int64_t src_col0 = 0);
+void launch_pack_q6_k(const void *d_src, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                      int64_t src_cols = 0, int64_t src_col0 = 0);
+void launch_randinit_q4_0(uint64_t key, float sigma, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                          int64_t src_row0 = 0, int64_t src_cols = 0, int64_t src_col0 = 0);
+void launch_randinit_q4_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                          int64_t src_row0 = 0, int64_t src_cols = 0, int64_t src_col0 = 0);
+void launch_randinit_q6_k(uint64_t key, int64_t rows, int64_t cols, void *d_packed, int64_t dst_row0, int64_t dst_row_stride, cudaStream_t st,
+                          int64_t src_row0 = 0, int64_t src_cols = 0, int64_t src_col0 = 0);
+void launch_randinit_f32(uint64_t key, float sigma, float offset, int64_t n, float *d_out, cudaStream_t st, int64_t i0 = 0);
 
 // matrix format index of the kernels: 0 = Q4_0, 1 = Q4_K, 2 = Q6_K
 static inline int qt_of(int type) { return type == B2_T_Q6_K ? 2 : type == B2_T_Q4_K ? 1 : 0; }
@@ -38,6 +46,25 @@ cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_pack
                            float eps, int plus_one, const void *act_in, float *y, const float *bias_or_res, void *act_out, int act,
                            float *pmax, int *pidx, int *grid_out, const void *next_w, uint64_t next_bytes, const float *xsq_in, int xsq_n,
                            float *xsq_out, cudaStream_t st, bool pdl);
+// tensor-parallel modes (gemv_tp.cu): GEMV_IN_TPNORM consumes an exchange round, GEMV_OUT_TPPART produces one
+enum { GEMV_IN_TPNORM = 3, GEMV_OUT_TPPART = 4 };
+struct GemvTp {
+    int n = 1;
+    float *dst[8] = {};                    // OUT_TPPART: slot of this rank in every rank's exchange buffer of the round
+    unsigned long long *sig[8] = {};       //             arrival counter of this rank on every rank
+    const float *res = nullptr;            // IN_TPNORM: residual before the exchange,
+    const float *slots = nullptr;          //            local slots of the round (slot r at r * slot_stride floats),
+    int slot_stride = 0;
+    const unsigned long long *cnt = nullptr, *fwd = nullptr;   // local arrival counters [n], forward passes completed
+    int round = 0, rounds = 1, per_round = 0;                  // counter value of the round: per_round * (*fwd * rounds + round + 1)
+    float *xout = nullptr;                 //            new residual (written by CTA 0)
+    unsigned int *err = nullptr;
+};
+cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols,
+                           const float *norm_w, float eps, int plus_one, const void *act_in, float *y, const float *bias, int act,
+                           float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl);
+void launch_tp_close(const unsigned long long *cnt, int n, unsigned long long *fwd, int rounds, int round, int per_round, bool wait,
+                     unsigned int *err, cudaStream_t st);
 void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);
 void launch_sumsq(const float *d_x, int64_t n, float *d_xsq, cudaStream_t st);
 

@@ -34,12 +34,56 @@ def host_random_tensors(a: Arch, seed: int, qtype: str = "q4_0") -> Dict[str, Tu
     return out
 
 
+TP_HANDLE_BYTES = 64
+
+
+def gather_tp_handles(mine: bytes, rank: int, size: int, all_gather) -> bytes:
+    """Rank-ordered concatenation of every rank's exchange handle.  `all_gather(obj) -> list` is the host transport
+    (torch.distributed.all_gather_object wrapped by the caller, a pipe, ...); entries are checked before they reach the
+    C ABI, because a short or misplaced handle would map the wrong memory."""
+    if len(mine) != TP_HANDLE_BYTES:
+        raise ValueError(f"handle of rank {rank} has {len(mine)} bytes, expected {TP_HANDLE_BYTES}")
+    got = all_gather((rank, mine))
+    if len(got) != size:
+        raise ValueError(f"gathered {len(got)} handles for a group of {size}")
+    by_rank = dict(got)
+    if sorted(by_rank) != list(range(size)):
+        raise ValueError(f"handles of ranks {sorted(by_rank)} for a group of {size}")
+    if any(len(h) != TP_HANDLE_BYTES for h in by_rank.values()):
+        raise ValueError("a peer sent a handle of the wrong size")
+    return b"".join(by_rank[r] for r in range(size))
+
+
 class Engine:
-    def __init__(self, device: int = 0):
+    """tp_size > 1: rank `tp_rank` of a tensor-parallel group (one process and one GPU per rank).  Call `tp_connect`
+    (or `tp_connect_torch`) on every rank before creating a model; afterwards every rank makes the same calls."""
+
+    def __init__(self, device: int = 0, tp_rank: int = 0, tp_size: int = 1):
         self.lib = _lib.load()
         self.h = C.c_void_p()
-        check(self.lib.b2_engine_create(device, 0, 1, None, C.byref(self.h)))
-        self.device = device
+        check(self.lib.b2_engine_create(device, tp_rank, tp_size, None, C.byref(self.h)))
+        self.device, self.tp_rank, self.tp_size = device, tp_rank, tp_size
+
+    def tp_handle(self) -> bytes:
+        buf = C.create_string_buffer(TP_HANDLE_BYTES)
+        check(self.lib.b2_engine_tp_handle(self.h, buf))
+        return buf.raw
+
+    def tp_connect(self, all_gather) -> None:
+        handles = gather_tp_handles(self.tp_handle(), self.tp_rank, self.tp_size, all_gather)
+        check(self.lib.b2_engine_tp_connect(self.h, handles))
+
+    def tp_connect_torch(self, group=None) -> None:
+        """Exchange the handles over an initialised torch.distributed process group (nccl or gloo)."""
+        import torch.distributed as dist
+
+        def all_gather(obj):
+            out = [None] * dist.get_world_size(group)
+            dist.all_gather_object(out, obj, group=group)
+            return out
+
+        self.tp_connect(all_gather)
+        dist.barrier(group)
 
     def close(self):
         if self.h:

@@ -95,10 +95,23 @@ const char *b2_last_error(void);
 const char *b2_version(void);
 
 /* ---- engine / model / session: the stages of one /api/generate request -------------------------- */
-/* Replaces: Ollama runner start-up (README.md:29-31 "install Ollama").  tp_size 1 = single GPU. */
+/* Replaces: Ollama runner start-up (README.md:29-31 "install Ollama").  tp_size 1 = single GPU.
+ * tp_size 2, 4 or 8: this engine is rank tp_rank of a tensor-parallel group, one process and one GPU per rank (SURVEY.md §8d
+ * config 4 / §8e; no reference counterpart: Ollama places a model on one GPU here).  nccl_uid is ignored: the ranks exchange
+ * partial sums through memory they map into each other (see b2_engine_tp_connect), not through a communicator. */
 int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, const void *nccl_uid, b2_engine **out);
 int b2_engine_destroy(b2_engine *e);
 int b2_engine_device(const b2_engine *e, int *device_ordinal);
+/* Tensor-parallel set-up, before any model is created on the engine: every rank calls b2_engine_tp_handle (B2_TP_HANDLE_BYTES
+ * bytes out: a CUDA IPC handle of its exchange block), the host side gathers the handles of all ranks in rank order (any
+ * transport: torch.distributed, a pipe, a file), and every rank passes the tp_size * B2_TP_HANDLE_BYTES bytes to
+ * b2_engine_tp_connect, which maps the peers' blocks (needs peer access between the GPUs: NVLink / NVSwitch on a B200 box).
+ * From then on every rank must make the same model / session / prefill / decode calls with the same arguments; each rank holds
+ * 1/tp_size of every layer matrix, computes all logits itself and returns the same tokens.  A rank whose peer does not show up
+ * within 2 s fails the call with B2_ENCCL instead of hanging.  Prompts are evaluated token by token in this mode. */
+#define B2_TP_HANDLE_BYTES 64
+int b2_engine_tp_handle(b2_engine *e, void *handle_out);
+int b2_engine_tp_connect(b2_engine *e, const void *handles);
 
 /* Replaces: Ollama model load on first request for a tag (RunnerConfig.py:128, field "model").
  * Uploads the tensors once and re-packs them into the engine's HBM layout. */

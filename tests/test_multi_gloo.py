@@ -59,3 +59,42 @@ def test_replica_sharding_covers_every_model_once():
     # heaviest models are spread first: gemma:7b and llama3.1:8b never share a shard when there are >= 2
     g2 = launch.shard_models(launch.MODELS, 2)
     assert not any({"gemma:7b", "llama3.1:8b"} <= set(g) for g in g2)
+
+
+def _handle_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200.engine import TP_HANDLE_BYTES, gather_tp_handles
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    def all_gather(obj):
+        got = [None] * world
+        dist.all_gather_object(got, obj)
+        return got[::-1]          # a transport may deliver in any order: the result must still be rank-ordered
+
+    blob = gather_tp_handles(bytes([rank + 1]) * TP_HANDLE_BYTES, rank, world, all_gather)
+    open(out + str(rank), "wb").write(blob)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_tp_handle_exchange_is_rank_ordered_world2(tmp_path):
+    """Host side of the tensor-parallel set-up: every rank ends up with the same rank-ordered block of handles."""
+    out = str(tmp_path / "handles")
+    mp.spawn(_handle_worker, args=(2, free_port(), out), nprocs=2, join=True)
+    want = bytes([1]) * 64 + bytes([2]) * 64
+    assert open(out + "0", "rb").read() == want and open(out + "1", "rb").read() == want
+
+
+def test_tp_handle_exchange_rejects_bad_input():
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200.engine import gather_tp_handles
+    ok = bytes(64)
+    with pytest.raises(ValueError):
+        gather_tp_handles(bytes(10), 0, 2, lambda o: [o, (1, ok)])
+    with pytest.raises(ValueError):
+        gather_tp_handles(ok, 0, 2, lambda o: [o])                       # a rank is missing
+    with pytest.raises(ValueError):
+        gather_tp_handles(ok, 0, 2, lambda o: [o, (0, ok)])              # the same rank twice
+    with pytest.raises(ValueError):
+        gather_tp_handles(ok, 0, 2, lambda o: [o, (1, bytes(8))])        # short handle from a peer
