@@ -454,7 +454,7 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
         if (q < n4) {
             const float4 v = ((const float4 *)sx)[q];
             if (IN == IN_NORM || IN == IN_TPNORM) {
-                const float4 w = ck < 2 ? wn[ck] : __ldg((const float4 *)pv.norm_w + q);
+                const float4 w = ck == 0 ? wn[0] : ck == 1 ? wn[1] : __ldg((const float4 *)pv.norm_w + q);   // constant indices: wn stays in registers
                 const float xs[4] = {v.x, v.y, v.z, v.w}, ws[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) yv[e] = __fmul_rn(__fmul_rn(xs[e], r), a.plus_one ? __fadd_rn(1.0f, ws[e]) : ws[e]);
@@ -520,9 +520,11 @@ __device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A 
     }
     return f;
 }
+struct FlushRun { float best_v; int best_i; float sumsq; };   // running arg-max / sum of squares of the rows this thread finalised
 template <int OUT, int QT>
-__device__ __noinline__ void flush_batch(const FlushArgs<OUT == OUT_TPPART> a, const float *bias_or_res, float *red, int batch_first, int batch_n, float &best_v, int &best_i,
-                                         float &sumsq) {
+__device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> a, const float *bias_or_res, float *red, int batch_first, int batch_n, FlushRun run) {
+    float best_v = run.best_v, sumsq = run.sumsq;
+    int best_i = run.best_i;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __syncthreads();
     if (warp < batch_n) {
@@ -572,6 +574,7 @@ __device__ __noinline__ void flush_batch(const FlushArgs<OUT == OUT_TPPART> a, c
         }
     }
     __syncthreads();   // the parked partials may be overwritten from here on
+    return FlushRun{best_v, best_i, sumsq};
 }
 
 // One GEMV phase executed by a whole 512-thread CTA.  MEGA = false: the body of the stand-alone kernel k_gemv (ordered after the
@@ -680,7 +683,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 const unsigned long long target =
                     (unsigned long long)a.tp_per_round * (__ldcg(a.tp_fwd) * (unsigned long long)a.tp_rounds + (unsigned long long)a.tp_round + 1ull);
                 const long long t_begin = global_timer_ns();
-                for (int p = 0; p < a.tp_n; ++p) {
+                for (int p = 0; p < a.tp_n && __ldcg(a.tp_err) == 0u; ++p) {   // after a time-out nothing waits any more: the call fails fast
                     while (ld_acquire_sys_u64(a.tp_cnt + p) < target) {
                         if (global_timer_ns() - t_begin > TP_TIMEOUT_NS) { atomicExch(a.tp_err, 1u + (unsigned)p); break; }
                     }
@@ -752,7 +755,8 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == a.rb) {
-            flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
+            const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
+            best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
             batch_first += batch_n;
             batch_n = 0;
         }
@@ -871,7 +875,10 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
     // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
     prefetch_next();
-    if (batch_n > 0) flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, best_v, best_i, sumsq);
+    if (batch_n > 0) {
+        const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
+        best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
+    }
     stamp(5);
     if (MEGA) prof_next();
     if constexpr (OUT == OUT_TPPART) if (tid == 0) {

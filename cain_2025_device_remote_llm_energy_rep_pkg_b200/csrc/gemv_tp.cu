@@ -54,7 +54,7 @@ __global__ void k_tp_close(const unsigned long long *cnt, int n, unsigned long l
     if (wait) {
         const unsigned long long target = (unsigned long long)per_round * (*fwd * (unsigned long long)rounds + (unsigned long long)round + 1ull);
         const long long t_begin = global_timer_ns();
-        for (int p = 0; p < n; ++p)
+        for (int p = 0; p < n && *err == 0u; ++p)
             while (ld_acquire_sys_u64(cnt + p) < target)
                 if (global_timer_ns() - t_begin > TP_TIMEOUT_NS) { atomicExch(err, 1u + (unsigned)p); break; }
     }
