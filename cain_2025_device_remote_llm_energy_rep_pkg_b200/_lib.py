@@ -8,7 +8,7 @@ import os
 from .archs import CArchCfg
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2llm.so")
+LIB_PATH = os.environ.get("B2_LIB") or os.path.join(_HERE, "libb2llm.so")   # B2_LIB: an experimental build (csrc/build.sh with OUT=, EXTRA=)
 
 T_F32, T_Q4_0, T_Q8_0, T_Q4_K, T_Q6_K = 0, 2, 8, 12, 14
 QTYPE = {"f32": T_F32, "q4_0": T_Q4_0, "q8_0": T_Q8_0, "q4_k": T_Q4_K, "q6_k": T_Q6_K}

@@ -44,12 +44,12 @@ extern "C" const char *b2_version(void) { return "b2llm 0.1 (sm_100a)"; }
 // ------------------------------------------------------------------------------------ objects
 // Exchange memory of a tensor-parallel group (one engine = one rank = one process = one GPU).  Every rank allocates one block,
 // hands its CUDA IPC handle to the others (b2_engine_tp_handle / b2_engine_tp_connect) and maps theirs.  Layout of a block:
-//   float slots[2 buffers][8 source ranks][TP_MAX_VEC]   partial sums pushed by the peers (and by this rank, into its own slot)
-//   u64   arrivals[2 buffers][8 source ranks]            CTAs of the producing kernel that have stored their rows, ever increasing
-//   u64   forwards                                       forward passes this rank has completed
-//   u32   error                                          1 + rank that did not arrive in time (sticky)
+//   pair  slots[2 buffers][8 source ranks][TP_MAX_VEC]   pair = (f32 partial sum, u32 tag of the exchange round), stored by the
+//                                                        peers (and by this rank, into its own slot) from inside their GEMVs
+//   u64   forwards                                       forward passes this rank has completed (the tags derive from it)
+//   u32   error                                          1 + a rank whose pairs did not arrive in time (sticky)
 // Buffer 0 carries the O-projection rounds, buffer 1 the down-projection rounds, so a rank that is one exchange ahead never
-// overwrites slots a slower rank still reads (a rank cannot be two exchanges ahead: each exchange waits for every rank).
+// overwrites slots a slower rank still reads (a rank cannot be two exchanges ahead: each exchange needs every rank's pairs).
 #define TP_MAX_VEC 8192
 #define TP_MAX_RANKS 8
 struct TpLink {
@@ -57,12 +57,11 @@ struct TpLink {
     void *local = nullptr;
     void *peer[TP_MAX_RANKS] = {};
     bool connected = false;
-    static constexpr size_t slots_bytes() { return (size_t)2 * TP_MAX_RANKS * TP_MAX_VEC * 4; }
-    static constexpr size_t bytes() { return slots_bytes() + 2 * TP_MAX_RANKS * 8 + 8 + 8 + 240; }
-    float *slot(int on_rank, int buf, int src) const { return (float *)peer[on_rank] + ((size_t)buf * TP_MAX_RANKS + src) * TP_MAX_VEC; }
-    unsigned long long *arrivals(int on_rank, int buf) const { return (unsigned long long *)((char *)peer[on_rank] + slots_bytes()) + buf * TP_MAX_RANKS; }
-    unsigned long long *forwards() const { return (unsigned long long *)((char *)local + slots_bytes()) + 2 * TP_MAX_RANKS; }
-    unsigned int *error() const { return (unsigned int *)(forwards() + 1); }
+    static constexpr size_t slots_bytes() { return (size_t)2 * TP_MAX_RANKS * TP_MAX_VEC * 8; }
+    static constexpr size_t bytes() { return slots_bytes() + 256; }
+    void *slot(int on_rank, int buf, int src) const { return (char *)peer[on_rank] + ((size_t)buf * TP_MAX_RANKS + src) * TP_MAX_VEC * 8; }
+    unsigned long long *forwards() const { return (unsigned long long *)((char *)local + slots_bytes()); }
+    unsigned int *error() const { return (unsigned int *)((char *)local + slots_bytes() + 128); }
 };
 struct b2_engine {
     int device = 0, tp_rank = 0, tp_size = 1;
@@ -643,11 +642,12 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
     const float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
     launch_embed_row(qt_of(m->embd.type), m->embd.packed, m->embd.cols, &s->state->cur_token, escale, X[0], s->xsq, st); n++;
     const uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
-    const int per_round = gemv_grid((int)ntiles(H), 1), rounds = c.n_layers;
-    auto producer = [&](int buf) {
+    const int rounds = 2 * c.n_layers;   // exchange rounds of a forward pass: O and down projection of every layer
+    auto producer = [&](int buf, int round) {
         GemvTp t;
         t.n = N;
-        for (int p = 0; p < N; ++p) { t.dst[p] = L.slot(p, buf, rk); t.sig[p] = L.arrivals(p, buf) + rk; }
+        for (int p = 0; p < N; ++p) t.dst[p] = L.slot(p, buf, rk);
+        t.fwd = L.forwards(); t.round = round; t.rounds = rounds;
         return t;
     };
     auto consumer = [&](int buf, int round) {
@@ -655,8 +655,8 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
         t.n = N;
         t.res = X[cur]; t.xout = X[cur ^ 1];
         t.slots = L.slot(rk, buf, 0); t.slot_stride = TP_MAX_VEC;
-        t.cnt = L.arrivals(rk, buf); t.fwd = L.forwards();
-        t.round = round; t.rounds = rounds; t.per_round = per_round;
+        t.fwd = L.forwards();
+        t.round = round; t.rounds = rounds;
         t.err = L.error();
         cur ^= 1;
         return t;
@@ -668,29 +668,29 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
             e = launch_gemv_qt(qt_of(ly.qkv.type), GEMV_IN_NORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, X[0], ly.attn_norm, c.rms_eps, c.norm_plus_one, nullptr,
                                s->qkv, ly.qkv_bias, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, s->xsq, 1, nullptr, st, pdl);
         else
-            e = launch_gemv_tp(consumer(1, l - 1), qt_of(ly.qkv.type), GEMV_IN_TPNORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, ly.attn_norm, c.rms_eps,
+            e = launch_gemv_tp(consumer(1, 2 * l - 1), qt_of(ly.qkv.type), GEMV_IN_TPNORM, GEMV_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, ly.attn_norm, c.rms_eps,
                                c.norm_plus_one, nullptr, s->qkv, ly.qkv_bias, 0, nullptr, nullptr, nullptr, st, pdl);
         n++;
         if (e != cudaSuccess) break;
         e = launch_attn_fused(s->qkv, m->heads(), m->kv_heads(), hd, &s->state->pos, 0, m->rope_cos, m->rope_sin, s->kcache + l * layer_kv,
                               s->vcache + l * layer_kv, s->page_table, nullptr, s->act_attn, attn_ctx, st, pdl); n++;
         if (e != cudaSuccess) break;
-        e = launch_gemv_tp(producer(0), qt_of(ly.o.type), GEMV_IN_ACT, GEMV_OUT_TPPART, ly.o.packed, H, qd, nullptr, 0.f, 0, s->act_attn, nullptr, nullptr, 0,
+        e = launch_gemv_tp(producer(0, 2 * l), qt_of(ly.o.type), GEMV_IN_ACT, GEMV_OUT_TPPART, ly.o.packed, H, qd, nullptr, 0.f, 0, s->act_attn, nullptr, nullptr, 0,
                            nullptr, nullptr, nullptr, st, pdl); n++;
         if (e != cudaSuccess) break;
-        e = launch_gemv_tp(consumer(0, l), qt_of(ly.gateup.type), GEMV_IN_TPNORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, ly.ffn_norm, c.rms_eps,
+        e = launch_gemv_tp(consumer(0, 2 * l), qt_of(ly.gateup.type), GEMV_IN_TPNORM, GEMV_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, ly.ffn_norm, c.rms_eps,
                            c.norm_plus_one, nullptr, s->h, nullptr, c.act, nullptr, nullptr, nullptr, st, pdl); n++;
         if (e != cudaSuccess) break;
-        e = launch_gemv_tp(producer(1), qt_of(ly.down.type), GEMV_IN_F32, GEMV_OUT_TPPART, ly.down.packed, H, I, nullptr, 0.f, 0, s->h, nullptr, nullptr, 0,
+        e = launch_gemv_tp(producer(1, 2 * l + 1), qt_of(ly.down.type), GEMV_IN_F32, GEMV_OUT_TPPART, ly.down.packed, H, I, nullptr, 0.f, 0, s->h, nullptr, nullptr, 0,
                            nullptr, nullptr, nullptr, st, pdl); n++;
     }
     if (e == cudaSuccess && with_head) {
-        e = launch_gemv_tp(consumer(1, c.n_layers - 1), qt_of(m->head.type), GEMV_IN_TPNORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, m->out_norm, c.rms_eps,
+        e = launch_gemv_tp(consumer(1, 2 * c.n_layers - 1), qt_of(m->head.type), GEMV_IN_TPNORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, m->out_norm, c.rms_eps,
                            c.norm_plus_one, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, &s->head_grid, st, pdl); n++;
     }
     if (e != cudaSuccess) { s->enqueue_error = e; return n; }
     // a pass without the LM head still has to see the last round complete before the next pass reuses the slots
-    launch_tp_close(L.arrivals(rk, 1), N, L.forwards(), rounds, c.n_layers - 1, per_round, !with_head, L.error(), st); n++;
+    launch_tp_close(L.slot(rk, 1, 0), TP_MAX_VEC, N, H, L.forwards(), rounds, 2 * c.n_layers - 1, !with_head, L.error(), st); n++;
     return n;
 }
 

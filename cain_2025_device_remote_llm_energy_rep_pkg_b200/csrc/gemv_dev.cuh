@@ -77,6 +77,9 @@ __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, ui
 #ifndef MEGA_ORDER
 #define MEGA_ORDER 2                         // persistent kernel: 2 = barrier, staging, first register loads (see stage_input)
 #endif
+#ifndef GEMV_ORDER
+#define GEMV_ORDER 0                         // stand-alone kernel: 0 = register loads, wait, staging; 1 = wait, staging, register loads; 2 = as 0 with the L2 window after the wait
+#endif
 #ifndef MMA_GROUP
 #define MMA_GROUP 2                          // independent MMAs in flight per warp before their results are scaled (4 costs 8 more registers)
 #endif
@@ -120,32 +123,37 @@ struct GemvPtrs {
     const float *bias_or_res;
 };
 struct GemvArgsTp : GemvArgs {
-    // ---- tensor-parallel decode (engine.cu: TpLink; one process per GPU, exchange buffers mapped into each other over NVLink).
-    // OUT_TPPART: this rank multiplied its share of K, so its rows are partial sums.  They are stored into slot [tp_rank] of
-    // EVERY rank's exchange buffer (tp_dst[p]: peer memory, plain stores), then each CTA adds 1 to every rank's arrival counter
-    // tp_sig[p].  IN_TPNORM: the consumer on each rank waits until its tp_n local counters reach the value of this round, copies
-    // the residual and the tp_n slots into shared memory (its own memory only) and forms x = res + slot_0 + ... + slot_{n-1} in
-    // that order on every rank, so all ranks hold bit-identical x; CTA 0 also writes x to tp_xout.  The all-reduce is the pair
-    // (epilogue of one GEMV, prologue of the next): no kernel of its own.
-    float *tp_dst[8];
-    unsigned long long *tp_sig[8];
+    // ---- tensor-parallel decode (engine.cu: TpLink; one process per GPU, exchange blocks mapped into each other over NVLink).
+    // OUT_TPPART: this rank multiplied its share of K, so its rows are partial sums.  Every row goes, as an 8-byte pair
+    // (value, tag of the round), into slot [this rank] of EVERY rank's exchange block (tp_dst[p]: peer memory, one store per
+    // rank; an aligned 8-byte store arrives whole).  There is no fence, no counter and no second message: a pair whose tag is
+    // the round's tag IS the arrived value.  IN_TPNORM: each warp of the consumer reads the pairs of its own columns from this
+    // GPU's block until all carry the tag and forms x = res + slot_0 + ... + slot_{n-1} in that order on every rank, so all
+    // ranks hold bit-identical x; CTA 0 also writes x to tp_xout.  The all-reduce is the pair (epilogue of one GEMV, prologue of
+    // the next): no kernel of its own, and one NVLink crossing of latency.
+    uint2 *tp_dst[8];
     int tp_n;
     const float *tp_res;                 // residual stream before the exchange (n_in floats)
-    const float *tp_slots;               // local exchange buffer of this round: slot r at r * tp_slot_stride floats
+    const uint2 *tp_slots;               // local exchange buffer of this round: slot r at r * tp_slot_stride pairs
     int tp_slot_stride;
-    const unsigned long long *tp_cnt;    // local arrival counters of this buffer, one per source rank (never reset)
     const unsigned long long *tp_fwd;    // forward passes completed so far on this engine (device counter)
-    int tp_round, tp_rounds, tp_per_round;   // counter value of this round = tp_per_round * (*tp_fwd * tp_rounds + tp_round + 1)
+    int tp_round, tp_rounds;             // tag of this round = low 32 bits of (*tp_fwd * tp_rounds + tp_round + 1): never 0, never repeated
     float *tp_xout;
-    unsigned int *tp_err;                // set to 1 + rank when a peer did not arrive within TP_TIMEOUT_NS (no hang: the caller reports it)
+    unsigned int *tp_err;                // set to 1 + rank when a peer's pairs did not arrive within TP_TIMEOUT_NS (no hang: the caller reports it)
 };
 enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2, IN_TPNORM = 3 };
 enum { OUT_BIAS = 0, OUT_RES = 1, OUT_ACTMUL = 2, OUT_LOGITS = 3, OUT_TPPART = 4 };
 #define TP_TIMEOUT_NS 2000000000ll
-__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
+__device__ __forceinline__ uint4 ld_volatile_v4(const void *p) {   // two (value, tag) pairs, re-read from L2 every time
+    uint4 r;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_volatile_v2(void *p, uint32_t x, uint32_t y) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(x), "r"(y) : "memory");
+}
+template <class A> __device__ __forceinline__ uint32_t tp_tag(const A &a) {
+    return (uint32_t)(__ldcg(a.tp_fwd) * (unsigned long long)a.tp_rounds + (unsigned long long)a.tp_round + 1ull);
 }
 __device__ __forceinline__ long long global_timer_ns() {
     long long t;
@@ -378,7 +386,7 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
 // Q4_K adds float ts[nbp] after the scales: ts[b] = sum of the gridded activations of block b (staging area moves up by nbp*4).
 template <int IN, int QT, class A>
 __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv, uint8_t *sact, uint64_t *bar, uint32_t parity, int cpt, int warp, int lane,
-                                                 const float4 (&wn)[2], float *scratch) {
+                                                 const float4 (&wn)[2], float *scratch, uint32_t tptag) {
     constexpr int A3S = 100 + 4 * QT;   // Q4_K: one block sum per block after the scales, Q6_K: two half-block sums
     float *sts = (float *)(sact + (size_t)a.nbp * 100);
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
@@ -409,10 +417,13 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
     prof_stamp(6);
     float r = 1.0f;
     if constexpr (IN == IN_TPNORM) {
-        // x = res + slot_0 + ... : this warp's columns, in place; the sum of squares needs every warp's share
+        // x = res + slot_0 + ... : this warp's columns, in place; the sum of squares needs every warp's share.
+        // Four ranks' pairs are requested at a time (32 bytes per lane and rank) and re-read until each carries the round's tag.
         float4 *sx4 = (float4 *)(sact + (size_t)a.nbp * A3S);
-        const float4 *sl4 = (const float4 *)(sx + a.n_in + 256);   // the slots follow the (unused) partials area
         const int n4s = a.n_in >> 2;
+        const uint32_t tag = tptag;
+        const long long t_begin = global_timer_ns();
+        bool give_up = false;
         float ss = 0.f;
         for (int ck = 0; ck < cpt; ++ck) {
             const int kbg = ck * (KC / 4) + warp;
@@ -420,12 +431,34 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
             const int q = kbg * 32 + lane;
             if (q < n4s) {
                 float4 v = sx4[q];
+                for (int p0 = 0; p0 < a.tp_n; p0 += 4) {
+                    uint4 lo[4], hi[4];
+                    uint32_t spins = 0;
+                    for (;;) {
+                        bool ok = true;
 #pragma unroll
-                for (int p = 0; p < 8; ++p)
-                    if (p < a.tp_n) {
-                        const float4 u = sl4[(size_t)p * n4s + q];
-                        v.x = __fadd_rn(v.x, u.x); v.y = __fadd_rn(v.y, u.y); v.z = __fadd_rn(v.z, u.z); v.w = __fadd_rn(v.w, u.w);
+                        for (int u = 0; u < 4; ++u)
+                            if (p0 + u < a.tp_n) {
+                                const uint4 *sp = (const uint4 *)(a.tp_slots + (size_t)(p0 + u) * a.tp_slot_stride) + 2 * q;
+                                lo[u] = ld_volatile_v4(sp);
+                                hi[u] = ld_volatile_v4(sp + 1);
+                            }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (p0 + u < a.tp_n) ok = ok && lo[u].y == tag && lo[u].w == tag && hi[u].y == tag && hi[u].w == tag;
+                        if (ok || give_up) break;
+                        if ((++spins & 255u) == 0u && (__ldcg(a.tp_err) != 0u || global_timer_ns() - t_begin > TP_TIMEOUT_NS)) {
+                            atomicCAS(a.tp_err, 0u, 1u + (unsigned)p0);
+                            give_up = true;   // a peer is missing: finish with what is there, the call reports the failure
+                        }
                     }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (p0 + u < a.tp_n) {
+                            v.x = __fadd_rn(v.x, __uint_as_float(lo[u].x)); v.y = __fadd_rn(v.y, __uint_as_float(lo[u].z));
+                            v.z = __fadd_rn(v.z, __uint_as_float(hi[u].x)); v.w = __fadd_rn(v.w, __uint_as_float(hi[u].z));
+                        }
+                }
                 sx4[q] = v;
                 if (blockIdx.x == 0) __stcg((float4 *)a.tp_xout + q, v);
                 ss = fmaf(v.x, v.x, ss); ss = fmaf(v.y, v.y, ss); ss = fmaf(v.z, v.z, ss); ss = fmaf(v.w, v.w, ss);
@@ -508,15 +541,16 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
 // What the epilogue needs from the argument block, by value: a reference to the kernel parameter would force the whole block
 // into local memory of every thread (this function is not inlined).
 template <bool TP> struct FlushArgs { float *y; int rows, act; };
-template <> struct FlushArgs<true> { float *y; int rows, act; float *tp_dst[8]; int tp_n; };
+template <> struct FlushArgs<true> { float *y; int rows, act; uint2 *tp_dst[8]; int tp_n; uint32_t tp_tag; };
 template <int OUT, class A>
-__device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A &a) {
+__device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A &a, uint32_t tptag) {
     FlushArgs<OUT == OUT_TPPART> f;
     f.y = a.y; f.rows = a.rows; f.act = a.act;
     if constexpr (OUT == OUT_TPPART) {
 #pragma unroll
         for (int p = 0; p < 8; ++p) f.tp_dst[p] = a.tp_dst[p];
         f.tp_n = a.tp_n;
+        f.tp_tag = tptag;
     }
     return f;
 }
@@ -556,10 +590,10 @@ __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> 
                 sumsq = fmaf(xn, xn, sumsq);
             }
         } else if constexpr (OUT == OUT_TPPART) {
-            if (lane < 16 && row < a.rows) {   // this rank's partial sum into its slot on every rank (16 lanes = 64 contiguous bytes per rank)
+            if (lane < 16 && row < a.rows) {   // this rank's partial sum into its slot on every rank (16 lanes = 128 contiguous bytes per rank)
 #pragma unroll
                 for (int p = 0; p < 8; ++p)
-                    if (p < a.tp_n) a.tp_dst[p][row] = yv;
+                    if (p < a.tp_n) st_volatile_v2(a.tp_dst[p] + row, __float_as_uint(yv), a.tp_tag);
             }
         } else if (OUT == OUT_LOGITS) {
             if (lane < 16 && row < a.rows) {
@@ -607,6 +641,10 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         }
     };
     stamp(0);
+    // tensor-parallel modes: the tag of this exchange round (a device counter of forward passes: the graph is replayed unchanged);
+    // requested here, first used after the wait / in the epilogue
+    uint32_t tptag = 0;
+    if constexpr (IN == IN_TPNORM || OUT == OUT_TPPART) tptag = tp_tag(a);
 
     // contiguous, aligned share of the tiles
     const int units = (a.n_tiles + a.tile_align - 1) / a.tile_align;
@@ -679,21 +717,11 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 }
             };
             if constexpr (IN == IN_TPNORM) {
-                // every rank's partial sums of this round must have landed in this GPU's exchange buffer
-                const unsigned long long target =
-                    (unsigned long long)a.tp_per_round * (__ldcg(a.tp_fwd) * (unsigned long long)a.tp_rounds + (unsigned long long)a.tp_round + 1ull);
-                const long long t_begin = global_timer_ns();
-                for (int p = 0; p < a.tp_n && __ldcg(a.tp_err) == 0u; ++p) {   // after a time-out nothing waits any more: the call fails fast
-                    while (ld_acquire_sys_u64(a.tp_cnt + p) < target) {
-                        if (global_timer_ns() - t_begin > TP_TIMEOUT_NS) { atomicExch(a.tp_err, 1u + (unsigned)p); break; }
-                    }
-                }
-                proxy_fence_async();   // the bulk copies below (async proxy) read what the peers stored (generic proxy)
+                // only the residual travels through shared memory; the warps read the exchange slots themselves
                 float *sx = (float *)(sact + (size_t)a.nbp * (100 + 4 * QT));
                 const uint32_t bytes = (uint32_t)a.n_in * 4;
-                mbar_expect_tx(bar, bytes * (uint32_t)(1 + a.tp_n));
+                mbar_expect_tx(bar, bytes);
                 bulk_g2s(sx, a.tp_res, bytes, bar);
-                for (int p = 0; p < a.tp_n; ++p) bulk_g2s(sx + a.n_in + 256 + (size_t)p * a.n_in, a.tp_slots + (size_t)p * a.tp_slot_stride, bytes, bar);
             } else if (IN == IN_ACT) {
                 const uint32_t bytes = (uint32_t)a.nbp * 100;
                 mbar_expect_tx(bar, bytes);
@@ -712,7 +740,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
     };
     // Wait for the copy and put this warp's columns of the input on the activation grid.
     auto input_stage = [&]() {
-        stage_warp_input<IN, QT>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn, scratch);
+        stage_warp_input<IN, QT>(a, pv, sact, bar, bar_parity, cpt, warp, lane, wn, scratch, tptag);
         bar_parity ^= 1;
         stamp(3);
     };
@@ -731,6 +759,10 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
             input_wait_copy();
             first_loads();
             input_stage();
+        } else if (GEMV_ORDER == 1) {   // experiment: staging before the first register loads (they then hit the L2 window)
+            input_wait_copy();
+            input_stage();
+            first_loads();
         } else {
             first_loads();
             input_wait_copy();
@@ -755,7 +787,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == a.rb) {
-            const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
+            const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
             best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
             batch_first += batch_n;
             batch_n = 0;
@@ -788,7 +820,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 pf += GEMV_CWARPS * 16384;
             }
         };
-        l2_window();
+        if (MEGA || GEMV_ORDER != 2) l2_window();
         auto load_full = [&](WPieceT<QT> &r) {
             if (l_rem > 0) { if (act_full) load_piece<QT>(lp, KC, warp, lane, r); lp += KC * WLay<QT>::BB; --l_rem; }
         };
@@ -846,10 +878,14 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 ++l_ck;
             }
         };
-        if (lane == 0 && a.l2_window) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
-            for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
-        }
+        auto l2_all = [&]() {
+            if (lane == 0 && a.l2_window) {   // a CTA's one or two tiles (<= 2 x 220 KB) go to L2 at once, a 16 KB block per warp and round
+                for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
+            }
+        };
+        if (MEGA || GEMV_ORDER != 2) l2_all();
         stage_input([&]() { load_step(buf0, buf1); load_step(buf2, buf3); });
+        if (!MEGA && GEMV_ORDER == 2) l2_all();
         BFragT<QT> bcur, bnxt;
         load_b(0, bcur);
         for (int ck = 0; ck < cpt; ck += 2) {
@@ -876,19 +912,11 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
     prefetch_next();
     if (batch_n > 0) {
-        const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
+        const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
         best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
     }
     stamp(5);
     if (MEGA) prof_next();
-    if constexpr (OUT == OUT_TPPART) if (tid == 0) {
-        // flush_batch ended with a CTA barrier: every row this CTA stored is ordered before this fence, which makes them
-        // visible system-wide before the arrival counts below
-        __threadfence_system();
-#pragma unroll
-        for (int p = 0; p < 8; ++p)
-            if (p < a.tp_n) atomicAdd_system(a.tp_sig[p], 1ull);
-    }
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
         sumsq = warp_sum(sumsq);
         __syncthreads();

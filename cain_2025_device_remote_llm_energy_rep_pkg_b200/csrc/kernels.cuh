@@ -50,21 +50,20 @@ cudaError_t launch_gemv_qt(int qt, int in_mode, int out_mode, const void *d_pack
 enum { GEMV_IN_TPNORM = 3, GEMV_OUT_TPPART = 4 };
 struct GemvTp {
     int n = 1;
-    float *dst[8] = {};                    // OUT_TPPART: slot of this rank in every rank's exchange buffer of the round
-    unsigned long long *sig[8] = {};       //             arrival counter of this rank on every rank
+    void *dst[8] = {};                     // OUT_TPPART: slot of this rank in every rank's exchange block of the round ((value, tag) pairs)
     const float *res = nullptr;            // IN_TPNORM: residual before the exchange,
-    const float *slots = nullptr;          //            local slots of the round (slot r at r * slot_stride floats),
+    const void *slots = nullptr;           //            local slots of the round (slot r at r * slot_stride pairs),
     int slot_stride = 0;
-    const unsigned long long *cnt = nullptr, *fwd = nullptr;   // local arrival counters [n], forward passes completed
-    int round = 0, rounds = 1, per_round = 0;                  // counter value of the round: per_round * (*fwd * rounds + round + 1)
+    const unsigned long long *fwd = nullptr;   // forward passes completed on this engine (device counter)
+    int round = 0, rounds = 1;                 // tag of the round: low 32 bits of *fwd * rounds + round + 1
     float *xout = nullptr;                 //            new residual (written by CTA 0)
     unsigned int *err = nullptr;
 };
 cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols,
                            const float *norm_w, float eps, int plus_one, const void *act_in, float *y, const float *bias, int act,
                            float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl);
-void launch_tp_close(const unsigned long long *cnt, int n, unsigned long long *fwd, int rounds, int round, int per_round, bool wait,
-                     unsigned int *err, cudaStream_t st);
+void launch_tp_close(const void *slots, int slot_stride, int n, int n_vec, unsigned long long *fwd, int rounds, int round, bool wait, unsigned int *err,
+                     cudaStream_t st);
 void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);
 void launch_sumsq(const float *d_x, int64_t n, float *d_xsq, cudaStream_t st);
 
