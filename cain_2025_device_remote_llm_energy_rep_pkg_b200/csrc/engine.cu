@@ -68,6 +68,8 @@ struct b2_engine {
     cudaStream_t stream = nullptr;
     int sm_count = 0;
     TpLink tp;
+    bool self_tags = false;   // B2_SELF_TAGS=1 on a single GPU: O / down hand their rows to the next GEMV as tagged pairs (the tensor-parallel path with one rank)
+    bool tp_nowait = false;   // B2_TP_NOWAIT=1: consumers of tagged rows skip griddepcontrol.wait
 };
 struct Mat {
     void *packed = nullptr;
@@ -153,6 +155,10 @@ struct b2_session {
     size_t mega_smem = 0;
     cudaGraphExec_t graphs[G_COUNT][2] = {};   // [..][0]: positions below ATTN_SHORT_CTX (one attention CTA per head), [..][1]: longer contexts
     int graph_launches[G_COUNT][2] = {};
+    // greedy decode also exists as a graph of `multi_n` consecutive tokens (B2_GRAPH_TOKENS, default 8): fewer graph launches,
+    // no gap between the tokens of one graph
+    cudaGraphExec_t multi[2] = {};
+    int multi_n = 8;
     bool use_graphs = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     b2_stats stats{};
@@ -194,6 +200,16 @@ extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, co
     e->tp.n = tp_size;
     e->tp.rank = tp_rank;
     B2_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    const char *nw = getenv("B2_TP_NOWAIT"), *sf = getenv("B2_SELF_TAGS");
+    e->tp_nowait = nw && nw[0] == '1';
+    if (tp_size == 1 && sf && sf[0] == '1') {
+        B2_CUDA(cudaMalloc(&e->tp.local, TpLink::bytes()));
+        B2_CUDA(cudaMemset(e->tp.local, 0, TpLink::bytes()));
+        B2_CUDA(cudaDeviceSynchronize());
+        e->tp.peer[0] = e->tp.local;
+        e->tp.connected = true;
+        e->self_tags = true;
+    }
     *out = e;
     return B2_OK;
 }
@@ -658,6 +674,7 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
         t.fwd = L.forwards();
         t.round = round; t.rounds = rounds;
         t.err = L.error();
+        t.skip_wait = m->e->tp_nowait ? 1 : 0;
         cur ^= 1;
         return t;
     };
@@ -696,7 +713,7 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
 
 // enqueue one forward pass for the token in state->cur_token at position state->pos; returns #launches
 static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
-    if (s->m->tp > 1) return enqueue_forward_tp(s, with_head, attn_ctx);
+    if (s->m->tp > 1 || s->m->e->self_tags) return enqueue_forward_tp(s, with_head, attn_ctx);
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
@@ -793,6 +810,8 @@ static void drop_graphs(b2_session *s) {
     for (int g = 0; g < G_COUNT; ++g)
         for (int v = 0; v < 2; ++v)
             if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
+    for (int v = 0; v < 2; ++v)
+        if (s->multi[v]) { cudaGraphExecDestroy(s->multi[v]); s->multi[v] = nullptr; }
 }
 
 // run graph `which` for `times` consecutive positions starting at `pos0` (captured lazily; plain launches when B2_NO_GRAPH=1).
@@ -801,6 +820,27 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
     cudaStream_t st = s->m->e->stream;
     for (int i = 0; i < times; ++i) {
         const int v = (pos0 + i) < ATTN_SHORT_CTX ? 0 : 1;
+        // several greedy tokens in one graph while they all use the same attention variant
+        const int U = s->multi_n;
+        if (which == G_DECODE && s->use_graphs && U > 1 && times - i >= U && ((pos0 + i + U - 1) < ATTN_SHORT_CTX ? 0 : 1) == v) {
+            if (!s->multi[v]) {
+                cudaGraph_t g = nullptr;
+                B2_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                int nl = 0;
+                for (int u = 0; u < U; ++u) nl += enqueue_graph_body(s, which, v);
+                s->graph_launches[which][v] = nl / U;
+                cudaError_t e1 = cudaStreamEndCapture(st, &g);
+                if (e1 == cudaSuccess && s->enqueue_error != cudaSuccess) { e1 = s->enqueue_error; cudaGraphDestroy(g); }
+                if (e1 != cudaSuccess) { b2_set_error("graph capture failed: %s", cudaGetErrorString(e1)); return B2_ECUDA; }
+                cudaError_t e2 = cudaGraphInstantiate(&s->multi[v], g, 0);
+                cudaGraphDestroy(g);
+                if (e2 != cudaSuccess) { b2_set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return B2_ECUDA; }
+            }
+            B2_CUDA(cudaGraphLaunch(s->multi[v], st));
+            s->stats.kernel_launches += (uint64_t)s->graph_launches[which][v] * U;
+            i += U - 1;
+            continue;
+        }
         if (!s->use_graphs) {
             s->graph_launches[which][v] = enqueue_graph_body(s, which, v);
             B2_CUDA(cudaGetLastError());
@@ -917,8 +957,9 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     s->fused_attn = !(nf && nf[0] == '1');
     const char *npg = getenv("B2_NO_PREFILL_GEMM");
     s->use_pf_gemm = !(npg && npg[0] == '1');
-    if (m->tp > 1) {   // the tensor-parallel pass exists for the per-stage decode kernels: prompts go through it token by token
-        s->use_pf_gemm = false;
+    if (const char *gt = getenv("B2_GRAPH_TOKENS")) { s->multi_n = atoi(gt); if (s->multi_n < 1 || s->multi_n > 64) s->multi_n = 1; }
+    if (m->tp > 1 || m->e->self_tags) {   // the tensor-parallel pass exists for the per-stage decode kernels: prompts go through it token by token
+        if (m->tp > 1) s->use_pf_gemm = false;
         s->fused_attn = true;
         for (const LayerW &ly : m->layers)
             if (ly.split_qkv) { delete s; b2_set_error("tensor parallel sessions need q, k and v of a layer in one format"); return B2_EINVAL; }
@@ -985,7 +1026,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         return B2_ECUDA;
     }
     const char *mg = getenv("B2_MEGA");
-    if (mg && mg[0] == '1' && m->tp == 1) s->use_mega = build_mega_plan(s);
+    if (mg && mg[0] == '1' && m->tp == 1 && !m->e->self_tags) s->use_mega = build_mega_plan(s);
     *out = s;
     return B2_OK;
 }
@@ -1057,7 +1098,7 @@ static int set_step_counters(b2_session *s) {   // step = 0, prompt_idx = 0, kee
 
 // tensor-parallel sessions: a rank that waited in vain for a peer left a mark instead of hanging
 static int tp_check(b2_session *s) {
-    if (s->m->tp == 1) return B2_OK;
+    if (s->m->tp == 1 && !s->m->e->self_tags) return B2_OK;
     unsigned int err = 0;
     B2_CUDA(cudaMemcpy(&err, s->m->e->tp.error(), 4, cudaMemcpyDeviceToHost));
     B2_CHECK(err == 0, B2_ENCCL, "tensor parallel exchange: rank %u did not arrive within 2 s (every rank must make the same calls with the same arguments)", err - 1);
