@@ -68,8 +68,6 @@ struct b2_engine {
     cudaStream_t stream = nullptr;
     int sm_count = 0;
     TpLink tp;
-    bool self_tags = false;   // B2_SELF_TAGS=1 on a single GPU: O / down hand their rows to the next GEMV as tagged pairs (the tensor-parallel path with one rank)
-    bool tp_nowait = false;   // B2_TP_NOWAIT=1: consumers of tagged rows skip griddepcontrol.wait
 };
 struct Mat {
     void *packed = nullptr;
@@ -200,16 +198,6 @@ extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, co
     e->tp.n = tp_size;
     e->tp.rank = tp_rank;
     B2_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
-    const char *nw = getenv("B2_TP_NOWAIT"), *sf = getenv("B2_SELF_TAGS");
-    e->tp_nowait = nw && nw[0] == '1';
-    if (tp_size == 1 && sf && sf[0] == '1') {
-        B2_CUDA(cudaMalloc(&e->tp.local, TpLink::bytes()));
-        B2_CUDA(cudaMemset(e->tp.local, 0, TpLink::bytes()));
-        B2_CUDA(cudaDeviceSynchronize());
-        e->tp.peer[0] = e->tp.local;
-        e->tp.connected = true;
-        e->self_tags = true;
-    }
     *out = e;
     return B2_OK;
 }
@@ -674,7 +662,6 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
         t.fwd = L.forwards();
         t.round = round; t.rounds = rounds;
         t.err = L.error();
-        t.skip_wait = m->e->tp_nowait ? 1 : 0;
         cur ^= 1;
         return t;
     };
@@ -713,7 +700,7 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
 
 // enqueue one forward pass for the token in state->cur_token at position state->pos; returns #launches
 static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
-    if (s->m->tp > 1 || s->m->e->self_tags) return enqueue_forward_tp(s, with_head, attn_ctx);
+    if (s->m->tp > 1) return enqueue_forward_tp(s, with_head, attn_ctx);
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
@@ -958,8 +945,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     const char *npg = getenv("B2_NO_PREFILL_GEMM");
     s->use_pf_gemm = !(npg && npg[0] == '1');
     if (const char *gt = getenv("B2_GRAPH_TOKENS")) { s->multi_n = atoi(gt); if (s->multi_n < 1 || s->multi_n > 64) s->multi_n = 1; }
-    if (m->tp > 1 || m->e->self_tags) {   // the tensor-parallel pass exists for the per-stage decode kernels: prompts go through it token by token
-        if (m->tp > 1) s->use_pf_gemm = false;
+    if (m->tp > 1) {   // the tensor-parallel pass exists for the per-stage decode kernels: prompts go through it token by token
+        s->use_pf_gemm = false;
         s->fused_attn = true;
         for (const LayerW &ly : m->layers)
             if (ly.split_qkv) { delete s; b2_set_error("tensor parallel sessions need q, k and v of a layer in one format"); return B2_EINVAL; }
@@ -1026,7 +1013,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         return B2_ECUDA;
     }
     const char *mg = getenv("B2_MEGA");
-    if (mg && mg[0] == '1' && m->tp == 1 && !m->e->self_tags) s->use_mega = build_mega_plan(s);
+    if (mg && mg[0] == '1' && m->tp == 1) s->use_mega = build_mega_plan(s);
     *out = s;
     return B2_OK;
 }
@@ -1098,7 +1085,7 @@ static int set_step_counters(b2_session *s) {   // step = 0, prompt_idx = 0, kee
 
 // tensor-parallel sessions: a rank that waited in vain for a peer left a mark instead of hanging
 static int tp_check(b2_session *s) {
-    if (s->m->tp == 1 && !s->m->e->self_tags) return B2_OK;
+    if (s->m->tp == 1) return B2_OK;
     unsigned int err = 0;
     B2_CUDA(cudaMemcpy(&err, s->m->e->tp.error(), 4, cudaMemcpyDeviceToHost));
     B2_CHECK(err == 0, B2_ENCCL, "tensor parallel exchange: rank %u did not arrive within 2 s (every rank must make the same calls with the same arguments)", err - 1);

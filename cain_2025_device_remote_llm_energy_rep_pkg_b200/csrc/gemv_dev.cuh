@@ -139,7 +139,6 @@ struct GemvArgsTp : GemvArgs {
     const unsigned long long *tp_fwd;    // forward passes completed so far on this engine (device counter)
     int tp_round, tp_rounds;             // tag of this round = low 32 bits of (*tp_fwd * tp_rounds + tp_round + 1): never 0, never repeated
     float *tp_xout;
-    int tp_skip_wait;                    // 1: the consumer does not call griddepcontrol.wait (everything it reads is tagged or older than two kernels)
     unsigned int *tp_err;                // set to 1 + rank when a peer's pairs did not arrive within TP_TIMEOUT_NS (no hang: the caller reports it)
 };
 enum { IN_NORM = 0, IN_ACT = 1, IN_F32 = 2, IN_TPNORM = 3 };
@@ -704,11 +703,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         else __syncthreads();       // everybody has issued its first weight loads; the mbarrier thread 0 initialised is visible
         if (tid == 0) {
             if (MEGA) proxy_fence_async();
-            else {                  // the copies below read what the previous kernel wrote
-                bool w = true;
-                if constexpr (IN == IN_TPNORM) w = !a.tp_skip_wait;   // tagged input: completion of the producing grid is not what is waited for
-                if (w) pdl_wait();
-            }
+            else pdl_wait();        // the copies below read what the previous kernel wrote
             // Every CTA copies the same vector at the same moment: each starts at a different 128-byte-aligned offset (and wraps
             // around) so the 148 copies do not walk the L2 slices in lock step.
             auto rot_copy = [&](uint8_t *dst, const uint8_t *src, uint32_t bytes) {

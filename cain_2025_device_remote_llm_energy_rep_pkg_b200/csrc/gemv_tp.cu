@@ -14,7 +14,7 @@ extern int gemv_grid(int n_tiles, int tile_align);
 cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols,
                            const float *norm_w, float eps, int plus_one, const void *act_in, float *y, const float *bias, int act,
                            float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl) {
-    if (tp.n < 1 || tp.n > 8) return cudaErrorInvalidValue;   // n = 1: a single GPU exchanging with itself (tagged hand-over between two GEMVs)
+    if (tp.n < 2 || tp.n > 8) return cudaErrorInvalidValue;
     GemvArgsTp a;
     size_t smem = 0;
     cudaError_t em = gemv_make_args(a, in_mode, d_packed, rows, cols, nullptr, norm_w, eps, plus_one, act_in, y, bias, nullptr, act, pmax, pidx,
@@ -24,7 +24,7 @@ cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, 
     a.tp_n = tp.n;
     for (int p = 0; p < 8; ++p) a.tp_dst[p] = p < tp.n ? (uint2 *)tp.dst[p] : nullptr;
     a.tp_res = tp.res; a.tp_slots = (const uint2 *)tp.slots; a.tp_slot_stride = tp.slot_stride; a.tp_fwd = tp.fwd;
-    a.tp_round = tp.round; a.tp_rounds = tp.rounds; a.tp_xout = tp.xout; a.tp_err = tp.err; a.tp_skip_wait = tp.skip_wait;
+    a.tp_round = tp.round; a.tp_rounds = tp.rounds; a.tp_xout = tp.xout; a.tp_err = tp.err;
     if (!tp.fwd) return cudaErrorInvalidValue;
     if (in_mode == IN_TPNORM && (!tp.res || !tp.slots || !tp.xout || !tp.err || (cols & 3))) return cudaErrorInvalidValue;
     if (out_mode == OUT_TPPART)

@@ -57,7 +57,6 @@ struct GemvTp {
     const unsigned long long *fwd = nullptr;   // forward passes completed on this engine (device counter)
     int round = 0, rounds = 1;                 // tag of the round: low 32 bits of *fwd * rounds + round + 1
     float *xout = nullptr;                 //            new residual (written by CTA 0)
-    int skip_wait = 0;                     //            1: no griddepcontrol.wait in the consumer
     unsigned int *err = nullptr;
 };
 cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols,
