@@ -121,9 +121,9 @@ def run_reference(args):
     info["value"] = v
     line = {"metric": "decode_tokens_per_s", "value": v, "unit": "tokens/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1000.0 * (time.perf_counter() - t0) / (args.warmup + args.steps),
-            "higher_is_better": True, "scaling": "strong" if tp else "weak",
+            "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, " + (f"one request stream over a tensor-parallel group of {world} GPUs (partial sums exchanged through peer memory inside the GEMV kernels)" if tp else "one replica per GPU"),
+            "config": {"workload": f"{args.model} {args.qtype}{'' if not args.head_qtype else ' + ' + args.head_qtype + ' head'} batch-1 greedy decode, random-init weights, one replica per GPU",
                        "new_tokens": args.new_tokens, "prompt_len": args.prompt_len, "requests_per_step_per_gpu": 1,
                        "step": f"bounded sample: {args.cpu_tokens} decode tokens of the oracle per step"},
             "cpu_baseline": info, "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -230,15 +230,15 @@ def aggregate(dist, wall_s, eval_s, tokens, launches, energy_j, device="cuda"):
 
 
 def ncu_traffic_per_token(model: str):
-    """DRAM bytes (read + write) of one decoded token from the committed ncu launch list (profiles/r01b_launches_summary.csv,
+    """DRAM bytes (read + write) of one decoded token from the committed ncu launch list (profiles/r01d_launches_summary.csv,
     captured on llama3.1:8b): per-launch bytes of every kernel x its launches per token.  None for other workloads."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01b_launches_summary.csv")
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01d_launches_summary.csv")
     if model != "llama3.1:8b" or not os.path.exists(path):
         return None
     import csv
     from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
-    per_layer = ("k_gemv<0, 2>", "k_gemv<2, 1>", "k_gemv<0, 0>", "k_gemv<1, 1>", "k_attn_fused")
-    once = ("k_gemv<0, 3>", "k_embed_row", "k_argmax_partials", "k_commit_sample", "k_advance")
+    per_layer = ("k_gemv<0, 2,", "k_gemv<2, 1,", "k_gemv<0, 0,", "k_gemv<1, 1,", "k_attn_fused")   # gate/up, down, QKV, O, attention
+    once = ("k_gemv<0, 3,", "k_embed_row", "k_argmax_partials", "k_commit_sample", "k_advance")
     total = 0.0
     for r in csv.DictReader(open(path)):
         b = (float(r["dram_read_MB_per_launch"]) + float(r["dram_write_MB_per_launch"])) * 1e6

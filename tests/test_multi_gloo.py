@@ -98,3 +98,18 @@ def test_tp_handle_exchange_rejects_bad_input():
         gather_tp_handles(ok, 0, 2, lambda o: [o, (0, ok)])              # the same rank twice
     with pytest.raises(ValueError):
         gather_tp_handles(ok, 0, 2, lambda o: [o, (1, bytes(8))])        # short handle from a peer
+
+
+@pytest.mark.timeout(600)
+def test_reference_arm_prints_one_json_line():
+    """`bench.py --impl reference` (the oracle on the host cores, bounded sample) end to end: one JSON line with the contract's keys."""
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-tokens", "2"],
+                       capture_output=True, text=True, env=env, timeout=580)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [ln for ln in p.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1, p.stderr[-2000:]
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "decode_tokens_per_s" and d["value"] > 0
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
