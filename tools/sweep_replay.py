@@ -88,6 +88,11 @@ def main():
     lib = _lib.load()
     models = args.models.split(",")
     shards = shard_models(models, args.gpus)
+    # GPUs left over (8 GPUs, 7 models): a second replica of the models that take longest per request
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
+    spare = args.gpus - len(shards)
+    for m in sorted(models, key=lambda m: -ARCHS[m].weight_bytes_q4())[:max(0, spare)]:
+        shards.append([m])
     rows = run_table(args.repetitions, args.seed, models, args.lengths.split(","))
     os.makedirs(args.out, exist_ok=True)
     procs = []
@@ -98,11 +103,20 @@ def main():
                                            "--port", str(args.port + i), "--preload", ",".join(ms)], cwd=ROOT, stdout=log, stderr=log))
         for i in range(len(shards)):
             wait_ready(args.port + i, time.time() + 300)
-        where = {m: i for i, ms in enumerate(shards) for m in ms}
+        # rows of a model go to its server; a model with two replicas has its rows dealt alternately
+        where = {}
+        for i, ms in enumerate(shards):
+            for m in ms:
+                where.setdefault(m, []).append(i)
+        seen = {}
+        for r in rows:
+            k = seen.get(r["model"], 0)
+            seen[r["model"]] = k + 1
+            r["_server"] = where[r["model"]][k % len(where[r["model"]])]
         done, lock = [], threading.Lock()
 
         def client(i):
-            for r in [r for r in rows if where[r["model"]] == i]:
+            for r in [r for r in rows if r["_server"] == i]:
                 prompt = f"In {r['length']} words, please give me information about " + r["topic"]      # RunnerConfig.py:120
                 e0, e1 = C.c_uint64(), C.c_uint64()
                 lib.b2_nvml_energy_mj(i, C.byref(e0))
