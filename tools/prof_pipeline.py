@@ -29,5 +29,8 @@ print("kernel: [ns since layer start]  first CTA start | median: loads issued, w
 for k in range(9):
     x = d[per_tok + 4 * 10 + k] - base
     print(f"{names[k % 4]:8s} start {x[:,0].min():7.0f} | " + " ".join(f"{np.median(x[:, i]):7.0f}" for i in range(1, 6)) + f" | end {x[:,5].max():7.0f}")
+    if len(sys.argv) > 2:   # spread over the CTAs: min / max of every stamp
+        print("          min    " + " ".join(f"{x[:, i].min():7.0f}" for i in range(0, 6)))
+        print("          max    " + " ".join(f"{x[:, i].max():7.0f}" for i in range(0, 6)))
 tok = d[per_tok:, :, :]
 print("token time (first start -> last flush of the LM head):", (tok[-1, :, 5].max() - tok[0, :, 0].min()) / 1e3, "us")
