@@ -502,18 +502,29 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
         const int ex = max((int)((__float_as_uint(m) >> 23) & 0xFF) - 127, -100);
         const float sc = __uint_as_float((uint32_t)(ex - (ACT_BITS - 1) + 127) << 23);
         const float inv = __uint_as_float((uint32_t)((ACT_BITS - 1) - ex + 127) << 23);
-        uint32_t w0 = 0, w1 = 0, w2 = 0;
+        // Balanced base-128 digits of four elements at once (same digits as act_digits, fewer instructions: every CTA grids the
+        // whole vector, sixteen warps on four issue ports).  With U = X + 64*(1 + 128 + 16384) > 0 the digits biased by 64 are
+        // U & 127, (U >> 7) & 127 and U >> 14; the low bytes of the four U (U >> 7, U >> 14) are gathered with PRMT, and
+        // "- 64" on 7-bit fields is a flip of bit 6 followed by its sign extension into bit 7.  The top digit can reach +64
+        // (|X| = 2^20 after rounding), so it is not masked but de-biased per element.
         int xsum = 0;
+        uint32_t U[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            int d0, d1, d2;
             const int X = __float2int_rn(yv[e] * inv);
             xsum += X;
-            act_digits(X, d0, d1, d2);
-            w0 |= (uint32_t)(d0 & 0xFF) << (8 * e);
-            w1 |= (uint32_t)(d1 & 0xFF) << (8 * e);
-            w2 |= (uint32_t)(d2 & 0xFF) << (8 * e);
+            U[e] = (uint32_t)(X + 64 * (1 + 128 + 16384));
         }
+        auto gather = [](uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3) {   // byte 0 of each word
+            return __byte_perm(__byte_perm(a0, a1, 0x0040), __byte_perm(a2, a3, 0x0040), 0x5410);
+        };
+        auto debias7 = [](uint32_t w) {   // four 7-bit fields u -> int8 (u - 64)
+            const uint32_t tt = (w & 0x7F7F7F7Fu) ^ 0x40404040u;
+            return tt | ((tt & 0x40404040u) << 1);
+        };
+        const uint32_t w0 = debias7(gather(U[0], U[1], U[2], U[3]));
+        const uint32_t w1 = debias7(gather(U[0] >> 7, U[1] >> 7, U[2] >> 7, U[3] >> 7));
+        const uint32_t w2 = gather((U[0] >> 14) - 64u, (U[1] >> 14) - 64u, (U[2] >> 14) - 64u, (U[3] >> 14) - 64u);
         const int b = q >> 3, k = q & 7;                    // elements 4k..4k+3 of block b
         uint8_t *dst = sact + a3_off(b, 0, 4 * k);
         *(uint32_t *)dst = w0;
