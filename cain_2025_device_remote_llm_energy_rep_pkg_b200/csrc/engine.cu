@@ -332,7 +332,7 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, const Mode
         B2_CHECK(cfg->n_kv_heads % tp == 0, B2_EINVAL, "%d KV heads do not split over %d ranks", cfg->n_kv_heads, tp);
         B2_CHECK(cfg->ffn % (QK * tp) == 0, B2_EINVAL, "ffn %d does not split over %d ranks in whole blocks", cfg->ffn, tp);
         B2_CHECK(cfg->hidden <= TP_MAX_VEC, B2_EINVAL, "hidden %d exceeds the exchange slots (%d)", cfg->hidden, TP_MAX_VEC);
-        bool kq = mt.embd != B2_T_Q4_0 && false;
+        bool kq = false;
         for (const LayerTypes &lt : mt.layers) kq = kq || lt.o != B2_T_Q4_0 || lt.down != B2_T_Q4_0;
         if (kq) {   // a column window of a K-quant matrix must start and end on a 256-element super-block
             B2_CHECK((cfg->n_heads / tp * cfg->head_dim) % 256 == 0 && (cfg->ffn / tp) % 256 == 0, B2_EINVAL,

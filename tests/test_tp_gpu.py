@@ -68,6 +68,15 @@ def _worker(rank, world, port, case, out_dir):
         res["prefill_logits"] = sess.prefill(PROMPT, want_logits=True)
         samp = engine.SamplerCfg(8, 0.8, 0.95, 1234)
         res["sampled"] = sess.decode(24, sampler=samp)
+    elif case["kind"] == "tiny_kq":   # K-quant layer matrices (column windows on super-block borders) and a Q6_K head, from host tensors
+        from oracle import randinit as orand
+        a, oa = tp_arch(case["key"])
+        tensors = orand.make_model(oa, seed=case["seed"], qtype="q4_k", head_qtype="q6_k")
+        model = engine.Model.from_tensors(eng, a, tensors, max_ctx=96)
+        sess = model.session(96)
+        res["logits"] = sess.forward_tokens(PROMPT)
+        sess.reset()
+        res["greedy"] = sess.generate_greedy(PROMPT, 40)
     else:
         a = archs.ARCHS[case["key"]]
         prompt = tokenizer.encode("In 100 words, please give me information about United States", a.V, a.family)
@@ -126,3 +135,23 @@ def test_tp2_llama31_8b_full_size_greedy_256(lib, tmp_path):
     scale = G[key + "/absmax"][[0, 1, 127, 255]]
     assert np.abs(r0["logits_sub"] - G[key + "/logits_sub"]).max() <= 1e-3 * scale.max()
     print(f"tp2 llama3.1:8b decode {float(r0['tok_per_s']):.1f} tokens/s")
+
+
+@needs2
+@pytest.mark.timeout(600)
+def test_tp2_q4k_layers_q6k_head_match_oracle(lib, tmp_path):
+    """Q4_K layer matrices and a Q6_K LM head split over two ranks (what config 4 of SURVEY.md 8d names): each rank packs its
+    column window of attn_output / ffn_down from the host GGML super-blocks; logits and greedy tokens against the oracle."""
+    from oracle import randinit as orand
+    from oracle.model import OracleModel
+    key = "llama3.1:8b"
+    a, oa = tp_arch(key)
+    assert a.H % 256 == 0 and (a.I // 2) % 256 == 0 and (a.nh // 2 * a.hd) % 256 == 0
+    r0, r1 = run_case(tmp_path, {"kind": "tiny_kq", "key": key, "seed": 21})
+    assert np.array_equal(r0["logits"], r1["logits"]) and np.array_equal(r0["greedy"], r1["greedy"])
+    tensors = orand.make_model(oa, seed=21, qtype="q4_k", head_qtype="q6_k")
+    om = OracleModel(oa, tensors)
+    os_ = om.session(96)
+    want = np.stack([os_.step(t).numpy() for t in PROMPT])
+    assert np.abs(r0["logits"] - want).max() <= 2e-4 * np.abs(want).max()      # bar of the single-GPU K-quant test (test_q4k_gpu.py)
+    assert list(map(int, r0["greedy"])) == om.session(96).generate_greedy(PROMPT, 40)
