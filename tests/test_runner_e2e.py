@@ -50,7 +50,7 @@ def test_unchanged_runner_end_to_end(tmp_path):
     cols = list(rows[0].keys())
     assert ref_header[-1] == "energy_usage_J" and cols[-1] == "energy_usage_J"
     assert cols[: len(ref_header) - 1] == ref_header[:-1]
-    assert [c for c in rows[0] if c.startswith("nvml__")] == [c.column for c in nvml_energy.ALL_COLUMNS]
+    assert [c for c in rows[0] if c.startswith(("nvml__", "rapl__"))] == [c.column for c in nvml_energy.ALL_COLUMNS]
     assert len(rows) == 2 and {r["method"] for r in rows} == {"remote", "on_device"}
     for r in rows:
         assert r["__done"] == "DONE" and r["model"] == "qwen2:1.5b" and r["length"] == "100"
@@ -98,3 +98,21 @@ def test_jsonpickle_shim_round_trip():
         if str(REF / "experiment-runner") in sys.path:
             sys.path.remove(str(REF / "experiment-runner"))
         sys.modules.pop("jsonpickle", None)
+
+
+def test_rapl_reader_sums_packages_and_handles_wraparound(tmp_path):
+    """Host CPU energy for the plugin's rapl__cpu_energy_J column, on a fake powercap tree (two packages, one sub-domain that
+    must be ignored, one counter wrapping inside the window)."""
+    for name, e, mx in (("intel-rapl:0", 1_000_000, 10_000_000), ("intel-rapl:1", 9_500_000, 10_000_000), ("intel-rapl:0:0", 5, 100)):
+        d = tmp_path / name
+        d.mkdir()
+        (d / "energy_uj").write_text(str(e))
+        (d / "max_energy_range_uj").write_text(str(mx))
+    r = nvml_energy.RaplReader(str(tmp_path))
+    assert len(r.domains) == 2
+    a = r.read_uj()
+    (tmp_path / "intel-rapl:0" / "energy_uj").write_text("3000000")     # + 2 J
+    (tmp_path / "intel-rapl:1" / "energy_uj").write_text("500000")      # wrapped: 9.5 -> 10 -> 0.5 = + 1 J
+    b = r.read_uj()
+    assert r.delta_j(a, b) == pytest.approx(3.0)
+    assert nvml_energy.RaplReader(str(tmp_path / "missing")).read_uj() is None
