@@ -86,4 +86,16 @@ __device__ __forceinline__ void act_digits(int X, int &d0, int &d1, int &d2) {
     d1 = ((X1 + 64) & 127) - 64;
     d2 = (X1 - d1) >> 7;
 }
+// arg-max with the lowest index on ties (greedy sampler)
+__device__ __forceinline__ void arg_better(float &v, int &i, float ov, int oi) {
+    if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+}
+__device__ __forceinline__ void warp_argmax(float &v, int &i) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, v, o);
+        int oi = __shfl_xor_sync(0xffffffffu, i, o);
+        arg_better(v, i, ov, oi);
+    }
+}
 #endif

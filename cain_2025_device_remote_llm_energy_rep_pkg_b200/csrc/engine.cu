@@ -48,6 +48,7 @@ extern "C" const char *b2_version(void) { return "b2llm 0.1 (sm_100a)"; }
 //                                                        peers (and by this rank, into its own slot) from inside their GEMVs
 //   u64   forwards                                       forward passes this rank has completed (the tags derive from it)
 //   u32   error                                          1 + a rank whose pairs did not arrive in time (sticky)
+//   u4    amax[8 source ranks]                           (best logit, its index, tag, tag) of every rank's share of the vocabulary
 // Buffer 0 carries the O-projection rounds, buffer 1 the down-projection rounds, so a rank that is one exchange ahead never
 // overwrites slots a slower rank still reads (a rank cannot be two exchanges ahead: each exchange needs every rank's pairs).
 #define TP_MAX_VEC 8192
@@ -58,7 +59,8 @@ struct TpLink {
     void *peer[TP_MAX_RANKS] = {};
     bool connected = false;
     static constexpr size_t slots_bytes() { return (size_t)2 * TP_MAX_RANKS * TP_MAX_VEC * 8; }
-    static constexpr size_t bytes() { return slots_bytes() + 256; }
+    static constexpr size_t bytes() { return slots_bytes() + 512; }
+    void *amax(int on_rank) const { return (char *)peer[on_rank] + slots_bytes() + 256; }
     void *slot(int on_rank, int buf, int src) const { return (char *)peer[on_rank] + ((size_t)buf * TP_MAX_RANKS + src) * TP_MAX_VEC * 8; }
     unsigned long long *forwards() const { return (unsigned long long *)((char *)local + slots_bytes()); }
     unsigned int *error() const { return (unsigned int *)((char *)local + slots_bytes() + 128); }
@@ -112,7 +114,7 @@ struct b2_model {
     int q_dim() const { return heads() * cfg.head_dim; }
     int kv_dim() const { return kv_heads() * cfg.head_dim; }
 };
-enum { G_PREFILL_BODY = 0, G_PREFILL_LAST, G_DECODE, G_DECODE_LOG, G_FORCED, G_SAMPLE, G_SAMPLE_LOG, G_COUNT };
+enum { G_PREFILL_BODY = 0, G_PREFILL_LAST, G_DECODE, G_DECODE_LOG, G_FORCED, G_SAMPLE, G_SAMPLE_LOG, G_DECODE_VP, G_COUNT };   // _VP: tensor parallel, LM head split by rows
 struct b2_session {
     b2_model *m = nullptr;
     int max_ctx = 0, n_pages = 0;
@@ -155,7 +157,7 @@ struct b2_session {
     int graph_launches[G_COUNT][2] = {};
     // greedy decode also exists as a graph of `multi_n` consecutive tokens (B2_GRAPH_TOKENS, default 8): fewer graph launches,
     // no gap between the tokens of one graph
-    cudaGraphExec_t multi[2] = {};
+    cudaGraphExec_t multi[2][2] = {};   // [G_DECODE / G_DECODE_VP][attention variant]
     int multi_n = 8;
     bool use_graphs = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -628,12 +630,31 @@ __global__ void k_copy_logits(const float *logits, int n, float *log, const DevS
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = logits[i];
 }
 
+// CTAs (= arg-max partials) of the LM-head GEMV of a tensor-parallel rank: replicated over the whole vocabulary, or over its row window
+static int tp_head_grid(const b2_model *m, bool vp) { return gemv_grid((int)ntiles(vp ? m->cfg.vocab / m->tp : m->cfg.vocab), 1); }
+static bool tp_vocab_parallel(const b2_model *m) {
+    static int off = -1;   // B2_TP_REPLICATED_HEAD=1: every rank multiplies the whole LM head in every step
+    if (off < 0) { const char *e = getenv("B2_TP_REPLICATED_HEAD"); off = (e && e[0] == '1') ? 1 : 0; }
+    return m->tp > 1 && !off && m->cfg.vocab % (TILE_ROWS * m->tp) == 0;
+}
+// greedy token of the step: arg-max over the partials of the last LM-head GEMV (tensor parallel: exchanged between the ranks)
+static void enqueue_greedy_pick(b2_session *s) {
+    b2_model *m = s->m;
+    cudaStream_t st = m->e->stream;
+    if (m->tp == 1) { launch_argmax_partials(s->pmax, s->pidx, s->head_grid, s->d_sampled, st); return; }
+    const TpLink &L = m->e->tp;
+    void *peers[TP_MAX_RANKS] = {};
+    for (int p = 0; p < L.n; ++p) peers[p] = L.amax(p);
+    launch_tp_argmax(s->pmax, s->pidx, std::max(tp_head_grid(m, false), tp_head_grid(m, true)), peers, L.n, L.rank, L.amax(L.rank), L.forwards(), L.error(),
+                     s->d_sampled, st);
+}
+
 // The same pass on one rank of a tensor-parallel group.  Per layer: QKV of this rank's heads, attention over them, O projection
 // of this rank's columns (partial rows -> every rank's slots, buffer 0), gate/up of this rank's rows (its prologue forms
 // x = residual + sum of the slots), down projection of this rank's columns (-> buffer 1), consumed by the next layer's QKV or by
 // the LM head (replicated: every rank computes all logits from the same x, so all ranks sample the same token without a further
 // exchange).  The residual alternates between two buffers: a consumer's CTA 0 writes the new one while the others read the old.
-static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
+static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx, bool vp) {
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     const TpLink &L = m->e->tp;
@@ -688,7 +709,16 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
         e = launch_gemv_tp(producer(1, 2 * l + 1), qt_of(ly.down.type), GEMV_IN_F32, GEMV_OUT_TPPART, ly.down.packed, H, I, nullptr, 0.f, 0, s->h, nullptr, nullptr, 0,
                            nullptr, nullptr, nullptr, st, pdl); n++;
     }
-    if (e == cudaSuccess && with_head) {
+    if (e == cudaSuccess && with_head && vp) {
+        // vocabulary-parallel LM head: this rank's window of rows (whole 16-row tiles, so the window is a pointer offset into the
+        // packed matrix); logits land in their place of the full vector, arg-max partials carry indices of the whole vocabulary
+        const int64_t Vl = c.vocab / N, row0 = (int64_t)rk * Vl;
+        const uint64_t off = (uint64_t)(row0 / TILE_ROWS) * nblocks_padded(H) * (packed_bytes_of(m->head.type, TILE_ROWS, H) / nblocks_padded(H));
+        int gvp = 0;
+        if (tp_head_grid(m, true) < tp_head_grid(m, false)) { launch_fill_partials(s->pmax, s->pidx, 1024, st); n++; }   // tiny vocabularies: fewer CTAs than the replicated head left partials for
+        e = launch_gemv_tp(consumer(1, 2 * c.n_layers - 1), qt_of(m->head.type), GEMV_IN_TPNORM, GEMV_OUT_LOGITS, (const char *)m->head.packed + off, Vl, H,
+                           m->out_norm, c.rms_eps, c.norm_plus_one, nullptr, s->logits + row0, nullptr, 0, s->pmax, s->pidx, &gvp, st, pdl, (int)row0); n++;
+    } else if (e == cudaSuccess && with_head) {
         e = launch_gemv_tp(consumer(1, 2 * c.n_layers - 1), qt_of(m->head.type), GEMV_IN_TPNORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, m->out_norm, c.rms_eps,
                            c.norm_plus_one, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, &s->head_grid, st, pdl); n++;
     }
@@ -699,8 +729,8 @@ static int enqueue_forward_tp(b2_session *s, bool with_head, int attn_ctx) {
 }
 
 // enqueue one forward pass for the token in state->cur_token at position state->pos; returns #launches
-static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx) {
-    if (s->m->tp > 1) return enqueue_forward_tp(s, with_head, attn_ctx);
+static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx, bool vp = false) {
+    if (s->m->tp > 1) return enqueue_forward_tp(s, with_head, attn_ctx, vp);
     b2_model *m = s->m;
     const b2_arch_cfg &c = m->cfg;
     cudaStream_t st = m->e->stream;
@@ -783,10 +813,11 @@ static int enqueue_graph_body(b2_session *s, int which, int variant) {
         break;
     case G_DECODE:
     case G_DECODE_LOG:
+    case G_DECODE_VP:
         if (which == G_DECODE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
-        launch_argmax_partials(s->pmax, s->pidx, s->head_grid, s->d_sampled, st); n++;
+        enqueue_greedy_pick(s); n++;
         k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
-        n += enqueue_forward(s, true, attn_ctx);
+        n += enqueue_forward(s, true, attn_ctx, which == G_DECODE_VP);
         k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
         break;
     }
@@ -797,8 +828,9 @@ static void drop_graphs(b2_session *s) {
     for (int g = 0; g < G_COUNT; ++g)
         for (int v = 0; v < 2; ++v)
             if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
-    for (int v = 0; v < 2; ++v)
-        if (s->multi[v]) { cudaGraphExecDestroy(s->multi[v]); s->multi[v] = nullptr; }
+    for (int k = 0; k < 2; ++k)
+        for (int v = 0; v < 2; ++v)
+            if (s->multi[k][v]) { cudaGraphExecDestroy(s->multi[k][v]); s->multi[k][v] = nullptr; }
 }
 
 // run graph `which` for `times` consecutive positions starting at `pos0` (captured lazily; plain launches when B2_NO_GRAPH=1).
@@ -809,8 +841,9 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
         const int v = (pos0 + i) < ATTN_SHORT_CTX ? 0 : 1;
         // several greedy tokens in one graph while they all use the same attention variant
         const int U = s->multi_n;
-        if (which == G_DECODE && s->use_graphs && U > 1 && times - i >= U && ((pos0 + i + U - 1) < ATTN_SHORT_CTX ? 0 : 1) == v) {
-            if (!s->multi[v]) {
+        if ((which == G_DECODE || which == G_DECODE_VP) && s->use_graphs && U > 1 && times - i >= U && ((pos0 + i + U - 1) < ATTN_SHORT_CTX ? 0 : 1) == v) {
+            const int mk = which == G_DECODE_VP ? 1 : 0;
+            if (!s->multi[mk][v]) {
                 cudaGraph_t g = nullptr;
                 B2_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
                 int nl = 0;
@@ -819,11 +852,11 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
                 cudaError_t e1 = cudaStreamEndCapture(st, &g);
                 if (e1 == cudaSuccess && s->enqueue_error != cudaSuccess) { e1 = s->enqueue_error; cudaGraphDestroy(g); }
                 if (e1 != cudaSuccess) { b2_set_error("graph capture failed: %s", cudaGetErrorString(e1)); return B2_ECUDA; }
-                cudaError_t e2 = cudaGraphInstantiate(&s->multi[v], g, 0);
+                cudaError_t e2 = cudaGraphInstantiate(&s->multi[mk][v], g, 0);
                 cudaGraphDestroy(g);
                 if (e2 != cudaSuccess) { b2_set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return B2_ECUDA; }
             }
-            B2_CUDA(cudaGraphLaunch(s->multi[v], st));
+            B2_CUDA(cudaGraphLaunch(s->multi[mk][v], st));
             s->stats.kernel_launches += (uint64_t)s->graph_launches[which][v] * U;
             i += U - 1;
             continue;
@@ -1210,7 +1243,12 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
         B2_CUDA(cudaMemcpyAsync(s->d_draw, &sampler->seed, 8, cudaMemcpyHostToDevice, st));
         B2_TRY(run_graph(s, logits_out ? G_SAMPLE_LOG : G_SAMPLE, n_steps, s->host_pos));
     } else if (s->use_mega) B2_TRY(run_mega(s, MEGA_DECODE, n_steps, 0, logits_out ? s->logits_log : nullptr));
-    else B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps, s->host_pos));
+    else if (!logits_out && n_steps > 1 && tp_vocab_parallel(s->m)) {
+        // all steps but the last with the LM head split over the ranks; the last one replicated, so that the call leaves complete
+        // logits behind whatever the next call wants (sampling, logits_out)
+        B2_TRY(run_graph(s, G_DECODE_VP, n_steps - 1, s->host_pos));
+        B2_TRY(run_graph(s, G_DECODE, 1, s->host_pos + n_steps - 1));
+    } else B2_TRY(run_graph(s, logits_out ? G_DECODE_LOG : G_DECODE, n_steps, s->host_pos));
     B2_CUDA(cudaEventRecord(s->ev1, st));
     B2_CUDA(cudaMemcpyAsync(out_tokens, s->d_out_tokens, (size_t)n_steps * 4, cudaMemcpyDeviceToHost, st));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n_steps * V * 4, cudaMemcpyDeviceToHost, st));

@@ -105,6 +105,7 @@ struct GemvArgs {
     int act;
     float *pmax;             // OUT_LOGITS: per-CTA arg-max partials
     int *pidx;
+    int row_off;             // OUT_LOGITS: index of row 0 in the whole vocabulary (a tensor-parallel rank multiplies a row window of the LM head)
     const float *xsq_in;     // IN_NORM: partial sums of x^2 left by the kernel that produced x (fixed order => deterministic)
     int xsq_n;
     float *xsq_out;          // OUT_RES: this CTA's partial sum of squares of the rows it wrote, at [blockIdx.x]
@@ -551,12 +552,12 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
 // re-synchronised on memory latency every other piece.
 // What the epilogue needs from the argument block, by value: a reference to the kernel parameter would force the whole block
 // into local memory of every thread (this function is not inlined).
-template <bool TP> struct FlushArgs { float *y; int rows, act; };
-template <> struct FlushArgs<true> { float *y; int rows, act; uint2 *tp_dst[8]; int tp_n; uint32_t tp_tag; };
+template <bool TP> struct FlushArgs { float *y; int rows, act, row_off; };
+template <> struct FlushArgs<true> { float *y; int rows, act, row_off; uint2 *tp_dst[8]; int tp_n; uint32_t tp_tag; };
 template <int OUT, class A>
 __device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A &a, uint32_t tptag) {
     FlushArgs<OUT == OUT_TPPART> f;
-    f.y = a.y; f.rows = a.rows; f.act = a.act;
+    f.y = a.y; f.rows = a.rows; f.act = a.act; f.row_off = a.row_off;
     if constexpr (OUT == OUT_TPPART) {
 #pragma unroll
         for (int p = 0; p < 8; ++p) f.tp_dst[p] = a.tp_dst[p];
@@ -609,7 +610,8 @@ __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> 
         } else if (OUT == OUT_LOGITS) {
             if (lane < 16 && row < a.rows) {
                 a.y[row] = yv;
-                if (yv > best_v || (yv == best_v && row < best_i)) { best_v = yv; best_i = row; }
+                const int grow = row + a.row_off;
+                if (yv > best_v || (yv == best_v && grow < best_i)) { best_v = yv; best_i = grow; }
             }
         } else {   // OUT_ACTMUL: rows (2j, 2j+1) = (gate_j, up_j)
             const float up = __shfl_down_sync(0xffffffffu, yv, 1);

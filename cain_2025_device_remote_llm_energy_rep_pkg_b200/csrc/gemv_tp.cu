@@ -10,10 +10,11 @@
 #include "gemv_launch.cuh"
 
 extern int gemv_grid(int n_tiles, int tile_align);
+struct TpArgmaxPeers { uint4 *p[8]; };
 
 cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols,
                            const float *norm_w, float eps, int plus_one, const void *act_in, float *y, const float *bias, int act,
-                           float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl) {
+                           float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl, int row_off) {
     if (tp.n < 2 || tp.n > 8) return cudaErrorInvalidValue;
     GemvArgsTp a;
     size_t smem = 0;
@@ -21,6 +22,7 @@ cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, 
                                     nullptr, 0, nullptr, 0, nullptr, &smem, qt);
     if (em != cudaSuccess) return em;
     a.pf_ptr = nullptr; a.pf_bytes = 0;
+    a.row_off = row_off;
     a.tp_n = tp.n;
     for (int p = 0; p < 8; ++p) a.tp_dst[p] = p < tp.n ? (uint2 *)tp.dst[p] : nullptr;
     a.tp_res = tp.res; a.tp_slots = (const uint2 *)tp.slots; a.tp_slot_stride = tp.slot_stride; a.tp_fwd = tp.fwd;
@@ -64,4 +66,43 @@ __global__ void __launch_bounds__(256) k_tp_close(const uint2 *slots, int slot_s
 void launch_tp_close(const void *slots, int slot_stride, int n, int n_vec, unsigned long long *fwd, int rounds, int round, bool wait, unsigned int *err,
                      cudaStream_t st) {
     k_tp_close<<<1, 256, 0, st>>>((const uint2 *)slots, slot_stride, n, n_vec, fwd, rounds, round, wait ? 1 : 0, err);
+}
+
+// Greedy sampling on a tensor-parallel group.  Every rank reduces the arg-max partials its LM-head GEMV left (over the whole
+// vocabulary when the head ran replicated, over the rank's row window with global indices when it ran vocabulary-parallel),
+// stores (value, index, tag, tag) as ONE 16-byte word into slot [this rank] of every rank's block, reads the tp_n slots of its own
+// block until they carry the tag, and takes the maximum with the lowest index on ties: the same token on every rank.
+__global__ void __launch_bounds__(32) k_tp_argmax(const float *__restrict__ pv, const int *__restrict__ pi, int n, TpArgmaxPeers peers, int tp_n, int rank,
+                                                  const uint4 *slots, const unsigned long long *fwd, unsigned int *err, int *__restrict__ out) {
+    float v = -INFINITY;
+    int idx = 0x7fffffff;
+    for (int b = threadIdx.x; b < n; b += 32) arg_better(v, idx, pv[b], pi[b]);
+    warp_argmax(v, idx);
+    const uint32_t tag = (uint32_t)(__ldcg(fwd) + 1ull) | 0x80000000u;   // never 0; changes with every forward pass
+    if ((int)threadIdx.x < tp_n) {
+        uint4 *dst = threadIdx.x == 0 ? peers.p[0] : threadIdx.x == 1 ? peers.p[1] : threadIdx.x == 2 ? peers.p[2] : threadIdx.x == 3 ? peers.p[3]
+                   : threadIdx.x == 4 ? peers.p[4] : threadIdx.x == 5 ? peers.p[5] : threadIdx.x == 6 ? peers.p[6] : peers.p[7];
+        asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(dst + rank), "r"(__float_as_uint(v)), "r"((uint32_t)idx), "r"(tag), "r"(tag) : "memory");
+        const long long t_begin = global_timer_ns();
+        uint4 w;
+        uint32_t spins = 0;
+        for (;;) {
+            w = ld_volatile_v4(slots + threadIdx.x);
+            if (w.z == tag && w.w == tag) break;
+            if ((++spins & 255u) == 0u && (__ldcg(err) != 0u || global_timer_ns() - t_begin > TP_TIMEOUT_NS)) { atomicCAS(err, 0u, 1u + threadIdx.x); break; }
+        }
+        v = __uint_as_float(w.x);
+        idx = (int)w.y;
+    } else {
+        v = -INFINITY;
+        idx = 0x7fffffff;
+    }
+    warp_argmax(v, idx);
+    if (threadIdx.x == 0) *out = idx;
+}
+void launch_tp_argmax(const float *pmax, const int *pidx, int n, void *const *peer_slots, int tp_n, int rank, const void *local_slots,
+                      const unsigned long long *fwd, unsigned int *err, int32_t *d_out, cudaStream_t st) {
+    TpArgmaxPeers peers;
+    for (int p = 0; p < 8; ++p) peers.p[p] = p < tp_n ? (uint4 *)peer_slots[p] : nullptr;
+    k_tp_argmax<<<1, 32, 0, st>>>(pmax, pidx, n, peers, tp_n, rank, (const uint4 *)local_slots, fwd, err, d_out);
 }

@@ -233,17 +233,6 @@ void launch_attn_decode(const float *d_q, int nh, int nkv, int hd, const int *d_
 // the last block to finish (ticket counter) reduces the per-block partials.
 uint64_t argmax_scratch_bytes() { return ARGMAX_BLOCKS * 8 + 4; }
 
-__device__ __forceinline__ void arg_better(float &v, int &i, float ov, int oi) {
-    if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
-}
-__device__ __forceinline__ void warp_argmax(float &v, int &i) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        float ov = __shfl_xor_sync(0xffffffffu, v, o);
-        int oi = __shfl_xor_sync(0xffffffffu, i, o);
-        arg_better(v, i, ov, oi);
-    }
-}
 __global__ void __launch_bounds__(256) k_argmax(const float *__restrict__ x, int n, int *__restrict__ out, float *__restrict__ pv,
                                                 int *__restrict__ pi, int *__restrict__ counter) {
     __shared__ float sv[8];

@@ -61,7 +61,10 @@ struct GemvTp {
 };
 cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, const void *d_packed, int64_t rows, int64_t cols,
                            const float *norm_w, float eps, int plus_one, const void *act_in, float *y, const float *bias, int act,
-                           float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl);
+                           float *pmax, int *pidx, int *grid_out, cudaStream_t st, bool pdl, int row_off = 0);
+// greedy token of a tensor-parallel group: local arg-max partials -> one tagged 16-byte word per rank -> the same index everywhere
+void launch_tp_argmax(const float *pmax, const int *pidx, int n, void *const *peer_slots, int tp_n, int rank, const void *local_slots,
+                      const unsigned long long *fwd, unsigned int *err, int32_t *d_out, cudaStream_t st);
 void launch_tp_close(const void *slots, int slot_stride, int n, int n_vec, unsigned long long *fwd, int rounds, int round, bool wait, unsigned int *err,
                      cudaStream_t st);
 void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);

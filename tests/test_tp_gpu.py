@@ -68,6 +68,22 @@ def _worker(rank, world, port, case, out_dir):
         res["prefill_logits"] = sess.prefill(PROMPT, want_logits=True)
         samp = engine.SamplerCfg(8, 0.8, 0.95, 1234)
         res["sampled"] = sess.decode(24, sampler=samp)
+        # a greedy call (LM head split over the ranks in all steps but its last) must leave complete logits for whatever comes next:
+        # greedy, then sampled, then logits -- against the same calls on a single-GPU engine with the same weights
+        sess.reset()
+        sess.prefill(PROMPT)
+        g1 = sess.decode(12)
+        s1 = sess.decode(6, sampler=samp)
+        g2, lg2 = sess.decode(3, want_logits=True)
+        res["mixed"] = np.concatenate([g1, s1, g2])
+        res["mixed_logits"] = lg2
+        solo = engine.Model.from_tensors(engine.Engine(rank), a, tensors, max_ctx=320).session(320)
+        solo.prefill(PROMPT)
+        h1 = solo.decode(12)
+        t1 = solo.decode(6, sampler=samp)
+        h2, lh2 = solo.decode(3, want_logits=True)
+        res["solo_mixed"] = np.concatenate([h1, t1, h2])
+        res["solo_mixed_logits"] = lh2
     elif case["kind"] == "tiny_kq":   # K-quant layer matrices (column windows on super-block borders) and a Q6_K head, from host tensors
         from oracle import randinit as orand
         a, oa = tp_arch(case["key"])
@@ -108,8 +124,10 @@ def test_tp2_tiny_matches_oracle_and_ranks_agree(lib, tmp_path, key):
     a, oa = tp_arch(key)
     r0, r1 = run_case(tmp_path, {"kind": "tiny", "key": key, "seed": 42, "n_new": 128})
     # every rank forms the same x in the same order and runs the whole LM head: bit-identical outputs
-    for k in ("logits", "greedy", "logits_devinit", "prefill_logits", "sampled"):
+    for k in ("logits", "greedy", "logits_devinit", "prefill_logits", "sampled", "mixed", "mixed_logits"):
         assert np.array_equal(r0[k], r1[k]), k
+    assert np.array_equal(r0["mixed"], r0["solo_mixed"])          # the tensor-parallel group and one GPU pick the same tokens
+    assert np.abs(r0["mixed_logits"] - r0["solo_mixed_logits"]).max() <= 1e-4 * np.abs(r0["solo_mixed_logits"]).max()
     tensors = engine.host_random_tensors(a, seed=42)
     om = OracleModel(oa, tensors)
     os_ = om.session(320)
