@@ -107,7 +107,8 @@ int b2_engine_device(const b2_engine *e, int *device_ordinal);
  * transport: torch.distributed, a pipe, a file), and every rank passes the tp_size * B2_TP_HANDLE_BYTES bytes to
  * b2_engine_tp_connect, which maps the peers' blocks (needs peer access between the GPUs: NVLink / NVSwitch on a B200 box).
  * From then on every rank must make the same model / session / prefill / decode calls with the same arguments; each rank holds
- * 1/tp_size of every layer matrix, computes all logits itself and returns the same tokens.  A rank whose peer does not show up
+ * 1/tp_size of every layer matrix and returns the same tokens and logits (the LM head is multiplied row-parallel in the steps of
+ * a greedy b2_decode call, with the arg-max exchanged between the ranks, and in full wherever logits are handed out).  A rank whose peer does not show up
  * within 2 s fails the call with B2_ENCCL instead of hanging.  Prompts are evaluated token by token in this mode. */
 #define B2_TP_HANDLE_BYTES 64
 int b2_engine_tp_handle(b2_engine *e, void *handle_out);
