@@ -275,6 +275,12 @@ def run_ours(args):
     r = bench_model(eng, args.model, args, lib, local, dist, args.steps, args.warmup)
     if tp:
         r["kv_bytes_per_token"] /= world
+        a_ = ARCHS[args.model]
+        if a_.V % (16 * world) == 0 and os.environ.get("B2_TP_REPLICATED_HEAD") != "1":
+            # greedy steps multiply only this rank's rows of the LM head: count 1/N of it, not the whole head the model holds
+            hq = args.head_qtype or args.qtype
+            head = a_.V * a_.H // 256 * 210 if hq == "q6_k" else a_.V * a_.H // 32 * 18
+            r["weight_bytes"] -= head - head // world
     (wall, eval_s), (tokens, launches, energy) = aggregate(dist, r["wall_s"], r["eval_s"], r["tokens"], r["launches"], r["energy_j"])
     if tp:
         tokens = r["tokens"]   # the ranks produced the same tokens once, not N times
