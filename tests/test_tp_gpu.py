@@ -102,6 +102,9 @@ def _worker(rank, world, port, case, out_dir):
         toks, lg = sess.decode(256, want_logits=True)
         res["tokens"] = toks
         res["logits_sub"] = lg[[0, 1, 127, 255]][:, ::97]
+        sess.reset()
+        sess.prefill(prompt)
+        res["tokens_vp"] = sess.decode(256)       # no logits asked for: the LM head runs vocabulary-parallel in all steps but the last
         st = sess.stats()
         res["tok_per_s"] = np.array(st["eval_count"] / (st["eval_ns"] * 1e-9))
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), **res)
@@ -143,16 +146,18 @@ def test_tp2_tiny_matches_oracle_and_ranks_agree(lib, tmp_path, key):
 
 @needs2
 @pytest.mark.timeout(900)
-def test_tp2_llama31_8b_full_size_greedy_256(lib, tmp_path):
-    """The north-star bar on two GPUs: the 256 greedy tokens of the committed oracle fixture, logits within 1e-3 of the scale."""
+@pytest.mark.parametrize("key", ["llama3.1:8b", "mistral:7b", "qwen2:7b", "gemma:7b", "phi3:3.8b", "qwen2:1.5b"])
+def test_tp2_full_size_greedy_256(lib, tmp_path, key):
+    """The north-star bar on two GPUs, for every architecture whose KV heads split in two (gemma:2b has one): the 256 greedy
+    tokens of the committed oracle fixture, logits within 1e-3 of the scale."""
     G = np.load(os.path.join(os.path.dirname(__file__), "golden", "full_size.npz"))
-    key = "llama3.1:8b"
     r0, r1 = run_case(tmp_path, {"kind": "full", "key": key})
     assert np.array_equal(r0["tokens"], r1["tokens"]) and np.array_equal(r0["logits_sub"], r1["logits_sub"])
     assert np.array_equal(r0["tokens"], G[key + "/tokens"])
+    assert np.array_equal(r0["tokens_vp"], G[key + "/tokens"]) and np.array_equal(r1["tokens_vp"], G[key + "/tokens"])
     scale = G[key + "/absmax"][[0, 1, 127, 255]]
     assert np.abs(r0["logits_sub"] - G[key + "/logits_sub"]).max() <= 1e-3 * scale.max()
-    print(f"tp2 llama3.1:8b decode {float(r0['tok_per_s']):.1f} tokens/s")
+    print(f"tp2 {key} decode {float(r0['tok_per_s']):.1f} tokens/s")
 
 
 @needs2
