@@ -84,6 +84,22 @@ def _worker(rank, world, port, case, out_dir):
         h2, lh2 = solo.decode(3, want_logits=True)
         res["solo_mixed"] = np.concatenate([h1, t1, h2])
         res["solo_mixed_logits"] = lh2
+    elif case["kind"] == "missing_peer":   # rank 1 never makes the call: rank 0 must get an error in seconds, not hang
+        import time
+        from cain_2025_device_remote_llm_energy_rep_pkg_b200._lib import B2Error
+        a, _ = tp_arch(case["key"])
+        model = engine.Model.random(eng, a, seed=3, max_ctx=64)
+        sess = model.session(64)
+        dist.barrier()
+        code, dt = 0, 0.0
+        if rank == 0:
+            t0 = time.time()
+            try:
+                sess.prefill(PROMPT)
+            except B2Error as ex:
+                code = ex.code
+            dt = time.time() - t0
+        res["code"], res["seconds"] = np.array(code), np.array(dt)
     elif case["kind"] == "tiny_kq":   # K-quant layer matrices (column windows on super-block borders) and a Q6_K head, from host tensors
         from oracle import randinit as orand
         a, oa = tp_arch(case["key"])
@@ -178,3 +194,14 @@ def test_tp2_q4k_layers_q6k_head_match_oracle(lib, tmp_path):
     want = np.stack([os_.step(t).numpy() for t in PROMPT])
     assert np.abs(r0["logits"] - want).max() <= 2e-4 * np.abs(want).max()      # bar of the single-GPU K-quant test (test_q4k_gpu.py)
     assert list(map(int, r0["greedy"])) == om.session(96).generate_greedy(PROMPT, 40)
+
+
+@needs2
+@pytest.mark.timeout(300)
+def test_tp2_missing_peer_is_an_error_not_a_hang(lib, tmp_path):
+    """Every wait on a peer inside the kernels is bounded (2 s) and leaves a mark: the call of the rank that waited in vain fails
+    with B2_ENCCL, its GPU stays usable (the process goes on to write its result and leave the barrier)."""
+    r0, r1 = run_case(tmp_path, {"kind": "missing_peer", "key": "llama3.1:8b"})
+    assert int(r0["code"]) == -6, int(r0["code"])          # B2_ENCCL
+    assert 1.5 <= float(r0["seconds"]) <= 30.0, float(r0["seconds"])
+    assert int(r1["code"]) == 0
