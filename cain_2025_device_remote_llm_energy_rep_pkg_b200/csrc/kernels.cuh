@@ -4,7 +4,10 @@
 #include "common.cuh"
 
 #define ATTN_NSPLIT 8       // KV splits per head in the decode attention kernel
-#define ATTN_SHORT_CTX 96   // up to this many positions the fused attention runs one CTA per head (no cluster)
+#ifndef ATTN_SHORT_CTX
+#define ATTN_SHORT_CTX 32   // up to this many positions the fused attention runs one CTA per head (no cluster); measured on llama3.1:8b,
+                            // contexts 32..288: 96 -> 659, 64 / 32 / 16 -> 665 tokens/s, 160 -> 641 (the cluster variant wins from the first page pair on)
+#endif
 #define ARGMAX_BLOCKS 128   // stage-1 blocks of the greedy sampler
 
 // device-resident request state: lets a captured CUDA graph be replayed for every token

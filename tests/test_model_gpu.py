@@ -43,17 +43,18 @@ def test_tiny_arch_logits_and_greedy_256(pk, gpu_engine, key):
 
 
 def test_attention_variant_switch_across_the_short_context_limit(pk, gpu_engine):
-    """Positions below ATTN_SHORT_CTX (96) use the one-CTA-per-head attention, later ones the cluster kernel: the greedy stream must not
-    notice (oracle comparison across the boundary)."""
+    """Positions below ATTN_SHORT_CTX (32) use the one-CTA-per-head attention, later ones the cluster kernel: the greedy stream must not
+    notice (oracle comparison across the boundary: a 20-token prompt and 40 new tokens, and an 80-token prompt that starts beyond it)."""
     archs, engine = pk
     a = archs.TINY["llama3.1:8b"]
     tensors = engine.host_random_tensors(a, seed=5)
     model = engine.Model.from_tensors(gpu_engine, a, tensors, max_ctx=160)
     om = OracleModel(OTINY["llama3.1:8b"], tensors)
-    prompt = [(7 * i + 3) % a.V for i in range(80)]
-    got = model.session(160).generate_greedy(prompt, 40)
-    want = om.session(160).generate_greedy(prompt, 40)
-    assert list(map(int, got)) == want
+    for n_prompt in (20, 80):
+        prompt = [(7 * i + 3) % a.V for i in range(n_prompt)]
+        got = model.session(160).generate_greedy(prompt, 40)
+        want = om.session(160).generate_greedy(prompt, 40)
+        assert list(map(int, got)) == want
 
 
 def test_device_random_init_equals_host_blobs(pk, gpu_engine):
