@@ -3,7 +3,9 @@
 #pragma once
 #include "common.cuh"
 
+#ifndef ATTN_NSPLIT
 #define ATTN_NSPLIT 8       // KV splits per head in the decode attention kernel
+#endif
 #ifndef ATTN_SHORT_CTX
 #define ATTN_SHORT_CTX 32   // up to this many positions the fused attention runs one CTA per head (no cluster); measured on llama3.1:8b,
                             // contexts 32..288: 96 -> 659, 64 / 32 / 16 -> 665 tokens/s, 160 -> 641 (the cluster variant wins from the first page pair on)
