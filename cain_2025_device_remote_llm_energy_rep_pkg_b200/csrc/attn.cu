@@ -12,7 +12,11 @@
 #include <stdlib.h>
 #define ATTN_PRE_DEFAULT 0
 
+#ifdef GEMV_EXP_NOWAIT
+__device__ __forceinline__ void pdl_wait_a() {}
+#else
 __device__ __forceinline__ void pdl_wait_a() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 __device__ __forceinline__ void pdl_launch_a() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // NSPLIT = ATTN_NSPLIT: one cluster per head (long contexts).  NSPLIT = 1: one plain CTA per head (contexts up to

@@ -57,7 +57,11 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+#ifdef GEMV_EXP_NOWAIT
+__device__ __forceinline__ void pdl_wait() {}   // what-if experiment: no ordering against the previous kernel (results are garbage)
+#else
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -113,6 +117,7 @@ struct GemvArgs {
     uint64_t pf_total;
     uint32_t l2_window;      // bytes the CTA's L2 prefetch cursor runs ahead of its register loads (0: off)
     uint32_t pf_bytes;       // bytes of the next kernel's weights each CTA pulls into L2 (0: off)
+    uint32_t pf_early;       // 1: that prefetch is issued BEFORE the wait for the input (a kernel that waits long: the O projection behind attention)
     long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
 };
 // The three pointers that differ from layer to layer travel beside the block: in the persistent kernel the block itself is a
@@ -370,9 +375,10 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
     }
 }
 
-// shared memory map (bytes): [header 512: 64 floats of scratch, the input-copy mbarrier at +256][red rb*16*16*4*4 = rb*4096]
+// shared memory map (bytes): [header 1024: 64 floats of scratch, the input-copy mbarrier at +256, at +512 the 128 act*mul values
+//                            of a flush on their way to the activation grid][red rb*16*16*4*4 = rb*4096]
 //                            [A3 of the input nbp*100 (+ fp32 staging)]     rb = GemvArgs::rb, tiles parked between two reductions
-#define GEMV_HDR_SMEM 512
+#define GEMV_HDR_SMEM 1024
 #define GEMV_RB_MAX 16                       // one warp finalises one parked tile
 #define GEMV_FIXED_SMEM(rb) (GEMV_HDR_SMEM + (rb) * 4096)
 
@@ -416,6 +422,20 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
     float *sscale = (float *)(sact + (size_t)a.nbp * 96);
     mbar_wait(bar, parity);
     prof_stamp(6);
+#ifdef GEMV_EXP_NOSTAGE
+    if (true) {   // what-if experiment: the input arrives, nothing is normalised or gridded: an all-zero image (wrong results, valid tokens)
+        for (int ck = 0; ck < cpt; ++ck) {
+            const int kbg = ck * (KC / 4) + warp;
+            if (kbg * 4 >= a.nbp) break;
+            const int q = kbg * 32 + lane, b = q >> 3, k = q & 7;
+            uint8_t *dst = sact + a3_off(b, 0, 4 * k);
+            *(uint32_t *)dst = 0u; *(uint32_t *)(dst + 128) = 0u; *(uint32_t *)(dst + 256) = 0u;
+            if (k == 0) sscale[b] = 0.f;
+        }
+        __syncwarp();
+        return;
+    }
+#endif
     float r = 1.0f;
     if constexpr (IN == IN_TPNORM) {
         // x = res + slot_0 + ... : this warp's columns, in place; the sum of squares needs every warp's share.
@@ -552,12 +572,13 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
 // re-synchronised on memory latency every other piece.
 // What the epilogue needs from the argument block, by value: a reference to the kernel parameter would force the whole block
 // into local memory of every thread (this function is not inlined).
-template <bool TP> struct FlushArgs { float *y; int rows, act, row_off; };
+template <bool TP> struct FlushArgs { float *y; int rows, act, row_off; uint8_t *act_out; int n_out_act; };
 template <> struct FlushArgs<true> { float *y; int rows, act, row_off; uint2 *tp_dst[8]; int tp_n; uint32_t tp_tag; };
 template <int OUT, class A>
 __device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A &a, uint32_t tptag) {
     FlushArgs<OUT == OUT_TPPART> f;
     f.y = a.y; f.rows = a.rows; f.act = a.act; f.row_off = a.row_off;
+    if constexpr (OUT != OUT_TPPART) { f.act_out = OUT == OUT_ACTMUL ? a.act_out : nullptr; f.n_out_act = a.n_out_act; }
     if constexpr (OUT == OUT_TPPART) {
 #pragma unroll
         for (int p = 0; p < 8; ++p) f.tp_dst[p] = a.tp_dst[p];
@@ -617,10 +638,27 @@ __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> 
             const float up = __shfl_down_sync(0xffffffffu, yv, 1);
             const float hv = act_fn(yv, a.act) * up;
             const int pair = tile * 8 + (r >> 1);
-            if (lane < 16 && !(r & 1) && 2 * pair < a.rows) a.y[pair] = hv;
+            if (lane < 16 && !(r & 1)) {
+                if (a.y && 2 * pair < a.rows) a.y[pair] = hv;
+                // on its way to the activation grid: a 32-element block of h is the output of four consecutive tiles
+                if (a.act_out) ((float *)((uint8_t *)red - 512))[warp * 8 + (r >> 1)] = 2 * pair < a.rows ? hv : 0.f;
+            }
         }
     }
     __syncthreads();   // the parked partials may be overwritten from here on
+    if constexpr (OUT == OUT_ACTMUL) {
+        // The down projection reads h as an activation image (as the O projection reads the attention output) instead of
+        // gridding 4*ffn bytes of fp32 in every CTA: tiles are dealt in fours (tile_align), so warp w < batch_n / 4 holds one
+        // whole block, puts it on the grid (oracle/model.py:fxp_round) and stores digits and scale.
+        if (a.act_out && warp < (batch_n >> 2)) {
+            const int blk = (batch_first >> 2) + warp;
+            if (blk * QK < a.n_out_act) {
+                float sv;
+                const int X = act_grid_lane(((const float *)((const uint8_t *)red - 512))[warp * 32 + lane], sv);
+                a3_store_block(a.act_out, a.n_out_act, blk, lane, X, sv);
+            }
+        }
+    }
     return FlushRun{best_v, best_i, sumsq};
 }
 
@@ -778,6 +816,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
             first_loads();
         } else {
             first_loads();
+            if (a.pf_early) prefetch_next();
             input_wait_copy();
             input_stage();
         }
@@ -923,7 +962,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
     stamp(4);
     // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
-    prefetch_next();
+    if (!a.pf_early) prefetch_next();
     if (batch_n > 0) {
         const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
         best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;

@@ -63,16 +63,56 @@ def sampler_from_options(options: dict, default_sampling: bool = False):
     return top_k, temperature, top_p, seed & 0xFFFFFFFFFFFFFFFF
 
 
-def chat_prompt(messages) -> str:
-    """/api/chat: the conversation flattened into one prompt (the byte-level stand-in tokenizer has no chat template)."""
+# Chat forms of the five model families (what their GGUF files carry in tokenizer.chat_template, restated as
+# (per-message format by role, generation prompt)); `{c}` is the message content.
+CHAT_FORMS = {
+    "llama": ({"*": "<|start_header_id|>{role}<|end_header_id|>\n\n{c}<|eot_id|>"}, "<|start_header_id|>assistant<|end_header_id|>\n\n"),
+    "qwen2": ({"*": "<|im_start|>{role}\n{c}<|im_end|>\n"}, "<|im_start|>assistant\n"),
+    "gemma": ({"user": "<start_of_turn>user\n{c}<end_of_turn>\n", "system": "<start_of_turn>user\n{c}<end_of_turn>\n",
+               "assistant": "<start_of_turn>model\n{c}<end_of_turn>\n"}, "<start_of_turn>model\n"),
+    "phi3": ({"*": "<|{role}|>\n{c}<|end|>\n"}, "<|assistant|>\n"),
+    "mistral": ({"user": "[INST] {c} [/INST]", "system": "[INST] {c} [/INST]", "assistant": "{c}</s>"}, ""),
+}
+
+
+def chat_family(family: str, template: str = "") -> str:
+    """The chat form to apply: recognised from the GGUF file's tokenizer.chat_template when it carries one (its marker
+    tokens decide), else the architecture family's."""
+    for fam, marker in (("llama", "<|start_header_id|>"), ("qwen2", "<|im_start|>"), ("gemma", "<start_of_turn>"),
+                        ("phi3", "<|assistant|>"), ("mistral", "[INST]")):
+        if marker in (template or ""):
+            return fam
+    return family
+
+
+def chat_prompt(messages, family: str = "", template: str = "") -> str:
+    """/api/chat: the conversation rendered with the model's chat form (already templated: encode with template=False)."""
     if not isinstance(messages, list) or not messages:
         raise ValueError("messages must be a non-empty list")
-    parts = []
     for m in messages:
         if not isinstance(m, dict) or not isinstance(m.get("content", ""), str):
             raise ValueError("each message needs a string 'content'")
-        parts.append(f"{m.get('role', 'user')}: {m.get('content', '')}")
-    return "\n".join(parts) + "\nassistant:"
+    fam = chat_family(family, template)
+    if fam not in CHAT_FORMS:
+        return "\n".join(f"{m.get('role', 'user')}: {m.get('content', '')}" for m in messages) + "\nassistant:"
+    forms, gen = CHAT_FORMS[fam]
+    out = ""
+    for m in messages:
+        role = str(m.get("role", "user"))
+        out += forms.get(role, forms.get("*", "{c}")).format(role=role, c=m.get("content", ""))
+    return out + gen
+
+
+def parse_keep_alive(v, default: float) -> float:
+    """Ollama's keep_alive: seconds as a number, or "10m" / "30s" / "1h"; negative = keep for good; 0 = unload at once."""
+    if v is None:
+        return default
+    if isinstance(v, (int, float)):
+        return float(v)
+    m = re.fullmatch(r"\s*(-?\d+(?:\.\d+)?)\s*(ms|s|m|h)?\s*", str(v))
+    if not m:
+        raise ValueError(f"bad keep_alive: {v!r}")
+    return float(m.group(1)) * {"ms": 1e-3, "s": 1.0, "m": 60.0, "h": 3600.0, None: 1.0}[m.group(2)]
 
 
 class GenerationResult:
@@ -84,16 +124,39 @@ class B2Backend:
     """Model residency + one serial session per model on one GPU (requests are serialised per backend)."""
 
     def __init__(self, device: int = 0, seed: int = 1, qtype: str = "q4_0", stream_chunk: int = 16, default_sampling: bool = False,
-                 gguf: Optional[Dict[str, str]] = None, requantize: bool = False):
+                 gguf: Optional[Dict[str, str]] = None, requantize: bool = False, keep_alive: float = 300.0):
         from .engine import Engine
         self.engine = Engine(device)
         self.device, self.seed, self.qtype, self.stream_chunk = device, seed, qtype, stream_chunk
         self.default_sampling = default_sampling
         self.gguf = dict(gguf or {})          # tag -> GGUF file: real weights and tokenizer instead of random init + byte stand-in
         self.requantize = requantize
+        self.keep_alive = keep_alive          # seconds a model stays resident after its last request (Ollama: 5 minutes); < 0: for good
         self.tokenizers: Dict[str, object] = {}
+        self.templates: Dict[str, str] = {}   # tag -> tokenizer.chat_template of its GGUF file
         self.models: Dict[str, tuple] = {}
+        self.expiry: Dict[str, float] = {}    # tag -> time.monotonic() after which the model may be unloaded
         self.lock = threading.Lock()
+
+    def chat_template(self, tag: str) -> str:
+        return self.templates.get(tag, "")
+
+    def family(self, tag: str) -> str:
+        try:
+            return self.arch(tag).family
+        except KeyError:
+            return "unknown"
+
+    def _unload(self, tag: str):
+        model, sess, _ = self.models.pop(tag)
+        self.expiry.pop(tag, None)
+        sess.close()
+        model.close()
+
+    def _evict_expired(self, keep: str):
+        now = time.monotonic()
+        for tag in [t for t, e in self.expiry.items() if t != keep and 0 <= e < now]:
+            self._unload(tag)
 
     def list_models(self) -> List[str]:
         return list(ARCHS) + [t for t in self.gguf if t not in ARCHS]
@@ -119,6 +182,7 @@ class B2Backend:
                 model = Model.from_tensors(self.engine, a, g.tensors)
                 if g.tokenizer.tokens:
                     self.tokenizers[tag] = tokenizer.GGUFTokenizer(g.tokenizer, a.family)
+                self.templates[tag] = g.tokenizer.chat_template or ""
             else:
                 a = self.arch(tag)
                 model = Model.random(self.engine, a, seed=self.seed, qtype=self.qtype)
@@ -139,15 +203,21 @@ class B2Backend:
         with self.lock:
             t_start = time.perf_counter_ns()
             e0 = self.energy_mj()
+            keep_s = parse_keep_alive(options.get("_keep_alive"), self.keep_alive)
+            self._evict_expired(tag)
             (model, sess, _), load_ns = self._load(tag)
             a = model.arch
             tk = self.tokenizers.get(tag)
             ptoks = tk.encode(prompt, template=not raw) if tk else tokenizer.encode(prompt, a.V, a.family, template=not raw)
             detok = tk.decode if tk else tokenizer.decode
             budget = int(options.get("num_predict", default_num_predict(prompt)))
-            room = a.max_ctx - len(ptoks)
+            try:   # options.num_ctx: the context window of this request (Ollama default 2048 = the session's size; never larger)
+                ctx = min(a.max_ctx, max(1, int(options.get("num_ctx", a.max_ctx))))
+            except (TypeError, ValueError) as ex:
+                raise ValueError(f"bad num_ctx: {ex}")
+            room = ctx - len(ptoks)
             if room <= 0:
-                raise ValueError(f"prompt of {len(ptoks)} tokens does not fit the {a.max_ctx}-token context")
+                raise ValueError(f"prompt of {len(ptoks)} tokens does not fit the {ctx}-token context")
             reason = "length"
             if budget < 0 or budget > room:
                 budget = room
@@ -171,11 +241,79 @@ class B2Backend:
                     break
             st = sess.stats()
             e1 = self.energy_mj()
+            self.expiry[tag] = -1.0 if keep_s < 0 else time.monotonic() + keep_s
+            if keep_s == 0:
+                self._unload(tag)
             yield {"done": True, "done_reason": reason, "prompt_tokens": ptoks, "tokens": out, "text": detok(out),
                    "total_duration": time.perf_counter_ns() - t_start, "load_duration": load_ns,
                    "prompt_eval_count": st["prompt_eval_count"], "prompt_eval_duration": st["prompt_eval_ns"],
                    "eval_count": st["eval_count"], "eval_duration": st["eval_ns"],
-                   "energy_mj": (e1 - e0) if (e0 is not None and e1 is not None) else None, "device": self.device}
+                   "energy_mj": (e1 - e0) if (e0 is not None and e1 is not None) else None, "device": self.device,
+                   "prompt": options.get("_prompt", prompt)}
+
+
+class MultiBackend:
+    """One backend per GPU behind ONE endpoint: the unchanged reference always calls port 11434
+    (experiment/RunnerConfig.py:130), so K runner processes that share a box all arrive here.  Every GPU may hold every
+    model (the seven tags are 21.4 GB of Q4 weights together against 180 GB per GPU); a request goes to an idle GPU that
+    already has the model resident, else to the least-loaded GPU (which then loads it).  Backends serialise their own
+    requests; different GPUs run concurrently (the C ABI calls release the GIL).  No collective anywhere."""
+
+    def __init__(self, backends):
+        self.backends = list(backends)
+        if not self.backends:
+            raise ValueError("MultiBackend needs at least one backend")
+        self.active = [0] * len(self.backends)
+        self._lock = threading.Lock()
+
+    def list_models(self) -> List[str]:
+        return self.backends[0].list_models()
+
+    def loaded(self) -> List[str]:
+        out = []
+        for b in self.backends:
+            out += [t for t in b.loaded() if t not in out]
+        return out
+
+    def family(self, tag: str) -> str:
+        return self.backends[0].family(tag) if hasattr(self.backends[0], "family") else "unknown"
+
+    def chat_template(self, tag: str) -> str:
+        b = self.backends[0]
+        return b.chat_template(tag) if hasattr(b, "chat_template") else ""
+
+    def busy_devices(self) -> List[int]:
+        with self._lock:
+            return [getattr(b, "device", i) for i, b in enumerate(self.backends) if self.active[i] > 0]
+
+    def pick(self, tag: str) -> int:
+        with self._lock:
+            i = min(range(len(self.backends)),
+                    key=lambda j: (self.active[j], 0 if tag in self.backends[j].loaded() else 1, len(self.backends[j].loaded()), j))
+            self.active[i] += 1
+            return i
+
+    def generate(self, tag: str, prompt: str, options: dict, raw: bool = False) -> Iterator[dict]:
+        i = self.pick(tag)
+        try:
+            yield from self.backends[i].generate(tag, prompt, options, raw=raw)
+        finally:
+            with self._lock:
+                self.active[i] -= 1
+
+
+def parse_devices(spec: str) -> List[int]:
+    """"0-7" / "0,2,5" / "0-3,6" -> device ordinals."""
+    out: List[int] = []
+    for part in filter(None, (p.strip() for p in spec.split(","))):
+        if "-" in part:
+            a, b = part.split("-", 1)
+            out += list(range(int(a), int(b) + 1))
+        else:
+            out.append(int(part))
+    if not out or len(set(out)) != len(out) or min(out) < 0:
+        raise ValueError(f"bad device list: {spec!r}")
+    return out
 
 
 def _now() -> str:
@@ -222,10 +360,13 @@ class Handler(BaseHTTPRequestHandler):
         elif self.path == "/api/version":
             self._send_json(200, {"version": "0.0.0-b2llm"})
         elif self.path == "/api/tags":
-            self._send_json(200, {"models": [{"name": m, "model": m, "details": {"quantization_level": "Q4_0",
-                                                                                 "family": ARCHS[m].family}} for m in b.list_models()]})
+            fam = lambda m: b.family(m) if hasattr(b, "family") else (ARCHS[m].family if m in ARCHS else "unknown")
+            self._send_json(200, {"models": [{"name": m, "model": m, "details": {"quantization_level": "Q4_0", "family": fam(m)}}
+                                             for m in b.list_models()]})
         elif self.path == "/api/ps":
             self._send_json(200, {"models": [{"name": m, "model": m} for m in b.loaded()]})
+        elif self.path.startswith("/b2/active"):   # devices serving a request right now (the powermetrics stand-in samples those)
+            self._send_json(200, {"devices": b.busy_devices() if hasattr(b, "busy_devices") else []})
         elif self.path.startswith("/b2/stats"):
             self._send_json(200, {"requests": self.server.stats_log[-int(self.server.keep_stats):]})
         else:
@@ -246,27 +387,40 @@ class Handler(BaseHTTPRequestHandler):
         model, prompt = req.get("model"), req.get("prompt", "")
         if not isinstance(model, str) or not model:
             return self._error(400, "missing field: model")
+        backend = self.server.backend
+        if model not in backend.list_models():
+            return self._error(404, f"model '{model}' not found")
+        raw_prompt = bool(req.get("raw", False))
         if chat:
             try:
-                prompt = chat_prompt(req.get("messages"))
+                fam = backend.family(model) if hasattr(backend, "family") else (ARCHS[model].family if model in ARCHS else "")
+                tmpl = backend.chat_template(model) if hasattr(backend, "chat_template") else ""
+                prompt = chat_prompt(req.get("messages"), fam, tmpl)
+                raw_prompt = chat_family(fam, tmpl) in CHAT_FORMS   # the conversation already carries the model's chat form
             except ValueError as ex:
                 return self._error(400, str(ex))
         if not isinstance(prompt, str):
             return self._error(400, "prompt must be a string")
-        backend = self.server.backend
-        if model not in backend.list_models():
-            return self._error(404, f"model '{model}' not found")
         stream = req.get("stream", True)
         options = dict(req.get("options") or {})
         options["_stream"] = bool(stream)
+        options["_prompt"] = prompt
+        if "keep_alive" in req:
+            options["_keep_alive"] = req.get("keep_alive")
+        headers_sent = False
         try:
-            gen = backend.generate(model, prompt, options, raw=bool(req.get("raw", False)))
+            if "_keep_alive" in options:
+                parse_keep_alive(options["_keep_alive"], 0.0)
+            gen = backend.generate(model, prompt, options, raw=raw_prompt)
             if stream:
+                first = next(gen)            # a request the engine rejects still gets a plain 4xx/5xx answer
                 self.send_response(200)
                 self.send_header("Content-Type", "application/x-ndjson")
                 self.send_header("Transfer-Encoding", "chunked")
                 self.end_headers()
-                for part in gen:
+                headers_sent = True
+                import itertools
+                for part in itertools.chain([first], gen):
                     if part.get("done"):
                         line = self._final(model, part, "", chat)
                     elif chat:
@@ -284,10 +438,18 @@ class Handler(BaseHTTPRequestHandler):
                     if part.get("done"):
                         final = part
                 self._send_json(200, self._final(model, final, final.get("text", tokenizer.decode(final["tokens"])), chat))
-        except ValueError as ex:
-            self._error(400, str(ex))
         except Exception as ex:  # engine failure: Ollama convention is {"error": ...} with a 5xx
-            self._error(500, f"{type(ex).__name__}: {ex}")
+            code, msg = (400, str(ex)) if isinstance(ex, ValueError) else (500, f"{type(ex).__name__}: {ex}")
+            if not headers_sent:
+                return self._error(code, msg)
+            # the chunked 200 answer is already on the wire: one NDJSON error record, then the terminating chunk
+            self.server.log(f"error {code} in mid-stream: {msg}")
+            try:
+                data = (json.dumps({"error": msg}) + "\n").encode()
+                self.wfile.write(b"%x\r\n%s\r\n0\r\n\r\n" % (len(data), data))
+                self.wfile.flush()
+            except OSError:
+                pass
 
     def _final(self, model: str, part: dict, text: str, chat: bool = False) -> dict:
         rec = {"model": model, "created_at": _now(), "response": text, "done": True, "done_reason": part["done_reason"],
@@ -301,7 +463,7 @@ class Handler(BaseHTTPRequestHandler):
         self.server.record({"t": time.time(), "model": model, "eval_count": part["eval_count"], "eval_duration": part["eval_duration"],
                             "prompt_eval_count": part["prompt_eval_count"], "prompt_eval_duration": part["prompt_eval_duration"],
                             "total_duration": part["total_duration"], "load_duration": part["load_duration"],
-                            "energy_mj": part.get("energy_mj"), "device": part.get("device")})
+                            "energy_mj": part.get("energy_mj"), "device": part.get("device"), "prompt": part.get("prompt")})
         return rec
 
 
@@ -343,6 +505,9 @@ def main():
     ap.add_argument("--host", default="0.0.0.0")
     ap.add_argument("--port", type=int, default=DEFAULT_PORT)
     ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--devices", default=None, help='several GPUs behind this one endpoint, e.g. "0-7" or "0,2,3": one backend per GPU, '
+                    "requests go to an idle GPU that holds the model, else to the least-loaded one")
+    ap.add_argument("--keep-alive", default="5m", help="how long a model stays resident after its last request (Ollama default 5m; -1: for good)")
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--stats-file", default=os.environ.get("B2_STATS_FILE"))
     ap.add_argument("--preload", default="", help="comma-separated model tags to load before serving")
@@ -352,12 +517,15 @@ def main():
                     help="serve TAG from a GGUF file (Q4_0 matrices; real tokenizer and EOS) instead of random-init weights")
     ap.add_argument("--requantize", action="store_true", help="convert non-Q4_0 matrices of a GGUF file to Q4_0 at load (lossy)")
     a = ap.parse_args()
-    backend = B2Backend(a.device, a.seed, default_sampling=a.ollama_sampling,
-                        gguf=dict(x.split("=", 1) for x in a.gguf), requantize=a.requantize)
+    devs = parse_devices(a.devices) if a.devices else [a.device]
+    backs = [B2Backend(d, a.seed, default_sampling=a.ollama_sampling, gguf=dict(x.split("=", 1) for x in a.gguf), requantize=a.requantize,
+                       keep_alive=parse_keep_alive(a.keep_alive, 300.0)) for d in devs]
     for tag in filter(None, a.preload.split(",")):
-        backend._load(tag)
+        for b in backs:
+            b._load(tag)
+    backend = MultiBackend(backs) if len(backs) > 1 else backs[0]
     srv = OllamaServer((a.host, a.port), backend, a.stats_file)
-    srv.log(f"listening on {a.host}:{a.port} (device {a.device})")
+    srv.log(f"listening on {a.host}:{a.port} (device{'s' if len(devs) > 1 else ''} {','.join(map(str, devs))})")
     try:
         srv.serve_forever()
     except KeyboardInterrupt:

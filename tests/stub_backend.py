@@ -35,4 +35,4 @@ class StubBackend:
             yield {"tokens": toks}
         yield {"done": True, "done_reason": "length", "prompt_tokens": ptoks, "tokens": toks, "total_duration": 1000, "load_duration": 0,
                "prompt_eval_count": len(ptoks), "prompt_eval_duration": 10, "eval_count": budget, "eval_duration": max(1, budget) * 1000000,
-               "energy_mj": 1234, "device": 0}
+               "energy_mj": 1234, "device": getattr(self, "device", 0), "prompt": options.get("_prompt", prompt)}

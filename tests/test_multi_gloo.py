@@ -104,6 +104,7 @@ def test_tp_handle_exchange_rejects_bad_input():
 def test_reference_arm_prints_one_json_line():
     """`bench.py --impl reference` (the oracle on the host cores, bounded sample) end to end: one JSON line with the contract's keys."""
     env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    env["B2_LIB"] = "/nonexistent/libb2llm.so"   # the reference arm must not load product code: with this it would fail loudly if it tried
     p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-tokens", "2"],
                        capture_output=True, text=True, env=env, timeout=580)
     assert p.returncode == 0, p.stderr[-2000:]
@@ -113,3 +114,9 @@ def test_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["metric"] == "decode_tokens_per_s" and d["value"] > 0
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    # both arms name the workload with the same dict (the driver compares them)
+    import argparse
+    import bench
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200.archs import ARCHS
+    ours = bench.workload_config(argparse.Namespace(model="llama3.1:8b", qtype="q4_0", head_qtype=None, new_tokens=256, prompt_len=32), ARCHS["llama3.1:8b"])
+    assert d["config"] == ours

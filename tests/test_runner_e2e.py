@@ -65,6 +65,33 @@ def test_unchanged_runner_end_to_end(tmp_path):
     assert (tmp_path / "experiment" / "topics.csv").is_symlink()
 
 
+@pytest.mark.timeout(300)
+def test_two_runner_shards_share_port_11434_and_split_the_rows(tmp_path):
+    """K unchanged runner processes all call :11434 (RunnerConfig.py:130); the rows of ONE seeded run table
+    are dealt over them, the server spreads concurrent requests over its backends, the merged CSV holds every row once and
+    each row's token count comes from its own request (matched by model and prompt)."""
+    if not port_free(11434):
+        pytest.skip("port 11434 is busy")
+    b0, b1 = StubBackend(delay_s=0.6), StubBackend(delay_s=0.6)
+    b0.device, b1.device = 0, 1
+    srv = server.serve(server.MultiBackend([b0, b1]), host="127.0.0.1", port=11434, verbose=False)
+    try:
+        rc = launch.main(["--reference-dir", str(REF), "--work-dir", str(tmp_path), "--name", "e2e", "--cooldown-ms", "0", "--repetitions", "1",
+                          "--models", "qwen2:1.5b,gemma:2b", "--lengths", "100,500", "--shards", "2", "--nvml-devices", "0,1"])
+        assert rc == 0, (tmp_path / "shard0" / "runner.log").read_text()[-3000:]
+    finally:
+        srv.shutdown()
+        srv.server_close()
+    rows = list(csv.DictReader(open(tmp_path / "run_table.csv")))
+    assert len(rows) == 8 and len({r["__run_id"] for r in rows}) == 8 and all(r["__done"] == "DONE" for r in rows)
+    assert {(r["model"], r["method"], r["length"]) for r in rows} == {(m, me, l) for m in ("qwen2:1.5b", "gemma:2b") for me in ("remote", "on_device") for l in ("100", "500")}
+    per_shard = [list(csv.DictReader(open(tmp_path / f"shard{i}" / "experiments_output" / f"e2e_s{i}" / "run_table.csv"))) for i in range(2)]
+    assert [len(t) for t in per_shard] == [4, 4] and not ({r["__run_id"] for r in per_shard[0]} & {r["__run_id"] for r in per_shard[1]})
+    for r in rows:   # 100 words -> 133 tokens, 500 -> 665: the record of this row's own request, not a neighbour's
+        assert float(r["nvml__eval_count"]) == {"100": 133, "500": 665}[r["length"]]
+    assert len(b0.requests) + len(b1.requests) == 8 and len(b0.requests) >= 2 and len(b1.requests) >= 2   # both backends worked
+
+
 def test_shard_assignment_is_a_partition():
     groups = launch.shard_models(launch.MODELS, 8)
     assert sorted(sum(groups, [])) == sorted(launch.MODELS) and len(groups) == 7

@@ -128,7 +128,8 @@ def test_chat_endpoint(srv):
     assert rec["done"] is True and rec["message"]["role"] == "assistant" and isinstance(rec["message"]["content"], str)
     assert "response" not in rec and rec["eval_count"] == 5
     tag, prompt, _ = srv.backend.requests[-1]
-    assert prompt == "system: be brief\nuser: hello\nassistant:"
+    # the model family's chat form (qwen2: ChatML), not a made-up "role: content" flattening; sent to the backend as a raw prompt
+    assert prompt == "<|im_start|>system\nbe brief<|im_end|>\n<|im_start|>user\nhello<|im_end|>\n<|im_start|>assistant\n"
     bad = urllib.request.Request(url(srv, "/api/chat"), data=json.dumps({"model": "qwen2:1.5b", "messages": []}).encode())
     with pytest.raises(urllib.error.HTTPError) as e:
         urllib.request.urlopen(bad, timeout=30)
@@ -137,3 +138,99 @@ def test_chat_endpoint(srv):
     body = json.dumps({"model": "qwen2:1.5b", "options": {"num_predict": 20}, "messages": [{"role": "user", "content": "hi"}]}).encode()
     lines = [json.loads(l) for l in urllib.request.urlopen(urllib.request.Request(url(srv, "/api/chat"), data=body), timeout=30).read().splitlines()]
     assert lines[-1]["done"] is True and all("message" in l for l in lines) and len(lines) >= 3
+
+
+def test_chat_forms_of_the_five_families():
+    msgs = [{"role": "system", "content": "S"}, {"role": "user", "content": "U"}, {"role": "assistant", "content": "A"}, {"role": "user", "content": "Q"}]
+    f = server.chat_prompt
+    assert f(msgs, "llama") == ("<|start_header_id|>system<|end_header_id|>\n\nS<|eot_id|><|start_header_id|>user<|end_header_id|>\n\nU<|eot_id|>"
+                                "<|start_header_id|>assistant<|end_header_id|>\n\nA<|eot_id|><|start_header_id|>user<|end_header_id|>\n\nQ<|eot_id|>"
+                                "<|start_header_id|>assistant<|end_header_id|>\n\n")
+    assert f(msgs[1:2], "gemma") == "<start_of_turn>user\nU<end_of_turn>\n<start_of_turn>model\n"
+    assert f(msgs[1:3], "gemma").endswith("<start_of_turn>model\nA<end_of_turn>\n<start_of_turn>model\n")
+    assert f(msgs[1:2], "phi3") == "<|user|>\nU<|end|>\n<|assistant|>\n"
+    assert f(msgs[1:2], "mistral") == "[INST] U [/INST]"
+    # a single user turn renders exactly as /api/generate's template for the family
+    for fam in ("llama", "qwen2", "gemma", "phi3", "mistral"):
+        assert f([{"role": "user", "content": "hello"}], fam) == tokenizer.TEMPLATES[fam].format(prompt="hello")
+    # the GGUF file's own tokenizer.chat_template decides when present (its marker tokens), whatever the architecture says
+    assert server.chat_family("llama", "{% for m in messages %}<|im_start|>{{ m.role }}...") == "qwen2"
+    assert server.chat_family("llama", "") == "llama"
+    assert f(msgs[1:2], "somethingelse") == "user: U\nassistant:"
+
+
+def test_keep_alive_and_devices_parsing():
+    assert server.parse_keep_alive("5m", 1.0) == 300.0 and server.parse_keep_alive(0, 1.0) == 0.0 and server.parse_keep_alive("-1", 1.0) == -1.0
+    assert server.parse_keep_alive(None, 7.0) == 7.0 and server.parse_keep_alive("1h", 0) == 3600.0 and server.parse_keep_alive("250ms", 0) == 0.25
+    with pytest.raises(ValueError):
+        server.parse_keep_alive("soon", 1.0)
+    assert server.parse_devices("0-3,6") == [0, 1, 2, 3, 6] and server.parse_devices("2") == [2]
+    with pytest.raises(ValueError):
+        server.parse_devices("1,1")
+
+
+def test_two_concurrent_requests_land_on_different_backends():
+    """SURVEY.md §8e / VERDICT r1 #3: K runner processes all call :11434 (RunnerConfig.py:130); the one server owns a backend per
+    GPU and spreads concurrent requests, preferring an idle backend that already holds the model."""
+    import threading
+    b0, b1 = StubBackend(delay_s=0.5), StubBackend(delay_s=0.5)
+    b0.device, b1.device = 0, 1
+    s = server.serve(server.MultiBackend([b0, b1]), host="127.0.0.1", port=0, verbose=False)
+    try:
+        def post(model, n):
+            body = json.dumps({"model": model, "prompt": f"In {n} words, please give me information about X", "stream": False}).encode()
+            return json.loads(urllib.request.urlopen(urllib.request.Request(url(s, "/api/generate"), data=body), timeout=30).read())
+        out = [None, None]
+        ts = [threading.Thread(target=lambda i=i: out.__setitem__(i, post("gemma:2b", 100 + i))) for i in range(2)]
+        for t in ts:
+            t.start()
+        import time as _t
+        _t.sleep(0.25)
+        busy = json.loads(urllib.request.urlopen(url(s, "/b2/active"), timeout=5).read())["devices"]
+        for t in ts:
+            t.join()
+        assert sorted(busy) == [0, 1]
+        assert len(b0.requests) == 1 and len(b1.requests) == 1 and all(o["done"] for o in out)
+        # a lone request for a model goes to the backend that already holds it; a new model to the one with fewer residents
+        post("gemma:2b", 100)
+        post("gemma:2b", 100)
+        assert len(b0.requests) == 3 and len(b1.requests) == 1
+        post("phi3:3.8b", 100)
+        assert b0.requests[-1][0] == "phi3:3.8b" and len(b1.requests) == 1
+        post("phi3:3.8b", 100)                                         # ... and stays where it is resident
+        assert len(b0.requests) == 5 and len(b1.requests) == 1
+        recs = json.loads(urllib.request.urlopen(url(s, "/b2/stats"), timeout=5).read())["requests"]
+        assert {r["device"] for r in recs} == {0, 1} and all("prompt" in r for r in recs)
+    finally:
+        s.shutdown()
+        s.server_close()
+
+
+def test_error_in_mid_stream_ends_the_chunked_answer_cleanly():
+    class Failing(StubBackend):
+        def generate(self, tag, prompt, options, raw=False):
+            yield {"tokens": [1, 2, 3]}
+            raise RuntimeError("engine fell over")
+    s = server.serve(Failing(), host="127.0.0.1", port=0, verbose=False)
+    try:
+        body = json.dumps({"model": "gemma:2b", "prompt": "hi"}).encode()
+        data = urllib.request.urlopen(urllib.request.Request(url(s, "/api/generate"), data=body), timeout=30).read()
+        lines = [json.loads(l) for l in data.splitlines()]            # every line is valid JSON: no second status line in the stream
+        assert lines[0]["done"] is False and "engine fell over" in lines[-1]["error"]
+    finally:
+        s.shutdown()
+        s.server_close()
+
+
+def test_tags_lists_a_model_outside_the_seven_architectures():
+    class WithGguf(StubBackend):
+        def list_models(self):
+            return super().list_models() + ["custom:latest"]
+    s = server.serve(WithGguf(), host="127.0.0.1", port=0, verbose=False)
+    try:
+        tags = json.loads(urllib.request.urlopen(url(s, "/api/tags"), timeout=5).read())["models"]
+        assert {"custom:latest", "llama3.1:8b"} <= {m["name"] for m in tags}
+        assert [m for m in tags if m["name"] == "custom:latest"][0]["details"]["family"] == "unknown"
+    finally:
+        s.shutdown()
+        s.server_close()
