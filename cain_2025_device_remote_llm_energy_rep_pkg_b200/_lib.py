@@ -26,7 +26,8 @@ class TensorDesc(C.Structure):
 
 
 class SamplerCfg(C.Structure):
-    _fields_ = [("top_k", C.c_int32), ("temperature", C.c_float), ("top_p", C.c_float), ("seed", C.c_uint64)]
+    _fields_ = [("top_k", C.c_int32), ("temperature", C.c_float), ("top_p", C.c_float), ("seed", C.c_uint64),
+                ("repeat_penalty", C.c_float), ("repeat_last_n", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -41,7 +42,7 @@ vp, i32, i64, u64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_float
 SIGNATURES = {
     "b2_last_error": (C.c_char_p, []),
     "b2_version": (C.c_char_p, []),
-    "b2_engine_create": (i32, [i32, i32, i32, vp, P(vp)]),
+    "b2_engine_create": (i32, [i32, i32, i32, P(vp)]),
     "b2_engine_destroy": (i32, [vp]),
     "b2_engine_device": (i32, [vp, P(i32)]),
     "b2_engine_tp_handle": (i32, [vp, vp]),
@@ -83,6 +84,7 @@ SIGNATURES = {
     "b2_op_argmax": (i32, [vp, i64, vp]),
     "b2_op_argmax_noalloc": (i32, [vp, i64, vp]),
     "b2_op_sample_topk": (i32, [vp, i64, i32, f32, f32, f32, vp]),
+    "b2_op_sample_topk_penalty": (i32, [vp, i64, i32, f32, f32, f32, vp, i32, f32, i32, vp]),
 }
 
 _lib = None

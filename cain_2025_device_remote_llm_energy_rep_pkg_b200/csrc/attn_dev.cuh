@@ -1,7 +1,5 @@
 // attn_dev.cuh — device side of the fused decode attention (see attn.cu for the design): one (head, context split) work item
-// executed by a group of 128 threads.  Shared by the stand-alone kernel (attn.cu: the group is the CTA, splits merge through
-// distributed shared memory of a cluster) and the persistent token kernel (mega.cu: four groups per CTA, splits merge through a
-// global scratch area and a per-head ticket).
+// executed by a group of 128 threads (attn.cu: the group is the CTA, splits merge through distributed shared memory of a cluster).
 // Numerics follow oracle/model.py: fp32 scores/softmax over f16-rounded K and V (the newest token included).
 #pragma once
 #include "kernels.cuh"
@@ -18,10 +16,8 @@ struct AttnArgs {
     float *out;            // optional fp32 [nh*hd]
     uint8_t *act_out;      // optional A3 image of the output
     int pps_max;           // pages per split the shared-memory score buffer is sized for
-    float *g_part;         // MERGE_GLOBAL: [nh][ATTN_NSPLIT][hd + 2] partials (m, l, o[])
-    int *g_cnt;            // MERGE_GLOBAL: [nh] arrival counters, zero between uses
 };
-enum { MERGE_NONE = 0, MERGE_CLUSTER = 1, MERGE_GLOBAL = 2 };
+enum { MERGE_NONE = 0, MERGE_CLUSTER = 1 };
 
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -306,30 +302,12 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
     if (MERGE == MERGE_CLUSTER) {
         cluster_sync_all();
         finisher = cluster_rank() == 0;
-    } else if (MERGE == MERGE_GLOBAL && nsplit > 1) {
-        // partials to the global scratch area; the last split of the head to arrive merges them
-        float *gp = a.g_part + ((int64_t)h * ATTN_NSPLIT + split) * (hd + 2);
-        group_sync(bar_id);
-        for (int d = tid; d < hd + 2; d += 128) gp[d] = part[d];
-        __threadfence();
-        group_sync(bar_id);
-        if (tid == 0) {
-            const int ticket = atomicAdd(a.g_cnt + h, 1);
-            const bool last = ticket == nsplit - 1;
-            if (last) { __threadfence(); a.g_cnt[h] = 0; }   // nobody else touches the counter before the next token
-            ((int *)red)[4] = last ? 1 : 0;
-        }
-        group_sync(bar_id);
-        finisher = ((int *)red)[4] != 0;
     } else {
         group_sync(bar_id);
     }
     if (finisher) {
         if (MERGE != MERGE_NONE && nsplit > 1) {
-            const float *gbase = a.g_part + (int64_t)h * ATTN_NSPLIT * (hd + 2);
-            auto pm = [&](int r, int idx) -> float {
-                return MERGE == MERGE_CLUSTER ? ld_dsmem_f32(part + idx, r) : __ldcg(gbase + (int64_t)r * (hd + 2) + idx);
-            };
+            auto pm = [&](int r, int idx) -> float { return ld_dsmem_f32(part + idx, r); };
             float M = -INFINITY;
 #pragma unroll
             for (int r = 0; r < ATTN_NSPLIT; ++r)

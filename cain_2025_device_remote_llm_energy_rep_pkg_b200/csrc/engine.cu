@@ -2,7 +2,6 @@
 // Replaces what happens inside Ollama's POST /api/generate (reference call site
 // experiment/RunnerConfig.py:128-131): model load, prompt evaluation, the batch-1 decode loop.
 #include "kernels.cuh"
-#include "mega.cuh"
 #include "prefill.cuh"
 #include "sampler.cuh"
 #include "layout.cuh"
@@ -102,7 +101,6 @@ struct b2_model {
     std::vector<LayerW> layers;
     float *rope_cos = nullptr, *rope_sin = nullptr;
     uint64_t weight_bytes = 0;
-    bool all_q4_0 = true;          // the persistent kernel takes Q4_0 matrices only
     bool layers_q4 = true;         // the tcgen05 prompt GEMM takes Q4_0 / Q4_K layer matrices (a Q6_K head is fine: it runs as a GEMV)
     std::vector<void *> allocs;
     // a rank of a tensor-parallel group holds n_heads / tp query heads, n_kv_heads / tp KV heads and ffn / tp rows of gate / up
@@ -126,6 +124,7 @@ struct b2_session {
     int *d_out_tokens = nullptr;
     int out_cap = 0;
     int *d_sampled = nullptr;
+    int *d_ctx = nullptr;          // the token at every position of the context (the repetition penalty looks back over it)
     float *x = nullptr, *qkv = nullptr, *attn_out = nullptr, *h = nullptr, *logits = nullptr;
     void *act_attn = nullptr, *act_h = nullptr, *attn_scratch = nullptr, *argmax_scratch = nullptr;
     float *pmax = nullptr;
@@ -148,11 +147,6 @@ struct b2_session {
     float *pf_part = nullptr;      // split-K partial sums
     uint64_t pf_part_floats = 0;
     bool use_pf_gemm = true;
-    // persistent token kernel (mega.cu): plan, grid and shared memory; use_mega = false falls back to one kernel per stage
-    MegaPlan *plan = nullptr;
-    bool use_mega = false;
-    int mega_grid_n = 0;
-    size_t mega_smem = 0;
     cudaGraphExec_t graphs[G_COUNT][2] = {};   // [..][0]: positions below ATTN_SHORT_CTX (one attention CTA per head), [..][1]: longer contexts
     int graph_launches[G_COUNT][2] = {};
     // greedy decode also exists as a graph of `multi_n` consecutive tokens (B2_GRAPH_TOKENS, default 8): fewer graph launches,
@@ -179,9 +173,8 @@ static int dev_alloc(std::vector<void *> &owner, void **p, uint64_t n) {
 }
 
 // ------------------------------------------------------------------------------------ engine
-extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, const void *nccl_uid, b2_engine **out) {
+extern "C" int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, b2_engine **out) {
     ApiScope _scope("b2_engine_create");
-    (void)nccl_uid;   // the exchange runs over peer memory mapped with b2_engine_tp_connect, not over a NCCL communicator
     B2_CHECK(out, B2_EINVAL, "b2_engine_create: out is NULL");
     B2_CHECK(tp_size == 1 || tp_size == 2 || tp_size == 4 || tp_size == 8, B2_EINVAL, "b2_engine_create: tensor parallel size %d (1, 2, 4 or 8)", tp_size);
     B2_CHECK(tp_rank >= 0 && tp_rank < tp_size, B2_EINVAL, "b2_engine_create: rank %d of %d", tp_rank, tp_size);
@@ -313,7 +306,6 @@ static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type
     mat.rows = rows;
     mat.cols = cols;
     mat.type = type;
-    if (type != B2_T_Q4_0) m->all_q4_0 = false;
     if (type == B2_T_Q6_K && &mat != &m->embd && &mat != &m->head) m->layers_q4 = false;
     B2_TRY(dev_alloc(m->allocs, &mat.packed, packed_bytes_of(type, rows, cols)));
     B2_CUDA(cudaMemsetAsync(mat.packed, 0, packed_bytes_of(type, rows, cols), m->e->stream));   // row / block padding must be zero
@@ -365,7 +357,7 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, const Mode
                 if ((rc = alloc_mat(m, ly.qkv, qd + 2 * kvd, H, lt.q))) break;
             } else {
                 ly.split_qkv = true;
-                m->all_q4_0 = m->layers_q4 = false;   // the tcgen05 prompt GEMM and the persistent kernel take the fused matrix
+                m->layers_q4 = false;   // the tcgen05 prompt GEMM takes the fused matrix
                 if ((rc = alloc_mat(m, ly.qkv_part[0], qd, H, lt.q))) break;
                 if ((rc = alloc_mat(m, ly.qkv_part[1], kvd, H, lt.k))) break;
                 if ((rc = alloc_mat(m, ly.qkv_part[2], kvd, H, lt.v))) break;
@@ -610,10 +602,11 @@ __global__ void k_load_prompt(DevState *st, const int *prompt) {
     st->cur_token = prompt[st->prompt_idx];
     st->prompt_idx += 1;
 }
-__global__ void k_commit_sample(DevState *st, const int *sampled, int *out_tokens) {
+__global__ void k_commit_sample(DevState *st, const int *sampled, int *out_tokens, int *ctx) {
     int t = *sampled;
     st->cur_token = t;
     out_tokens[st->step] = t;
+    ctx[st->pos] = t;   // the forward pass that follows puts it at position pos
 }
 __global__ void k_advance(DevState *st, int inc_step) {
     st->pos += 1;
@@ -805,8 +798,9 @@ static int enqueue_graph_body(b2_session *s, int which, int variant) {
         if (which == G_SAMPLE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
         k_make_u<<<1, 1, 0, st>>>(s->d_draw, s->d_u); n++;
         launch_sample_topk(s->logits, s->m->cfg.vocab, s->graph_sampler.top_k, s->graph_sampler.temperature, s->graph_sampler.top_p, s->d_u, 0.f,
-                           s->d_sampled, s->sample_scratch, st); n++;
-        k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
+                           s->d_sampled, s->sample_scratch, st, s->d_ctx, &s->state->pos, 0, s->graph_sampler.repeat_penalty,
+                           s->graph_sampler.repeat_last_n); n++;
+        k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens, s->d_ctx); n++;
         launch_fill_partials(s->pmax, s->pidx, 1024, st); n++;   // a later greedy step reads every partial slot
         n += enqueue_forward(s, true, attn_ctx);
         k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
@@ -816,7 +810,7 @@ static int enqueue_graph_body(b2_session *s, int which, int variant) {
     case G_DECODE_VP:
         if (which == G_DECODE_LOG) { k_copy_logits<<<64, 256, 0, st>>>(s->logits, s->m->cfg.vocab, s->logits_log, s->state); n++; }
         enqueue_greedy_pick(s); n++;
-        k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens); n++;
+        k_commit_sample<<<1, 1, 0, st>>>(s->state, s->d_sampled, s->d_out_tokens, s->d_ctx); n++;
         n += enqueue_forward(s, true, attn_ctx, which == G_DECODE_VP);
         k_advance<<<1, 1, 0, st>>>(s->state, 1); n++;
         break;
@@ -884,81 +878,6 @@ static int run_graph(b2_session *s, int which, int times, int pos0) {
     return B2_OK;
 }
 
-// ------------------------------------------------------------------------------------ persistent token kernel
-// Build the constant-memory plan of the session (mega.cuh).  Returns false (and leaves use_mega off) when a shape does not fit
-// the persistent kernel; the session then runs one kernel per stage under CUDA graphs.
-static bool build_mega_plan(b2_session *s) {
-    b2_model *m = s->m;
-    const b2_arch_cfg &c = m->cfg;
-    if (c.n_layers > MEGA_MAX_LAYERS || !s->fused_attn || !m->all_q4_0) return false;
-    const int H = c.hidden, I = m->ffn(), qd = m->q_dim(), hd = c.head_dim;
-    MegaPlan *P = new MegaPlan();
-    memset(P, 0, sizeof *P);
-    size_t smem = 0, sm1 = 0;
-    // the grid is what the kernel's shared memory allows co-resident: fixed point of (plan -> smem -> grid); one CTA per SM
-    const int max_pages = (s->max_ctx + PAGE_TOKENS - 1) / PAGE_TOKENS;
-    const int pps_short = (ATTN_SHORT_CTX + PAGE_TOKENS - 1) / PAGE_TOKENS, pps_long = (max_pages + ATTN_NSPLIT - 1) / ATTN_NSPLIT;
-    const int pps_max = pps_short > pps_long ? pps_short : pps_long;
-    const LayerW &l0 = m->layers[0];
-    int grid = m->e->sm_count > 0 ? m->e->sm_count : 148;
-    bool ok = true;
-    auto mk = [&](GemvArgs &a, int in_mode, const Mat &mt, const float *x, const float *norm_w, const void *act_in, float *y, const float *bias_or_res,
-                  int act, float *pmax, int *pidx, const float *xsq_in, float *xsq_out) {
-        if (gemv_make_args(a, in_mode, mt.packed, mt.rows, mt.cols, x, norm_w, c.rms_eps, c.norm_plus_one, act_in, y, bias_or_res, nullptr, act, pmax,
-                           pidx, nullptr, 0, xsq_in, xsq_in ? grid : 0, xsq_out, &sm1) != cudaSuccess) { ok = false; return; }
-        if (a.k_outer && (a.n_tiles + grid - 1) / grid > GEMV_MAXT) ok = false;   // accumulators of a CTA's tiles must fit its registers
-        if (sm1 > smem) smem = sm1;
-    };
-    mk(P->qkv, GEMV_IN_NORM, l0.qkv, s->x, l0.attn_norm, nullptr, s->qkv, l0.qkv_bias, 0, nullptr, nullptr, s->xsq, nullptr);
-    mk(P->o, GEMV_IN_ACT, l0.o, nullptr, nullptr, s->act_attn, s->x, s->x, 0, nullptr, nullptr, nullptr, s->xsq + 512);
-    mk(P->gateup, GEMV_IN_NORM, l0.gateup, s->x, l0.ffn_norm, nullptr, s->h, nullptr, c.act, nullptr, nullptr, s->xsq + 512, nullptr);
-    mk(P->down, GEMV_IN_F32, l0.down, nullptr, nullptr, s->h, s->x, s->x, 0, nullptr, nullptr, nullptr, s->xsq);
-    mk(P->head, GEMV_IN_NORM, m->head, s->x, m->out_norm, nullptr, s->logits, nullptr, 0, s->pmax, s->pidx, s->xsq, nullptr);
-    const size_t attn_smem = GEMV_FIXED_SMEM(GEMV_RB_MAX) + (size_t)4 * attn_group_floats(hd, pps_max) * 4;
-    if (attn_smem > smem) smem = attn_smem;
-    if (m->heads() * ATTN_NSPLIT > 4 * grid || grid > 512 || (H % QK) != 0) ok = false;   // one attention item per 128-thread group; xsq halves hold 512 partials
-    int g2 = 0;
-    if (ok && mega_grid(smem, &g2) != cudaSuccess) { ok = false; cudaGetLastError(); }
-    if (ok && g2 != grid) ok = false;
-    if (!ok) { delete P; return false; }
-    AttnArgs &A = P->attn;
-    A.qkv = s->qkv; A.nh = m->heads(); A.nkv = m->kv_heads(); A.hd = hd; A.d_pos = nullptr; A.pos_imm = 0;
-    A.cs = m->rope_cos; A.sn = m->rope_sin; A.kc = s->kcache; A.vc = s->vcache; A.page_table = s->page_table;
-    A.out = nullptr; A.act_out = (uint8_t *)s->act_attn; A.pps_max = pps_max;
-    A.g_part = (float *)s->attn_scratch;
-    A.g_cnt = (int *)((float *)s->attn_scratch + (size_t)m->heads() * ATTN_NSPLIT * (hd + 2));
-    P->n_layers = c.n_layers; P->n_embd = H; P->vocab = c.vocab; P->n_part = grid;
-    P->embd_w = (const uint8_t *)m->embd.packed; P->embd_nbp = (int)nblocks_padded(m->embd.cols);
-    P->embd_scale = c.embed_scale ? sqrtf((float)H) : 1.0f;
-    P->x = s->x; P->xsq = s->xsq; P->logits = s->logits; P->pmax = s->pmax; P->pidx = s->pidx;
-    const uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
-    for (int l = 0; l < c.n_layers; ++l) {
-        const LayerW &ly = m->layers[l];
-        MegaLayer &L = P->layers[l];
-        L.qkv_w = (const uint8_t *)ly.qkv.packed; L.o_w = (const uint8_t *)ly.o.packed;
-        L.gateup_w = (const uint8_t *)ly.gateup.packed; L.down_w = (const uint8_t *)ly.down.packed;
-        L.attn_norm = ly.attn_norm; L.ffn_norm = ly.ffn_norm; L.qkv_bias = ly.qkv_bias;
-        L.kc = s->kcache + l * layer_kv; L.vc = s->vcache + l * layer_kv;
-    }
-    (void)I; (void)qd;
-    s->plan = P;
-    s->mega_grid_n = grid;
-    s->mega_smem = smem;
-    s->head_grid = grid;
-    return true;
-}
-
-// n consecutive tokens in one cooperative launch
-static int run_mega(b2_session *s, int mode, int n, int head_from, float *logits_log) {
-    MegaRun r;
-    r.mode = mode; r.n_tokens = n; r.head_from = head_from; r.pos0 = s->host_pos;
-    r.prompt = s->d_prompt; r.out_tokens = s->d_out_tokens; r.logits_log = logits_log; r.state = s->state;
-    cudaError_t e = launch_mega(s->plan, s, r, s->mega_grid_n, s->mega_smem, s->m->e->stream);
-    if (e != cudaSuccess) { b2_set_error("token kernel launch failed: %s", cudaGetErrorString(e)); cudaGetLastError(); return B2_ECUDA; }
-    s->stats.kernel_launches += 1;
-    return B2_OK;
-}
-
 extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     ApiScope _scope("b2_session_create");
     B2_CHECK(m && out, B2_EINVAL, "b2_session_create: NULL");
@@ -997,6 +916,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_prompt, s->prompt_cap * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_out_tokens, s->out_cap * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_sampled, 4))) break;
+        if ((rc = dev_alloc(s->allocs, (void **)&s->d_ctx, (uint64_t)max_ctx * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->x, H * 4 * 2))) break;   // tensor parallel: the residual alternates between the halves
         if ((rc = dev_alloc(s->allocs, (void **)&s->qkv, (qd + 2 * kvd) * 4))) break;
         if ((rc = dev_alloc(s->allocs, (void **)&s->attn_out, qd * 4))) break;
@@ -1045,8 +965,6 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         b2_session_destroy(s);
         return B2_ECUDA;
     }
-    const char *mg = getenv("B2_MEGA");
-    if (mg && mg[0] == '1' && m->tp == 1) s->use_mega = build_mega_plan(s);
     *out = s;
     return B2_OK;
 }
@@ -1055,8 +973,6 @@ extern "C" int b2_session_destroy(b2_session *s) {
     if (!s) return B2_OK;
     if (s->m && s->m->e) cudaSetDevice(s->m->e->device);
     drop_graphs(s);
-    mega_forget(s);
-    delete s->plan;
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->logits_log) cudaFree(s->logits_log);
@@ -1170,7 +1086,7 @@ static int prefill_batched(b2_session *s, int n) {
             int grid = 0;
             B2_CUDA(launch_gemv_qt(qt_of(m->head.type), GEMV_IN_NORM, GEMV_OUT_LOGITS, m->head.packed, c.vocab, H, s->x, m->out_norm, c.rms_eps, c.norm_plus_one, nullptr,
                                 s->logits, nullptr, nullptr, 0, s->pmax, s->pidx, &grid, nullptr, 0, s->xsq, 1, nullptr, st, false));
-            if (!s->use_mega) s->head_grid = grid;
+            s->head_grid = grid;
             launches += 3;
         }
     }
@@ -1188,12 +1104,11 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     cudaStream_t st = s->m->e->stream;
     B2_CUDA(cudaSetDevice(s->m->e->device));
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    B2_CUDA(cudaMemcpyAsync(s->d_ctx + s->host_pos, s->d_prompt, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
     if (s->use_pf_gemm && s->m->layers_q4 && n >= 3) {
         B2_TRY(prefill_batched(s, n));
-    } else if (s->use_mega) {
-        B2_TRY(run_mega(s, MEGA_PROMPT, n, n - 1, nullptr));
     } else {
         if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1, s->host_pos));
         B2_TRY(run_graph(s, G_PREFILL_LAST, 1, s->host_pos + n - 1));
@@ -1220,6 +1135,7 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
         B2_CHECK(sampler->top_k <= SAMPLE_MAX_K, B2_EINVAL, "b2_decode: top_k %d > %d", sampler->top_k, SAMPLE_MAX_K);
         B2_CHECK(sampler->temperature > 0.f, B2_EINVAL, "b2_decode: temperature must be > 0 (use top_k <= 1 for greedy)");
         B2_CHECK(sampler->top_p > 0.f && sampler->top_p <= 1.0f, B2_EINVAL, "b2_decode: top_p must be in (0, 1]");
+        B2_CHECK(sampler->repeat_penalty >= 0.f && sampler->repeat_last_n >= 0, B2_EINVAL, "b2_decode: repeat_penalty / repeat_last_n must not be negative");
     }
     B2_CHECK(s->host_pos + n_steps <= s->max_ctx, B2_ECTX, "b2_decode: %d + %d tokens exceed the context window %d", s->host_pos, n_steps, s->max_ctx);
     B2_CHECK(n_steps <= s->out_cap, B2_EINVAL, "b2_decode: n_steps %d > %d", n_steps, s->out_cap);
@@ -1233,7 +1149,8 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
         // k / T / p are kernel arguments inside the captured graphs: new values -> new graphs.  The seed travels through device
         // memory; the draw counter continues across calls (reset by b2_session_reset).
         if (sampler->top_k != s->graph_sampler.top_k || sampler->temperature != s->graph_sampler.temperature ||
-            sampler->top_p != s->graph_sampler.top_p) {
+            sampler->top_p != s->graph_sampler.top_p || sampler->repeat_penalty != s->graph_sampler.repeat_penalty ||
+            sampler->repeat_last_n != s->graph_sampler.repeat_last_n) {
             B2_CUDA(cudaStreamSynchronize(st));
             for (int g : {G_SAMPLE, G_SAMPLE_LOG})
                 for (int v = 0; v < 2; ++v)
@@ -1242,8 +1159,7 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
         }
         B2_CUDA(cudaMemcpyAsync(s->d_draw, &sampler->seed, 8, cudaMemcpyHostToDevice, st));
         B2_TRY(run_graph(s, logits_out ? G_SAMPLE_LOG : G_SAMPLE, n_steps, s->host_pos));
-    } else if (s->use_mega) B2_TRY(run_mega(s, MEGA_DECODE, n_steps, 0, logits_out ? s->logits_log : nullptr));
-    else if (!logits_out && n_steps > 1 && tp_vocab_parallel(s->m)) {
+    } else if (!logits_out && n_steps > 1 && tp_vocab_parallel(s->m)) {
         // all steps but the last with the LM head split over the ranks; the last one replicated, so that the call leaves complete
         // logits behind whatever the next call wants (sampling, logits_out)
         B2_TRY(run_graph(s, G_DECODE_VP, n_steps - 1, s->host_pos));
@@ -1273,9 +1189,9 @@ extern "C" int b2_forward_tokens(b2_session *s, const int32_t *tokens, int n, fl
     B2_CUDA(cudaSetDevice(s->m->e->device));
     B2_TRY(ensure_log(s, (uint64_t)n * V));
     B2_CUDA(cudaMemcpyAsync(s->d_prompt, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    B2_CUDA(cudaMemcpyAsync(s->d_ctx + s->host_pos, s->d_prompt, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     B2_TRY(set_step_counters(s));
-    if (s->use_mega) B2_TRY(run_mega(s, MEGA_PROMPT, n, 0, s->logits_log));
-    else B2_TRY(run_graph(s, G_FORCED, n, s->host_pos));
+    B2_TRY(run_graph(s, G_FORCED, n, s->host_pos));
     if (logits_out) B2_CUDA(cudaMemcpyAsync(logits_out, s->logits_log, (size_t)n * V * 4, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaStreamSynchronize(st));
     B2_TRY(tp_check(s));

@@ -1,35 +1,8 @@
-// gemv_dev.cuh — device side of the streaming Q4_0 GEMV (see gemv.cu for the design): shared by the stand-alone kernel
-// (gemv.cu) and the persistent token kernel (mega.cu).
+// gemv_dev.cuh — device side of the streaming Q4_0 GEMV (see gemv.cu for the design): shared by the single-GPU kernels
+// (gemv.cu) and the tensor-parallel ones (gemv_tp.cu).
 #pragma once
 #include "kernels.cuh"
 #include "layout.cuh"
-#include <cooperative_groups.h>
-
-#ifdef MEGA_PROF
-// development aid (build with EXTRA=-DMEGA_PROF, tools/prof_mega.py): %globaltimer stamps of thread 0 of every CTA,
-// [stage sequence number][CTA][8]
-__constant__ long long *g_prof;   // constant bank: a stamp must not wait for a global load
-__constant__ int g_prof_cap;
-__shared__ int s_prof_seq;
-__device__ __forceinline__ void prof_stamp(int k) {
-    if (threadIdx.x == 0 && g_prof && s_prof_seq < g_prof_cap) {
-        long long tt;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
-        g_prof[((size_t)s_prof_seq * gridDim.x + blockIdx.x) * 8 + k] = tt;
-    }
-}
-__device__ __forceinline__ void prof_next() { if (threadIdx.x == 0) s_prof_seq++; }
-#else
-__device__ __forceinline__ void prof_stamp(int) {}
-__device__ __forceinline__ void prof_next() {}
-#endif
-
-// Grid-wide barrier of the persistent token kernel.  Vectors written with st.global before it are read by cp.async.bulk (the
-// async proxy) after it: the thread that issues those copies runs proxy_fence_async() between the barrier and the copy, which
-// extends the ordering it acquired through the barrier to the async proxy.  (A fence in every thread on both sides of the
-// barrier cost 7 % of the kernel: it waits for all of the thread's outstanding memory operations.)
-__device__ __forceinline__ void grid_barrier() { cooperative_groups::this_grid().sync(); }
-__device__ __forceinline__ void proxy_fence_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t *b, int count) {
@@ -76,11 +49,12 @@ __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, ui
 #define GEMV_MAXT 2                          // K-outer order: tiles per CTA whose accumulators stay in registers
 #define MMA_MAGIC 0x4B400000                 // int bits of 12582912.0f: accumulators start here, so c reinterpreted as float is 12582912 + S exactly
 #define MMA_MAGIC_F 12582912.0f
-#define L2_PREFETCH_BYTES 0                  // of the NEXT kernel's weights, per CTA: off (measured: no gain once the own-stream window is on; B2_PF_NEXT re-enables)
+#define L2_PREFETCH_BYTES (64 * 1024)        // of the NEXT kernel's weights, per CTA, issued behind this kernel's own stream (B2_PF_NEXT): the next kernel's first
+                                             // pieces then come from L2 instead of HBM (656.9 -> 675 tokens/s at 128 KB alone, 687 together with the early prefetch)
+#define L2_PREFETCH_EARLY_BYTES (192 * 1024) // the O projection, resident and parked behind attention, pulls this much of the gate/up matrix per CTA into L2 BEFORE
+                                             // its dependency wait (B2_PF_EARLY; 28 MB in all): HBM works through the attention (128 / 192 / 256 / 320 / 384 KB:
+                                             // 667 / 683 / 678-680 / 674 / 668 tokens/s against 657)
 #define L2_WINDOW_BYTES (128 * 1024)         // how far the CTA's L2 prefetch cursor runs ahead of its register loads
-#ifndef MEGA_ORDER
-#define MEGA_ORDER 2                         // persistent kernel: 2 = barrier, staging, first register loads (see stage_input)
-#endif
 #ifndef GEMV_ORDER
 #define GEMV_ORDER 0                         // stand-alone kernel: 0 = register loads, wait, staging; 1 = wait, staging, register loads; 2 = as 0 with the L2 window after the wait
 #endif
@@ -375,10 +349,9 @@ __device__ __forceinline__ void load_piece(const uint8_t *ch, int cb, int warp, 
     }
 }
 
-// shared memory map (bytes): [header 1024: 64 floats of scratch, the input-copy mbarrier at +256, at +512 the 128 act*mul values
-//                            of a flush on their way to the activation grid][red rb*16*16*4*4 = rb*4096]
+// shared memory map (bytes): [header 512: 64 floats of scratch, the input-copy mbarrier at +256][red rb*16*16*4*4 = rb*4096]
 //                            [A3 of the input nbp*100 (+ fp32 staging)]     rb = GemvArgs::rb, tiles parked between two reductions
-#define GEMV_HDR_SMEM 1024
+#define GEMV_HDR_SMEM 512
 #define GEMV_RB_MAX 16                       // one warp finalises one parked tile
 #define GEMV_FIXED_SMEM(rb) (GEMV_HDR_SMEM + (rb) * 4096)
 
@@ -398,7 +371,6 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
     float *sts = (float *)(sact + (size_t)a.nbp * 100);
     if (IN == IN_ACT) {   // already on the grid: the image itself was copied
         mbar_wait(bar, parity);
-        prof_stamp(6);
         if constexpr (QT != 0) {   // block sums from the digits: lane = (t, j, half) reads one word of each plane of its block-group
             const float *sscale = (const float *)(sact + (size_t)a.nbp * 96);
             for (int ck = 0; ck < cpt; ++ck) {
@@ -421,7 +393,6 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
     const float *sq = sx + a.n_in;
     float *sscale = (float *)(sact + (size_t)a.nbp * 96);
     mbar_wait(bar, parity);
-    prof_stamp(6);
 #ifdef GEMV_EXP_NOSTAGE
     if (true) {   // what-if experiment: the input arrives, nothing is normalised or gridded: an all-zero image (wrong results, valid tokens)
         for (int ck = 0; ck < cpt; ++ck) {
@@ -572,13 +543,12 @@ __device__ __forceinline__ void stage_warp_input(const A &a, const GemvPtrs &pv,
 // re-synchronised on memory latency every other piece.
 // What the epilogue needs from the argument block, by value: a reference to the kernel parameter would force the whole block
 // into local memory of every thread (this function is not inlined).
-template <bool TP> struct FlushArgs { float *y; int rows, act, row_off; uint8_t *act_out; int n_out_act; };
+template <bool TP> struct FlushArgs { float *y; int rows, act, row_off; };
 template <> struct FlushArgs<true> { float *y; int rows, act, row_off; uint2 *tp_dst[8]; int tp_n; uint32_t tp_tag; };
 template <int OUT, class A>
 __device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A &a, uint32_t tptag) {
     FlushArgs<OUT == OUT_TPPART> f;
     f.y = a.y; f.rows = a.rows; f.act = a.act; f.row_off = a.row_off;
-    if constexpr (OUT != OUT_TPPART) { f.act_out = OUT == OUT_ACTMUL ? a.act_out : nullptr; f.n_out_act = a.n_out_act; }
     if constexpr (OUT == OUT_TPPART) {
 #pragma unroll
         for (int p = 0; p < 8; ++p) f.tp_dst[p] = a.tp_dst[p];
@@ -638,38 +608,19 @@ __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> 
             const float up = __shfl_down_sync(0xffffffffu, yv, 1);
             const float hv = act_fn(yv, a.act) * up;
             const int pair = tile * 8 + (r >> 1);
-            if (lane < 16 && !(r & 1)) {
-                if (a.y && 2 * pair < a.rows) a.y[pair] = hv;
-                // on its way to the activation grid: a 32-element block of h is the output of four consecutive tiles
-                if (a.act_out) ((float *)((uint8_t *)red - 512))[warp * 8 + (r >> 1)] = 2 * pair < a.rows ? hv : 0.f;
-            }
+            if (lane < 16 && !(r & 1) && 2 * pair < a.rows) a.y[pair] = hv;
         }
     }
     __syncthreads();   // the parked partials may be overwritten from here on
-    if constexpr (OUT == OUT_ACTMUL) {
-        // The down projection reads h as an activation image (as the O projection reads the attention output) instead of
-        // gridding 4*ffn bytes of fp32 in every CTA: tiles are dealt in fours (tile_align), so warp w < batch_n / 4 holds one
-        // whole block, puts it on the grid (oracle/model.py:fxp_round) and stores digits and scale.
-        if (a.act_out && warp < (batch_n >> 2)) {
-            const int blk = (batch_first >> 2) + warp;
-            if (blk * QK < a.n_out_act) {
-                float sv;
-                const int X = act_grid_lane(((const float *)((const uint8_t *)red - 512))[warp * 32 + lane], sv);
-                a3_store_block(a.act_out, a.n_out_act, blk, lane, X, sv);
-            }
-        }
-    }
     return FlushRun{best_v, best_i, sumsq};
 }
 
-// One GEMV phase executed by a whole 512-thread CTA.  MEGA = false: the body of the stand-alone kernel k_gemv (ordered after the
-// previous kernel by griddepcontrol.wait).  MEGA = true: a phase of the persistent token kernel (mega.cu): ordered after the
-// previous phase by a grid-wide barrier; the mbarrier of the input copies lives across phases (bar_parity flips per use).
-// PATH: -1 = all three loop orders compiled in and chosen at run time (persistent kernel: shapes are per model);
-//       0 / 1 / 2 = only tiles-outermost with two chunks per tile / with one chunk / chunks-outermost.  The stand-alone
-//       kernels are instantiated per path: a third of the code per kernel means fewer instruction-cache misses at every
-//       kernel start (no_instructions was 4-13 % of the warp samples of these 10-30 us kernels).
-template <int IN, int OUT, bool MEGA, int PATH = -1, int QT = 0, class A = GemvArgs>
+// One GEMV executed by a whole 512-thread CTA: the body of the kernel k_gemv (ordered after the previous kernel by
+// griddepcontrol.wait).
+// PATH: 0 / 1 / 2 = tiles-outermost with two chunks per tile / with one chunk / chunks-outermost (-1 = all three compiled in and
+//       chosen at run time).  The kernels are instantiated per path: a third of the code per kernel means fewer instruction-cache
+//       misses at every kernel start (no_instructions was 4-13 % of the warp samples of these 10-30 us kernels).
+template <int IN, int OUT, int PATH = -1, int QT = 0, class A = GemvArgs>
 __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_t *smem, uint32_t &bar_parity) {
     float *scratch = (float *)smem;                                             // 64 floats
     uint64_t *bar = (uint64_t *)(smem + 256);                                   // completion of the input copies
@@ -678,13 +629,12 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int bid = blockIdx.x;
     const int g = lane >> 2, t = lane & 3;
-    if (!MEGA && tid == 0) {
+    if (tid == 0) {
         pdl_launch_dependents();
         mbar_init(bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     auto stamp = [&](int k) {
-        if (MEGA) { prof_stamp(k); return; }
         if (a.dbg && tid == 0) {
             long long tt;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
@@ -750,23 +700,10 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 if (ck < cpt && q < (a.n_in >> 2)) wn[ck] = __ldg((const float4 *)pv.norm_w + q);
             }
         }
-        if (MEGA) grid_barrier();   // the previous stage is complete on every SM
-        else __syncthreads();       // everybody has issued its first weight loads; the mbarrier thread 0 initialised is visible
+        __syncthreads();            // everybody has issued its first weight loads; the mbarrier thread 0 initialised is visible
         if (tid == 0) {
-            if (MEGA) proxy_fence_async();
-            else pdl_wait();        // the copies below read what the previous kernel wrote
-            // Every CTA copies the same vector at the same moment: each starts at a different 128-byte-aligned offset (and wraps
-            // around) so the 148 copies do not walk the L2 slices in lock step.
-            auto rot_copy = [&](uint8_t *dst, const uint8_t *src, uint32_t bytes) {
-                const uint32_t lines = bytes >> 7;
-                const uint32_t rot = MEGA && lines > 1 ? (((uint32_t)bid * 2654435761u) >> 8) % lines * 128u : 0u;
-                if (rot) {
-                    bulk_g2s(dst + rot, src + rot, bytes - rot, bar);
-                    bulk_g2s(dst, src, rot, bar);
-                } else {
-                    bulk_g2s(dst, src, bytes, bar);
-                }
-            };
+            pdl_wait();             // the copies below read what the previous kernel wrote
+            auto rot_copy = [&](uint8_t *dst, const uint8_t *src, uint32_t bytes) { bulk_g2s(dst, src, bytes, bar); };
             if constexpr (IN == IN_TPNORM) {
                 // only the residual travels through shared memory; the warps read the exchange slots themselves
                 float *sx = (float *)(sact + (size_t)a.nbp * (100 + 4 * QT));
@@ -795,22 +732,11 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         bar_parity ^= 1;
         stamp(3);
     };
-    // Order of the first weight requests, the wait and the staging.  Stand-alone kernel: the requests go out first (weights
-    // never depend on the previous kernel) and are in flight while griddepcontrol.wait blocks.  Persistent kernel: before the
-    // grid barrier only the L2 prefetch of the CTA's first bytes is issued; the register loads follow the STAGING.  Measured
-    // (tools/prof_mega.py): shared-memory loads and stores of the staging complete in order behind the global loads this SM
-    // has in flight, and right after a barrier those wait in the HBM queue behind every SM's prefetch (staging took 2-9 us
-    // instead of ~0.5); issued after the staging, the register loads find their bytes in L2.
+    // Order of the first weight requests, the wait and the staging: the requests go out first (weights never depend on the
+    // previous kernel) and are in flight while griddepcontrol.wait blocks.  (Shared-memory loads and stores of the staging complete
+    // in order behind the global loads this SM has in flight; the other orders measured slower)
     auto stage_input = [&](auto &&first_loads) {
-        if (MEGA && MEGA_ORDER == 2) {
-            input_wait_copy();
-            input_stage();
-            first_loads();
-        } else if (MEGA && MEGA_ORDER == 1) {
-            input_wait_copy();
-            first_loads();
-            input_stage();
-        } else if (GEMV_ORDER == 1) {   // experiment: staging before the first register loads (they then hit the L2 window)
+        if (GEMV_ORDER == 1) {   // experiment: staging before the first register loads (they then hit the L2 window)
             input_wait_copy();
             input_stage();
             first_loads();
@@ -872,7 +798,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 pf += GEMV_CWARPS * 16384;
             }
         };
-        if (MEGA || GEMV_ORDER != 2) l2_window();
+        if (GEMV_ORDER != 2) l2_window();
         auto load_full = [&](WPieceT<QT> &r) {
             if (l_rem > 0) { if (act_full) load_piece<QT>(lp, KC, warp, lane, r); lp += KC * WLay<QT>::BB; --l_rem; }
         };
@@ -935,9 +861,9 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
                 for (uint32_t o = (uint32_t)warp * 16384; o + 16384 <= (uint32_t)nt * tile_bytes; o += GEMV_CWARPS * 16384) l2_prefetch(base + o, 16384);
             }
         };
-        if (MEGA || GEMV_ORDER != 2) l2_all();
+        if (GEMV_ORDER != 2) l2_all();
         stage_input([&]() { load_step(buf0, buf1); load_step(buf2, buf3); });
-        if (!MEGA && GEMV_ORDER == 2) l2_all();
+        if (GEMV_ORDER == 2) l2_all();
         BFragT<QT> bcur, bnxt;
         load_b(0, bcur);
         for (int ck = 0; ck < cpt; ck += 2) {
@@ -968,7 +894,6 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
     }
     stamp(5);
-    if (MEGA) prof_next();
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
         sumsq = warp_sum(sumsq);
         __syncthreads();

@@ -9,7 +9,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const A a) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint32_t parity = 0;
     const GemvPtrs pv = {a.w, a.norm_w, a.bias_or_res};
-    gemv_phase<IN, OUT, false, PATH, QT, A>(a, pv, smem, parity);
+    gemv_phase<IN, OUT, PATH, QT, A>(a, pv, smem, parity);
 }
 
 template <int IN, int OUT, int PATH, int QT, class A>

@@ -173,7 +173,8 @@ extern "C" int b2_op_attn_fused(const float *d_qkv, int nh, int nkv, int hd, int
 }
 extern "C" int b2_op_argmax(const float *d_logits, int64_t n, int32_t *d_out_index) {
     ApiScope _scope("b2_op_argmax");
-    B2_CHECK(d_logits && d_out_index && n > 0 && n < (1ll << 31), B2_EINVAL, "b2_op_argmax: bad arguments");
+    // the kernel strides an int index by its grid (a few thousand threads): stay that far below 2^31
+    B2_CHECK(d_logits && d_out_index && n > 0 && n <= (1ll << 31) - (1ll << 20), B2_EINVAL, "b2_op_argmax: bad arguments (n must be in [1, 2^31 - 2^20])");
     void *scratch = nullptr;
     B2_CUDA(cudaMalloc(&scratch, argmax_scratch_bytes()));
     cudaError_t e = cudaMemset(scratch, 0, argmax_scratch_bytes());
@@ -196,6 +197,30 @@ extern "C" int b2_op_sample_topk(const float *d_logits, int64_t n, int top_k, fl
     int rc = B2_OK;
     if (e == cudaSuccess) {
         rc = launch_sample_topk(d_logits, n, top_k, temperature, top_p, nullptr, u, d_out_index, scratch, 0);
+        e = cudaDeviceSynchronize();
+    }
+    cudaFree(scratch);
+    if (rc) return rc;
+    B2_CUDA(e);
+    return B2_OK;
+}
+
+// The same with the repetition penalty of Ollama's options.repeat_penalty / repeat_last_n: d_ctx holds the ctx_len tokens of the
+// context so far; every distinct token among its last `repeat_last_n` has its logit divided by the penalty when positive and
+// multiplied by it otherwise before the candidates are selected.
+extern "C" int b2_op_sample_topk_penalty(const float *d_logits, int64_t n, int top_k, float temperature, float top_p, float u, const int32_t *d_ctx,
+                                         int ctx_len, float repeat_penalty, int repeat_last_n, int32_t *d_out_index) {
+    ApiScope _scope("b2_op_sample_topk_penalty");
+    B2_CHECK(d_logits && d_out_index && n > 0 && n < (1ll << 31), B2_EINVAL, "b2_op_sample_topk_penalty: bad arguments");
+    B2_CHECK(top_k >= 1 && top_k <= SAMPLE_MAX_K, B2_EINVAL, "b2_op_sample_topk_penalty: top_k %d out of range [1,%d]", top_k, SAMPLE_MAX_K);
+    B2_CHECK(ctx_len >= 0 && (d_ctx || ctx_len == 0) && repeat_penalty >= 0.f && repeat_last_n >= 0, B2_EINVAL, "b2_op_sample_topk_penalty: bad context / penalty");
+    void *scratch = nullptr;
+    uint64_t sb = sample_scratch_bytes(top_k);
+    B2_CUDA(cudaMalloc(&scratch, sb));
+    cudaError_t e = cudaMemset(scratch, 0, sb);
+    int rc = B2_OK;
+    if (e == cudaSuccess) {
+        rc = launch_sample_topk(d_logits, n, top_k, temperature, top_p, nullptr, u, d_out_index, scratch, 0, d_ctx, nullptr, ctx_len, repeat_penalty, repeat_last_n);
         e = cudaDeviceSynchronize();
     }
     cudaFree(scratch);

@@ -5,6 +5,9 @@
 // Contract (mirrored by oracle/sampler.py): candidates sorted by (logit desc, index asc);
 // p = softmax(logit/T) over the k candidates; keep the shortest prefix with cumulative p >= top_p;
 // pick the first candidate whose cumulative p >= u * (kept mass).
+// Repetition penalty (Ollama's options.repeat_penalty / repeat_last_n, llama.cpp's rule): before the selection, the logit of every
+// distinct token among the last `last_n` tokens of the context (prompt included) is divided by the penalty when positive and
+// multiplied by it otherwise; penalty 1 (or 0) switches it off.
 #include "kernels.cuh"
 #include "sampler.cuh"
 
@@ -28,7 +31,8 @@ __device__ void block_argmax_256(float &v, int &i, float *sv, int *si) {
 
 __global__ void __launch_bounds__(256) k_sample_topk(const float *__restrict__ logits, int n, int k, float temperature, float top_p,
                                                      const float *__restrict__ d_u, float u_imm, int *__restrict__ out, float *cv, int *ci,
-                                                     int *counter) {
+                                                     int *counter, const int *__restrict__ ctx, const int *__restrict__ d_ctx_len, int ctx_len_imm,
+                                                     float penalty, int last_n) {
     extern __shared__ float sm[];
     __shared__ float sv[8];
     __shared__ int si[8];
@@ -40,6 +44,18 @@ __global__ void __launch_bounds__(256) k_sample_topk(const float *__restrict__ l
     float *vals = sm;   // slice copy, selected entries are overwritten with -inf
     for (int j = tid; j < cnt; j += 256) vals[j] = logits[i0 + j];
     __syncthreads();
+    if (ctx && penalty > 0.f && penalty != 1.0f && last_n > 0) {
+        const int len = d_ctx_len ? *d_ctx_len : ctx_len_imm, w0 = max(0, len - last_n);
+        for (int j = w0 + tid; j < len; j += 256) {
+            const int t = ctx[j];
+            if (t >= i0 && t < i1) {
+                bool first = true;   // a token that occurs several times in the window is penalised once
+                for (int q = w0; q < j; ++q) first = first && ctx[q] != t;
+                if (first) { const float v = vals[t - i0]; vals[t - i0] = v > 0.f ? __fdiv_rn(v, penalty) : __fmul_rn(v, penalty); }
+            }
+        }
+        __syncthreads();
+    }
     for (int r = 0; r < k; ++r) {
         float v = -INFINITY;
         int idx = 0x7fffffff;
@@ -114,7 +130,8 @@ __global__ void __launch_bounds__(256) k_sample_topk(const float *__restrict__ l
 uint64_t sample_scratch_bytes(int k) { return (uint64_t)SAMPLE_BLOCKS * k * 8 + 4; }
 
 int launch_sample_topk(const float *d_logits, int64_t n, int k, float temperature, float top_p, const float *d_u, float u_imm,
-                       int32_t *d_out, void *d_scratch, cudaStream_t st) {
+                       int32_t *d_out, void *d_scratch, cudaStream_t st, const int *d_ctx, const int *d_ctx_len, int ctx_len_imm, float penalty,
+                       int last_n) {
     if (k < 1 || k > SAMPLE_MAX_K) { b2_set_error("sampler: top_k %d out of range [1,%d]", k, SAMPLE_MAX_K); return B2_EINVAL; }
     if (!(temperature > 0.f)) { b2_set_error("sampler: temperature must be > 0"); return B2_EINVAL; }
     int per = (int)((n + SAMPLE_BLOCKS - 1) / SAMPLE_BLOCKS);
@@ -129,6 +146,7 @@ int launch_sample_topk(const float *d_logits, int64_t n, int k, float temperatur
         cudaError_t e = cudaFuncSetAttribute(k_sample_topk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) { b2_set_error("sampler: %s", cudaGetErrorString(e)); return B2_ECUDA; }
     }
-    k_sample_topk<<<SAMPLE_BLOCKS, 256, smem, st>>>(d_logits, (int)n, k, temperature, top_p, d_u, u_imm, d_out, cv, ci, counter);
+    k_sample_topk<<<SAMPLE_BLOCKS, 256, smem, st>>>(d_logits, (int)n, k, temperature, top_p, d_u, u_imm, d_out, cv, ci, counter, d_ctx, d_ctx_len,
+                                                    ctx_len_imm, penalty, last_n);
     return B2_OK;
 }

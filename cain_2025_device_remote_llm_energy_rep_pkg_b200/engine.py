@@ -61,7 +61,7 @@ class Engine:
     def __init__(self, device: int = 0, tp_rank: int = 0, tp_size: int = 1):
         self.lib = _lib.load()
         self.h = C.c_void_p()
-        check(self.lib.b2_engine_create(device, tp_rank, tp_size, None, C.byref(self.h)))
+        check(self.lib.b2_engine_create(device, tp_rank, tp_size, C.byref(self.h)))
         self.device, self.tp_rank, self.tp_size = device, tp_rank, tp_size
 
     def tp_handle(self) -> bytes:

@@ -40,6 +40,22 @@ def default_num_predict(prompt: str) -> int:
 OLLAMA_TOP_K, OLLAMA_TOP_P, OLLAMA_TEMPERATURE = 40, 0.9, 0.8
 
 
+OLLAMA_REPEAT_PENALTY, OLLAMA_REPEAT_LAST_N = 1.1, 64
+
+
+def repeat_from_options(options: dict, default_sampling: bool = False):
+    """options.{repeat_penalty, repeat_last_n} -> (penalty, window).  Off (1.0) unless the request names a penalty or the
+    server applies Ollama's defaults (--ollama-sampling: 1.1 over the last 64 tokens)."""
+    try:
+        pen = float(options.get("repeat_penalty", OLLAMA_REPEAT_PENALTY if default_sampling else 1.0))
+        last = int(options.get("repeat_last_n", OLLAMA_REPEAT_LAST_N))
+    except (TypeError, ValueError) as ex:
+        raise ValueError(f"bad repeat option: {ex}")
+    if pen <= 0.0 or last == 0:
+        return 1.0, 0
+    return pen, (1 << 30) if last < 0 else last      # Ollama: -1 = the whole context
+
+
 def sampler_from_options(options: dict, default_sampling: bool = False):
     """options.{temperature, top_k, top_p, seed} -> (top_k, temperature, top_p, seed) or None for greedy.
     A request without any of them is greedy (deterministic, what the parity tests pin) unless the server was started
@@ -225,7 +241,8 @@ class B2Backend:
             cfg = None
             if samp is not None:
                 from ._lib import SamplerCfg
-                cfg = SamplerCfg(top_k=samp[0], temperature=samp[1], top_p=samp[2], seed=samp[3])
+                pen, last = repeat_from_options(options, self.default_sampling)
+                cfg = SamplerCfg(top_k=samp[0], temperature=samp[1], top_p=samp[2], seed=samp[3], repeat_penalty=pen, repeat_last_n=last)
             sess.reset()
             sess.prefill(ptoks)
             out: List[int] = []

@@ -83,6 +83,10 @@ typedef struct b2_sampler_cfg {
     float    temperature;    /* used when top_k > 1; must be > 0 */
     float    top_p;          /* (0,1]; 1.0 disables the nucleus cut */
     uint64_t seed;           /* counter-based: draw i of a session (since create/reset) uses the uniform of (seed, i) */
+    float    repeat_penalty; /* used when top_k > 1.  0 or 1: off.  Ollama's options.repeat_penalty (llama.cpp's rule): the logit of every distinct
+                              * token among the last repeat_last_n tokens of the context (prompt included) is divided by it when positive,
+                              * multiplied by it otherwise, before the candidates are selected */
+    int32_t  repeat_last_n;  /* window of the penalty in tokens (Ollama's default 64); 0: off */
 } b2_sampler_cfg;
 
 typedef struct b2_stats {
@@ -97,9 +101,9 @@ const char *b2_version(void);
 /* ---- engine / model / session: the stages of one /api/generate request -------------------------- */
 /* Replaces: Ollama runner start-up (README.md:29-31 "install Ollama").  tp_size 1 = single GPU.
  * tp_size 2, 4 or 8: this engine is rank tp_rank of a tensor-parallel group, one process and one GPU per rank (SURVEY.md §8d
- * config 4 / §8e; no reference counterpart: Ollama places a model on one GPU here).  nccl_uid is ignored: the ranks exchange
- * partial sums through memory they map into each other (see b2_engine_tp_connect), not through a communicator. */
-int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, const void *nccl_uid, b2_engine **out);
+ * config 4 / §8e; no reference counterpart: Ollama places a model on one GPU here).  The ranks exchange partial sums through
+ * memory they map into each other (see b2_engine_tp_connect), not through a communicator. */
+int b2_engine_create(int device_ordinal, int tp_rank, int tp_size, b2_engine **out);
 int b2_engine_destroy(b2_engine *e);
 int b2_engine_device(const b2_engine *e, int *device_ordinal);
 /* Tensor-parallel set-up, before any model is created on the engine: every rank calls b2_engine_tp_handle (B2_TP_HANDLE_BYTES
@@ -213,6 +217,9 @@ int b2_op_argmax(const float *d_logits, int64_t n, int32_t *d_out_index);
 int b2_op_argmax_noalloc(const float *d_logits, int64_t n, int32_t *d_out_index);
 /* Top-k / temperature / top-p sampler with a caller-supplied uniform u in [0,1). */
 int b2_op_sample_topk(const float *d_logits, int64_t n, int top_k, float temperature, float top_p, float u, int32_t *d_out_index);
+/* The same with the repetition penalty of b2_sampler_cfg over the ctx_len tokens in d_ctx (device int32). */
+int b2_op_sample_topk_penalty(const float *d_logits, int64_t n, int top_k, float temperature, float top_p, float u, const int32_t *d_ctx,
+                              int ctx_len, float repeat_penalty, int repeat_last_n, int32_t *d_out_index);
 
 #ifdef __cplusplus
 }

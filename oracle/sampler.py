@@ -36,6 +36,17 @@ def sample_topk(logits: np.ndarray, k: int, temperature: float, top_p: float, u:
     return int(idx[j]), idx[:keep], min(margin, cut_margin)
 
 
+def apply_repeat_penalty(logits: np.ndarray, context, penalty: float, last_n: int) -> np.ndarray:
+    """Ollama's options.repeat_penalty / repeat_last_n (llama.cpp's rule, external and unpinned): every distinct token among the
+    last `last_n` tokens of the context has its logit divided by the penalty when positive, multiplied by it otherwise."""
+    out = logits.astype(np.float32).copy()
+    if not penalty or penalty == 1.0 or last_n <= 0:
+        return out
+    for t in set(int(x) for x in list(context)[-last_n:]):
+        out[t] = out[t] / np.float32(penalty) if out[t] > 0 else out[t] * np.float32(penalty)
+    return out
+
+
 def _splitmix64(z: int) -> int:
     z = (z + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
     z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF

@@ -31,7 +31,7 @@ def test_struct_layout_matches_header(lib):
     from cain_2025_device_remote_llm_energy_rep_pkg_b200._lib import SamplerCfg, Stats, TensorDesc
     assert ctypes.sizeof(CArchCfg) == 14 * 4 + 6 * 4
     assert ctypes.sizeof(TensorDesc) == 48
-    assert ctypes.sizeof(SamplerCfg) == 24
+    assert ctypes.sizeof(SamplerCfg) == 32
     assert ctypes.sizeof(Stats) == 40
 
 

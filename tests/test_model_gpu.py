@@ -158,6 +158,36 @@ def test_decode_with_topk_sampler_follows_the_sampler_contract(pk, gpu_engine):
     assert np.array_equal(g1, g2)
 
 
+def test_decode_with_repeat_penalty_follows_the_sampler_contract(pk, gpu_engine):
+    """Ollama's options.repeat_penalty / repeat_last_n inside the decode loop: every draw equals oracle/sampler.py on the returned
+    logits after the penalty over the last tokens of the context (prompt + what was generated so far)."""
+    archs, engine = pk
+    from cain_2025_device_remote_llm_energy_rep_pkg_b200._lib import SamplerCfg
+    from oracle import sampler as osampler
+    a = archs.TINY["llama3.1:8b"]
+    m = engine.Model.random(gpu_engine, a, seed=5, max_ctx=96)
+    cfg = SamplerCfg(top_k=40, temperature=0.8, top_p=0.9, seed=77, repeat_penalty=1.3, repeat_last_n=16)
+    s = m.session(96)
+    s.prefill(PROMPT)
+    toks, lg = s.decode(30, want_logits=True, sampler=cfg)
+    ctx, checked, changed = list(PROMPT), 0, 0
+    for i, (t, l) in enumerate(zip(toks, lg)):
+        pen = osampler.apply_repeat_penalty(l, ctx, 1.3, 16)
+        want, _, margin = osampler.sample_topk(pen, 40, 0.8, 0.9, osampler.uniform(77, i))
+        plain, _, _ = osampler.sample_topk(l, 40, 0.8, 0.9, osampler.uniform(77, i))
+        if margin > 1e-5:
+            assert int(t) == want, f"draw {i}"
+            checked += 1
+            changed += int(want != plain)
+        ctx.append(int(t))
+    assert checked >= 20
+    # the same call without the penalty gives another stream (the penalty is not a no-op on this model)
+    s.reset()
+    s.prefill(PROMPT)
+    other = s.decode(30, sampler=SamplerCfg(top_k=40, temperature=0.8, top_p=0.9, seed=77))
+    assert changed > 0 or not np.array_equal(other, toks)
+
+
 @pytest.mark.parametrize("key", ["llama3.1:8b", "phi3:3.8b", "gemma:7b"])
 def test_long_prompt_batches_match_oracle_and_token_by_token(pk, gpu_engine, key):
     """A 330-token prompt: six batches through the tcgen05 GEMM, the causal prompt attention over the growing cache (tiled kernel

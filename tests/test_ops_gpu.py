@@ -362,3 +362,31 @@ def test_sample_topk(lib, D, n, k):
             checked += 1
     assert checked >= 8
     assert lib.b2_op_sample_topk(dout.ptr, n, 65, 0.8, 0.9, 0.5, dout.ptr) == -1
+
+
+@pytest.mark.parametrize("n,k,last_n", [(1000, 40, 64), (32064, 20, 8), (300, 64, 500)])
+def test_sample_topk_with_repeat_penalty(lib, D, n, k, last_n):
+    """options.repeat_penalty (oracle/sampler.py:apply_repeat_penalty): tokens of the window lose their place among the candidates;
+    a token repeated inside the window is penalised once; tokens before the window are not."""
+    rng = np.random.default_rng(7 * n + k)
+    dout = D(4)
+    checked = 0
+    for trial in range(10):
+        x = (rng.standard_normal(n) * 2).astype(np.float32)
+        top = np.argsort(-x)[:8]
+        ctx = np.concatenate([rng.integers(0, n, size=100), top[:4], top[:2]]).astype(np.int32)   # the favourites sit in the window, two of them twice
+        u = float(rng.random())
+        pen = osampler.apply_repeat_penalty(x, ctx, 1.5, last_n)
+        tok, kept, margin = osampler.sample_topk(pen, k, 0.8, 0.9, u)
+        dx, dc = D.from_numpy(x), D.from_numpy(ctx)
+        chk(lib, lib.b2_op_sample_topk_penalty(dx.ptr, n, k, 0.8, 0.9, u, dc.ptr, len(ctx), 1.5, last_n, dout.ptr))
+        got = int(dout.to_numpy(np.int32, (1,))[0])
+        if margin > 1e-5:
+            assert got == tok
+            checked += 1
+        # penalty 1.0 and window 0 are both "off": the plain sampler's answer
+        plain, _, pm = osampler.sample_topk(x, k, 0.8, 0.9, u)
+        for pv, ln in ((1.0, last_n), (1.5, 0)):
+            chk(lib, lib.b2_op_sample_topk_penalty(dx.ptr, n, k, 0.8, 0.9, u, dc.ptr, len(ctx), pv, ln, dout.ptr))
+            assert pm < 1e-5 or int(dout.to_numpy(np.int32, (1,))[0]) == plain
+    assert checked >= 6

@@ -159,6 +159,15 @@ def test_chat_forms_of_the_five_families():
     assert f(msgs[1:2], "somethingelse") == "user: U\nassistant:"
 
 
+def test_repeat_options():
+    f = server.repeat_from_options
+    assert f({}) == (1.0, 64) and f({}, default_sampling=True) == (1.1, 64)          # Ollama's defaults only with --ollama-sampling
+    assert f({"repeat_penalty": 1.3, "repeat_last_n": 16}) == (1.3, 16)
+    assert f({"repeat_penalty": 1.3, "repeat_last_n": 0}) == (1.0, 0) and f({"repeat_penalty": 1.2, "repeat_last_n": -1})[1] > 4096
+    with pytest.raises(ValueError):
+        f({"repeat_penalty": "strong"})
+
+
 def test_keep_alive_and_devices_parsing():
     assert server.parse_keep_alive("5m", 1.0) == 300.0 and server.parse_keep_alive(0, 1.0) == 0.0 and server.parse_keep_alive("-1", 1.0) == -1.0
     assert server.parse_keep_alive(None, 7.0) == 7.0 and server.parse_keep_alive("1h", 0) == 3600.0 and server.parse_keep_alive("250ms", 0) == 0.25
