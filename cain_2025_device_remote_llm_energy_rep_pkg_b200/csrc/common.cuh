@@ -37,6 +37,7 @@ struct ApiScope {
 #define QK_K      256     // weights per K-quant super-block
 #define ACT_BITS  20      // |X| <= 2^20 on the activation grid
 #define PAGE_TOKENS 16    // tokens per KV page
+#define B2_MAX_DEVICES 64 // GPUs one process may drive (per-device caches of function attributes)
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------- warp helpers

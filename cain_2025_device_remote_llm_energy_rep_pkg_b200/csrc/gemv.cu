@@ -247,7 +247,7 @@ cudaError_t gemv_make_args(GemvArgs &a, int in_mode, const void *d_packed, int64
     a.pf_bytes = (uint32_t)env_pf;
     static int env_early = -1;   // B2_PF_EARLY (bytes per CTA): the O projection, parked behind attention, pulls the head of the gate/up matrix into L2 before it waits
     if (env_early < 0) { const char *e3 = getenv("B2_PF_EARLY"); env_early = e3 ? atoi(e3) : L2_PREFETCH_EARLY_BYTES; }
-    if (env_early > 0 && in_mode == IN_ACT && next_w) { a.pf_bytes = (uint32_t)env_early; a.pf_early = 1; }
+    if (in_mode == IN_ACT) a.pf_bytes = (uint32_t)env_early;
     a.k_outer = (a.nbp + KC - 1) / KC > 2;
     // a flush costs two CTA barriers and stalls all sixteen streams: park as many tiles as there are warps to finalise them
     // (LM head 62.5 -> 60.3 us, +1.7 % tokens/s against 8); with chunks outermost a CTA has at most GEMV_MAXT tiles

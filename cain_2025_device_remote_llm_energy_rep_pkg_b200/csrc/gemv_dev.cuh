@@ -90,8 +90,8 @@ struct GemvArgs {
     const uint8_t *pf_ptr;   // weights the NEXT kernel will stream: each CTA pulls the head of its share into L2
     uint64_t pf_total;
     uint32_t l2_window;      // bytes the CTA's L2 prefetch cursor runs ahead of its register loads (0: off)
-    uint32_t pf_bytes;       // bytes of the next kernel's weights each CTA pulls into L2 (0: off)
-    uint32_t pf_early;       // 1: that prefetch is issued BEFORE the wait for the input (a kernel that waits long: the O projection behind attention)
+    uint32_t pf_bytes;       // bytes of the next kernel's weights each CTA pulls into L2 (0: off).  IN_ACT kernels (the O projection, resident and
+                             // parked behind attention) issue it BEFORE the wait for their input, the others behind their own stream
     long long *dbg;          // optional [grid][8] %globaltimer stamps of thread 0 (development aid, tools/prof_gemv.py)
 };
 // The three pointers that differ from layer to layer travel beside the block: in the persistent kernel the block itself is a
@@ -557,11 +557,10 @@ __device__ __forceinline__ FlushArgs<OUT == OUT_TPPART> make_flush_args(const A 
     }
     return f;
 }
-struct FlushRun { float best_v; int best_i; float sumsq; };   // running arg-max / sum of squares of the rows this thread finalised
+struct FlushRun { float sumsq; };   // running sum of squares of the rows this thread finalised (OUT_RES)
 template <int OUT, int QT>
 __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> a, const float *bias_or_res, float *red, int batch_first, int batch_n, FlushRun run) {
-    float best_v = run.best_v, sumsq = run.sumsq;
-    int best_i = run.best_i;
+    float sumsq = run.sumsq;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     __syncthreads();
     if (warp < batch_n) {
@@ -599,10 +598,25 @@ __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> 
                     if (p < a.tp_n) st_volatile_v2(a.tp_dst[p] + row, __float_as_uint(yv), a.tp_tag);
             }
         } else if (OUT == OUT_LOGITS) {
+            // the running arg-max lives in shared memory, one (value, index) per warp in the header in front of the parked tiles (scratch[32..47],
+            // scratch[48..63]; the first 32 floats serve the staging): two registers less across the whole stream loop (this variant spilled four around every block-group)
+            float bv = -INFINITY;
+            int bi = 0x7fffffff;
             if (lane < 16 && row < a.rows) {
                 a.y[row] = yv;
-                const int grow = row + a.row_off;
-                if (yv > best_v || (yv == best_v && grow < best_i)) { best_v = yv; best_i = grow; }
+                bv = yv;
+                bi = row + a.row_off;
+            }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            }
+            if (lane == 0) {
+                float *sv = (float *)((uint8_t *)red - GEMV_HDR_SMEM) + 32;
+                int *si = (int *)sv + 16;
+                if (bv > sv[warp] || (bv == sv[warp] && bi < si[warp])) { sv[warp] = bv; si[warp] = bi; }
             }
         } else {   // OUT_ACTMUL: rows (2j, 2j+1) = (gate_j, up_j)
             const float up = __shfl_down_sync(0xffffffffu, yv, 1);
@@ -612,7 +626,7 @@ __device__ __noinline__ FlushRun flush_batch(const FlushArgs<OUT == OUT_TPPART> 
         }
     }
     __syncthreads();   // the parked partials may be overwritten from here on
-    return FlushRun{best_v, best_i, sumsq};
+    return FlushRun{sumsq};
 }
 
 // One GEMV executed by a whole 512-thread CTA: the body of the kernel k_gemv (ordered after the previous kernel by
@@ -742,14 +756,19 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
             first_loads();
         } else {
             first_loads();
-            if (a.pf_early) prefetch_next();
+            if constexpr (IN == IN_ACT) prefetch_next();   // one call site per kernel: a second copy of it costs the main kernels registers (spills)
             input_wait_copy();
             input_stage();
         }
     };
-    float best_v = -INFINITY;
-    int best_i = 0x7fffffff;
+    if (OUT == OUT_LOGITS && lane == 0) { scratch[32 + warp] = -INFINITY; ((int *)scratch)[48 + warp] = 0x7fffffff; }   // read and written by the same lane only, in flush_batch
     int batch_first = t0, batch_n = 0;
+    // only the residual epilogue carries a value across flushes in registers (its sum of squares); the arg-max of the LM head lives in
+    // shared memory.  Nothing else travels through the call: what does costs registers through the whole stream loop.
+    auto do_flush = [&]() {
+        if constexpr (OUT == OUT_RES) sumsq = flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{sumsq}).sumsq;
+        else (void)flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{0.f});
+    };
     auto park = [&](float (&acc)[4], float (&off)[2]) {   // park the finished tile's partial; reduce when a.rb tiles are waiting
         float *rb = red + (size_t)batch_n * (GEMV_CWARPS * 16 * 4);
         if constexpr (QT != 0) {   // the four t lanes covered one block each: their sum rides in the unused fourth column (plane "3")
@@ -765,8 +784,7 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
         }
         acc[0] = acc[1] = acc[2] = acc[3] = 0.f;
         if (++batch_n == a.rb) {
-            const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
-            best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
+            do_flush();
             batch_first += batch_n;
             batch_n = 0;
         }
@@ -888,10 +906,9 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
     stamp(4);
     // This CTA has requested all of its own weights: the head of its share of the NEXT kernel's weights starts flowing HBM -> L2
     // now, behind the stream, and fills the time HBM would idle through this kernel's tail and the hand-over to the next one.
-    if (!a.pf_early) prefetch_next();
+    if constexpr (IN != IN_ACT) prefetch_next();
     if (batch_n > 0) {
-        const FlushRun fr = flush_batch<OUT, QT>(make_flush_args<OUT>(a, tptag), pv.bias_or_res, red, batch_first, batch_n, FlushRun{best_v, best_i, sumsq});
-        best_v = fr.best_v; best_i = fr.best_i; sumsq = fr.sumsq;
+        do_flush();
     }
     stamp(5);
     if (OUT == OUT_RES && a.xsq_out) {   // partial sum of squares of the rows this CTA wrote (input of the next RMSNorm)
@@ -906,21 +923,13 @@ __device__ __forceinline__ void gemv_phase(const A &a, const GemvPtrs pv, uint8_
             a.xsq_out[bid] = tot;
         }
     }
-    if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima
-        float *sv = scratch;
-        int *si = (int *)(scratch + 16);
-        __syncthreads();
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) {
-            float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
-            int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
-            if (ov > best_v || (ov == best_v && oi < best_i)) { best_v = ov; best_i = oi; }
-        }
-        if (lane == 0) { sv[warp] = best_v; si[warp] = best_i; }
+    if (OUT == OUT_LOGITS) {   // every warp finalised some tiles: merge the sixteen running maxima flush_batch left in shared memory
+        float *sv = scratch + 32;
+        int *si = (int *)(scratch + 48);
         __syncthreads();
         if (warp == 0) {
-            best_v = lane < GEMV_CWARPS ? sv[lane] : -INFINITY;
-            best_i = lane < GEMV_CWARPS ? si[lane] : 0x7fffffff;
+            float best_v = lane < GEMV_CWARPS ? sv[lane] : -INFINITY;
+            int best_i = lane < GEMV_CWARPS ? si[lane] : 0x7fffffff;
 #pragma unroll
             for (int o = 8; o > 0; o >>= 1) {
                 float ov = __shfl_xor_sync(0xffffffffu, best_v, o);

@@ -14,11 +14,14 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) k_gemv(const A a) {
 
 template <int IN, int OUT, int PATH, int QT, class A>
 static cudaError_t launch_path(const A &a, int grid, size_t smem, cudaStream_t st, bool pdl) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // function attributes belong to a device: a server process drives one engine per GPU (server.py --devices)
+    static bool attr_set[B2_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= B2_MAX_DEVICES || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(k_gemv<IN, OUT, PATH, QT, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        if (dev >= 0 && dev < B2_MAX_DEVICES) attr_set[dev] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);

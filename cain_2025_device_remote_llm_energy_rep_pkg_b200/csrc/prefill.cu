@@ -415,11 +415,13 @@ __global__ void __launch_bounds__(256) k_prefill_finish(const float *__restrict_
 template <int T, int OUT, int QT>
 static cudaError_t launch_pf_qt(const PfArgs &a, int grid, cudaStream_t st) {
     using S = PfSmem<T>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[B2_MAX_DEVICES] = {};   // function attributes belong to a device (one engine per GPU in one server process)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= B2_MAX_DEVICES || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(k_prefill_gemm<T, OUT, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        if (dev >= 0 && dev < B2_MAX_DEVICES) attr_set[dev] = true;
     }
     k_prefill_gemm<T, OUT, QT><<<grid, PF_THREADS, S::TOTAL, st>>>(a);
     return cudaGetLastError();
