@@ -1,18 +1,21 @@
 // prefill.cu — batched prompt evaluation on tcgen05 tensor cores (see prefill.cuh for the data layout and the numerics).
 //
-// k_prefill_gemm: one CTA per SM, persistent over groups of 128 weight rows; fourteen warps in four roles:
-//   warps 8-11 stream the packed Q4_0 rows of the group from HBM (the decode layout, layout.cuh), turn the nibbles into int8
-//              (16*(q-8): nibble in the high half of the byte) and store them in shared memory as the A operand
-//              (K-major core matrices), one block-group (4 blocks = 128 k) per stage, with the rows' f16 scales as floats
-//   warp 13    copies the B operand of the stage (activation digits of T tokens, already in operand layout) and the
-//              activation scales with cp.async.bulk
-//   warp 12    one thread issues tcgen05.mma.kind::i8 (M=128, N=3T, K=32) per block, accumulate OFF, into one of two tensor-memory
-//              buffers and commits to mbarriers
-//   warps 0-7  read the int32 dot products with tcgen05.ld (thread = weight row, TMEM lane quadrant = warp % 4; for T >= 32 the
-//              tokens are split between warps 0-3 and 4-7), combine the
-//              three digit planes, scale by d_w * s_act and accumulate T fp32 sums per thread; after the last block they apply
+// k_prefill_gemm: one CTA per SM, persistent over work items (128 weight rows x a K range); fourteen warps in four roles:
+//   warps 4-11 stream the packed rows of the group from HBM (the decode layout, layout.cuh: no second copy of the weights),
+//              dequantise them exactly to fp32 (Q4_0: d*(q-8); Q4_K: d*sc*q - dmin*m with the oracle's roundings), split each value
+//              EXACTLY into NPART bf16 parts (Q4_0: 15 significant bits = 2 parts, Q4_K: 24 = 3) and store the parts as A operands
+//              (K-major 8 x 16-byte core matrices), one stage = 2 blocks = 64 k = 4 MMA k-steps
+//   warp 13    copies the B operand of the stage with cp.async.bulk: the three digit planes of the T tokens, already scaled
+//              (digit * 2^e * 128^plane is exact in bf16) and already in operand layout
+//   warp 12    one thread issues, per k-step, NPART x 3 tcgen05.mma.kind::f16 (M = 128, N = T, K = 16, bf16 x bf16 -> fp32) that all
+//              ACCUMULATE into the same T columns of tensor memory: every product is exact (8 x 8 significant bits), so the sum over
+//              parts, planes and k is the fp32 dot product of the dequantised row with the gridded activations
+//   warps 0-3  drain the accumulator into fp32 registers once per PF_SEG stages (a bounded chain of tensor-core additions, then one
+//              IEEE addition per segment), double-buffered against the MMAs of the next segment; after the last segment they apply
 //              the epilogue (+bias, +residual, act(gate)*up) and write y
-// The per-block scales of Q4_0 are the reason the accumulation across K cannot stay in tensor memory.
+// Round 1 issued one int8 MMA per 32-element block with accumulation off and combined the digit planes and the two per-block
+// scales on the CUDA cores (about ten operations per row, token and block, and a hand-over between the MMA and the epilogue warps
+// per block): the tensor pipe was 7-8 % busy.  Folding both scales into the operands keeps the whole K loop in tensor memory.
 #include "prefill.cuh"
 #include "gemv_dev.cuh"
 
@@ -23,7 +26,6 @@ __global__ void __launch_bounds__(256) k_prefill_quant(const float *__restrict__
     __shared__ float red[8];
     __shared__ float s_r;
     const int m = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    float *sa = (float *)(pb + pb_scale_off(T, nbp));
     const bool live = m < M;
     const float *xr = x + (int64_t)(live ? m : 0) * ldx;
     float r = 1.0f;
@@ -42,7 +44,8 @@ __global__ void __launch_bounds__(256) k_prefill_quant(const float *__restrict__
         __syncthreads();
         r = s_r;
     }
-    for (int kb = warp; kb < nbp; kb += 8) {
+    // the blocks of a row are dealt over gridDim.y CTAs (32 CTAs of one token each left most of the GPU idle: 24 us per launch)
+    for (int kb = blockIdx.y * 8 + warp; kb < nbp; kb += 8 * gridDim.y) {
         const int i = kb * QK + lane;
         float y = 0.f;
         if (live && i < n) {
@@ -56,17 +59,11 @@ __global__ void __launch_bounds__(256) k_prefill_quant(const float *__restrict__
         const int X = act_grid_lane(y, sc);
         int d0, d1, d2;
         act_digits(X, d0, d1, d2);
-        pb[pb_off(T, kb, 0, m, lane)] = (uint8_t)d0;
-        pb[pb_off(T, kb, 1, m, lane)] = (uint8_t)d1;
-        pb[pb_off(T, kb, 2, m, lane)] = (uint8_t)d2;
-        int xs = X;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) xs += __shfl_xor_sync(0xffffffffu, xs, o);
-        if (lane == 0) {
-            const bool on = live && kb * QK < n;
-            sa[(int64_t)kb * 2 * T + m] = on ? sc * 0.0625f : 0.f;
-            sa[(int64_t)kb * 2 * T + T + m] = on ? (float)xs * sc : 0.f;
-        }
+        // digit * 2^(e-19) * 128^plane: at most 7 significant bits, so the fp32 product is exact and its upper half is the bf16 value
+        const float v0 = (float)d0 * sc, v1 = (float)d1 * (sc * 128.0f), v2 = (float)d2 * (sc * 16384.0f);
+        *(uint16_t *)(pb + pb_off(T, kb, 0, m, lane)) = (uint16_t)(__float_as_uint(v0) >> 16);
+        *(uint16_t *)(pb + pb_off(T, kb, 1, m, lane)) = (uint16_t)(__float_as_uint(v1) >> 16);
+        *(uint16_t *)(pb + pb_off(T, kb, 2, m, lane)) = (uint16_t)(__float_as_uint(v2) >> 16);
     }
 }
 
@@ -74,8 +71,9 @@ cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M
                                  void *pb, cudaStream_t st) {
     if (M <= 0 || M > T || (T != 16 && T != 32 && T != 64) || n <= 0) return cudaErrorInvalidValue;
     const int nbp = (int)nblocks_padded(n);
-    if (in_mode == PF_IN_NORM) k_prefill_quant<PF_IN_NORM><<<T, 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, norm_w, eps, plus_one, (uint8_t *)pb);
-    else k_prefill_quant<PF_IN_F32><<<T, 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, nullptr, 0.f, 0, (uint8_t *)pb);
+    const int slices = nbp >= 256 ? 8 : nbp >= 64 ? 4 : 1;   // every CTA of a token recomputes the row's sum of squares (a few KB from L2)
+    if (in_mode == PF_IN_NORM) k_prefill_quant<PF_IN_NORM><<<dim3(T, slices), 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, norm_w, eps, plus_one, (uint8_t *)pb);
+    else k_prefill_quant<PF_IN_F32><<<dim3(T, slices), 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, nullptr, 0.f, 0, (uint8_t *)pb);
     return cudaGetLastError();
 }
 
@@ -89,19 +87,19 @@ __device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t cols) { 
 __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {      // the same warp
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
 }
-// D[tmem] = A[smem] * B[smem], int8 x int8 -> int32, M = 128, K = 32 (one 32-element block), no accumulate
-__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc) {
+// D[tmem] (+)= A[smem] * B[smem], bf16 x bf16 -> fp32, M = 128, K = 16; accumulate = 0 overwrites D
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
-        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(0u), "r"(0u) : "memory");
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
 }
 // the mbarrier gets one arrival when every MMA this thread has issued so far has completed
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 // 16 consecutive 32-bit columns of this thread's TMEM lane
-__device__ __forceinline__ void tmem_ld16(uint32_t addr, int (&v)[16]) {
+__device__ __forceinline__ void tmem_ld16(uint32_t addr, uint32_t (&v)[16]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
                    "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
@@ -109,17 +107,17 @@ __device__ __forceinline__ void tmem_ld16(uint32_t addr, int (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // shared-memory matrix descriptor: K-major, no swizzle; core matrix = 8 rows x 16 bytes (128 contiguous bytes), the two 16-byte
-// K halves of a 32-byte row 128 bytes apart (leading-dimension offset), 8-row groups 256 bytes apart (stride offset)
+// K halves of a 32-byte row (16 bf16) 128 bytes apart (leading-dimension offset), 8-row groups 256 bytes apart (stride offset)
 __device__ __forceinline__ uint64_t umma_desc(const void *smem) {
     return (uint64_t)((smem_u32(smem) >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46);
 }
-// instruction descriptor: D s32, A and B signed int8, both K-major, N = n, M = 128
-__host__ __device__ inline uint32_t umma_idesc_i8(int n) {
-    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(PF_ROWS >> 4) << 24);
+// instruction descriptor of kind::f16: D fp32, A and B bf16, both K-major, N = n, M = 128
+__host__ __device__ inline uint32_t umma_idesc_bf16(int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(PF_ROWS >> 4) << 24);
 }
 
 struct PfArgs {
-    const uint8_t *w;        // packed Q4_0 matrix (layout.cuh)
+    const uint8_t *w;        // packed Q4_0 / Q4_K matrix (layout.cuh)
     int rows, nbp, n_tiles;
     const uint8_t *pb;       // B operand of the batch (prefill.cuh)
     int M;                   // live tokens (<= T)
@@ -131,270 +129,298 @@ struct PfArgs {
     float *part;             // [ksplit][T][rows] fp32 partial sums (k_prefill_finish adds them in a fixed order)
 };
 
-// shared memory: [A stages: PF_STAGES x 4 blocks x 4 KB][B stages: PF_STAGES x 4 x N*32][dw: PF_STAGES x 4 x 128 floats]
-//                [sa: PF_STAGES x 4 x T floats][barriers]
-template <int T>
+// shared memory: [A stages: PF_STAGES x (4 k-steps x NPART images of 128 rows x 32 bytes)][B stages: PF_STAGES x (4 k-steps x 3T rows x 32 bytes)][barriers]
+template <int T, int NPART>
 struct PfSmem {
-    static constexpr int N = 3 * T;
-    static constexpr int A_STAGE = 4 * PF_ROWS * 32;
-    static constexpr int B_STAGE = 4 * N * 32;
+    // as many stages as fit: the round trip of a stage (MMAs done -> rebuilt -> MMAs issued again) is several times the work of a stage
+    static constexpr int FIT = (227 * 1024 - 256) / (4 * NPART * PF_ROWS * 32 + 4 * 3 * T * 32);
+    static constexpr int STAGES = FIT > 6 ? 6 : FIT;
+    static constexpr int A_IMG = PF_ROWS * 32;                 // one A operand: 128 rows x 16 bf16
+    static constexpr int A_STAGE = 4 * NPART * A_IMG;
+    static constexpr int B_KSTEP = 3 * T * 32;                 // one k-step of B: 3 planes x T tokens x 16 bf16
+    static constexpr int B_STAGE = 4 * B_KSTEP;                // = 2 blocks of the PB image
     static constexpr int A_OFF = 0;
-    static constexpr int B_OFF = A_OFF + PF_STAGES * A_STAGE;
-    static constexpr int DW_OFF = B_OFF + PF_STAGES * B_STAGE;
-    static constexpr int CW_OFF = DW_OFF + PF_STAGES * 4 * PF_ROWS * 4;     // Q4_K: 8A - B per (block, row)
-    static constexpr int SA_OFF = CW_OFF + PF_STAGES * 4 * PF_ROWS * 4;
-    static constexpr int SA_STAGE = 4 * 2 * T * 4;                          // per block: sa[T], ts[T]
-    static constexpr int BAR_OFF = SA_OFF + PF_STAGES * SA_STAGE;
-    static constexpr int TOTAL = BAR_OFF + 128;
+    static constexpr int B_OFF = A_OFF + STAGES * A_STAGE;
+    static constexpr int BAR_OFF = B_OFF + STAGES * B_STAGE;
+    static constexpr int TOTAL = BAR_OFF + 256;
 };
+
+// one fp32 value as NPART bf16 parts whose sum is the value (truncation leaves a remainder with 8 significant bits less)
+template <int NPART>
+__device__ __forceinline__ void split_bf16(float w, uint32_t (&part)[NPART]) {
+#pragma unroll
+    for (int p = 0; p < NPART; ++p) {
+        part[p] = __float_as_uint(w) & 0xFFFF0000u;
+        if (p + 1 < NPART) w = __fsub_rn(w, __uint_as_float(part[p]));
+    }
+}
 
 template <int T, int OUT, int QT>
 __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) {
-    using S = PfSmem<T>;
-    constexpr int N = S::N;
+    constexpr int NPART = QT ? 3 : 2;
+    // One MMA per (k-step, part) with N = 3T: the three digit planes are columns [plane*T + token] of the same MMA, so an A image
+    // (4 KB) is fetched from shared memory once per k-step and part instead of once per plane.  Measured with N = T and three MMAs
+    // per part: 14 ms per pass over llama3.1:8b whatever T was, because every small MMA re-reads its whole A operand and the
+    // operand fetch (24 x 4 KB per 64 k) was what the tensor pipe waited for.  The parts alternate between NACC accumulators.
+    constexpr int N = 3 * T;
+    constexpr int NACC = T <= 32 ? 2 : 1;              // 2 buffers x NACC x 3T columns <= 384 of the 512 columns of tensor memory
+    using S = PfSmem<T, NPART>;
+    constexpr int PF_STAGES = S::STAGES;
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint64_t *full = (uint64_t *)(smem + S::BAR_OFF);   // [stage] A unpacked (4 warp arrivals) + B copied (1 arrival + bytes)
-    uint64_t *empty = full + PF_STAGES;                 // [stage] MMAs of the stage done (commit) + scales read (4 epilogue warps)
-    uint64_t *tfull = empty + PF_STAGES;                // [buf]   dot products of one block are in tensor memory
-    uint64_t *tempty = tfull + 2;                       // [buf]   the four epilogue warps have read them
+    uint64_t *full = (uint64_t *)(smem + S::BAR_OFF);   // [stage] A built (8 warp arrivals) + B copied (1 arrival + bytes)
+    uint64_t *empty = full + PF_STAGES;                 // [stage] the MMAs that read the stage are done (commit)
+    uint64_t *tfull = empty + PF_STAGES;                // [buf]   a segment's sums are complete in tensor memory
+    uint64_t *tempty = tfull + 2;                       // [buf]   the four epilogue warps have drained them
     uint32_t *tmem_ptr = (uint32_t *)(tempty + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    constexpr int EPI_SETS = T >= 32 ? 2 : 1;   // epilogue warp sets, each with T / EPI_SETS tokens of all 128 rows
-    constexpr int TS = T / EPI_SETS;
     if (tid == 0) {
-        for (int s = 0; s < PF_STAGES; ++s) { mbar_init(full + s, 5); mbar_init(empty + s, 1 + 4 * EPI_SETS); }
-        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4 * EPI_SETS); }
+        for (int s = 0; s < PF_STAGES; ++s) { mbar_init(full + s, 9); mbar_init(empty + s, 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 12) tmem_alloc(tmem_ptr, 512);
+    if (warp == 12) tmem_alloc(tmem_ptr, 512);          // two buffers of NACC accumulators of T columns
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_ptr;
     const int n_items = ((a.n_tiles + 7) >> 3) * a.ksplit;   // work item = (row group, K piece)
-    const int nbg_all = a.nbp >> 2;                          // block-groups (stages) along K
+    const int nbg_all = a.nbp >> 2;                          // block-groups along K; a block-group is two stages
+    auto item_range = [&](int wi, int &grp, int &ks, int &bg0, int &bg1) {
+        grp = wi / a.ksplit;
+        ks = wi - grp * a.ksplit;
+        bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit);
+        bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+    };
 
-    if (warp < 8) {
-        if (warp >= 4 * EPI_SETS) goto done;
-        // ===================== epilogue: thread = (weight row, token set), TS fp32 sums
-        const int quad = warp & 3, tset = warp >> 2, tk0 = tset * TS;
-        const int row_l = quad * 32 + lane;
-        const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
-        int it = 0, kbi = 0;
+    if (warp < 4) {
+        // ===================== accumulator drain + epilogue: thread = weight row (TMEM lane), T fp32 sums
+        const int row_l = warp * 32 + lane;
+        const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
+        int seg = 0;
         for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
-            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
-            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
-            float acc[TS];
+            int grp, ks, bg0, bg1;
+            item_range(wi, grp, ks, bg0, bg1);
+            const int n_seg = (2 * (bg1 - bg0) + PF_SEG - 1) / PF_SEG;
+            float acc[T];
 #pragma unroll
-            for (int m = 0; m < TS; ++m) acc[m] = 0.f;
-            for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
-                const int slot = it % PF_STAGES;
-                const float *dws = (const float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
-                const float *sas = (const float *)(smem + S::SA_OFF + slot * S::SA_STAGE);
-                const float *cws = (const float *)(smem + S::CW_OFF) + slot * 4 * PF_ROWS;
-                mbar_wait(full + slot, (it / PF_STAGES) & 1);   // scales of the stage are in shared memory
-#pragma unroll 1
-                for (int b = 0; b < 4; ++b, ++kbi) {
-                    const int buf = kbi & 1;
-                    mbar_wait(tfull + buf, (kbi >> 1) & 1);
-                    tc_fence_after();
-                    const float dw = dws[b * PF_ROWS + row_l];
-                    const float cw = QT ? cws[b * PF_ROWS + row_l] : 0.f;
+            for (int m = 0; m < T; ++m) acc[m] = 0.f;
+            for (int sg = 0; sg < n_seg; ++sg, ++seg) {
+                const int buf = seg & 1;
+                mbar_wait(tfull + buf, (seg >> 1) & 1);
+                tc_fence_after();
 #pragma unroll
-                    for (int t0 = 0; t0 < TS; t0 += 16) {
-                        int c0[16], c1[16], c2[16];
-                        tmem_ld16(tlane + buf * 256 + tk0 + t0, c0);
-                        tmem_ld16(tlane + buf * 256 + T + tk0 + t0, c1);
-                        tmem_ld16(tlane + buf * 256 + 2 * T + tk0 + t0, c2);
+                for (int ai = 0; ai < NACC; ++ai) {
+#pragma unroll
+                    for (int t0 = 0; t0 < T; t0 += 16) {
+                        uint32_t c0[16], c1[16], c2[16];   // the three digit planes of 16 tokens (already scaled by 128^plane)
+                        tmem_ld16(tlane + (buf * NACC + ai) * N + t0, c0);
+                        tmem_ld16(tlane + (buf * NACC + ai) * N + T + t0, c1);
+                        tmem_ld16(tlane + (buf * NACC + ai) * N + 2 * T + t0, c2);
                         tmem_ld_wait();
 #pragma unroll
-                        for (int u = 0; u < 16; ++u) {
-                            // |c| <= 2^18: int -> float as an integer add and a float subtract (I2F runs at a quarter of their rate)
-                            const float f0 = __int_as_float(c0[u] + 0x4B400000) - 12582912.0f;
-                            const float f1 = __int_as_float(c1[u] + 0x4B400000) - 12582912.0f;
-                            const float f2 = __int_as_float(c2[u] + 0x4B400000) - 12582912.0f;
-                            const float xf = fmaf(16384.0f, f2, fmaf(128.0f, f1, f0));
-                            acc[t0 + u] = fmaf(xf, dw * sas[b * 2 * T + tk0 + t0 + u], acc[t0 + u]);
-                            if (QT) acc[t0 + u] = fmaf(cw, sas[b * 2 * T + T + tk0 + t0 + u], acc[t0 + u]);
-                        }
+                        for (int u = 0; u < 16; ++u)
+                            acc[t0 + u] = __fadd_rn(acc[t0 + u], __fadd_rn(__fadd_rn(__uint_as_float(c0[u]), __uint_as_float(c1[u])), __uint_as_float(c2[u])));
                     }
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(tempty + buf);
                 }
+                tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(empty + slot);
+                if (lane == 0) mbar_arrive(tempty + buf);
             }
             const int row = grp * PF_ROWS + row_l;
             if (a.ksplit > 1) {
 #pragma unroll
-                for (int u = 0; u < TS; ++u)
-                    if (tk0 + u < a.M && row < a.rows) a.part[((int64_t)ks * T + tk0 + u) * a.rows + row] = acc[u];
+                for (int u = 0; u < T; ++u)
+                    if (u < a.M && row < a.rows) a.part[((int64_t)ks * T + u) * a.rows + row] = acc[u];
                 continue;
             }
 #pragma unroll
-            for (int u = 0; u < TS; ++u) {
-                const int m = tk0 + u;
-                if (m < a.M) {   // uniform
+            for (int u = 0; u < T; ++u) {
+                if (u < a.M) {   // uniform
                     if (OUT == PF_OUT_ACTMUL) {   // rows (2j, 2j+1) = (gate_j, up_j)
                         const float up = __shfl_down_sync(0xffffffffu, acc[u], 1);
-                        if (!(row & 1) && row < a.rows) a.y[(int64_t)m * a.ldy + (row >> 1)] = act_fn(acc[u], a.act) * up;
+                        if (!(row & 1) && row < a.rows) a.y[(int64_t)u * a.ldy + (row >> 1)] = act_fn(acc[u], a.act) * up;
                     } else if (row < a.rows) {
-                        if (OUT == PF_OUT_RES) a.y[(int64_t)m * a.ldy + row] = a.bias_or_res[(int64_t)m * a.ldy + row] + acc[u];
-                        else a.y[(int64_t)m * a.ldy + row] = a.bias_or_res ? acc[u] + a.bias_or_res[row] : acc[u];
+                        if (OUT == PF_OUT_RES) a.y[(int64_t)u * a.ldy + row] = a.bias_or_res[(int64_t)u * a.ldy + row] + acc[u];
+                        else a.y[(int64_t)u * a.ldy + row] = a.bias_or_res ? acc[u] + a.bias_or_res[row] : acc[u];
                     }
                 }
             }
         }
     } else if (warp < 12) {
-        // ===================== weights: packed nibbles -> int8 A operand.  Warp lw unpacks (tile, half) pairs 4*lw .. 4*lw+3 of the
-        // group; lane (g, t) holds word t of four consecutive blocks of tile row half*8 + g (one LDG.128, as the decode GEMV).
-        const int lw = warp - 8, g = lane >> 2, t = lane & 3;
-        // the weights of a work item go HBM -> L2 one item ahead (lane 0, one bulk prefetch per tile and chunk), so the loads below
-        // are L2 hits; the register loads of the next stage are issued before the current stage is unpacked
+        // ===================== weights: packed nibbles -> exact fp32 -> NPART bf16 A operands.  Warp lw owns tile lw of the group
+        // (16 rows); lane (g, t) holds word t (elements 4t..4t+3 in the low nibbles, 16+4t.. in the high ones) of four consecutive
+        // blocks of tile rows g and g+8 (two LDG.128 per block-group, as the decode GEMV reads them).
+        const int lw = warp - 4, g = lane >> 2, t = lane & 3;
+        constexpr int BB = QT ? BLOCK_BYTES_K : BLOCK_BYTES, SCB = QT ? 192 : 128;
+        // the weights of a work item go HBM -> L2 one item ahead (lane 0, one bulk prefetch per chunk), so the loads below are L2 hits
         auto prefetch_item = [&](int wi) {
             if (lane != 0 || wi >= n_items) return;
-            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
-            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
-            for (int til = lw * 2; til < lw * 2 + 2; ++til) {
-                const int tg = grp * 8 + til;
-                if (tg >= a.n_tiles) continue;
-                for (int ck = bg0 >> 4; ck <= (bg1 - 1) >> 4; ++ck) {
-                    const int cb = min(KC, a.nbp - ck * KC);
-                    l2_prefetch(a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * (QT ? BLOCK_BYTES_K : BLOCK_BYTES), (uint32_t)cb * (QT ? BLOCK_BYTES_K : BLOCK_BYTES));
-                }
+            int grp, ks, bg0, bg1;
+            item_range(wi, grp, ks, bg0, bg1);
+            const int tg = grp * 8 + lw;
+            if (tg >= a.n_tiles || bg1 <= bg0) return;
+            for (int ck = bg0 >> 4; ck <= (bg1 - 1) >> 4; ++ck) {
+                const int cb = min(KC, a.nbp - ck * KC);
+                l2_prefetch(a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BB, (uint32_t)cb * BB);
             }
         };
-        constexpr int BB = QT ? BLOCK_BYTES_K : BLOCK_BYTES, SCB = QT ? 192 : 128;
-        auto issue = [&](int grp, int bgi, uint4 (&v)[4], uint32_t (&sc)[2], uint2 (&dm)[2]) {
-            const int ck = bgi >> 4, j = bgi & 15;
+        // one block-group of the tile in registers: nibble words of rows g / g+8, this lane's scale word, (d, dmin) of both rows
+        struct Regs { uint4 v0, v1; uint32_t sc; uint2 dm; };
+        auto issue = [&](int grp, int bgi, Regs &r) {
+            const int ck = bgi >> 4, j = bgi & 15, tg = grp * 8 + lw;
             const int cb = min(KC, a.nbp - ck * KC);
-            sc[0] = sc[1] = 0u;
-            dm[0] = dm[1] = make_uint2(0u, 0u);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1, tg = grp * 8 + til;
-                v[i] = make_uint4(0u, 0u, 0u, 0u);
-                if (tg < a.n_tiles) {
-                    const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BB;
-                    v[i] = ldg_stream4(chunk + (size_t)j * 1024 + hf * 512 + lane * 16);
-                    if (hf == 0) {   // Q4_0: half2 (d_g, d_g+8); Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) and half2 (d, dmin) of both rows
-                        sc[i >> 1] = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * SCB + lane * 4));
-                        if (QT) dm[i >> 1] = __ldg((const uint2 *)(chunk + (size_t)cb * 256 + j * SCB + 128 + (lane >> 2) * 8));
-                    }
-                }
+            r.v0 = r.v1 = make_uint4(0u, 0u, 0u, 0u);
+            r.sc = 0u;
+            r.dm = make_uint2(0u, 0u);
+            if (tg < a.n_tiles) {
+                const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BB;
+                r.v0 = ldg_stream4(chunk + (size_t)j * 1024 + lane * 16);
+                r.v1 = ldg_stream4(chunk + (size_t)j * 1024 + 512 + lane * 16);
+                // Q4_0: half2 (d of row g, d of row g+8) of block t; Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) of block t and half2 (d, dmin) of both rows
+                r.sc = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * SCB + lane * 4));
+                if (QT) r.dm = __ldg((const uint2 *)(chunk + (size_t)cb * 256 + j * SCB + 128 + (lane >> 2) * 8));
             }
         };
-        auto item_range = [&](int wi, int &grp, int &bg0, int &bg1) {
-            grp = wi / a.ksplit;
-            const int ks = wi - grp * a.ksplit;
-            bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit);
-            bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
+        // Three block-groups of registers rotate: while one is turned into A operands the loads of the next two are in flight.  The
+        // loop is unrolled by three so that the rotation costs no register copies (a copy would wait for the load it copies).
+        // (Measured: the depth does not matter, 0 / 1 / 2 block-groups ahead give 9.4 / 9.3 / 9.8 ms per 32-token prompt; the loads hit
+        // L2 behind the item-ahead bulk prefetch.)
+        struct Cursor { int wi, grp, ks, bgi, bg1; };
+        auto start = [&](Cursor &c, int wi) {
+            c.wi = wi; c.grp = c.ks = c.bgi = c.bg1 = 0;
+            if (wi < n_items) item_range(wi, c.grp, c.ks, c.bgi, c.bg1);
+        };
+        auto advance = [&](Cursor &c, bool prefetch) {   // to the next block-group, possibly the first of the CTA's next work item
+            if (c.wi >= n_items) return;
+            if (++c.bgi >= c.bg1) {
+                start(c, c.wi + gridDim.x);
+                if (prefetch) prefetch_item(c.wi + gridDim.x);
+            }
         };
         int it = 0;
-        int wi = blockIdx.x, grp = 0, bgi = 0, bg1 = 0;
-        uint4 v[4], vn[4];
-        uint32_t sc[2], scn[2];
-        uint2 dm[2], dmn[2];
-        prefetch_item(wi);
-        if (wi < n_items) {
-            item_range(wi, grp, bgi, bg1);
-            prefetch_item(wi + gridDim.x);
-            issue(grp, bgi, v, sc, dm);
-        }
-        while (wi < n_items) {
-            // the stage after this one (possibly the first of the next work item)
-            int nwi = wi, ngrp = grp, nbgi = bgi + 1, nbg1 = bg1;
-            if (nbgi >= bg1) {
-                nwi = wi + gridDim.x;
-                if (nwi < n_items) { item_range(nwi, ngrp, nbgi, nbg1); prefetch_item(nwi + gridDim.x); }
-            }
-            if (nwi < n_items) issue(ngrp, nbgi, vn, scn, dmn);
-            const int slot = it % PF_STAGES;
-            mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
-            uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
-            float *dws = (float *)(smem + S::DW_OFF) + slot * 4 * PF_ROWS;
-            float *cws = (float *)(smem + S::CW_OFF) + slot * 4 * PF_ROWS;
+        Cursor use, fill;
+        start(use, blockIdx.x);
+        fill = use;
+        prefetch_item(use.wi);
+        prefetch_item(use.wi + gridDim.x);
+        Regs r0, r1, r2;
+        if (fill.wi < n_items) issue(fill.grp, fill.bgi, r0);
+        advance(fill, true);
+        if (fill.wi < n_items) issue(fill.grp, fill.bgi, r1);
+        advance(fill, true);
+        auto build = [&](const Regs &cur) {
+            const uint32_t w0[4] = {cur.v0.x ^ 0x88888888u, cur.v0.y ^ 0x88888888u, cur.v0.z ^ 0x88888888u, cur.v0.w ^ 0x88888888u};   // GGML nibbles q of row g
+            const uint32_t w1[4] = {cur.v1.x ^ 0x88888888u, cur.v1.y ^ 0x88888888u, cur.v1.z ^ 0x88888888u, cur.v1.w ^ 0x88888888u};   // row g+8
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int combo = lw * 4 + i, til = combo >> 1, hf = combo & 1;
-                const uint32_t wd[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-                uint8_t *dst = As + (til * 2 + hf) * 256 + g * 16 + t * 4;
+            for (int hs = 0; hs < 2; ++hs, ++it) {   // the two stages of the block-group: blocks 2hs, 2hs+1
+                const int slot = it % PF_STAGES;
+                mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
+                uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
 #pragma unroll
-                for (int jj = 0; jj < 4; ++jj) {
-                    *(uint32_t *)(dst + jj * 4096) = (wd[jj] << 4) & 0xF0F0F0F0u;        // elements 4t..4t+3   (k half 0)
-                    *(uint32_t *)(dst + jj * 4096 + 128) = wd[jj] & 0xF0F0F0F0u;         // elements 16+4t..    (k half 1)
-                }
-                if (hf == 0) {   // lane = (row g, block jj = t)
-                    if (QT == 0) {   // half2 = (d of row g, d of row g+8)
-                        const float2 d2 = __half22float2(*(const __half2 *)&sc[i >> 1]);
-                        dws[t * PF_ROWS + til * 16 + g] = d2.x;
-                        dws[t * PF_ROWS + til * 16 + g + 8] = d2.y;
-                    } else {         // A = d*sc, C = 8A - dmin*m (the same roundings as the decode GEMV)
-                        const uint32_t w = sc[i >> 1];
-                        const float2 dg = __half22float2(*(const __half2 *)&dm[i >> 1].x), dg8 = __half22float2(*(const __half2 *)&dm[i >> 1].y);
-                        const float a0 = __fmul_rn(dg.x, byte_to_float(w, 0)), a1 = __fmul_rn(dg8.x, byte_to_float(w, 2));
-                        dws[t * PF_ROWS + til * 16 + g] = a0;
-                        dws[t * PF_ROWS + til * 16 + g + 8] = a1;
-                        cws[t * PF_ROWS + til * 16 + g] = __fsub_rn(8.0f * a0, __fmul_rn(dg.y, byte_to_float(w, 1)));
-                        cws[t * PF_ROWS + til * 16 + g + 8] = __fsub_rn(8.0f * a1, __fmul_rn(dg8.y, byte_to_float(w, 3)));
+                for (int bb = 0; bb < 2; ++bb) {
+                    const int jj = 2 * hs + bb;
+                    const uint32_t scw = __shfl_sync(0xffffffffu, cur.sc, g * 4 + jj);   // the scale word of (rows g / g+8, block jj)
+                    float mul[2], sub[2];
+                    if (QT == 0) {
+                        const float2 d2 = __half22float2(*(const __half2 *)&scw);
+                        mul[0] = d2.x; mul[1] = d2.y;
+                        sub[0] = sub[1] = 0.f;
+                    } else {   // d1 = d*sc, m1 = dmin*m, each rounded (gguf-py / oracle/quants.py order)
+                        const float2 dg = __half22float2(*(const __half2 *)&cur.dm.x), dg8 = __half22float2(*(const __half2 *)&cur.dm.y);
+                        mul[0] = __fmul_rn(dg.x, byte_to_float(scw, 0)); sub[0] = __fmul_rn(dg.y, byte_to_float(scw, 1));
+                        mul[1] = __fmul_rn(dg8.x, byte_to_float(scw, 2)); sub[1] = __fmul_rn(dg8.y, byte_to_float(scw, 3));
+                    }
+#pragma unroll
+                    for (int hf = 0; hf < 2; ++hf) {          // tile row g (hf 0) / g+8 (hf 1)
+                        const uint32_t word = hf ? w1[jj] : w0[jj];
+#pragma unroll
+                        for (int kh = 0; kh < 2; ++kh) {      // k-step 0: elements 4t..4t+3 (low nibbles), k-step 1: 16+4t.. (high nibbles)
+                            uint32_t parts[4][NPART];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const uint32_t q = (word >> (8 * e + 4 * kh)) & 0xFu;
+                                const float qf = __uint_as_float(0x4B000000u | q) - 8388608.0f;           // q as a float without I2F
+                                const float wv = QT == 0 ? __fmul_rn(mul[hf], qf - 8.0f) : __fsub_rn(__fmul_rn(qf, mul[hf]), sub[hf]);
+                                split_bf16<NPART>(wv, parts[e]);
+                            }
+                            // 4 consecutive k of row (hf*8 + g) of tile lw: 8 bytes of the image of k-step (bb*2 + kh)
+                            uint8_t *dst = As + ((bb * 2 + kh) * NPART) * S::A_IMG + (lw * 2 + hf) * 256 + (t >> 1) * 128 + g * 16 + (t & 1) * 8;
+#pragma unroll
+                            for (int p = 0; p < NPART; ++p)
+                                *(uint2 *)(dst + p * S::A_IMG) = make_uint2(__byte_perm(parts[0][p], parts[1][p], 0x7632), __byte_perm(parts[2][p], parts[3][p], 0x7632));
+                        }
                     }
                 }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tensor core reads these stores through the async proxy
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full + slot);
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tensor core reads these stores through the async proxy
-            __syncwarp();
-            if (lane == 0) mbar_arrive(full + slot);
-            ++it;
-            wi = nwi; grp = ngrp; bgi = nbgi; bg1 = nbg1;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) v[i] = vn[i];
-            sc[0] = scn[0]; sc[1] = scn[1];
-            dm[0] = dmn[0]; dm[1] = dmn[1];
+        };
+        auto step = [&](const Regs &cur, Regs &spare) {   // spare <- the block-group two ahead; cur -> shared memory
+            if (use.wi >= n_items) return;
+            if (fill.wi < n_items) issue(fill.grp, fill.bgi, spare);
+            advance(fill, true);
+            build(cur);
+            advance(use, false);
+        };
+        while (use.wi < n_items) {
+            step(r0, r2);
+            step(r1, r0);
+            step(r2, r1);
         }
     } else if (warp == 12) {
         // ===================== MMA issue (one thread)
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_i8(N);
-            int it = 0, kbi = 0;
+            const uint32_t idesc = umma_idesc_bf16(N);
+            // descriptors by addition: the start-address field (bits 0-13, in 16-byte units) of a descriptor of the first image plus
+            // the image's offset; one thread issues everything here, so every instruction it saves shortens the stage
+            const uint64_t descA0 = umma_desc(smem + S::A_OFF), descB0 = umma_desc(smem + S::B_OFF);
+            int it = 0, seg = 0;
             for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
-            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
-            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
-                for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
-                    const int slot = it % PF_STAGES;
+                int grp, ks, bg0, bg1;
+                item_range(wi, grp, ks, bg0, bg1);
+                const int n_st = 2 * (bg1 - bg0);
+                for (int st = 0; st < n_st; ++st, ++it) {
+                    const int slot = it % PF_STAGES, in_seg = st % PF_SEG, buf = seg & 1;
+                    if (in_seg == 0) {   // a new segment: its accumulator buffer must have been drained
+                        mbar_wait(tempty + buf, ((seg >> 1) & 1) ^ 1);
+                        tc_fence_after();
+                    }
                     mbar_wait(full + slot, (it / PF_STAGES) & 1);
                     tc_fence_after();
-                    const uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE, *Bs = smem + S::B_OFF + slot * S::B_STAGE;
-#pragma unroll 1
-                    for (int b = 0; b < 4; ++b, ++kbi) {
-                        const int buf = kbi & 1;
-                        mbar_wait(tempty + buf, ((kbi >> 1) & 1) ^ 1);
-                        tc_fence_after();
-                        umma_i8(tmem + buf * 256, umma_desc(As + b * 4096), umma_desc(Bs + b * (N * 32)), idesc);
-                        umma_commit(tfull + buf);
+                    const uint64_t da_s = descA0 + (uint64_t)((slot * S::A_STAGE) >> 4), db_s = descB0 + (uint64_t)((slot * S::B_STAGE) >> 4);
+                    const uint32_t acc_on = in_seg ? 1u : 0u;
+#pragma unroll
+                    for (int kst = 0; kst < 4; ++kst) {
+                        const uint64_t db = db_s + (uint64_t)((kst * S::B_KSTEP) >> 4);
+#pragma unroll
+                        for (int p = 0; p < NPART; ++p) {
+                            const int ai = p % NACC;     // the first MMA into an accumulator of a segment overwrites it
+                            umma_bf16(tmem + (buf * NACC + ai) * N, da_s + (uint64_t)(((kst * NPART + p) * S::A_IMG) >> 4), db, idesc,
+                                      (kst || p >= NACC) ? 1u : acc_on);
+                        }
                     }
                     umma_commit(empty + slot);
+                    if (in_seg == PF_SEG - 1 || st == n_st - 1) { umma_commit(tfull + buf); ++seg; }
                 }
             }
         }
     } else {
-        // ===================== B operand + activation scales of the stage: two bulk copies
+        // ===================== B operand of the stage: one bulk copy (two blocks of the PB image)
         if (lane == 0) {
-            const uint8_t *pbs = a.pb + pb_scale_off(T, a.nbp);
             int it = 0;
             for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
-            const int grp = wi / a.ksplit, ks = wi - grp * a.ksplit;
-            const int bg0 = (int)(((int64_t)nbg_all * ks) / a.ksplit), bg1 = (int)(((int64_t)nbg_all * (ks + 1)) / a.ksplit);
-                for (int bgi = bg0; bgi < bg1; ++bgi, ++it) {
+                int grp, ks, bg0, bg1;
+                item_range(wi, grp, ks, bg0, bg1);
+                for (int st = 2 * bg0; st < 2 * bg1; ++st, ++it) {
                     const int slot = it % PF_STAGES;
                     mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
-                    mbar_expect_tx(full + slot, (uint32_t)(S::B_STAGE + S::SA_STAGE));
-                    bulk_g2s(smem + S::B_OFF + slot * S::B_STAGE, a.pb + (size_t)bgi * S::B_STAGE, (uint32_t)S::B_STAGE, full + slot);
-                    bulk_g2s(smem + S::SA_OFF + slot * S::SA_STAGE, pbs + (size_t)bgi * S::SA_STAGE, (uint32_t)S::SA_STAGE, full + slot);
+                    mbar_expect_tx(full + slot, (uint32_t)S::B_STAGE);
+                    bulk_g2s(smem + S::B_OFF + slot * S::B_STAGE, a.pb + (size_t)st * S::B_STAGE, (uint32_t)S::B_STAGE, full + slot);
                 }
             }
         }
     }
-done:
     tc_fence_before();
     __syncthreads();
     if (warp == 12) tmem_dealloc(tmem, 512);
@@ -414,7 +440,8 @@ __global__ void __launch_bounds__(256) k_prefill_finish(const float *__restrict_
 
 template <int T, int OUT, int QT>
 static cudaError_t launch_pf_qt(const PfArgs &a, int grid, cudaStream_t st) {
-    using S = PfSmem<T>;
+    using S = PfSmem<T, QT ? 3 : 2>;
+    static_assert(S::TOTAL <= 227 * 1024, "prompt GEMM: shared memory");
     static bool attr_set[B2_MAX_DEVICES] = {};   // function attributes belong to a device (one engine per GPU in one server process)
     int dev = 0;
     cudaGetDevice(&dev);
@@ -448,7 +475,7 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
     if (part && out_mode != PF_OUT_ACTMUL && n_groups * 2 <= sm_count) {
         ksplit = sm_count / n_groups;
         const int nbg = a.nbp >> 2;
-        if (ksplit > nbg / 8) ksplit = nbg / 8;   // at least 8 stages per item
+        if (ksplit > nbg / 8) ksplit = nbg / 8;   // at least 8 block-groups (16 stages) per item
         if (ksplit > 8) ksplit = 8;
         while (ksplit > 1 && (uint64_t)ksplit * T * rows > part_floats) --ksplit;
         if (ksplit < 1) ksplit = 1;

@@ -1,35 +1,34 @@
 // prefill.cuh — batched prompt evaluation (the "prompt eval" half of Ollama's /api/generate):
 // T prompt tokens go through a weight matrix in ONE pass over its bytes, on the 5th-generation tensor cores
-// (tcgen05.mma kind::i8, accumulators in tensor memory), instead of T passes of the decode GEMV.
+// (tcgen05.mma kind::f16 on bf16 operands, fp32 accumulators in tensor memory), instead of T passes of the decode GEMV.
 //
 // Numerics are those of the decode path: the activation vector of every token is put on the block
-// fixed-point grid (21-bit integers as three balanced base-128 int8 digits), the weights are the int4 values times 16, so
-// each 32-element block contributes three exact int32 dot products per (row, token); they are combined and scaled by
-// d_w(row, block) * s_act(token, block) in fp32.
+// fixed-point grid (21-bit integers X times 2^(e-19) per 32-element block), the weights are the exact dequantised values.
+// Both are split into bf16 pieces WITHOUT rounding: X * 2^(e-19) = sum over three balanced base-128 digits of
+// digit * 128^plane * 2^(e-19) (7 significant bits each), a Q4_0 weight d*(q-8) has at most 15 significant bits = two bf16 parts,
+// a Q4_K weight (24 bits) three.  Every bf16 x bf16 product is exact in fp32, so the tensor cores add up, in fp32, exactly the
+// terms of the dot product of the dequantised row with the gridded activations; only the order and the tensor core's fp32
+// addition differ from the CPU oracle.
 //
-// "PB" = the B operand of the GEMM for a batch of T tokens (T = 16, 32 or 64; N = 3T int8 columns):
-//   [kb 0..nbp)  one image of N rows x 32 bytes per 32-element block, already in the shared-memory layout tcgen05.mma wants
-//                (K-major, no swizzle: 8-row x 16-byte core matrices; row n = d*T + m for digit plane d of token m):
-//                byte of (n, k) at kb*N*32 + (n>>3)*256 + (k>>4)*128 + (n&7)*16 + (k&15)  -- one cp.async.bulk per stage
-//   then per block kb 2T floats: sa[T] = 2^(e-19)/16 (the 1/16 undoes the weights' x16; 0 for padding blocks and tokens >= M)
-//   and ts[T] = the sum of the token's gridded activations over the block (the Q4_K "- dmin*m" term multiplies it).
+// "PB" = the B operand of the GEMM for a batch of T tokens (T = 16, 32 or 64):
+//   [kb 0..nbp)  per 32-element block two images (k-steps of 16 elements) of 3T rows x 16 bf16 in the shared-memory layout
+//                tcgen05.mma wants (K-major, no swizzle: 8-row x 16-byte core matrices; row n = plane*T + m for digit plane `plane`
+//                of token m): the bf16 of (n, k) at kb*192T + (k>>4)*96T + (n>>3)*256 + ((k&15)>>3)*128 + (n&7)*16 + (k&7)*2.
+//                Two blocks = one stage = one cp.async.bulk.
 #pragma once
 #include "kernels.cuh"
 #include "layout.cuh"
 
 #define PF_ROWS 128          // weight rows per CTA tile (UMMA M)
-#define PF_STAGES 3          // shared-memory stages of one block-group (4 blocks = 128 k) each
-#define PF_THREADS 448       // warps 0-7 epilogue (TMEM quadrant = warp % 4, token half = warp / 4), 8-11 weight unpack, 12 MMA issue, 13 B-operand copies
+#define PF_SEG 8             // stages whose products accumulate in tensor memory before they are drained into fp32 registers (512 k)
+#define PF_THREADS 448       // warps 0-3 accumulator drain + epilogue (TMEM quadrant = warp), 4-11 weight dequantisation, 12 MMA issue, 13 B-operand copies
 
-__host__ __device__ inline size_t pb_block_bytes(int T) { return (size_t)3 * T * 32; }
-__host__ __device__ inline size_t pb_scale_off(int T, int64_t nbp) { return (size_t)nbp * pb_block_bytes(T); }
-__host__ __device__ inline size_t pb_bytes(int T, int64_t n) {
-    const int64_t nbp = nblocks_padded(n);
-    return pb_scale_off(T, nbp) + (size_t)nbp * T * 8;
-}
+__host__ __device__ inline size_t pb_block_bytes(int T) { return (size_t)2 * 3 * T * 32; }
+__host__ __device__ inline size_t pb_bytes(int T, int64_t n) { return (size_t)nblocks_padded(n) * pb_block_bytes(T); }
 __host__ __device__ inline size_t pb_off(int T, int64_t kb, int d, int m, int k) {
-    const int n = d * T + m;
-    return (size_t)kb * pb_block_bytes(T) + (size_t)(n >> 3) * 256 + (size_t)(k >> 4) * 128 + (size_t)(n & 7) * 16 + (size_t)(k & 15);
+    const int n = d * T + m, kk = k & 15;
+    return (size_t)kb * pb_block_bytes(T) + (size_t)(k >> 4) * (3 * T * 32) + (size_t)(n >> 3) * 256 + (size_t)(kk >> 3) * 128 + (size_t)(n & 7) * 16 +
+           (size_t)(kk & 7) * 2;
 }
 // smallest supported batch size holding m tokens (0 if m > 64)
 inline int pf_batch(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 0; }
