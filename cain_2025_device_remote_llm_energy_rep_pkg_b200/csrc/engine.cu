@@ -101,7 +101,6 @@ struct b2_model {
     std::vector<LayerW> layers;
     float *rope_cos = nullptr, *rope_sin = nullptr;
     uint64_t weight_bytes = 0;
-    bool layers_q4 = true;         // the tcgen05 prompt GEMM takes Q4_0 / Q4_K layer matrices (a Q6_K head is fine: it runs as a GEMV)
     std::vector<void *> allocs;
     // a rank of a tensor-parallel group holds n_heads / tp query heads, n_kv_heads / tp KV heads and ffn / tp rows of gate / up
     // (column-parallel QKV, gate, up; row-parallel O, down); norms, embedding and LM head are replicated.  tp = 1: everything.
@@ -306,7 +305,6 @@ static int alloc_mat(b2_model *m, Mat &mat, int64_t rows, int64_t cols, int type
     mat.rows = rows;
     mat.cols = cols;
     mat.type = type;
-    if (type == B2_T_Q6_K && &mat != &m->embd && &mat != &m->head) m->layers_q4 = false;
     B2_TRY(dev_alloc(m->allocs, &mat.packed, packed_bytes_of(type, rows, cols)));
     B2_CUDA(cudaMemsetAsync(mat.packed, 0, packed_bytes_of(type, rows, cols), m->e->stream));   // row / block padding must be zero
     return B2_OK;
@@ -357,7 +355,6 @@ static int alloc_model_skeleton(b2_engine *e, const b2_arch_cfg *cfg, const Mode
                 if ((rc = alloc_mat(m, ly.qkv, qd + 2 * kvd, H, lt.q))) break;
             } else {
                 ly.split_qkv = true;
-                m->layers_q4 = false;   // the tcgen05 prompt GEMM takes the fused matrix
                 if ((rc = alloc_mat(m, ly.qkv_part[0], qd, H, lt.q))) break;
                 if ((rc = alloc_mat(m, ly.qkv_part[1], kvd, H, lt.k))) break;
                 if ((rc = alloc_mat(m, ly.qkv_part[2], kvd, H, lt.v))) break;
@@ -1068,15 +1065,25 @@ static int prefill_batched(b2_session *s, int n) {
         for (int l = 0; l < c.n_layers; ++l) {
             LayerW &ly = m->layers[l];
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.attn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm_qt(ly.qkv.type == B2_T_Q4_K, PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, s->pf_part, s->pf_part_floats, st));
+            if (ly.split_qkv) {   // q, k, v in different formats (llama.cpp's Q4_K_M keeps attn_v in Q6_K): three GEMMs into the columns of the QKV batch
+                int64_t row0 = 0;
+                for (int part = 0; part < 3; ++part) {
+                    const Mat &pm = ly.qkv_part[part];
+                    B2_CUDA(launch_prefill_gemm_qt(qt_of(pm.type), PF_OUT_BIAS, pm.packed, pm.rows, H, s->pf_pb, mb, T, s->pf_qkv + row0, ldq,
+                                                   ly.qkv_bias ? ly.qkv_bias + row0 : nullptr, 0, sms, s->pf_part, s->pf_part_floats, st));
+                    row0 += pm.rows;
+                    launches += part ? 1 : 0;
+                }
+            } else
+            B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.qkv.type), PF_OUT_BIAS, ly.qkv.packed, ly.qkv.rows, H, s->pf_pb, mb, T, s->pf_qkv, ldq, ly.qkv_bias, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, m->heads(), m->kv_heads(), hd, pos0, m->rope_cos, m->rope_sin,
                                              s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, s->pf_attn, qd, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_attn, qd, mb, T, qd, nullptr, 0.f, 0, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm_qt(ly.o.type == B2_T_Q4_K, PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
+            B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.o.type), PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.ffn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm_qt(ly.gateup.type == B2_T_Q4_K, PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
+            B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.gateup.type), PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_h, I, mb, T, I, nullptr, 0.f, 0, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm_qt(ly.down.type == B2_T_Q4_K, PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
+            B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.down.type), PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             launches += 10;
         }
         if (m0 + mb == n) {   // LM head for the last token of the prompt
@@ -1107,7 +1114,7 @@ extern "C" int b2_prefill(b2_session *s, const int32_t *tokens, int n, float *lo
     B2_CUDA(cudaMemcpyAsync(s->d_ctx + s->host_pos, s->d_prompt, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
     B2_TRY(set_step_counters(s));
     B2_CUDA(cudaEventRecord(s->ev0, st));
-    if (s->use_pf_gemm && s->m->layers_q4 && n >= 3) {
+    if (s->use_pf_gemm && n >= 3) {
         B2_TRY(prefill_batched(s, n));
     } else {
         if (n > 1) B2_TRY(run_graph(s, G_PREFILL_BODY, n - 1, s->host_pos));

@@ -235,8 +235,8 @@ extern "C" int b2_op_sample_topk_penalty(const float *d_logits, int64_t n, int t
 extern "C" int b2_op_prefill_gemm(int type, const void *d_packed, int64_t rows, int64_t cols, const float *d_x, int M, const float *d_norm_w,
                                   float eps, int plus_one, const float *d_bias_or_res, int mode, int act, float *d_y) {
     ApiScope _scope("b2_op_prefill_gemm");
-    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K, B2_EINVAL, "b2_op_prefill_gemm: type %d not supported", type);
-    B2_CHECK(type != B2_T_Q4_K || cols % 256 == 0, B2_EINVAL, "b2_op_prefill_gemm: Q4_K needs cols %% 256 == 0");
+    B2_CHECK(type == B2_T_Q4_0 || type == B2_T_Q4_K || type == B2_T_Q6_K, B2_EINVAL, "b2_op_prefill_gemm: type %d not supported", type);
+    B2_CHECK(type == B2_T_Q4_0 || cols % 256 == 0, B2_EINVAL, "b2_op_prefill_gemm: K-quants need cols %% 256 == 0");
     B2_CHECK(d_packed && d_x && d_y && rows > 0 && cols > 0 && cols % QK == 0 && M > 0, B2_EINVAL, "b2_op_prefill_gemm: bad arguments");
     B2_CHECK(mode >= 0 && mode <= 2, B2_EINVAL, "b2_op_prefill_gemm: mode %d", mode);
     B2_CHECK(mode != 1 || d_bias_or_res, B2_EINVAL, "b2_op_prefill_gemm: mode 1 needs the residual matrix");
@@ -255,7 +255,7 @@ extern "C" int b2_op_prefill_gemm(int type, const void *d_packed, int64_t rows, 
         const int mb = M - m0 < 64 ? M - m0 : 64, T = pf_batch(mb);
         e = launch_prefill_quant(d_norm_w ? PF_IN_NORM : PF_IN_F32, d_x + (int64_t)m0 * cols, cols, mb, T, cols, d_norm_w, eps, plus_one, pb, 0);
         if (e == cudaSuccess)
-            e = launch_prefill_gemm_qt(type == B2_T_Q4_K, mode, d_packed, rows, cols, pb, mb, T, d_y + (int64_t)m0 * ldy, ldy,
+            e = launch_prefill_gemm_qt(qt_of(type), mode, d_packed, rows, cols, pb, mb, T, d_y + (int64_t)m0 * ldy, ldy,
                                     mode == 1 ? d_bias_or_res + (int64_t)m0 * ldy : d_bias_or_res, act, sms, part, part_floats, 0);
     }
     if (e == cudaSuccess) e = cudaDeviceSynchronize();

@@ -2,8 +2,9 @@
 //
 // k_prefill_gemm: one CTA per SM, persistent over work items (128 weight rows x a K range); fourteen warps in four roles:
 //   warps 4-11 stream the packed rows of the group from HBM (the decode layout, layout.cuh: no second copy of the weights),
-//              dequantise them exactly to fp32 (Q4_0: d*(q-8); Q4_K: d*sc*q - dmin*m with the oracle's roundings), split each value
-//              EXACTLY into NPART bf16 parts (Q4_0: 15 significant bits = 2 parts, Q4_K: 24 = 3) and store the parts as A operands
+//              dequantise them exactly to fp32 (Q4_0: d*(q-8); Q4_K: d*sc*q - dmin*m; Q6_K: d*sc*(q-32), each with the oracle's
+//              roundings), split each value EXACTLY into NPART bf16 parts (Q4_0: 15 significant bits = 2 parts, K-quants: 24 = 3) and
+//              store the parts as A operands
 //              (K-major 8 x 16-byte core matrices), one stage = 2 blocks = 64 k = 4 MMA k-steps
 //   warp 13    copies the B operand of the stage with cp.async.bulk: the three digit planes of the T tokens, already scaled
 //              (digit * 2^e * 128^plane is exact in bf16) and already in operand layout
@@ -18,6 +19,7 @@
 // per block): the tensor pipe was 7-8 % busy.  Folding both scales into the operands keeps the whole K loop in tensor memory.
 #include "prefill.cuh"
 #include "gemv_dev.cuh"
+#include <type_traits>
 
 // ------------------------------------------------------------------------------------------ activation batch -> PB
 template <int IN>
@@ -251,7 +253,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         // (16 rows); lane (g, t) holds word t (elements 4t..4t+3 in the low nibbles, 16+4t.. in the high ones) of four consecutive
         // blocks of tile rows g and g+8 (two LDG.128 per block-group, as the decode GEMV reads them).
         const int lw = warp - 4, g = lane >> 2, t = lane & 3;
-        constexpr int BB = QT ? BLOCK_BYTES_K : BLOCK_BYTES, SCB = QT ? 192 : 128;
+        constexpr int BB = QT == 2 ? BLOCK_BYTES_6 : QT ? BLOCK_BYTES_K : BLOCK_BYTES, SCB = QT ? 192 : 128;
         // the weights of a work item go HBM -> L2 one item ahead (lane 0, one bulk prefetch per chunk), so the loads below are L2 hits
         auto prefetch_item = [&](int wi) {
             if (lane != 0 || wi >= n_items) return;
@@ -265,20 +267,30 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
             }
         };
         // one block-group of the tile in registers: nibble words of rows g / g+8, this lane's scale word, (d, dmin) of both rows
-        struct Regs { uint4 v0, v1; uint32_t sc; uint2 dm; };
+        // Q6_K adds the high bits of the same elements (wh), keeps the scale words of all four blocks of its rows in the lane (sd4: int8
+        // (sc_lo_g, sc_hi_g, sc_lo_g+8, sc_hi_g+8) per block) and half2 (d_g, d_g+8) in sc
+        struct Regs4 { uint4 v0, v1; uint32_t sc; uint2 dm; };
+        struct Regs6 { uint4 v0, v1, wh, sd4; uint32_t sc; };
+        using Regs = typename std::conditional<QT == 2, Regs6, Regs4>::type;
         auto issue = [&](int grp, int bgi, Regs &r) {
             const int ck = bgi >> 4, j = bgi & 15, tg = grp * 8 + lw;
             const int cb = min(KC, a.nbp - ck * KC);
             r.v0 = r.v1 = make_uint4(0u, 0u, 0u, 0u);
             r.sc = 0u;
-            r.dm = make_uint2(0u, 0u);
+            if constexpr (QT == 2) { r.wh = r.sd4 = make_uint4(0u, 0u, 0u, 0u); } else { r.dm = make_uint2(0u, 0u); }
             if (tg < a.n_tiles) {
                 const uint8_t *chunk = a.w + ((uint64_t)tg * a.nbp + (uint64_t)ck * KC) * BB;
                 r.v0 = ldg_stream4(chunk + (size_t)j * 1024 + lane * 16);
                 r.v1 = ldg_stream4(chunk + (size_t)j * 1024 + 512 + lane * 16);
-                // Q4_0: half2 (d of row g, d of row g+8) of block t; Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) of block t and half2 (d, dmin) of both rows
-                r.sc = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * SCB + lane * 4));
-                if (QT) r.dm = __ldg((const uint2 *)(chunk + (size_t)cb * 256 + j * SCB + 128 + (lane >> 2) * 8));
+                if constexpr (QT == 2) {
+                    r.wh = ldg_stream4(chunk + (size_t)cb * 256 + (size_t)j * 512 + lane * 16);
+                    r.sd4 = ldg_stream4(chunk + (size_t)cb * 384 + j * 160 + (lane >> 2) * 16);
+                    r.sc = __ldg((const uint32_t *)(chunk + (size_t)cb * 384 + j * 160 + 128 + (lane >> 2) * 4));
+                } else {
+                    // Q4_0: half2 (d of row g, d of row g+8) of block t; Q4_K: bytes (sc_g, m_g, sc_g+8, m_g+8) of block t and half2 (d, dmin) of both rows
+                    r.sc = __ldg((const uint32_t *)(chunk + (size_t)cb * 256 + j * SCB + lane * 4));
+                    if constexpr (QT == 1) r.dm = __ldg((const uint2 *)(chunk + (size_t)cb * 256 + j * SCB + 128 + (lane >> 2) * 8));
+                }
             }
         };
         // Three block-groups of registers rotate: while one is turned into A operands the loads of the next two are in flight.  The
@@ -319,16 +331,28 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
 #pragma unroll
                 for (int bb = 0; bb < 2; ++bb) {
                     const int jj = 2 * hs + bb;
-                    const uint32_t scw = __shfl_sync(0xffffffffu, cur.sc, g * 4 + jj);   // the scale word of (rows g / g+8, block jj)
-                    float mul[2], sub[2];
-                    if (QT == 0) {
+                    // mul[row half][k-step], sub[row half]: Q4_0 w = mul*(q-8); Q4_K w = q*mul - sub; Q6_K w = mul*(q-32), mul per 16 elements
+                    float mul[2][2], sub[2];
+                    uint32_t hbits[2] = {0u, 0u};   // Q6_K: the 16-bit field of high bits of (row half, block jj): byte kh, 2 bits per element
+                    if constexpr (QT == 0) {
+                        const uint32_t scw = __shfl_sync(0xffffffffu, cur.sc, g * 4 + jj);   // the scale word of (rows g / g+8, block jj)
                         const float2 d2 = __half22float2(*(const __half2 *)&scw);
-                        mul[0] = d2.x; mul[1] = d2.y;
+                        mul[0][0] = mul[0][1] = d2.x; mul[1][0] = mul[1][1] = d2.y;
                         sub[0] = sub[1] = 0.f;
-                    } else {   // d1 = d*sc, m1 = dmin*m, each rounded (gguf-py / oracle/quants.py order)
+                    } else if constexpr (QT == 1) {   // d1 = d*sc, m1 = dmin*m, each rounded (gguf-py / oracle/quants.py order)
+                        const uint32_t scw = __shfl_sync(0xffffffffu, cur.sc, g * 4 + jj);
                         const float2 dg = __half22float2(*(const __half2 *)&cur.dm.x), dg8 = __half22float2(*(const __half2 *)&cur.dm.y);
-                        mul[0] = __fmul_rn(dg.x, byte_to_float(scw, 0)); sub[0] = __fmul_rn(dg.y, byte_to_float(scw, 1));
-                        mul[1] = __fmul_rn(dg8.x, byte_to_float(scw, 2)); sub[1] = __fmul_rn(dg8.y, byte_to_float(scw, 3));
+                        mul[0][0] = mul[0][1] = __fmul_rn(dg.x, byte_to_float(scw, 0)); sub[0] = __fmul_rn(dg.y, byte_to_float(scw, 1));
+                        mul[1][0] = mul[1][1] = __fmul_rn(dg8.x, byte_to_float(scw, 2)); sub[1] = __fmul_rn(dg8.y, byte_to_float(scw, 3));
+                    } else {   // dsc = d*sc per 16-element half, rounded (oracle/quants.py order); int8 scale as byte + 128
+                        const uint32_t sw = (jj == 0 ? cur.sd4.x : jj == 1 ? cur.sd4.y : jj == 2 ? cur.sd4.z : cur.sd4.w) ^ 0x80808080u;
+                        const float2 dd = __half22float2(*(const __half2 *)&cur.sc);
+                        mul[0][0] = __fmul_rn(dd.x, byte_to_float(sw, 0) - 128.0f); mul[0][1] = __fmul_rn(dd.x, byte_to_float(sw, 1) - 128.0f);
+                        mul[1][0] = __fmul_rn(dd.y, byte_to_float(sw, 2) - 128.0f); mul[1][1] = __fmul_rn(dd.y, byte_to_float(sw, 3) - 128.0f);
+                        sub[0] = sub[1] = 0.f;
+                        const uint32_t hg = jj < 2 ? cur.wh.x : cur.wh.y, hg8 = jj < 2 ? cur.wh.z : cur.wh.w;
+                        hbits[0] = (hg >> (16 * (jj & 1))) & 0xFFFFu;
+                        hbits[1] = (hg8 >> (16 * (jj & 1))) & 0xFFFFu;
                     }
 #pragma unroll
                     for (int hf = 0; hf < 2; ++hf) {          // tile row g (hf 0) / g+8 (hf 1)
@@ -338,9 +362,11 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                             uint32_t parts[4][NPART];
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
-                                const uint32_t q = (word >> (8 * e + 4 * kh)) & 0xFu;
-                                const float qf = __uint_as_float(0x4B000000u | q) - 8388608.0f;           // q as a float without I2F
-                                const float wv = QT == 0 ? __fmul_rn(mul[hf], qf - 8.0f) : __fsub_rn(__fmul_rn(qf, mul[hf]), sub[hf]);
+                                uint32_t q = (word >> (8 * e + 4 * kh)) & 0xFu;
+                                if constexpr (QT == 2) q |= ((hbits[hf] >> (8 * kh + 2 * e)) & 3u) << 4;
+                                // q as a float without I2F: 0x4B000000 | q is 8388608 + q; the offset of the format goes into the same subtraction
+                                const float qf = __uint_as_float(0x4B000000u | q) - (QT == 0 ? 8388616.0f : QT == 1 ? 8388608.0f : 8388640.0f);
+                                const float wv = QT == 1 ? __fsub_rn(__fmul_rn(qf, mul[hf][kh]), sub[hf]) : __fmul_rn(mul[hf][kh], qf);
                                 split_bf16<NPART>(wv, parts[e]);
                             }
                             // 4 consecutive k of row (hf*8 + g) of tile lw: 8 bytes of the image of k-step (bb*2 + kh)
@@ -455,7 +481,7 @@ static cudaError_t launch_pf_qt(const PfArgs &a, int grid, cudaStream_t st) {
 }
 template <int T, int OUT>
 static cudaError_t launch_pf(const PfArgs &a, int qt, int grid, cudaStream_t st) {
-    return qt ? launch_pf_qt<T, OUT, 1>(a, grid, st) : launch_pf_qt<T, OUT, 0>(a, grid, st);
+    return qt == 2 ? launch_pf_qt<T, OUT, 2>(a, grid, st) : qt ? launch_pf_qt<T, OUT, 1>(a, grid, st) : launch_pf_qt<T, OUT, 0>(a, grid, st);
 }
 
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,

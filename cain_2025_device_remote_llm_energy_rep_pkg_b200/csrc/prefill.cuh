@@ -41,7 +41,7 @@ cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M
                                  void *pb, cudaStream_t st);
 // `part` (may be NULL): scratch of part_floats floats for split-K partial sums (up to 8 * T * rows are used)
 // y[m][row] (row stride ldy) = sum_k W[row][k] * grid(x[m])[k]  (+ bias[row] | + res[m][row] | act(gate)*up with ldy = rows/2)
-// qt: 0 = Q4_0 matrix, 1 = Q4_K matrix
+// qt: 0 = Q4_0 matrix, 1 = Q4_K, 2 = Q6_K
 cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
                                    const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,

@@ -40,6 +40,26 @@ def test_q6k_gemv(lib, D, rows, cols):
     assert np.all(np.abs(dy2.to_numpy(np.float32, (rows,)) - want) <= 8e-6 * mag + 1e-30)
 
 
+@pytest.mark.parametrize("rows,cols,M", [(128, 256, 3), (1000, 512, 17), (4096, 4096, 33), (256, 14336, 64)])
+def test_q6k_prefill_gemm(lib, D, rows, cols, M):
+    """The tcgen05 prompt GEMM on a Q6_K matrix (llama.cpp's Q4_K_M keeps attn_v and ffn_down in this format) against the
+    dequantised reference and the decode GEMV: the builder dequantises d*sc*(q-32) exactly and splits it into three bf16 parts."""
+    rng = np.random.default_rng(rows + cols + M)
+    blob = Q.quantize_q6_k((rng.standard_normal((rows, cols)) * 0.02).astype(np.float32))
+    x = (rng.standard_normal((M, cols)) * np.exp(rng.standard_normal((M, cols)))).astype(np.float32)
+    dW, dx = pack6(lib, D, blob, rows, cols), D.from_numpy(x)
+    dy = D(M * rows * 4)
+    chk(lib, lib.b2_op_prefill_gemm(Q6K, dW.ptr, rows, cols, dx.ptr, M, None, 0.0, 0, None, 0, 0, dy.ptr))
+    y = dy.to_numpy(np.float32, (M, rows))
+    dy1, dx1 = D(rows * 4), D(cols * 4)
+    for m in sorted({0, M // 2, M - 1}):
+        want, mag = ref(blob, x[m])
+        assert np.all(np.abs(y[m] - want) <= 8e-6 * mag + 1e-30), f"token {m} vs reference"
+        chk(lib, lib.b2_dev_upload(dx1.ptr, x[m].ctypes.data, cols * 4))
+        chk(lib, lib.b2_op_gemv_f32(Q6K, dW.ptr, rows, cols, dx1.ptr, None, 0, dy1.ptr))
+        assert np.all(np.abs(y[m] - dy1.to_numpy(np.float32, (rows,))) <= 8e-6 * mag + 1e-30), f"token {m} vs decode kernel"
+
+
 def test_q6k_head_logits(lib, D):
     rng = np.random.default_rng(9)
     V, H = 5000, 4096
@@ -78,6 +98,13 @@ def test_model_with_q6k_head_matches_oracle(key, qtype, gpu_engine):
     assert np.abs(got - want).max() <= 2e-4 * np.abs(want).max()
     s = m.session(96)
     assert list(map(int, s.generate_greedy(prompt, 40))) == om.session(96).generate_greedy(prompt, 40)
+    # the prompt as ONE batch: q, k, v of different formats and the Q6_K ffn_down all go through the tcgen05 prompt GEMM
+    long_prompt = [1 + (i * 37) % (a.V - 1) for i in range(70)]
+    s2 = m.session(96)
+    lg = s2.prefill(long_prompt, want_logits=True)
+    want_lg = om.session(96).prefill(long_prompt).numpy()
+    assert np.abs(lg - want_lg).max() <= 2e-4 * np.abs(want_lg).max()
+    assert list(map(int, s2.decode(20))) == om.session(96).generate_greedy(long_prompt, 20)
 
 
 def test_q4_k_m_style_mixed_formats_match_oracle(gpu_engine):
@@ -101,3 +128,10 @@ def test_q4_k_m_style_mixed_formats_match_oracle(gpu_engine):
     assert np.abs(got - want).max() <= 2e-4 * np.abs(want).max()
     s = m.session(96)
     assert list(map(int, s.generate_greedy(prompt, 40))) == om.session(96).generate_greedy(prompt, 40)
+    # the prompt as ONE batch: q, k, v of different formats and the Q6_K ffn_down all go through the tcgen05 prompt GEMM
+    long_prompt = [1 + (i * 37) % (a.V - 1) for i in range(70)]
+    s2 = m.session(96)
+    lg = s2.prefill(long_prompt, want_logits=True)
+    want_lg = om.session(96).prefill(long_prompt).numpy()
+    assert np.abs(lg - want_lg).max() <= 2e-4 * np.abs(want_lg).max()
+    assert list(map(int, s2.decode(20))) == om.session(96).generate_greedy(long_prompt, 20)
