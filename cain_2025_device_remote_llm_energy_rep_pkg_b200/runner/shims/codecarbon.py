@@ -22,8 +22,25 @@ def _rapl_uj():
     return tot if ok else None
 
 
+def _server_mj(devs):
+    """The server's side channel first: it holds NVML open, this process was forked for one run and would pay an NVML start-up."""
+    try:
+        import json
+        import urllib.request
+        host = os.environ.get("B2_SERVER_HOST") or "127.0.0.1"
+        with urllib.request.urlopen(f"http://{host}:{os.environ.get('B2_SERVER_PORT', '11434')}/b2/gpus", timeout=1.0) as r:
+            gpus = json.loads(r.read().decode()).get("gpus", {})
+        vals = [gpus[str(d)]["energy_mj"] for d in devs]
+        return None if any(v is None for v in vals) else sum(vals)
+    except Exception:
+        return None
+
+
 def _nvml_mj():
     devs = [int(d) for d in os.environ.get("B2_NVML_DEVICES", "0").split(",") if d != ""]
+    got = _server_mj(devs)
+    if got is not None:
+        return got
     try:
         import pynvml
         pynvml.nvmlInit()

@@ -203,6 +203,14 @@ class B2Backend:
                 a = self.arch(tag)
                 model = Model.random(self.engine, a, seed=self.seed, qtype=self.qtype)
             sess = model.session(a.max_ctx)
+            # one throw-away generation: the CUDA graphs of both attention variants (contexts below / above 32 positions) and of the
+            # multi-token decode are captured here, not inside the first measured request (0.8 s instead of 0.2 s on the first hit)
+            try:
+                sess.prefill([1, 2, 3])
+                sess.decode(min(48, a.max_ctx - 4))
+                sess.reset()
+            except Exception:
+                pass
             self.models[tag] = (model, sess, time.perf_counter_ns() - t0)
             return self.models[tag], self.models[tag][2]
         return self.models[tag], 0
@@ -213,6 +221,16 @@ class B2Backend:
             return nvml_energy_mj(self.device)
         except Exception:
             return None
+
+    def gpu_status(self) -> dict:
+        """NVML counters of this backend's GPU, read in the server process (which holds NVML open): the runner's measurement
+        processes are forked per run and would otherwise each pay an NVML initialisation, which on an 8-GPU box costs more than a
+        short request."""
+        import ctypes as C
+        lib = self.engine.lib
+        gpu, mem = C.c_uint32(), C.c_uint32()
+        util = gpu.value if lib.b2_nvml_util(self.device, C.byref(gpu), C.byref(mem)) == 0 else None
+        return {str(self.device): {"energy_mj": self.energy_mj(), "util": gpu.value if util is not None else None}}
 
     def generate(self, tag: str, prompt: str, options: dict, raw: bool = False) -> Iterator[dict]:
         """Yields {"tokens": [...]} chunks, then a final {"done": True, ...stats}."""
@@ -303,6 +321,13 @@ class MultiBackend:
         with self._lock:
             return [getattr(b, "device", i) for i, b in enumerate(self.backends) if self.active[i] > 0]
 
+    def gpu_status(self) -> dict:
+        out = {}
+        for b in self.backends:
+            if hasattr(b, "gpu_status"):
+                out.update(b.gpu_status())
+        return out
+
     def pick(self, tag: str) -> int:
         with self._lock:
             i = min(range(len(self.backends)),
@@ -341,8 +366,9 @@ class Handler(BaseHTTPRequestHandler):
     protocol_version = "HTTP/1.1"
     server_version = "b2llm"
 
-    def log_message(self, fmt, *args):  # requests are logged by the server object
-        self.server.log(fmt % args)
+    def log_message(self, fmt, *args):  # requests are logged by the server object; the side channel's polls are not
+        if not str(self.path).startswith("/b2/"):
+            self.server.log(fmt % args)
 
     # ------------------------------------------------------------------ helpers
     def _send_json(self, code: int, obj, extra_headers=None):
@@ -384,6 +410,9 @@ class Handler(BaseHTTPRequestHandler):
             self._send_json(200, {"models": [{"name": m, "model": m} for m in b.loaded()]})
         elif self.path.startswith("/b2/active"):   # devices serving a request right now (the powermetrics stand-in samples those)
             self._send_json(200, {"devices": b.busy_devices() if hasattr(b, "busy_devices") else []})
+        elif self.path.startswith("/b2/gpus"):     # NVML energy counters and utilisation per GPU, for the runner's per-run processes
+            self._send_json(200, {"gpus": b.gpu_status() if hasattr(b, "gpu_status") else {},
+                                  "busy": b.busy_devices() if hasattr(b, "busy_devices") else []})
         elif self.path.startswith("/b2/stats"):
             self._send_json(200, {"requests": self.server.stats_log[-int(self.server.keep_stats):]})
         else:
@@ -492,7 +521,7 @@ class OllamaServer(ThreadingHTTPServer):
         super().__init__(addr, Handler)
         self.backend, self.stats_file, self.verbose = backend, stats_file, verbose
         self.stats_log: List[dict] = []
-        self.keep_stats = 64
+        self.keep_stats = 256
         self._lock = threading.Lock()
 
     def log(self, msg: str):

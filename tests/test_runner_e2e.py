@@ -89,6 +89,9 @@ def test_two_runner_shards_share_port_11434_and_split_the_rows(tmp_path):
     assert [len(t) for t in per_shard] == [4, 4] and not ({r["__run_id"] for r in per_shard[0]} & {r["__run_id"] for r in per_shard[1]})
     for r in rows:   # 100 words -> 133 tokens, 500 -> 665: the record of this row's own request, not a neighbour's
         assert float(r["nvml__eval_count"]) == {"100": 133, "500": 665}[r["length"]]
+        # energy and utilisation came through the server's side channel (no NVML in this container): the stub's counters; the
+        # sampler's first line is 0 % while it starts, so the mean sits a little below the stub's 42 %
+        assert float(r["nvml__energy_J"]) > 0 and 30.0 < float(r["gpu_usage"]) <= 42.0 and float(r["codecarbon__energy_consumed"]) > 0
     assert len(b0.requests) + len(b1.requests) == 8 and len(b0.requests) >= 2 and len(b1.requests) >= 2   # both backends worked
 
 

@@ -84,6 +84,28 @@ def _worker(rank, world, port, case, out_dir):
         h2, lh2 = solo.decode(3, want_logits=True)
         res["solo_mixed"] = np.concatenate([h1, t1, h2])
         res["solo_mixed_logits"] = lh2
+    elif case["kind"] == "stress":
+        # passes without the LM head (prompt body), vocabulary-parallel greedy steps, sampled steps (no arg-max exchange)
+        # and replicated steps alternate for more than a thousand forward passes; the slot buffers and tags must never mix rounds.
+        if case.get("no_pdl"):
+            os.environ["B2_NO_PDL"] = "1"       # read at b2_session_create: plain stream order instead of programmatic launches
+        a, _ = tp_arch(case["key"])
+        tensors = engine.host_random_tensors(a, seed=case["seed"])
+        sess = engine.Model.from_tensors(eng, a, tensors, max_ctx=160).session(160)
+        solo = engine.Model.from_tensors(engine.Engine(rank), a, tensors, max_ctx=160).session(160)
+        samp = engine.SamplerCfg(8, 0.8, 0.95, 99)
+        got, want, passes = [], [], 0
+        for rnd in range(case["rounds"]):
+            prompt = [1 + (7 * i + 13 * rnd) % (a.V - 1) for i in range(40 + rnd % 5)]
+            for s_, out in ((sess, got), (solo, want)):
+                s_.reset()
+                s_.prefill(prompt)                       # tensor parallel: token by token, every pass but the last without the LM head
+                out.append(s_.decode(24))                # greedy: LM head split over the ranks, last step replicated
+                out.append(s_.decode(16, sampler=samp))  # sampled: whole head on every rank, no arg-max exchange
+                out.append(s_.decode(1))                 # a single greedy step: replicated
+                out.append(s_.decode(9))
+            passes += len(prompt) + 50
+        res["got"], res["want"], res["passes"] = np.concatenate(got), np.concatenate(want), np.array(passes)
     elif case["kind"] == "missing_peer":   # rank 1 never makes the call: rank 0 must get an error in seconds, not hang
         import time
         from cain_2025_device_remote_llm_energy_rep_pkg_b200._lib import B2Error
@@ -194,6 +216,20 @@ def test_tp2_q4k_layers_q6k_head_match_oracle(lib, tmp_path):
     want = np.stack([os_.step(t).numpy() for t in PROMPT])
     assert np.abs(r0["logits"] - want).max() <= 2e-4 * np.abs(want).max()      # bar of the single-GPU K-quant test (test_q4k_gpu.py)
     assert list(map(int, r0["greedy"])) == om.session(96).generate_greedy(PROMPT, 40)
+
+
+@needs2
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("no_pdl", [False, True])
+def test_tp2_alternating_calls_for_a_thousand_passes(lib, tmp_path, no_pdl):
+    """Long prompts (passes without the LM head), vocabulary-parallel greedy, sampled and replicated steps in turn, > 1 000 forward
+    passes on one pair of engines: every token equals the single-GPU engine's on the same weights, on both ranks, and no wait on a
+    peer ever timed out (a call would have failed with B2_ENCCL).  Also with programmatic launches off (B2_NO_PDL=1), which would
+    tell an ordering problem of the launch chain from one of the exchange itself."""
+    r0, r1 = run_case(tmp_path, {"kind": "stress", "key": "llama3.1:8b", "seed": 17, "rounds": 12, "no_pdl": no_pdl})
+    assert int(r0["passes"]) >= 1000
+    assert np.array_equal(r0["got"], r1["got"])
+    assert np.array_equal(r0["got"], r0["want"]) and np.array_equal(r1["got"], r1["want"])
 
 
 @needs2

@@ -7,6 +7,7 @@ set -u
 cd "$(dirname "$0")/.."
 N=${1:-8}
 REPS=${2:-1}
+ONLY=${3:-both}
 OUT=gpurun_out/r02_sweep
 mkdir -p $OUT
 ALL="llama3.1:8b,gemma:2b,gemma:7b,phi3:3.8b,qwen2:1.5b,qwen2:7b,mistral:7b"
@@ -21,10 +22,12 @@ run() {  # run <shards> <devices>
   echo "shards=$k devices=$devs rc=$rc total_with_server_start_s=$(python -c "print(round($t1-$t0,1))") $(grep 'sweep wall time' $OUT/launch_$k.log)" | tee -a $OUT/summary.txt
   if [ $k -gt 1 ]; then cp $work/run_table.csv $OUT/run_table_${k}gpu.csv 2>/dev/null; else cp $work/experiments_output/b200/run_table.csv $OUT/run_table_1gpu.csv 2>/dev/null; fi
   cp $work/server.log $OUT/server_$k.log 2>/dev/null
+  cp $work/server_stats.jsonl $OUT/server_stats_$k.jsonl 2>/dev/null
+  for i in 0 1; do cp $work/shard$i/runner.log $OUT/runner_${k}_shard$i.log 2>/dev/null; done
   tail -3 $work/shard0/runner.log $work/runner.log 2>/dev/null | tail -5 >> $OUT/launch_$k.log
 }
-: > $OUT/summary.txt
-run 1 0
+[ "$ONLY" = both ] && : > $OUT/summary.txt
+if [ "$ONLY" = both ] || [ "$N" -eq 1 ]; then run 1 0; fi
 if [ "$N" -gt 1 ]; then run $N 0-$((N-1)); fi
 python - <<PY
 import csv, json, collections
