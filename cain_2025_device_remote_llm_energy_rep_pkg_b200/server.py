@@ -222,15 +222,14 @@ class B2Backend:
         except Exception:
             return None
 
-    def gpu_status(self) -> dict:
-        """NVML counters of this backend's GPU, read in the server process (which holds NVML open): the runner's measurement
-        processes are forked per run and would otherwise each pay an NVML initialisation, which on an 8-GPU box costs more than a
-        short request."""
+    def gpu_status(self, energy: bool = True) -> dict:
+        """NVML counters of this backend's GPU, read in the server process (which holds NVML open) for the runner's measurement
+        processes, which are forked per run.  The energy counter costs 4.5 ms per read (the utilisation 25 us): pollers ask without it."""
         import ctypes as C
         lib = self.engine.lib
         gpu, mem = C.c_uint32(), C.c_uint32()
-        util = gpu.value if lib.b2_nvml_util(self.device, C.byref(gpu), C.byref(mem)) == 0 else None
-        return {str(self.device): {"energy_mj": self.energy_mj(), "util": gpu.value if util is not None else None}}
+        ok = lib.b2_nvml_util(self.device, C.byref(gpu), C.byref(mem)) == 0
+        return {str(self.device): {"energy_mj": self.energy_mj() if energy else None, "util": gpu.value if ok else None}}
 
     def generate(self, tag: str, prompt: str, options: dict, raw: bool = False) -> Iterator[dict]:
         """Yields {"tokens": [...]} chunks, then a final {"done": True, ...stats}."""
@@ -321,11 +320,11 @@ class MultiBackend:
         with self._lock:
             return [getattr(b, "device", i) for i, b in enumerate(self.backends) if self.active[i] > 0]
 
-    def gpu_status(self) -> dict:
+    def gpu_status(self, energy: bool = True) -> dict:
         out = {}
         for b in self.backends:
             if hasattr(b, "gpu_status"):
-                out.update(b.gpu_status())
+                out.update(b.gpu_status(energy))
         return out
 
     def pick(self, tag: str) -> int:
@@ -411,7 +410,7 @@ class Handler(BaseHTTPRequestHandler):
         elif self.path.startswith("/b2/active"):   # devices serving a request right now (the powermetrics stand-in samples those)
             self._send_json(200, {"devices": b.busy_devices() if hasattr(b, "busy_devices") else []})
         elif self.path.startswith("/b2/gpus"):     # NVML energy counters and utilisation per GPU, for the runner's per-run processes
-            self._send_json(200, {"gpus": b.gpu_status() if hasattr(b, "gpu_status") else {},
+            self._send_json(200, {"gpus": b.gpu_status("util_only" not in self.path) if hasattr(b, "gpu_status") else {},
                                   "busy": b.busy_devices() if hasattr(b, "busy_devices") else []})
         elif self.path.startswith("/b2/stats"):
             self._send_json(200, {"requests": self.server.stats_log[-int(self.server.keep_stats):]})

@@ -16,7 +16,7 @@ class StubBackend:
     def list_models(self):
         return list(ARCHS)
 
-    def gpu_status(self):
+    def gpu_status(self, energy=True):
         """Side channel of the real backend (GET /b2/gpus): a fake energy counter that advances 1 J per call, 42 % utilisation."""
         self._mj = getattr(self, "_mj", 5_000_000) + 1000
         return {str(getattr(self, "device", 0)): {"energy_mj": self._mj, "util": 42}}
