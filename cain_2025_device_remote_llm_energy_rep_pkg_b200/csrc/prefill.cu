@@ -157,6 +157,12 @@ __device__ __forceinline__ void split_bf16(float w, uint32_t (&part)[NPART]) {
     }
 }
 
+#ifndef PF_RING3
+#define PF_RING3 0          // 1: three register sets of weights rotate through a loop unrolled by three (two block-groups ahead)
+#endif
+#ifndef PF_HS_UNROLL
+#define PF_HS_UNROLL 2      // 1: the two stages of a block-group share one copy of the dequantisation code
+#endif
 template <int T, int OUT, int QT>
 __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) {
     constexpr int NPART = QT ? 3 : 2;
@@ -293,10 +299,11 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                 }
             }
         };
-        // Three block-groups of registers rotate: while one is turned into A operands the loads of the next two are in flight.  The
-        // loop is unrolled by three so that the rotation costs no register copies (a copy would wait for the load it copies).
-        // (Measured: the depth does not matter, 0 / 1 / 2 block-groups ahead give 9.4 / 9.3 / 9.8 ms per 32-token prompt; the loads hit
-        // L2 behind the item-ahead bulk prefetch.)
+        // The loads of the next block-group are in flight while the current one is turned into A operands.  How far ahead does not
+        // matter (0 / 1 block-groups ahead: 9.4 / 9.3 ms per 32-token prompt; the loads hit L2 behind the item-ahead bulk prefetch), how
+        // much CODE the loop has does: ncu shows 21-33 % of the warp samples of this kernel waiting for instructions.  Two block-groups
+        // ahead through a loop unrolled by three (three copies of the dequantisation code, -DPF_RING3=1) costs 14 %: 9.8 / 11.1 / 96 ms
+        // against 8.6 / 9.7 / 85 ms for prompts of 32 / 64 / 512 tokens with the single copy below.
         struct Cursor { int wi, grp, ks, bgi, bg1; };
         auto start = [&](Cursor &c, int wi) {
             c.wi = wi; c.grp = c.ks = c.bgi = c.bg1 = 0;
@@ -318,12 +325,15 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         Regs r0, r1, r2;
         if (fill.wi < n_items) issue(fill.grp, fill.bgi, r0);
         advance(fill, true);
+#if PF_RING3
         if (fill.wi < n_items) issue(fill.grp, fill.bgi, r1);
         advance(fill, true);
+#endif
         auto build = [&](const Regs &cur) {
             const uint32_t w0[4] = {cur.v0.x ^ 0x88888888u, cur.v0.y ^ 0x88888888u, cur.v0.z ^ 0x88888888u, cur.v0.w ^ 0x88888888u};   // GGML nibbles q of row g
             const uint32_t w1[4] = {cur.v1.x ^ 0x88888888u, cur.v1.y ^ 0x88888888u, cur.v1.z ^ 0x88888888u, cur.v1.w ^ 0x88888888u};   // row g+8
-#pragma unroll
+            constexpr int HS_UNROLL = PF_HS_UNROLL;
+#pragma unroll HS_UNROLL
             for (int hs = 0; hs < 2; ++hs, ++it) {   // the two stages of the block-group: blocks 2hs, 2hs+1
                 const int slot = it % PF_STAGES;
                 mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
@@ -389,11 +399,22 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
             build(cur);
             advance(use, false);
         };
+#if PF_RING3
         while (use.wi < n_items) {
             step(r0, r2);
             step(r1, r0);
             step(r2, r1);
         }
+#else
+        (void)r2;
+        while (use.wi < n_items) {   // one block-group ahead, one copy of the build code
+            if (fill.wi < n_items) issue(fill.grp, fill.bgi, r1);
+            advance(fill, true);
+            build(r0);
+            advance(use, false);
+            r0 = r1;
+        }
+#endif
     } else if (warp == 12) {
         // ===================== MMA issue (one thread)
         if (lane == 0) {
