@@ -52,13 +52,19 @@ extern "C" const char *b2_version(void) { return "b2llm 0.1 (sm_100a)"; }
 // overwrites slots a slower rank still reads (a rank cannot be two exchanges ahead: each exchange needs every rank's pairs).
 #define TP_MAX_VEC 8192
 #define TP_MAX_RANKS 8
+#define TP_PF_TOKENS 64
 struct TpLink {
     int n = 1, rank = 0;
     void *local = nullptr;
     void *peer[TP_MAX_RANKS] = {};
     bool connected = false;
     static constexpr size_t slots_bytes() { return (size_t)2 * TP_MAX_RANKS * TP_MAX_VEC * 8; }
-    static constexpr size_t bytes() { return slots_bytes() + 512; }
+    // batched prompt evaluation: the same two buffers of eight slots, TP_PF_TOKENS tokens deep (behind the 512 bytes of flags)
+    static constexpr size_t batch_slot_pairs() { return (size_t)TP_PF_TOKENS * TP_MAX_VEC; }
+    static constexpr size_t bytes() { return slots_bytes() + 512 + (size_t)2 * TP_MAX_RANKS * batch_slot_pairs() * 8; }
+    void *batch_slot(int on_rank, int buf, int src) const {
+        return (char *)peer[on_rank] + slots_bytes() + 512 + ((size_t)buf * TP_MAX_RANKS + src) * batch_slot_pairs() * 8;
+    }
     void *amax(int on_rank) const { return (char *)peer[on_rank] + slots_bytes() + 256; }
     void *slot(int on_rank, int buf, int src) const { return (char *)peer[on_rank] + ((size_t)buf * TP_MAX_RANKS + src) * TP_MAX_VEC * 8; }
     unsigned long long *forwards() const { return (unsigned long long *)((char *)local + slots_bytes()); }
@@ -894,8 +900,7 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
     const char *npg = getenv("B2_NO_PREFILL_GEMM");
     s->use_pf_gemm = !(npg && npg[0] == '1');
     if (const char *gt = getenv("B2_GRAPH_TOKENS")) { s->multi_n = atoi(gt); if (s->multi_n < 1 || s->multi_n > 64) s->multi_n = 1; }
-    if (m->tp > 1) {   // the tensor-parallel pass exists for the per-stage decode kernels: prompts go through it token by token
-        s->use_pf_gemm = false;
+    if (m->tp > 1) {   // prompts of three tokens and more are evaluated in batches here too (prefill_batched: the row-parallel GEMMs end in an exchange)
         s->fused_attn = true;
         for (const LayerW &ly : m->layers)
             if (ly.split_qkv) { delete s; b2_set_error("tensor parallel sessions need q, k and v of a layer in one format"); return B2_EINVAL; }
@@ -1059,6 +1064,21 @@ static int prefill_batched(b2_session *s, int n) {
     const float escale = c.embed_scale ? sqrtf((float)H) : 1.0f;
     const uint64_t layer_kv = (uint64_t)s->n_pages * m->kv_heads() * PAGE_TOKENS * hd;
     int launches = 0;
+    // tensor parallel: QKV and gate/up are column-parallel (this rank's rows, complete sums), O and down row-parallel: their split-K
+    // partials are exchanged as tagged pairs (buffer 0: O rounds, buffer 1: down rounds, as in the decode pass) and the residual is added
+    // to the sum over the ranks in rank order, so every rank holds the same batch of residuals
+    const TpLink &L = m->e->tp;
+    const int tpn = m->tp, rounds = 2 * c.n_layers;
+    auto row_parallel = [&](const Mat &mt, int64_t kcols, int buf, int round, int mb, int T) -> int {
+        int ks = 1;
+        B2_CUDA(launch_prefill_gemm_qt(qt_of(mt.type), PF_OUT_BIAS, mt.packed, H, kcols, s->pf_pb, mb, T, nullptr, H, nullptr, 0, sms, s->pf_part, s->pf_part_floats, st,
+                                       true, &ks));
+        void *dst[TP_MAX_RANKS] = {};
+        for (int p = 0; p < tpn; ++p) dst[p] = L.batch_slot(p, buf, L.rank);
+        launch_pf_tp_exchange(s->pf_part, ks, T, mb, H, dst, L.batch_slot(L.rank, buf, 0), TpLink::batch_slot_pairs(), tpn, s->pf_x, s->pf_x, H, L.forwards(), rounds, round,
+                              L.error(), st);
+        return B2_OK;
+    };
     for (int m0 = 0; m0 < n; m0 += 64) {
         const int mb = n - m0 < 64 ? n - m0 : 64, T = pf_batch(mb), pos0 = s->host_pos + m0;
         launch_prefill_embed(qt_of(m->embd.type), m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
@@ -1079,12 +1099,20 @@ static int prefill_batched(b2_session *s, int n) {
             B2_CUDA(launch_prefill_attention(s->pf_qkv, ldq, mb, m->heads(), m->kv_heads(), hd, pos0, m->rope_cos, m->rope_sin,
                                              s->kcache + l * layer_kv, s->vcache + l * layer_kv, s->page_table, s->pf_attn, qd, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_attn, qd, mb, T, qd, nullptr, 0.f, 0, s->pf_pb, st));
+            if (tpn > 1) B2_TRY(row_parallel(ly.o, qd, 0, 2 * l, mb, T));
+            else
             B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.o.type), PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.ffn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
             B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.gateup.type), PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_h, I, mb, T, I, nullptr, 0.f, 0, s->pf_pb, st));
+            if (tpn > 1) B2_TRY(row_parallel(ly.down, I, 1, 2 * l + 1, mb, T));
+            else
             B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.down.type), PF_OUT_RES, ly.down.packed, H, I, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
-            launches += 10;
+            launches += tpn > 1 ? 14 : 10;
+        }
+        if (tpn > 1) {   // the batch counts as one forward pass: the next pass's tags differ (every round of this one was seen complete by its gather)
+            launch_tp_close(L.slot(L.rank, 1, 0), TP_MAX_VEC, tpn, H, L.forwards(), rounds, rounds - 1, false, L.error(), st);
+            launches++;
         }
         if (m0 + mb == n) {   // LM head for the last token of the prompt
             B2_CUDA(cudaMemcpyAsync(s->x, s->pf_x + (int64_t)(mb - 1) * H, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));

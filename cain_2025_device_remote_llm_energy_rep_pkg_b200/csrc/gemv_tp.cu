@@ -106,3 +106,53 @@ void launch_tp_argmax(const float *pmax, const int *pidx, int n, void *const *pe
     for (int p = 0; p < 8; ++p) peers.p[p] = p < tp_n ? (uint4 *)peer_slots[p] : nullptr;
     k_tp_argmax<<<1, 32, 0, st>>>(pmax, pidx, n, peers, tp_n, rank, (const uint4 *)local_slots, fwd, err, d_out);
 }
+
+// ------------------------------------------------------------------------------------------ batched prompt evaluation
+// The row-parallel prompt GEMMs (O projection, down projection) of a tensor-parallel rank end in the same exchange as the decode
+// GEMVs, for a whole batch of tokens: k_pf_tp_scatter adds the GEMM's split-K partials in their fixed order and stores every
+// (token, row) sum as a tagged pair into slot [this rank] of EVERY rank's batch buffer (plain stores over NVLink); k_pf_tp_gather
+// reads the pairs of this GPU's buffer until they carry the round's tag and forms x = residual + slot_0 + ... + slot_{n-1} in rank
+// order, bit-identical on every rank.  Loads only ever read this GPU's memory.
+struct PfTpDst { uint2 *p[8]; };
+__global__ void __launch_bounds__(256) k_pf_tp_scatter(const float *__restrict__ part, int ksplit, int T, int M, int rows, PfTpDst dst, int tp_n,
+                                                       const unsigned long long *fwd, int rounds, int round) {
+    const int row = blockIdx.x * 256 + threadIdx.x, m = blockIdx.y;
+    if (row >= rows || m >= M) return;
+    float v = 0.f;
+    for (int s = 0; s < ksplit; ++s) v += part[((int64_t)s * T + m) * rows + row];
+    const uint32_t tag = (uint32_t)(__ldcg(fwd) * (unsigned long long)rounds + (unsigned long long)round + 1ull);
+    const size_t i = (size_t)m * rows + row;
+#pragma unroll
+    for (int p = 0; p < 8; ++p)
+        if (p < tp_n) st_volatile_v2(dst.p[p] + i, __float_as_uint(v), tag);
+}
+__global__ void __launch_bounds__(256) k_pf_tp_gather(const uint2 *slots, size_t slot_stride, int tp_n, int M, int rows, const float *res, float *y,
+                                                      int64_t ld, const unsigned long long *fwd, int rounds, int round, unsigned int *err) {
+    const int row = blockIdx.x * 256 + threadIdx.x, m = blockIdx.y;
+    if (row >= rows || m >= M) return;
+    const uint32_t tag = (uint32_t)(__ldcg(fwd) * (unsigned long long)rounds + (unsigned long long)round + 1ull);
+    const size_t i = (size_t)m * rows + row;
+    float v = res[(int64_t)m * ld + row];
+    const long long t_begin = global_timer_ns();
+    for (int r = 0; r < tp_n; ++r) {
+        const uint2 *sp = slots + (size_t)r * slot_stride + i;
+        uint2 pr;
+        uint32_t spins = 0;
+        for (;;) {
+            asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(pr.x), "=r"(pr.y) : "l"(sp) : "memory");
+            if (pr.y == tag) break;
+            if ((++spins & 255u) == 0u && (__ldcg(err) != 0u || global_timer_ns() - t_begin > TP_TIMEOUT_NS)) { atomicCAS(err, 0u, 1u + (unsigned)r); break; }
+        }
+        v = __fadd_rn(v, __uint_as_float(pr.x));
+    }
+    y[(int64_t)m * ld + row] = v;
+}
+void launch_pf_tp_exchange(const float *part, int ksplit, int T, int M, int rows, void *const *peer_slots, const void *local_slots, size_t slot_stride,
+                           int tp_n, const float *res, float *y, int64_t ld, const unsigned long long *fwd, int rounds, int round, unsigned int *err,
+                           cudaStream_t st) {
+    PfTpDst dst;
+    for (int p = 0; p < 8; ++p) dst.p[p] = p < tp_n ? (uint2 *)peer_slots[p] : nullptr;
+    const dim3 grid((unsigned)((rows + 255) / 256), M);
+    k_pf_tp_scatter<<<grid, 256, 0, st>>>(part, ksplit, T, M, rows, dst, tp_n, fwd, rounds, round);
+    k_pf_tp_gather<<<grid, 256, 0, st>>>((const uint2 *)local_slots, slot_stride, tp_n, M, rows, res, y, ld, fwd, rounds, round, err);
+}

@@ -70,6 +70,11 @@ cudaError_t launch_gemv_tp(const GemvTp &tp, int qt, int in_mode, int out_mode, 
 // greedy token of a tensor-parallel group: local arg-max partials -> one tagged 16-byte word per rank -> the same index everywhere
 void launch_tp_argmax(const float *pmax, const int *pidx, int n, void *const *peer_slots, int tp_n, int rank, const void *local_slots,
                       const unsigned long long *fwd, unsigned int *err, int32_t *d_out, cudaStream_t st);
+// batched prompt evaluation on a tensor-parallel rank: split-K partials of a row-parallel GEMM -> tagged pairs into every rank's batch
+// buffer (peer_slots[p] = slot of this rank on rank p), then y = res + sum over the ranks' slots of this GPU's buffer (rank order)
+void launch_pf_tp_exchange(const float *part, int ksplit, int T, int M, int rows, void *const *peer_slots, const void *local_slots, size_t slot_stride,
+                           int tp_n, const float *res, float *y, int64_t ld, const unsigned long long *fwd, int rounds, int round, unsigned int *err,
+                           cudaStream_t st);
 void launch_tp_close(const void *slots, int slot_stride, int n, int n_vec, unsigned long long *fwd, int rounds, int round, bool wait, unsigned int *err,
                      cudaStream_t st);
 void launch_embed_row(int qt, const void *d_packed, int64_t cols, const int *d_token, float scale, float *d_x, float *d_xsq, cudaStream_t st);

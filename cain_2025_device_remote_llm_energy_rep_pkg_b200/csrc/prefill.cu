@@ -127,6 +127,7 @@ struct PfArgs {
     int64_t ldy;
     const float *bias_or_res;
     int act;
+    int force_part;          // 1: raw sums go to `part` even when ksplit is 1 (tensor parallel: the sums are exchanged, not finished here)
     int ksplit;              // > 1: the K range of a row group is cut into ksplit pieces, one work item each; raw sums go to `part`
     float *part;             // [ksplit][T][rows] fp32 partial sums (k_prefill_finish adds them in a fixed order)
 };
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                 if (lane == 0) mbar_arrive(tempty + buf);
             }
             const int row = grp * PF_ROWS + row_l;
-            if (a.ksplit > 1) {
+            if (a.ksplit > 1 || a.force_part) {
 #pragma unroll
                 for (int u = 0; u < T; ++u)
                     if (u < a.M && row < a.rows) a.part[((int64_t)ks * T + u) * a.rows + row] = acc[u];
@@ -510,8 +511,10 @@ cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows
     return launch_prefill_gemm_qt(0, out_mode, d_packed, rows, cols, pb, M, T, y, ldy, bias_or_res, act, sm_count, part, part_floats, st);
 }
 cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
-                                   const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st) {
+                                   const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st,
+                                   bool partials_only, int *ksplit_out) {
     if (M <= 0 || M > T || rows <= 0 || cols <= 0) return cudaErrorInvalidValue;
+    if (partials_only && (!part || out_mode == PF_OUT_ACTMUL || (uint64_t)T * rows > part_floats)) return cudaErrorInvalidValue;
     if (out_mode == PF_OUT_RES && !bias_or_res) return cudaErrorInvalidValue;
     PfArgs a;
     a.w = (const uint8_t *)d_packed; a.rows = (int)rows; a.nbp = (int)nblocks_padded(cols); a.n_tiles = (int)ntiles(rows);
@@ -527,7 +530,8 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
         while (ksplit > 1 && (uint64_t)ksplit * T * rows > part_floats) --ksplit;
         if (ksplit < 1) ksplit = 1;
     }
-    a.ksplit = ksplit; a.part = part;
+    a.ksplit = ksplit; a.part = part; a.force_part = partials_only ? 1 : 0;
+    if (ksplit_out) *ksplit_out = ksplit;
     const int n_items = n_groups * ksplit;
     const int grid = n_items < sm_count ? n_items : sm_count;
     cudaError_t e = cudaErrorInvalidValue;
@@ -536,7 +540,7 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
     PF_CASE(32, PF_OUT_BIAS); PF_CASE(32, PF_OUT_RES); PF_CASE(32, PF_OUT_ACTMUL);
     PF_CASE(64, PF_OUT_BIAS); PF_CASE(64, PF_OUT_RES); PF_CASE(64, PF_OUT_ACTMUL);
 #undef PF_CASE
-    if (e != cudaSuccess || ksplit == 1) return e;
+    if (e != cudaSuccess || ksplit == 1 || partials_only) return e;
     k_prefill_finish<<<dim3((unsigned)((rows + 255) / 256), M), 256, 0, st>>>(part, ksplit, T, M, (int)rows, y, ldy, bias_or_res, out_mode);
     return cudaGetLastError();
 }

@@ -42,8 +42,11 @@ cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M
 // `part` (may be NULL): scratch of part_floats floats for split-K partial sums (up to 8 * T * rows are used)
 // y[m][row] (row stride ldy) = sum_k W[row][k] * grid(x[m])[k]  (+ bias[row] | + res[m][row] | act(gate)*up with ldy = rows/2)
 // qt: 0 = Q4_0 matrix, 1 = Q4_K, 2 = Q6_K
+// partials_only: the raw split-K sums stay in `part` ([ksplit][T][rows], *ksplit_out pieces, possibly 1) and no epilogue runs: a
+// tensor-parallel rank's row-parallel GEMM, whose sums are exchanged before the residual is added
 cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
-                                   const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
+                                   const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st,
+                                   bool partials_only = false, int *ksplit_out = nullptr);
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
                                 const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
 void launch_prefill_embed(int qt, const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st);

@@ -113,7 +113,8 @@ int b2_engine_device(const b2_engine *e, int *device_ordinal);
  * From then on every rank must make the same model / session / prefill / decode calls with the same arguments; each rank holds
  * 1/tp_size of every layer matrix and returns the same tokens and logits (the LM head is multiplied row-parallel in the steps of
  * a greedy b2_decode call, with the arg-max exchanged between the ranks, and in full wherever logits are handed out).  A rank whose peer does not show up
- * within 2 s fails the call with B2_ENCCL instead of hanging.  Prompts are evaluated token by token in this mode. */
+ * within 2 s fails the call with B2_ENCCL instead of hanging.  Prompts of three tokens and more are evaluated in
+ * batches in this mode too (the partial sums of the row-parallel prompt GEMMs travel the same way, a batch at a time). */
 #define B2_TP_HANDLE_BYTES 64
 int b2_engine_tp_handle(b2_engine *e, void *handle_out);
 int b2_engine_tp_connect(b2_engine *e, const void *handles);

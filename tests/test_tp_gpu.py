@@ -179,7 +179,10 @@ def test_tp2_tiny_matches_oracle_and_ranks_agree(lib, tmp_path, key):
     want = om.session(320).generate_greedy(PROMPT, 128)
     assert list(map(int, r0["greedy"])) == want
     assert np.array_equal(r0["logits_devinit"], r0["logits"][:len(PROMPT)])
-    assert np.array_equal(r0["prefill_logits"], r0["logits"][len(PROMPT) - 1])
+    # the prompt as one batch (tcgen05 GEMM, partial sums of the row-parallel products exchanged per batch) against token by token: the
+    # same terms in another order (bar of the single-GPU engine, test_model_gpu.py)
+    want_last = r0["logits"][len(PROMPT) - 1]
+    assert np.abs(r0["prefill_logits"] - want_last).max() <= 2e-4 * np.abs(want_last).max()
 
 
 @needs2
