@@ -291,7 +291,7 @@ def aggregate(dist, wall_s, eval_s, tokens, launches, energy_j, device="cuda"):
     return vec.tolist(), tot.tolist()
 
 
-TRAFFIC_FILE = "profiles/r01d_launches_summary.csv"
+TRAFFIC_FILE = "profiles/r02_launches_summary.csv"
 
 
 def ncu_traffic_per_token(model: str):
