@@ -36,11 +36,28 @@ __global__ void __launch_bounds__(128) k_attn_fused(const AttnArgs a) {
     attn_main<NSPLIT == 1 ? MERGE_NONE : MERGE_CLUSTER, PRE>(a, s, tid, h, split, NSPLIT, pos, 0, R);
 }
 
+// One CTA of NG groups of 128 threads per head: the groups split the context as the CTAs of a cluster do, but merge through the
+// CTA's shared memory (one __syncthreads instead of two cluster barriers and remote reads), and a layer's attention occupies nh SMs
+// instead of all of them, so that the O projection's CTAs become resident (and request their weights) while attention runs.
+template <int NG>
+__global__ void __launch_bounds__(128 * NG, 1) k_attn_fused_cta(const AttnArgs a) {
+    extern __shared__ __align__(16) float sm[];
+    const int tid = threadIdx.x & 127, grp = threadIdx.x >> 7, h = blockIdx.x;
+    const AttnSmem s = attn_carve(sm + (size_t)grp * a.group_stride, a.hd, a.pps_max);
+    if (threadIdx.x == 0) pdl_launch_a();
+    const int pos = a.d_pos ? __ldcg(a.d_pos) : a.pos_imm;
+    attn_pages(a, s, tid, h, grp, NG, pos);
+    AttnRegs R;
+    pdl_wait_a();
+    attn_main<MERGE_CTA, 0, 2, 4>(a, s, tid, h, grp, NG, pos, grp + 1, R);   // named barrier grp + 1 (0 is __syncthreads)
+}
+
 static size_t attn_fused_smem(int hd, int pps) {
     return (size_t)attn_group_floats(hd, pps) * 4;
 }
 
-// max_ctx sizes the score buffer.  Contexts up to ATTN_SHORT_CTX run one CTA per head; longer ones one cluster per head.
+// max_ctx sizes the score buffer and picks the kernel: contexts up to ATTN_SHORT_CTX run one 128-thread CTA per head, up to ATTN_CTA_CTX one
+// 1024-thread CTA per head, longer ones one cluster per head.
 cudaError_t launch_attn_fused(const float *d_qkv, int nh, int nkv, int hd, const int *d_pos, int pos_imm, const float *d_cos,
                               const float *d_sin, __half *d_k, __half *d_v, const int32_t *d_page_table, float *d_out, void *d_act_out,
                               int max_ctx, cudaStream_t st, bool pdl) {
@@ -57,6 +74,27 @@ cudaError_t launch_attn_fused(const float *d_qkv, int nh, int nkv, int hd, const
     // 2 = after the wait, q first and then all of K and V in one burst, so the three round trips overlap.
     static int pre = -1;
     if (pre < 0) { const char *e = getenv("B2_ATTN_PRE"); pre = e ? atoi(e) : ATTN_PRE_DEFAULT; if (pre < 0 || pre > 2) pre = 0; }
+    static int cta_merge = -1;   // contexts in (ATTN_SHORT_CTX, ATTN_CTA_CTX] run one 1024-thread CTA per head (k_attn_fused_cta); B2_ATTN_CTA=0: the cluster kernel
+    if (cta_merge < 0) { const char *e = getenv("B2_ATTN_CTA"); cta_merge = (e && e[0] == '0') ? 0 : 1; }
+    if (!one && cta_merge && max_ctx <= ATTN_CTA_CTX) {
+        a.group_stride = attn_group_floats(hd, a.pps_max);
+        const size_t smem_c = (size_t)ATTN_NSPLIT * a.group_stride * 4;
+        if (smem_c > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(k_attn_fused_cta<ATTN_NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c);
+            if (e != cudaSuccess) return e;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(nh);
+        cfg.blockDim = dim3(128 * ATTN_NSPLIT);
+        cfg.dynamicSmemBytes = smem_c;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = pdl ? 1 : 0;
+        return cudaLaunchKernelEx(&cfg, k_attn_fused_cta<ATTN_NSPLIT>, a);
+    }
     const void *fn = nullptr;
     if (one) fn = pre == 2 ? (const void *)k_attn_fused<1, 2> : pre == 1 ? (const void *)k_attn_fused<1, 1> : (const void *)k_attn_fused<1, 0>;
     else fn = pre == 2 ? (const void *)k_attn_fused<ATTN_NSPLIT, 2> : pre == 1 ? (const void *)k_attn_fused<ATTN_NSPLIT, 1> : (const void *)k_attn_fused<ATTN_NSPLIT, 0>;

@@ -16,8 +16,9 @@ struct AttnArgs {
     float *out;            // optional fp32 [nh*hd]
     uint8_t *act_out;      // optional A3 image of the output
     int pps_max;           // pages per split the shared-memory score buffer is sized for
+    int group_stride;      // MERGE_CTA: floats of shared memory between the areas of two groups (splits) of one CTA
 };
-enum { MERGE_NONE = 0, MERGE_CLUSTER = 1 };
+enum { MERGE_NONE = 0, MERGE_CLUSTER = 1, MERGE_CTA = 2 };   // splits of a head: none / CTAs of a cluster (DSMEM) / 128-thread groups of one CTA
 
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -145,7 +146,8 @@ __device__ __forceinline__ void attn_preload(const AttnArgs &a, const AttnSmem &
 // Part 2: RoPE on q (and on the new k), KV append, scores, softmax, weighted values, merge of the splits, activation grid.
 // All 128 threads of the group call it with the same (h, split, nsplit, pos).
 // PRE: the first batches of K and V and the RoPE row were fetched by attn_preload into R.
-template <int MERGE, int PRE>   // PRE: 0 no preload, 1 attn_preload<false> before the wait, 2 attn_preload<true> after it (q, k, v in R too)
+// KD / VD: pages of keys / tokens of values (per thread) requested before the first of them is used
+template <int MERGE, int PRE, int KD = 4, int VD = 8>   // PRE: 0 no preload, 1 attn_preload<false> before the wait, 2 attn_preload<true> after it (q, k, v in R too)
 __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, int tid, int h, int split, int nsplit, int pos, int bar_id, AttnRegs &R) {
     const int hd = a.hd, half = hd >> 1;
     float *sq = s.sq, *part = s.part, *og = s.og, *sc = s.sc, *red = s.red;
@@ -189,10 +191,10 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
     //      Cache rows are read with ld.global.cg: in the persistent kernel this SM's L1 may hold a line of an earlier token.
     const int key = tid >> 3, sub = tid & 7, nchunk = hd >> 3;   // 16-byte chunks per key row: 12 / 16 / 32
     float lmax = -INFINITY;
-    for (int pb = p0; pb < p1; pb += 4) {
-        uint4 kv[4][4];
+    for (int pb = p0; pb < p1; pb += KD) {
+        uint4 kv[KD][4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < KD; ++u) {
             const int p = pb + u, tk = p * PAGE_TOKENS + key;
             const bool valid = p < p1 && tk < n_ctx, fresh = tk == pos;
             const bool pre = PRE != 0 && pb == p0;   // older tokens of the first batch are already in registers
@@ -200,7 +202,7 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
 #pragma unroll
             for (int c4 = 0; c4 < 4; ++c4) {
                 const int c = sub + 8 * c4;
-                kv[u][c4] = pre ? R.kv[u][c4] : make_uint4(0u, 0u, 0u, 0u);   // defined on every path (see the note on buf0..3 in gemv_dev.cuh)
+                kv[u][c4] = (pre && u < 4) ? R.kv[u < 4 ? u : 0][c4] : make_uint4(0u, 0u, 0u, 0u);   // defined on every path (see the note on buf0..3 in gemv_dev.cuh)
                 if (valid && c < nchunk) {
                     if (fresh) kv[u][c4] = *(const uint4 *)(kr + c * 8);
                     else if (!pre) kv[u][c4] = __ldcg((const uint4 *)(kr + c * 8));
@@ -208,7 +210,7 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
             }
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < KD; ++u) {
             const int p = pb + u, tk = p * PAGE_TOKENS + key;
             float dot = 0.f;
             if (p < p1 && tk < n_ctx) {
@@ -258,13 +260,13 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
     const int grp = tid / tpt, dq = tid - grp * tpt;
     float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (grp < ngrp) {
-        for (int ib = grp; ib < nt; ib += 8 * ngrp) {
-            uint4 vv[8];
+        for (int ib = grp; ib < nt; ib += VD * ngrp) {
+            uint4 vv[VD];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < VD; ++u) {
                 const int i = ib + u * ngrp;
                 const bool pre = PRE != 0 && ib == grp;
-                vv[u] = pre ? R.vv[u] : make_uint4(0u, 0u, 0u, 0u);
+                vv[u] = pre ? R.vv[u < 8 ? u : 0] : make_uint4(0u, 0u, 0u, 0u);
                 if (i < nt) {
                     const int tk = t0 + i;
                     if (tk == pos) vv[u] = *(const uint4 *)(vnew + dq * 8);
@@ -273,7 +275,7 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < VD; ++u) {
                 const int i = ib + u * ngrp;
                 if (i < nt) {
                     const float pe = sc[i];
@@ -302,12 +304,17 @@ __device__ __forceinline__ void attn_main(const AttnArgs &a, const AttnSmem &s, 
     if (MERGE == MERGE_CLUSTER) {
         cluster_sync_all();
         finisher = cluster_rank() == 0;
+    } else if (MERGE == MERGE_CTA) {
+        __syncthreads();       // every group of the CTA has left its partial (m, l, o[]) in its own shared-memory area
+        finisher = split == 0;
     } else {
         group_sync(bar_id);
     }
     if (finisher) {
         if (MERGE != MERGE_NONE && nsplit > 1) {
-            auto pm = [&](int r, int idx) -> float { return ld_dsmem_f32(part + idx, r); };
+            auto pm = [&](int r, int idx) -> float {
+                return MERGE == MERGE_CLUSTER ? ld_dsmem_f32(part + idx, r) : (part + (r - split) * a.group_stride)[idx];
+            };
             float M = -INFINITY;
 #pragma unroll
             for (int r = 0; r < ATTN_NSPLIT; ++r)

@@ -152,11 +152,13 @@ struct b2_session {
     float *pf_part = nullptr;      // split-K partial sums
     uint64_t pf_part_floats = 0;
     bool use_pf_gemm = true;
-    cudaGraphExec_t graphs[G_COUNT][2] = {};   // [..][0]: positions below ATTN_SHORT_CTX (one attention CTA per head), [..][1]: longer contexts
-    int graph_launches[G_COUNT][2] = {};
+    // attention variants: [..][0] positions below ATTN_SHORT_CTX (one 128-thread CTA per head), [..][1] below ATTN_CTA_CTX (one 1024-thread
+    // CTA per head, its eight groups split the context), [..][2] longer contexts (a cluster of eight CTAs per head)
+    cudaGraphExec_t graphs[G_COUNT][ATTN_VARIANTS] = {};
+    int graph_launches[G_COUNT][ATTN_VARIANTS] = {};
     // greedy decode also exists as a graph of `multi_n` consecutive tokens (B2_GRAPH_TOKENS, default 8): fewer graph launches,
     // no gap between the tokens of one graph
-    cudaGraphExec_t multi[2][2] = {};   // [G_DECODE / G_DECODE_VP][attention variant]
+    cudaGraphExec_t multi[2][ATTN_VARIANTS] = {};   // [G_DECODE / G_DECODE_VP][attention variant]
     int multi_n = 8;
     bool use_graphs = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -783,8 +785,11 @@ static int enqueue_forward(b2_session *s, bool with_head, int attn_ctx, bool vp 
     return n;
 }
 
+// which attention kernel serves a position (attn.cu picks the kernel from the context bound it is launched with)
+static inline int attn_variant(int pos) { return pos < ATTN_SHORT_CTX ? 0 : pos < ATTN_CTA_CTX ? 1 : 2; }
 static int enqueue_graph_body(b2_session *s, int which, int variant) {
-    const int attn_ctx = (variant == 0 && s->max_ctx > ATTN_SHORT_CTX) ? ATTN_SHORT_CTX : s->max_ctx;
+    const int bound = variant == 0 ? ATTN_SHORT_CTX : variant == 1 ? ATTN_CTA_CTX : s->max_ctx;   // the context the variant's attention kernel is sized for
+    const int attn_ctx = s->max_ctx < bound ? s->max_ctx : bound;
     cudaStream_t st = s->m->e->stream;
     int n = 0;
     switch (which) {
@@ -823,10 +828,10 @@ static int enqueue_graph_body(b2_session *s, int which, int variant) {
 
 static void drop_graphs(b2_session *s) {
     for (int g = 0; g < G_COUNT; ++g)
-        for (int v = 0; v < 2; ++v)
+        for (int v = 0; v < ATTN_VARIANTS; ++v)
             if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
     for (int k = 0; k < 2; ++k)
-        for (int v = 0; v < 2; ++v)
+        for (int v = 0; v < ATTN_VARIANTS; ++v)
             if (s->multi[k][v]) { cudaGraphExecDestroy(s->multi[k][v]); s->multi[k][v] = nullptr; }
 }
 
@@ -835,10 +840,10 @@ static void drop_graphs(b2_session *s) {
 static int run_graph(b2_session *s, int which, int times, int pos0) {
     cudaStream_t st = s->m->e->stream;
     for (int i = 0; i < times; ++i) {
-        const int v = (pos0 + i) < ATTN_SHORT_CTX ? 0 : 1;
+        const int v = attn_variant(pos0 + i);
         // several greedy tokens in one graph while they all use the same attention variant
         const int U = s->multi_n;
-        if ((which == G_DECODE || which == G_DECODE_VP) && s->use_graphs && U > 1 && times - i >= U && ((pos0 + i + U - 1) < ATTN_SHORT_CTX ? 0 : 1) == v) {
+        if ((which == G_DECODE || which == G_DECODE_VP) && s->use_graphs && U > 1 && times - i >= U && attn_variant(pos0 + i + U - 1) == v) {
             const int mk = which == G_DECODE_VP ? 1 : 0;
             if (!s->multi[mk][v]) {
                 cudaGraph_t g = nullptr;
@@ -1015,7 +1020,7 @@ static int ensure_log(b2_session *s, uint64_t floats) {
     s->logits_log_cap = 0;
     // graphs bake the log pointer: re-capture the ones that use it
     for (int g : {G_DECODE_LOG, G_FORCED, G_SAMPLE_LOG})
-        for (int v = 0; v < 2; ++v)
+        for (int v = 0; v < ATTN_VARIANTS; ++v)
             if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
     cudaError_t e = cudaMalloc((void **)&s->logits_log, floats * 4);
     if (e != cudaSuccess) { b2_set_error("logits log: cudaMalloc(%llu) failed: %s", (unsigned long long)floats * 4, cudaGetErrorString(e)); return B2_ENOMEM; }
@@ -1188,7 +1193,7 @@ extern "C" int b2_decode(b2_session *s, int n_steps, const b2_sampler_cfg *sampl
             sampler->repeat_last_n != s->graph_sampler.repeat_last_n) {
             B2_CUDA(cudaStreamSynchronize(st));
             for (int g : {G_SAMPLE, G_SAMPLE_LOG})
-                for (int v = 0; v < 2; ++v)
+                for (int v = 0; v < ATTN_VARIANTS; ++v)
                     if (s->graphs[g][v]) { cudaGraphExecDestroy(s->graphs[g][v]); s->graphs[g][v] = nullptr; }
             s->graph_sampler = *sampler;
         }

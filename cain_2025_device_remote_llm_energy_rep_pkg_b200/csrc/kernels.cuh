@@ -6,6 +6,12 @@
 #ifndef ATTN_NSPLIT
 #define ATTN_NSPLIT 8       // KV splits per head in the decode attention kernel
 #endif
+#ifndef ATTN_CTA_CTX
+#define ATTN_CTA_CTX 256    // up to this many positions one 1024-thread CTA per head (eight groups merging through shared memory, two pages of
+                            // keys per group in flight): +1.3 % tokens/s over the cluster kernel at contexts 32..288 (it occupies nh SMs instead of
+                            // all of them, so the O projection's CTAs become resident while it runs), -3.3 % at contexts up to 1 365
+#endif
+#define ATTN_VARIANTS 3
 #ifndef ATTN_SHORT_CTX
 #define ATTN_SHORT_CTX 32   // up to this many positions the fused attention runs one CTA per head (no cluster); measured on llama3.1:8b,
                             // contexts 32..288: 96 -> 659, 64 / 32 / 16 -> 665 tokens/s, 160 -> 641 (the cluster variant wins from the first page pair on)
