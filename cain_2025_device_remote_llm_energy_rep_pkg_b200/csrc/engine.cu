@@ -146,7 +146,7 @@ struct b2_session {
     float *d_u = nullptr;
     uint64_t *d_draw = nullptr;
     b2_sampler_cfg graph_sampler{};
-    // batched prompt evaluation (prefill.cu): activations of up to 64 prompt tokens and the GEMM's B operand
+    // batched prompt evaluation (prefill.cu): activations of up to PF_MAX_TOKENS prompt tokens and the GEMM's B operand
     float *pf_x = nullptr, *pf_qkv = nullptr, *pf_attn = nullptr, *pf_h = nullptr;
     void *pf_pb = nullptr;
     float *pf_part = nullptr;      // split-K partial sums
@@ -941,12 +941,12 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
         if ((rc = dev_alloc(s->allocs, (void **)&s->d_draw, 16))) break;
         if (s->use_pf_gemm) {
             const int64_t widest = std::max<int64_t>(std::max<int64_t>(H, I), qd);
-            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_x, (uint64_t)64 * H * 4))) break;
-            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_qkv, (uint64_t)64 * (qd + 2 * kvd) * 4))) break;
-            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_attn, (uint64_t)64 * qd * 4))) break;
-            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_h, (uint64_t)64 * I * 4))) break;
-            if ((rc = dev_alloc(s->allocs, &s->pf_pb, pb_bytes(64, widest)))) break;
-            s->pf_part_floats = (uint64_t)8 * 64 * std::max<int64_t>(H, qd + 2 * kvd);
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_x, (uint64_t)PF_MAX_TOKENS * H * 4))) break;
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_qkv, (uint64_t)PF_MAX_TOKENS * (qd + 2 * kvd) * 4))) break;
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_attn, (uint64_t)PF_MAX_TOKENS * qd * 4))) break;
+            if ((rc = dev_alloc(s->allocs, (void **)&s->pf_h, (uint64_t)PF_MAX_TOKENS * I * 4))) break;
+            if ((rc = dev_alloc(s->allocs, &s->pf_pb, pb_bytes(PF_MAX_TOKENS, widest)))) break;
+            s->pf_part_floats = (uint64_t)8 * PF_MAX_TOKENS * std::max<int64_t>(H, qd + 2 * kvd);
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_part, s->pf_part_floats * 4))) break;
         }
     } while (0);
@@ -1057,7 +1057,7 @@ static int elapsed_ns(b2_session *s, uint64_t *ns) {
 }
 
 // ------------------------------------------------------------------------------------ batched prompt evaluation
-// n prompt tokens (already in s->d_prompt) at positions host_pos.. : every weight matrix is read once per batch of up to 64 tokens
+// n prompt tokens (already in s->d_prompt) at positions host_pos.. : every weight matrix is read once per batch of up to 128 tokens
 // (tcgen05 GEMM, prefill.cu) instead of once per token; the LM head runs for the last token only, through the decode GEMV, and
 // leaves logits and arg-max partials exactly where b2_decode expects them.
 static int prefill_batched(b2_session *s, int n) {
@@ -1084,8 +1084,12 @@ static int prefill_batched(b2_session *s, int n) {
                               L.error(), st);
         return B2_OK;
     };
-    for (int m0 = 0; m0 < n; m0 += 64) {
-        const int mb = n - m0 < 64 ? n - m0 : 64, T = pf_batch(mb), pos0 = s->host_pos + m0;
+    // tokens per pass over the weights: 128 (B2_PF_TOKENS=64 / 32 / 16: experiments); a tensor-parallel group exchanges batches of TP_PF_TOKENS
+    static int pf_tokens = 0;
+    if (!pf_tokens) { const char *e = getenv("B2_PF_TOKENS"); const int v = e ? atoi(e) : 0; pf_tokens = (v == 16 || v == 32 || v == 64) ? v : PF_MAX_TOKENS; }
+    const int step = tpn > 1 ? std::min(pf_tokens, TP_PF_TOKENS) : pf_tokens;
+    for (int m0 = 0; m0 < n; m0 += step) {
+        const int mb = n - m0 < step ? n - m0 : step, T = pf_batch(mb), pos0 = s->host_pos + m0;
         launch_prefill_embed(qt_of(m->embd.type), m->embd.packed, m->embd.cols, s->d_prompt + m0, mb, escale, s->pf_x, st); launches++;
         for (int l = 0; l < c.n_layers; ++l) {
             LayerW &ly = m->layers[l];

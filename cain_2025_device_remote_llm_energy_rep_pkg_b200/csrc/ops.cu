@@ -246,13 +246,13 @@ extern "C" int b2_op_prefill_gemm(int type, const void *d_packed, int64_t rows, 
     B2_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     void *pb = nullptr;
     float *part = nullptr;
-    const uint64_t part_floats = (uint64_t)8 * 64 * rows;
-    B2_CUDA(cudaMalloc(&pb, pb_bytes(64, cols)));
+    const uint64_t part_floats = (uint64_t)8 * PF_MAX_TOKENS * rows;
+    B2_CUDA(cudaMalloc(&pb, pb_bytes(PF_MAX_TOKENS, cols)));
     if (cudaMalloc((void **)&part, part_floats * 4) != cudaSuccess) { cudaFree(pb); cudaGetLastError(); b2_set_error("b2_op_prefill_gemm: out of memory"); return B2_ENOMEM; }
     const int64_t ldy = mode == 2 ? rows / 2 : rows;
     cudaError_t e = cudaSuccess;
-    for (int m0 = 0; m0 < M && e == cudaSuccess; m0 += 64) {
-        const int mb = M - m0 < 64 ? M - m0 : 64, T = pf_batch(mb);
+    for (int m0 = 0; m0 < M && e == cudaSuccess; m0 += PF_MAX_TOKENS) {
+        const int mb = M - m0 < PF_MAX_TOKENS ? M - m0 : PF_MAX_TOKENS, T = pf_batch(mb);
         e = launch_prefill_quant(d_norm_w ? PF_IN_NORM : PF_IN_F32, d_x + (int64_t)m0 * cols, cols, mb, T, cols, d_norm_w, eps, plus_one, pb, 0);
         if (e == cudaSuccess)
             e = launch_prefill_gemm_qt(qt_of(type), mode, d_packed, rows, cols, pb, mb, T, d_y + (int64_t)m0 * ldy, ldy,

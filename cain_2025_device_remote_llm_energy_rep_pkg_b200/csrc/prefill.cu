@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) k_prefill_quant(const float *__restrict__
 
 cudaError_t launch_prefill_quant(int in_mode, const float *x, int64_t ldx, int M, int T, int64_t n, const float *norm_w, float eps, int plus_one,
                                  void *pb, cudaStream_t st) {
-    if (M <= 0 || M > T || (T != 16 && T != 32 && T != 64) || n <= 0) return cudaErrorInvalidValue;
+    if (M <= 0 || M > T || (T != 16 && T != 32 && T != 64 && T != 128) || n <= 0) return cudaErrorInvalidValue;
     const int nbp = (int)nblocks_padded(n);
     const int slices = nbp >= 256 ? 8 : nbp >= 64 ? 4 : 1;   // every CTA of a token recomputes the row's sum of squares (a few KB from L2)
     if (in_mode == PF_IN_NORM) k_prefill_quant<PF_IN_NORM><<<dim3(T, slices), 256, 0, st>>>(x, ldx, M, T, (int)n, nbp, norm_w, eps, plus_one, (uint8_t *)pb);
@@ -135,13 +135,16 @@ struct PfArgs {
 // shared memory: [A stages: PF_STAGES x (4 k-steps x NPART images of 128 rows x 32 bytes)][B stages: PF_STAGES x (4 k-steps x 3T rows x 32 bytes)][barriers]
 template <int T, int NPART>
 struct PfSmem {
+    // blocks (32 k = 2 k-steps) per stage: two up to 64 tokens; one for 128 tokens, whose B operand is twice as large: two 64-k stages
+    // would be all that fits, and the B copy of a stage (issued when the stage's previous MMAs are done) would have one stage to land
+    static constexpr int SB = T > 64 ? 1 : 2;
     // as many stages as fit: the round trip of a stage (MMAs done -> rebuilt -> MMAs issued again) is several times the work of a stage
-    static constexpr int FIT = (227 * 1024 - 256) / (4 * NPART * PF_ROWS * 32 + 4 * 3 * T * 32);
+    static constexpr int FIT = (227 * 1024 - 256) / (2 * SB * NPART * PF_ROWS * 32 + 2 * SB * 3 * T * 32);
     static constexpr int STAGES = FIT > 6 ? 6 : FIT;
     static constexpr int A_IMG = PF_ROWS * 32;                 // one A operand: 128 rows x 16 bf16
-    static constexpr int A_STAGE = 4 * NPART * A_IMG;
+    static constexpr int A_STAGE = 2 * SB * NPART * A_IMG;
     static constexpr int B_KSTEP = 3 * T * 32;                 // one k-step of B: 3 planes x T tokens x 16 bf16
-    static constexpr int B_STAGE = 4 * B_KSTEP;                // = 2 blocks of the PB image
+    static constexpr int B_STAGE = 2 * SB * B_KSTEP;           // = SB blocks of the PB image
     static constexpr int A_OFF = 0;
     static constexpr int B_OFF = A_OFF + STAGES * A_STAGE;
     static constexpr int BAR_OFF = B_OFF + STAGES * B_STAGE;
@@ -173,8 +176,15 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
     // operand fetch (24 x 4 KB per 64 k) was what the tensor pipe waited for.  The parts alternate between NACC accumulators.
     constexpr int N = 3 * T;
     constexpr int NACC = T <= 32 ? 2 : 1;              // 2 buffers x NACC x 3T columns <= 384 of the 512 columns of tensor memory
+    // 128 tokens: N = 384 is two MMAs of 192 columns per part and k-step, and the 384 columns exist once.  The sums of a work item's whole
+    // K range then stay in tensor memory (one segment) and are drained once, 16 tokens at a time straight into the epilogue: a thread
+    // cannot hold 128 running sums.  Measured on same-sign data, K = 14 336: 1.3e-6 of sum |w||x| against 2e-7 with 512-k segments.
+    constexpr int NM = N > 256 ? 2 : 1, NMMA = N / NM;
+    constexpr int NBUF = 2 * NACC * N <= 512 ? 2 : 1;
+    constexpr bool ONE_SEG = NBUF == 1;
     using S = PfSmem<T, NPART>;
-    constexpr int PF_STAGES = S::STAGES;
+    constexpr int PF_STAGES = S::STAGES, SB = S::SB, ST_PER_BG = 4 / SB;   // a block-group (4 blocks) is ST_PER_BG stages
+    constexpr int SEG = ONE_SEG ? (1 << 30) : PF_SEG * (SB == 2 ? 1 : 2);
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t *full = (uint64_t *)(smem + S::BAR_OFF);   // [stage] A built (8 warp arrivals) + B copied (1 arrival + bytes)
     uint64_t *empty = full + PF_STAGES;                 // [stage] the MMAs that read the stage are done (commit)
@@ -184,16 +194,16 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < PF_STAGES; ++s) { mbar_init(full + s, 9); mbar_init(empty + s, 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(tfull + b, 1); mbar_init(tempty + b, 4); }   // NBUF of them are used
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 12) tmem_alloc(tmem_ptr, 512);          // two buffers of NACC accumulators of T columns
+    if (warp == 12) tmem_alloc(tmem_ptr, 512);          // NBUF buffers of NACC accumulators of 3T columns
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_ptr;
     const int n_items = ((a.n_tiles + 7) >> 3) * a.ksplit;   // work item = (row group, K piece)
-    const int nbg_all = a.nbp >> 2;                          // block-groups along K; a block-group is two stages
+    const int nbg_all = a.nbp >> 2;                          // block-groups along K; a block-group is ST_PER_BG stages
     auto item_range = [&](int wi, int &grp, int &ks, int &bg0, int &bg1) {
         grp = wi / a.ksplit;
         ks = wi - grp * a.ksplit;
@@ -209,49 +219,83 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
             int grp, ks, bg0, bg1;
             item_range(wi, grp, ks, bg0, bg1);
-            const int n_seg = (2 * (bg1 - bg0) + PF_SEG - 1) / PF_SEG;
-            float acc[T];
+            const int n_seg = ONE_SEG ? 1 : (ST_PER_BG * (bg1 - bg0) + SEG - 1) / SEG;
+            const int row = grp * PF_ROWS + row_l;
+            // the finished sums of tokens t0 .. t0+15 of this thread's row
+            auto emit16 = [&](int t0, const float (&v)[16]) {
+                if (a.ksplit > 1 || a.force_part) {
 #pragma unroll
-            for (int m = 0; m < T; ++m) acc[m] = 0.f;
-            for (int sg = 0; sg < n_seg; ++sg, ++seg) {
-                const int buf = seg & 1;
-                mbar_wait(tfull + buf, (seg >> 1) & 1);
-                tc_fence_after();
+                    for (int u = 0; u < 16; ++u)
+                        if (t0 + u < a.M && row < a.rows) a.part[((int64_t)ks * T + t0 + u) * a.rows + row] = v[u];
+                    return;
+                }
 #pragma unroll
-                for (int ai = 0; ai < NACC; ++ai) {
-#pragma unroll
-                    for (int t0 = 0; t0 < T; t0 += 16) {
-                        uint32_t c0[16], c1[16], c2[16];   // the three digit planes of 16 tokens (already scaled by 128^plane)
-                        tmem_ld16(tlane + (buf * NACC + ai) * N + t0, c0);
-                        tmem_ld16(tlane + (buf * NACC + ai) * N + T + t0, c1);
-                        tmem_ld16(tlane + (buf * NACC + ai) * N + 2 * T + t0, c2);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int u = 0; u < 16; ++u)
-                            acc[t0 + u] = __fadd_rn(acc[t0 + u], __fadd_rn(__fadd_rn(__uint_as_float(c0[u]), __uint_as_float(c1[u])), __uint_as_float(c2[u])));
+                for (int u = 0; u < 16; ++u) {
+                    const int tk = t0 + u;
+                    if (tk < a.M) {   // uniform
+                        if (OUT == PF_OUT_ACTMUL) {   // rows (2j, 2j+1) = (gate_j, up_j)
+                            const float up = __shfl_down_sync(0xffffffffu, v[u], 1);
+                            if (!(row & 1) && row < a.rows) a.y[(int64_t)tk * a.ldy + (row >> 1)] = act_fn(v[u], a.act) * up;
+                        } else if (row < a.rows) {
+                            if (OUT == PF_OUT_RES) a.y[(int64_t)tk * a.ldy + row] = a.bias_or_res[(int64_t)tk * a.ldy + row] + v[u];
+                            else a.y[(int64_t)tk * a.ldy + row] = a.bias_or_res ? v[u] + a.bias_or_res[row] : v[u];
+                        }
                     }
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(tempty + buf);
-            }
-            const int row = grp * PF_ROWS + row_l;
-            if (a.ksplit > 1 || a.force_part) {
-#pragma unroll
-                for (int u = 0; u < T; ++u)
-                    if (u < a.M && row < a.rows) a.part[((int64_t)ks * T + u) * a.rows + row] = acc[u];
-                continue;
-            }
-#pragma unroll
-            for (int u = 0; u < T; ++u) {
-                if (u < a.M) {   // uniform
-                    if (OUT == PF_OUT_ACTMUL) {   // rows (2j, 2j+1) = (gate_j, up_j)
-                        const float up = __shfl_down_sync(0xffffffffu, acc[u], 1);
-                        if (!(row & 1) && row < a.rows) a.y[(int64_t)u * a.ldy + (row >> 1)] = act_fn(acc[u], a.act) * up;
-                    } else if (row < a.rows) {
-                        if (OUT == PF_OUT_RES) a.y[(int64_t)u * a.ldy + row] = a.bias_or_res[(int64_t)u * a.ldy + row] + acc[u];
-                        else a.y[(int64_t)u * a.ldy + row] = a.bias_or_res ? acc[u] + a.bias_or_res[row] : acc[u];
+            };
+            if constexpr (ONE_SEG) {
+                mbar_wait(tfull, seg & 1);
+                tc_fence_after();
+#pragma unroll 1
+                for (int t0 = 0; t0 < T; t0 += 16) {
+                    uint32_t c0[16], c1[16], c2[16];
+                    tmem_ld16(tlane + t0, c0);
+                    tmem_ld16(tlane + T + t0, c1);
+                    tmem_ld16(tlane + 2 * T + t0, c2);
+                    tmem_ld_wait();
+                    if (t0 + 16 >= T) {   // everything is in registers: the MMAs of the next item may overwrite the columns
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(tempty);
                     }
+                    float v[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) v[u] = __fadd_rn(__fadd_rn(__uint_as_float(c0[u]), __uint_as_float(c1[u])), __uint_as_float(c2[u]));
+                    emit16(t0, v);
+                }
+                ++seg;
+            } else {
+                float acc[T];
+#pragma unroll
+                for (int m = 0; m < T; ++m) acc[m] = 0.f;
+                for (int sg = 0; sg < n_seg; ++sg, ++seg) {
+                    const int buf = seg & 1;
+                    mbar_wait(tfull + buf, (seg >> 1) & 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int ai = 0; ai < NACC; ++ai) {
+#pragma unroll
+                        for (int t0 = 0; t0 < T; t0 += 16) {
+                            uint32_t c0[16], c1[16], c2[16];   // the three digit planes of 16 tokens (already scaled by 128^plane)
+                            tmem_ld16(tlane + (buf * NACC + ai) * N + t0, c0);
+                            tmem_ld16(tlane + (buf * NACC + ai) * N + T + t0, c1);
+                            tmem_ld16(tlane + (buf * NACC + ai) * N + 2 * T + t0, c2);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int u = 0; u < 16; ++u)
+                                acc[t0 + u] = __fadd_rn(acc[t0 + u], __fadd_rn(__fadd_rn(__uint_as_float(c0[u]), __uint_as_float(c1[u])), __uint_as_float(c2[u])));
+                        }
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty + buf);
+                }
+#pragma unroll
+                for (int t0 = 0; t0 < T; t0 += 16) {
+                    float v[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) v[u] = acc[t0 + u];
+                    emit16(t0, v);
                 }
             }
         }
@@ -333,15 +377,15 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         auto build = [&](const Regs &cur) {
             const uint32_t w0[4] = {cur.v0.x ^ 0x88888888u, cur.v0.y ^ 0x88888888u, cur.v0.z ^ 0x88888888u, cur.v0.w ^ 0x88888888u};   // GGML nibbles q of row g
             const uint32_t w1[4] = {cur.v1.x ^ 0x88888888u, cur.v1.y ^ 0x88888888u, cur.v1.z ^ 0x88888888u, cur.v1.w ^ 0x88888888u};   // row g+8
-            constexpr int HS_UNROLL = PF_HS_UNROLL;
+            constexpr int HS_UNROLL = SB == 2 ? PF_HS_UNROLL : 4;   // the block index jj must be a constant: it selects registers
 #pragma unroll HS_UNROLL
-            for (int hs = 0; hs < 2; ++hs, ++it) {   // the two stages of the block-group: blocks 2hs, 2hs+1
+            for (int hs = 0; hs < ST_PER_BG; ++hs, ++it) {   // the stages of the block-group: blocks SB*hs .. SB*hs + SB-1
                 const int slot = it % PF_STAGES;
                 mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
                 uint8_t *As = smem + S::A_OFF + slot * S::A_STAGE;
 #pragma unroll
-                for (int bb = 0; bb < 2; ++bb) {
-                    const int jj = 2 * hs + bb;
+                for (int bb = 0; bb < SB; ++bb) {
+                    const int jj = SB * hs + bb;
                     // mul[row half][k-step], sub[row half]: Q4_0 w = mul*(q-8); Q4_K w = q*mul - sub; Q6_K w = mul*(q-32), mul per 16 elements
                     float mul[2][2], sub[2];
                     uint32_t hbits[2] = {0u, 0u};   // Q6_K: the 16-bit field of high bits of (row half, block jj): byte kh, 2 bits per element
@@ -419,7 +463,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
     } else if (warp == 12) {
         // ===================== MMA issue (one thread)
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(N);
+            const uint32_t idesc = umma_idesc_bf16(NMMA);
             // descriptors by addition: the start-address field (bits 0-13, in 16-byte units) of a descriptor of the first image plus
             // the image's offset; one thread issues everything here, so every instruction it saves shortens the stage
             const uint64_t descA0 = umma_desc(smem + S::A_OFF), descB0 = umma_desc(smem + S::B_OFF);
@@ -427,11 +471,11 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
             for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
                 int grp, ks, bg0, bg1;
                 item_range(wi, grp, ks, bg0, bg1);
-                const int n_st = 2 * (bg1 - bg0);
+                const int n_st = ST_PER_BG * (bg1 - bg0);
                 for (int st = 0; st < n_st; ++st, ++it) {
-                    const int slot = it % PF_STAGES, in_seg = st % PF_SEG, buf = seg & 1;
+                    const int slot = it % PF_STAGES, in_seg = ONE_SEG ? st : st % SEG, buf = seg % NBUF;
                     if (in_seg == 0) {   // a new segment: its accumulator buffer must have been drained
-                        mbar_wait(tempty + buf, ((seg >> 1) & 1) ^ 1);
+                        mbar_wait(tempty + buf, ((seg / NBUF) & 1) ^ 1);
                         tc_fence_after();
                     }
                     mbar_wait(full + slot, (it / PF_STAGES) & 1);
@@ -439,28 +483,30 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
                     const uint64_t da_s = descA0 + (uint64_t)((slot * S::A_STAGE) >> 4), db_s = descB0 + (uint64_t)((slot * S::B_STAGE) >> 4);
                     const uint32_t acc_on = in_seg ? 1u : 0u;
 #pragma unroll
-                    for (int kst = 0; kst < 4; ++kst) {
+                    for (int kst = 0; kst < 2 * SB; ++kst) {
                         const uint64_t db = db_s + (uint64_t)((kst * S::B_KSTEP) >> 4);
 #pragma unroll
                         for (int p = 0; p < NPART; ++p) {
                             const int ai = p % NACC;     // the first MMA into an accumulator of a segment overwrites it
-                            umma_bf16(tmem + (buf * NACC + ai) * N, da_s + (uint64_t)(((kst * NPART + p) * S::A_IMG) >> 4), db, idesc,
-                                      (kst || p >= NACC) ? 1u : acc_on);
+#pragma unroll
+                            for (int j = 0; j < NM; ++j)   // N > 256: columns [j*NMMA, (j+1)*NMMA) = rows of the B image 256 bytes per 8 apart
+                                umma_bf16(tmem + (buf * NACC + ai) * N + j * NMMA, da_s + (uint64_t)(((kst * NPART + p) * S::A_IMG) >> 4),
+                                          db + (uint64_t)((j * (NMMA / 8) * 256) >> 4), idesc, (kst || p >= NACC) ? 1u : acc_on);
                         }
                     }
                     umma_commit(empty + slot);
-                    if (in_seg == PF_SEG - 1 || st == n_st - 1) { umma_commit(tfull + buf); ++seg; }
+                    if ((!ONE_SEG && in_seg == SEG - 1) || st == n_st - 1) { umma_commit(tfull + buf); ++seg; }
                 }
             }
         }
     } else {
-        // ===================== B operand of the stage: one bulk copy (two blocks of the PB image)
+        // ===================== B operand of the stage: one bulk copy (SB blocks of the PB image)
         if (lane == 0) {
             int it = 0;
             for (int wi = blockIdx.x; wi < n_items; wi += gridDim.x) {
                 int grp, ks, bg0, bg1;
                 item_range(wi, grp, ks, bg0, bg1);
-                for (int st = 2 * bg0; st < 2 * bg1; ++st, ++it) {
+                for (int st = ST_PER_BG * bg0; st < ST_PER_BG * bg1; ++st, ++it) {
                     const int slot = it % PF_STAGES;
                     mbar_wait(empty + slot, ((it / PF_STAGES) & 1) ^ 1);
                     mbar_expect_tx(full + slot, (uint32_t)S::B_STAGE);
@@ -539,6 +585,7 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
     PF_CASE(16, PF_OUT_BIAS); PF_CASE(16, PF_OUT_RES); PF_CASE(16, PF_OUT_ACTMUL);
     PF_CASE(32, PF_OUT_BIAS); PF_CASE(32, PF_OUT_RES); PF_CASE(32, PF_OUT_ACTMUL);
     PF_CASE(64, PF_OUT_BIAS); PF_CASE(64, PF_OUT_RES); PF_CASE(64, PF_OUT_ACTMUL);
+    PF_CASE(128, PF_OUT_BIAS); PF_CASE(128, PF_OUT_RES); PF_CASE(128, PF_OUT_ACTMUL);
 #undef PF_CASE
     if (e != cudaSuccess || ksplit == 1 || partials_only) return e;
     k_prefill_finish<<<dim3((unsigned)((rows + 255) / 256), M), 256, 0, st>>>(part, ksplit, T, M, (int)rows, y, ldy, bias_or_res, out_mode);

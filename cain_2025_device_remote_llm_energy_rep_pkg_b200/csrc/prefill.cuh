@@ -10,17 +10,19 @@
 // terms of the dot product of the dequantised row with the gridded activations; only the order and the tensor core's fp32
 // addition differ from the CPU oracle.
 //
-// "PB" = the B operand of the GEMM for a batch of T tokens (T = 16, 32 or 64):
+// "PB" = the B operand of the GEMM for a batch of T tokens (T = 16, 32, 64 or 128):
 //   [kb 0..nbp)  per 32-element block two images (k-steps of 16 elements) of 3T rows x 16 bf16 in the shared-memory layout
 //                tcgen05.mma wants (K-major, no swizzle: 8-row x 16-byte core matrices; row n = plane*T + m for digit plane `plane`
 //                of token m): the bf16 of (n, k) at kb*192T + (k>>4)*96T + (n>>3)*256 + ((k&15)>>3)*128 + (n&7)*16 + (k&7)*2.
-//                Two blocks = one stage = one cp.async.bulk.
+//                One stage = one cp.async.bulk of two blocks (T <= 64) or one block (T = 128).
 #pragma once
 #include "kernels.cuh"
 #include "layout.cuh"
 
 #define PF_ROWS 128          // weight rows per CTA tile (UMMA M)
+#ifndef PF_SEG
 #define PF_SEG 8             // stages whose products accumulate in tensor memory before they are drained into fp32 registers (512 k)
+#endif
 #define PF_THREADS 448       // warps 0-3 accumulator drain + epilogue (TMEM quadrant = warp), 4-11 weight dequantisation, 12 MMA issue, 13 B-operand copies
 
 __host__ __device__ inline size_t pb_block_bytes(int T) { return (size_t)2 * 3 * T * 32; }
@@ -30,8 +32,9 @@ __host__ __device__ inline size_t pb_off(int T, int64_t kb, int d, int m, int k)
     return (size_t)kb * pb_block_bytes(T) + (size_t)(k >> 4) * (3 * T * 32) + (size_t)(n >> 3) * 256 + (size_t)(kk >> 3) * 128 + (size_t)(n & 7) * 16 +
            (size_t)(kk & 7) * 2;
 }
-// smallest supported batch size holding m tokens (0 if m > 64)
-inline int pf_batch(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 0; }
+// smallest supported batch size holding m tokens (0 if m > 128)
+inline int pf_batch(int m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : m <= 128 ? 128 : 0; }
+#define PF_MAX_TOKENS 128   // tokens per pass over the weights
 
 enum { PF_IN_NORM = 0, PF_IN_F32 = 2 };
 enum { PF_OUT_BIAS = 0, PF_OUT_RES = 1, PF_OUT_ACTMUL = 2 };

@@ -12,7 +12,8 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("rows,cols,M", [(128, 128, 1), (256, 288, 5), (384, 4096, 16), (1000, 512, 17), (4096, 4096, 33),
-                                         (128, 14336, 64), (6144, 4096, 64), (2048, 1536, 70)])
+                                         (128, 14336, 64), (6144, 4096, 64), (2048, 1536, 70),
+                                         (4096, 4096, 128), (128, 14336, 100), (1000, 1536, 200)])   # > 64 tokens: 128 per weight pass, one drain
 def test_prefill_gemm_matches_decode_gemv(lib, D, rows, cols, M):
     rng = np.random.default_rng(rows * 3 + cols + M)
     blob = Q.quantize_q4_0((rng.standard_normal((rows, cols)) * 0.02).astype(np.float32))
@@ -32,7 +33,7 @@ def test_prefill_gemm_matches_decode_gemv(lib, D, rows, cols, M):
         assert np.all(np.abs(y[m] - g) <= 2e-6 * mag + 1e-30), f"token {m} vs decode kernel"
 
 
-@pytest.mark.parametrize("H,M,plus_one", [(288, 3, 0), (2048, 20, 1), (4096, 40, 0)])
+@pytest.mark.parametrize("H,M,plus_one", [(288, 3, 0), (2048, 20, 1), (4096, 40, 0), (4096, 128, 0)])
 def test_prefill_gemm_norm_and_residual(lib, D, H, M, plus_one):
     rng = np.random.default_rng(H + M)
     rows = 256
@@ -51,7 +52,7 @@ def test_prefill_gemm_norm_and_residual(lib, D, H, M, plus_one):
         assert np.all(np.abs(y[m] - (ref + res[m])) <= 8e-6 * mag + 1e-6 * np.abs(res[m]) + 1e-30)
 
 
-@pytest.mark.parametrize("act_id,I,H,M", [(0, 416, 288, 7), (1, 512, 256, 33), (0, 1024, 4096, 64)])
+@pytest.mark.parametrize("act_id,I,H,M", [(0, 416, 288, 7), (1, 512, 256, 33), (0, 1024, 4096, 64), (0, 1024, 4096, 97)])
 def test_prefill_gemm_gate_up(lib, D, act_id, I, H, M):
     rng = np.random.default_rng(I + H + M)
     g = Q.quantize_q4_0((rng.standard_normal((I, H)) * 0.05).astype(np.float32))

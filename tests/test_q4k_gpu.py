@@ -111,7 +111,7 @@ def test_q4k_model_matches_oracle(key, head_qtype, gpu_engine):
     assert list(map(int, toks)) == om.session(96).generate_greedy(prompt, 40)
 
 
-@pytest.mark.parametrize("rows,cols,M", [(128, 256, 3), (1000, 512, 17), (4096, 4096, 33), (256, 14336, 64)])
+@pytest.mark.parametrize("rows,cols,M", [(128, 256, 3), (1000, 512, 17), (4096, 4096, 33), (256, 14336, 64), (512, 4096, 128), (256, 14336, 90)])
 def test_q4k_prefill_gemm(lib, D, rows, cols, M):
     """The tcgen05 prompt GEMM on a Q4_K matrix against the decode GEMV and the dequantised reference."""
     rng = np.random.default_rng(rows + cols + M)

@@ -40,7 +40,7 @@ def test_q6k_gemv(lib, D, rows, cols):
     assert np.all(np.abs(dy2.to_numpy(np.float32, (rows,)) - want) <= 8e-6 * mag + 1e-30)
 
 
-@pytest.mark.parametrize("rows,cols,M", [(128, 256, 3), (1000, 512, 17), (4096, 4096, 33), (256, 14336, 64)])
+@pytest.mark.parametrize("rows,cols,M", [(128, 256, 3), (1000, 512, 17), (4096, 4096, 33), (256, 14336, 64), (512, 4096, 128), (256, 14336, 90)])
 def test_q6k_prefill_gemm(lib, D, rows, cols, M):
     """The tcgen05 prompt GEMM on a Q6_K matrix (llama.cpp's Q4_K_M keeps attn_v and ffn_down in this format) against the
     dequantised reference and the decode GEMV: the builder dequantises d*sc*(q-32) exactly and splits it into three bf16 parts."""
