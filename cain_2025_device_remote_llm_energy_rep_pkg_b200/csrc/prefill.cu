@@ -5,15 +5,17 @@
 //              dequantise them exactly to fp32 (Q4_0: d*(q-8); Q4_K: d*sc*q - dmin*m; Q6_K: d*sc*(q-32), each with the oracle's
 //              roundings), split each value EXACTLY into NPART bf16 parts (Q4_0: 15 significant bits = 2 parts, K-quants: 24 = 3) and
 //              store the parts as A operands
-//              (K-major 8 x 16-byte core matrices), one stage = 2 blocks = 64 k = 4 MMA k-steps
+//              (K-major 8 x 16-byte core matrices), one stage = 2 blocks = 64 k = 4 MMA k-steps (128 tokens: 1 block = 2 k-steps)
 //   warp 13    copies the B operand of the stage with cp.async.bulk: the three digit planes of the T tokens, already scaled
 //              (digit * 2^e * 128^plane is exact in bf16) and already in operand layout
-//   warp 12    one thread issues, per k-step, NPART x 3 tcgen05.mma.kind::f16 (M = 128, N = T, K = 16, bf16 x bf16 -> fp32) that all
-//              ACCUMULATE into the same T columns of tensor memory: every product is exact (8 x 8 significant bits), so the sum over
-//              parts, planes and k is the fp32 dot product of the dequantised row with the gridded activations
+//   warp 12    one thread issues, per k-step and part, ONE tcgen05.mma.kind::f16 (M = 128, N = 3T, K = 16, bf16 x bf16 -> fp32; T = 128:
+//              two of N = 192) whose columns are the three digit planes of the T tokens; all parts and k-steps ACCUMULATE into the same
+//              columns of tensor memory: every product is exact (8 x 8 significant bits), so the sum over parts and k (and, in the
+//              drain, planes) is the fp32 dot product of the dequantised row with the gridded activations
 //   warps 0-3  drain the accumulator into fp32 registers once per PF_SEG stages (a bounded chain of tensor-core additions, then one
 //              IEEE addition per segment), double-buffered against the MMAs of the next segment; after the last segment they apply
-//              the epilogue (+bias, +residual, act(gate)*up) and write y
+//              the epilogue (+bias, +residual, act(gate)*up) and write y.  T = 128 fills 384 of the 512 columns with ONE accumulator:
+//              the whole K range of a work item stays in tensor memory and is drained once, 16 tokens at a time into the epilogue
 // Round 1 issued one int8 MMA per 32-element block with accumulation off and combined the digit planes and the two per-block
 // scales on the CUDA cores (about ten operations per row, token and block, and a hand-over between the MMA and the epilogue warps
 // per block): the tensor pipe was 7-8 % busy.  Folding both scales into the operands keeps the whole K loop in tensor memory.

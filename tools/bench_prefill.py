@@ -18,5 +18,7 @@ for n in lens:
         ns = s.stats()["prompt_eval_ns"]
         best = ns if best is None else min(best, ns)
     wbytes = a.weight_bytes_q4()
-    print(f"{name} prompt {n:5d} tokens: {best/1e6:9.3f} ms  {n/(best/1e9):10.0f} tokens/s   weight passes {-(-n//64)}  "
-          f"({-(-n//64)*wbytes/(best/1e9)/1e9:7.0f} GB/s of weights)")
+    per_pass = int(os.environ.get("B2_PF_TOKENS", "128"))   # tokens per pass over the weights (engine.cu: prefill_batched)
+    passes = -(-n // per_pass)
+    print(f"{name} prompt {n:5d} tokens: {best/1e6:9.3f} ms  {n/(best/1e9):10.0f} tokens/s   weight passes {passes}  "
+          f"({passes*wbytes/(best/1e9)/1e9:7.0f} GB/s of weights)")
