@@ -134,14 +134,21 @@ struct PfArgs {
     float *part;             // [ksplit][T][rows] fp32 partial sums (k_prefill_finish adds them in a fixed order)
 };
 
-// shared memory: [A stages: PF_STAGES x (4 k-steps x NPART images of 128 rows x 32 bytes)][B stages: PF_STAGES x (4 k-steps x 3T rows x 32 bytes)][barriers]
+#ifndef PF_STAGE_BLOCKS
+#define PF_STAGE_BLOCKS 4   // 32-element blocks per stage: 4 (a whole block-group) where two such stages fit, else 2; 1 and 2 force smaller stages
+#endif
+// Measured, llama3.1:8b, ms per prompt with stages of 1 / 2 / 4 blocks: 16 tokens 8.8 / 8.1 / 7.7, 32 tokens 9.2 / 8.7 / 8.2, 64 tokens 10.4 / 9.7 / 9.3,
+// 128 tokens 14.5 / 13.2 / - (five stages of 40 KB against two of 80 KB), 512 tokens 62.1 / 57.0 / -.  What a stage costs beyond its arithmetic
+// (barrier round trips, the proxy fence, the commit, the MMA thread's wake-up) is per stage, and a deeper ring buys nothing back; one fence
+// per two one-block stages changed nothing (14.5).
+// shared memory: [A stages: STAGES x (2 SB k-steps x NPART images of 128 rows x 32 bytes)][B stages: STAGES x (2 SB k-steps x 3T rows x 32 bytes)][barriers]
 template <int T, int NPART>
 struct PfSmem {
-    // blocks (32 k = 2 k-steps) per stage: two up to 64 tokens; one for 128 tokens, whose B operand is twice as large: two 64-k stages
-    // would be all that fits, and the B copy of a stage (issued when the stage's previous MMAs are done) would have one stage to land
-    static constexpr int SB = T > 64 ? 1 : 2;
+    static constexpr int stage_bytes(int sb) { return 2 * sb * NPART * PF_ROWS * 32 + 2 * sb * 3 * T * 32; }
+    // blocks (32 k = 2 k-steps) per stage; a whole block-group (4) only where two such stages fit
+    static constexpr int SB = (PF_STAGE_BLOCKS == 4 && (227 * 1024 - 256) / stage_bytes(4) >= 2) ? 4 : PF_STAGE_BLOCKS >= 2 ? 2 : 1;
     // as many stages as fit: the round trip of a stage (MMAs done -> rebuilt -> MMAs issued again) is several times the work of a stage
-    static constexpr int FIT = (227 * 1024 - 256) / (2 * SB * NPART * PF_ROWS * 32 + 2 * SB * 3 * T * 32);
+    static constexpr int FIT = (227 * 1024 - 256) / stage_bytes(SB);
     static constexpr int STAGES = FIT > 6 ? 6 : FIT;
     static constexpr int A_IMG = PF_ROWS * 32;                 // one A operand: 128 rows x 16 bf16
     static constexpr int A_STAGE = 2 * SB * NPART * A_IMG;
@@ -186,7 +193,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
     constexpr bool ONE_SEG = NBUF == 1;
     using S = PfSmem<T, NPART>;
     constexpr int PF_STAGES = S::STAGES, SB = S::SB, ST_PER_BG = 4 / SB;   // a block-group (4 blocks) is ST_PER_BG stages
-    constexpr int SEG = ONE_SEG ? (1 << 30) : PF_SEG * (SB == 2 ? 1 : 2);
+    constexpr int SEG = ONE_SEG ? (1 << 30) : PF_SEG * 2 / SB;   // PF_SEG counts two-block stages
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t *full = (uint64_t *)(smem + S::BAR_OFF);   // [stage] A built (8 warp arrivals) + B copied (1 arrival + bytes)
     uint64_t *empty = full + PF_STAGES;                 // [stage] the MMAs that read the stage are done (commit)
@@ -379,7 +386,7 @@ __global__ void __launch_bounds__(PF_THREADS, 1) k_prefill_gemm(const PfArgs a) 
         auto build = [&](const Regs &cur) {
             const uint32_t w0[4] = {cur.v0.x ^ 0x88888888u, cur.v0.y ^ 0x88888888u, cur.v0.z ^ 0x88888888u, cur.v0.w ^ 0x88888888u};   // GGML nibbles q of row g
             const uint32_t w1[4] = {cur.v1.x ^ 0x88888888u, cur.v1.y ^ 0x88888888u, cur.v1.z ^ 0x88888888u, cur.v1.w ^ 0x88888888u};   // row g+8
-            constexpr int HS_UNROLL = SB == 2 ? PF_HS_UNROLL : 4;   // the block index jj must be a constant: it selects registers
+            constexpr int HS_UNROLL = SB == 2 ? PF_HS_UNROLL : SB == 1 ? 4 : 1;   // the block index jj must be a constant: it selects registers
 #pragma unroll HS_UNROLL
             for (int hs = 0; hs < ST_PER_BG; ++hs, ++it) {   // the stages of the block-group: blocks SB*hs .. SB*hs + SB-1
                 const int slot = it % PF_STAGES;
