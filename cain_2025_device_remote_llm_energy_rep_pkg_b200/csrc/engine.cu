@@ -946,7 +946,8 @@ extern "C" int b2_session_create(b2_model *m, int max_ctx, b2_session **out) {
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_attn, (uint64_t)PF_MAX_TOKENS * qd * 4))) break;
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_h, (uint64_t)PF_MAX_TOKENS * I * 4))) break;
             if ((rc = dev_alloc(s->allocs, &s->pf_pb, pb_bytes(PF_MAX_TOKENS, widest)))) break;
-            s->pf_part_floats = (uint64_t)8 * PF_MAX_TOKENS * std::max<int64_t>(H, qd + 2 * kvd);
+            // split-K partial sums: up to 8 pieces of the H- or QKV-wide outputs, up to 3 of the gate/up pairs (prefill.cu: launch_prefill_gemm_qt)
+            s->pf_part_floats = (uint64_t)PF_MAX_TOKENS * std::max<int64_t>(8 * std::max<int64_t>(H, qd + 2 * kvd), 3 * 2 * (int64_t)I);
             if ((rc = dev_alloc(s->allocs, (void **)&s->pf_part, s->pf_part_floats * 4))) break;
         }
     } while (0);
@@ -1112,7 +1113,7 @@ static int prefill_batched(b2_session *s, int n) {
             else
             B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.o.type), PF_OUT_RES, ly.o.packed, H, qd, s->pf_pb, mb, T, s->pf_x, H, s->pf_x, 0, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_quant(PF_IN_NORM, s->pf_x, H, mb, T, H, ly.ffn_norm, c.rms_eps, c.norm_plus_one, s->pf_pb, st));
-            B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.gateup.type), PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, nullptr, 0, st));
+            B2_CUDA(launch_prefill_gemm_qt(qt_of(ly.gateup.type), PF_OUT_ACTMUL, ly.gateup.packed, 2 * (int64_t)I, H, s->pf_pb, mb, T, s->pf_h, I, nullptr, c.act, sms, s->pf_part, s->pf_part_floats, st));
             B2_CUDA(launch_prefill_quant(PF_IN_F32, s->pf_h, I, mb, T, I, nullptr, 0.f, 0, s->pf_pb, st));
             if (tpn > 1) B2_TRY(row_parallel(ly.down, I, 1, 2 * l + 1, mb, T));
             else

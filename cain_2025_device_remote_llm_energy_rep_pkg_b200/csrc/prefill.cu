@@ -540,6 +540,19 @@ __global__ void __launch_bounds__(256) k_prefill_finish(const float *__restrict_
     else if (bias_or_res) v += bias_or_res[row];
     y[(int64_t)m * ldy + row] = v;
 }
+// the same for the gate/up GEMM: rows (2j, 2j+1) = (gate_j, up_j), y[m][j] = act(gate) * up
+__global__ void __launch_bounds__(256) k_prefill_finish_actmul(const float *__restrict__ part, int ksplit, int T, int M, int rows, float *__restrict__ y,
+                                                               int64_t ldy, int act) {
+    const int j = blockIdx.x * 256 + threadIdx.x, m = blockIdx.y;
+    if (2 * j + 1 >= rows || m >= M) return;
+    float g = 0.f, u = 0.f;
+    for (int s = 0; s < ksplit; ++s) {
+        const float2 gu = *(const float2 *)(part + ((int64_t)s * T + m) * rows + 2 * j);
+        g += gu.x;
+        u += gu.y;
+    }
+    y[(int64_t)m * ldy + j] = act_fn(g, act) * u;
+}
 
 template <int T, int OUT, int QT>
 static cudaError_t launch_pf_qt(const PfArgs &a, int grid, cudaStream_t st) {
@@ -575,15 +588,21 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
     a.w = (const uint8_t *)d_packed; a.rows = (int)rows; a.nbp = (int)nblocks_padded(cols); a.n_tiles = (int)ntiles(rows);
     a.pb = (const uint8_t *)pb; a.M = M; a.y = y; a.ldy = ldy; a.bias_or_res = bias_or_res; a.act = act;
     const int n_groups = (a.n_tiles + 7) / 8;
-    // matrices with few row groups (O, down, QKV) leave most SMs idle: cut K so that there are about as many work items as SMs
+    // Work items are dealt round robin to one CTA per SM, so a launch takes ceil(items / SMs) item times.  Matrices with few row groups
+    // (O, down, QKV) would leave most SMs idle, and 224 row groups (llama3.1:8b gate/up) on 148 SMs take two rounds for 1.5 rounds of
+    // work: K is cut into the smallest number of pieces that brings the launch within 5 % of the best reachable (224 groups: 3 pieces,
+    // 672 items = 5 rounds of a third).  The pieces' raw sums go to `part` and a second kernel adds them in a fixed order.
     int ksplit = 1;
-    if (part && out_mode != PF_OUT_ACTMUL && n_groups * 2 <= sm_count) {
-        ksplit = sm_count / n_groups;
+    if (part && (out_mode != PF_OUT_ACTMUL || (rows & 1) == 0)) {
         const int nbg = a.nbp >> 2;
-        if (ksplit > nbg / 8) ksplit = nbg / 8;   // at least 8 block-groups (16 stages) per item
-        if (ksplit > 8) ksplit = 8;
-        while (ksplit > 1 && (uint64_t)ksplit * T * rows > part_floats) --ksplit;
-        if (ksplit < 1) ksplit = 1;
+        int kmax = nbg / 8 < 8 ? nbg / 8 : 8;   // at least 8 block-groups per item
+        const uint64_t per_piece = (uint64_t)T * rows;
+        if (per_piece * (uint64_t)kmax > part_floats) kmax = (int)(part_floats / per_piece);
+        double best = (double)((n_groups + sm_count - 1) / sm_count);
+        for (int ks = 2; ks <= kmax; ++ks) {
+            const double t = (double)((n_groups * ks + sm_count - 1) / sm_count) / ks;
+            if (t < 0.95 * best) { best = t; ksplit = ks; }
+        }
     }
     a.ksplit = ksplit; a.part = part; a.force_part = partials_only ? 1 : 0;
     if (ksplit_out) *ksplit_out = ksplit;
@@ -597,7 +616,8 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
     PF_CASE(128, PF_OUT_BIAS); PF_CASE(128, PF_OUT_RES); PF_CASE(128, PF_OUT_ACTMUL);
 #undef PF_CASE
     if (e != cudaSuccess || ksplit == 1 || partials_only) return e;
-    k_prefill_finish<<<dim3((unsigned)((rows + 255) / 256), M), 256, 0, st>>>(part, ksplit, T, M, (int)rows, y, ldy, bias_or_res, out_mode);
+    if (out_mode == PF_OUT_ACTMUL) k_prefill_finish_actmul<<<dim3((unsigned)((rows / 2 + 255) / 256), M), 256, 0, st>>>(part, ksplit, T, M, (int)rows, y, ldy, act);
+    else k_prefill_finish<<<dim3((unsigned)((rows + 255) / 256), M), 256, 0, st>>>(part, ksplit, T, M, (int)rows, y, ldy, bias_or_res, out_mode);
     return cudaGetLastError();
 }
 
