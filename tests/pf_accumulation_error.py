@@ -2,8 +2,8 @@
 """Development aid: error of the prompt GEMM against a float64 product on the activation grid, as a multiple of sum |w||x|
 (the unit of the tolerances in tests/test_prefill_gpu.py: 6e-6 against the oracle, 2e-6 against the decode GEMV).
 Run it with B2_LIB pointing at an experimental build to compare accumulation schemes:
-    python tools/pf_err.py ; B2_LIB=$PWD/tools/bin/lib_x.so python tools/pf_err.py
-Uses oracle/ as the checker (test infrastructure), like the tests it mirrors."""
+    python tests/pf_accumulation_error.py ; B2_LIB=$PWD/tools/bin/lib_x.so python tests/pf_accumulation_error.py
+Not collected by pytest (a measurement, no assertions); it lives under tests/ because it uses oracle/ as the checker, like the tests it mirrors."""
 import os
 import sys
 
@@ -11,7 +11,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # test_ops_gpu helpers
 
 from oracle import quants as Q   # noqa: E402
 from test_ops_gpu import pack, ref_gemv   # noqa: E402
