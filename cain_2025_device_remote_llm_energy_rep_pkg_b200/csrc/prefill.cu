@@ -574,6 +574,20 @@ static cudaError_t launch_pf(const PfArgs &a, int qt, int grid, cudaStream_t st)
     return qt == 2 ? launch_pf_qt<T, OUT, 2>(a, grid, st) : qt ? launch_pf_qt<T, OUT, 1>(a, grid, st) : launch_pf_qt<T, OUT, 0>(a, grid, st);
 }
 
+// number of K pieces for n_groups row groups on sm_count CTAs: the smallest count whose launch time, ceil(groups * pieces / CTAs) / pieces
+// item times, is within 5 % of the best reachable with at most kmax pieces
+int pf_pick_ksplit(int n_groups, int sm_count, int kmax) {
+    int ksplit = 1;
+    if (n_groups <= 0 || sm_count <= 0) return 1;
+    double best = (double)((n_groups + sm_count - 1) / sm_count);
+    for (int ks = 2; ks <= kmax; ++ks) {
+        const double t = (double)(((int64_t)n_groups * ks + sm_count - 1) / sm_count) / ks;
+        if (t < 0.95 * best) { best = t; ksplit = ks; }
+    }
+    return ksplit;
+}
+extern "C" int b2dbg_pf_ksplit(int n_groups, int sm_count, int kmax) { return pf_pick_ksplit(n_groups, sm_count, kmax); }   // host logic, tested on CPU
+
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
                                 const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st) {
     return launch_prefill_gemm_qt(0, out_mode, d_packed, rows, cols, pb, M, T, y, ldy, bias_or_res, act, sm_count, part, part_floats, st);
@@ -598,11 +612,7 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
         int kmax = nbg / 8 < 8 ? nbg / 8 : 8;   // at least 8 block-groups per item
         const uint64_t per_piece = (uint64_t)T * rows;
         if (per_piece * (uint64_t)kmax > part_floats) kmax = (int)(part_floats / per_piece);
-        double best = (double)((n_groups + sm_count - 1) / sm_count);
-        for (int ks = 2; ks <= kmax; ++ks) {
-            const double t = (double)((n_groups * ks + sm_count - 1) / sm_count) / ks;
-            if (t < 0.95 * best) { best = t; ksplit = ks; }
-        }
+        ksplit = pf_pick_ksplit(n_groups, sm_count, kmax);
     }
     a.ksplit = ksplit; a.part = part; a.force_part = partials_only ? 1 : 0;
     if (ksplit_out) *ksplit_out = ksplit;

@@ -52,6 +52,7 @@ cudaError_t launch_prefill_gemm_qt(int qt, int out_mode, const void *d_packed, i
                                    bool partials_only = false, int *ksplit_out = nullptr);
 cudaError_t launch_prefill_gemm(int out_mode, const void *d_packed, int64_t rows, int64_t cols, const void *pb, int M, int T, float *y, int64_t ldy,
                                 const float *bias_or_res, int act, int sm_count, float *part, uint64_t part_floats, cudaStream_t st);
+int pf_pick_ksplit(int n_groups, int sm_count, int kmax);
 void launch_prefill_embed(int qt, const void *d_packed, int64_t cols, const int *d_tokens, int M, float scale, float *d_x, cudaStream_t st);
 // RoPE (q in place) + KV append of M tokens at pos0.., then causal attention over the cache; out[m][nh*hd] fp32
 cudaError_t launch_prefill_attention(float *d_qkv, int64_t ld, int M, int nh, int nkv, int hd, int pos0, const float *d_cos, const float *d_sin,

@@ -84,3 +84,25 @@ def test_product_and_oracle_arch_tables_agree():
             assert dataclasses.asdict(table[k]) == dataclasses.asdict(otable[k]), k
             assert archs.tensor_table(table[k]) == oarchs.tensor_table(otable[k])
     assert set(archs.ARCHS) == {"llama3.1:8b", "gemma:2b", "gemma:7b", "phi3:3.8b", "qwen2:1.5b", "qwen2:7b", "mistral:7b"}
+
+
+def test_prompt_gemm_k_split_against_wave_quantisation(lib):
+    """Host logic of csrc/prefill.cu (launch_prefill_gemm_qt): work items are dealt round robin to one CTA per SM, so a launch takes
+    ceil(groups * pieces / SMs) / pieces item times; the chooser takes the smallest number of K pieces within 5 % of the best."""
+    import math
+    f = lib.b2dbg_pf_ksplit
+    f.argtypes, f.restype = [ctypes.c_int] * 3, ctypes.c_int
+    assert f(224, 148, 4) == 3      # llama3.1:8b gate/up: two rounds for 1.5 rounds of work -> five rounds of a third
+    assert f(296, 148, 4) == 1      # qwen2:7b gate/up: exactly two rounds
+    assert f(32, 148, 4) == 4       # O / down projection: 128 items on 148 SMs
+    assert f(32, 148, 8) == 4       # more pieces would not shorten the launch
+    assert f(48, 148, 4) == 3       # QKV: 144 items
+    assert f(384, 148, 3) == 3      # gemma:7b gate/up
+    assert f(5, 148, 1) == 1 and f(0, 148, 8) == 1 and f(10, 0, 8) == 1
+    for groups in (1, 7, 16, 96, 148, 149, 224, 500):
+        for kmax in (1, 2, 4, 8):
+            ks = f(groups, 148, kmax)
+            assert 1 <= ks <= kmax
+            t = lambda k: math.ceil(groups * k / 148) / k
+            assert t(ks) <= t(1) + 1e-12
+            assert t(ks) <= min(t(k) for k in range(1, kmax + 1)) / 0.95 / 0.95 + 1e-12   # within the tolerance of the greedy scan
