@@ -759,15 +759,17 @@ __global__ void __launch_bounds__(128) k_prefill_attn(const float *__restrict__ 
 // once for the 16 queries (the one-CTA-per-query kernel above re-reads the cache for every query: 2 000-token prompts spent half
 // their time there).  Thread (query qi = tid / 8, lane l8 = tid % 8) owns DPL = hd / 8 head dimensions: partial dot products over
 // its dimensions for the 16 keys, three shuffles per key to complete them, online softmax (running maximum and sum per query),
-// and the weighted values of its own dimensions.  fp32 throughout, f16 K / V as stored.
-template <int DPL>
-__global__ void __launch_bounds__(128) k_prefill_attn_tiled(const float *__restrict__ qkv, int64_t ld, int nh, int nkv, int M, int pos0,
+// and the weighted values of its own dimensions.  fp32 throughout, f16 K / V as stored.  Head dim 256 (gemma) runs LPQ = 16 lanes per
+// query (256 threads, four shuffles), which keeps DPL = 16 dimensions per thread: with 8 lanes and 32 dimensions per thread the kernel
+// sat at 128 registers and lost to the one-CTA-per-query kernel.
+template <int DPL, int LPQ>
+__global__ void __launch_bounds__(16 * LPQ) k_prefill_attn_tiled(const float *__restrict__ qkv, int64_t ld, int nh, int nkv, int M, int pos0,
                                                             const __half *__restrict__ kc, const __half *__restrict__ vc,
                                                             const int32_t *__restrict__ page_table, float *__restrict__ out, int64_t ldo) {
-    constexpr int HD = DPL * 8;
+    constexpr int HD = DPL * LPQ, NT = 16 * LPQ;
     __shared__ __align__(16) __half sk[PAGE_TOKENS * HD], sv[PAGE_TOKENS * HD];
     const int h = blockIdx.x, qb = blockIdx.y, kvh = h / (nh / nkv);
-    const int tid = threadIdx.x, qi = tid >> 3, l8 = tid & 7;
+    const int tid = threadIdx.x, qi = tid / LPQ, l8 = tid % LPQ;
     const int m = qb * 16 + qi;                       // query token of this thread (may be >= M in the last block)
     const int qpos = pos0 + min(m, M - 1);
     const float scale = 1.0f / sqrtf((float)HD);
@@ -782,14 +784,13 @@ __global__ void __launch_bounds__(128) k_prefill_attn_tiled(const float *__restr
     const int n_pages = last_pos / PAGE_TOKENS + 1;
     // the next page travels L2 -> registers while the current one is worked on (a CTA walks its pages one after the other; without
     // this every page costs an exposed L2 round trip)
-    constexpr int NV = PAGE_TOKENS * HD / 8 / 128;                  // uint4 per thread and matrix: 1.5 -> hd 96 handled by the bound check
-    constexpr int NVU = (PAGE_TOKENS * HD / 8 + 127) / 128;
+    constexpr int NVU = (PAGE_TOKENS * HD / 8 + NT - 1) / NT;       // uint4 per thread and matrix (hd 96: 1.5 -> 2 with a bound check)
     uint4 rk[NVU], rv[NVU];
     auto fetch = [&](int p) {
         const size_t base = ((size_t)page_table[p] * nkv + kvh) * PAGE_TOKENS * HD;
 #pragma unroll
         for (int u = 0; u < NVU; ++u) {
-            const int i = tid + u * 128;
+            const int i = tid + u * NT;
             rk[u] = rv[u] = make_uint4(0u, 0u, 0u, 0u);
             if (i < PAGE_TOKENS * HD / 8) {
                 rk[u] = ((const uint4 *)(kc + base))[i];
@@ -797,13 +798,12 @@ __global__ void __launch_bounds__(128) k_prefill_attn_tiled(const float *__restr
             }
         }
     };
-    (void)NV;
     fetch(0);
     for (int p = 0; p < n_pages; ++p) {
         __syncthreads();                                           // the previous page is consumed
 #pragma unroll
         for (int u = 0; u < NVU; ++u) {
-            const int i = tid + u * 128;
+            const int i = tid + u * NT;
             if (i < PAGE_TOKENS * HD / 8) { ((uint4 *)sk)[i] = rk[u]; ((uint4 *)sv)[i] = rv[u]; }
         }
         if (p + 1 < n_pages) fetch(p + 1);
@@ -821,6 +821,7 @@ __global__ void __launch_bounds__(128) k_prefill_attn_tiled(const float *__restr
             dot += __shfl_xor_sync(0xffffffffu, dot, 1);
             dot += __shfl_xor_sync(0xffffffffu, dot, 2);
             dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+            if (LPQ == 16) dot += __shfl_xor_sync(0xffffffffu, dot, 8);
             sc[k] = (p * PAGE_TOKENS + k <= qpos) ? dot : -INFINITY;   // causal mask (and slots not written yet)
         }
         float pm = mx;
@@ -855,11 +856,14 @@ cudaError_t launch_prefill_attention(float *d_qkv, int64_t ld, int M, int nh, in
     k_prefill_rope_kv<<<dim3(nh + 2 * nkv, M), 128, 0, st>>>(d_qkv, ld, nh, nkv, hd, pos0, d_cos, d_sin, d_k, d_v, d_page_table);
     const dim3 grid(nh, (M + 15) / 16);
     // short contexts: one CTA per query has 16x the CTAs and wins (32-token prompt 9.2 vs 9.6 ms); long ones: the tiled kernel reads
-    // the cache once per 16 queries (2 000-token prompt, llama3.1:8b: 763 -> 517 ms).  hd 256 (gemma) stays on the per-query kernel:
-    // at 128 registers the tiled one measured slower (716 vs 615 ms).
+    // the cache once per 16 queries (2 000-token prompt, llama3.1:8b: 763 -> 517 ms).  hd 256 (gemma): 16 lanes per query; with 8 lanes
+    // (32 dimensions per thread, 128 registers) the tiled kernel measured slower than one CTA per query (716 vs 615 ms).
+    static int tiled256 = -1;   // B2_PF_ATTN_TILED256=0: head dim 256 back on the per-query kernel
+    if (tiled256 < 0) { const char *e = getenv("B2_PF_ATTN_TILED256"); tiled256 = (e && e[0] == '0') ? 0 : 1; }
     const bool tiled = pos0 + M > 256;
-    if (tiled && hd == 128) k_prefill_attn_tiled<16><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
-    else if (tiled && hd == 96) k_prefill_attn_tiled<12><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
+    if (tiled && hd == 128) k_prefill_attn_tiled<16, 8><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
+    else if (tiled && hd == 96) k_prefill_attn_tiled<12, 8><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
+    else if (tiled && hd == 256 && tiled256) k_prefill_attn_tiled<16, 16><<<grid, 256, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
     else {   // one CTA per query
         const size_t smem = (size_t)(hd + pos0 + M) * sizeof(float);
         if (smem > 48 * 1024) {
