@@ -190,8 +190,8 @@ def test_decode_with_repeat_penalty_follows_the_sampler_contract(pk, gpu_engine)
 
 @pytest.mark.parametrize("key", ["llama3.1:8b", "phi3:3.8b", "gemma:7b"])
 def test_long_prompt_batches_match_oracle_and_token_by_token(pk, gpu_engine, key):
-    """A 330-token prompt: six batches through the tcgen05 GEMM, the causal prompt attention over the growing cache (tiled kernel
-    for head dims 128 / 96 once the context passes 256, one CTA per query for head dim 256), against the CPU ORACLE (last-token
+    """A 330-token prompt: three batches (128 + 128 + 74 tokens) through the tcgen05 GEMM, the causal prompt attention over the growing
+    cache (one CTA per query up to 256 positions, then the tiled kernel: head dims 128 / 96 / 256), against the CPU ORACLE (last-token
     logits within 2e-4 of the logit scale, 24 greedy tokens identical) and against the decode kernels fed token by token."""
     archs, engine = pk
     a = archs.TINY[key]
