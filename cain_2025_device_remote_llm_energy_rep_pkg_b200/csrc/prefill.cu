@@ -861,7 +861,12 @@ cudaError_t launch_prefill_attention(float *d_qkv, int64_t ld, int M, int nh, in
     static int tiled256 = -1;   // B2_PF_ATTN_TILED256=0: head dim 256 back on the per-query kernel
     if (tiled256 < 0) { const char *e = getenv("B2_PF_ATTN_TILED256"); tiled256 = (e && e[0] == '0') ? 0 : 1; }
     const bool tiled = pos0 + M > 256;
-    if (tiled && hd == 128) k_prefill_attn_tiled<16, 8><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
+    // head dim 128 with 16 lanes per query as well (8 dimensions per thread, twice the threads per CTA): llama3.1:8b 2 000-token prompt
+    // 271 -> 261 ms, 512 tokens 53.6 -> 53.0; B2_PF_ATTN_LPQ16=0: 8 lanes
+    static int lpq16 = -1;
+    if (lpq16 < 0) { const char *e = getenv("B2_PF_ATTN_LPQ16"); lpq16 = (e && e[0] == '0') ? 0 : 1; }
+    if (tiled && hd == 128 && lpq16) k_prefill_attn_tiled<8, 16><<<grid, 256, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
+    else if (tiled && hd == 128) k_prefill_attn_tiled<16, 8><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
     else if (tiled && hd == 96) k_prefill_attn_tiled<12, 8><<<grid, 128, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
     else if (tiled && hd == 256 && tiled256) k_prefill_attn_tiled<16, 16><<<grid, 256, 0, st>>>(d_qkv, ld, nh, nkv, M, pos0, d_k, d_v, d_page_table, d_out, ldo);
     else {   // one CTA per query
